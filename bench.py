@@ -1,0 +1,317 @@
+#!/usr/bin/env python
+"""bench.py — throughput of the batched GP log-likelihood hot path on B200 (BASELINE.json).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg2]
+
+A "step" is one pass of the hot path (fused factorisation + log-likelihood) over one batch of
+synthetic irregularly-sampled series.  Workloads (BASELINE.json `configs`):
+    cfg2  65,536 series x N=2,000, one SHO term (J=2), log_likelihood      <- default, the metric's config
+    cfg5  per-GPU slice of 10^6 series x N=1,000, two SHO terms (J=4)
+metric = point-terms/s = B*N*J / device time, whole job over all ranks (weak scaling: every rank
+sweeps its own batch of the named size; no data-path collective).
+
+Keys beyond the base contract:
+    roofline      algorithmic HBM bytes (24 B/point in, 32 B/series out) / CUDA-event time of the
+                  kernel, against MEASURED_PEAKS.json
+    cpu_baseline  the UNMODIFIED reference (oracle/_ref) timed on this box's host cores on a
+                  bounded sample of the same workload
+    e2e           same metric through the C ABI with HOST (pinned) buffers: H2D of every input
+                  and D2H of every result inside the timed region
+`--impl reference` times the reference's own CPU implementation (all host threads, one series
+per task) on a bounded sample of the same config.
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (B per GPU, N, Jr, Jc)
+    "cfg2": dict(B=65536, N=2000, Jr=0, Jc=1, desc="cfg2: 65,536 series x N=2,000, one SHOTerm (J=2), log_likelihood"),
+    "cfg5": dict(B=125000, N=1000, Jr=0, Jc=2, desc="cfg5: 10^6 series x N=1,000 over 8 GPUs (125,000 per GPU), two SHOTerms (J=4), log_likelihood"),
+}
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md: 6.65 TB/s)"
+
+
+def ncu_traffic(workload):
+    """dram bytes per launch of the dominant kernel from the committed ncu summary, if any."""
+    p = os.path.join(ROOT, "profiles", "ncu_summary.json")
+    try:
+        return json.load(open(p))[workload]["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
+def run_reference(args, wl):
+    """--impl reference: the reference's CPU solver on all host threads, bounded sample."""
+    rank = env_int("RANK", 0)
+    if rank != 0:
+        return 0
+    import oracle
+    from celerite_b200 import synth
+    chk = oracle.best()
+    cores = os.cpu_count() or 1
+    N, Jr, Jc = wl["N"], wl["Jr"], wl["Jc"]
+    J = Jr + 2 * Jc
+    # about 0.1 us per point-term per core: size each step to roughly 1 s of wall time
+    sample = int(min(wl["B"], max(256, cores * int(1.0e7 / (N * J)))))
+    b = synth.make_batch(sample, N, Jr, Jc, seed=42)
+    P = b["coeffs"].shape[1]
+    call = lambda: chk.batched_loglik(sample, N, N, Jr, Jc, b["coeffs"], P, b["t"], b["diag"], b["y"],  # noqa: E731
+                                      nthreads=cores)
+    for _ in range(args.warmup):
+        call()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        out = call()
+    dt = (time.perf_counter() - t0) / args.steps
+    assert np.all(out[:, 2] == 0)
+    value = sample * N * J / dt
+    line = {
+        "impl": "reference", "metric": "GP log-likelihood point-terms/sec (N*J*batch / time)", "value": value,
+        "unit": "point-terms/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": wl["desc"], "sample": "%d of %d series per step" % (sample, wl["B"])},
+        "cpu_baseline": {"value": value, "unit": "point-terms/s", "cores": cores, "kind": chk.kind,
+                         "sample": "%d series x N=%d per step, %d threads, one series per task" % (sample, N, cores)},
+        "e2e": {"value": value, "unit": "point-terms/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0, help="override series per GPU (debug)")
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    wl = dict(WORKLOADS[args.workload])
+    if args.batch:
+        wl["B"] = args.batch
+        wl["desc"] += " [batch overridden to %d]" % args.batch
+
+    if args.impl == "reference":
+        return run_reference(args, wl)
+
+    import torch
+    import torch.distributed as dist
+    from celerite_b200 import synth
+    from celerite_b200.batched import BatchedSolver
+    from celerite_b200 import _capi
+
+    rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (celerite_b200 has no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    B, N, Jr, Jc = wl["B"], wl["N"], wl["Jr"], wl["Jc"]
+    J, P = Jr + 2 * Jc, 1 + 2 * Jr + 4 * Jc
+
+    # ---- synthetic inputs: generated straight into pinned host buffers, then copied to HBM ----
+    ht = torch.empty((B, N), dtype=torch.float64).pin_memory()
+    hd = torch.empty((B, N), dtype=torch.float64).pin_memory()
+    hy = torch.empty((B, N), dtype=torch.float64).pin_memory()
+    rng = np.random.Generator(np.random.PCG64(42 + rank))
+    coeffs_np = synth.make_coeffs(rng, B, Jr, Jc)
+    synth.fill_series(rng, ht.numpy(), hd.numpy(), hy.numpy())
+    hc = torch.from_numpy(coeffs_np).pin_memory()
+    h_out = torch.empty((3, B), dtype=torch.float64).pin_memory()
+    h_status = torch.empty(B, dtype=torch.int32).pin_memory()
+    dt_, dd_, dy_, dc_ = ht.to(dev), hd.to(dev), hy.to(dev), hc.to(dev)
+    d_out = torch.empty((3, B), dtype=torch.float64, device=dev)
+    d_status = torch.empty(B, dtype=torch.int32, device=dev)
+
+    bs = BatchedSolver(local)
+    stream = torch.cuda.current_stream(dev)
+
+    def step_device():
+        bs.raw_log_likelihood(B, N, N, Jr, Jc, dc_.data_ptr(), P, dt_.data_ptr(), dd_.data_ptr(), dy_.data_ptr(),
+                              d_out[0].data_ptr(), d_out[1].data_ptr(), d_out[2].data_ptr(), d_status.data_ptr(),
+                              flags=0, stream=stream.cuda_stream)
+
+    def step_host():
+        bs.raw_log_likelihood(B, N, N, Jr, Jc, hc.data_ptr(), P, ht.data_ptr(), hd.data_ptr(), hy.data_ptr(),
+                              h_out[0].data_ptr(), h_out[1].data_ptr(), h_out[2].data_ptr(), h_status.data_ptr(),
+                              flags=_capi.HOST_POINTERS, stream=stream.cuda_stream)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            tms = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+            ms = float(tms.item())
+        return ms / steps
+
+    # ---- device-resident metric -------------------------------------------------------------
+    for _ in range(args.warmup):
+        step_device()
+    torch.cuda.synchronize(dev)
+    assert int(d_status.sum().item()) == 0, "a synthetic series failed to factorise"
+    launches0 = bs.launch_count()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms_step = timed(step_device, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    launches = bs.launch_count() - launches0
+    value = world * B * N * J / (ms_step * 1e-3)
+
+    # ---- end-to-end through the C ABI with host buffers -------------------------------------
+    step_host()  # warm-up (allocates the staging buffers)
+    e2e_ms = timed(step_host, max(1, args.e2e_steps))
+    e2e_value = world * B * N * J / (e2e_ms * 1e-3)
+    # the e2e path must give the same answer as the device-resident path
+    torch.cuda.synchronize(dev)
+    same = bool(torch.equal(h_out.to(dev), d_out))
+
+    if rank == 0:
+        peak, peak_src = measured_peak_gbs()
+        alg_bytes = B * N * 24 + B * 28          # t, diag, y in; logdet, quad, ll, status out
+        achieved = alg_bytes / (ms_step * 1e-3) / 1e9
+        line = {
+            "metric": "GP log-likelihood point-terms/sec (N*J*batch / device time)",
+            "value": value, "unit": "point-terms/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": wl["desc"], "series_per_gpu": B, "N": N, "J": J,
+                       "inputs": "%.2f GB per step per GPU, larger than the 126 MB L2 (no flush needed)"
+                                 % (3 * B * N * 8 / 1e9),
+                       "sharding": "batch index, no data-path collective"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": ncu_traffic(args.workload), "peak_source": peak_src,
+                         "kernel": "k_loglik_lockstep" if J <= 6 else "k_factor_coop",
+                         "algorithmic_bytes_per_launch": alg_bytes},
+            "e2e": {"value": e2e_value, "unit": "point-terms/s", "ms_per_step": e2e_ms,
+                    "h2d_bytes_per_step": 3 * B * N * 8 + B * P * 8, "d2h_bytes_per_step": B * 28,
+                    "matches_device_path": same},
+            "gpu_launches": launches,
+            "clocks": clocks,
+        }
+        if not args.no_cpu_baseline:
+            import oracle
+            chk = oracle.best()
+            cores = os.cpu_count() or 1
+            sample = int(min(B, max(256, cores * 1024)))
+            call = lambda: chk.batched_loglik(sample, N, N, Jr, Jc, coeffs_np[:sample], P,  # noqa: E731
+                                              ht.numpy()[:sample], hd.numpy()[:sample], hy.numpy()[:sample],
+                                              nthreads=cores)
+            call()
+            t0 = time.perf_counter()
+            reps = 3
+            for _ in range(reps):
+                ref = call()
+            cdt = (time.perf_counter() - t0) / reps
+            got = d_out[:, :sample].cpu().numpy()
+            par = float(max(np.max(np.abs(got[0] - ref[:, 0]) / np.abs(ref[:, 0])),
+                            np.max(np.abs(got[1] - ref[:, 1]) / np.abs(ref[:, 1]))))
+            line["cpu_baseline"] = {"value": sample * N * J / cdt, "unit": "point-terms/s", "cores": cores,
+                                    "kind": chk.kind,
+                                    "sample": "first %d of %d series, %d threads, one series per task" % (sample, B, cores),
+                                    "max_rel_diff_vs_gpu": par}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

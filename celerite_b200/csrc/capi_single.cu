@@ -1,0 +1,339 @@
+// C ABI, part 2: the single-series entry points that mirror CholeskySolver<double>
+// (include/celerite_b200.h).  Host pointers in, host pointers out, synchronous.
+#include <cfloat>
+#include <cmath>
+#include <vector>
+
+#include "solver_handle.h"
+
+namespace {
+
+int pack_coeffs(cel_solver* s, double jitter, int Jr, const double* a_real, const double* c_real, int Jc,
+                const double* a_comp, const double* b_comp, const double* c_comp, const double* d_comp,
+                std::vector<double>& row) {
+  if (Jr < 0 || Jc < 0) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "negative term count");
+  if ((Jr > 0 && (!a_real || !c_real)) || (Jc > 0 && (!a_comp || !b_comp || !c_comp || !d_comp)))
+    CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null coefficient array");
+  row.resize(1 + 2 * Jr + 4 * Jc);
+  row[0] = jitter;
+  size_t o = 1;
+  for (int j = 0; j < Jr; ++j) row[o++] = a_real[j];
+  for (int j = 0; j < Jr; ++j) row[o++] = c_real[j];
+  for (int j = 0; j < Jc; ++j) row[o++] = a_comp[j];
+  for (int j = 0; j < Jc; ++j) row[o++] = b_comp[j];
+  for (int j = 0; j < Jc; ++j) row[o++] = c_comp[j];
+  for (int j = 0; j < Jc; ++j) row[o++] = d_comp[j];
+  return CEL_OK;
+}
+
+inline size_t dbytes(size_t n) { return n * sizeof(double); }
+
+}  // namespace
+
+extern "C" {
+
+int cel_computed(const cel_solver* s) { return (s && s->computed) ? 1 : 0; }
+
+int cel_log_determinant(const cel_solver* s, double* out) {
+  if (!s || !out) return CEL_INVALID_ARGUMENT;
+  if (!s->computed) return CEL_NOT_COMPUTED;  // solver.h:74-77
+  *out = s->log_det;
+  return CEL_OK;
+}
+
+int cel_dims(const cel_solver* s, int* N, int* J) {
+  if (!s) return CEL_INVALID_ARGUMENT;
+  if (N) *N = s->N;
+  if (J) *J = s->J;
+  return CEL_OK;
+}
+
+int cel_compute(cel_solver* s, double jitter, int Jr, const double* a_real, const double* c_real, int Jc,
+                const double* a_comp, const double* b_comp, const double* c_comp, const double* d_comp, int Jg,
+                const double* A, const double* U, const double* V, int N, const double* x, const double* diag) {
+  if (!s) return CEL_INVALID_ARGUMENT;
+  s->computed = false;  // cholesky.h:57
+  if (N < 1 || !x || !diag) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "empty series");
+  if (Jg < 0 || (Jg > 0 && (!U || !V))) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "general term needs U and V");
+  std::vector<double> row;
+  int rc = pack_coeffs(s, jitter, Jr, a_real, c_real, Jc, a_comp, b_comp, c_comp, d_comp, row);
+  if (rc != CEL_OK) return rc;
+  const int J = Jr + 2 * Jc + Jg;
+  if (J > cel::kCoopMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "J > 32 is not supported yet");
+  CEL_CUDA_TRY(s, cudaSetDevice(s->device));
+  cudaStream_t st = s->stream;
+
+  const size_t nJ = (size_t)(J > 0 ? J : 1);
+  CEL_CUDA_TRY(s, s->phi.reserve(dbytes(nJ * (size_t)(N > 1 ? N - 1 : 1))));
+  CEL_CUDA_TRY(s, s->u.reserve(dbytes(nJ * (size_t)(N > 1 ? N - 1 : 1))));
+  CEL_CUDA_TRY(s, s->W.reserve(dbytes(nJ * (size_t)N)));
+  CEL_CUDA_TRY(s, s->D.reserve(dbytes(N)));
+  CEL_CUDA_TRY(s, s->t.reserve(dbytes(N)));
+  CEL_CUDA_TRY(s, s->coeffs.reserve(dbytes(row.size())));
+  CEL_CUDA_TRY(s, s->in0.reserve(dbytes(N)));                       // diag
+  CEL_CUDA_TRY(s, s->in1.reserve(dbytes(A ? N : 1)));               // A
+  CEL_CUDA_TRY(s, s->in2.reserve(dbytes((size_t)(Jg > 0 ? Jg : 1) * N)));  // U
+  CEL_CUDA_TRY(s, s->in3.reserve(dbytes((size_t)(Jg > 0 ? Jg : 1) * N)));  // V
+  CEL_CUDA_TRY(s, s->out0.reserve(64));
+
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(s->t.p, x, dbytes(N), cudaMemcpyHostToDevice, st));
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(s->in0.p, diag, dbytes(N), cudaMemcpyHostToDevice, st));
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(s->coeffs.p, row.data(), dbytes(row.size()), cudaMemcpyHostToDevice, st));
+  if (A) CEL_CUDA_TRY(s, cudaMemcpyAsync(s->in1.p, A, dbytes(N), cudaMemcpyHostToDevice, st));  // cholesky.h:65,99
+  if (Jg > 0) {
+    CEL_CUDA_TRY(s, cudaMemcpyAsync(s->in2.p, U, dbytes((size_t)Jg * N), cudaMemcpyHostToDevice, st));
+    CEL_CUDA_TRY(s, cudaMemcpyAsync(s->in3.p, V, dbytes((size_t)Jg * N), cudaMemcpyHostToDevice, st));
+  }
+
+  double* res = static_cast<double*>(s->pinned);  // [logdet, status(int), fail(int)]
+  int* ires = reinterpret_cast<int*>(res + 1);
+  if (J == 0) {
+    CEL_CUDA_TRY(s, cel::launch_jitter_only(N, s->in0.d(), jitter, s->D.d(), s->out0.d(), st));
+    s->launches += 1;
+    CEL_CUDA_TRY(s, cudaMemcpyAsync(res, s->out0.p, sizeof(double), cudaMemcpyDeviceToHost, st));
+    CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
+    s->N = N; s->J = 0; s->Jr = s->Jc = s->Jg = 0;
+    s->log_det = res[0];
+    s->computed = true;
+    return CEL_OK;
+  }
+
+  cel::BatchArgs a{};
+  a.B = 1; a.N = N; a.stride = N; a.Jr = Jr; a.Jc = Jc; a.Jg = Jg;
+  a.coeffs = s->coeffs.d(); a.coeff_stride = (long long)row.size();
+  a.t = s->t.d(); a.diag = s->in0.d(); a.y = nullptr;
+  a.A = A ? s->in1.d() : nullptr;
+  a.U = Jg > 0 ? s->in2.d() : nullptr;
+  a.V = Jg > 0 ? s->in3.d() : nullptr;
+  a.out_logdet = s->out0.d();
+  a.status = reinterpret_cast<int*>(s->out0.d() + 1);
+  a.fail_index = a.status + 1;
+  a.phi = s->phi.d(); a.u = s->u.d(); a.W = s->W.d(); a.D = s->D.d();
+  CEL_CUDA_TRY(s, cel::launch_loglik_coop(a, st));
+  s->launches += 1;
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(res, s->out0.p, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
+  CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
+  s->N = N; s->J = J; s->Jr = Jr; s->Jc = Jc; s->Jg = Jg;
+  if (ires[0] != 0) {
+    char buf[128];
+    snprintf(buf, sizeof(buf), "failed to factorize or solve matrix (D_n < 0 at n = %d)", ires[1] - 1);
+    CEL_FAIL(s, CEL_NOT_POSITIVE_DEFINITE, buf);
+  }
+  s->log_det = res[0];
+  s->computed = true;
+  return CEL_OK;
+}
+
+// ---- helpers for the sweeps -------------------------------------------------------------------
+static int sweep_prepare(cel_solver* s, int N, int nrhs, const double* in, const void* out) {
+  if (!s) return CEL_INVALID_ARGUMENT;
+  if (N != s->N && s->computed) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "dimension mismatch");  // cholesky.h:219
+  if (!s->computed) CEL_FAIL(s, CEL_NOT_COMPUTED, "you must call 'compute' first");          // cholesky.h:220
+  if (nrhs < 0 || !in || !out) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null right-hand side");
+  CEL_CUDA_TRY(s, cudaSetDevice(s->device));
+  CEL_CUDA_TRY(s, s->in0.reserve(dbytes((size_t)N * (nrhs > 0 ? nrhs : 1))));
+  CEL_CUDA_TRY(s, s->out1.reserve(dbytes((size_t)N * (nrhs > 0 ? nrhs : 1))));
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(s->in0.p, in, dbytes((size_t)N * nrhs), cudaMemcpyHostToDevice, s->stream));
+  return CEL_OK;
+}
+
+static cel::SweepArgs sweep_args(cel_solver* s, int nrhs) {
+  cel::SweepArgs a{};
+  a.N = s->N; a.J = s->J; a.nrhs = nrhs;
+  a.phi = s->phi.d(); a.u = s->u.d(); a.W = s->W.d(); a.D = s->D.d();
+  a.in = s->in0.d(); a.out = s->out1.d(); a.scalar_out = nullptr;
+  return a;
+}
+
+int cel_dot_solve(cel_solver* s, int N, const double* b, double* out) {
+  int rc = sweep_prepare(s, N, 1, b, out);
+  if (rc != CEL_OK) return rc;
+  cudaStream_t st = s->stream;
+  CEL_CUDA_TRY(s, s->out0.reserve(64));
+  double* res = static_cast<double*>(s->pinned);
+  // J == 0 (cholesky.h:334-339) runs through the same kernel: no rows, x = b, sum b^2/D
+  cel::SweepArgs a = sweep_args(s, 1);
+  a.out = nullptr;
+  a.scalar_out = s->out0.d();
+  CEL_CUDA_TRY(s, cel::launch_dot_solve(a, st));
+  s->launches += 1;
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(res, s->out0.p, sizeof(double), cudaMemcpyDeviceToHost, st));
+  CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
+  *out = res[0];
+  return CEL_OK;
+}
+
+int cel_solve(cel_solver* s, int N, int nrhs, const double* b, double* out) {
+  int rc = sweep_prepare(s, N, nrhs, b, out);
+  if (rc != CEL_OK) return rc;
+  if (nrhs == 0) return CEL_OK;
+  cudaStream_t st = s->stream;
+  // J == 0 (cholesky.h:226-231) degenerates to out = b / D inside the same kernels
+  CEL_CUDA_TRY(s, cel::launch_solve(sweep_args(s, nrhs), st));
+  s->launches += 2;
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(out, s->out1.p, dbytes((size_t)N * nrhs), cudaMemcpyDeviceToHost, st));
+  CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
+  return CEL_OK;
+}
+
+int cel_dot_L(cel_solver* s, int N, int nrhs, const double* z, double* out) {
+  int rc = sweep_prepare(s, N, nrhs, z, out);
+  if (rc != CEL_OK) return rc;
+  if (nrhs == 0) return CEL_OK;
+  cudaStream_t st = s->stream;
+  CEL_CUDA_TRY(s, cel::launch_dot_L(sweep_args(s, nrhs), st));
+  s->launches += 1;
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(out, s->out1.p, dbytes((size_t)N * nrhs), cudaMemcpyDeviceToHost, st));
+  CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
+  return CEL_OK;
+}
+
+int cel_dot(cel_solver* s, double jitter, int Jr, const double* a_real, const double* c_real, int Jc,
+            const double* a_comp, const double* b_comp, const double* c_comp, const double* d_comp, int Jg,
+            const double* A, const double* U, const double* V, int N, const double* x, int nrhs, const double* z,
+            double* out) {
+  if (!s) return CEL_INVALID_ARGUMENT;
+  if (N < 1 || nrhs < 0 || !x || !z || !out) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "dimension mismatch");
+  if (Jg < 0 || (Jg > 0 && (!U || !V))) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "general term needs U and V");
+  std::vector<double> row;
+  int rc = pack_coeffs(s, jitter, Jr, a_real, c_real, Jc, a_comp, b_comp, c_comp, d_comp, row);
+  if (rc != CEL_OK) return rc;
+  const int J = Jr + 2 * Jc + Jg;
+  if (J > cel::kCoopMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "J > 32 is not supported yet");
+  if (nrhs == 0) return CEL_OK;
+  CEL_CUDA_TRY(s, cudaSetDevice(s->device));
+  cudaStream_t st = s->stream;
+  const size_t nz = (size_t)N * nrhs;
+  // scratch buffers distinct from the stored factor and from compute's inputs
+  CEL_CUDA_TRY(s, s->scratch0.reserve(dbytes(nz)));                         // z
+  CEL_CUDA_TRY(s, s->scratch1.reserve(dbytes(nz)));                         // out
+  CEL_CUDA_TRY(s, s->scratch2.reserve(dbytes((size_t)N * (2 + 2 * (Jg > 0 ? Jg : 0)) + row.size())));
+  double* dx = s->scratch2.d();
+  double* dA = dx + N;
+  double* dU = dA + N;
+  double* dV = dU + (size_t)Jg * N;
+  double* dc = dV + (size_t)Jg * N;
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(s->scratch0.p, z, dbytes(nz), cudaMemcpyHostToDevice, st));
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(dx, x, dbytes(N), cudaMemcpyHostToDevice, st));
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(dc, row.data(), dbytes(row.size()), cudaMemcpyHostToDevice, st));
+  if (A) CEL_CUDA_TRY(s, cudaMemcpyAsync(dA, A, dbytes(N), cudaMemcpyHostToDevice, st));  // cholesky.h:485
+  if (Jg > 0) {
+    CEL_CUDA_TRY(s, cudaMemcpyAsync(dU, U, dbytes((size_t)Jg * N), cudaMemcpyHostToDevice, st));
+    CEL_CUDA_TRY(s, cudaMemcpyAsync(dV, V, dbytes((size_t)Jg * N), cudaMemcpyHostToDevice, st));
+  }
+  if (J == 0) {  // cholesky.h:477-481
+    CEL_CUDA_TRY(s, cel::launch_scale((int)nz, N, s->scratch0.d(), nullptr, jitter, 1, s->scratch1.d(), st));
+  } else {
+    cel::DotArgs a{};
+    a.N = N; a.Jr = Jr; a.Jc = Jc; a.Jg = Jg; a.nrhs = nrhs;
+    a.coeffs = dc; a.A = A ? dA : nullptr; a.U = Jg > 0 ? dU : nullptr; a.V = Jg > 0 ? dV : nullptr;
+    a.x = dx; a.z = s->scratch0.d(); a.out = s->scratch1.d();
+    CEL_CUDA_TRY(s, cel::launch_dot(a, st));
+  }
+  s->launches += 1;
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(out, s->scratch1.p, dbytes(nz), cudaMemcpyDeviceToHost, st));
+  CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
+  return CEL_OK;
+}
+
+// ---- not built yet (declared so the boundary is stable) ---------------------------------------
+int cel_predict(cel_solver* s, int N, const double* y, int M, const double* xs, double* out) {
+  (void)N; (void)y; (void)M; (void)xs; (void)out;
+  if (!s) return CEL_INVALID_ARGUMENT;
+  CEL_FAIL(s, CEL_UNSUPPORTED, "cel_predict is not implemented yet");
+}
+
+int cel_grad_log_likelihood(cel_solver* s, double jitter, int Jr, const double* a_real, const double* c_real,
+                            int Jc, const double* a_comp, const double* b_comp, const double* c_comp,
+                            const double* d_comp, int Jg, const double* A, const double* U, const double* V,
+                            int N, const double* x, const double* y, const double* diag, double* val,
+                            double* grad) {
+  (void)jitter; (void)Jr; (void)a_real; (void)c_real; (void)Jc; (void)a_comp; (void)b_comp; (void)c_comp;
+  (void)d_comp; (void)Jg; (void)A; (void)U; (void)V; (void)N; (void)x; (void)y; (void)diag; (void)val; (void)grad;
+  if (!s) return CEL_INVALID_ARGUMENT;
+  CEL_FAIL(s, CEL_UNSUPPORTED, "cel_grad_log_likelihood is not implemented yet");
+}
+
+int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t stride, int Jr, int Jc,
+                                    const double* coeffs, int64_t coeff_stride, const double* t,
+                                    const double* diag, const double* y, double* out_val, double* out_grad,
+                                    int32_t* status, unsigned flags) {
+  (void)B; (void)N; (void)stride; (void)Jr; (void)Jc; (void)coeffs; (void)coeff_stride; (void)t; (void)diag;
+  (void)y; (void)out_val; (void)out_grad; (void)status; (void)flags;
+  if (!s) return CEL_INVALID_ARGUMENT;
+  CEL_FAIL(s, CEL_UNSUPPORTED, "cel_batched_grad_log_likelihood is not implemented yet");
+}
+
+// ---- state (pickle) ---------------------------------------------------------------------------
+int cel_get_state(cel_solver* s, int* computed, int* N, int* J, double* log_det, double* phi, double* u, double* W,
+                  double* D) {
+  if (!s) return CEL_INVALID_ARGUMENT;
+  if (computed) *computed = s->computed ? 1 : 0;
+  if (N) *N = s->N;
+  if (J) *J = s->J;
+  if (log_det) *log_det = s->log_det;
+  if (!s->computed || s->N == 0) return CEL_OK;
+  CEL_CUDA_TRY(s, cudaSetDevice(s->device));
+  cudaStream_t st = s->stream;
+  const size_t nJ = (size_t)s->J, n = (size_t)s->N;
+  if (phi && nJ && n > 1) CEL_CUDA_TRY(s, cudaMemcpyAsync(phi, s->phi.p, dbytes(nJ * (n - 1)), cudaMemcpyDeviceToHost, st));
+  if (u && nJ && n > 1) CEL_CUDA_TRY(s, cudaMemcpyAsync(u, s->u.p, dbytes(nJ * (n - 1)), cudaMemcpyDeviceToHost, st));
+  if (W && nJ) CEL_CUDA_TRY(s, cudaMemcpyAsync(W, s->W.p, dbytes(nJ * n), cudaMemcpyDeviceToHost, st));
+  if (D) CEL_CUDA_TRY(s, cudaMemcpyAsync(D, s->D.p, dbytes(n), cudaMemcpyDeviceToHost, st));
+  CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
+  return CEL_OK;
+}
+
+int cel_set_state(cel_solver* s, int computed, int N, int J, double log_det, const double* phi, const double* u,
+                  const double* W, const double* D) {
+  if (!s) return CEL_INVALID_ARGUMENT;
+  if (N < 0 || J < 0) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "negative size");
+  if (J > cel::kCoopMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "J > 32 is not supported yet");
+  s->computed = false;
+  s->N = N; s->J = J; s->log_det = log_det;
+  s->Jr = s->Jc = s->Jg = 0;  // coefficients are not part of the pickled state (solver.cpp:36-42)
+  if (computed && N > 0) {
+    if (!D || (J > 0 && (!W || (N > 1 && (!phi || !u))))) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null factor array");
+    CEL_CUDA_TRY(s, cudaSetDevice(s->device));
+    cudaStream_t st = s->stream;
+    const size_t nJ = (size_t)J, n = (size_t)N;
+    CEL_CUDA_TRY(s, s->phi.reserve(dbytes((nJ ? nJ : 1) * (n > 1 ? n - 1 : 1))));
+    CEL_CUDA_TRY(s, s->u.reserve(dbytes((nJ ? nJ : 1) * (n > 1 ? n - 1 : 1))));
+    CEL_CUDA_TRY(s, s->W.reserve(dbytes((nJ ? nJ : 1) * n)));
+    CEL_CUDA_TRY(s, s->D.reserve(dbytes(n)));
+    if (nJ && n > 1) {
+      CEL_CUDA_TRY(s, cudaMemcpyAsync(s->phi.p, phi, dbytes(nJ * (n - 1)), cudaMemcpyHostToDevice, st));
+      CEL_CUDA_TRY(s, cudaMemcpyAsync(s->u.p, u, dbytes(nJ * (n - 1)), cudaMemcpyHostToDevice, st));
+    }
+    if (nJ) CEL_CUDA_TRY(s, cudaMemcpyAsync(s->W.p, W, dbytes(nJ * n), cudaMemcpyHostToDevice, st));
+    CEL_CUDA_TRY(s, cudaMemcpyAsync(s->D.p, D, dbytes(n), cudaMemcpyHostToDevice, st));
+    CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
+  }
+  s->computed = computed != 0;
+  return CEL_OK;
+}
+
+// ---- batched compute (materialising) ----------------------------------------------------------
+int cel_batched_compute(cel_solver* s, int64_t B, int N, int64_t stride, int Jr, int Jc, const double* coeffs,
+                        int64_t coeff_stride, const double* t, const double* diag, double* phi, double* u,
+                        double* W, double* D, double* out_logdet, int32_t* status) {
+  if (!s) return CEL_INVALID_ARGUMENT;
+  if (B < 0 || N < 1 || Jr < 0 || Jc < 0 || stride < 0 || coeff_stride < 0)
+    CEL_FAIL(s, CEL_INVALID_ARGUMENT, "negative size");
+  const int J = Jr + 2 * Jc;
+  if (J < 1 || J > cel::kCoopMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "batched compute supports 1 <= J <= 32");
+  if (!coeffs || !t || !diag || !phi || !u || !W || !D) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null pointer");
+  if (B == 0) return CEL_OK;
+  CEL_CUDA_TRY(s, cudaSetDevice(s->device));
+  cel::BatchArgs a{};
+  a.B = B; a.N = N; a.stride = stride; a.Jr = Jr; a.Jc = Jc; a.Jg = 0;
+  a.coeffs = coeffs; a.coeff_stride = coeff_stride;
+  a.t = t; a.diag = diag; a.y = nullptr;
+  a.out_logdet = out_logdet; a.status = status;
+  a.phi = phi; a.u = u; a.W = W; a.D = D;
+  CEL_CUDA_TRY(s, cel::launch_loglik_coop(a, s->stream));
+  s->launches += 1;
+  return CEL_OK;
+}
+
+}  // extern "C"

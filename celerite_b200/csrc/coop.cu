@@ -1,0 +1,285 @@
+// K1c / K1m — cooperative factorisation sweep: L = pow2ceil(J) lanes per series.
+//
+// Replaces CholeskySolver::compute (cholesky.h:41-210), optionally fused with dot_solve
+// (cholesky.h:326-401) and the log-determinant (cholesky.h:208), for any J <= 32 including the
+// general rank-Jg rows (cholesky.h:148-152).  This is the "one warp per series" mapping of the
+// design: lane k owns ROW k of the symmetric J x J state S (J doubles in registers, full row so
+// that S u needs no cross-lane traffic), W_k, f_k; D_n = A_n - u^T S u and the forward-solve
+// residual are two values reduced together with one butterfly of warp shuffles per step.  The
+// only vector every lane needs from its neighbours is D_{n-1} W_{n-1}: it is exchanged through
+// a double-buffered shared-memory row (one __syncwarp per step).
+//
+// The transcendental part (exp / sincos per term and time step) does not depend on the
+// recursion, so each tile of T steps starts with a generator phase in which all lanes of the
+// group evaluate phi, u, v for the whole tile in parallel into shared memory; the serial phase
+// then only reads broadcast rows.  In the materialising variant those tiles ARE the output
+// (reference layout, J fastest) and are written back with coalesced stores.
+//
+// For J <= 16 a warp carries 32/L series side by side.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace cel {
+namespace {
+
+constexpr double kLog2Pi = 1.8378770664093454836;
+
+constexpr int pow2ceil(int x) { return x <= 1 ? 1 : x <= 2 ? 2 : x <= 4 ? 4 : x <= 8 ? 8 : x <= 16 ? 16 : 32; }
+
+template <int JP, bool STORE>
+struct CoopCfg {
+  static constexpr int L = pow2ceil(JP);
+  static constexpr int G = kWarp / L;               // series per warp
+  static constexpr int T = 16;                      // steps per tile
+  // per-group shared memory, in doubles
+  static constexpr int kIn = 3 * T + 2;             // t (with one leading slot), diag(+A), y
+  static constexpr int kGen = 3 * T * JP;           // phi, u, v tiles
+  static constexpr int kX = 2 * JP;                 // D*W exchange, double buffered
+  static constexpr int kOut = STORE ? T * JP + T : 0;  // W tile, D tile (materialising variant)
+  static constexpr int kCoef = 4 * JP + 2;          // coefficient row (<= 1 + 4*Jc + 2*Jr <= 1 + 2J)
+  static constexpr int kGroup = kIn + kGen + kX + kOut + kCoef;
+  static constexpr size_t smem = (size_t)G * kGroup * sizeof(double);
+};
+
+template <int JP, bool STORE>
+__global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
+  using C = CoopCfg<JP, STORE>;
+  constexpr int L = C::L, G = C::G, T = C::T;
+  extern __shared__ __align__(16) double smem[];
+  const int lane = threadIdx.x, g = lane / L, k = lane % L;
+  const long long b = (long long)blockIdx.x * G + g;
+  const bool active = b < a.B;
+  const long long bb = active ? b : a.B - 1;
+
+  double* base = smem + (size_t)g * C::kGroup;
+  double* t_s = base;                    // [T+1]  t_s[0] = previous time
+  double* d_s = t_s + T + 2;             // [T]    diag + A
+  double* y_s = d_s + T;                 // [T]
+  double* phi_s = y_s + T;               // [T][JP]
+  double* u_s = phi_s + T * JP;
+  double* v_s = u_s + T * JP;
+  double* x_s = v_s + T * JP;            // [2][JP] exchange of D*W
+  double* w_s = x_s + 2 * JP;            // [T][JP] W tile
+  double* dd_s = w_s + T * JP;           // [T]     D tile
+  double* cf_s = x_s + 2 * JP + C::kOut;  // coefficient row (w_s/dd_s exist only when STORE)
+
+  const int N = a.N, Jr = a.Jr, Jc = a.Jc, Jg = a.Jg, J = Jr + 2 * Jc + Jg, P = 1 + 2 * Jr + 4 * Jc;
+  const double* tp = a.t + bb * a.stride;
+  const double* dp = a.diag + bb * a.stride;
+  const double* yp = a.y ? a.y + bb * a.stride : nullptr;
+  const double* Ap = a.A ? a.A + bb * a.stride : nullptr;
+  const double* Up = a.U ? a.U + bb * a.stride * Jg : nullptr;
+  const double* Vp = a.V ? a.V + bb * a.stride * Jg : nullptr;
+
+  // coefficient row -> shared; zero the generator tiles once (padded columns stay zero)
+  {
+    const double* row = a.coeffs + bb * a.coeff_stride;
+    for (int i = k; i < P; i += L) cf_s[i] = row[i];
+    for (int i = k; i < 3 * T * JP; i += L) phi_s[i] = 0.0;
+    for (int i = k; i < 2 * JP; i += L) x_s[i] = 0.0;
+  }
+  __syncwarp();
+  const double jitter = cf_s[0];
+  const double* a_real = cf_s + 1;
+  const double* c_real = a_real + Jr;
+  const double* a_comp = c_real + Jr;
+  const double* b_comp = a_comp + Jc;
+  const double* c_comp = b_comp + Jc;
+  const double* d_comp = c_comp + Jc;
+  double sum_ar = 0.0, sum_ac = 0.0;
+  for (int j = 0; j < Jr; ++j) sum_ar += a_real[j];
+  for (int j = 0; j < Jc; ++j) sum_ac += a_comp[j];
+
+  const bool row_ok = k < JP;            // lanes JP..L-1 (JP not a power of two) carry zeros
+  const int kk = row_ok ? k : JP - 1;
+
+  double S[JP];
+#pragma unroll
+  for (int j = 0; j < JP; ++j) S[j] = 0.0;
+  double dw_own = 0.0, r_prev = 0.0, f_own = 0.0, xprev = 0.0, quad = 0.0;
+  LogAcc ld;
+  ld.init();
+  int fail = 0;
+
+  // register prefetch of the next input tile
+  constexpr int PF = (T + L - 1) / L;
+  double pt[PF], pd[PF], py[PF];
+  auto prefetch = [&](int n0) {
+#pragma unroll
+    for (int q = 0; q < PF; ++q) {
+      const int i = k + q * L;
+      const int n = min(n0 + i, N - 1);
+      pt[q] = __ldg(tp + n);
+      pd[q] = __ldg(dp + n) + (Ap ? __ldg(Ap + n) : 0.0);
+      py[q] = yp ? __ldg(yp + n) : 0.0;
+    }
+  };
+  prefetch(0);
+  double t_last = __ldg(tp);             // time of the step before the tile
+
+  const int ntiles = (N + T - 1) / T;
+  for (int tile = 0; tile < ntiles; ++tile) {
+    const int n0 = tile * T;
+    const int nt = min(T, N - n0);
+    // ---- inputs of this tile -> shared; start fetching the next tile ----------------------
+    if (k == 0) t_s[0] = t_last;
+#pragma unroll
+    for (int q = 0; q < PF; ++q) {
+      const int i = k + q * L;
+      if (i < T) { t_s[1 + i] = pt[q]; d_s[i] = pd[q]; y_s[i] = py[q]; }
+    }
+    __syncwarp();
+    t_last = t_s[nt];
+    if (tile + 1 < ntiles) prefetch(n0 + T);
+
+    // ---- generator phase: phi, u, v for the whole tile (cholesky.h:127-152) ---------------
+    {
+      const int nterm = Jr + Jc;
+      for (int item = k; item < nt * nterm; item += L) {
+        const int i = item / nterm, term = item - i * nterm;
+        const double tn = t_s[1 + i], dx = tn - t_s[i];
+        if (term < Jr) {
+          phi_s[i * JP + term] = exp(-c_real[term] * dx);
+          u_s[i * JP + term] = a_real[term];
+          v_s[i * JP + term] = 1.0;
+        } else {
+          const int q = term - Jr, r0 = Jr + 2 * q;
+          double sd, cd;
+          sincos(d_comp[q] * tn, &sd, &cd);
+          const double e = exp(-c_comp[q] * dx);
+          const double aa = a_comp[q], bq = b_comp[q];
+          phi_s[i * JP + r0] = e;
+          phi_s[i * JP + r0 + 1] = e;
+          u_s[i * JP + r0] = aa * cd + bq * sd;
+          u_s[i * JP + r0 + 1] = aa * sd - bq * cd;
+          v_s[i * JP + r0] = cd;
+          v_s[i * JP + r0 + 1] = sd;
+        }
+      }
+      for (int item = k; item < nt * Jg; item += L) {
+        const int i = item / Jg, q = item - i * Jg, r0 = Jr + 2 * Jc + q;
+        phi_s[i * JP + r0] = 1.0;
+        u_s[i * JP + r0] = __ldg(Up + (size_t)(n0 + i) * Jg + q);
+        v_s[i * JP + r0] = __ldg(Vp + (size_t)(n0 + i) * Jg + q);
+      }
+    }
+    __syncwarp();
+
+    // ---- serial phase ---------------------------------------------------------------------
+    for (int i = 0; i < nt; ++i) {
+      const int par = (n0 + i) & 1;
+      const double* ph = phi_s + i * JP;
+      const double* uu = u_s + i * JP;
+      const double* xw = x_s + par * JP;             // D_{n-1} W_{n-1}
+      const double phk = row_ok ? ph[kk] : 0.0;
+      const double uk = row_ok ? uu[kk] : 0.0;
+      const double vk = row_ok ? v_s[i * JP + kk] : 0.0;
+      // S_k. <- phi_k phi_. o (S_k. + W_k (D W).)  and  acc = (S u)_k     — cholesky.h:154-175
+      double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
+#pragma unroll
+      for (int j = 0; j < JP; j += 2) {
+        const double2 p2 = *reinterpret_cast<const double2*>(ph + j);
+        const double2 x2 = *reinterpret_cast<const double2*>(xw + j);
+        const double2 u2 = *reinterpret_cast<const double2*>(uu + j);
+        const double q0 = dw_own * x2.x, q1 = dw_own * x2.y;
+        const double s0 = (phk * p2.x) * fma(r_prev, q0, S[j]);
+        const double s1 = (phk * p2.y) * fma(r_prev, q1, S[j + 1]);
+        S[j] = s0;
+        S[j + 1] = s1;
+        if ((j & 2) == 0) { acc0 = fma(s0, u2.x, acc0); acc1 = fma(s1, u2.y, acc1); }
+        else { acc2 = fma(s0, u2.x, acc2); acc3 = fma(s1, u2.y, acc3); }
+      }
+      const double su = (acc0 + acc1) + (acc2 + acc3);
+      // forward substitution — cholesky.h:350-354
+      f_own = phk * fma(dw_own * r_prev, xprev, f_own);
+      double red0 = uk * su, red1 = uk * f_own;
+      group_sum2<L>(red0, red1);
+      const double Dn = ((d_s[i] + sum_ar) + sum_ac) + jitter - red0;
+      const double x = y_s[i] - red1;
+      const double dw = vk - su;
+      if (row_ok) x_s[(par ^ 1) * JP + kk] = dw;
+      if (Dn < 0.0 && fail == 0) fail = n0 + i + 1;  // cholesky.h:176
+      const double r = 1.0 / Dn;
+      if (STORE) {
+        if (row_ok) w_s[i * JP + kk] = dw * r;
+        if (k == 0) dd_s[i] = Dn;
+      }
+      quad = fma(x * x, r, quad);
+      xprev = x;
+      dw_own = dw;
+      r_prev = r;
+      ld.add(Dn);
+      __syncwarp();
+    }
+    ld.renorm();
+
+    // ---- materialise (reference layout: J fastest, column n-1 of phi/u = time n) ------------
+    if (STORE) {
+      if (active) {
+        double* Wg = a.W + (size_t)b * N * J + (size_t)n0 * J;
+        for (int e = k; e < nt * J; e += L) {
+          const int i = e / J, j = e - i * J;
+          Wg[e] = w_s[i * JP + j];
+        }
+        double* Dg = a.D + (size_t)b * N + n0;
+        for (int i = k; i < nt; i += L) Dg[i] = dd_s[i];
+        if (N > 1) {
+          double* phg = a.phi + (size_t)b * (N - 1) * J;
+          double* ug = a.u + (size_t)b * (N - 1) * J;
+          const int i0 = (n0 == 0) ? 1 : 0;
+          for (int e = k + i0 * J; e < nt * J; e += L) {
+            const int i = e / J, j = e - i * J;
+            const size_t o = (size_t)(n0 + i - 1) * J + j;
+            phg[o] = phi_s[i * JP + j];
+            ug[o] = u_s[i * JP + j];
+          }
+        }
+      }
+      __syncwarp();
+    }
+  }
+
+  if (active && k == 0) {
+    const double nan = __longlong_as_double(0x7ff8000000000000LL);
+    const double logdet = fail ? nan : ld.value();
+    const double q = fail ? nan : quad;
+    if (a.out_logdet) a.out_logdet[b] = logdet;
+    if (a.out_quad) a.out_quad[b] = q;
+    if (a.out_ll) a.out_ll[b] = -0.5 * (q + logdet + (double)N * kLog2Pi);
+    if (a.status) a.status[b] = fail ? 3 : 0;
+    if (a.fail_index) a.fail_index[b] = fail;
+  }
+}
+
+template <int JP, bool STORE>
+cudaError_t launch_one(const BatchArgs& a, cudaStream_t stream) {
+  using C = CoopCfg<JP, STORE>;
+  auto kern = k_factor_coop<JP, STORE>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::smem);
+  if (e != cudaSuccess) return e;
+  const long long grid = (a.B + C::G - 1) / C::G;
+  kern<<<(unsigned)grid, kWarp, C::smem, stream>>>(a);
+  return cudaGetLastError();
+}
+
+template <bool STORE>
+cudaError_t dispatch(const BatchArgs& a, cudaStream_t stream) {
+  const int J = a.Jr + 2 * a.Jc + a.Jg;
+  if (J <= 2) return launch_one<2, STORE>(a, stream);
+  if (J <= 4) return launch_one<4, STORE>(a, stream);
+  if (J <= 6) return launch_one<6, STORE>(a, stream);
+  if (J <= 8) return launch_one<8, STORE>(a, stream);
+  if (J <= 12) return launch_one<12, STORE>(a, stream);
+  if (J <= 16) return launch_one<16, STORE>(a, stream);
+  if (J <= 24) return launch_one<24, STORE>(a, stream);
+  if (J <= 32) return launch_one<32, STORE>(a, stream);
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace
+
+cudaError_t launch_loglik_coop(const BatchArgs& a, cudaStream_t stream) {
+  return a.phi ? dispatch<true>(a, stream) : dispatch<false>(a, stream);
+}
+
+}  // namespace cel

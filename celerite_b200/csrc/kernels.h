@@ -1,0 +1,81 @@
+// Host-visible launch interface of the CUDA kernels (internal to the library; the public
+// boundary is include/celerite_b200.h).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace cel {
+
+// One batch of independent series + kernels, all DEVICE pointers (see the C ABI for layout).
+struct BatchArgs {
+  long long B;
+  int N;
+  long long stride;        // elements between series in t/diag/y/A (0 = shared)
+  int Jr, Jc, Jg;
+  const double* coeffs;    // rows [jitter, a_real, c_real, a_comp, b_comp, c_comp, d_comp]
+  long long coeff_stride;  // 0 = shared
+  const double* t;
+  const double* diag;
+  const double* y;         // may be NULL when only the factor is wanted
+  const double* A;         // general rows (cholesky.h:49-51): NULL or N per series
+  const double* U;         // Jg x N per series, Jg fastest
+  const double* V;
+  double* out_logdet;      // any may be NULL
+  double* out_quad;
+  double* out_ll;
+  int* status;             // 0 or 3 per series
+  int* fail_index;         // optional: 1 + index of the first D_n < 0 (0 = none)
+  // materialised factor in the reference layout (all NULL for the fused log-likelihood)
+  double* phi;             // B x (N-1) x J
+  double* u;               // B x (N-1) x J
+  double* W;               // B x N x J
+  double* D;               // B x N
+};
+
+// Thread-per-series lockstep sweep (fused log-likelihood), J = Jr + 2*Jc <= kLockstepMaxJ, Jg = 0.
+constexpr int kLockstepMaxJ = 8;
+constexpr int kLockstepFastJ = 6;   // beyond this the register state spills: use the cooperative kernel
+cudaError_t launch_loglik_lockstep(const BatchArgs& a, cudaStream_t stream);
+
+// Cooperative sweep: L = pow2ceil(J) lanes per series, one row of S per lane.  Fused
+// log-likelihood when a.phi == NULL, materialising compute otherwise.  J <= kCoopMaxJ.
+constexpr int kCoopMaxJ = 32;
+cudaError_t launch_loglik_coop(const BatchArgs& a, cudaStream_t stream);
+
+// One stored factor (reference layout) applied to nrhs right-hand sides, DEVICE pointers.
+struct SweepArgs {
+  int N, J, nrhs;
+  const double* phi;
+  const double* u;
+  const double* W;
+  const double* D;
+  const double* in;    // N x nrhs column-major
+  double* out;         // N x nrhs
+  double* scalar_out;  // nrhs (dot_solve)
+};
+cudaError_t launch_solve(const SweepArgs& a, cudaStream_t stream);      // forward + backward
+cudaError_t launch_dot_solve(const SweepArgs& a, cudaStream_t stream);
+cudaError_t launch_dot_L(const SweepArgs& a, cudaStream_t stream);
+
+// Stateless K z (cholesky.h:444-590)
+struct DotArgs {
+  int N, Jr, Jc, Jg, nrhs;
+  const double* coeffs;  // one row [jitter, a_real, c_real, a_comp, b_comp, c_comp, d_comp]
+  const double* A;       // NULL or N
+  const double* U;       // Jg x N
+  const double* V;
+  const double* x;       // times
+  const double* z;       // N x nrhs
+  double* out;
+};
+cudaError_t launch_dot(const DotArgs& a, cudaStream_t stream);
+
+// elementwise helper for the J == 0 paths: mode 0 out=in/D, 1 out=scalar*in, 2 out=sqrt(D)*in
+cudaError_t launch_scale(int n, int N, const double* in, const double* D, double scalar, int mode, double* out,
+                         cudaStream_t stream);
+// J == 0 "factorisation": D = diag + jitter (+A), logdet = sum log D   (cholesky.h:90-95)
+cudaError_t launch_jitter_only(int N, const double* diag, double jitter, double* D, double* logdet,
+                               cudaStream_t stream);
+
+}  // namespace cel

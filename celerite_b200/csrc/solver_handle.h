@@ -1,0 +1,86 @@
+// Internal definition of the opaque handle behind include/celerite_b200.h.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <string>
+
+#include "../../include/celerite_b200.h"
+#include "kernels.h"
+
+namespace cel {
+
+// Device buffer that only ever grows (the reference re-allocates phi/u/W on every compute,
+// cholesky.h:76-78; we keep the high-water mark instead).
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t reserve(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+  double* d() const { return static_cast<double*>(p); }
+  int* i() const { return static_cast<int*>(p); }
+};
+
+}  // namespace cel
+
+struct cel_solver {
+  int device = 0;
+  cudaStream_t own_stream = nullptr;
+  cudaStream_t stream = nullptr;   // the stream work is issued on (own_stream unless overridden)
+  cudaStream_t copy_stream[2] = {nullptr, nullptr};
+  cudaEvent_t ev_in[2] = {nullptr, nullptr};
+  cudaEvent_t ev_done[2] = {nullptr, nullptr};
+  std::string err;
+  long long launches = 0;
+
+  // ---- stored factor of the single-series API (cholesky.h:702-706) ----
+  bool computed = false;
+  int N = 0, J = 0, Jr = 0, Jc = 0, Jg = 0;
+  double log_det = 0.0;
+  cel::DevBuf phi, u, W, D;        // reference layout, J fastest
+  cel::DevBuf t;                   // kept for predict (cholesky.h:81-87)
+  cel::DevBuf coeffs;              // [jitter, a_real, c_real, a_comp, b_comp, c_comp, d_comp]
+  double h_coeffs_jitter = 0.0;
+
+  // ---- scratch ----
+  cel::DevBuf in0, in1, in2, in3;  // single-series inputs / rhs
+  cel::DevBuf out0, out1;
+  cel::DevBuf scratch0, scratch1, scratch2;
+  cel::DevBuf stage_t[2], stage_d[2], stage_y[2], stage_c[2], stage_o[2], stage_s[2];
+  void* pinned = nullptr;          // small pinned mailbox for scalar results
+  size_t pinned_cap = 0;
+};
+
+#define CEL_CUDA_TRY(s, expr)                                                          \
+  do {                                                                                 \
+    cudaError_t _e = (expr);                                                           \
+    if (_e != cudaSuccess) {                                                           \
+      char _buf[512];                                                                  \
+      snprintf(_buf, sizeof(_buf), "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
+               __FILE__, __LINE__);                                                    \
+      (s)->err = _buf;                                                                 \
+      cudaGetLastError();                                                              \
+      return CEL_CUDA_ERROR;                                                           \
+    }                                                                                  \
+  } while (0)
+
+#define CEL_FAIL(s, code, msg) \
+  do {                         \
+    (s)->err = (msg);          \
+    return (code);             \
+  } while (0)

@@ -1,0 +1,345 @@
+// K2-K5 — the linear recursions on a stored factor, serial-in-time variant.
+//
+//   K2 dot_solve  cholesky.h:326-401      K3 solve  cholesky.h:218-318
+//   K4 dot_L      cholesky.h:409-431      K5 dot    cholesky.h:444-590 (stateless)
+//
+// Mapping: one group of L = pow2ceil(J) lanes per right-hand-side column, lane k owns row k of
+// the J-vector state f; the inner product over rows is one shuffle butterfly per step.  Every
+// lane streams its own row of phi/u/W (J-fastest layout => the group's loads are contiguous)
+// through a register ring filled one 8-step tile ahead, so the global-memory latency never sits
+// on the recurrence's critical path.  The chunked two-pass scan for long series (scan.cu) reuses
+// the same step functions.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace cel {
+namespace {
+
+constexpr int TT = 8;  // steps per register tile
+
+// ---------------------------------------------------------------------------------------------
+// forward family: solve (forward half), dot_solve, dot_L
+// ---------------------------------------------------------------------------------------------
+enum { MODE_SOLVE_FWD = 0, MODE_DOT_SOLVE = 1, MODE_DOT_L = 2 };
+
+template <int L, int MODE>
+__global__ void __launch_bounds__(kWarp) k_forward(SweepArgs a) {
+  constexpr int G = kWarp / L;
+  const int lane = threadIdx.x, g = lane / L, k = lane % L;
+  const int col = blockIdx.x * G + g;
+  const bool active = col < a.nrhs;
+  const int cc = active ? col : a.nrhs - 1;
+  const int N = a.N, J = a.J;
+  const bool row_ok = k < J;
+  const int kk = row_ok ? k : 0;
+  const double* in = a.in + (size_t)cc * N;
+  double* out = a.out ? a.out + (size_t)cc * N : nullptr;
+
+  struct Tile { double ph[TT], uu[TT], ww[TT], bn[TT], dn[TT]; };
+  auto load = [&](Tile& tl, int n0) {
+#pragma unroll
+    for (int i = 0; i < TT; ++i) {
+      const int n = min(n0 + i, N - 1);
+      const bool has_prev = (n >= 1) && row_ok;
+      tl.ph[i] = has_prev ? __ldg(a.phi + (size_t)(n - 1) * J + kk) : 0.0;
+      tl.uu[i] = has_prev ? __ldg(a.u + (size_t)(n - 1) * J + kk) : 0.0;
+      tl.ww[i] = row_ok ? __ldg(a.W + (size_t)n * J + kk) : 0.0;
+      tl.bn[i] = __ldg(in + n);
+      tl.dn[i] = __ldg(a.D + n);
+    }
+  };
+
+  double f = 0.0, wprev = 0.0, sprev = 0.0, quad = 0.0;
+  auto run = [&](const Tile& tl, int n0) {
+#pragma unroll
+    for (int i = 0; i < TT; ++i) {
+      if (n0 + i < N) {
+        f = tl.ph[i] * fma(wprev, sprev, f);
+        const double red = group_sum<L>(tl.uu[i] * f);
+        const double d = tl.dn[i];
+        if (MODE == MODE_DOT_L) {
+          const double tmp = sqrt(d) * tl.bn[i];
+          if (k == 0 && active) out[n0 + i] = tmp + red;
+          sprev = tmp;
+        } else {
+          const double x = tl.bn[i] - red;
+          if (MODE == MODE_SOLVE_FWD) {
+            if (k == 0 && active) out[n0 + i] = x / d;
+          } else {
+            quad += x * x / d;
+          }
+          sprev = x;
+        }
+        wprev = tl.ww[i];
+      }
+    }
+  };
+  // two tiles in flight through registers: while one is consumed the next is being fetched
+  Tile ta, tb;
+  load(ta, 0);
+  for (int n0 = 0; n0 < N; n0 += 2 * TT) {
+    if (n0 + TT < N) load(tb, n0 + TT);
+    run(ta, n0);
+    if (n0 + 2 * TT < N) load(ta, n0 + 2 * TT);
+    if (n0 + TT < N) run(tb, n0 + TT);
+  }
+  if (MODE == MODE_DOT_SOLVE && k == 0 && active) a.scalar_out[col] = quad;
+}
+
+// backward half of solve: out holds x/D on entry, K^-1 b on exit  (cholesky.h:251-259)
+template <int L>
+__global__ void __launch_bounds__(kWarp) k_solve_backward(SweepArgs a) {
+  constexpr int G = kWarp / L;
+  const int lane = threadIdx.x, g = lane / L, k = lane % L;
+  const int col = blockIdx.x * G + g;
+  const bool active = col < a.nrhs;
+  const int cc = active ? col : a.nrhs - 1;
+  const int N = a.N, J = a.J;
+  const bool row_ok = k < J;
+  const int kk = row_ok ? k : 0;
+  double* out = a.out + (size_t)cc * N;
+
+  struct Tile { double ph[TT], uu[TT], ww[TT], xn[TT]; };
+  // m counts from the end: step m is n = N-1-m
+  auto load = [&](Tile& tl, int m0) {
+#pragma unroll
+    for (int i = 0; i < TT; ++i) {
+      const int n = max(N - 1 - (m0 + i), 0);
+      const bool has_next = (n < N - 1) && row_ok;
+      tl.ph[i] = has_next ? __ldg(a.phi + (size_t)n * J + kk) : 0.0;  // phi_{n+1}
+      tl.uu[i] = has_next ? __ldg(a.u + (size_t)n * J + kk) : 0.0;    // u_{n+1}
+      tl.ww[i] = row_ok ? __ldg(a.W + (size_t)n * J + kk) : 0.0;
+      tl.xn[i] = out[n];
+    }
+  };
+  double f = 0.0, znext = 0.0;
+  auto run = [&](const Tile& tl, int m0) {
+#pragma unroll
+    for (int i = 0; i < TT; ++i) {
+      if (m0 + i < N) {
+        const int n = N - 1 - (m0 + i);
+        f = tl.ph[i] * fma(tl.uu[i], znext, f);
+        const double red = group_sum<L>(tl.ww[i] * f);
+        znext = tl.xn[i] - red;
+        if (k == 0 && active) out[n] = znext;
+      }
+    }
+  };
+  Tile ta, tb;
+  load(ta, 0);
+  for (int m0 = 0; m0 < N; m0 += 2 * TT) {
+    if (m0 + TT < N) load(tb, m0 + TT);
+    run(ta, m0);
+    if (m0 + 2 * TT < N) load(ta, m0 + 2 * TT);
+    if (m0 + TT < N) run(tb, m0 + TT);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K5: y = K z without a factor.  Each lane regenerates its own row of phi/u/v on the fly.
+// ---------------------------------------------------------------------------------------------
+struct RowGen {
+  int type;        // 0 real, 1 complex-cos row, 2 complex-sin row, 3 general, 4 padding
+  double a, b, c, d;
+  __device__ __forceinline__ void eval(double tn, double dx, double Un, double Vn, double& phi, double& u,
+                                       double& v) const {
+    if (type == 0) { phi = exp(-c * dx); u = a; v = 1.0; }
+    else if (type == 1 || type == 2) {
+      double sd, cd;
+      sincos(d * tn, &sd, &cd);
+      phi = exp(-c * dx);
+      if (type == 1) { u = a * cd + b * sd; v = cd; } else { u = a * sd - b * cd; v = sd; }
+    } else if (type == 3) { phi = 1.0; u = Un; v = Vn; }
+    else { phi = 0.0; u = 0.0; v = 0.0; }
+  }
+};
+
+__device__ __forceinline__ RowGen make_rowgen(const DotArgs& a, int k) {
+  RowGen r;
+  const double* row = a.coeffs;
+  const int Jr = a.Jr, Jc = a.Jc, Jg = a.Jg;
+  const double* a_real = row + 1;
+  const double* c_real = a_real + Jr;
+  const double* a_comp = c_real + Jr;
+  const double* b_comp = a_comp + Jc;
+  const double* c_comp = b_comp + Jc;
+  const double* d_comp = c_comp + Jc;
+  r.a = r.b = r.c = r.d = 0.0;
+  if (k < Jr) { r.type = 0; r.a = a_real[k]; r.c = c_real[k]; }
+  else if (k < Jr + 2 * Jc) {
+    const int q = (k - Jr) >> 1;
+    r.type = 1 + ((k - Jr) & 1);
+    r.a = a_comp[q]; r.b = b_comp[q]; r.c = c_comp[q]; r.d = d_comp[q];
+  } else if (k < Jr + 2 * Jc + Jg) r.type = 3;
+  else r.type = 4;
+  return r;
+}
+
+template <int L>
+__global__ void __launch_bounds__(kWarp) k_dot(DotArgs a) {
+  constexpr int G = kWarp / L;
+  const int lane = threadIdx.x, g = lane / L, k = lane % L;
+  const int col = blockIdx.x * G + g;
+  const bool active = col < a.nrhs;
+  const int cc = active ? col : a.nrhs - 1;
+  const int N = a.N, Jr = a.Jr, Jc = a.Jc, Jg = a.Jg;
+  const RowGen rg = make_rowgen(a, k);
+  const int gq = (rg.type == 3) ? k - Jr - 2 * Jc : 0;
+  const double* z = a.z + (size_t)cc * N;
+  double* y = a.out + (size_t)cc * N;
+  double diag0 = a.coeffs[0];  // jitter + sum a  (cholesky.h:483-485: no measurement variance here)
+  {
+    double sr = 0.0, sc = 0.0;
+    for (int j = 0; j < Jr; ++j) sr += a.coeffs[1 + j];
+    for (int j = 0; j < Jc; ++j) sc += a.coeffs[1 + 2 * Jr + j];
+    diag0 = (sr + sc) + diag0;
+  }
+
+  // ---- upper sweep, n = N-1 .. 0 (cholesky.h:536-547) ----
+  {
+    double f = 0.0, uprev = 0.0, zprev = 0.0, tnext = __ldg(a.x + N - 1);
+    bool first = true;
+    for (int n = N - 1; n >= 0; --n) {
+      const double tn = __ldg(a.x + n), zn = __ldg(z + n);
+      double Un = 0.0, Vn = 0.0;
+      if (rg.type == 3) { Un = __ldg(a.U + (size_t)n * Jg + gq); Vn = __ldg(a.V + (size_t)n * Jg + gq); }
+      double phi_next, un, vn;
+      // phi_{n+1} depends on t_{n+1}-t_n; u_n, v_n on t_n
+      rg.eval(tn, tnext - tn, Un, Vn, phi_next, un, vn);
+      if (first) phi_next = 0.0;
+      f = phi_next * fma(uprev, zprev, f);
+      const double red = group_sum<L>(vn * f);
+      const double dg = diag0 + (a.A ? __ldg(a.A + n) : 0.0);
+      if (k == 0 && active) y[n] = dg * zn + red;
+      uprev = un; zprev = zn; tnext = tn; first = false;
+    }
+  }
+  __syncwarp();
+  // ---- lower sweep, n = 0 .. N-1 (cholesky.h:549-559) ----
+  {
+    double f = 0.0, vprev = 0.0, zprev = 0.0, tprev = __ldg(a.x);
+    for (int n = 0; n < N; ++n) {
+      const double tn = __ldg(a.x + n), zn = __ldg(z + n);
+      double Un = 0.0, Vn = 0.0;
+      if (rg.type == 3) { Un = __ldg(a.U + (size_t)n * Jg + gq); Vn = __ldg(a.V + (size_t)n * Jg + gq); }
+      double phi_n, un, vn;
+      rg.eval(tn, tn - tprev, Un, Vn, phi_n, un, vn);
+      if (n == 0) phi_n = 0.0;
+      f = phi_n * fma(vprev, zprev, f);
+      const double red = group_sum<L>(un * f);
+      if (k == 0 && active) y[n] += red;
+      vprev = vn; zprev = zn; tprev = tn;
+    }
+  }
+}
+
+// J == 0 helpers (cholesky.h:90-95, 226-231, 334-339, 477-481)
+__global__ void k_scale(int n, int N, const double* in, const double* D, double scalar, int mode, double* out) {
+  // n = N*nrhs elements.  mode 0: out = in / D   mode 1: out = scalar * in   mode 2: out = sqrt(D) * in
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    if (mode == 0) out[i] = in[i] / D[i % N];
+    else if (mode == 1) out[i] = scalar * in[i];
+    else out[i] = sqrt(D[i % N]) * in[i];
+  }
+}
+
+}  // namespace
+
+#define CEL_DISPATCH_L(J, CALL)                   \
+  do {                                            \
+    if ((J) <= 1) { CALL(1); }                    \
+    else if ((J) <= 2) { CALL(2); }               \
+    else if ((J) <= 4) { CALL(4); }               \
+    else if ((J) <= 8) { CALL(8); }               \
+    else if ((J) <= 16) { CALL(16); }             \
+    else { CALL(32); }                            \
+  } while (0)
+
+cudaError_t launch_solve(const SweepArgs& a, cudaStream_t stream) {
+  if (a.J > kCoopMaxJ) return cudaErrorInvalidValue;
+#define CALL(LL)                                                                       \
+  {                                                                                    \
+    const int G = kWarp / LL, grid = (a.nrhs + G - 1) / G;                             \
+    k_forward<LL, MODE_SOLVE_FWD><<<grid, kWarp, 0, stream>>>(a);                      \
+    k_solve_backward<LL><<<grid, kWarp, 0, stream>>>(a);                               \
+  }
+  CEL_DISPATCH_L(a.J, CALL);
+#undef CALL
+  return cudaGetLastError();
+}
+
+cudaError_t launch_dot_solve(const SweepArgs& a, cudaStream_t stream) {
+  if (a.J > kCoopMaxJ) return cudaErrorInvalidValue;
+#define CALL(LL)                                                                       \
+  {                                                                                    \
+    const int G = kWarp / LL, grid = (a.nrhs + G - 1) / G;                             \
+    k_forward<LL, MODE_DOT_SOLVE><<<grid, kWarp, 0, stream>>>(a);                      \
+  }
+  CEL_DISPATCH_L(a.J, CALL);
+#undef CALL
+  return cudaGetLastError();
+}
+
+cudaError_t launch_dot_L(const SweepArgs& a, cudaStream_t stream) {
+  if (a.J > kCoopMaxJ) return cudaErrorInvalidValue;
+#define CALL(LL)                                                                       \
+  {                                                                                    \
+    const int G = kWarp / LL, grid = (a.nrhs + G - 1) / G;                             \
+    k_forward<LL, MODE_DOT_L><<<grid, kWarp, 0, stream>>>(a);                          \
+  }
+  CEL_DISPATCH_L(a.J, CALL);
+#undef CALL
+  return cudaGetLastError();
+}
+
+cudaError_t launch_dot(const DotArgs& a, cudaStream_t stream) {
+  const int J = a.Jr + 2 * a.Jc + a.Jg;
+  if (J > kCoopMaxJ) return cudaErrorInvalidValue;
+#define CALL(LL)                                                                       \
+  {                                                                                    \
+    const int G = kWarp / LL, grid = (a.nrhs + G - 1) / G;                             \
+    k_dot<LL><<<grid, kWarp, 0, stream>>>(a);                                          \
+  }
+  CEL_DISPATCH_L(J, CALL);
+#undef CALL
+  return cudaGetLastError();
+}
+
+cudaError_t launch_scale(int n, int N, const double* in, const double* D, double scalar, int mode, double* out,
+                         cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  const int threads = 256, grid = min((n + threads - 1) / threads, 148 * 8);
+  k_scale<<<grid, threads, 0, stream>>>(n, N, in, D, scalar, mode, out);
+  return cudaGetLastError();
+}
+
+}  // namespace cel
+
+namespace cel {
+namespace {
+__global__ void __launch_bounds__(256) k_jitter_only(int N, const double* diag, double jitter, double* D,
+                                                      double* logdet) {
+  __shared__ double part[8];
+  double acc = 0.0;
+  for (int i = threadIdx.x; i < N; i += blockDim.x) {
+    const double d = diag[i] + jitter;
+    D[i] = d;
+    acc += log(d);
+  }
+  acc = group_sum<32>(acc);
+  if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s = 0.0;
+    for (int i = 0; i < 8; ++i) s += part[i];
+    *logdet = s;
+  }
+}
+}  // namespace
+
+cudaError_t launch_jitter_only(int N, const double* diag, double jitter, double* D, double* logdet,
+                               cudaStream_t stream) {
+  k_jitter_only<<<1, 256, 0, stream>>>(N, diag, jitter, D, logdet);
+  return cudaGetLastError();
+}
+}  // namespace cel

@@ -1,0 +1,162 @@
+/* celerite_b200 — C ABI of the B200-native semiseparable Cholesky GP solver.
+ *
+ * This is the drop-in boundary: every entry point below replaces one piece of the reference's
+ * `celerite::solver::CholeskySolver<double>` (cpp/include/celerite/solver/cholesky.h) or of its
+ * pybind11 binding (celerite/solver.cpp); the replaced lines are cited on each declaration.
+ * Plain pointers and sizes only; no C++/torch/Eigen types cross this boundary.  The host C++
+ * class (celerite_b200/csrc/cholesky_solver.hpp), the pybind11 module and the ctypes wrapper
+ * are thin layers over exactly these symbols.
+ *
+ * Conventions
+ *   - all arithmetic fp64; all arrays `double` unless stated.
+ *   - J = Jr + 2*Jc + Jg solver rows, ordered: real terms, (cos,sin) pairs of the complex terms,
+ *     general rank-Jg rows (cholesky.h:72-74, 106-116).
+ *   - factor layout (cholesky.h:76-78, 702-706): phi, u are J x (N-1) column-major (J fastest;
+ *     column n-1 holds the values at time index n), W is J x N, D has N entries.
+ *   - right-hand sides / results are N x nrhs column-major, like Eigen::MatrixXd.
+ *   - A is NULL or has N entries; U, V are NULL (Jg = 0) or Jg x N column-major.
+ *   - single-series calls take HOST pointers and are synchronous (drop-in semantics of the
+ *     reference: one call = one series, result ready on return).
+ *   - batched calls take DEVICE pointers by default; pass CEL_HOST_POINTERS in `flags` to hand
+ *     host buffers (ideally pinned) and let the library stage them in chunks, overlapping the
+ *     copies with the kernels.
+ *   - there is no CPU fallback: without a CUDA device every call returns CEL_CUDA_ERROR.
+ *
+ * Return codes (the host class maps them onto the reference's exception types,
+ * cpp/include/celerite/exceptions.h:8-36):
+ */
+#ifndef CELERITE_B200_H
+#define CELERITE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CEL_OK                    0
+#define CEL_DIMENSION_MISMATCH    1  /* celerite::dimension_mismatch                        */
+#define CEL_NOT_COMPUTED          2  /* celerite::compute_exception                         */
+#define CEL_NOT_POSITIVE_DEFINITE 3  /* celerite::linalg_exception  (D_n < 0, cholesky.h:176) */
+#define CEL_CUDA_ERROR            4  /* no device / launch failure; see cel_last_error()     */
+#define CEL_INVALID_ARGUMENT      5
+#define CEL_UNSUPPORTED           6
+
+#define CEL_HOST_POINTERS 1u        /* flags: t/diag/y/coeffs/outputs are host memory        */
+
+typedef struct cel_solver cel_solver;
+
+/* ---- lifetime ------------------------------------------------------------------------------
+ * Replaces construction/destruction of CholeskySolver<double> (cholesky.h:25-26).  The handle
+ * owns the device-resident factor, scratch buffers (grown monotonically, never shrunk) and one
+ * CUDA stream.  `device` < 0 keeps the current device. */
+int cel_create(cel_solver** out, int device);
+int cel_destroy(cel_solver* s);
+/* Human-readable text for the last non-OK return on this handle (or the last cel_create
+ * failure when s == NULL). */
+const char* cel_last_error(const cel_solver* s);
+/* Library self-description: "celerite_b200 <version> sm_100a". */
+const char* cel_version(void);
+/* Run the handle's work on a caller-owned cudaStream_t (e.g. torch's current stream) instead
+ * of its own; pass NULL to go back. */
+int cel_set_stream(cel_solver* s, void* cuda_stream);
+
+/* ---- CholeskySolver::compute (cholesky.h:41-210) ---------------------------------------------
+ * Factorises K = L D L^T for one series and keeps phi,u,W,D on the device.  Returns
+ * CEL_NOT_POSITIVE_DEFINITE as soon as some D_n < 0 was met; the handle is then "not computed"
+ * exactly like the reference (cholesky.h:57). */
+int cel_compute(cel_solver* s, double jitter,
+                int Jr, const double* a_real, const double* c_real,
+                int Jc, const double* a_comp, const double* b_comp,
+                const double* c_comp, const double* d_comp,
+                int Jg, const double* A, const double* U, const double* V,
+                int N, const double* x, const double* diag);
+
+/* Solver::computed / Solver::log_determinant (solver.h:74-81) */
+int cel_computed(const cel_solver* s);
+int cel_log_determinant(const cel_solver* s, double* out);
+/* Sizes of the stored factor (0,0 before the first compute). */
+int cel_dims(const cel_solver* s, int* N, int* J);
+
+/* CholeskySolver::dot_solve (cholesky.h:326-401): *out = b^T K^-1 b */
+int cel_dot_solve(cel_solver* s, int N, const double* b, double* out);
+/* CholeskySolver::solve (cholesky.h:218-318): out = K^-1 b, N x nrhs */
+int cel_solve(cel_solver* s, int N, int nrhs, const double* b, double* out);
+/* CholeskySolver::dot_L (cholesky.h:409-431): out = L z with K = L L^T */
+int cel_dot_L(cel_solver* s, int N, int nrhs, const double* z, double* out);
+/* CholeskySolver::dot (cholesky.h:444-590): out = K z, stateless (no factor needed; the
+ * diagonal is sum(a)+jitter(+A), *without* the measurement variances, cholesky.h:483-485) */
+int cel_dot(cel_solver* s, double jitter,
+            int Jr, const double* a_real, const double* c_real,
+            int Jc, const double* a_comp, const double* b_comp,
+            const double* c_comp, const double* d_comp,
+            int Jg, const double* A, const double* U, const double* V,
+            int N, const double* x, int nrhs, const double* z, double* out);
+/* CholeskySolver::predict (cholesky.h:599-698): conditional mean at M sorted points xs */
+int cel_predict(cel_solver* s, int N, const double* y, int M, const double* xs, double* out);
+
+/* grad_log_likelihood lambda of the binding (celerite/solver.cpp:347-463).  Stateless like the
+ * reference's (it ignores the cached factor).  *val = -0.5*(y^T K^-1 y + logdet) WITHOUT any
+ * constant: the binding layer adds the reference's -0.5*M_PI*log(N) (solver.cpp:415).
+ * grad[0 .. 2Jr+4Jc] = d val / d [jitter, a_real, c_real, a_comp, b_comp, c_comp, d_comp]; the
+ * jitter slot is forced to 0 when jitter <= DBL_EPSILON (solver.cpp:377-389, 418-426).
+ * Computed by a reverse-mode sweep (one forward + one adjoint pass), not forward-mode AD. */
+int cel_grad_log_likelihood(cel_solver* s, double jitter,
+                            int Jr, const double* a_real, const double* c_real,
+                            int Jc, const double* a_comp, const double* b_comp,
+                            const double* c_comp, const double* d_comp,
+                            int Jg, const double* A, const double* U, const double* V,
+                            int N, const double* x, const double* y, const double* diag,
+                            double* val, double* grad);
+
+/* PicklableCholeskySolver::serialize / deserialize (celerite/solver.cpp:36-58).  Buffers may be
+ * NULL in cel_get_state to query only the scalars. */
+int cel_get_state(cel_solver* s, int* computed, int* N, int* J, double* log_det,
+                  double* phi, double* u, double* W, double* D);
+int cel_set_state(cel_solver* s, int computed, int N, int J, double log_det,
+                  const double* phi, const double* u, const double* W, const double* D);
+
+/* ---- batched additions (no counterpart in the reference, which is one series per call) -----
+ * B independent series, each with its own (or a shared) kernel; one launch sweeps them in
+ * lockstep.  This fuses compute (cholesky.h:41-210) + dot_solve (326-401) + the scalar
+ * reduction of log_determinant (208) + GP.log_likelihood's constant (celerite/celerite.py:
+ * 214-216) and never writes the factor.
+ *
+ *   series b : t/diag/y + b*stride, N points (stride in elements; 0 = all series share it)
+ *   kernel b : coeffs + b*coeff_stride = [jitter, a_real[Jr], c_real[Jr], a_comp[Jc],
+ *              b_comp[Jc], c_comp[Jc], d_comp[Jc]]   (the order of the reference's gradient
+ *              vector, solver.cpp:392-406); coeff_stride 0 = one kernel for the whole batch
+ *   outputs  : any of out_logdet/out_quad/out_ll may be NULL.
+ *              out_ll[b] = -0.5*(quad + logdet + N*log(2*pi))
+ *              status[b] = CEL_OK or CEL_NOT_POSITIVE_DEFINITE (the batch never fails as a
+ *              whole; a failed series reports NaN, the Python layer maps that to -inf like
+ *              celerite.py:211-218) */
+int cel_batched_log_likelihood(cel_solver* s, int64_t B, int N, int64_t stride,
+                               int Jr, int Jc, const double* coeffs, int64_t coeff_stride,
+                               const double* t, const double* diag, const double* y,
+                               double* out_logdet, double* out_quad, double* out_ll,
+                               int32_t* status, unsigned flags);
+
+/* Same sweep plus the reverse-mode gradient (solver.cpp:347-463 per series).
+ * out_val[b] = -0.5*(quad+logdet) (no constant), out_grad[b*P + k], P = 1+2Jr+4Jc. */
+int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t stride,
+                                    int Jr, int Jc, const double* coeffs, int64_t coeff_stride,
+                                    const double* t, const double* diag, const double* y,
+                                    double* out_val, double* out_grad,
+                                    int32_t* status, unsigned flags);
+
+/* Batched compute that DOES materialise the factor (cholesky.h:41-210 per series):
+ * phi,u: B x (N-1) x J, W: B x N x J, D: B x N, logdet: B.  Device pointers only. */
+int cel_batched_compute(cel_solver* s, int64_t B, int N, int64_t stride,
+                        int Jr, int Jc, const double* coeffs, int64_t coeff_stride,
+                        const double* t, const double* diag,
+                        double* phi, double* u, double* W, double* D, double* out_logdet,
+                        int32_t* status);
+
+/* Number of kernels this handle has launched since creation (bench.py's gpu_launches). */
+int64_t cel_launch_count(const cel_solver* s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CELERITE_B200_H */

@@ -1,0 +1,136 @@
+"""GPU parity, batched fused log-likelihood (K1) vs the CPU oracle on identical seeded inputs."""
+import numpy as np
+import pytest
+
+import oracle
+from tests.util import RTOL_SCALAR, rel_inf
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def bs():
+    from celerite_b200.batched import BatchedSolver
+    return BatchedSolver()
+
+
+def _check(bs, B, N, Jr, Jc, seed, torch_path=False):
+    from celerite_b200 import synth
+    b = synth.make_batch(B, N, Jr, Jc, seed=seed)
+    P = b["coeffs"].shape[1]
+    ref = oracle.best().batched_loglik(B, N, N, Jr, Jc, b["coeffs"], P, b["t"], b["diag"], b["y"], nthreads=8)
+    assert np.all(ref[:, 2] == 0)
+    if torch_path:
+        import torch
+        dev = torch.device("cuda:0")
+        tt = lambda a: torch.from_numpy(a).to(dev)  # noqa: E731
+        ll, logdet, quad, status = bs.log_likelihood(tt(b["coeffs"]), tt(b["t"]), tt(b["diag"]), tt(b["y"]),
+                                                     Jr, Jc, return_parts=True)
+        torch.cuda.synchronize()
+        ll, logdet, quad, status = (x.cpu().numpy() for x in (ll, logdet, quad, status))
+    else:
+        ll, logdet, quad, status = bs.log_likelihood(b["coeffs"], b["t"], b["diag"], b["y"], Jr, Jc,
+                                                     return_parts=True)
+    assert np.all(status == 0)
+    assert np.max(np.abs(logdet - ref[:, 0]) / np.abs(ref[:, 0])) < RTOL_SCALAR
+    assert np.max(np.abs(quad - ref[:, 1]) / np.abs(ref[:, 1])) < RTOL_SCALAR
+    ll_ref = -0.5 * (ref[:, 1] + ref[:, 0] + N * np.log(2 * np.pi))
+    assert np.max(np.abs(ll - ll_ref) / np.abs(ll_ref)) < RTOL_SCALAR
+
+
+@pytest.mark.parametrize("B,N,Jr,Jc", [
+    (300, 2000, 0, 1),    # cfg2 unit (J=2), B not a multiple of the CTA size
+    (130, 1000, 0, 2),    # cfg5 unit (J=4)
+    (64, 4096, 1, 1),     # cfg1 kernel (J=3)
+    (33, 777, 2, 0),      # real only, odd N (unaligned rows: the non-TMA path)
+    (17, 501, 1, 2),      # J=5
+    (40, 1500, 0, 3),     # J=6
+    (9, 1203, 0, 4),      # J=8  (cooperative kernel, 8 lanes per series)
+    (5, 900, 2, 5),       # J=12
+    (3, 800, 0, 8),       # J=16
+    (3, 640, 4, 11),      # J=26 (the widest kernel of tests/test_celerite.py)
+    (2, 700, 0, 16),      # J=32
+])
+def test_batched_loglik_host(bs, B, N, Jr, Jc):
+    _check(bs, B, N, Jr, Jc, seed=B + N)
+
+
+@pytest.mark.parametrize("B,N,Jr,Jc", [(257, 2000, 0, 1), (10, 333, 1, 1), (4, 1000, 0, 8)])
+def test_batched_loglik_device(bs, B, N, Jr, Jc):
+    _check(bs, B, N, Jr, Jc, seed=7 * B + N, torch_path=True)
+
+
+def test_edge_sizes(bs):
+    for (B, N) in [(1, 1), (1, 2), (2, 7), (65, 8), (3, 9), (1, 16), (1, 17)]:
+        _check(bs, B, N, 0, 1, seed=B * 100 + N)
+
+
+def test_shared_data_many_kernels(bs):
+    """MCMC-walker layout: one light curve, many kernels (stride 0 on the data)."""
+    from celerite_b200 import synth
+    B, N, Jr, Jc = 50, 800, 0, 2
+    b = synth.make_batch(B, N, Jr, Jc, seed=5)
+    t, d, y = b["t"][0], b["diag"][0], b["y"][0]
+    ll = bs.log_likelihood(b["coeffs"], t, d, y, Jr, Jc)
+    T, Dg, Y = (np.repeat(a[None], B, 0) for a in (t, d, y))
+    ref = oracle.best().batched_loglik(B, N, N, Jr, Jc, b["coeffs"], b["coeffs"].shape[1], T, Dg, Y)
+    ll_ref = -0.5 * (ref[:, 1] + ref[:, 0] + N * np.log(2 * np.pi))
+    assert rel_inf(ll, ll_ref) < RTOL_SCALAR
+
+
+def test_shared_kernel_many_series(bs):
+    from celerite_b200 import synth
+    B, N, Jr, Jc = 40, 600, 1, 1
+    b = synth.make_batch(B, N, Jr, Jc, seed=6)
+    row = b["coeffs"][0].copy()
+    ll = bs.log_likelihood(row, b["t"], b["diag"], b["y"], Jr, Jc)
+    C = np.repeat(row[None], B, 0)
+    ref = oracle.best().batched_loglik(B, N, N, Jr, Jc, C, C.shape[1], b["t"], b["diag"], b["y"])
+    ll_ref = -0.5 * (ref[:, 1] + ref[:, 0] + N * np.log(2 * np.pi))
+    assert rel_inf(ll, ll_ref) < RTOL_SCALAR
+
+
+def test_not_positive_definite_series_is_flagged_not_fatal(bs):
+    """cholesky.h:176 per series: the bad series reports status 3 / -inf, the others are fine."""
+    from celerite_b200 import synth
+    B, N = 70, 300
+    b = synth.make_batch(B, N, 1, 0, seed=11)
+    b["coeffs"][13, 0] = 0.0
+    b["coeffs"][13, 1] = -1.0          # negative amplitude
+    b["diag"][13] = 1e-3
+    ll, logdet, quad, status = bs.log_likelihood(b["coeffs"], b["t"], b["diag"], b["y"], 1, 0, return_parts=True)
+    ref = oracle.best().batched_loglik(B, N, N, 1, 0, b["coeffs"], 3, b["t"], b["diag"], b["y"])
+    assert ref[13, 2] == 3 and status[13] == 3 and ll[13] == -np.inf
+    ok = np.arange(B) != 13
+    assert np.all(status[ok] == 0)
+    assert np.max(np.abs(logdet[ok] - ref[ok, 0]) / np.abs(ref[ok, 0])) < RTOL_SCALAR
+
+
+def test_full_size_properties(bs):
+    """cfg2 at full per-series size on a slice of the batch: size-independent properties.
+    (1) duplicating the batch gives identical results per copy (determinism / no cross-talk);
+    (2) scaling y by 2 scales the quadratic form by 4 and leaves log det unchanged."""
+    import torch
+    from celerite_b200 import synth
+    B, N = 4096, 2000
+    b = synth.make_batch(B, N, 0, 1, seed=2)
+    dev = torch.device("cuda:0")
+    tt = lambda a: torch.from_numpy(a).to(dev)  # noqa: E731
+    c, t, d, y = tt(b["coeffs"]), tt(b["t"]), tt(b["diag"]), tt(b["y"])
+    ll1, ld1, q1, st1 = bs.log_likelihood(c, t, d, y, 0, 1, return_parts=True)
+    ll2, ld2, q2, st2 = bs.log_likelihood(c, t, d, 2.0 * y, 0, 1, return_parts=True)
+    torch.cuda.synchronize()
+    assert int(st1.sum()) == 0
+    assert torch.equal(ld1, ld2)
+    assert float(((q2 - 4 * q1).abs() / q1.abs()).max()) < 1e-13
+    idx = torch.randperm(B, device=dev)
+    ll3 = bs.log_likelihood(c[idx].contiguous(), t[idx].contiguous(), d[idx].contiguous(), y[idx].contiguous(), 0, 1)
+    torch.cuda.synchronize()
+    assert torch.equal(ll3, ll1[idx])
+    # and a sample of series against the oracle
+    pick = np.arange(0, B, 257)
+    ref = oracle.best().batched_loglik(len(pick), N, N, 0, 1, np.ascontiguousarray(b["coeffs"][pick]), 5,
+                                       np.ascontiguousarray(b["t"][pick]), np.ascontiguousarray(b["diag"][pick]),
+                                       np.ascontiguousarray(b["y"][pick]))
+    assert np.max(np.abs(ld1.cpu().numpy()[pick] - ref[:, 0]) / np.abs(ref[:, 0])) < RTOL_SCALAR
+    assert np.max(np.abs(q1.cpu().numpy()[pick] - ref[:, 1]) / np.abs(ref[:, 1])) < RTOL_SCALAR
