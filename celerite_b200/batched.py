@@ -95,7 +95,9 @@ class BatchedSolver(object):
         B, N, stride, cstride = self._shapes(coeffs, t, Jr, Jc)
         out = torch.empty((3, B), dtype=torch.float64, device=t.device)
         status = torch.empty(B, dtype=torch.int32, device=t.device)
-        self._lib.cel_set_stream(self._h, C.c_void_p(torch.cuda.current_stream(t.device).cuda_stream))
+        # torch's default stream has handle 0; the C ABI reads NULL as "use your own stream", so
+        # name the legacy default stream explicitly (cudaStreamLegacy == 0x1)
+        self._lib.cel_set_stream(self._h, C.c_void_p(torch.cuda.current_stream(t.device).cuda_stream or 1))
         p = lambda a: C.c_void_p(a.data_ptr())  # noqa: E731
         rc = self._lib.cel_batched_log_likelihood(self._h, B, N, stride, Jr, Jc, p(coeffs), cstride,
                                                   p(t), p(diag), p(y), p(out[0]), p(out[1]), p(out[2]),
@@ -109,7 +111,7 @@ class BatchedSolver(object):
         """Thin pass-through of cel_batched_log_likelihood for callers that manage memory
         themselves (bench.py): integers are raw device (or host, with HOST_POINTERS) addresses."""
         if stream is not None:
-            self._lib.cel_set_stream(self._h, C.c_void_p(stream))
+            self._lib.cel_set_stream(self._h, C.c_void_p(stream or 1))  # 0 -> cudaStreamLegacy
         v = lambda x: C.c_void_p(x) if x else None  # noqa: E731
         rc = self._lib.cel_batched_log_likelihood(self._h, B, N, stride, Jr, Jc, v(coeffs_ptr), cstride,
                                                   v(t_ptr), v(diag_ptr), v(y_ptr), v(logdet_ptr), v(quad_ptr),

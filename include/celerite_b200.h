@@ -58,7 +58,8 @@ const char* cel_last_error(const cel_solver* s);
 /* Library self-description: "celerite_b200 <version> sm_100a". */
 const char* cel_version(void);
 /* Run the handle's work on a caller-owned cudaStream_t (e.g. torch's current stream) instead
- * of its own; pass NULL to go back. */
+ * of its own; pass NULL to go back.  The legacy default stream, whose handle is also 0, must be
+ * named explicitly as cudaStreamLegacy ((void*)0x1). */
 int cel_set_stream(cel_solver* s, void* cuda_stream);
 
 /* ---- CholeskySolver::compute (cholesky.h:41-210) ---------------------------------------------

@@ -18,6 +18,14 @@ def rel_scalar(a, b):
     return abs(a - b) / max(abs(b), 1e-300)
 
 
+def rel_sum(a, b, N):
+    """Parity metric for extensive scalars (log det, quadratic form, log-likelihood): they are
+    sums of N terms of order one that may cancel (a log-determinant of -1.05 made of 800 logs),
+    so the error is measured against max(|ref|, N) rather than |ref| alone."""
+    a, b = np.asarray(a, dtype=float), np.asarray(b, dtype=float)
+    return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), float(N))))
+
+
 def rel_inf(a, b):
     """||a-b||_inf / ||b||_inf  (SURVEY.md §8c parity metric for vectors)."""
     a, b = np.asarray(a), np.asarray(b)
