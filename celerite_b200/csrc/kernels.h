@@ -34,7 +34,7 @@ struct BatchArgs {
 };
 
 // Thread-per-series lockstep sweep (fused log-likelihood), J = Jr + 2*Jc <= kLockstepMaxJ, Jg = 0.
-constexpr int kLockstepMaxJ = 8;
+constexpr int kLockstepMaxJ = 6;
 constexpr int kLockstepFastJ = 6;   // beyond this the register state spills: use the cooperative kernel
 cudaError_t launch_loglik_lockstep(const BatchArgs& a, cudaStream_t stream);
 

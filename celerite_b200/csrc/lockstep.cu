@@ -2,19 +2,26 @@
 //
 // Replaces, per series, CholeskySolver::compute (cholesky.h:41-210) followed by dot_solve
 // (cholesky.h:326-401) and the log-determinant reduction (cholesky.h:208) without ever writing
-// the factor: 24 bytes are read per point (t, diag, y) and 8-32 bytes are written per series.
+// the factor: 24 bytes are read per point (t, diag, y) and 28 bytes are written per series.
 //
 // Mapping (small J, many series): every lane of a warp owns one series and keeps its whole
 // J x J state (upper triangle of S), W, D*W and the forward-substitution vector f in registers;
-// the 32 series of a warp advance in lockstep.  Each lane's three input streams are staged into
-// shared memory by 1-D bulk async copies (TMA engine, mbarrier-tracked, STAGES-deep ring of
-// T-point segments per lane) so DRAM sees 64-128 B requests while the lanes read their private
-// segments with conflict-free 16-byte shared loads.  Warps are fully independent (own
-// barriers, no __syncthreads).
+// the 32 series of a warp advance in lockstep.  The three input streams of the warp's 32 series
+// are staged through shared memory by the TMA engine: the batch is described to the hardware as
+// a 2-D tensor [B][N] (cuTensorMapEncodeTiled), and ONE cp.async.bulk.tensor.2d per array
+// fetches a [32 series x T points] box into a 64-byte-swizzled tile, completion tracked by an
+// mbarrier, STAGES tiles in flight per warp.  DRAM sees 64-byte row segments (= 2 sectors, no
+// over-fetch: ncu dram bytes == algorithmic bytes), and each lane reads its own row back with
+// conflict-free 16-byte shared loads thanks to the swizzle.  Out-of-range rows/columns are
+// zero-filled by the TMA unit, so ragged tails need no special code.  Warps are fully independent
+// (own barriers, no __syncthreads).  A plain-load variant of the same kernel serves batches the
+// TMA unit cannot describe (odd strides, unaligned bases, shared series).
 //
 // Row order inside the kernel is complex pairs first, then real rows (so that (cos,sin) pairs
 // sit on even/odd register pairs for any Jr); the recursion is order-invariant and nothing
 // row-indexed leaves the kernel in the fused variant.
+#include <cuda.h>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -26,37 +33,38 @@ constexpr int kLockThreads = 64;   // 2 independent warps per CTA
 constexpr double kLog2Pi = 1.8378770664093454836;
 
 template <int J>
-struct LockState {
-  double S[J * (J + 1) / 2];  // upper triangle, S(k,j) k<=j at j*(j+1)/2+k
-  double W[J];                // W_{n-1}
-  double DW[J];               // D_{n-1} * W_{n-1}
-  double f[J];                // forward-substitution state
-};
-
-template <int J>
 __device__ __forceinline__ constexpr int tri(int k, int j) { return j * (j + 1) / 2 + k; }
 
-template <int J, int T, int STAGES>
-__global__ void __launch_bounds__(kLockThreads) k_loglik_lockstep(BatchArgs a) {
-  static_assert(T % 2 == 0, "segments are copied in 16-byte units");
-  constexpr int NP = (J + 1) / 2;
-  constexpr int SEG = T + 2;  // padded lane segment: 16B-aligned and bank-conflict-free for LDS.128
-  constexpr int WARPS = kLockThreads / kWarp;
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  double* wbuf = reinterpret_cast<double*>(smem_raw) + (size_t)warp * (STAGES * 3 * kWarp * SEG);
-  uint64_t* bars =
-      reinterpret_cast<uint64_t*>(reinterpret_cast<double*>(smem_raw) + (size_t)WARPS * (STAGES * 3 * kWarp * SEG)) +
-      warp * STAGES;
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+      : "memory");
+}
 
-  const long long b = (long long)blockIdx.x * kLockThreads + threadIdx.x;
+template <int J, int T, int STAGES, bool TMA>
+__global__ void __launch_bounds__(kLockThreads)
+k_loglik_lockstep(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const __grid_constant__ CUtensorMap tm_d,
+                  const __grid_constant__ CUtensorMap tm_y) {
+  static_assert(T == 8, "64-byte swizzled rows: 8 doubles per row segment");
+  constexpr int NP = (J + 1) / 2;
+  constexpr int WARPS = kLockThreads / kWarp;
+  constexpr int kTile = kWarp * T * 8;  // bytes of one [32 x T] box
+  extern __shared__ unsigned char smem_dyn[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // swizzled TMA destinations want 1024-byte alignment
+  unsigned char* smem_al = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
+  unsigned char* wbuf = smem_al + (size_t)warp * (STAGES * 3 * kTile);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_al + (size_t)WARPS * (STAGES * 3 * kTile)) + warp * STAGES;
+
+  const long long b0 = (long long)blockIdx.x * kLockThreads + warp * kWarp;
+  const long long b = b0 + lane;
   const bool active = b < a.B;
   const long long bb = active ? b : a.B - 1;  // idle lanes shadow the last series, store nothing
   const int N = a.N;
   const double* tp = a.t + bb * a.stride;
   const double* dp = a.diag + bb * a.stride;
   const double* yp = a.y + bb * a.stride;
-  const bool lane_tma = aligned16(tp) && aligned16(dp) && aligned16(yp);
 
   // ---- per-series kernel coefficients -> registers ------------------------------------
   const int Jr = a.Jr, Jc = a.Jc;
@@ -83,27 +91,26 @@ __global__ void __launch_bounds__(kLockThreads) k_loglik_lockstep(BatchArgs a) {
   }
   for (int j = 0; j < Jr; ++j) sum_ar += a_real[j];
   for (int j = 0; j < Jc; ++j) sum_ac += a_comp[j];
+  const double asum = sum_ar + sum_ac;  // (diag + sum_ar) + sum_ac in the reference; see D_n below
 
   // ---- staging ring ----------------------------------------------------------------------
-  if (lane == 0) {
-#pragma unroll
-    for (int s = 0; s < STAGES; ++s) mbar_init(&bars[s], 1);
-    mbar_fence_init();
-  }
-  __syncwarp();
   const int ntiles = (N + T - 1) / T;
-
-  auto issue = [&](int k) {
-    const int s = k % STAGES, n0 = k * T;
-    const bool use = lane_tma && (n0 + T <= N);
-    const unsigned cnt = __popc(__ballot_sync(kFull, use));
-    if (lane == 0) mbar_arrive_expect_tx(&bars[s], cnt * (3u * T * 8u));
+  if (TMA) {
+    if (lane == 0) {
+#pragma unroll
+      for (int s = 0; s < STAGES; ++s) mbar_init(&bars[s], 1);
+      mbar_fence_init();
+    }
     __syncwarp();
-    if (use) {
-      double* dst = wbuf + (size_t)(s * 3) * kWarp * SEG + (size_t)lane * SEG;
-      bulk_g2s(dst, tp + n0, T * 8, &bars[s]);
-      bulk_g2s(dst + kWarp * SEG, dp + n0, T * 8, &bars[s]);
-      bulk_g2s(dst + 2 * kWarp * SEG, yp + n0, T * 8, &bars[s]);
+  }
+  auto issue = [&](int k) {
+    if (TMA && lane == 0) {
+      const int s = k % STAGES;
+      unsigned char* dst = wbuf + (size_t)s * 3 * kTile;
+      mbar_arrive_expect_tx(&bars[s], 3u * kTile);
+      tma_load_2d(dst, &tm_t, k * T, (int)b0, &bars[s]);
+      tma_load_2d(dst + kTile, &tm_d, k * T, (int)b0, &bars[s]);
+      tma_load_2d(dst + 2 * kTile, &tm_y, k * T, (int)b0, &bars[s]);
     }
   };
 #pragma unroll
@@ -111,41 +118,43 @@ __global__ void __launch_bounds__(kLockThreads) k_loglik_lockstep(BatchArgs a) {
     if (k < ntiles) issue(k);
 
   // ---- recursion state -------------------------------------------------------------------
-  LockState<J> st;
+  double S[J * (J + 1) / 2], Wp[J], DW[J], f[J];
 #pragma unroll
-  for (int i = 0; i < J * (J + 1) / 2; ++i) st.S[i] = 0.0;
+  for (int i = 0; i < J * (J + 1) / 2; ++i) S[i] = 0.0;
 #pragma unroll
-  for (int j = 0; j < J; ++j) { st.W[j] = 0.0; st.DW[j] = 0.0; st.f[j] = 0.0; }
-  double xprev = 0.0, quad = 0.0, tprev = tp[0];
+  for (int j = 0; j < J; ++j) { Wp[j] = 0.0; DW[j] = 0.0; f[j] = 0.0; }
+  double xprev = 0.0, quad = 0.0, tprev = __ldg(tp);
   LogAcc ld;
   ld.init();
   int fail = 0;
+  const int swz = (lane >> 1) & 3;  // 64B swizzle: 16-byte chunk index ^= bits 7..8 of the address
 
   for (int k = 0; k < ntiles; ++k) {
-    const int s = k % STAGES, n0 = k * T;
+    const int n0 = k * T;
     double rt[T], rd[T], ry[T];
-    const bool use = lane_tma && (n0 + T <= N);
-    if (use) {
+    if (TMA) {
+      const int s = k % STAGES;
       mbar_wait(&bars[s], (k / STAGES) & 1);
-      const double* src = wbuf + (size_t)(s * 3) * kWarp * SEG + (size_t)lane * SEG;
+      const unsigned char* src = wbuf + (size_t)s * 3 * kTile + lane * (T * 8);
 #pragma unroll
-      for (int i = 0; i < T; i += 2) {
-        double2 v0 = *reinterpret_cast<const double2*>(src + i);
-        double2 v1 = *reinterpret_cast<const double2*>(src + kWarp * SEG + i);
-        double2 v2 = *reinterpret_cast<const double2*>(src + 2 * kWarp * SEG + i);
-        rt[i] = v0.x; rt[i + 1] = v0.y;
-        rd[i] = v1.x; rd[i + 1] = v1.y;
-        ry[i] = v2.x; ry[i + 1] = v2.y;
+      for (int c = 0; c < T / 2; ++c) {
+        const int off = (c ^ swz) << 4;
+        const double2 v0 = *reinterpret_cast<const double2*>(src + off);
+        const double2 v1 = *reinterpret_cast<const double2*>(src + kTile + off);
+        const double2 v2 = *reinterpret_cast<const double2*>(src + 2 * kTile + off);
+        rt[2 * c] = v0.x; rt[2 * c + 1] = v0.y;
+        rd[2 * c] = v1.x; rd[2 * c + 1] = v1.y;
+        ry[2 * c] = v2.x; ry[2 * c + 1] = v2.y;
       }
+      __syncwarp();
+      if (k + STAGES < ntiles) issue(k + STAGES);
     } else {
 #pragma unroll
       for (int i = 0; i < T; ++i) {
-        int n = min(n0 + i, N - 1);
+        const int n = min(n0 + i, N - 1);
         rt[i] = __ldg(tp + n); rd[i] = __ldg(dp + n); ry[i] = __ldg(yp + n);
       }
     }
-    __syncwarp();
-    if (k + STAGES < ntiles) issue(k + STAGES);
 
 #pragma unroll
     for (int i = 0; i < T; ++i) {
@@ -159,7 +168,7 @@ __global__ void __launch_bounds__(kLockThreads) k_loglik_lockstep(BatchArgs a) {
           if (p < Jc) {  // complex term: rows 2p (cos), 2p+1 (sin)  — cholesky.h:134-147
             double sd, cd;
             sincos(cf[p][3] * tn, &sd, &cd);
-            double e = exp(-cf[p][2] * dx);
+            const double e = exp(-cf[p][2] * dx);
             phi[2 * p] = e;
             u[2 * p] = cf[p][0] * cd + cf[p][1] * sd;
             v[2 * p] = cd;
@@ -184,17 +193,17 @@ __global__ void __launch_bounds__(kLockThreads) k_loglik_lockstep(BatchArgs a) {
         for (int j = 0; j < J; ++j) {
 #pragma unroll
           for (int q = 0; q <= j; ++q)
-            st.S[tri<J>(q, j)] = phi[j] * (phi[q] * (st.S[tri<J>(q, j)] + st.DW[j] * st.W[q]));
+            S[tri<J>(q, j)] = phi[j] * (phi[q] * fma(DW[j], Wp[q], S[tri<J>(q, j)]));
         }
         // forward substitution with the previous column of W — cholesky.h:350-354
         double x = ry[i];
 #pragma unroll
         for (int j = 0; j < J; ++j) {
-          st.f[j] = phi[j] * (st.f[j] + st.W[j] * xprev);
-          x -= u[j] * st.f[j];
+          f[j] = phi[j] * fma(Wp[j], xprev, f[j]);
+          x = fma(-u[j], f[j], x);
         }
         // D_n = A_n - u^T S u ;  W_n = (v - S u) / D_n   — cholesky.h:98, 162-178
-        double Dn = ((rd[i] + sum_ar) + sum_ac) + jitter;
+        double Dn = (rd[i] + asum) + jitter;
         double wn[J];
 #pragma unroll
         for (int j = 0; j < J; ++j) wn[j] = v[j];
@@ -203,23 +212,23 @@ __global__ void __launch_bounds__(kLockThreads) k_loglik_lockstep(BatchArgs a) {
           const double uj = u[j];
 #pragma unroll
           for (int q = 0; q < j; ++q) {
-            const double sq = st.S[tri<J>(q, j)];
+            const double sq = S[tri<J>(q, j)];
             const double tmp = u[q] * sq;
-            Dn -= 2.0 * (uj * tmp);
+            Dn = fma(-2.0 * uj, tmp, Dn);
             wn[j] -= tmp;
-            wn[q] -= uj * sq;
+            wn[q] = fma(-uj, sq, wn[q]);
           }
-          const double tmp = uj * st.S[tri<J>(j, j)];
-          Dn -= uj * tmp;
+          const double tmp = uj * S[tri<J>(j, j)];
+          Dn = fma(-uj, tmp, Dn);
           wn[j] -= tmp;
         }
         if (Dn < 0.0 && fail == 0) fail = n0 + i + 1;  // cholesky.h:176
         const double r = 1.0 / Dn;
 #pragma unroll
-        for (int j = 0; j < J; ++j) { st.DW[j] = wn[j]; st.W[j] = wn[j] * r; }
-        quad += x * x * r;  // cholesky.h:356
+        for (int j = 0; j < J; ++j) { DW[j] = wn[j]; Wp[j] = wn[j] * r; }
+        quad = fma(x * x, r, quad);  // cholesky.h:356
         xprev = x;
-        ld.add(Dn);         // cholesky.h:208
+        ld.add(Dn);                  // cholesky.h:208
       }
     }
     ld.renorm();
@@ -233,19 +242,64 @@ __global__ void __launch_bounds__(kLockThreads) k_loglik_lockstep(BatchArgs a) {
     if (a.out_quad) a.out_quad[b] = q;
     if (a.out_ll) a.out_ll[b] = -0.5 * (q + logdet + (double)N * kLog2Pi);  // celerite.py:214-216
     if (a.status) a.status[b] = fail ? 3 : 0;
+    if (a.fail_index) a.fail_index[b] = fail;
   }
+}
+
+// ---- host side: describe [B][N] to the TMA unit ------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+    else
+      cudaGetLastError();
+  }
+  return fn;
+}
+
+bool make_series_map(CUtensorMap* map, const double* base, long long B, int N, long long stride, int T) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return false;
+  if (stride <= 0 || (stride & 1) || (reinterpret_cast<uintptr_t>(base) & 15u)) return false;
+  if (B > 0x7fffffffLL) return false;
+  cuuint64_t dims[2] = {(cuuint64_t)N, (cuuint64_t)B};
+  cuuint64_t strides[1] = {(cuuint64_t)stride * sizeof(double)};
+  cuuint32_t box[2] = {(cuuint32_t)T, (cuuint32_t)kWarp};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
 }
 
 template <int J, int T, int STAGES>
 cudaError_t launch_one(const BatchArgs& a, cudaStream_t stream) {
-  constexpr int SEG = T + 2;
   constexpr int WARPS = kLockThreads / kWarp;
-  constexpr size_t smem = (size_t)WARPS * STAGES * 3 * kWarp * SEG * sizeof(double) + WARPS * STAGES * sizeof(uint64_t);
-  auto kern = k_loglik_lockstep<J, T, STAGES>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) return e;
+  constexpr size_t smem = (size_t)WARPS * STAGES * 3 * kWarp * T * 8 + WARPS * STAGES * sizeof(uint64_t) + 1024;
   const long long grid = (a.B + kLockThreads - 1) / kLockThreads;
-  kern<<<(unsigned)grid, kLockThreads, smem, stream>>>(a);
+  alignas(64) CUtensorMap mt, md, my;
+  const bool tma = make_series_map(&mt, a.t, a.B, a.N, a.stride, T) &&
+                   make_series_map(&md, a.diag, a.B, a.N, a.stride, T) &&
+                   make_series_map(&my, a.y, a.B, a.N, a.stride, T);
+  if (tma) {
+    auto kern = k_loglik_lockstep<J, T, STAGES, true>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    kern<<<(unsigned)grid, kLockThreads, smem, stream>>>(a, mt, md, my);
+  } else {
+    memset(&mt, 0, sizeof(mt));
+    k_loglik_lockstep<J, T, STAGES, false><<<(unsigned)grid, kLockThreads, 0, stream>>>(a, mt, mt, mt);
+  }
   return cudaGetLastError();
 }
 
@@ -260,8 +314,6 @@ cudaError_t launch_loglik_lockstep(const BatchArgs& a, cudaStream_t stream) {
     case 4: return launch_one<4, 8, 2>(a, stream);
     case 5: return launch_one<5, 8, 2>(a, stream);
     case 6: return launch_one<6, 8, 2>(a, stream);
-    case 7: return launch_one<7, 8, 2>(a, stream);
-    case 8: return launch_one<8, 8, 2>(a, stream);
     default: return cudaErrorInvalidValue;
   }
 }
