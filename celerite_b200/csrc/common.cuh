@@ -137,6 +137,49 @@ struct LogAcc {
   }
 };
 
+// Branch-free variant for the unrolled hot loops (a branch per step would split the loop body
+// into basic blocks and stop the scheduler from interleaving independent chains).  Zero,
+// denormal, negative, inf and nan pivots only raise flags; the caller turns them into the
+// values the reference would produce (log(0) = -inf, log(<0) = nan, ...) at the very end.
+struct LogAccFast {
+  double mant;
+  long long expo;
+  int e32;       // exponents of the current tile
+  int low, high; // saw (<= denormal or negative) / saw (inf or nan)
+
+  __device__ __forceinline__ void init() { mant = 1.0; expo = 0; e32 = 0; low = 0; high = 0; }
+  __device__ __forceinline__ void add(double d) {
+    const int hi = __double2hiint(d);
+    low |= (hi < 0x00100000);
+    high |= (hi >= 0x7ff00000);
+    e32 += ((hi >> 20) & 0x7ff) - 1023;
+    mant *= __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(d));
+  }
+  __device__ __forceinline__ void renorm() {  // at least every 512 adds
+    const int hi = __double2hiint(mant);
+    expo += e32 + (((hi >> 20) & 0x7ff) - 1023);
+    e32 = 0;
+    mant = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(mant));
+  }
+  __device__ __forceinline__ double value() const {
+    if (high) return __longlong_as_double(0x7ff8000000000000LL);
+    if (low) return -__longlong_as_double(0x7ff0000000000000LL);  // a zero pivot: log det = -inf
+    return log(mant) + 0.6931471805599453094 * static_cast<double>(expo);
+  }
+};
+
+// reciprocal without the range guard: two Newton steps on the MUFU.RCP64H seed.  Only valid for
+// normal finite d; the hot loops pair it with LogAccFast, whose flags catch everything else.
+__device__ __forceinline__ double fast_rcp_nocheck(double d) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+  double err = fma(-d, r, 1.0);
+  r = fma(r, err, r);
+  err = fma(-d, r, 1.0);
+  r = fma(r, err, r);
+  return r;
+}
+
 // reciprocal: MUFU.RCP64H seed (about 20 bits) + two Newton steps; falls back to an IEEE
 // division outside the normal range.  Relative error <= ~1 ulp, far inside the 1e-10 bar.
 __device__ __forceinline__ double fast_rcp(double d) {

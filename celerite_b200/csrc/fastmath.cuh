@@ -1,0 +1,103 @@
+// exp / sincos for the recursion kernels.
+//
+// The factorisation needs one exp and one sincos per complex term and time step
+// (cholesky.h:130, 137-140); with the stock libdevice routines more issue slots went to
+// materialising 64-bit polynomial coefficients (UMOV pairs) than to arithmetic.  These versions
+// keep their coefficients in constant memory (uniform-register operands), use a 3-term
+// Cody-Waite reduction that stays accurate up to |x| = 1e9 (no Payne-Hanek branch for the
+// d*t ~ 1e6 arguments of the N = 1e7 series) and fall back to libdevice outside their range.
+// Accuracy: <= ~1.5 ulp (polynomial error 2e-17, see math_tables.cuh), far inside the 1e-10
+// parity bar.
+#pragma once
+
+#include "math_tables.cuh"
+
+namespace cel {
+
+constexpr double kRintMagic = 6755399441055744.0;  // 1.5 * 2^52
+
+template <int N>
+__device__ __forceinline__ double horner(const double* c, double x) {
+  double p = c[N - 1];
+#pragma unroll
+  for (int i = N - 2; i >= 0; --i) p = fma(p, x, c[i]);
+  return p;
+}
+
+// Branch-free core: x must already lie in [-700, 700].
+__device__ __forceinline__ double cel_exp_core(double x) {
+  const double kd = fma(x, tab::kExpR[0], kRintMagic);
+  const int k = __double2loint(kd);
+  const double kf = kd - kRintMagic;
+  double r = fma(kf, tab::kExpR[1], x);
+  r = fma(kf, tab::kExpR[2], r);
+  const double q = horner<10>(tab::kExpQ, r);
+  const double p = fma(r, fma(r, q, 1.0), 1.0);
+  return __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));
+}
+
+// exp of a decay exponent -c*dt for the unrolled hot loops: the argument is clamped to
+// [-700, 700] instead of branching.  exp(-700) = 1e-304 stands in for anything smaller (phi is
+// only ever multiplied into O(1) quantities, so this is far below round-off); a nan argument
+// comes out as exp(-700), which is harmless because a nan time stamp already poisons D_n.
+__device__ __forceinline__ double cel_exp_clamped(double x) {
+  return cel_exp_core(fmin(fmax(x, -700.0), 700.0));
+}
+
+// Branch-free sincos, valid for |x| < 1e9 (callers check the range once per series).
+__device__ __forceinline__ void cel_sincos_core(double x, double* s, double* c) {
+  const double kd = fma(x, tab::kTrigR[0], kRintMagic);
+  const int k = __double2loint(kd);
+  const double kf = kd - kRintMagic;
+  double r = fma(kf, tab::kTrigR[1], x);
+  r = fma(kf, tab::kTrigR[2], r);
+  r = fma(kf, tab::kTrigR[3], r);
+  const double z = r * r;
+  const double ps = horner<6>(tab::kSinP, z);
+  const double pc = horner<6>(tab::kCosP, z);
+  double sn = fma(r * z, ps, r);
+  double cs = fma(z * z, pc, fma(z, -0.5, 1.0));
+  if (k & 1) { const double t = sn; sn = cs; cs = -t; }
+  if (k & 2) { sn = -sn; cs = -cs; }
+  *s = sn;
+  *c = cs;
+}
+constexpr double kFastTrigLimit = 1.0e9;
+
+// Out-of-line stock routines for the rare slow paths (keeps the hot loops small).
+__device__ __noinline__ double slow_exp(double x) { return exp(x); }
+__device__ __noinline__ void slow_sincos(double x, double* s, double* c) { sincos(x, s, c); }
+
+__device__ __forceinline__ double cel_exp(double x) {
+  if (!(fabs(x) < 700.0)) return slow_exp(x);  // overflow / underflow / nan: stock routine
+  const double kd = fma(x, tab::kExpR[0], kRintMagic);
+  const int k = __double2loint(kd);
+  const double kf = kd - kRintMagic;
+  double r = fma(kf, tab::kExpR[1], x);
+  r = fma(kf, tab::kExpR[2], r);
+  const double q = horner<10>(tab::kExpQ, r);
+  const double p = fma(r, fma(r, q, 1.0), 1.0);  // 1 + r + r^2 q(r), in [0.70, 1.42]
+  return __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));
+}
+
+__device__ __forceinline__ void cel_sincos(double x, double* s, double* c) {
+  if (!(fabs(x) < kFastTrigLimit)) { slow_sincos(x, s, c); return; }
+  const double kd = fma(x, tab::kTrigR[0], kRintMagic);
+  const int k = __double2loint(kd);
+  const double kf = kd - kRintMagic;
+  double r = fma(kf, tab::kTrigR[1], x);
+  r = fma(kf, tab::kTrigR[2], r);
+  r = fma(kf, tab::kTrigR[3], r);
+  const double z = r * r;
+  const double ps = horner<6>(tab::kSinP, z);
+  const double pc = horner<6>(tab::kCosP, z);
+  double sn = fma(r * z, ps, r);
+  double cs = fma(z * z, pc, fma(z, -0.5, 1.0));
+  // x = k*pi/2 + r
+  if (k & 1) { const double t = sn; sn = cs; cs = -t; }
+  if (k & 2) { sn = -sn; cs = -cs; }
+  *s = sn;
+  *c = cs;
+}
+
+}  // namespace cel
