@@ -20,7 +20,7 @@ LIB = os.path.join(HERE, "libcelerite_b200.so")
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-         "-Xcompiler", "-fPIC,-O2", "-I", os.path.join(ROOT, "include")]
+         "-Xcompiler", "-fPIC,-O2", "-I", os.path.join(ROOT, "include")] + os.environ.get("CEL_EXTRA_NVCC_FLAGS", "").split()
 
 
 def _sources():

@@ -36,12 +36,19 @@ __device__ __forceinline__ double cel_exp_core(double x) {
   return __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));
 }
 
-// exp of a decay exponent -c*dt for the unrolled hot loops: the argument is clamped to
-// [-700, 700] instead of branching.  exp(-700) = 1e-304 stands in for anything smaller (phi is
-// only ever multiplied into O(1) quantities, so this is far below round-off); a nan argument
-// comes out as exp(-700), which is harmless because a nan time stamp already poisons D_n.
+// exp of a decay exponent -c*dt for the unrolled hot loops, without a range branch: the power
+// of two is clamped to [-1022, 1023] with one integer min/max, so arguments below -708 come
+// out as ~1e-308 instead of a denormal/zero and arguments above 709 as ~1e308 instead of inf.
+// phi only ever multiplies O(1) quantities, so both are far below round-off; nan stays nan.
 __device__ __forceinline__ double cel_exp_clamped(double x) {
-  return cel_exp_core(fmin(fmax(x, -700.0), 700.0));
+  const double kd = fma(x, tab::kExpR[0], kRintMagic);
+  const int k = min(max(__double2loint(kd), -1022), 1023);
+  const double kf = kd - kRintMagic;
+  double r = fma(kf, tab::kExpR[1], x);
+  r = fma(kf, tab::kExpR[2], r);
+  const double q = horner<10>(tab::kExpQ, r);
+  const double p = fma(r, fma(r, q, 1.0), 1.0);
+  return __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));
 }
 
 // Branch-free sincos, valid for |x| < 1e9 (callers check the range once per series).
@@ -55,12 +62,13 @@ __device__ __forceinline__ void cel_sincos_core(double x, double* s, double* c) 
   const double z = r * r;
   const double ps = horner<6>(tab::kSinP, z);
   const double pc = horner<6>(tab::kCosP, z);
-  double sn = fma(r * z, ps, r);
-  double cs = fma(z * z, pc, fma(z, -0.5, 1.0));
-  if (k & 1) { const double t = sn; sn = cs; cs = -t; }
-  if (k & 2) { sn = -sn; cs = -cs; }
-  *s = sn;
-  *c = cs;
+  const double sn = fma(r * z, ps, r);
+  const double cs = fma(z * z, pc, fma(z, -0.5, 1.0));
+  // x = k*pi/2 + r: swap for odd k, then flip signs with integer ops (keeps the fp64 pipe free)
+  const bool sw = (k & 1) != 0;
+  const double a = sw ? cs : sn, b = sw ? sn : cs;
+  *s = __hiloint2double(__double2hiint(a) ^ ((k & 2) << 30), __double2loint(a));
+  *c = __hiloint2double(__double2hiint(b) ^ (((k + 1) & 2) << 30), __double2loint(b));
 }
 constexpr double kFastTrigLimit = 1.0e9;
 

@@ -56,23 +56,26 @@ struct LockState {
   int fail;
 };
 
-// G consecutive time steps of one series.  FAST = branch-free math (the whole body is one basic
-// block, so the G independent exp/sincos chains and the serial recursion interleave); otherwise
-// guarded routines with out-of-line stock fallbacks.  `nvalid` < G only in the ragged tail.
-template <int J, int G, bool FAST, bool GUARD>
-__device__ __forceinline__ void lock_group(LockState<J>& st, const double (&cf)[(J + 1) / 2][4], const int Jc,
-                                           const double asum, const double jitter, const double (&tt)[G],
-                                           const double (&dd)[G], const double (&yy)[G], const double tprev,
-                                           const int n0, const int nvalid) {
-  constexpr int NP = (J + 1) / 2;
+// phi, u, v of G consecutive time steps (cholesky.h:127-147): the part of the work that does not
+// depend on the recursion.
+template <int J, int G>
+struct LockGen {
   double phi[G][J], u[G][J], v[G][J];
+};
+
+// FAST = branch-free math (no basic-block boundaries, so independent chains interleave);
+// otherwise guarded routines with out-of-line stock fallbacks.
+template <int J, int G, bool FAST, bool ALLC>
+__device__ __forceinline__ void lock_gen(LockGen<J, G>& o, const double (&cf)[(J + 1) / 2][4], const int Jc,
+                                         const double (&tt)[G], const double tprev) {
+  constexpr int NP = (J + 1) / 2;
 #pragma unroll
   for (int g = 0; g < G; ++g) {
     const double tn = tt[g];
     const double dx = tn - (g == 0 ? tprev : tt[g == 0 ? 0 : g - 1]);
 #pragma unroll
     for (int p = 0; p < NP; ++p) {
-      if (p < Jc) {  // complex term: rows 2p (cos), 2p+1 (sin)  — cholesky.h:134-147
+      if (ALLC || p < Jc) {  // complex term: rows 2p (cos), 2p+1 (sin)  — cholesky.h:134-147
         double sd, cd, e;
         if (FAST) {
           cel_sincos_core(cf[p][3] * tn, &sd, &cd);
@@ -81,62 +84,79 @@ __device__ __forceinline__ void lock_group(LockState<J>& st, const double (&cf)[
           cel_sincos(cf[p][3] * tn, &sd, &cd);
           e = cel_exp(-cf[p][2] * dx);
         }
-        phi[g][2 * p] = e;
-        u[g][2 * p] = cf[p][0] * cd + cf[p][1] * sd;
-        v[g][2 * p] = cd;
+        o.phi[g][2 * p] = e;
+        o.u[g][2 * p] = fma(cf[p][0], cd, cf[p][1] * sd);
+        o.v[g][2 * p] = cd;
         if (2 * p + 1 < J) {
-          phi[g][2 * p + 1] = e;
-          u[g][2 * p + 1] = cf[p][0] * sd - cf[p][1] * cd;
-          v[g][2 * p + 1] = sd;
+          o.phi[g][2 * p + 1] = e;
+          o.u[g][2 * p + 1] = fma(cf[p][0], sd, -(cf[p][1] * cd));
+          o.v[g][2 * p + 1] = sd;
         }
       } else {  // two real terms — cholesky.h:129-133
-        phi[g][2 * p] = FAST ? cel_exp_clamped(-cf[p][1] * dx) : cel_exp(-cf[p][1] * dx);
-        u[g][2 * p] = cf[p][0];
-        v[g][2 * p] = 1.0;
+        o.phi[g][2 * p] = FAST ? cel_exp_clamped(-cf[p][1] * dx) : cel_exp(-cf[p][1] * dx);
+        o.u[g][2 * p] = cf[p][0];
+        o.v[g][2 * p] = 1.0;
         if (2 * p + 1 < J) {
-          phi[g][2 * p + 1] = FAST ? cel_exp_clamped(-cf[p][3] * dx) : cel_exp(-cf[p][3] * dx);
-          u[g][2 * p + 1] = cf[p][2];
-          v[g][2 * p + 1] = 1.0;
+          o.phi[g][2 * p + 1] = FAST ? cel_exp_clamped(-cf[p][3] * dx) : cel_exp(-cf[p][3] * dx);
+          o.u[g][2 * p + 1] = cf[p][2];
+          o.v[g][2 * p + 1] = 1.0;
         }
       }
     }
   }
+}
+
+// The serial part: G steps of cholesky.h:154-178 fused with the forward substitution of
+// dot_solve (cholesky.h:350-356).  ALLC: every row belongs to a complex pair, whose two rows
+// share phi, so the products phi_q*phi_j are formed once per pair of pairs.
+template <int J, int G, bool ALLC, bool GUARD>
+__device__ __forceinline__ void lock_rec(LockState<J>& st, const LockGen<J, G>& gn, const double asum,
+                                         const double jitter, const double (&dd)[G], const double (&yy)[G],
+                                         const int n0, const int nvalid) {
 #pragma unroll
   for (int g = 0; g < G; ++g) {
     if (!GUARD || g < nvalid) {
       // S <- phi phi^T o (S + D W W^T)   — cholesky.h:154-160
+      if constexpr (ALLC) {
+        constexpr int NP = J / 2;
+        double pp[NP][NP];
 #pragma unroll
-      for (int j = 0; j < J; ++j) {
+        for (int a = 0; a < NP; ++a)
 #pragma unroll
-        for (int q = 0; q <= j; ++q)
-          st.S[tri<J>(q, j)] = phi[g][j] * (phi[g][q] * fma(st.DW[j], st.Wp[q], st.S[tri<J>(q, j)]));
+          for (int c = a; c < NP; ++c) pp[a][c] = gn.phi[g][2 * a] * gn.phi[g][2 * c];
+#pragma unroll
+        for (int j = 0; j < J; ++j)
+#pragma unroll
+          for (int q = 0; q <= j; ++q)
+            st.S[tri<J>(q, j)] = pp[q / 2][j / 2] * fma(st.DW[j], st.Wp[q], st.S[tri<J>(q, j)]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < J; ++j)
+#pragma unroll
+          for (int q = 0; q <= j; ++q)
+            st.S[tri<J>(q, j)] =
+                gn.phi[g][j] * (gn.phi[g][q] * fma(st.DW[j], st.Wp[q], st.S[tri<J>(q, j)]));
       }
       // forward substitution with the previous column of W — cholesky.h:350-354
       double x = yy[g];
 #pragma unroll
       for (int j = 0; j < J; ++j) {
-        st.f[j] = phi[g][j] * fma(st.Wp[j], st.xprev, st.f[j]);
-        x = fma(-u[g][j], st.f[j], x);
+        st.f[j] = gn.phi[g][j] * fma(st.Wp[j], st.xprev, st.f[j]);
+        x = fma(-gn.u[g][j], st.f[j], x);
       }
-      // D_n = A_n - u^T S u ;  W_n = (v - S u) / D_n   — cholesky.h:98, 162-178
+      // su = S u (symmetric matvec); D_n = A_n - u.su ; W_n = (v - su)/D_n — cholesky.h:98, 162-178
       double Dn = (dd[g] + asum) + jitter;
       double wn[J];
 #pragma unroll
-      for (int j = 0; j < J; ++j) wn[j] = v[g][j];
-#pragma unroll
       for (int j = 0; j < J; ++j) {
-        const double uj = u[g][j];
+        double su = 0.0;
 #pragma unroll
-        for (int q = 0; q < j; ++q) {
-          const double sq = st.S[tri<J>(q, j)];
-          const double tmp = u[g][q] * sq;
-          Dn = fma(-2.0 * uj, tmp, Dn);
-          wn[j] -= tmp;
-          wn[q] = fma(-uj, sq, wn[q]);
+        for (int q = 0; q < J; ++q) {
+          const double s = (q <= j) ? st.S[tri<J>(q, j)] : st.S[tri<J>(j, q)];
+          su = (q == 0) ? s * gn.u[g][0] : fma(s, gn.u[g][q], su);
         }
-        const double tmp = uj * st.S[tri<J>(j, j)];
-        Dn = fma(-uj, tmp, Dn);
-        wn[j] -= tmp;
+        Dn = fma(-gn.u[g][j], su, Dn);
+        wn[j] = gn.v[g][j] - su;
       }
       st.fail = (Dn < 0.0 && st.fail == 0) ? n0 + g + 1 : st.fail;  // cholesky.h:176
       const double r = fast_rcp_nocheck(Dn);
@@ -153,8 +173,8 @@ __device__ __forceinline__ void lock_group(LockState<J>& st, const double (&cf)[
 // lets cfg2's 2048 warps run as ONE wave on 148 SMs
 constexpr int lock_maxreg(int J) { return J <= 2 ? 128 : (J <= 4 ? 200 : 255); }
 
-template <int J, int G, int T, int STAGES, bool TMA>
-__global__ void __launch_bounds__(kLockThreads) __maxnreg__(lock_maxreg(J))
+template <int J, int G, int T, int STAGES, bool TMA, bool ALLC, int CAP, bool PIPE>
+__global__ void __launch_bounds__(kLockThreads) __maxnreg__(CAP)
 k_loglik_lockstep(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const __grid_constant__ CUtensorMap tm_d,
                   const __grid_constant__ CUtensorMap tm_y) {
   static_assert(T == 8, "64-byte swizzled rows: 8 doubles per row segment");
@@ -222,6 +242,10 @@ k_loglik_lockstep(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const _
     if (TMA && lane == 0) {
       const int s = k % STAGES;
       unsigned char* dst = wbuf + (size_t)s * 3 * kTile;
+      // The slot was just read through the generic proxy (LDS); the TMA write that refills it
+      // goes through the async proxy.  Without this proxy fence the refill can overtake the
+      // reads on B200 (observed: a few warps per launch consumed half-overwritten tiles).
+      fence_async_smem();
       mbar_arrive_expect_tx(&bars[s], 3u * kTile);
       tma_load_2d(dst, &tm_t, k * T, (int)b0, &bars[s]);
       tma_load_2d(dst + kTile, &tm_d, k * T, (int)b0, &bars[s]);
@@ -239,7 +263,7 @@ k_loglik_lockstep(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const _
   for (int j = 0; j < J; ++j) { st.Wp[j] = 0.0; st.DW[j] = 0.0; st.f[j] = 0.0; }
   st.xprev = 0.0; st.quad = 0.0; st.fail = 0;
   st.ld.init();
-  double tprev = __ldg(tp);
+  const double tprev = __ldg(tp);
   const int swz = (lane >> 1) & 3;  // 64B swizzle: 16-byte chunk index ^= bits 7..8 of the address
 
   // fetch the G points starting at n0 (h = n0 % T inside tile k) into registers
@@ -271,30 +295,66 @@ k_loglik_lockstep(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const _
     }
   };
 
+  // Software pipeline: while the serial recursion of group g runs, the generators of group g+1
+  // (independent exp/sincos chains) are evaluated in the same basic block and hide its latency.
   const int nfull = N / G;
-  if (warp_fast) {
+  auto fetch_or_zero = [&](int n0, double (&tt)[G], double (&dd)[G], double (&yy)[G]) {
+    if (n0 < N) {
+      fetch(n0, tt, dd, yy);
+    } else {
+#pragma unroll
+      for (int g = 0; g < G; ++g) { tt[g] = 0.0; dd[g] = 0.0; yy[g] = 0.0; }
+    }
+  };
+  LockGen<J, G> ga, gb;
+  double ta[G], da[G], ya[G], tb[G], db[G], yb[G];
+  fetch_or_zero(0, ta, da, ya);
+  if (warp_fast && !PIPE) {
+    // plain order: generators of G steps, then their recursion (lowest register pressure)
     for (int grp = 0; grp < nfull; ++grp) {
-      double tt[G], dd[G], yy[G];
-      fetch(grp * G, tt, dd, yy);
-      lock_group<J, G, true, false>(st, cf, Jc, asum, jitter, tt, dd, yy, tprev, grp * G, G);
-      tprev = tt[G - 1];
-      if ((grp & 63) == 63) st.ld.renorm();
+      lock_gen<J, G, true, ALLC>(ga, cf, Jc, ta, grp == 0 ? tprev : tb[G - 1]);
+      lock_rec<J, G, ALLC, false>(st, ga, asum, jitter, da, ya, grp * G, G);
+      tb[G - 1] = ta[G - 1];
+      fetch_or_zero((grp + 1) * G, ta, da, ya);
+      if ((grp & 127) == 127) st.ld.renorm();
+    }
+    lock_gen<J, G, true, ALLC>(ga, cf, Jc, ta, tb[G - 1]);
+  } else if (warp_fast) {
+    lock_gen<J, G, true, ALLC>(ga, cf, Jc, ta, tprev);
+    int grp = 0;
+    for (; grp + 1 < nfull; grp += 2) {
+      fetch_or_zero((grp + 1) * G, tb, db, yb);
+      lock_gen<J, G, true, ALLC>(gb, cf, Jc, tb, ta[G - 1]);
+      lock_rec<J, G, ALLC, false>(st, ga, asum, jitter, da, ya, grp * G, G);
+      fetch_or_zero((grp + 2) * G, ta, da, ya);
+      lock_gen<J, G, true, ALLC>(ga, cf, Jc, ta, tb[G - 1]);
+      lock_rec<J, G, ALLC, false>(st, gb, asum, jitter, db, yb, (grp + 1) * G, G);
+      if ((grp & 126) == 126) st.ld.renorm();
+    }
+    if (grp < nfull) {  // odd number of full groups
+      fetch_or_zero((grp + 1) * G, tb, db, yb);
+      lock_gen<J, G, true, ALLC>(gb, cf, Jc, tb, ta[G - 1]);
+      lock_rec<J, G, ALLC, false>(st, ga, asum, jitter, da, ya, grp * G, G);
+      ga = gb;
+#pragma unroll
+      for (int g = 0; g < G; ++g) { da[g] = db[g]; ya[g] = yb[g]; }
     }
   } else {
+    lock_gen<J, G, false, ALLC>(ga, cf, Jc, ta, tprev);
 #pragma unroll 1
     for (int grp = 0; grp < nfull; ++grp) {
-      double tt[G], dd[G], yy[G];
-      fetch(grp * G, tt, dd, yy);
-      lock_group<J, G, false, false>(st, cf, Jc, asum, jitter, tt, dd, yy, tprev, grp * G, G);
-      tprev = tt[G - 1];
-      if ((grp & 63) == 63) st.ld.renorm();
+      fetch_or_zero((grp + 1) * G, tb, db, yb);
+      lock_gen<J, G, false, ALLC>(gb, cf, Jc, tb, ta[G - 1]);
+      lock_rec<J, G, ALLC, false>(st, ga, asum, jitter, da, ya, grp * G, G);
+      ga = gb;
+#pragma unroll
+      for (int g = 0; g < G; ++g) { ta[g] = tb[g]; da[g] = db[g]; ya[g] = yb[g]; }
+      if ((grp & 127) == 127) st.ld.renorm();
     }
   }
-  if (nfull * G < N) {  // ragged tail (< G steps); out-of-range points are zero-filled / clamped
-    double tt[G], dd[G], yy[G];
-    fetch(nfull * G, tt, dd, yy);
-    lock_group<J, G, false, true>(st, cf, Jc, asum, jitter, tt, dd, yy, tprev, nfull * G, N - nfull * G);
-  }
+  // ragged tail (< G steps): its generators are already in ga (out-of-range points were
+  // zero-filled / clamped and are skipped by the guard)
+  if (nfull * G < N) lock_rec<J, G, ALLC, true>(st, ga, asum, jitter, da, ya, nfull * G, N - nfull * G);
   st.ld.renorm();
 
   if (active) {
@@ -345,23 +405,29 @@ bool make_series_map(CUtensorMap* map, const double* base, long long B, int N, l
   return r == CUDA_SUCCESS;
 }
 
-template <int J, int G, int T, int STAGES>
+template <int J, int G, int T, int STAGES, int CAP = lock_maxreg(J), bool PIPE = false>
 cudaError_t launch_one(const BatchArgs& a, cudaStream_t stream) {
   constexpr int WARPS = kLockThreads / kWarp;
   constexpr size_t smem = (size_t)WARPS * STAGES * 3 * kWarp * T * 8 + WARPS * STAGES * sizeof(uint64_t) + 1024;
   const long long grid = (a.B + kLockThreads - 1) / kLockThreads;
   alignas(64) CUtensorMap mt, md, my;
-  const bool tma = make_series_map(&mt, a.t, a.B, a.N, a.stride, T) &&
+  static const bool no_tma = getenv("CEL_LOCK_NOTMA") != nullptr;  // debugging knob: force the plain-load path
+  const bool tma = !no_tma && make_series_map(&mt, a.t, a.B, a.N, a.stride, T) &&
                    make_series_map(&md, a.diag, a.B, a.N, a.stride, T) &&
                    make_series_map(&my, a.y, a.B, a.N, a.stride, T);
+  constexpr bool kEven = (J % 2) == 0;
+  const bool allc = kEven && a.Jr == 0;  // all rows are (cos,sin) pairs: SHO-type kernels
   if (tma) {
-    auto kern = k_loglik_lockstep<J, G, T, STAGES, true>;
+    auto kern = allc ? k_loglik_lockstep<J, G, T, STAGES, true, kEven, CAP, PIPE> : k_loglik_lockstep<J, G, T, STAGES, true, false, CAP, PIPE>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     kern<<<(unsigned)grid, kLockThreads, smem, stream>>>(a, mt, md, my);
   } else {
     memset(&mt, 0, sizeof(mt));
-    k_loglik_lockstep<J, G, T, STAGES, false><<<(unsigned)grid, kLockThreads, 0, stream>>>(a, mt, mt, mt);
+    if (allc)
+      k_loglik_lockstep<J, G, T, STAGES, false, kEven, CAP, PIPE><<<(unsigned)grid, kLockThreads, 0, stream>>>(a, mt, mt, mt);
+    else
+      k_loglik_lockstep<J, G, T, STAGES, false, false, CAP, PIPE><<<(unsigned)grid, kLockThreads, 0, stream>>>(a, mt, mt, mt);
   }
   return cudaGetLastError();
 }
@@ -371,10 +437,16 @@ cudaError_t launch_one(const BatchArgs& a, cudaStream_t stream) {
 cudaError_t launch_loglik_lockstep(const BatchArgs& a, cudaStream_t stream) {
   const int J = a.Jr + 2 * a.Jc;
   switch (J) {
-    case 1: return launch_one<1, 4, 8, 2>(a, stream);
+    case 1: return launch_one<1, 2, 8, 2>(a, stream);
     case 2: {
-      static const char* g = getenv("CEL_LOCK_G");  // tuning knob: generator batch of the J=2 kernel
-      return (g && g[0] == '2') ? launch_one<2, 2, 8, 2>(a, stream) : launch_one<2, 4, 8, 2>(a, stream);
+      static const char* g = getenv("CEL_LOCK_VARIANT");  // tuning knob for the J=2 kernel
+      const char v = g ? g[0] : 'a';
+      if (v == 'b') return launch_one<2, 2, 8, 2, 168, true>(a, stream);
+      if (v == 'e') return launch_one<2, 2, 8, 2, 128, true>(a, stream);
+      if (v == 'c') return launch_one<2, 2, 8, 2, 128, false>(a, stream);
+      if (v == 'd') return launch_one<2, 4, 8, 2, 168, false>(a, stream);
+      if (v == 'f') return launch_one<2, 4, 8, 2, 128, false>(a, stream);
+      return launch_one<2, 2, 8, 2, 128, false>(a, stream);
     }
     case 3: return launch_one<3, 2, 8, 2>(a, stream);
     case 4: return launch_one<4, 2, 8, 2>(a, stream);

@@ -134,3 +134,26 @@ def test_full_size_properties(bs):
                                        np.ascontiguousarray(b["y"][pick]))
     assert rel_sum(ld1.cpu().numpy()[pick], ref[:, 0], N) < RTOL_SCALAR
     assert rel_sum(q1.cpu().numpy()[pick], ref[:, 1], N) < RTOL_SCALAR
+
+
+def test_repeatable_at_full_size(bs):
+    """Regression test for a cross-proxy hazard in the TMA staging ring (generic-proxy reads of a
+    slot vs the async-proxy refill): the cfg2-sized launch must give bit-identical results on
+    every repetition."""
+    import torch
+    from celerite_b200 import synth
+    B, N = 65536, 2000
+    rng = np.random.Generator(np.random.PCG64(4))
+    c = synth.make_coeffs(rng, B, 0, 1)
+    t = np.empty((B, N)); d = np.empty((B, N)); y = np.empty((B, N))
+    synth.fill_series(rng, t, d, y)
+    dev = torch.device("cuda:0")
+    tt = lambda a: torch.from_numpy(a).to(dev)  # noqa: E731
+    C, T, D, Y = tt(c), tt(t), tt(d), tt(y)
+    ll0, ld0, q0, st0 = bs.log_likelihood(C, T, D, Y, 0, 1, return_parts=True)
+    torch.cuda.synchronize()
+    assert int(st0.sum()) == 0
+    for _ in range(25):
+        ll, ld, q, st = bs.log_likelihood(C, T, D, Y, 0, 1, return_parts=True)
+        torch.cuda.synchronize()
+        assert torch.equal(ld, ld0) and torch.equal(q, q0) and torch.equal(st, st0)
