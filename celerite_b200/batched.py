@@ -106,6 +106,40 @@ class BatchedSolver(object):
         ll = torch.where(torch.isfinite(out[2]), out[2], torch.full_like(out[2], float("-inf")))
         return (ll, out[0], out[1], status) if return_parts else ll
 
+    def grad_log_likelihood(self, coeffs, t, diag, y, Jr, Jc):
+        """Per series: val = -0.5*(y^T K^-1 y + log det K) (no constant) and its gradient with
+        respect to the coefficient row, in the layout of the reference's gradient vector
+        (solver.cpp:392-434, incl. the zeroed jitter slot for jitter <= DBL_EPSILON).
+        Returns (val[B], grad[B, P], status[B]); numpy in -> numpy out, torch CUDA in -> torch out."""
+        Pn = 1 + 2 * Jr + 4 * Jc
+        if _is_torch(t):
+            import torch
+            for a in (coeffs, t, diag, y):
+                if not (a.is_cuda and a.dtype == torch.float64 and a.is_contiguous()):
+                    raise RuntimeError("expected contiguous float64 CUDA tensors")
+            B, N, stride, cstride = self._shapes(coeffs, t, Jr, Jc)
+            val = torch.empty(B, dtype=torch.float64, device=t.device)
+            grad = torch.empty((B, Pn), dtype=torch.float64, device=t.device)
+            status = torch.empty(B, dtype=torch.int32, device=t.device)
+            self._lib.cel_set_stream(self._h, C.c_void_p(torch.cuda.current_stream(t.device).cuda_stream or 1))
+            p = lambda a: C.c_void_p(a.data_ptr())  # noqa: E731
+            flags = 0
+        else:
+            coeffs = np.ascontiguousarray(coeffs, dtype=np.float64)
+            t = np.ascontiguousarray(t, dtype=np.float64)
+            diag = np.ascontiguousarray(diag, dtype=np.float64)
+            y = np.ascontiguousarray(y, dtype=np.float64)
+            B, N, stride, cstride = self._shapes(coeffs, t, Jr, Jc)
+            val = np.empty(B); grad = np.empty((B, Pn)); status = np.empty(B, dtype=np.int32)
+            p = lambda a: C.c_void_p(a.ctypes.data)  # noqa: E731
+            flags = _capi.HOST_POINTERS
+        if diag.shape != t.shape or y.shape != t.shape:
+            raise RuntimeError("dimension mismatch")
+        rc = self._lib.cel_batched_grad_log_likelihood(self._h, B, N, stride, Jr, Jc, p(coeffs), cstride,
+                                                       p(t), p(diag), p(y), p(val), p(grad), p(status), flags)
+        _capi.check(rc, self._h)
+        return val, grad, status
+
     def raw_log_likelihood(self, B, N, stride, Jr, Jc, coeffs_ptr, cstride, t_ptr, diag_ptr, y_ptr,
                            logdet_ptr, quad_ptr, ll_ptr, status_ptr, flags=0, stream=None):
         """Thin pass-through of cel_batched_log_likelihood for callers that manage memory

@@ -248,20 +248,148 @@ int cel_grad_log_likelihood(cel_solver* s, double jitter, int Jr, const double* 
                             const double* d_comp, int Jg, const double* A, const double* U, const double* V,
                             int N, const double* x, const double* y, const double* diag, double* val,
                             double* grad) {
-  (void)jitter; (void)Jr; (void)a_real; (void)c_real; (void)Jc; (void)a_comp; (void)b_comp; (void)c_comp;
-  (void)d_comp; (void)Jg; (void)A; (void)U; (void)V; (void)N; (void)x; (void)y; (void)diag; (void)val; (void)grad;
   if (!s) return CEL_INVALID_ARGUMENT;
-  CEL_FAIL(s, CEL_UNSUPPORTED, "cel_grad_log_likelihood is not implemented yet");
+  if (N < 1 || !x || !y || !diag || !val || !grad) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "dimension mismatch");
+  if (Jg < 0 || (Jg > 0 && (!U || !V))) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "general term needs U and V");
+  std::vector<double> row;
+  int rc = pack_coeffs(s, jitter, Jr, a_real, c_real, Jc, a_comp, b_comp, c_comp, d_comp, row);
+  if (rc != CEL_OK) return rc;
+  const int J = Jr + 2 * Jc + Jg, P = (int)row.size();
+  if (J > cel::kCoopMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "J > 32 is not supported yet");
+  CEL_CUDA_TRY(s, cudaSetDevice(s->device));
+  cudaStream_t st = s->stream;
+  double* res = static_cast<double*>(s->pinned);
+  if (J == 0) {
+    // jitter only (cholesky.h:90-95, 334-339): D = diag + jitter; d/djitter = sum(0.5 y^2/D^2 - 0.5/D)
+    CEL_CUDA_TRY(s, s->scratch0.reserve(dbytes(2 * (size_t)N)));
+    CEL_CUDA_TRY(s, s->out0.reserve(64));
+    double* dy = s->scratch0.d();
+    double* dd = dy + N;
+    CEL_CUDA_TRY(s, cudaMemcpyAsync(dy, y, dbytes(N), cudaMemcpyHostToDevice, st));
+    CEL_CUDA_TRY(s, cudaMemcpyAsync(dd, diag, dbytes(N), cudaMemcpyHostToDevice, st));
+    CEL_CUDA_TRY(s, cel::launch_jitter_only_grad(N, dd, dy, jitter, s->out0.d(), st));
+    s->launches += 1;
+    CEL_CUDA_TRY(s, cudaMemcpyAsync(res, s->out0.p, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
+    *val = res[0];
+    grad[0] = (jitter > DBL_EPSILON) ? res[1] : 0.0;
+    return CEL_OK;
+  }
+  const int seg = cel::grad_default_segment(N);
+  const size_t nscr = cel::grad_scratch_doubles(1, N, J, seg);
+  const size_t nin = 3 * (size_t)N + (A ? N : 0) + 2 * (size_t)Jg * N + P;
+  CEL_CUDA_TRY(s, s->scratch0.reserve(dbytes(nscr)));
+  CEL_CUDA_TRY(s, s->scratch1.reserve(dbytes(nin)));
+  CEL_CUDA_TRY(s, s->scratch2.reserve(dbytes((size_t)P + 8)));
+  double* dx = s->scratch1.d();
+  double* dy = dx + N;
+  double* dd = dy + N;
+  double* dA = dd + N;
+  double* dU = dA + (A ? N : 0);
+  double* dV = dU + (size_t)Jg * N;
+  double* dc = dV + (size_t)Jg * N;
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(dx, x, dbytes(N), cudaMemcpyHostToDevice, st));
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(dy, y, dbytes(N), cudaMemcpyHostToDevice, st));
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(dd, diag, dbytes(N), cudaMemcpyHostToDevice, st));
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(dc, row.data(), dbytes(P), cudaMemcpyHostToDevice, st));
+  if (A) CEL_CUDA_TRY(s, cudaMemcpyAsync(dA, A, dbytes(N), cudaMemcpyHostToDevice, st));
+  if (Jg > 0) {
+    CEL_CUDA_TRY(s, cudaMemcpyAsync(dU, U, dbytes((size_t)Jg * N), cudaMemcpyHostToDevice, st));
+    CEL_CUDA_TRY(s, cudaMemcpyAsync(dV, V, dbytes((size_t)Jg * N), cudaMemcpyHostToDevice, st));
+  }
+  cel::GradArgs a{};
+  a.B = 1; a.N = N; a.stride = N; a.Jr = Jr; a.Jc = Jc; a.Jg = Jg;
+  a.coeffs = dc; a.coeff_stride = P;
+  a.t = dx; a.diag = dd; a.y = dy;
+  a.A = A ? dA : nullptr; a.U = Jg > 0 ? dU : nullptr; a.V = Jg > 0 ? dV : nullptr;
+  double* dout = s->scratch2.d();
+  a.out_val = dout; a.out_grad = dout + 2;
+  a.status = reinterpret_cast<int*>(dout + 1);
+  a.scratch = s->scratch0.d(); a.seg = seg;
+  CEL_CUDA_TRY(s, cel::launch_grad_coop(a, st));
+  s->launches += 1;
+  if (s->pinned_cap < dbytes((size_t)P + 2)) CEL_FAIL(s, CEL_UNSUPPORTED, "too many coefficients");
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(res, dout, dbytes((size_t)P + 2), cudaMemcpyDeviceToHost, st));
+  CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
+  if (*reinterpret_cast<int*>(res + 1) != 0)
+    CEL_FAIL(s, CEL_NOT_POSITIVE_DEFINITE, "failed to factorize or solve matrix");
+  *val = res[0];
+  for (int i = 0; i < P; ++i) grad[i] = res[2 + i];
+  return CEL_OK;
 }
 
 int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t stride, int Jr, int Jc,
                                     const double* coeffs, int64_t coeff_stride, const double* t,
                                     const double* diag, const double* y, double* out_val, double* out_grad,
                                     int32_t* status, unsigned flags) {
-  (void)B; (void)N; (void)stride; (void)Jr; (void)Jc; (void)coeffs; (void)coeff_stride; (void)t; (void)diag;
-  (void)y; (void)out_val; (void)out_grad; (void)status; (void)flags;
   if (!s) return CEL_INVALID_ARGUMENT;
-  CEL_FAIL(s, CEL_UNSUPPORTED, "cel_batched_grad_log_likelihood is not implemented yet");
+  if (B < 0 || N < 1 || Jr < 0 || Jc < 0 || stride < 0 || coeff_stride < 0)
+    CEL_FAIL(s, CEL_INVALID_ARGUMENT, "negative size");
+  if (stride != 0 && stride < N) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "stride < N");
+  const int J = Jr + 2 * Jc, P = 1 + 2 * Jr + 4 * Jc;
+  if (coeff_stride != 0 && coeff_stride < P) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "coeff_stride < 1+2Jr+4Jc");
+  if (J < 1 || J > cel::kCoopMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "batched gradient supports 1 <= J <= 32");
+  if (!coeffs || !t || !diag || !y || !out_val || !out_grad) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null pointer");
+  if (B == 0) return CEL_OK;
+  CEL_CUDA_TRY(s, cudaSetDevice(s->device));
+  cudaStream_t st = s->stream;
+  const int seg = cel::grad_default_segment(N);
+
+  cel::GradArgs a{};
+  a.N = N; a.Jr = Jr; a.Jc = Jc; a.Jg = 0; a.seg = seg;
+  if (!(flags & CEL_HOST_POINTERS)) {
+    CEL_CUDA_TRY(s, s->scratch0.reserve(dbytes(cel::grad_scratch_doubles(B, N, J, seg))));
+    a.B = B; a.stride = stride; a.coeffs = coeffs; a.coeff_stride = coeff_stride;
+    a.t = t; a.diag = diag; a.y = y;
+    a.out_val = out_val; a.out_grad = out_grad; a.status = status; a.scratch = s->scratch0.d();
+    CEL_CUDA_TRY(s, cel::launch_grad_coop(a, st));
+    s->launches += 1;
+    return CEL_OK;
+  }
+  // host buffers: chunks of the batch, staged one after the other on the handle's stream
+  const size_t series_bytes = dbytes(N);
+  int64_t chunk = (int64_t)((size_t)(256u << 20) / (3 * series_bytes));
+  if (chunk < 64) chunk = 64;
+  if (chunk > B) chunk = B;
+  if (stride == 0) chunk = B;
+  const size_t ndata = (stride == 0 ? 1 : (size_t)chunk) * N;
+  CEL_CUDA_TRY(s, s->scratch0.reserve(dbytes(cel::grad_scratch_doubles(chunk, N, J, seg))));
+  CEL_CUDA_TRY(s, s->stage_t[0].reserve(dbytes(ndata)));
+  CEL_CUDA_TRY(s, s->stage_d[0].reserve(dbytes(ndata)));
+  CEL_CUDA_TRY(s, s->stage_y[0].reserve(dbytes(ndata)));
+  CEL_CUDA_TRY(s, s->stage_c[0].reserve(dbytes((coeff_stride == 0 ? 1 : (size_t)chunk) * P)));
+  CEL_CUDA_TRY(s, s->stage_o[0].reserve(dbytes((size_t)chunk * (P + 1))));
+  CEL_CUDA_TRY(s, s->stage_s[0].reserve((size_t)chunk * sizeof(int)));
+  for (int64_t b0 = 0; b0 < B; b0 += chunk) {
+    const int64_t nb = (b0 + chunk <= B) ? chunk : (B - b0);
+    const size_t ns = (stride == 0) ? 1 : (size_t)nb;
+    const double* ht = t + (stride == 0 ? 0 : b0 * stride);
+    const double* hd = diag + (stride == 0 ? 0 : b0 * stride);
+    const double* hy = y + (stride == 0 ? 0 : b0 * stride);
+    const size_t spitch = (stride == 0 ? N : stride) * sizeof(double);
+    CEL_CUDA_TRY(s, cudaMemcpy2DAsync(s->stage_t[0].p, series_bytes, ht, spitch, series_bytes, ns, cudaMemcpyHostToDevice, st));
+    CEL_CUDA_TRY(s, cudaMemcpy2DAsync(s->stage_d[0].p, series_bytes, hd, spitch, series_bytes, ns, cudaMemcpyHostToDevice, st));
+    CEL_CUDA_TRY(s, cudaMemcpy2DAsync(s->stage_y[0].p, series_bytes, hy, spitch, series_bytes, ns, cudaMemcpyHostToDevice, st));
+    if (coeff_stride == 0) {
+      CEL_CUDA_TRY(s, cudaMemcpyAsync(s->stage_c[0].p, coeffs, dbytes(P), cudaMemcpyHostToDevice, st));
+    } else {
+      CEL_CUDA_TRY(s, cudaMemcpy2DAsync(s->stage_c[0].p, dbytes(P), coeffs + b0 * coeff_stride,
+                                        coeff_stride * sizeof(double), dbytes(P), (size_t)nb,
+                                        cudaMemcpyHostToDevice, st));
+    }
+    a.B = nb; a.stride = (stride == 0) ? 0 : N; a.coeff_stride = (coeff_stride == 0) ? 0 : P;
+    a.coeffs = s->stage_c[0].d();
+    a.t = s->stage_t[0].d(); a.diag = s->stage_d[0].d(); a.y = s->stage_y[0].d();
+    a.out_val = s->stage_o[0].d(); a.out_grad = s->stage_o[0].d() + chunk;
+    a.status = s->stage_s[0].i(); a.scratch = s->scratch0.d();
+    CEL_CUDA_TRY(s, cel::launch_grad_coop(a, st));
+    s->launches += 1;
+    CEL_CUDA_TRY(s, cudaMemcpyAsync(out_val + b0, a.out_val, dbytes(nb), cudaMemcpyDeviceToHost, st));
+    CEL_CUDA_TRY(s, cudaMemcpyAsync(out_grad + b0 * P, a.out_grad, dbytes((size_t)nb * P), cudaMemcpyDeviceToHost, st));
+    if (status) CEL_CUDA_TRY(s, cudaMemcpyAsync(status + b0, a.status, nb * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
+  }
+  return CEL_OK;
 }
 
 // ---- state (pickle) ---------------------------------------------------------------------------

@@ -73,8 +73,8 @@ __device__ __forceinline__ void cel_sincos_core(double x, double* s, double* c) 
 constexpr double kFastTrigLimit = 1.0e9;
 
 // Out-of-line stock routines for the rare slow paths (keeps the hot loops small).
-__device__ __noinline__ double slow_exp(double x) { return exp(x); }
-__device__ __noinline__ void slow_sincos(double x, double* s, double* c) { sincos(x, s, c); }
+static __device__ __noinline__ double slow_exp(double x) { return exp(x); }
+static __device__ __noinline__ void slow_sincos(double x, double* s, double* c) { sincos(x, s, c); }
 
 __device__ __forceinline__ double cel_exp(double x) {
   if (!(fabs(x) < 700.0)) return slow_exp(x);  // overflow / underflow / nan: stock routine

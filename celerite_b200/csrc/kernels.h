@@ -43,6 +43,32 @@ cudaError_t launch_loglik_lockstep(const BatchArgs& a, cudaStream_t stream);
 constexpr int kCoopMaxJ = 32;
 cudaError_t launch_loglik_coop(const BatchArgs& a, cudaStream_t stream);
 
+// Fused log-likelihood + reverse-mode gradient (celerite/solver.cpp:347-463), DEVICE pointers.
+struct GradArgs {
+  long long B;
+  int N;
+  long long stride;
+  int Jr, Jc, Jg;
+  const double* coeffs;
+  long long coeff_stride;
+  const double* t;
+  const double* diag;
+  const double* y;
+  const double* A;
+  const double* U;
+  const double* V;
+  double* out_val;      // -0.5*(quad + logdet), no constant
+  double* out_grad;     // B x (1 + 2Jr + 4Jc)
+  double* out_logdet;   // optional
+  double* out_quad;     // optional
+  int* status;
+  double* scratch;      // grad_scratch_doubles(B, N, J, seg) doubles
+  int seg;              // checkpoint distance (multiple of 16)
+};
+int grad_default_segment(int N);
+size_t grad_scratch_doubles(long long B, int N, int J, int seg);
+cudaError_t launch_grad_coop(const GradArgs& a, cudaStream_t stream);
+
 // One stored factor (reference layout) applied to nrhs right-hand sides, DEVICE pointers.
 struct SweepArgs {
   int N, J, nrhs;
@@ -77,5 +103,9 @@ cudaError_t launch_scale(int n, int N, const double* in, const double* D, double
 // J == 0 "factorisation": D = diag + jitter (+A), logdet = sum log D   (cholesky.h:90-95)
 cudaError_t launch_jitter_only(int N, const double* diag, double jitter, double* D, double* logdet,
                                cudaStream_t stream);
+
+// J == 0 value and d/djitter: out[0] = -0.5*sum(y^2/D + log D), out[1] = sum(0.5 y^2/D^2 - 0.5/D)
+cudaError_t launch_jitter_only_grad(int N, const double* diag, const double* y, double jitter, double* out2,
+                                    cudaStream_t stream);
 
 }  // namespace cel

@@ -343,3 +343,32 @@ cudaError_t launch_jitter_only(int N, const double* diag, double jitter, double*
   return cudaGetLastError();
 }
 }  // namespace cel
+
+namespace cel {
+namespace {
+__global__ void __launch_bounds__(256) k_jitter_only_grad(int N, const double* diag, const double* y, double jitter,
+                                                           double* out2) {
+  __shared__ double part[2][8];
+  double v = 0.0, g = 0.0;
+  for (int i = threadIdx.x; i < N; i += blockDim.x) {
+    const double d = diag[i] + jitter, r = 1.0 / d, yi = y[i];
+    v += yi * yi * r + log(d);
+    g += 0.5 * (yi * r) * (yi * r) - 0.5 * r;
+  }
+  group_sum2<32>(v, g);
+  if ((threadIdx.x & 31) == 0) { part[0][threadIdx.x >> 5] = v; part[1][threadIdx.x >> 5] = g; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double sv = 0.0, sg = 0.0;
+    for (int i = 0; i < 8; ++i) { sv += part[0][i]; sg += part[1][i]; }
+    out2[0] = -0.5 * sv;
+    out2[1] = sg;
+  }
+}
+}  // namespace
+cudaError_t launch_jitter_only_grad(int N, const double* diag, const double* y, double jitter, double* out2,
+                                    cudaStream_t stream) {
+  k_jitter_only_grad<<<1, 256, 0, stream>>>(N, diag, y, jitter, out2);
+  return cudaGetLastError();
+}
+}  // namespace cel
