@@ -10,6 +10,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libcelerite_b200.so")
 
 OK, DIMENSION_MISMATCH, NOT_COMPUTED, NOT_POSITIVE_DEFINITE, CUDA_ERROR, INVALID_ARGUMENT, UNSUPPORTED = range(7)
+EXCEEDS_STATIC_SCRATCH = 7
+STATIC_SCRATCH_BYTES = 32 << 20
 HOST_POINTERS = 1
 
 _dp = C.POINTER(C.c_double)
@@ -44,6 +46,8 @@ SIGNATURES = {
                                                   _vp, _vp, _vp, _vp, _vp, _vp, C.c_uint]),
     "cel_batched_compute": (C.c_int, [_vp, _i64, C.c_int, _i64, C.c_int, C.c_int, _vp, _i64,
                                       _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "cel_grad_log_likelihood_static_scratch": (C.c_int, [C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp,
+                                                         _vp, _vp, _vp, _vp]),
     "cel_launch_count": (_i64, [_vp]),
 }
 

@@ -42,6 +42,8 @@ extern "C" {
 #define CEL_INVALID_ARGUMENT      5
 #define CEL_UNSUPPORTED           6
 
+#define CEL_EXCEEDS_STATIC_SCRATCH 7  /* cel_grad_log_likelihood_static_scratch: problem too large */
+
 #define CEL_HOST_POINTERS 1u        /* flags: t/diag/y/coeffs/outputs are host memory        */
 
 typedef struct cel_solver cel_solver;
@@ -153,6 +155,37 @@ int cel_batched_compute(cel_solver* s, int64_t B, int N, int64_t stride,
                         const double* t, const double* diag,
                         double* phi, double* u, double* W, double* D, double* out_logdet,
                         int32_t* status);
+
+/* ---- gradient without any allocation (no counterpart in the reference) ----------------------
+ * For callers that must not allocate: applications that gave the whole GPU to their own pool
+ * allocator and forbid cudaMalloc/cudaFree once running (both synchronise the device), fixed
+ * memory budgets, latency-critical sections.  The other gradient entry points keep grow-only
+ * device buffers in a handle and may allocate whenever a call is larger than any before; this
+ * one takes no handle and allocates nothing, neither on the device nor on the host.
+ *
+ * Same computation as cel_batched_grad_log_likelihood with B = 1 (one series, real + complex
+ * terms, 1 <= Jr + 2*Jc <= 32): d_val[0] = -0.5*(y^T K^-1 y + log det K) without constant,
+ * d_grad[0 .. 2Jr+4Jc] as in solver.cpp:392-434, d_status[0] = CEL_OK or
+ * CEL_NOT_POSITIVE_DEFINITE.  ALL pointers are DEVICE memory owned by the caller; d_coeffs is one
+ * row [jitter, a_real, c_real, a_comp, b_comp, c_comp, d_comp].  The kernel is queued on
+ * `cuda_stream` (NULL = the default stream) and the call returns without synchronising.
+ *
+ * The checkpoint/tape scratch of the reverse sweep lives in a fixed array inside the library
+ * image: CEL_STATIC_SCRATCH_BYTES (32 MiB) on every GPU that loads the library, until exit.
+ *   - Problems needing more are refused with CEL_EXCEEDS_STATIC_SCRATCH and nothing is launched.
+ *     Need = G*(ceil(N/C) + C)*(JP^2 + 2*JP + 2)*8 bytes with C = 16*ceil(sqrt(N)/16), JP = J
+ *     rounded up to {2,4,6,8,12,16,24,32}, G = 32/pow2ceil(JP): e.g. J = 8 fits up to N ~ 3e7,
+ *     J = 32 up to N ~ 3e6.
+ *   - All calls on a GPU share the one array: two calls whose kernels overlap on the device
+ *     (different streams, different host threads) corrupt each other.  Serialise them.
+ *   - Nothing has to be cleared between calls: every word is written before it is read.
+ *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress,
+ *     with that device current); make that first call before starting any stream capture. */
+#define CEL_STATIC_SCRATCH_BYTES (32u << 20)
+int cel_grad_log_likelihood_static_scratch(int N, int Jr, int Jc, const double* d_coeffs,
+                                           const double* d_t, const double* d_diag, const double* d_y,
+                                           double* d_val, double* d_grad, int32_t* d_status,
+                                           void* cuda_stream);
 
 /* Number of kernels this handle has launched since creation (bench.py's gpu_launches). */
 int64_t cel_launch_count(const cel_solver* s);
