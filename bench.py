@@ -38,6 +38,8 @@ WORKLOADS = {
     # name: (B per GPU, N, Jr, Jc)
     "cfg2": dict(B=65536, N=2000, Jr=0, Jc=1, desc="cfg2: 65,536 series x N=2,000, one SHOTerm (J=2), log_likelihood"),
     "cfg5": dict(B=125000, N=1000, Jr=0, Jc=2, desc="cfg5: 10^6 series x N=1,000 over 8 GPUs (125,000 per GPU), two SHOTerms (J=4), log_likelihood"),
+    # cfg3 is a sweep over J in BASELINE.json; --jc picks the number of SHO terms (J = 2*jc)
+    "cfg3": dict(B=1024, N=100000, Jr=0, Jc=4, grad=True, desc="cfg3: 1,024 series x N=100,000, J=2*jc (SHOTerms), grad_log_likelihood"),
 }
 
 
@@ -167,12 +169,17 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="override series per GPU (debug)")
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--jc", type=int, default=0, help="cfg3: number of SHO terms (J = 2*jc)")
+    ap.add_argument("--no-grad", action="store_true", help="skip the extra log-lik+grad measurement")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     wl = dict(WORKLOADS[args.workload])
     if args.batch:
         wl["B"] = args.batch
         wl["desc"] += " [batch overridden to %d]" % args.batch
+    if args.jc:
+        wl["Jc"] = args.jc
+        wl["desc"] += " [jc=%d]" % args.jc
 
     if args.impl == "reference":
         return run_reference(args, wl)
@@ -221,6 +228,23 @@ def main():
                               h_out[0].data_ptr(), h_out[1].data_ptr(), h_out[2].data_ptr(), h_status.data_ptr(),
                               flags=_capi.HOST_POINTERS, stream=stream.cuda_stream)
 
+    d_gval = torch.empty(B, dtype=torch.float64, device=dev)
+    d_grad = torch.empty((B, P), dtype=torch.float64, device=dev)
+
+    def step_grad():
+        import ctypes as C
+        lib = bs._lib
+        lib.cel_set_stream(bs._h, C.c_void_p(stream.cuda_stream or 1))
+        v = lambda x: C.c_void_p(x)  # noqa: E731
+        rc = lib.cel_batched_grad_log_likelihood(bs._h, B, N, N, Jr, Jc, v(dc_.data_ptr()), P, v(dt_.data_ptr()),
+                                                 v(dd_.data_ptr()), v(dy_.data_ptr()), v(d_gval.data_ptr()),
+                                                 v(d_grad.data_ptr()), v(d_status.data_ptr()), 0)
+        _capi.check(rc, bs._h)
+
+    primary_is_grad = bool(wl.get("grad"))
+    if primary_is_grad:
+        step_device = step_grad  # noqa: F811
+
     def barrier():
         if world > 1:
             dist.barrier()
@@ -256,12 +280,36 @@ def main():
     value = world * B * N * J / (ms_step * 1e-3)
 
     # ---- end-to-end through the C ABI with host buffers -------------------------------------
+    if primary_is_grad:
+        h_gval = torch.empty(B, dtype=torch.float64).pin_memory()
+        h_grad = torch.empty((B, P), dtype=torch.float64).pin_memory()
+
+        def step_host():  # noqa: F811
+            import ctypes as C
+            lib = bs._lib
+            lib.cel_set_stream(bs._h, C.c_void_p(stream.cuda_stream or 1))
+            v = lambda x: C.c_void_p(x)  # noqa: E731
+            rc = lib.cel_batched_grad_log_likelihood(bs._h, B, N, N, Jr, Jc, v(hc.data_ptr()), P, v(ht.data_ptr()),
+                                                     v(hd.data_ptr()), v(hy.data_ptr()), v(h_gval.data_ptr()),
+                                                     v(h_grad.data_ptr()), v(h_status.data_ptr()), _capi.HOST_POINTERS)
+            _capi.check(rc, bs._h)
     step_host()  # warm-up (allocates the staging buffers)
     e2e_ms = timed(step_host, max(1, args.e2e_steps))
     e2e_value = world * B * N * J / (e2e_ms * 1e-3)
     # the e2e path must give the same answer as the device-resident path
     torch.cuda.synchronize(dev)
-    same = bool(torch.equal(h_out.to(dev), d_out))
+    if primary_is_grad:
+        same = bool(torch.equal(h_grad.to(dev), d_grad))
+    else:
+        same = bool(torch.equal(h_out.to(dev), d_out))
+    # ---- the same batch with the gradient (the "log-lik+grad" half of the metric's name) ----
+    grad_extra = None
+    if not primary_is_grad and not args.no_grad:
+        step_grad()
+        torch.cuda.synchronize(dev)
+        g_ms = timed(step_grad, 3)
+        grad_extra = {"value": world * B * N * J / (g_ms * 1e-3), "unit": "point-terms/s", "ms_per_step": g_ms,
+                      "what": "cel_batched_grad_log_likelihood on the same batch (value + 1+2Jr+4Jc derivatives per series)"}
 
     if rank == 0:
         peak, peak_src = measured_peak_gbs()
@@ -286,11 +334,36 @@ def main():
             "gpu_launches": launches,
             "clocks": clocks,
         }
+        if grad_extra:
+            line["with_grad"] = grad_extra
+        if primary_is_grad:
+            line["metric"] = "GP log-likelihood + gradient point-terms/sec (N*J*batch / device time)"
+            line["roofline"]["kernel"] = "k_grad_coop"
+            line["roofline"]["algorithmic_bytes_per_launch"] = B * N * 24 + B * (P + 1) * 8
+            line["roofline"]["achieved"] = line["roofline"]["algorithmic_bytes_per_launch"] / (ms_step * 1e-3) / 1e9
+            line["roofline"]["frac"] = line["roofline"]["achieved"] / peak
+            line["roofline"]["note"] = "fp64-pipe/latency bound (1,024 independent recurrences); HBM fraction is not the limiter"
+            line["e2e"]["d2h_bytes_per_step"] = B * (P + 1) * 8 + B * 4
         if not args.no_cpu_baseline:
             import oracle
             chk = oracle.best()
             cores = os.cpu_count() or 1
             sample = int(min(B, max(256, cores * 1024)))
+            if primary_is_grad:
+                sample = int(min(B, cores))
+                Nc = min(N, 20000)   # the AD reference takes ~1.7 s per 1e5 points at J=8: bound the sample in N too
+                tN, dN, yN = (np.ascontiguousarray(a.numpy()[:sample, :Nc]) for a in (ht, hd, hy))
+                t0 = time.perf_counter()
+                gv, gg, gs = chk.batched_grad(sample, Nc, Nc, Jr, Jc, coeffs_np[:sample], P, tN, dN, yN, nthreads=cores)
+                cdt = time.perf_counter() - t0
+                line["cpu_baseline"] = {"value": sample * Nc * J / cdt, "unit": "point-terms/s", "cores": cores,
+                                        "kind": chk.kind,
+                                        "sample": "first %d series truncated to N=%d, forward-mode AD gradient "
+                                                  "(solver.cpp:347-463), %d threads" % (sample, Nc, cores)}
+                print(json.dumps(line))
+                if world > 1:
+                    dist.destroy_process_group()
+                return 0
             call = lambda: chk.batched_loglik(sample, N, N, Jr, Jc, coeffs_np[:sample], P,  # noqa: E731
                                               ht.numpy()[:sample], hd.numpy()[:sample], hy.numpy()[:sample],
                                               nthreads=cores)
