@@ -28,6 +28,10 @@ int pack_coeffs(cel_solver* s, double jitter, int Jr, const double* a_real, cons
 
 inline size_t dbytes(size_t n) { return n * sizeof(double); }
 
+// from this length on, solve / dot_L run as chunked scans (6-7 short launches instead of one
+// serial sweep of N dependent steps)
+constexpr int kChunkedMinN = 16384;
+
 }  // namespace
 
 extern "C" {
@@ -53,6 +57,9 @@ int cel_compute(cel_solver* s, double jitter, int Jr, const double* a_real, cons
                 const double* A, const double* U, const double* V, int N, const double* x, const double* diag) {
   if (!s) return CEL_INVALID_ARGUMENT;
   s->computed = false;  // cholesky.h:57
+  s->n_off = 0;
+  s->scan_nchunks = 0;
+  s->maps_valid[0] = s->maps_valid[1] = s->maps_valid[2] = false;
   if (N < 1 || !x || !diag) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "empty series");
   if (Jg < 0 || (Jg > 0 && (!U || !V))) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "general term needs U and V");
   std::vector<double> row;
@@ -168,9 +175,15 @@ int cel_solve(cel_solver* s, int N, int nrhs, const double* b, double* out) {
   if (rc != CEL_OK) return rc;
   if (nrhs == 0) return CEL_OK;
   cudaStream_t st = s->stream;
-  // J == 0 (cholesky.h:226-231) degenerates to out = b / D inside the same kernels
-  CEL_CUDA_TRY(s, cel::launch_solve(sweep_args(s, nrhs), st));
-  s->launches += 2;
+  if (s->J >= 1 && N >= kChunkedMinN) {
+    // long series: chunked two-pass scans (scan.cu) instead of one serial sweep
+    rc = cel_solve_device(s, nrhs, s->in0.d(), s->out1.d());
+    if (rc != CEL_OK) return rc;
+  } else {
+    // J == 0 (cholesky.h:226-231) degenerates to out = b / D inside the same kernels
+    CEL_CUDA_TRY(s, cel::launch_solve(sweep_args(s, nrhs), st));
+    s->launches += 2;
+  }
   CEL_CUDA_TRY(s, cudaMemcpyAsync(out, s->out1.p, dbytes((size_t)N * nrhs), cudaMemcpyDeviceToHost, st));
   CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
   return CEL_OK;
@@ -181,8 +194,13 @@ int cel_dot_L(cel_solver* s, int N, int nrhs, const double* z, double* out) {
   if (rc != CEL_OK) return rc;
   if (nrhs == 0) return CEL_OK;
   cudaStream_t st = s->stream;
-  CEL_CUDA_TRY(s, cel::launch_dot_L(sweep_args(s, nrhs), st));
-  s->launches += 1;
+  if (s->J >= 1 && N >= kChunkedMinN) {
+    rc = cel_dot_L_device(s, nrhs, s->in0.d(), s->out1.d());
+    if (rc != CEL_OK) return rc;
+  } else {
+    CEL_CUDA_TRY(s, cel::launch_dot_L(sweep_args(s, nrhs), st));
+    s->launches += 1;
+  }
   CEL_CUDA_TRY(s, cudaMemcpyAsync(out, s->out1.p, dbytes((size_t)N * nrhs), cudaMemcpyDeviceToHost, st));
   CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
   return CEL_OK;
@@ -418,6 +436,9 @@ int cel_set_state(cel_solver* s, int computed, int N, int J, double log_det, con
   if (N < 0 || J < 0) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "negative size");
   if (J > cel::kCoopMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "J > 32 is not supported yet");
   s->computed = false;
+  s->n_off = 0;
+  s->scan_nchunks = 0;
+  s->maps_valid[0] = s->maps_valid[1] = s->maps_valid[2] = false;
   s->N = N; s->J = J; s->log_det = log_det;
   s->Jr = s->Jc = s->Jg = 0;  // coefficients are not part of the pickled state (solver.cpp:36-42)
   if (computed && N > 0) {

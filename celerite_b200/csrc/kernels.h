@@ -104,6 +104,32 @@ cudaError_t launch_scale(int n, int N, const double* in, const double* D, double
 cudaError_t launch_jitter_only(int N, const double* diag, double jitter, double* D, double* logdet,
                                cudaStream_t stream);
 
+// Chunked affine scans over a stored factor (scan.cu).  mode: 0 forward solve (out = x/D),
+// 1 dot_L, 2 backward solve (in = x/D, out = K^-1 b).
+struct ScanArgs {
+  int N, J;
+  int n_off;            // local step n lives at stored index n + n_off (warm-up halo in front)
+  int nrhs, nbasis;     // columns [0,nrhs) right-hand sides, then nbasis unit carries (zero rhs)
+  int chunk_len, nchunks;
+  const double* phi;
+  const double* u;
+  const double* W;
+  const double* D;
+  const double* in;     // N x nrhs
+  double* out;          // N x nrhs or NULL
+  const double* init;   // [nchunks][ncols][J] incoming carries or NULL
+  double* carry;        // [nchunks][ncols][J] outgoing carries or NULL
+  int mode;
+  int diag_basis;       // the single basis column is the all-ones carry (diagonal maps: dot_L)
+};
+cudaError_t launch_chunk_sweep(const ScanArgs& a, cudaStream_t stream);
+cudaError_t launch_pack_records(int nchunks, int J, int nrhs, int nbasis, const double* vecs, const double* maps,
+                                double* rec, cudaStream_t stream);
+cudaError_t launch_middle(int J, int nrhs, int nbasis, int diag, int reverse, int nunits, const double* rec,
+                          double* srec, double* sg, const double* g0, double* gin, double* total,
+                          int compose_only, int skip_compose, cudaStream_t stream);
+int middle_nsuper(int nunits);
+
 // J == 0 value and d/djitter: out[0] = -0.5*sum(y^2/D + log D), out[1] = sum(0.5 y^2/D^2 - 0.5/D)
 cudaError_t launch_jitter_only_grad(int N, const double* diag, const double* y, double jitter, double* out2,
                                     cudaStream_t stream);

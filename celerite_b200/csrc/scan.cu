@@ -1,0 +1,383 @@
+// K3s / K4s — the linear recursions on a stored factor as CHUNKED TWO-PASS AFFINE SCANS, for long
+// single series (solve: cholesky.h:218-318, dot_L: cholesky.h:409-431).
+//
+// Each sweep is an affine recurrence in a J-vector carry:
+//   forward  solve : G_n = f_n + W_n x_n,  f_{n+1} = phi_{n+1} o G_n,  x_n = b_n - u_n.f_n
+//   forward  dot_L : same with s_n = sqrt(D_n) z_n in place of x_n (the map is diagonal)
+//   backward solve : F_{n-1} = phi_n o (F_n + u_n z_n),  z_n = x'_n - W_n.F_n,  x' = x / D
+// so a chunk of steps maps its incoming carry to its outgoing one by  g_out = M g_in + c.
+// The time axis is cut into chunks that are swept concurrently:
+//   pass 1  every chunk runs from a ZERO carry with the real right-hand side  -> c
+//           (and once per factor, from the J unit carries with a zero rhs     -> columns of M;
+//            M depends on the factor only and is cached in the handle)
+//   middle  the chunk maps are composed hierarchically (sqrt(K) super-chunks): compose inside
+//           each super-chunk in parallel, scan the few super-chunk maps serially, then walk each
+//           super-chunk again to hand every chunk its true incoming carry
+//   pass 2  every chunk re-runs from its true carry and writes the result.
+// Only (J^2+J) doubles per chunk travel between the passes; across GPUs, one such record per
+// rank (cel_span_summarize / cel_span_apply: an all-gather of J^2+J doubles per sweep).
+//
+// Mapping: one group of L = pow2ceil(J) lanes per (chunk, column); lane k owns row k; the factor
+// rows of a step are J contiguous doubles, so a group's loads are coalesced; a register ring
+// keeps one 8-step tile of loads in flight ahead of the recurrence.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace cel {
+namespace {
+
+constexpr int TT = 8;
+
+// --------------------------------------------------------------------------------------------
+// chunk sweeps
+// --------------------------------------------------------------------------------------------
+template <int L>
+__global__ void __launch_bounds__(kWarp) k_chunk_forward(ScanArgs a) {
+  constexpr int G = kWarp / L;
+  const int lane = threadIdx.x, g = lane / L, k = lane % L;
+  const int ncols = a.nrhs + a.nbasis;
+  const long long total = (long long)a.nchunks * ncols;
+  const long long gid0 = (long long)blockIdx.x * G + g;
+  const bool active = gid0 < total;
+  const long long gid = active ? gid0 : total - 1;
+  const int chunk = (int)(gid / ncols), col = (int)(gid % ncols);
+  const bool is_rhs = col < a.nrhs;
+  const int N = a.N, J = a.J, off = a.n_off;
+  const bool row_ok = k < J;
+  const int kk = row_ok ? k : 0;
+  const int n0 = chunk * a.chunk_len, n1 = min(N, n0 + a.chunk_len);
+  const double* in = is_rhs ? a.in + (size_t)col * N : nullptr;
+  double* out = (is_rhs && a.out) ? a.out + (size_t)col * N : nullptr;
+
+  double f;
+  if (a.init) f = row_ok ? a.init[((size_t)chunk * ncols + col) * J + kk] : 0.0;
+  else if (is_rhs) f = 0.0;
+  else f = (row_ok && (a.diag_basis || kk == col - a.nrhs)) ? 1.0 : 0.0;
+
+  struct Tile { double ph[TT], uu[TT], ww[TT], bn[TT], dn[TT]; };
+  auto load = [&](Tile& tl, int m0) {
+#pragma unroll
+    for (int i = 0; i < TT; ++i) {
+      const int n = min(m0 + i, n1 - 1), s = n + off;
+      const bool has_prev = (s >= 1) && row_ok;
+      tl.ph[i] = has_prev ? __ldg(a.phi + (size_t)(s - 1) * J + kk) : 0.0;
+      tl.uu[i] = has_prev ? __ldg(a.u + (size_t)(s - 1) * J + kk) : 0.0;
+      tl.ww[i] = row_ok ? __ldg(a.W + (size_t)s * J + kk) : 0.0;
+      tl.bn[i] = in ? __ldg(in + n) : 0.0;
+      tl.dn[i] = __ldg(a.D + s);
+    }
+  };
+  double wprev = 0.0, sprev = 0.0;
+  auto run = [&](const Tile& tl, int m0) {
+#pragma unroll
+    for (int i = 0; i < TT; ++i) {
+      if (m0 + i < n1) {
+        f = tl.ph[i] * fma(wprev, sprev, f);
+        const double red = group_sum<L>(tl.uu[i] * f);
+        if (a.mode == 1) {
+          const double tmp = sqrt(tl.dn[i]) * tl.bn[i];
+          if (out && k == 0 && active) out[m0 + i] = tmp + red;
+          sprev = tmp;
+        } else {
+          const double x = tl.bn[i] - red;
+          if (out && k == 0 && active) out[m0 + i] = x / tl.dn[i];
+          sprev = x;
+        }
+        wprev = tl.ww[i];
+      }
+    }
+  };
+  Tile ta, tb;
+  load(ta, n0);
+  for (int m0 = n0; m0 < n1; m0 += 2 * TT) {
+    if (m0 + TT < n1) load(tb, m0 + TT);
+    run(ta, m0);
+    if (m0 + 2 * TT < n1) load(ta, m0 + 2 * TT);
+    if (m0 + TT < n1) run(tb, m0 + TT);
+  }
+  if (a.carry && row_ok && active) a.carry[((size_t)chunk * ncols + col) * J + kk] = fma(wprev, sprev, f);
+}
+
+// backward half of solve; `in` holds x/D, chunks are independent given F at their upper edge
+template <int L>
+__global__ void __launch_bounds__(kWarp) k_chunk_backward(ScanArgs a) {
+  constexpr int G = kWarp / L;
+  const int lane = threadIdx.x, g = lane / L, k = lane % L;
+  const int ncols = a.nrhs + a.nbasis;
+  const long long total = (long long)a.nchunks * ncols;
+  const long long gid0 = (long long)blockIdx.x * G + g;
+  const bool active = gid0 < total;
+  const long long gid = active ? gid0 : total - 1;
+  const int chunk = (int)(gid / ncols), col = (int)(gid % ncols);
+  const bool is_rhs = col < a.nrhs;
+  const int N = a.N, J = a.J, off = a.n_off;
+  const bool row_ok = k < J;
+  const int kk = row_ok ? k : 0;
+  const int n0 = chunk * a.chunk_len, n1 = min(N, n0 + a.chunk_len);
+  const double* in = is_rhs ? a.in + (size_t)col * N : nullptr;
+  double* out = (is_rhs && a.out) ? a.out + (size_t)col * N : nullptr;
+
+  double f;  // F_n of the step about to be processed
+  if (a.init) f = row_ok ? a.init[((size_t)chunk * ncols + col) * J + kk] : 0.0;
+  else if (is_rhs) f = 0.0;
+  else f = (row_ok && kk == col - a.nrhs) ? 1.0 : 0.0;
+
+  struct Tile { double ph[TT], uu[TT], ww[TT], xn[TT]; };
+  // m counts down from the chunk's upper edge: step m is n = n1-1-m
+  auto load = [&](Tile& tl, int m0) {
+#pragma unroll
+    for (int i = 0; i < TT; ++i) {
+      const int n = max(n1 - 1 - (m0 + i), n0), s = n + off;
+      const bool has_prev = (s >= 1) && row_ok;
+      tl.ph[i] = has_prev ? __ldg(a.phi + (size_t)(s - 1) * J + kk) : 0.0;   // phi_n
+      tl.uu[i] = has_prev ? __ldg(a.u + (size_t)(s - 1) * J + kk) : 0.0;     // u_n
+      tl.ww[i] = row_ok ? __ldg(a.W + (size_t)s * J + kk) : 0.0;
+      tl.xn[i] = in ? __ldg(in + n) : 0.0;
+    }
+  };
+  const int len = n1 - n0;
+  auto run = [&](const Tile& tl, int m0) {
+#pragma unroll
+    for (int i = 0; i < TT; ++i) {
+      if (m0 + i < len) {
+        const int n = n1 - 1 - (m0 + i);
+        const double red = group_sum<L>(tl.ww[i] * f);
+        const double z = tl.xn[i] - red;
+        if (out && k == 0 && active) out[n] = z;
+        f = tl.ph[i] * fma(tl.uu[i], z, f);   // F_{n-1}
+      }
+    }
+  };
+  Tile ta, tb;
+  load(ta, 0);
+  for (int m0 = 0; m0 < len; m0 += 2 * TT) {
+    if (m0 + TT < len) load(tb, m0 + TT);
+    run(ta, m0);
+    if (m0 + 2 * TT < len) load(ta, m0 + 2 * TT);
+    if (m0 + TT < len) run(tb, m0 + TT);
+  }
+  if (a.carry && row_ok && active) a.carry[((size_t)chunk * ncols + col) * J + kk] = f;
+}
+
+// --------------------------------------------------------------------------------------------
+// middle: compose / scan / distribute the chunk maps.  Records are [unit][col][J] with
+// col < nrhs the affine offsets c and col >= nrhs the columns of M (one column = all-ones image
+// when diag).  `reverse` walks the units from the last to the first (backward sweep).
+// One warp per super-chunk; lane k = row k (J <= 32).
+// --------------------------------------------------------------------------------------------
+struct MidArgs {
+  int J, nrhs, nbasis, diag, reverse;
+  int nunits, per_super, nsuper;
+  const double* rec;      // [nunits][ncols][J]  chunk maps
+  double* srec;           // [nsuper][ncols][J]  super-chunk maps (out of compose)
+  const double* g0;       // [nrhs][J] carry entering the first unit of the walk (or NULL = 0)
+  double* sg;             // [nsuper][nrhs][J] carries entering each super-chunk
+  double* gin;            // [nunits][ncols][J] carries entering each chunk (rhs columns only)
+  double* total;          // [ncols][J] composition of all super-chunks (optional)
+};
+
+constexpr int kMidMaxJ = 32;
+
+// running map of one warp, in shared memory: Mr[i][k] (column i), cr[r][k]
+__device__ __forceinline__ void mid_compose(const MidArgs& m, const double* unit_rec, double* Mr, double* cr,
+                                            double* Mn, int k, bool row_ok) {
+  const int J = m.J, nrhs = m.nrhs;
+  const double* Mc = unit_rec + (size_t)nrhs * J;   // columns of the unit's M (or its diagonal)
+  if (m.diag) {
+    if (row_ok) {
+      const double d = Mc[k];
+      Mr[k] *= d;
+      for (int r = 0; r < nrhs; ++r) cr[r * J + k] = fma(d, cr[r * J + k], unit_rec[r * J + k]);
+    }
+    __syncwarp();
+    return;
+  }
+  if (row_ok) {
+    for (int i = 0; i < J; ++i) {           // new column i = Mc * (old column i)
+      double acc = 0.0;
+      for (int j = 0; j < J; ++j) acc = fma(Mc[j * J + k], Mr[i * J + j], acc);
+      Mn[i * J + k] = acc;
+    }
+    for (int r = 0; r < nrhs; ++r) {
+      double acc = unit_rec[r * J + k];
+      for (int j = 0; j < J; ++j) acc = fma(Mc[j * J + k], cr[r * J + j], acc);
+      Mn[(J + r) * J + k] = acc;
+    }
+  }
+  __syncwarp();
+  if (row_ok) {
+    for (int i = 0; i < J; ++i) Mr[i * J + k] = Mn[i * J + k];
+    for (int r = 0; r < nrhs; ++r) cr[r * J + k] = Mn[(J + r) * J + k];
+  }
+  __syncwarp();
+}
+
+// apply one unit's map to carries g[r][k] held in shared memory
+__device__ __forceinline__ void mid_apply(const MidArgs& m, const double* unit_rec, double* gs, double* gn, int k,
+                                          bool row_ok) {
+  const int J = m.J, nrhs = m.nrhs;
+  const double* Mc = unit_rec + (size_t)nrhs * J;
+  if (row_ok) {
+    for (int r = 0; r < nrhs; ++r) {
+      double acc = unit_rec[r * J + k];
+      if (m.diag) acc = fma(Mc[k], gs[r * J + k], acc);
+      else for (int j = 0; j < J; ++j) acc = fma(Mc[j * J + k], gs[r * J + j], acc);
+      gn[r * J + k] = acc;
+    }
+  }
+  __syncwarp();
+  if (row_ok) for (int r = 0; r < nrhs; ++r) gs[r * J + k] = gn[r * J + k];
+  __syncwarp();
+}
+
+__global__ void __launch_bounds__(kWarp) k_mid_compose(MidArgs m, int level_total) {
+  // level_total == 0: block b composes the chunks of super-chunk b into srec[b]
+  // level_total == 1: one block composes all super-chunk maps (srec) into total
+  extern __shared__ double sm[];
+  const int J = m.J, ncols = m.nrhs + m.nbasis, k = threadIdx.x;
+  const bool row_ok = k < J;
+  double* Mr = sm;                          // J*J (or J when diag)
+  double* cr = Mr + J * J;                  // nrhs*J
+  double* Mn = cr + m.nrhs * J;             // (J+nrhs)*J scratch
+  for (int i = k; i < J * J; i += kWarp) Mr[i] = m.diag ? 1.0 : ((i / J) == (i % J) ? 1.0 : 0.0);
+  for (int i = k; i < m.nrhs * J; i += kWarp) cr[i] = 0.0;
+  __syncwarp();
+  int first, count;
+  const double* src;
+  if (level_total == 0) { first = blockIdx.x * m.per_super; count = min(m.per_super, m.nunits - first); src = m.rec; }
+  else { first = 0; count = m.nsuper; src = m.srec; }
+  const int nwalk = (level_total == 0) ? m.nunits : m.nsuper;
+  for (int q = first; q < first + count; ++q) {
+    // chunk records are indexed by position in time, super-chunk records by position in the walk
+    const int unit = (level_total == 0 && m.reverse) ? nwalk - 1 - q : q;
+    mid_compose(m, src + (size_t)unit * ncols * J, Mr, cr, Mn, k, row_ok);
+  }
+  double* dst = (level_total == 0) ? m.srec + (size_t)blockIdx.x * ncols * J : m.total;
+  if (row_ok) {
+    for (int r = 0; r < m.nrhs; ++r) dst[r * J + k] = cr[r * J + k];
+    if (m.diag) dst[m.nrhs * J + k] = Mr[k];
+    else for (int i = 0; i < J; ++i) dst[(m.nrhs + i) * J + k] = Mr[i * J + k];
+  }
+}
+
+__global__ void __launch_bounds__(kWarp) k_mid_scan(MidArgs m) {
+  // serial over the super-chunk maps: carry entering each super-chunk (walk order)
+  extern __shared__ double sm[];
+  const int J = m.J, ncols = m.nrhs + m.nbasis, k = threadIdx.x;
+  const bool row_ok = k < J;
+  double* gs = sm;
+  double* gn = gs + m.nrhs * J;
+  for (int i = k; i < m.nrhs * J; i += kWarp) gs[i] = m.g0 ? m.g0[i] : 0.0;
+  __syncwarp();
+  for (int q = 0; q < m.nsuper; ++q) {
+    if (row_ok) for (int r = 0; r < m.nrhs; ++r) m.sg[((size_t)q * m.nrhs + r) * J + k] = gs[r * J + k];
+    mid_apply(m, m.srec + (size_t)q * ncols * J, gs, gn, k, row_ok);
+  }
+}
+
+__global__ void __launch_bounds__(kWarp) k_mid_distribute(MidArgs m) {
+  // block b walks super-chunk b (walk order) and hands every chunk its incoming carry
+  extern __shared__ double sm[];
+  const int J = m.J, ncols = m.nrhs + m.nbasis, k = threadIdx.x;
+  const bool row_ok = k < J;
+  double* gs = sm;
+  double* gn = gs + m.nrhs * J;
+  for (int i = k; i < m.nrhs * J; i += kWarp) gs[i] = m.sg[(size_t)blockIdx.x * m.nrhs * J + i];
+  __syncwarp();
+  const int first = blockIdx.x * m.per_super, count = min(m.per_super, m.nunits - first);
+  for (int q = first; q < first + count; ++q) {
+    const int unit = m.reverse ? m.nunits - 1 - q : q;
+    if (row_ok) for (int r = 0; r < m.nrhs; ++r) m.gin[((size_t)unit * m.nrhs + r) * J + k] = gs[r * J + k];
+    mid_apply(m, m.rec + (size_t)unit * ncols * J, gs, gn, k, row_ok);
+  }
+}
+
+}  // namespace
+
+#define CEL_DISPATCH_L(J, CALL)                   \
+  do {                                            \
+    if ((J) <= 1) { CALL(1); }                    \
+    else if ((J) <= 2) { CALL(2); }               \
+    else if ((J) <= 4) { CALL(4); }               \
+    else if ((J) <= 8) { CALL(8); }               \
+    else if ((J) <= 16) { CALL(16); }             \
+    else { CALL(32); }                            \
+  } while (0)
+
+cudaError_t launch_chunk_sweep(const ScanArgs& a, cudaStream_t stream) {
+  if (a.J > kMidMaxJ || a.nchunks < 1) return cudaErrorInvalidValue;
+  const long long total = (long long)a.nchunks * (a.nrhs + a.nbasis);
+  if (total == 0) return cudaSuccess;
+#define CALL(LL)                                                                  \
+  {                                                                               \
+    const int G = kWarp / LL;                                                     \
+    const unsigned grid = (unsigned)((total + G - 1) / G);                        \
+    if (a.mode == 2) k_chunk_backward<LL><<<grid, kWarp, 0, stream>>>(a);         \
+    else k_chunk_forward<LL><<<grid, kWarp, 0, stream>>>(a);                      \
+  }
+  CEL_DISPATCH_L(a.J, CALL);
+#undef CALL
+  return cudaGetLastError();
+}
+
+// Merge the basis columns of `maps` ([nchunks][nbasis][J]) and the offsets of `vecs`
+// ([nchunks][nrhs][J]) into one record array [nchunks][nrhs+nbasis][J].
+__global__ void k_pack_records(int nchunks, int J, int nrhs, int nbasis, const double* vecs, const double* maps,
+                               double* rec) {
+  const int ncols = nrhs + nbasis;
+  const long long total = (long long)nchunks * ncols * J;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(i % J);
+    const long long cc = i / J;
+    const int col = (int)(cc % ncols), chunk = (int)(cc / ncols);
+    rec[i] = (col < nrhs) ? vecs[((size_t)chunk * nrhs + col) * J + k]
+                          : maps[((size_t)chunk * nbasis + (col - nrhs)) * J + k];
+  }
+}
+
+cudaError_t launch_pack_records(int nchunks, int J, int nrhs, int nbasis, const double* vecs, const double* maps,
+                                double* rec, cudaStream_t stream) {
+  const long long total = (long long)nchunks * (nrhs + nbasis) * J;
+  if (total == 0) return cudaSuccess;
+  const int threads = 256;
+  const long long want = (total + threads - 1) / threads;
+  const unsigned grid = (unsigned)(want < 148 * 8 ? want : 148 * 8);
+  k_pack_records<<<grid, threads, 0, stream>>>(nchunks, J, nrhs, nbasis, vecs, maps, rec);
+  return cudaGetLastError();
+}
+
+// middle stage driver.  Buffers: rec [nunits][ncols][J] in; srec [nsuper][ncols][J], sg
+// [nsuper][nrhs][J] scratch; gin [nunits][nrhs][J] out; total [ncols][J] out (optional);
+// g0 [nrhs][J] in (optional).  Set compose_only to stop after the total map (multi-GPU summary).
+cudaError_t launch_middle(int J, int nrhs, int nbasis, int diag, int reverse, int nunits, const double* rec,
+                          double* srec, double* sg, const double* g0, double* gin, double* total,
+                          int compose_only, int skip_compose, cudaStream_t stream) {
+  if (J > kMidMaxJ || J < 1) return cudaErrorInvalidValue;
+  MidArgs m{};
+  m.J = J; m.nrhs = nrhs; m.nbasis = nbasis; m.diag = diag; m.reverse = reverse;
+  m.nunits = nunits;
+  int ps = 1;
+  while ((long long)ps * ps < nunits) ++ps;
+  m.per_super = ps;
+  m.nsuper = (nunits + ps - 1) / ps;
+  m.rec = rec; m.srec = srec; m.g0 = g0; m.sg = sg; m.gin = gin; m.total = total;
+  const size_t smem = (size_t)(J * J + nrhs * J + (J + nrhs) * J) * sizeof(double);
+  if (!skip_compose) {
+    k_mid_compose<<<m.nsuper, kWarp, smem, stream>>>(m, 0);
+    if (total) k_mid_compose<<<1, kWarp, smem, stream>>>(m, 1);
+  }
+  if (!compose_only) {
+    const size_t smem2 = (size_t)(2 * nrhs * J) * sizeof(double);
+    k_mid_scan<<<1, kWarp, smem2, stream>>>(m);
+    k_mid_distribute<<<m.nsuper, kWarp, smem2, stream>>>(m);
+  }
+  return cudaGetLastError();
+}
+
+int middle_nsuper(int nunits) {
+  int ps = 1;
+  while ((long long)ps * ps < nunits) ++ps;
+  return (nunits + ps - 1) / ps;
+}
+
+}  // namespace cel

@@ -57,6 +57,13 @@ struct cel_solver {
   cel::DevBuf coeffs;              // [jitter, a_real, c_real, a_comp, b_comp, c_comp, d_comp]
   double h_coeffs_jitter = 0.0;
 
+  // ---- chunked scans (scan.cu): per-direction chunk maps, valid for the current factor ----
+  int n_off = 0;                   // stored steps in front of the span (warm-up halo), see cel_span_trim
+  int scan_chunk_len = 0, scan_nchunks = 0;
+  bool maps_valid[3] = {false, false, false};
+  cel::DevBuf maps[3];             // [nchunks][nbasis][J] per mode
+  cel::DevBuf scan_vecs, scan_rec, scan_srec, scan_sg, scan_gin, scan_total, scan_tmp;
+
   // ---- scratch ----
   cel::DevBuf in0, in1, in2, in3;  // single-series inputs / rhs
   cel::DevBuf out0, out1;

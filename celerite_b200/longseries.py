@@ -1,0 +1,195 @@
+"""Long single series: apply_inverse (solve) and dot_L as chunked scans, on one GPU or with the
+time axis split over the GPUs of a node (BASELINE.json config 4).
+
+Single GPU:  ``LongSeries().compute(...)`` then ``.solve(b)`` / ``.dot_L(z)`` with torch CUDA
+tensors (N,) or (N, nrhs) — everything stays on the device.
+
+Multi GPU (one process per GPU, ``torch.distributed`` initialised by the caller):
+``DistributedLongSeries`` gives rank r the span [lo_r, hi_r) of the series.  Each rank factorises
+its own span preceded by a warm-up halo (the factorisation recursion forgets its past like
+prod(phi^2), so a halo long enough reproduces the serial factor to round-off), and a sweep is
+
+    summarize (local)  ->  all_gather of (J^2+J) doubles per rank  ->  fold  ->  apply (local)
+
+which is the only communication on the data path.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _capi
+
+OP_SOLVE_FORWARD, OP_DOT_L, OP_SOLVE_BACKWARD = 0, 1, 2
+
+
+def span_bounds(N, world, rank):
+    """Contiguous split of [0, N) into `world` spans; returns (lo, hi) of `rank`."""
+    base, rem = divmod(N, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def safe_halo(c_min, dt_mean, tol=1e-18, cap=None):
+    """Warm-up length after which a cold-started factorisation agrees with the serial one to
+    `tol`: the open-loop bound ln(1/tol) / (2 c_min dt) of SURVEY.md §7.3-3."""
+    h = int(np.ceil(np.log(1.0 / tol) / (2.0 * max(c_min * dt_mean, 1e-300))))
+    return h if cap is None else min(h, cap)
+
+
+def fold_carries(summaries, rank, op, nrhs, J):
+    """Incoming carry of `rank` from the gathered span summaries.
+
+    summaries: tensor (world, nrhs + nb, J) as written by cel_span_summarize — rows [0, nrhs) are
+    the offsets c, rows [nrhs, nrhs+nb) the columns of M (nb = J) or its diagonal (nb = 1, dot_L).
+    Forward ops fold ranks 0..rank-1 in order, the backward op folds world-1..rank+1.
+    Returns a (nrhs, J) tensor (zeros for the first rank of the walk)."""
+    import torch
+    world = summaries.shape[0]
+    g = torch.zeros((nrhs, J), dtype=summaries.dtype, device=summaries.device)
+    order = range(0, rank) if op != OP_SOLVE_BACKWARD else range(world - 1, rank, -1)
+    for q in order:
+        c = summaries[q, :nrhs, :]
+        if op == OP_DOT_L:
+            g = g * summaries[q, nrhs, :][None, :] + c
+        else:
+            M = summaries[q, nrhs:nrhs + J, :].transpose(0, 1)   # M[k][i] = column i, row k
+            g = g @ M.transpose(0, 1) + c
+    return g.contiguous()
+
+
+class LongSeries(object):
+    """One long series on one GPU (the whole factor is resident)."""
+
+    def __init__(self, device=-1):
+        self._lib = _capi.lib()
+        self._h = _capi.create(device)
+        self.N = 0
+        self.J = 0
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h is not None:
+            try:
+                self._lib.cel_destroy(h)
+            except Exception:
+                pass
+
+    def compute(self, jitter, a_real, c_real, a_comp, b_comp, c_comp, d_comp, x, diag, halo=0):
+        """cholesky.h:41-210 on host arrays; `halo` leading steps only warm the recursion up."""
+        v = lambda a: np.ascontiguousarray(np.asarray(a, dtype=np.float64).reshape(-1))  # noqa: E731
+        a_real, c_real, a_comp, b_comp, c_comp, d_comp, x, diag = map(v, (a_real, c_real, a_comp, b_comp, c_comp,
+                                                                          d_comp, x, diag))
+        p = lambda a: C.c_void_p(a.ctypes.data)  # noqa: E731
+        rc = self._lib.cel_compute(self._h, float(jitter), a_real.size, p(a_real), p(c_real), a_comp.size,
+                                   p(a_comp), p(b_comp), p(c_comp), p(d_comp), 0, None, None, None,
+                                   x.size, p(x), p(diag))
+        _capi.check(rc, self._h)
+        if halo:
+            _capi.check(self._lib.cel_span_trim(self._h, int(halo)), self._h)
+        self.N = x.size - int(halo)
+        self.J = a_real.size + 2 * a_comp.size
+
+    def _use_stream(self, t):
+        import torch
+        self._lib.cel_set_stream(self._h, C.c_void_p(torch.cuda.current_stream(t.device).cuda_stream or 1))
+
+    def _cols(self, b):
+        import torch
+        if not (b.is_cuda and b.dtype == torch.float64):
+            raise RuntimeError("expected a float64 CUDA tensor")
+        squeeze = b.dim() == 1
+        bm = b[:, None] if squeeze else b
+        if bm.shape[0] != self.N:
+            raise RuntimeError("dimension mismatch")
+        # column-major N x nrhs, as the C ABI (and Eigen) lays matrices out
+        return bm.transpose(0, 1).contiguous(), squeeze
+
+    def solve(self, b):
+        """K^-1 b (GP.apply_inverse, celerite.py:307-328) for a device tensor (N,) or (N, nrhs)."""
+        import torch
+        cols, squeeze = self._cols(b)
+        out = torch.empty_like(cols)
+        self._use_stream(b)
+        rc = self._lib.cel_solve_device(self._h, cols.shape[0], C.c_void_p(cols.data_ptr()), C.c_void_p(out.data_ptr()))
+        _capi.check(rc, self._h)
+        out = out.transpose(0, 1)
+        return out[:, 0] if squeeze else out
+
+    def dot_L(self, z):
+        """L z with K = L L^T (cholesky.h:409-431)."""
+        import torch
+        cols, squeeze = self._cols(z)
+        out = torch.empty_like(cols)
+        self._use_stream(z)
+        rc = self._lib.cel_dot_L_device(self._h, cols.shape[0], C.c_void_p(cols.data_ptr()), C.c_void_p(out.data_ptr()))
+        _capi.check(rc, self._h)
+        out = out.transpose(0, 1)
+        return out[:, 0] if squeeze else out
+
+    # ---- span primitives (used by DistributedLongSeries) -----------------------------------
+    def summarize(self, op, cols):
+        import torch
+        nrhs = cols.shape[0]
+        nb = 1 if op == OP_DOT_L else self.J
+        out = torch.empty((nrhs + nb, self.J), dtype=torch.float64, device=cols.device)
+        self._use_stream(cols)
+        rc = self._lib.cel_span_summarize(self._h, op, nrhs, C.c_void_p(cols.data_ptr()), C.c_void_p(out.data_ptr()))
+        _capi.check(rc, self._h)
+        return out
+
+    def apply(self, op, cols, carry_in, reuse_summary=True):
+        import torch
+        out = torch.empty_like(cols)
+        self._use_stream(cols)
+        cptr = C.c_void_p(carry_in.data_ptr()) if carry_in is not None else None
+        rc = self._lib.cel_span_apply(self._h, op, cols.shape[0], C.c_void_p(cols.data_ptr()), cptr,
+                                      C.c_void_p(out.data_ptr()), 1 if reuse_summary else 0)
+        _capi.check(rc, self._h)
+        return out
+
+    def launch_count(self):
+        return int(self._lib.cel_launch_count(self._h))
+
+
+class DistributedLongSeries(object):
+    """One long series split by time over the ranks of ``torch.distributed`` (one GPU each)."""
+
+    def __init__(self, device=-1, group=None):
+        import torch.distributed as dist
+        self.dist = dist
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.local = LongSeries(device)
+        self.lo = self.hi = self.halo = 0
+
+    def compute(self, jitter, a_real, c_real, a_comp, b_comp, c_comp, d_comp, x, diag, halo):
+        """x, diag: the FULL host arrays (every rank slices its own span + halo)."""
+        N = len(x)
+        self.lo, self.hi = span_bounds(N, self.world, self.rank)
+        self.halo = min(int(halo), self.lo)
+        s0 = self.lo - self.halo
+        self.local.compute(jitter, a_real, c_real, a_comp, b_comp, c_comp, d_comp, x[s0:self.hi], diag[s0:self.hi],
+                           halo=self.halo)
+
+    def _sweep(self, op, cols):
+        import torch
+        summ = self.local.summarize(op, cols)
+        # concatenated along dim 0 (the form both NCCL and gloo accept), viewed per rank afterwards
+        gathered = torch.empty((self.world * summ.shape[0], summ.shape[1]), dtype=summ.dtype, device=summ.device)
+        self.dist.all_gather_into_tensor(gathered, summ, group=self.group)
+        gathered = gathered.view(self.world, summ.shape[0], summ.shape[1])
+        carry = fold_carries(gathered, self.rank, op, cols.shape[0], self.local.J)
+        return self.local.apply(op, cols, carry, reuse_summary=True)
+
+    def solve(self, b_local):
+        cols, squeeze = self.local._cols(b_local)
+        xd = self._sweep(OP_SOLVE_FORWARD, cols)
+        z = self._sweep(OP_SOLVE_BACKWARD, xd)
+        z = z.transpose(0, 1)
+        return z[:, 0] if squeeze else z
+
+    def dot_L(self, z_local):
+        cols, squeeze = self.local._cols(z_local)
+        out = self._sweep(OP_DOT_L, cols).transpose(0, 1)
+        return out[:, 0] if squeeze else out

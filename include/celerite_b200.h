@@ -156,6 +156,35 @@ int cel_batched_compute(cel_solver* s, int64_t B, int N, int64_t stride,
                         double* phi, double* u, double* W, double* D, double* out_logdet,
                         int32_t* status);
 
+/* ---- long single series: chunked two-pass scans on device-resident data -------------------
+ * (no counterpart in the reference, whose sweeps are N dependent steps on one thread,
+ * cholesky.h:239-259, 419-428).  The stored factor of the handle is applied to DEVICE-resident
+ * right-hand sides (N_local x nrhs column-major): the time axis is cut into chunks swept
+ * concurrently, chunk-to-chunk carries (J^2+J doubles) are composed in a short middle stage, and
+ * a second pass writes the result.  cel_solve / cel_dot_L use the same path automatically for
+ * N >= 16384.  d_out must not alias d_b. */
+int cel_solve_device(cel_solver* s, int nrhs, const double* d_b, double* d_out);   /* cholesky.h:218-318 */
+int cel_dot_L_device(cel_solver* s, int nrhs, const double* d_z, double* d_out);   /* cholesky.h:409-431 */
+
+/* Multi-GPU form: every rank holds the factor of ITS span of the series.  A rank factorises
+ * [lo - halo, hi) with cel_compute (the halo warms the recursion up: its memory of the past decays
+ * like prod(phi^2)) and then declares the first `halo` steps as not belonging to
+ * the span.  One sweep is then
+ *     cel_span_summarize  -> this span's affine map: d_summary[(nrhs + nb) * J], first the nrhs
+ *                            offsets c, then the nb columns of M (nb = J; dot_L: nb = 1, the
+ *                            diagonal)            op: 0 forward solve (out = x/D), 1 dot_L,
+ *                                                     2 backward solve (in = x/D, out = K^-1 b)
+ *     all-gather of the summaries (the only collective: (J^2+J)*8 bytes per rank), each rank
+ *     folds the maps of the ranks before it (after it, for op 2) into its incoming carry
+ *     cel_span_apply      -> result for the span from that carry (d_carry_in: nrhs*J, NULL = 0;
+ *                            reuse_summary != 0 skips pass 1 when it directly follows the
+ *                            summarize call of the same op and input). */
+int cel_span_trim(cel_solver* s, int halo);
+int cel_span_summarize(cel_solver* s, int op, int nrhs, const double* d_in, double* d_summary);
+int cel_span_apply(cel_solver* s, int op, int nrhs, const double* d_in, const double* d_carry_in,
+                   double* d_out, int reuse_summary);
+int cel_span_dims(const cel_solver* s, int* n_local, int* J, int* nchunks, int* chunk_len);
+
 /* ---- gradient without any allocation (no counterpart in the reference) ----------------------
  * For callers that must not allocate: applications that gave the whole GPU to their own pool
  * allocator and forbid cudaMalloc/cudaFree once running (both synchronise the device), fixed

@@ -1,0 +1,110 @@
+"""GPU parity of the chunked two-pass scans (scan.cu): solve and dot_L on long series against
+the CPU oracle, through the drop-in host API (cel_solve / cel_dot_L switch to the chunked path
+at N >= 16384), the device API, and the multi-GPU span protocol emulated on one GPU."""
+import numpy as np
+import pytest
+
+import oracle
+from tests.util import RTOL_SOLVE, rel_inf
+
+pytestmark = pytest.mark.gpu
+E0, E2 = np.empty(0), np.empty((0, 0))
+
+
+def _problem(N, Jr, Jc, seed):
+    from celerite_b200 import synth
+    b = synth.make_batch(1, N, Jr, Jc, seed=seed)
+    j, ar, cr, ac, bc, cc, dc = synth.split_row(b["coeffs"][0], Jr, Jc)
+    return oracle.Problem(j, ar, cr, ac, bc, cc, dc, b["t"][0], b["diag"][0]), b["y"][0]
+
+
+@pytest.mark.parametrize("N,Jr,Jc,nrhs", [(16384, 0, 1, 1), (50001, 1, 1, 2), (40000, 0, 4, 3), (20000, 2, 6, 1),
+                                          (17000, 0, 16, 1)])
+def test_host_api_uses_chunked_path(N, Jr, Jc, nrhs):
+    from celerite_b200 import solver
+    p, y = _problem(N, Jr, Jc, seed=N)
+    chk = oracle.best()
+    f = chk.factor(p)
+    s = solver.CholeskySolver()
+    s.compute(p.jitter, p.a_real, p.c_real, p.a_comp, p.b_comp, p.c_comp, p.d_comp, E0, E2, E2, p.x, p.diag)
+    rhs = np.random.default_rng(N).standard_normal((N, nrhs))
+    rhs[:, 0] = y
+    n0 = s.launch_count()
+    z = s.solve(rhs)
+    assert s.launch_count() - n0 > 4          # the multi-kernel chunked path, not the 2-kernel serial one
+    assert rel_inf(z, chk.solve(f, rhs)) < RTOL_SOLVE
+    assert rel_inf(s.dot_L(rhs), chk.dot_L(f, rhs)) < RTOL_SOLVE
+    # second call reuses the cached chunk maps
+    assert rel_inf(s.solve(rhs), chk.solve(f, rhs)) < RTOL_SOLVE
+
+
+def test_device_api_and_span_protocol_on_one_gpu():
+    """Three spans with warm-up halos on ONE GPU, the all-gather done by hand: must reproduce
+    the single-span result (and the oracle)."""
+    import torch
+    from celerite_b200 import longseries as ls
+    N, Jr, Jc = 60000, 0, 2
+    p, y = _problem(N, Jr, Jc, seed=77)
+    chk = oracle.best()
+    f = chk.factor(p)
+    dev = torch.device("cuda:0")
+    rng = np.random.default_rng(1)
+    B = np.stack([y, rng.standard_normal(N)], axis=1)
+    zref, lref = chk.solve(f, B), chk.dot_L(f, B)
+
+    whole = ls.LongSeries(0)
+    whole.compute(p.jitter, p.a_real, p.c_real, p.a_comp, p.b_comp, p.c_comp, p.d_comp, p.x, p.diag)
+    bt = torch.from_numpy(B).to(dev)
+    assert rel_inf(whole.solve(bt).cpu().numpy(), zref) < RTOL_SOLVE
+    assert rel_inf(whole.dot_L(bt).cpu().numpy(), lref) < RTOL_SOLVE
+    assert rel_inf(whole.solve(bt[:, 0]).cpu().numpy(), zref[:, 0]) < RTOL_SOLVE
+
+    world, halo = 3, 4000
+    spans = [ls.span_bounds(N, world, r) for r in range(world)]
+    locs = []
+    for (lo, hi) in spans:
+        h = min(halo, lo)
+        L = ls.LongSeries(0)
+        L.compute(p.jitter, p.a_real, p.c_real, p.a_comp, p.b_comp, p.c_comp, p.d_comp,
+                  p.x[lo - h:hi], p.diag[lo - h:hi], halo=h)
+        locs.append(L)
+
+    def sweep(op, cols_per_rank):
+        summ = torch.stack([L.summarize(op, c) for L, c in zip(locs, cols_per_rank)])
+        outs = []
+        for r, (L, c) in enumerate(zip(locs, cols_per_rank)):
+            carry = ls.fold_carries(summ, r, op, c.shape[0], L.J)
+            # summaries of all ranks were taken before any apply: pass 1 must be redone per rank
+            outs.append(L.apply(op, c, carry, reuse_summary=False))
+        return outs
+
+    cols = [torch.from_numpy(np.ascontiguousarray(B[lo:hi].T)).to(dev) for (lo, hi) in spans]
+    xd = sweep(ls.OP_SOLVE_FORWARD, cols)
+    z = sweep(ls.OP_SOLVE_BACKWARD, xd)
+    zz = np.concatenate([t.cpu().numpy().T for t in z], axis=0)
+    assert rel_inf(zz, zref) < RTOL_SOLVE
+    lz = sweep(ls.OP_DOT_L, cols)
+    ll = np.concatenate([t.cpu().numpy().T for t in lz], axis=0)
+    assert rel_inf(ll, lref) < RTOL_SOLVE
+
+
+def test_full_size_properties_cfg4_like():
+    """N = 2e6, J = 8 (a fifth of config 4): size-independent properties.
+    K (K^-1 b) = b through the stateless dot() + measurement variances, and linearity."""
+    import torch
+    from celerite_b200 import longseries as ls, solver
+    N, Jr, Jc = 2_000_000, 0, 4
+    p, y = _problem(N, Jr, Jc, seed=5)
+    dev = torch.device("cuda:0")
+    L = ls.LongSeries(0)
+    L.compute(p.jitter, p.a_real, p.c_real, p.a_comp, p.b_comp, p.c_comp, p.d_comp, p.x, p.diag)
+    b1 = torch.from_numpy(y).to(dev)
+    b2 = torch.from_numpy(np.random.default_rng(2).standard_normal(N)).to(dev)
+    z1, z2, z12 = L.solve(b1), L.solve(b2), L.solve(b1 + 2.0 * b2)
+    scale = float(z12.abs().max())
+    assert float((z12 - (z1 + 2.0 * z2)).abs().max()) / scale < 1e-11
+    s = solver.CholeskySolver()
+    z = z1.cpu().numpy()
+    kz = s.dot(p.jitter, p.a_real, p.c_real, p.a_comp, p.b_comp, p.c_comp, p.d_comp, E0, E2, E2, p.x, z)[:, 0]
+    kz += p.diag * z
+    assert rel_inf(kz, y) < 1e-8
