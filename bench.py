@@ -159,13 +159,186 @@ def run_reference(args, wl):
     return 0
 
 
+def cfg4_series(N, jc=4, seed=42):
+    """The one long series of config 4: N points, jc SHO terms (J = 2*jc)."""
+    from celerite_b200 import synth
+    rng = np.random.Generator(np.random.PCG64(seed))
+    coeffs = synth.make_coeffs(rng, 1, 0, jc)
+    t = np.empty((1, N)); d = np.empty((1, N)); y = np.empty((1, N))
+    synth.fill_series(rng, t, d, y)
+    z = rng.standard_normal(N)
+    return coeffs[0], t[0], d[0], y[0], z
+
+
+def cfg4_cpu(chk, coeffs, t, d, y, z, jc, n_sample):
+    """reference solve + dot_L on ONE host thread (a single series is inherently serial on the
+    CPU), on the first n_sample points; returns seconds for (solve + dot_L), compute untimed."""
+    import oracle
+    from celerite_b200 import synth
+    j, ar, cr, ac, bc, cc, dc = synth.split_row(coeffs, 0, jc)
+    p = oracle.Problem(j, ar, cr, ac, bc, cc, dc, t[:n_sample], d[:n_sample])
+    f = chk.factor(p)
+    t0 = time.perf_counter()
+    chk.solve(f, y[:n_sample])
+    chk.dot_L(f, z[:n_sample])
+    dt = time.perf_counter() - t0
+    if hasattr(chk, "release"):
+        chk.release(f)
+    return dt
+
+
+def run_cfg4(args):
+    """config 4: one series, N = 1e7, J = 8: apply_inverse + dot_L as chunked scans; the time
+    axis is split over the ranks (strong scaling), carries exchanged with one all-gather per sweep."""
+    N, jc = (args.batch or 10_000_000), (args.jc or 4)
+    J = 2 * jc
+    desc = "cfg4: single series N=%d, J=%d (%d SHOTerms), apply_inverse + dot_L via chunked scan" % (N, J, jc)
+    rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+    metric = "GP apply_inverse + dot_L point-terms/sec (2*N*J / device time)"
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        import oracle
+        chk = oracle.best()
+        n_sample = min(N, 1_000_000)
+        coeffs, t, d, y, z = cfg4_series(n_sample, jc)
+        for _ in range(max(0, min(args.warmup, 1))):
+            cfg4_cpu(chk, coeffs, t, d, y, z, jc, n_sample)
+        steps = max(1, min(args.steps, 5))
+        dt = sum(cfg4_cpu(chk, coeffs, t, d, y, z, jc, n_sample) for _ in range(steps)) / steps
+        value = 2.0 * n_sample * J / dt
+        print(json.dumps({
+            "impl": "reference", "metric": metric, "value": value, "unit": "point-terms/s", "n_gpus": args.gpus,
+            "steps": steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": desc, "sample": "first %d points" % n_sample},
+            "cpu_baseline": {"value": value, "unit": "point-terms/s", "cores": 1, "kind": chk.kind,
+                             "sample": "first %d of %d points, 1 thread (one series is serial on the CPU)" % (n_sample, N)},
+            "e2e": {"value": value, "unit": "point-terms/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}))
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    from celerite_b200 import longseries as ls, solver, synth
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    coeffs, t, d, y, z = cfg4_series(N, jc)
+    j, ar, cr, ac, bc, cc, dc = synth.split_row(coeffs, 0, jc)
+    halo = ls.safe_halo(float(np.min(cc)), float(np.mean(np.diff(t[:100000]))), tol=1e-18, cap=N // (2 * world))
+    if world > 1:
+        eng = ls.DistributedLongSeries(local)
+        eng.compute(j, ar, cr, ac, bc, cc, dc, t, d, halo)
+        lo, hi = eng.lo, eng.hi
+        loc = eng.local
+    else:
+        eng = ls.LongSeries(local)
+        eng.compute(j, ar, cr, ac, bc, cc, dc, t, d)
+        lo, hi = 0, N
+        loc = eng
+    yb = torch.from_numpy(y[lo:hi]).to(dev)
+    zb = torch.from_numpy(z[lo:hi]).to(dev)
+    stream = torch.cuda.current_stream(dev)
+
+    def step():
+        return eng.solve(yb), eng.dot_L(zb)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for _ in range(max(3, args.warmup)):
+        a_inv, lz = step()
+    l0 = loc.launch_count()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        a_inv, lz = step()
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1) / args.steps
+    if world > 1:
+        tms = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        ms = float(tms.item())
+    clocks = sampler.stop() if rank == 0 else None
+    launches = (loc.launch_count() - l0)
+    value = 2.0 * N * J / (ms * 1e-3)
+
+    # parity on this rank's span against the reference on the first points (rank 0) ------------
+    line = None
+    if rank == 0:
+        peak, peak_src = measured_peak_gbs()
+        alg = (hi - lo) * ((6 * J + 5) * 8 + (3 * J + 3) * 8)     # solve + dot_L, SURVEY.md §8d
+        line = {
+            "metric": metric, "value": value, "unit": "point-terms/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": desc, "N": N, "J": J, "halo": int(halo) if world > 1 else 0,
+                       "sharding": "time axis split into %d spans; one all-gather of (J^2+J) doubles per sweep" % world,
+                       "inputs": "factor %.2f GB per rank, larger than the 126 MB L2" % ((hi - lo) * (3 * J + 1) * 8 / 1e9)},
+            "roofline": {"bound": "hbm", "achieved": alg / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": alg / (ms * 1e-3) / 1e9 / peak, "traffic": ncu_traffic("cfg4"),
+                         "peak_source": peak_src, "kernel": "k_chunk_forward/backward (two passes each)",
+                         "algorithmic_bytes_per_launch": alg,
+                         "note": "algorithmic = one streaming pass; the two-pass scan reads the factor twice"},
+            "gpu_launches": launches, "clocks": clocks,
+        }
+    # e2e through the drop-in host API (single GPU only: cel_solve / cel_dot_L with host arrays)
+    if world == 1:
+        s = solver.CholeskySolver(local)
+        E0, E2 = np.empty(0), np.empty((0, 0))
+        s.compute(j, ar, cr, ac, bc, cc, dc, E0, E2, E2, t, d)
+        s.solve(y); s.dot_L(z)
+        t0 = time.perf_counter()
+        reps = 2
+        for _ in range(reps):
+            zi = s.solve(y)
+            lzi = s.dot_L(z)
+        edt = (time.perf_counter() - t0) / reps
+        line["e2e"] = {"value": 2.0 * N * J / edt, "unit": "point-terms/s", "ms_per_step": edt * 1e3,
+                       "h2d_bytes_per_step": 2 * N * 8, "d2h_bytes_per_step": 2 * N * 8,
+                       "matches_device_path": bool(np.allclose(zi[:, 0], a_inv.cpu().numpy(), rtol=1e-12, atol=0)),
+                       "note": "cel_solve + cel_dot_L with pageable host arrays, wall clock"}
+    elif rank == 0:
+        line["e2e"] = {"value": None, "unit": "point-terms/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                       "note": "the drop-in host API is single-GPU; multi-GPU spans are device-resident"}
+    if rank == 0 and not args.no_cpu_baseline:
+        import oracle
+        chk = oracle.best()
+        n_sample = min(N, 1_000_000)
+        cdt = cfg4_cpu(chk, coeffs, t, d, y, z, jc, n_sample)
+        jj, a_r, c_r, a_c, b_c, c_c, d_c = synth.split_row(coeffs, 0, jc)
+        p = oracle.Problem(jj, a_r, c_r, a_c, b_c, c_c, d_c, t[:n_sample], d[:n_sample])
+        f = chk.factor(p)
+        zr = chk.solve(f, y[:n_sample])[:, 0]
+        m = min(n_sample, hi - lo) // 2      # away from the truncated end of the CPU sample
+        got = a_inv[:m].cpu().numpy()
+        line["cpu_baseline"] = {"value": 2.0 * n_sample * J / cdt, "unit": "point-terms/s", "cores": 1,
+                                "kind": chk.kind,
+                                "sample": "first %d of %d points, 1 thread (one series is serial on the CPU)" % (n_sample, N),
+                                "max_rel_diff_vs_gpu": float(np.max(np.abs(got - zr[:m])) / np.max(np.abs(zr[:m])))}
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS) + ["cfg4"])
     ap.add_argument("--batch", type=int, default=0, help="override series per GPU (debug)")
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -173,6 +346,8 @@ def main():
     ap.add_argument("--no-grad", action="store_true", help="skip the extra log-lik+grad measurement")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.workload == "cfg4":
+        return run_cfg4(args)
     wl = dict(WORKLOADS[args.workload])
     if args.batch:
         wl["B"] = args.batch
