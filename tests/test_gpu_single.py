@@ -13,10 +13,11 @@ pytestmark = pytest.mark.gpu
 NAMES = golden_names()
 
 
-@pytest.fixture(scope="module")
-def S():
-    from celerite_b200 import solver
-    return solver
+@pytest.fixture(scope="module", params=["solver", "solver_ext"])
+def S(request):
+    """both host layers over the C ABI: the ctypes mirror and the pybind11/C++ host class"""
+    import importlib
+    return importlib.import_module("celerite_b200." + request.param)
 
 
 def _compute(solver_mod, p):
