@@ -100,6 +100,7 @@ int cel_compute(cel_solver* s, double jitter, int Jr, const double* a_real, cons
     CEL_CUDA_TRY(s, cudaMemcpyAsync(res, s->out0.p, sizeof(double), cudaMemcpyDeviceToHost, st));
     CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
     s->N = N; s->J = 0; s->Jr = s->Jc = s->Jg = 0;
+    s->have_coeffs = true;
     s->log_det = res[0];
     s->computed = true;
     return CEL_OK;
@@ -121,6 +122,7 @@ int cel_compute(cel_solver* s, double jitter, int Jr, const double* a_real, cons
   CEL_CUDA_TRY(s, cudaMemcpyAsync(res, s->out0.p, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
   CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
   s->N = N; s->J = J; s->Jr = Jr; s->Jc = Jc; s->Jg = Jg;
+  s->have_coeffs = true;
   if (ires[0] != 0) {
     char buf[128];
     snprintf(buf, sizeof(buf), "failed to factorize or solve matrix (D_n < 0 at n = %d)", ires[1] - 1);
@@ -256,9 +258,38 @@ int cel_dot(cel_solver* s, double jitter, int Jr, const double* a_real, const do
 
 // ---- not built yet (declared so the boundary is stable) ---------------------------------------
 int cel_predict(cel_solver* s, int N, const double* y, int M, const double* xs, double* out) {
-  (void)N; (void)y; (void)M; (void)xs; (void)out;
   if (!s) return CEL_INVALID_ARGUMENT;
-  CEL_FAIL(s, CEL_UNSUPPORTED, "cel_predict is not implemented yet");
+  if (s->computed && N != s->N) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "dimension mismatch");   // cholesky.h:600
+  if (!s->computed) CEL_FAIL(s, CEL_NOT_COMPUTED, "you must call 'compute' first");          // cholesky.h:601
+  if (M < 0 || !y || (M > 0 && (!xs || !out))) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null pointer");
+  if (!s->have_coeffs)
+    CEL_FAIL(s, CEL_NOT_COMPUTED, "predict needs the kernel coefficients of compute(): they are not part of "
+                                  "the pickled state (solver.cpp:36-42)");
+  if (M == 0) return CEL_OK;
+  // alpha = K^-1 y stays on the device (cholesky.h:608)
+  double* dummy = static_cast<double*>(s->pinned);
+  int rc = sweep_prepare(s, N, 1, y, dummy);
+  if (rc != CEL_OK) return rc;
+  cudaStream_t st = s->stream;
+  if (s->J >= 1 && N >= kChunkedMinN) {
+    rc = cel_solve_device(s, 1, s->in0.d(), s->out1.d());
+    if (rc != CEL_OK) return rc;
+  } else {
+    CEL_CUDA_TRY(s, cel::launch_solve(sweep_args(s, 1), st));
+    s->launches += 2;
+  }
+  CEL_CUDA_TRY(s, s->scratch0.reserve(dbytes(2 * (size_t)M)));
+  double* dxs = s->scratch0.d();
+  double* dout = dxs + M;
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(dxs, xs, dbytes(M), cudaMemcpyHostToDevice, st));
+  cel::PredictArgs a{};
+  a.N = N; a.M = M; a.Jr = s->Jr; a.Jc = s->Jc;
+  a.coeffs = s->coeffs.d(); a.t = s->t.d(); a.alpha = s->out1.d(); a.xs = dxs; a.out = dout;
+  CEL_CUDA_TRY(s, cel::launch_predict(a, st));
+  s->launches += 1;
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(out, dout, dbytes(M), cudaMemcpyDeviceToHost, st));
+  CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
+  return CEL_OK;
 }
 
 int cel_grad_log_likelihood(cel_solver* s, double jitter, int Jr, const double* a_real, const double* c_real,
@@ -441,6 +472,7 @@ int cel_set_state(cel_solver* s, int computed, int N, int J, double log_det, con
   s->maps_valid[0] = s->maps_valid[1] = s->maps_valid[2] = false;
   s->N = N; s->J = J; s->log_det = log_det;
   s->Jr = s->Jc = s->Jg = 0;  // coefficients are not part of the pickled state (solver.cpp:36-42)
+  s->have_coeffs = false;
   if (computed && N > 0) {
     if (!D || (J > 0 && (!W || (N > 1 && (!phi || !u))))) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null factor array");
     CEL_CUDA_TRY(s, cudaSetDevice(s->device));

@@ -130,6 +130,17 @@ cudaError_t launch_middle(int J, int nrhs, int nbasis, int diag, int reverse, in
                           int compose_only, int skip_compose, cudaStream_t stream);
 int middle_nsuper(int nunits);
 
+// predict (cholesky.h:599-698): merge sweeps over data times t[N] and sorted test points xs[M]
+struct PredictArgs {
+  int N, M, Jr, Jc;
+  const double* coeffs;   // one coefficient row
+  const double* t;
+  const double* alpha;    // K^-1 y
+  const double* xs;
+  double* out;            // M
+};
+cudaError_t launch_predict(const PredictArgs& a, cudaStream_t stream);
+
 // J == 0 value and d/djitter: out[0] = -0.5*sum(y^2/D + log D), out[1] = sum(0.5 y^2/D^2 - 0.5/D)
 cudaError_t launch_jitter_only_grad(int N, const double* diag, const double* y, double jitter, double* out2,
                                     cudaStream_t stream);

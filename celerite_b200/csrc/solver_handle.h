@@ -55,7 +55,7 @@ struct cel_solver {
   cel::DevBuf phi, u, W, D;        // reference layout, J fastest
   cel::DevBuf t;                   // kept for predict (cholesky.h:81-87)
   cel::DevBuf coeffs;              // [jitter, a_real, c_real, a_comp, b_comp, c_comp, d_comp]
-  double h_coeffs_jitter = 0.0;
+  bool have_coeffs = false;        // false after set_state (unpickle): predict is then unavailable
 
   // ---- chunked scans (scan.cu): per-direction chunk maps, valid for the current factor ----
   int n_off = 0;                   // stored steps in front of the span (warm-up halo), see cel_span_trim

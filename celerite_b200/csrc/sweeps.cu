@@ -372,3 +372,111 @@ cudaError_t launch_jitter_only_grad(int N, const double* diag, const double* y, 
   return cudaGetLastError();
 }
 }  // namespace cel
+
+// ---------------------------------------------------------------------------------------------
+// predict — conditional mean at M sorted test points in O(N + M) (cholesky.h:599-698).
+// alpha = K^-1 y comes from the solve kernels; this kernel is the two merge sweeps.  One warp;
+// lane j owns row j of the J_real + 2 J_comp state Q (general rows take no part, 624-634).  The
+// control flow (which test points fall between which data points) depends only on shared
+// scalars, so all lanes stay converged.
+// ---------------------------------------------------------------------------------------------
+namespace cel {
+namespace {
+template <int L>
+__global__ void __launch_bounds__(kWarp) k_predict(PredictArgs a) {
+  const int k = threadIdx.x % L;
+  const int N = a.N, M = a.M, Jr = a.Jr, Jc = a.Jc, Jp = Jr + 2 * Jc;
+  const double* row = a.coeffs;
+  const double* a_real = row + 1;
+  const double* c_real = a_real + Jr;
+  const double* a_comp = c_real + Jr;
+  const double* b_comp = a_comp + Jc;
+  const double* c_comp = b_comp + Jc;
+  const double* d_comp = c_comp + Jc;
+  int type = 3;  // 0 real, 1 cos row, 2 sin row, 3 idle
+  double ca = 0.0, cb = 0.0, cc = 0.0, cd_ = 0.0;
+  if (k < Jr) { type = 0; ca = a_real[k]; cc = c_real[k]; }
+  else if (k < Jp) {
+    const int q = (k - Jr) >> 1;
+    type = 1 + ((k - Jr) & 1);
+    ca = a_comp[q]; cb = b_comp[q]; cc = c_comp[q]; cd_ = d_comp[q];
+  }
+  const double* t = a.t;
+  const double* xs = a.xs;
+  const double* alpha = a.alpha;
+  double* pred = a.out;
+  const bool lead = threadIdx.x == 0;
+
+  // ---- forward pass (614-653) ----
+  int m = 0;
+  while (m < M && xs[m] <= t[0]) { if (lead) pred[m] = 0.0; ++m; }
+  double Q = 0.0;
+  for (int n = 0; n < N; ++n) {
+    const double alphan = alpha[n];
+    const double tref = (n < N - 1) ? t[n + 1] : t[N - 1];
+    const double tn = t[n], dt = tref - tn;
+    if (type == 0) { Q += alphan; Q *= exp(-cc * dt); }
+    else if (type != 3) {
+      double sd, cd;
+      sincos(cd_ * tn, &sd, &cd);
+      Q += alphan * (type == 1 ? cd : sd);
+      Q *= exp(-cc * dt);
+    }
+    while (m < M && (n == N - 1 || xs[m] <= tref)) {
+      const double xm = xs[m], dtm = xm - tref;
+      double term = 0.0;
+      if (type == 0) term = ca * exp(-cc * dtm) * Q;
+      else if (type != 3) {
+        double sd, cd;
+        sincos(cd_ * xm, &sd, &cd);
+        const double tmp = exp(-cc * dtm);
+        term = (type == 1 ? (ca * cd + cb * sd) : (ca * sd - cb * cd)) * tmp * Q;
+      }
+      term = group_sum<L>(term);
+      if (lead) pred[m] = term;
+      ++m;
+    }
+  }
+  __syncwarp();
+  // ---- backward pass (655-695) ----
+  m = M - 1;
+  while (m >= 0 && xs[m] > t[N - 1]) --m;
+  Q = 0.0;
+  for (int n = N - 1; n >= 0; --n) {
+    const double alphan = alpha[n];
+    const double tref = (n > 0) ? t[n - 1] : t[0];
+    const double tn = t[n], dt = tn - tref;
+    if (type == 0) { Q += alphan * ca; Q *= exp(-cc * dt); }
+    else if (type != 3) {
+      double sd, cd;
+      sincos(cd_ * tn, &sd, &cd);
+      Q += alphan * (type == 1 ? (ca * cd + cb * sd) : (ca * sd - cb * cd));
+      Q *= exp(-cc * dt);
+    }
+    while (m >= 0 && (n == 0 || xs[m] > tref)) {
+      const double xm = xs[m], dtm = tref - xm;
+      double term = 0.0;
+      if (type == 0) term = exp(-cc * dtm) * Q;
+      else if (type != 3) {
+        double sd, cd;
+        sincos(cd_ * xm, &sd, &cd);
+        term = (type == 1 ? cd : sd) * exp(-cc * dtm) * Q;
+      }
+      term = group_sum<L>(term);
+      if (lead) pred[m] += term;
+      --m;
+    }
+  }
+}
+}  // namespace
+
+cudaError_t launch_predict(const PredictArgs& a, cudaStream_t stream) {
+  const int Jp = a.Jr + 2 * a.Jc;
+  if (Jp > kCoopMaxJ) return cudaErrorInvalidValue;
+#define CALL(LL) { k_predict<LL><<<1, LL < 32 ? 32 : LL, 0, stream>>>(a); }
+  if (Jp <= 1) { CALL(1); } else if (Jp <= 2) { CALL(2); } else if (Jp <= 4) { CALL(4); }
+  else if (Jp <= 8) { CALL(8); } else if (Jp <= 16) { CALL(16); } else { CALL(32); }
+#undef CALL
+  return cudaGetLastError();
+}
+}  // namespace cel

@@ -96,6 +96,23 @@ def test_gp_apply_inverse_dot_sample(cel):
     assert s.shape == (3, len(t)) and np.all(np.isfinite(s))
 
 
+def test_gp_predict(cel):
+    """tests/test_celerite.py:468-496: GP.predict mean (O(N+M) solver.predict path) vs dense."""
+    rng = np.random.default_rng(11)
+    t = np.sort(rng.uniform(0, 5, 200))
+    yerr = rng.uniform(0.1, 0.5, len(t))
+    y = np.sin(t)
+    kernel = cel.terms.RealTerm(0.1, 0.5) + cel.terms.ComplexTerm(0.6, 0.7, 1.0)
+    gp = cel.GP(kernel)
+    gp.compute(t, yerr)
+    x = np.linspace(-1.0, 6.0, 500)
+    K = _dense(cel, kernel, t, yerr)
+    Ks = kernel.get_value(x[:, None] - t[None, :])
+    mu0 = Ks @ np.linalg.solve(K, y)
+    mu = gp.predict(y, x, return_cov=False, return_var=False)
+    assert np.allclose(mu, mu0)
+
+
 def test_gp_not_positive_definite_and_quiet(cel):
     """tests/test_celerite.py:326-345: LinAlgError from compute and log_likelihood, -inf when
     quiet, RuntimeError before compute."""

@@ -63,6 +63,31 @@ def test_golden(golden, S, name):
                 p.U if p.U is not None else np.empty((0, 0)),
                 p.V if p.V is not None else np.empty((0, 0)), p.x, c.rhs)
     assert rel_inf(out, c.dot) < RTOL_SOLVE
+    pred = s.predict(c.y, c.xs)                       # cholesky.h:599-698
+    assert pred.shape == c.predict.shape
+    assert rel_inf(pred, c.predict) < RTOL_SOLVE
+
+
+def test_predict_needs_coefficients_after_unpickle(golden, S):
+    """The pickled state holds no coefficients (solver.cpp:36-42): predict on an unpickled solver
+    is undefined in the reference; here it is refused with a RuntimeError."""
+    c = golden["mixed_j6"]
+    s2 = pickle.loads(pickle.dumps(_compute(S, c.problem), -1))
+    with pytest.raises(RuntimeError):
+        s2.predict(c.y, c.xs)
+
+
+def test_predict_long_series(S):
+    from celerite_b200 import synth
+    chk = oracle.best()
+    N, M = 20000, 3000
+    b = synth.make_batch(1, N, 1, 2, seed=8)
+    j, ar, cr, ac, bc, cc, dc = synth.split_row(b["coeffs"][0], 1, 2)
+    p = oracle.Problem(j, ar, cr, ac, bc, cc, dc, b["t"][0], b["diag"][0])
+    f = chk.factor(p)
+    xs = np.sort(np.random.default_rng(0).uniform(p.x[0] - 1, p.x[-1] + 1, M))
+    s = _compute(S, p)
+    assert rel_inf(s.predict(b["y"][0], xs), chk.predict(p, f, b["y"][0], xs)) < RTOL_SOLVE
 
 
 def test_not_computed_raises(S):
