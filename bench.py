@@ -38,6 +38,10 @@ WORKLOADS = {
     # name: (B per GPU, N, Jr, Jc)
     "cfg2": dict(B=65536, N=2000, Jr=0, Jc=1, desc="cfg2: 65,536 series x N=2,000, one SHOTerm (J=2), log_likelihood"),
     "cfg5": dict(B=125000, N=1000, Jr=0, Jc=2, desc="cfg5: 10^6 series x N=1,000 over 8 GPUs (125,000 per GPU), two SHOTerms (J=4), log_likelihood"),
+    # the materialising batched factorisation (compute, factor written in the reference layout) on cfg2's
+    # batch: the HBM-bound member of the family, (3J+3)*8 = 72 B/point at J=2
+    "cfg2m": dict(B=65536, N=2000, Jr=0, Jc=1, materialise=True,
+                  desc="cfg2m: 65,536 series x N=2,000, one SHOTerm (J=2), batched compute writing phi,u,W,D"),
     # cfg3 is a sweep over J in BASELINE.json; --jc picks the number of SHO terms (J = 2*jc)
     "cfg3": dict(B=1024, N=100000, Jr=0, Jc=4, grad=True, desc="cfg3: 1,024 series x N=100,000, J=2*jc (SHOTerms), grad_log_likelihood"),
 }
@@ -419,6 +423,22 @@ def main():
     primary_is_grad = bool(wl.get("grad"))
     if primary_is_grad:
         step_device = step_grad  # noqa: F811
+    materialise = bool(wl.get("materialise"))
+    if materialise:
+        m_phi = torch.empty((B, N - 1, J), dtype=torch.float64, device=dev)
+        m_u = torch.empty((B, N - 1, J), dtype=torch.float64, device=dev)
+        m_W = torch.empty((B, N, J), dtype=torch.float64, device=dev)
+        m_D = torch.empty((B, N), dtype=torch.float64, device=dev)
+
+        def step_device():  # noqa: F811
+            import ctypes as C
+            lib = bs._lib
+            lib.cel_set_stream(bs._h, C.c_void_p(stream.cuda_stream or 1))
+            v = lambda x: C.c_void_p(x)  # noqa: E731
+            rc = lib.cel_batched_compute(bs._h, B, N, N, Jr, Jc, v(dc_.data_ptr()), P, v(dt_.data_ptr()),
+                                         v(dd_.data_ptr()), v(m_phi.data_ptr()), v(m_u.data_ptr()), v(m_W.data_ptr()),
+                                         v(m_D.data_ptr()), v(d_out[0].data_ptr()), v(d_status.data_ptr()))
+            _capi.check(rc, bs._h)
 
     def barrier():
         if world > 1:
@@ -454,6 +474,29 @@ def main():
     launches = bs.launch_count() - launches0
     value = world * B * N * J / (ms_step * 1e-3)
 
+    if materialise:
+        # no host-buffer variant of the materialising call exists (the factor is 7.3 GB): report device numbers only
+        if rank == 0:
+            peak, peak_src = measured_peak_gbs()
+            alg_bytes = B * N * 16 + B * (2 * (N - 1) * J + N * J + N) * 8 + B * 12
+            achieved = alg_bytes / (ms_step * 1e-3) / 1e9
+            print(json.dumps({
+                "metric": "GP batched factorisation (materialised) point-terms/sec (N*J*batch / device time)",
+                "value": value, "unit": "point-terms/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f64", "data": "synthetic",
+                "config": {"workload": wl["desc"], "series_per_gpu": B, "N": N, "J": J,
+                           "inputs": "%.2f GB read + %.2f GB written per step per GPU, larger than the 126 MB L2"
+                                     % (2 * B * N * 8 / 1e9, (alg_bytes - 2 * B * N * 8) / 1e9)},
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": ncu_traffic(args.workload), "peak_source": peak_src,
+                             "kernel": "k_compute_lockstep", "algorithmic_bytes_per_launch": alg_bytes},
+                "e2e": {"value": None, "unit": "point-terms/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                        "note": "device-resident API only"},
+                "gpu_launches": launches, "clocks": clocks}))
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
     # ---- end-to-end through the C ABI with host buffers -------------------------------------
     if primary_is_grad:
         h_gval = torch.empty(B, dtype=torch.float64).pin_memory()

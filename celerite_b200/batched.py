@@ -140,6 +140,30 @@ class BatchedSolver(object):
         _capi.check(rc, self._h)
         return val, grad, status
 
+    def compute(self, coeffs, t, diag, Jr, Jc):
+        """Batched CholeskySolver::compute (cholesky.h:41-210) on torch CUDA tensors: returns
+        (phi, u, W, D, logdet, status) with phi,u: (B, N-1, J), W: (B, N, J), D: (B, N) — per
+        series the reference's factor layout (J fastest)."""
+        import torch
+        for a in (coeffs, t, diag):
+            if not (a.is_cuda and a.dtype == torch.float64 and a.is_contiguous()):
+                raise RuntimeError("expected contiguous float64 CUDA tensors")
+        B, N, stride, cstride = self._shapes(coeffs, t, Jr, Jc)
+        J = Jr + 2 * Jc
+        dev = t.device
+        phi = torch.empty((B, max(N - 1, 0), J), dtype=torch.float64, device=dev)
+        u = torch.empty((B, max(N - 1, 0), J), dtype=torch.float64, device=dev)
+        W = torch.empty((B, N, J), dtype=torch.float64, device=dev)
+        D = torch.empty((B, N), dtype=torch.float64, device=dev)
+        logdet = torch.empty(B, dtype=torch.float64, device=dev)
+        status = torch.empty(B, dtype=torch.int32, device=dev)
+        self._lib.cel_set_stream(self._h, C.c_void_p(torch.cuda.current_stream(dev).cuda_stream or 1))
+        p = lambda a: C.c_void_p(a.data_ptr())  # noqa: E731
+        rc = self._lib.cel_batched_compute(self._h, B, N, stride, Jr, Jc, p(coeffs), cstride, p(t), p(diag),
+                                           p(phi), p(u), p(W), p(D), p(logdet), p(status))
+        _capi.check(rc, self._h)
+        return phi, u, W, D, logdet, status
+
     def raw_log_likelihood(self, B, N, stride, Jr, Jc, coeffs_ptr, cstride, t_ptr, diag_ptr, y_ptr,
                            logdet_ptr, quad_ptr, ll_ptr, status_ptr, flags=0, stream=None):
         """Thin pass-through of cel_batched_log_likelihood for callers that manage memory

@@ -512,7 +512,9 @@ int cel_batched_compute(cel_solver* s, int64_t B, int N, int64_t stride, int Jr,
   a.t = t; a.diag = diag; a.y = nullptr;
   a.out_logdet = out_logdet; a.status = status;
   a.phi = phi; a.u = u; a.W = W; a.D = D;
-  CEL_CUDA_TRY(s, cel::launch_loglik_coop(a, s->stream));
+  bool used = false;
+  CEL_CUDA_TRY(s, cel::launch_compute_lockstep(a, s->stream, &used));
+  if (!used) CEL_CUDA_TRY(s, cel::launch_loglik_coop(a, s->stream));
   s->launches += 1;
   return CEL_OK;
 }

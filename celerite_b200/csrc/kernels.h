@@ -38,6 +38,10 @@ constexpr int kLockstepMaxJ = 6;
 constexpr int kLockstepFastJ = 6;   // beyond this the register state spills: use the cooperative kernel
 cudaError_t launch_loglik_lockstep(const BatchArgs& a, cudaStream_t stream);
 
+// Thread-per-series MATERIALISING compute with TMA stores (lockstep_store.cu); *used = false when
+// the batch does not qualify (then call launch_loglik_coop with a.phi set).
+cudaError_t launch_compute_lockstep(const BatchArgs& a, cudaStream_t stream, bool* used);
+
 // Cooperative sweep: L = pow2ceil(J) lanes per series, one row of S per lane.  Fused
 // log-likelihood when a.phi == NULL, materialising compute otherwise.  J <= kCoopMaxJ.
 constexpr int kCoopMaxJ = 32;

@@ -23,151 +23,16 @@
 #include <cuda.h>
 #include <cstdlib>
 
-#include "common.cuh"
-#include "fastmath.cuh"
-#include "kernels.h"
+#include "lockstep_common.cuh"
 
 namespace cel {
 
 namespace {
 
+using namespace lockstep;
+
 constexpr int kLockThreads = 64;   // 2 independent warps per CTA
 constexpr double kLog2Pi = 1.8378770664093454836;
-
-template <int J>
-__device__ __forceinline__ constexpr int tri(int k, int j) { return j * (j + 1) / 2 + k; }
-
-__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(smem_u32(bar))
-      : "memory");
-}
-
-// Per-series recursion state, all in registers.
-template <int J>
-struct LockState {
-  double S[J * (J + 1) / 2];  // upper triangle, S(q,j) q<=j at j*(j+1)/2+q
-  double Wp[J];               // W_{n-1}
-  double DW[J];               // D_{n-1} W_{n-1}
-  double f[J];                // forward-substitution state (cholesky.h:344-354)
-  double xprev, quad;
-  LogAccFast ld;
-  int fail;
-};
-
-// phi, u, v of G consecutive time steps (cholesky.h:127-147): the part of the work that does not
-// depend on the recursion.
-template <int J, int G>
-struct LockGen {
-  double phi[G][J], u[G][J], v[G][J];
-};
-
-// FAST = branch-free math (no basic-block boundaries, so independent chains interleave);
-// otherwise guarded routines with out-of-line stock fallbacks.
-template <int J, int G, bool FAST, bool ALLC>
-__device__ __forceinline__ void lock_gen(LockGen<J, G>& o, const double (&cf)[(J + 1) / 2][4], const int Jc,
-                                         const double (&tt)[G], const double tprev) {
-  constexpr int NP = (J + 1) / 2;
-#pragma unroll
-  for (int g = 0; g < G; ++g) {
-    const double tn = tt[g];
-    const double dx = tn - (g == 0 ? tprev : tt[g == 0 ? 0 : g - 1]);
-#pragma unroll
-    for (int p = 0; p < NP; ++p) {
-      if (ALLC || p < Jc) {  // complex term: rows 2p (cos), 2p+1 (sin)  — cholesky.h:134-147
-        double sd, cd, e;
-        if (FAST) {
-          cel_sincos_core(cf[p][3] * tn, &sd, &cd);
-          e = cel_exp_clamped(-cf[p][2] * dx);
-        } else {
-          cel_sincos(cf[p][3] * tn, &sd, &cd);
-          e = cel_exp(-cf[p][2] * dx);
-        }
-        o.phi[g][2 * p] = e;
-        o.u[g][2 * p] = fma(cf[p][0], cd, cf[p][1] * sd);
-        o.v[g][2 * p] = cd;
-        if (2 * p + 1 < J) {
-          o.phi[g][2 * p + 1] = e;
-          o.u[g][2 * p + 1] = fma(cf[p][0], sd, -(cf[p][1] * cd));
-          o.v[g][2 * p + 1] = sd;
-        }
-      } else {  // two real terms — cholesky.h:129-133
-        o.phi[g][2 * p] = FAST ? cel_exp_clamped(-cf[p][1] * dx) : cel_exp(-cf[p][1] * dx);
-        o.u[g][2 * p] = cf[p][0];
-        o.v[g][2 * p] = 1.0;
-        if (2 * p + 1 < J) {
-          o.phi[g][2 * p + 1] = FAST ? cel_exp_clamped(-cf[p][3] * dx) : cel_exp(-cf[p][3] * dx);
-          o.u[g][2 * p + 1] = cf[p][2];
-          o.v[g][2 * p + 1] = 1.0;
-        }
-      }
-    }
-  }
-}
-
-// The serial part: G steps of cholesky.h:154-178 fused with the forward substitution of
-// dot_solve (cholesky.h:350-356).  ALLC: every row belongs to a complex pair, whose two rows
-// share phi, so the products phi_q*phi_j are formed once per pair of pairs.
-template <int J, int G, bool ALLC, bool GUARD>
-__device__ __forceinline__ void lock_rec(LockState<J>& st, const LockGen<J, G>& gn, const double asum,
-                                         const double jitter, const double (&dd)[G], const double (&yy)[G],
-                                         const int n0, const int nvalid) {
-#pragma unroll
-  for (int g = 0; g < G; ++g) {
-    if (!GUARD || g < nvalid) {
-      // S <- phi phi^T o (S + D W W^T)   — cholesky.h:154-160
-      if constexpr (ALLC) {
-        constexpr int NP = J / 2;
-        double pp[NP][NP];
-#pragma unroll
-        for (int a = 0; a < NP; ++a)
-#pragma unroll
-          for (int c = a; c < NP; ++c) pp[a][c] = gn.phi[g][2 * a] * gn.phi[g][2 * c];
-#pragma unroll
-        for (int j = 0; j < J; ++j)
-#pragma unroll
-          for (int q = 0; q <= j; ++q)
-            st.S[tri<J>(q, j)] = pp[q / 2][j / 2] * fma(st.DW[j], st.Wp[q], st.S[tri<J>(q, j)]);
-      } else {
-#pragma unroll
-        for (int j = 0; j < J; ++j)
-#pragma unroll
-          for (int q = 0; q <= j; ++q)
-            st.S[tri<J>(q, j)] =
-                gn.phi[g][j] * (gn.phi[g][q] * fma(st.DW[j], st.Wp[q], st.S[tri<J>(q, j)]));
-      }
-      // forward substitution with the previous column of W — cholesky.h:350-354
-      double x = yy[g];
-#pragma unroll
-      for (int j = 0; j < J; ++j) {
-        st.f[j] = gn.phi[g][j] * fma(st.Wp[j], st.xprev, st.f[j]);
-        x = fma(-gn.u[g][j], st.f[j], x);
-      }
-      // su = S u (symmetric matvec); D_n = A_n - u.su ; W_n = (v - su)/D_n — cholesky.h:98, 162-178
-      double Dn = (dd[g] + asum) + jitter;
-      double wn[J];
-#pragma unroll
-      for (int j = 0; j < J; ++j) {
-        double su = 0.0;
-#pragma unroll
-        for (int q = 0; q < J; ++q) {
-          const double s = (q <= j) ? st.S[tri<J>(q, j)] : st.S[tri<J>(j, q)];
-          su = (q == 0) ? s * gn.u[g][0] : fma(s, gn.u[g][q], su);
-        }
-        Dn = fma(-gn.u[g][j], su, Dn);
-        wn[j] = gn.v[g][j] - su;
-      }
-      st.fail = (Dn < 0.0 && st.fail == 0) ? n0 + g + 1 : st.fail;  // cholesky.h:176
-      const double r = fast_rcp_nocheck(Dn);
-#pragma unroll
-      for (int j = 0; j < J; ++j) { st.DW[j] = wn[j]; st.Wp[j] = wn[j] * r; }
-      st.quad = fma(x * x, r, st.quad);  // cholesky.h:356
-      st.xprev = x;
-      st.ld.add(Dn);                     // cholesky.h:208
-    }
-  }
-}
 
 // register budget per J: 144 keeps 14 warps (7 CTAs) per SM resident for J <= 2, which is what
 // lets cfg2's 2048 warps run as ONE wave on 148 SMs
@@ -367,42 +232,6 @@ k_loglik_lockstep(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const _
     if (a.status) a.status[b] = st.fail ? 3 : 0;
     if (a.fail_index) a.fail_index[b] = st.fail;
   }
-}
-
-// ---- host side: describe [B][N] to the TMA unit ------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static bool tried = false;
-  if (!tried) {
-    tried = true;
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(p);
-    else
-      cudaGetLastError();
-  }
-  return fn;
-}
-
-bool make_series_map(CUtensorMap* map, const double* base, long long B, int N, long long stride, int T) {
-  EncodeTiledFn fn = encode_fn();
-  if (!fn) return false;
-  if (stride <= 0 || (stride & 1) || (reinterpret_cast<uintptr_t>(base) & 15u)) return false;
-  if (B > 0x7fffffffLL) return false;
-  cuuint64_t dims[2] = {(cuuint64_t)N, (cuuint64_t)B};
-  cuuint64_t strides[1] = {(cuuint64_t)stride * sizeof(double)};
-  cuuint32_t box[2] = {(cuuint32_t)T, (cuuint32_t)kWarp};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double*>(base), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  return r == CUDA_SUCCESS;
 }
 
 template <int J, int G, int T, int STAGES, int CAP = lock_maxreg(J), bool PIPE = false>

@@ -157,3 +157,31 @@ def test_repeatable_at_full_size(bs):
         ll, ld, q, st = bs.log_likelihood(C, T, D, Y, 0, 1, return_parts=True)
         torch.cuda.synchronize()
         assert torch.equal(ld, ld0) and torch.equal(q, q0) and torch.equal(st, st0)
+
+
+@pytest.mark.parametrize("B,N,Jr,Jc", [(100, 500, 0, 1), (70, 403, 0, 2), (40, 300, 0, 3), (33, 200, 1, 1),
+                                       (5, 333, 0, 1), (3, 150, 0, 8)])
+def test_batched_compute_materialises_reference_factor(bs, B, N, Jr, Jc):
+    """cel_batched_compute: phi,u,W,D of every series vs the oracle's factor (the TMA-store
+    lockstep kernel for all-complex even J <= 6 with aligned rows, the cooperative kernel else)."""
+    import torch
+    from celerite_b200 import synth
+    from tests.util import RTOL_SOLVE
+    b = synth.make_batch(B, N, Jr, Jc, seed=3 * B + N)
+    dev = torch.device("cuda:0")
+    tt = lambda a: torch.from_numpy(a).to(dev)  # noqa: E731
+    phi, u, W, D, logdet, status = bs.compute(tt(b["coeffs"]), tt(b["t"]), tt(b["diag"]), Jr, Jc)
+    torch.cuda.synchronize()
+    assert int(status.sum()) == 0
+    chk = oracle.best()
+    for i in list(range(0, B, max(1, B // 7))) + [B - 1]:
+        j, ar, cr, ac, bc, cc, dc = synth.split_row(b["coeffs"][i], Jr, Jc)
+        p = oracle.Problem(j, ar, cr, ac, bc, cc, dc, b["t"][i], b["diag"][i])
+        f = chk.factor(p)
+        assert rel_inf(phi[i].cpu().numpy(), f.phi) < RTOL_SOLVE
+        assert rel_inf(u[i].cpu().numpy(), f.u) < RTOL_SOLVE
+        assert rel_inf(W[i].cpu().numpy(), f.W) < RTOL_SOLVE
+        assert rel_inf(D[i].cpu().numpy(), f.D) < RTOL_SOLVE
+        assert rel_sum(float(logdet[i]), f.log_det, N) < RTOL_SCALAR
+        if hasattr(chk, "release"):
+            chk.release(f)
