@@ -185,3 +185,61 @@ def test_batched_compute_materialises_reference_factor(bs, B, N, Jr, Jc):
         assert rel_sum(float(logdet[i]), f.log_det, N) < RTOL_SCALAR
         if hasattr(chk, "release"):
             chk.release(f)
+
+
+def test_jitter_only_batch(bs):
+    """J = 0 (cholesky.h:90-95, 334-339): K = diag(sigma^2 + jitter)."""
+    rng = np.random.default_rng(0)
+    B, N = 37, 100
+    diag = rng.uniform(0.1, 0.5, (B, N)) ** 2
+    y = rng.standard_normal((B, N))
+    t = np.sort(rng.uniform(0, 10, (B, N)), axis=1)
+    coeffs = rng.uniform(0.01, 0.1, (B, 1))
+    ll, logdet, quad, status = bs.log_likelihood(coeffs, t, diag, y, 0, 0, return_parts=True)
+    D = diag + coeffs
+    assert np.all(status == 0)
+    assert rel_inf(logdet, np.log(D).sum(1)) < RTOL_SCALAR
+    assert rel_inf(quad, (y * y / D).sum(1)) < RTOL_SCALAR
+
+
+def test_padded_rows_device_and_host(bs):
+    """stride > N (rows padded to a fixed pitch), on both the device and the host-pointer path."""
+    import ctypes as C
+    import torch
+    from celerite_b200 import _capi, synth
+    B, N, pitch, Jr, Jc = 70, 333, 400, 0, 1
+    b = synth.make_batch(B, N, Jr, Jc, seed=21)
+    pad = lambda a: np.ascontiguousarray(np.pad(a, ((0, 0), (0, pitch - N)), constant_values=np.nan))  # noqa: E731
+    T, D, Y = pad(b["t"]), pad(b["diag"]), pad(b["y"])
+    ref = oracle.best().batched_loglik(B, N, N, Jr, Jc, b["coeffs"], 5, b["t"], b["diag"], b["y"])
+    lib = bs._lib
+    p = lambda a: C.c_void_p(a.ctypes.data)  # noqa: E731
+    ld = np.empty(B); q = np.empty(B); ll = np.empty(B); st = np.empty(B, dtype=np.int32)
+    rc = lib.cel_batched_log_likelihood(bs._h, B, N, pitch, Jr, Jc, p(b["coeffs"]), 5, p(T), p(D), p(Y),
+                                        p(ld), p(q), p(ll), p(st), _capi.HOST_POINTERS)
+    assert rc == 0 and np.all(st == 0)
+    assert rel_sum(ld, ref[:, 0], N) < RTOL_SCALAR and rel_sum(q, ref[:, 1], N) < RTOL_SCALAR
+    dev = torch.device("cuda:0")
+    dT, dD, dY, dC = (torch.from_numpy(a).to(dev) for a in (T, D, Y, b["coeffs"]))
+    out = torch.empty((3, B), dtype=torch.float64, device=dev)
+    dst = torch.empty(B, dtype=torch.int32, device=dev)
+    lib.cel_set_stream(bs._h, C.c_void_p(torch.cuda.current_stream(dev).cuda_stream or 1))
+    v = lambda a: C.c_void_p(a.data_ptr())  # noqa: E731
+    rc = lib.cel_batched_log_likelihood(bs._h, B, N, pitch, Jr, Jc, v(dC), 5, v(dT), v(dD), v(dY),
+                                        v(out[0]), v(out[1]), v(out[2]), v(dst), 0)
+    torch.cuda.synchronize()
+    assert rc == 0 and int(dst.sum()) == 0
+    assert rel_sum(out[0].cpu().numpy(), ref[:, 0], N) < RTOL_SCALAR
+    assert rel_sum(out[1].cpu().numpy(), ref[:, 1], N) < RTOL_SCALAR
+
+
+def test_argument_errors(bs):
+    import ctypes as C
+    from celerite_b200 import _capi
+    lib = bs._lib
+    a = np.zeros(16)
+    p = C.c_void_p(a.ctypes.data)
+    assert lib.cel_batched_log_likelihood(bs._h, 1, 0, 0, 0, 1, p, 5, p, p, p, p, p, p, p, 1) == _capi.INVALID_ARGUMENT
+    assert lib.cel_batched_log_likelihood(bs._h, 2, 8, 4, 0, 1, p, 5, p, p, p, p, p, p, p, 1) == _capi.DIMENSION_MISMATCH
+    assert lib.cel_batched_log_likelihood(bs._h, 2, 8, 8, 0, 17, p, 69, p, p, p, p, p, p, p, 1) == _capi.UNSUPPORTED
+    assert lib.cel_batched_log_likelihood(bs._h, 0, 8, 8, 0, 1, p, 5, p, p, p, p, p, p, p, 1) == _capi.OK
