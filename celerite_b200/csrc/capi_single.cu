@@ -386,12 +386,27 @@ int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t str
 
   cel::GradArgs a{};
   a.N = N; a.Jr = Jr; a.Jc = Jc; a.Jg = 0; a.seg = seg;
+  // small all-complex kernels: thread-per-series sweep (falls back when TMA cannot describe the batch)
+  const bool lock = cel::grad_lockstep_applies(Jr, Jc, 0, stride);
+  auto scratch_need = [&](int64_t nb) {
+    size_t n = cel::grad_scratch_doubles(nb, N, J, seg);
+    if (lock) { const size_t m = cel::grad_lockstep_scratch_doubles(nb, N, Jc, seg); if (m > n) n = m; }
+    return dbytes(n);
+  };
+  auto launch = [&](cel::GradArgs& ga) -> cudaError_t {
+    bool used = false;
+    if (lock) {
+      cudaError_t e = cel::launch_grad_lockstep(ga, st, &used);
+      if (e != cudaSuccess) return e;
+    }
+    return used ? cudaSuccess : cel::launch_grad_coop(ga, st);
+  };
   if (!(flags & CEL_HOST_POINTERS)) {
-    CEL_CUDA_TRY(s, s->scratch0.reserve(dbytes(cel::grad_scratch_doubles(B, N, J, seg))));
+    CEL_CUDA_TRY(s, s->scratch0.reserve(scratch_need(B)));
     a.B = B; a.stride = stride; a.coeffs = coeffs; a.coeff_stride = coeff_stride;
     a.t = t; a.diag = diag; a.y = y;
     a.out_val = out_val; a.out_grad = out_grad; a.status = status; a.scratch = s->scratch0.d();
-    CEL_CUDA_TRY(s, cel::launch_grad_coop(a, st));
+    CEL_CUDA_TRY(s, launch(a));
     s->launches += 1;
     return CEL_OK;
   }
@@ -402,7 +417,7 @@ int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t str
   if (chunk > B) chunk = B;
   if (stride == 0) chunk = B;
   const size_t ndata = (stride == 0 ? 1 : (size_t)chunk) * N;
-  CEL_CUDA_TRY(s, s->scratch0.reserve(dbytes(cel::grad_scratch_doubles(chunk, N, J, seg))));
+  CEL_CUDA_TRY(s, s->scratch0.reserve(scratch_need(chunk)));
   CEL_CUDA_TRY(s, s->stage_t[0].reserve(dbytes(ndata)));
   CEL_CUDA_TRY(s, s->stage_d[0].reserve(dbytes(ndata)));
   CEL_CUDA_TRY(s, s->stage_y[0].reserve(dbytes(ndata)));
@@ -431,7 +446,7 @@ int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t str
     a.t = s->stage_t[0].d(); a.diag = s->stage_d[0].d(); a.y = s->stage_y[0].d();
     a.out_val = s->stage_o[0].d(); a.out_grad = s->stage_o[0].d() + chunk;
     a.status = s->stage_s[0].i(); a.scratch = s->scratch0.d();
-    CEL_CUDA_TRY(s, cel::launch_grad_coop(a, st));
+    CEL_CUDA_TRY(s, launch(a));
     s->launches += 1;
     CEL_CUDA_TRY(s, cudaMemcpyAsync(out_val + b0, a.out_val, dbytes(nb), cudaMemcpyDeviceToHost, st));
     CEL_CUDA_TRY(s, cudaMemcpyAsync(out_grad + b0 * P, a.out_grad, dbytes((size_t)nb * P), cudaMemcpyDeviceToHost, st));

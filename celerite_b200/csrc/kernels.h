@@ -73,6 +73,11 @@ int grad_default_segment(int N);
 size_t grad_scratch_doubles(long long B, int N, int J, int seg);
 cudaError_t launch_grad_coop(const GradArgs& a, cudaStream_t stream);
 
+// Thread-per-series variant of the same sweep (lockstep_grad.cu) for all-complex J = 2, 4.
+bool grad_lockstep_applies(int Jr, int Jc, int Jg, long long stride);
+size_t grad_lockstep_scratch_doubles(long long B, int N, int Jc, int seg);
+cudaError_t launch_grad_lockstep(const GradArgs& a, cudaStream_t stream, bool* used);
+
 // One stored factor (reference layout) applied to nrhs right-hand sides, DEVICE pointers.
 struct SweepArgs {
   int N, J, nrhs;
