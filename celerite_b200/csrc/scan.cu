@@ -178,7 +178,32 @@ struct MidArgs {
 
 constexpr int kMidMaxJ = 32;
 
-// running map of one warp, in shared memory: Mr[i][k] (column i), cr[r][k]
+// The three middle kernels walk a sequence of records; the record of step q+1 is copied into
+// shared memory with cp.async while step q is being applied (the walk is a chain of dependent
+// small matrix products, so a global-load latency per step would dominate it).
+struct RecStream {
+  const double* src;    // records, `len` doubles each
+  double* buf;          // [2][len] in shared memory
+  int len, first, count, nwalk, reverse;
+  __device__ __forceinline__ int unit(int q) const { return reverse ? nwalk - 1 - q : q; }
+  __device__ __forceinline__ void fetch(int q, int lane) const {
+    if (q < first + count) {
+      const double* s = src + (size_t)unit(q) * len;
+      double* d = buf + ((q - first) & 1) * len;
+      for (int e = lane; e < len; e += kWarp) cp_async_8(d + e, s + e);
+    }
+    cp_async_commit_group();
+  }
+  // record of step q (after the previous fetch(q) has landed); starts the fetch of q+1
+  __device__ __forceinline__ const double* get(int q, int lane) const {
+    fetch(q + 1, lane);
+    cp_async_wait_group<1>();
+    __syncwarp();
+    return buf + ((q - first) & 1) * len;
+  }
+};
+
+// compose the running map (Mr[i][k] column i, cr[r][k]; shared memory) with one unit's map
 __device__ __forceinline__ void mid_compose(const MidArgs& m, const double* unit_rec, double* Mr, double* cr,
                                             double* Mn, int k, bool row_ok) {
   const int J = m.J, nrhs = m.nrhs;
@@ -234,25 +259,29 @@ __global__ void __launch_bounds__(kWarp) k_mid_compose(MidArgs m, int level_tota
   // level_total == 0: block b composes the chunks of super-chunk b into srec[b]
   // level_total == 1: one block composes all super-chunk maps (srec) into total
   extern __shared__ double sm[];
-  const int J = m.J, ncols = m.nrhs + m.nbasis, k = threadIdx.x;
+  const int J = m.J, ncols = m.nrhs + m.nbasis, k = threadIdx.x, len = ncols * J;
   const bool row_ok = k < J;
   double* Mr = sm;                          // J*J (or J when diag)
   double* cr = Mr + J * J;                  // nrhs*J
   double* Mn = cr + m.nrhs * J;             // (J+nrhs)*J scratch
+  double* rb = Mn + (J + m.nrhs) * J;       // [2][len] record ring
   for (int i = k; i < J * J; i += kWarp) Mr[i] = m.diag ? 1.0 : ((i / J) == (i % J) ? 1.0 : 0.0);
   for (int i = k; i < m.nrhs * J; i += kWarp) cr[i] = 0.0;
-  __syncwarp();
-  int first, count;
-  const double* src;
-  if (level_total == 0) { first = blockIdx.x * m.per_super; count = min(m.per_super, m.nunits - first); src = m.rec; }
-  else { first = 0; count = m.nsuper; src = m.srec; }
-  const int nwalk = (level_total == 0) ? m.nunits : m.nsuper;
-  for (int q = first; q < first + count; ++q) {
-    // chunk records are indexed by position in time, super-chunk records by position in the walk
-    const int unit = (level_total == 0 && m.reverse) ? nwalk - 1 - q : q;
-    mid_compose(m, src + (size_t)unit * ncols * J, Mr, cr, Mn, k, row_ok);
+  RecStream rs;
+  rs.buf = rb; rs.len = len;
+  if (level_total == 0) {
+    rs.first = blockIdx.x * m.per_super; rs.count = min(m.per_super, m.nunits - rs.first);
+    rs.src = m.rec; rs.nwalk = m.nunits; rs.reverse = m.reverse;
+  } else {  // super-chunk records are indexed by position in the walk already
+    rs.first = 0; rs.count = m.nsuper; rs.src = m.srec; rs.nwalk = m.nsuper; rs.reverse = 0;
   }
-  double* dst = (level_total == 0) ? m.srec + (size_t)blockIdx.x * ncols * J : m.total;
+  rs.fetch(rs.first, k);
+  __syncwarp();
+  for (int q = rs.first; q < rs.first + rs.count; ++q) {
+    const double* rec = rs.get(q, k);
+    mid_compose(m, rec, Mr, cr, Mn, k, row_ok);
+  }
+  double* dst = (level_total == 0) ? m.srec + (size_t)blockIdx.x * len : m.total;
   if (row_ok) {
     for (int r = 0; r < m.nrhs; ++r) dst[r * J + k] = cr[r * J + k];
     if (m.diag) dst[m.nrhs * J + k] = Mr[k];
@@ -263,32 +292,42 @@ __global__ void __launch_bounds__(kWarp) k_mid_compose(MidArgs m, int level_tota
 __global__ void __launch_bounds__(kWarp) k_mid_scan(MidArgs m) {
   // serial over the super-chunk maps: carry entering each super-chunk (walk order)
   extern __shared__ double sm[];
-  const int J = m.J, ncols = m.nrhs + m.nbasis, k = threadIdx.x;
+  const int J = m.J, ncols = m.nrhs + m.nbasis, k = threadIdx.x, len = ncols * J;
   const bool row_ok = k < J;
   double* gs = sm;
   double* gn = gs + m.nrhs * J;
+  double* rb = gn + m.nrhs * J;
   for (int i = k; i < m.nrhs * J; i += kWarp) gs[i] = m.g0 ? m.g0[i] : 0.0;
+  RecStream rs;
+  rs.buf = rb; rs.len = len; rs.first = 0; rs.count = m.nsuper; rs.src = m.srec; rs.nwalk = m.nsuper; rs.reverse = 0;
+  rs.fetch(0, k);
   __syncwarp();
   for (int q = 0; q < m.nsuper; ++q) {
+    const double* rec = rs.get(q, k);
     if (row_ok) for (int r = 0; r < m.nrhs; ++r) m.sg[((size_t)q * m.nrhs + r) * J + k] = gs[r * J + k];
-    mid_apply(m, m.srec + (size_t)q * ncols * J, gs, gn, k, row_ok);
+    mid_apply(m, rec, gs, gn, k, row_ok);
   }
 }
 
 __global__ void __launch_bounds__(kWarp) k_mid_distribute(MidArgs m) {
   // block b walks super-chunk b (walk order) and hands every chunk its incoming carry
   extern __shared__ double sm[];
-  const int J = m.J, ncols = m.nrhs + m.nbasis, k = threadIdx.x;
+  const int J = m.J, ncols = m.nrhs + m.nbasis, k = threadIdx.x, len = ncols * J;
   const bool row_ok = k < J;
   double* gs = sm;
   double* gn = gs + m.nrhs * J;
+  double* rb = gn + m.nrhs * J;
   for (int i = k; i < m.nrhs * J; i += kWarp) gs[i] = m.sg[(size_t)blockIdx.x * m.nrhs * J + i];
+  RecStream rs;
+  rs.buf = rb; rs.len = len; rs.first = blockIdx.x * m.per_super; rs.count = min(m.per_super, m.nunits - rs.first);
+  rs.src = m.rec; rs.nwalk = m.nunits; rs.reverse = m.reverse;
+  rs.fetch(rs.first, k);
   __syncwarp();
-  const int first = blockIdx.x * m.per_super, count = min(m.per_super, m.nunits - first);
-  for (int q = first; q < first + count; ++q) {
-    const int unit = m.reverse ? m.nunits - 1 - q : q;
+  for (int q = rs.first; q < rs.first + rs.count; ++q) {
+    const double* rec = rs.get(q, k);
+    const int unit = rs.unit(q);
     if (row_ok) for (int r = 0; r < m.nrhs; ++r) m.gin[((size_t)unit * m.nrhs + r) * J + k] = gs[r * J + k];
-    mid_apply(m, m.rec + (size_t)unit * ncols * J, gs, gn, k, row_ok);
+    mid_apply(m, rec, gs, gn, k, row_ok);
   }
 }
 
@@ -361,13 +400,14 @@ cudaError_t launch_middle(int J, int nrhs, int nbasis, int diag, int reverse, in
   m.per_super = ps;
   m.nsuper = (nunits + ps - 1) / ps;
   m.rec = rec; m.srec = srec; m.g0 = g0; m.sg = sg; m.gin = gin; m.total = total;
-  const size_t smem = (size_t)(J * J + nrhs * J + (J + nrhs) * J) * sizeof(double);
+  const size_t ring = (size_t)2 * (nrhs + nbasis) * J;
+  const size_t smem = (size_t)(J * J + nrhs * J + (J + nrhs) * J + ring) * sizeof(double);
   if (!skip_compose) {
     k_mid_compose<<<m.nsuper, kWarp, smem, stream>>>(m, 0);
     if (total) k_mid_compose<<<1, kWarp, smem, stream>>>(m, 1);
   }
   if (!compose_only) {
-    const size_t smem2 = (size_t)(2 * nrhs * J) * sizeof(double);
+    const size_t smem2 = (size_t)(2 * nrhs * J + ring) * sizeof(double);
     k_mid_scan<<<1, kWarp, smem2, stream>>>(m);
     k_mid_distribute<<<m.nsuper, kWarp, smem2, stream>>>(m);
   }
