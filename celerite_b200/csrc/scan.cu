@@ -178,32 +178,38 @@ struct MidArgs {
 
 constexpr int kMidMaxJ = 32;
 
-// The three middle kernels walk a sequence of records; the record of step q+1 is copied into
-// shared memory with cp.async while step q is being applied (the walk is a chain of dependent
-// small matrix products, so a global-load latency per step would dominate it).
+// The three middle kernels walk a sequence of records; records are copied into a 4-deep shared
+// memory ring with cp.async three steps ahead of their use (the walk is a chain of dependent
+// small matrix products, so a global-load latency per step would dominate it), and all loops over
+// J are unrolled at compile time (JT = J rounded up; rows/columns >= J are predicated off).
+constexpr int kRing = 4;
 struct RecStream {
   const double* src;    // records, `len` doubles each
-  double* buf;          // [2][len] in shared memory
+  double* buf;          // [kRing][len] in shared memory
   int len, first, count, nwalk, reverse;
   __device__ __forceinline__ int unit(int q) const { return reverse ? nwalk - 1 - q : q; }
   __device__ __forceinline__ void fetch(int q, int lane) const {
     if (q < first + count) {
       const double* s = src + (size_t)unit(q) * len;
-      double* d = buf + ((q - first) & 1) * len;
+      double* d = buf + ((q - first) % kRing) * len;
       for (int e = lane; e < len; e += kWarp) cp_async_8(d + e, s + e);
     }
     cp_async_commit_group();
   }
-  // record of step q (after the previous fetch(q) has landed); starts the fetch of q+1
+  __device__ __forceinline__ void prime(int lane) const {
+    for (int i = 0; i < kRing - 1; ++i) fetch(first + i, lane);
+  }
+  // record of step q; also starts the fetch of step q + kRing - 1
   __device__ __forceinline__ const double* get(int q, int lane) const {
-    fetch(q + 1, lane);
-    cp_async_wait_group<1>();
+    fetch(q + kRing - 1, lane);
+    cp_async_wait_group<kRing - 1>();
     __syncwarp();
-    return buf + ((q - first) & 1) * len;
+    return buf + ((q - first) % kRing) * len;
   }
 };
 
 // compose the running map (Mr[i][k] column i, cr[r][k]; shared memory) with one unit's map
+template <int JT>
 __device__ __forceinline__ void mid_compose(const MidArgs& m, const double* unit_rec, double* Mr, double* cr,
                                             double* Mn, int k, bool row_ok) {
   const int J = m.J, nrhs = m.nrhs;
@@ -217,15 +223,20 @@ __device__ __forceinline__ void mid_compose(const MidArgs& m, const double* unit
     __syncwarp();
     return;
   }
+  double row[JT];                         // row k of the unit's M
+#pragma unroll
+  for (int j = 0; j < JT; ++j) row[j] = (row_ok && j < J) ? Mc[j * J + k] : 0.0;
   if (row_ok) {
-    for (int i = 0; i < J; ++i) {           // new column i = Mc * (old column i)
+    for (int i = 0; i < J; ++i) {         // new column i = Mc * (old column i)
       double acc = 0.0;
-      for (int j = 0; j < J; ++j) acc = fma(Mc[j * J + k], Mr[i * J + j], acc);
+#pragma unroll
+      for (int j = 0; j < JT; ++j) acc = fma(row[j], (j < J) ? Mr[i * J + j] : 0.0, acc);
       Mn[i * J + k] = acc;
     }
     for (int r = 0; r < nrhs; ++r) {
       double acc = unit_rec[r * J + k];
-      for (int j = 0; j < J; ++j) acc = fma(Mc[j * J + k], cr[r * J + j], acc);
+#pragma unroll
+      for (int j = 0; j < JT; ++j) acc = fma(row[j], (j < J) ? cr[r * J + j] : 0.0, acc);
       Mn[(J + r) * J + k] = acc;
     }
   }
@@ -238,15 +249,25 @@ __device__ __forceinline__ void mid_compose(const MidArgs& m, const double* unit
 }
 
 // apply one unit's map to carries g[r][k] held in shared memory
+template <int JT>
 __device__ __forceinline__ void mid_apply(const MidArgs& m, const double* unit_rec, double* gs, double* gn, int k,
                                           bool row_ok) {
   const int J = m.J, nrhs = m.nrhs;
   const double* Mc = unit_rec + (size_t)nrhs * J;
+  if (m.diag) {
+    if (row_ok)
+      for (int r = 0; r < nrhs; ++r) gs[r * J + k] = fma(Mc[k], gs[r * J + k], unit_rec[r * J + k]);
+    __syncwarp();
+    return;
+  }
+  double row[JT];
+#pragma unroll
+  for (int j = 0; j < JT; ++j) row[j] = (row_ok && j < J) ? Mc[j * J + k] : 0.0;
   if (row_ok) {
     for (int r = 0; r < nrhs; ++r) {
       double acc = unit_rec[r * J + k];
-      if (m.diag) acc = fma(Mc[k], gs[r * J + k], acc);
-      else for (int j = 0; j < J; ++j) acc = fma(Mc[j * J + k], gs[r * J + j], acc);
+#pragma unroll
+      for (int j = 0; j < JT; ++j) acc = fma(row[j], (j < J) ? gs[r * J + j] : 0.0, acc);
       gn[r * J + k] = acc;
     }
   }
@@ -255,6 +276,7 @@ __device__ __forceinline__ void mid_apply(const MidArgs& m, const double* unit_r
   __syncwarp();
 }
 
+template <int JT>
 __global__ void __launch_bounds__(kWarp) k_mid_compose(MidArgs m, int level_total) {
   // level_total == 0: block b composes the chunks of super-chunk b into srec[b]
   // level_total == 1: one block composes all super-chunk maps (srec) into total
@@ -264,7 +286,7 @@ __global__ void __launch_bounds__(kWarp) k_mid_compose(MidArgs m, int level_tota
   double* Mr = sm;                          // J*J (or J when diag)
   double* cr = Mr + J * J;                  // nrhs*J
   double* Mn = cr + m.nrhs * J;             // (J+nrhs)*J scratch
-  double* rb = Mn + (J + m.nrhs) * J;       // [2][len] record ring
+  double* rb = Mn + (J + m.nrhs) * J;       // [kRing][len] record ring
   for (int i = k; i < J * J; i += kWarp) Mr[i] = m.diag ? 1.0 : ((i / J) == (i % J) ? 1.0 : 0.0);
   for (int i = k; i < m.nrhs * J; i += kWarp) cr[i] = 0.0;
   RecStream rs;
@@ -275,11 +297,11 @@ __global__ void __launch_bounds__(kWarp) k_mid_compose(MidArgs m, int level_tota
   } else {  // super-chunk records are indexed by position in the walk already
     rs.first = 0; rs.count = m.nsuper; rs.src = m.srec; rs.nwalk = m.nsuper; rs.reverse = 0;
   }
-  rs.fetch(rs.first, k);
+  rs.prime(k);
   __syncwarp();
   for (int q = rs.first; q < rs.first + rs.count; ++q) {
     const double* rec = rs.get(q, k);
-    mid_compose(m, rec, Mr, cr, Mn, k, row_ok);
+    mid_compose<JT>(m, rec, Mr, cr, Mn, k, row_ok);
   }
   double* dst = (level_total == 0) ? m.srec + (size_t)blockIdx.x * len : m.total;
   if (row_ok) {
@@ -289,6 +311,7 @@ __global__ void __launch_bounds__(kWarp) k_mid_compose(MidArgs m, int level_tota
   }
 }
 
+template <int JT>
 __global__ void __launch_bounds__(kWarp) k_mid_scan(MidArgs m) {
   // serial over the super-chunk maps: carry entering each super-chunk (walk order)
   extern __shared__ double sm[];
@@ -300,15 +323,16 @@ __global__ void __launch_bounds__(kWarp) k_mid_scan(MidArgs m) {
   for (int i = k; i < m.nrhs * J; i += kWarp) gs[i] = m.g0 ? m.g0[i] : 0.0;
   RecStream rs;
   rs.buf = rb; rs.len = len; rs.first = 0; rs.count = m.nsuper; rs.src = m.srec; rs.nwalk = m.nsuper; rs.reverse = 0;
-  rs.fetch(0, k);
+  rs.prime(k);
   __syncwarp();
   for (int q = 0; q < m.nsuper; ++q) {
     const double* rec = rs.get(q, k);
     if (row_ok) for (int r = 0; r < m.nrhs; ++r) m.sg[((size_t)q * m.nrhs + r) * J + k] = gs[r * J + k];
-    mid_apply(m, rec, gs, gn, k, row_ok);
+    mid_apply<JT>(m, rec, gs, gn, k, row_ok);
   }
 }
 
+template <int JT>
 __global__ void __launch_bounds__(kWarp) k_mid_distribute(MidArgs m) {
   // block b walks super-chunk b (walk order) and hands every chunk its incoming carry
   extern __shared__ double sm[];
@@ -321,13 +345,31 @@ __global__ void __launch_bounds__(kWarp) k_mid_distribute(MidArgs m) {
   RecStream rs;
   rs.buf = rb; rs.len = len; rs.first = blockIdx.x * m.per_super; rs.count = min(m.per_super, m.nunits - rs.first);
   rs.src = m.rec; rs.nwalk = m.nunits; rs.reverse = m.reverse;
-  rs.fetch(rs.first, k);
+  rs.prime(k);
   __syncwarp();
   for (int q = rs.first; q < rs.first + rs.count; ++q) {
     const double* rec = rs.get(q, k);
     const int unit = rs.unit(q);
     if (row_ok) for (int r = 0; r < m.nrhs; ++r) m.gin[((size_t)unit * m.nrhs + r) * J + k] = gs[r * J + k];
-    mid_apply(m, rec, gs, gn, k, row_ok);
+    mid_apply<JT>(m, rec, gs, gn, k, row_ok);
+  }
+}
+
+template <int JT>
+void launch_mid(const MidArgs& m, size_t smem, size_t smem2, bool with_total, int compose_only, int skip_compose,
+                cudaStream_t stream) {
+  if (smem > 48 * 1024) {   // wide kernels with several right-hand sides: opt in to large shared memory
+    cudaFuncSetAttribute(k_mid_compose<JT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(k_mid_scan<JT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+    cudaFuncSetAttribute(k_mid_distribute<JT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+  }
+  if (!skip_compose) {
+    k_mid_compose<JT><<<m.nsuper, kWarp, smem, stream>>>(m, 0);
+    if (with_total) k_mid_compose<JT><<<1, kWarp, smem, stream>>>(m, 1);
+  }
+  if (!compose_only) {
+    k_mid_scan<JT><<<1, kWarp, smem2, stream>>>(m);
+    k_mid_distribute<JT><<<m.nsuper, kWarp, smem2, stream>>>(m);
   }
 }
 
@@ -400,17 +442,16 @@ cudaError_t launch_middle(int J, int nrhs, int nbasis, int diag, int reverse, in
   m.per_super = ps;
   m.nsuper = (nunits + ps - 1) / ps;
   m.rec = rec; m.srec = srec; m.g0 = g0; m.sg = sg; m.gin = gin; m.total = total;
-  const size_t ring = (size_t)2 * (nrhs + nbasis) * J;
+  const size_t ring = (size_t)kRing * (nrhs + nbasis) * J;
   const size_t smem = (size_t)(J * J + nrhs * J + (J + nrhs) * J + ring) * sizeof(double);
-  if (!skip_compose) {
-    k_mid_compose<<<m.nsuper, kWarp, smem, stream>>>(m, 0);
-    if (total) k_mid_compose<<<1, kWarp, smem, stream>>>(m, 1);
-  }
-  if (!compose_only) {
-    const size_t smem2 = (size_t)(2 * nrhs * J + ring) * sizeof(double);
-    k_mid_scan<<<1, kWarp, smem2, stream>>>(m);
-    k_mid_distribute<<<m.nsuper, kWarp, smem2, stream>>>(m);
-  }
+  const size_t smem2 = (size_t)(2 * nrhs * J + ring) * sizeof(double);
+  if (smem > 200 * 1024) return cudaErrorInvalidValue;   // too many right-hand sides for one middle pass
+  const bool wt = total != nullptr;
+  if (J <= 2) launch_mid<2>(m, smem, smem2, wt, compose_only, skip_compose, stream);
+  else if (J <= 4) launch_mid<4>(m, smem, smem2, wt, compose_only, skip_compose, stream);
+  else if (J <= 8) launch_mid<8>(m, smem, smem2, wt, compose_only, skip_compose, stream);
+  else if (J <= 16) launch_mid<16>(m, smem, smem2, wt, compose_only, skip_compose, stream);
+  else launch_mid<32>(m, smem, smem2, wt, compose_only, skip_compose, stream);
   return cudaGetLastError();
 }
 
