@@ -15,8 +15,20 @@
 // then only reads broadcast rows.  In the materialising variant those tiles ARE the output
 // (reference layout, J fastest) and are written back with coalesced stores.
 //
+// The recursion is written so that the ONLY cross-lane result on its critical path is one
+// scalar, b_n = (phi_n o u_n) . (D W)_{n-1}.  With a_n = S_{n-1} (phi_n o u_n) (old S, known one
+// step early) the step is
+//   D_n = A_n - (phi u).a_n - b_n^2 / D_{n-1}            x_n = y_n - (phi u).f_{n-1} - b_n x_{n-1}/D_{n-1}
+//   (D W)_n = v_n - phi_n o (a_n + (D W)_{n-1} b_n / D_{n-1})
+//   S_n = phi phi^T o (S_{n-1} + (D W)_{n-1} (D W)_{n-1}^T / D_{n-1})        <- needs nothing of step n
+// which is algebraically the reference's update (cholesky.h:154-178) but lets the S update, the
+// matvec and two of the three reductions run ahead of the scalar chain: per step the chain is one
+// shuffle butterfly plus ~4 dependent fp64 operations instead of matvec -> butterfly -> divide ->
+// exchange -> update in sequence.
+//
 // For J <= 16 a warp carries 32/L series side by side.
 #include "common.cuh"
+#include "fastmath.cuh"
 #include "kernels.h"
 
 namespace cel {
@@ -33,7 +45,7 @@ struct CoopCfg {
   static constexpr int T = 16;                      // steps per tile
   // per-group shared memory, in doubles
   static constexpr int kIn = 3 * T + 2;             // t (with one leading slot), diag(+A), y
-  static constexpr int kGen = 3 * T * JP;           // phi, u, v tiles
+  static constexpr int kGen = 4 * T * JP;           // phi, u, v and phi*u tiles
   static constexpr int kX = 2 * JP;                 // D*W exchange, double buffered
   static constexpr int kOut = STORE ? T * JP + T : 0;  // W tile, D tile (materialising variant)
   static constexpr int kCoef = 4 * JP + 2;          // coefficient row (<= 1 + 4*Jc + 2*Jr <= 1 + 2J)
@@ -58,7 +70,8 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
   double* phi_s = y_s + T;               // [T][JP]
   double* u_s = phi_s + T * JP;
   double* v_s = u_s + T * JP;
-  double* x_s = v_s + T * JP;            // [2][JP] exchange of D*W
+  double* ut_s = v_s + T * JP;           // [T][JP] phi o u
+  double* x_s = ut_s + T * JP;           // [2][JP] exchange of D*W
   double* w_s = x_s + 2 * JP;            // [T][JP] W tile
   double* dd_s = w_s + T * JP;           // [T]     D tile
   double* cf_s = x_s + 2 * JP + C::kOut;  // coefficient row (w_s/dd_s exist only when STORE)
@@ -75,7 +88,7 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
   {
     const double* row = a.coeffs + bb * a.coeff_stride;
     for (int i = k; i < P; i += L) cf_s[i] = row[i];
-    for (int i = k; i < 3 * T * JP; i += L) phi_s[i] = 0.0;
+    for (int i = k; i < 4 * T * JP; i += L) phi_s[i] = 0.0;
     for (int i = k; i < 2 * JP; i += L) x_s[i] = 0.0;
   }
   __syncwarp();
@@ -90,14 +103,20 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
   for (int j = 0; j < Jr; ++j) sum_ar += a_real[j];
   for (int j = 0; j < Jc; ++j) sum_ac += a_comp[j];
 
+  // the branch-free sincos needs |d t| < 1e9; t is sorted, so its two ends bound every argument
+  double dmax = 0.0;
+  for (int j = 0; j < Jc; ++j) dmax = fmax(dmax, fabs(d_comp[j]));
+  const bool fast_math =
+      __all_sync(kFull, dmax * fmax(fabs(__ldg(tp)), fabs(__ldg(tp + N - 1))) < kFastTrigLimit);
+
   const bool row_ok = k < JP;            // lanes JP..L-1 (JP not a power of two) carry zeros
   const int kk = row_ok ? k : JP - 1;
 
   double S[JP];
 #pragma unroll
   for (int j = 0; j < JP; ++j) S[j] = 0.0;
-  double dw_own = 0.0, r_prev = 0.0, f_own = 0.0, xprev = 0.0, quad = 0.0;
-  LogAcc ld;
+  double dw_own = 0.0, r_prev = 0.0, f_own = 0.0, s_prev = 0.0, quad = 0.0;   // s = x / D
+  LogAccFast ld;
   ld.init();
   int fail = 0;
 
@@ -133,35 +152,91 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
     if (tile + 1 < ntiles) prefetch(n0 + T);
 
     // ---- generator phase: phi, u, v for the whole tile (cholesky.h:127-152) ---------------
-    {
+    // Every (step, term) item is independent; with few series in flight the phase is latency
+    // bound, so four items per lane are evaluated together with the branch-free routines.
+    if (fast_math) {
+      const int nc = nt * Jc;
+      for (int item0 = k; item0 < nc; item0 += 4 * L) {
+        double sd[4], cd[4], e[4];
+        int ii[4], qq[4];
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+          const int item = min(item0 + m * L, nc - 1);
+          ii[m] = item / Jc; qq[m] = item - ii[m] * Jc;
+          const double tn = t_s[1 + ii[m]], dx = tn - t_s[ii[m]];
+          cel_sincos_core(d_comp[qq[m]] * tn, &sd[m], &cd[m]);
+          e[m] = cel_exp_clamped(-c_comp[qq[m]] * dx);
+        }
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+          if (item0 + m * L < nc) {
+            const int i = ii[m], q = qq[m], r0 = Jr + 2 * q;
+            const double aa = a_comp[q], bq = b_comp[q];
+            const double u0 = aa * cd[m] + bq * sd[m], u1 = aa * sd[m] - bq * cd[m];
+            phi_s[i * JP + r0] = e[m]; phi_s[i * JP + r0 + 1] = e[m];
+            u_s[i * JP + r0] = u0; u_s[i * JP + r0 + 1] = u1;
+            ut_s[i * JP + r0] = e[m] * u0; ut_s[i * JP + r0 + 1] = e[m] * u1;
+            v_s[i * JP + r0] = cd[m]; v_s[i * JP + r0 + 1] = sd[m];
+          }
+        }
+      }
+      const int nr = nt * Jr;
+      for (int item0 = k; item0 < nr; item0 += 4 * L) {
+        double e[4];
+        int ii[4], qq[4];
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+          const int item = min(item0 + m * L, nr - 1);
+          ii[m] = item / Jr; qq[m] = item - ii[m] * Jr;
+          e[m] = cel_exp_clamped(-c_real[qq[m]] * (t_s[1 + ii[m]] - t_s[ii[m]]));
+        }
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+          if (item0 + m * L < nr) {
+            const int i = ii[m], q = qq[m];
+            phi_s[i * JP + q] = e[m];
+            u_s[i * JP + q] = a_real[q];
+            ut_s[i * JP + q] = e[m] * a_real[q];
+            v_s[i * JP + q] = 1.0;
+          }
+        }
+      }
+    } else {
       const int nterm = Jr + Jc;
       for (int item = k; item < nt * nterm; item += L) {
         const int i = item / nterm, term = item - i * nterm;
         const double tn = t_s[1 + i], dx = tn - t_s[i];
         if (term < Jr) {
-          phi_s[i * JP + term] = exp(-c_real[term] * dx);
+          const double e = cel_exp(-c_real[term] * dx);
+          phi_s[i * JP + term] = e;
           u_s[i * JP + term] = a_real[term];
+          ut_s[i * JP + term] = e * a_real[term];
           v_s[i * JP + term] = 1.0;
         } else {
           const int q = term - Jr, r0 = Jr + 2 * q;
           double sd, cd;
-          sincos(d_comp[q] * tn, &sd, &cd);
-          const double e = exp(-c_comp[q] * dx);
+          cel_sincos(d_comp[q] * tn, &sd, &cd);
+          const double e = cel_exp(-c_comp[q] * dx);
           const double aa = a_comp[q], bq = b_comp[q];
+          const double u0 = aa * cd + bq * sd, u1 = aa * sd - bq * cd;
           phi_s[i * JP + r0] = e;
           phi_s[i * JP + r0 + 1] = e;
-          u_s[i * JP + r0] = aa * cd + bq * sd;
-          u_s[i * JP + r0 + 1] = aa * sd - bq * cd;
+          u_s[i * JP + r0] = u0;
+          u_s[i * JP + r0 + 1] = u1;
+          ut_s[i * JP + r0] = e * u0;
+          ut_s[i * JP + r0 + 1] = e * u1;
           v_s[i * JP + r0] = cd;
           v_s[i * JP + r0 + 1] = sd;
         }
       }
-      for (int item = k; item < nt * Jg; item += L) {
-        const int i = item / Jg, q = item - i * Jg, r0 = Jr + 2 * Jc + q;
-        phi_s[i * JP + r0] = 1.0;
-        u_s[i * JP + r0] = __ldg(Up + (size_t)(n0 + i) * Jg + q);
-        v_s[i * JP + r0] = __ldg(Vp + (size_t)(n0 + i) * Jg + q);
-      }
+    }
+    for (int item = k; item < nt * Jg; item += L) {
+      const int i = item / Jg, q = item - i * Jg, r0 = Jr + 2 * Jc + q;
+      const double ug = __ldg(Up + (size_t)(n0 + i) * Jg + q);
+      phi_s[i * JP + r0] = 1.0;
+      u_s[i * JP + r0] = ug;
+      ut_s[i * JP + r0] = ug;
+      v_s[i * JP + r0] = __ldg(Vp + (size_t)(n0 + i) * Jg + q);
     }
     __syncwarp();
 
@@ -169,43 +244,43 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
     for (int i = 0; i < nt; ++i) {
       const int par = (n0 + i) & 1;
       const double* ph = phi_s + i * JP;
-      const double* uu = u_s + i * JP;
-      const double* xw = x_s + par * JP;             // D_{n-1} W_{n-1}
+      const double* ut = ut_s + i * JP;
+      const double* xw = x_s + par * JP;             // (D W)_{n-1}, all rows
       const double phk = row_ok ? ph[kk] : 0.0;
-      const double uk = row_ok ? uu[kk] : 0.0;
+      const double utk = row_ok ? ut[kk] : 0.0;
       const double vk = row_ok ? v_s[i * JP + kk] : 0.0;
-      // S_k. <- phi_k phi_. o (S_k. + W_k (D W).)  and  acc = (S u)_k     — cholesky.h:154-175
+      const double dwr = dw_own * r_prev;            // W_{n-1}[k]
+      // a = (S_{n-1} (phi o u))_k with the old S, then S <- phi_k phi_. o (S + W_k (D W).)
       double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
 #pragma unroll
       for (int j = 0; j < JP; j += 2) {
         const double2 p2 = *reinterpret_cast<const double2*>(ph + j);
         const double2 x2 = *reinterpret_cast<const double2*>(xw + j);
-        const double2 u2 = *reinterpret_cast<const double2*>(uu + j);
-        const double q0 = dw_own * x2.x, q1 = dw_own * x2.y;
-        const double s0 = (phk * p2.x) * fma(r_prev, q0, S[j]);
-        const double s1 = (phk * p2.y) * fma(r_prev, q1, S[j + 1]);
-        S[j] = s0;
-        S[j + 1] = s1;
+        const double2 u2 = *reinterpret_cast<const double2*>(ut + j);
+        const double s0 = S[j], s1 = S[j + 1];
         if ((j & 2) == 0) { acc0 = fma(s0, u2.x, acc0); acc1 = fma(s1, u2.y, acc1); }
         else { acc2 = fma(s0, u2.x, acc2); acc3 = fma(s1, u2.y, acc3); }
+        S[j] = (phk * p2.x) * fma(dwr, x2.x, s0);
+        S[j + 1] = (phk * p2.y) * fma(dwr, x2.y, s1);
       }
-      const double su = (acc0 + acc1) + (acc2 + acc3);
-      // forward substitution — cholesky.h:350-354
-      f_own = phk * fma(dw_own * r_prev, xprev, f_own);
-      double red0 = uk * su, red1 = uk * f_own;
-      group_sum2<L>(red0, red1);
-      const double Dn = ((d_s[i] + sum_ar) + sum_ac) + jitter - red0;
-      const double x = y_s[i] - red1;
-      const double dw = vk - su;
+      const double av = (acc0 + acc1) + (acc2 + acc3);
+      double red_a = utk * av, red_f = utk * f_own, red_b = utk * dw_own;
+      group_sum2<L>(red_a, red_f);                   // known early: off the scalar chain
+      red_b = group_sum<L>(red_b);                   // the one reduction on the chain
+      const double tb = red_b * r_prev;
+      const double Dn = (((d_s[i] + sum_ar) + sum_ac) + jitter - red_a) - red_b * tb;
+      const double x = (y_s[i] - red_f) - red_b * s_prev;
+      const double dw = vk - phk * fma(dw_own, tb, av);
+      f_own = phk * fma(dw_own, s_prev, f_own);
       if (row_ok) x_s[(par ^ 1) * JP + kk] = dw;
-      if (Dn < 0.0 && fail == 0) fail = n0 + i + 1;  // cholesky.h:176
-      const double r = 1.0 / Dn;
+      fail = (Dn < 0.0 && fail == 0) ? n0 + i + 1 : fail;   // cholesky.h:176
+      const double r = fast_rcp_nocheck(Dn);
       if (STORE) {
         if (row_ok) w_s[i * JP + kk] = dw * r;
         if (k == 0) dd_s[i] = Dn;
       }
-      quad = fma(x * x, r, quad);
-      xprev = x;
+      s_prev = r * x;
+      quad = fma(x, s_prev, quad);
       dw_own = dw;
       r_prev = r;
       ld.add(Dn);

@@ -1,0 +1,24 @@
+"""Forward-only vs gradient time on config 3 shapes (development aid)."""
+import sys, os, time
+sys.path.insert(0, os.getcwd())
+import numpy as np, torch
+from celerite_b200 import synth
+from celerite_b200.batched import BatchedSolver
+B, N = 1024, int(sys.argv[1]) if len(sys.argv) > 1 else 100000
+dev = torch.device("cuda:0")
+bs = BatchedSolver(0)
+for jc in (1, 2, 4, 8, 16):
+    b = synth.make_batch(B, N, 0, jc, seed=jc)
+    tt = lambda a: torch.from_numpy(a).to(dev)
+    C, T, D, Y = tt(b["coeffs"]), tt(b["t"]), tt(b["diag"]), tt(b["y"])
+    def timeit(fn, reps=2):
+        fn(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps): fn()
+        e1.record(); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+    tf = timeit(lambda: bs.log_likelihood(C, T, D, Y, 0, jc))
+    tg = timeit(lambda: bs.grad_log_likelihood(C, T, D, Y, 0, jc))
+    print("J=%2d forward %.1f ms (%.2e pt-terms/s)  grad %.1f ms (%.2e)  ratio %.1f" %
+          (2 * jc, tf, B * N * 2 * jc / tf * 1e3, tg, B * N * 2 * jc / tg * 1e3, tg / tf))
