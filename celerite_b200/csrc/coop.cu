@@ -122,14 +122,15 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
 
   // register prefetch of the next input tile
   constexpr int PF = (T + L - 1) / L;
-  double pt[PF], pd[PF], py[PF];
-  auto prefetch = [&](int n0) {
+  double pt[PF], pd[PF], py[PF], pa[PF];
+  auto prefetch = [&](int n0) {   // loads only: nothing here may wait for the data
 #pragma unroll
     for (int q = 0; q < PF; ++q) {
       const int i = k + q * L;
       const int n = min(n0 + i, N - 1);
       pt[q] = __ldg(tp + n);
-      pd[q] = __ldg(dp + n) + (Ap ? __ldg(Ap + n) : 0.0);
+      pd[q] = __ldg(dp + n);
+      pa[q] = Ap ? __ldg(Ap + n) : 0.0;
       py[q] = yp ? __ldg(yp + n) : 0.0;
     }
   };
@@ -145,7 +146,7 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
 #pragma unroll
     for (int q = 0; q < PF; ++q) {
       const int i = k + q * L;
-      if (i < T) { t_s[1 + i] = pt[q]; d_s[i] = pd[q]; y_s[i] = py[q]; }
+      if (i < T) { t_s[1 + i] = pt[q]; d_s[i] = pd[q] + pa[q]; y_s[i] = py[q]; }
     }
     __syncwarp();
     t_last = t_s[nt];
