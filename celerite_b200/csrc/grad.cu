@@ -43,9 +43,10 @@ struct GradCfg {
   static constexpr int JJ = JP * JP;
   static constexpr int E = JJ + 2 * JP + 2;          // one tape / checkpoint record, in doubles
   static constexpr int kIn = 3 * T + 2;
-  static constexpr int kGen = 3 * T * JP;
+  static constexpr int kGen = 4 * T * JP;          // phi, u, v, phi o u
   static constexpr int kX = 4 * JP;                  // [2][2*JP] exchange rows
-  static constexpr int kP = 2 * JJ;                  // cp.async staging of two tape blocks
+  static constexpr int RD = JP >= 24 ? 2 : 4;        // cp.async ring: tape blocks staged RD-1 steps ahead
+  static constexpr int kP = RD * JJ;
   static constexpr int kCoef = 4 * JP + 2;
   static constexpr int kR = 6 * JP;
   static constexpr int kGroup = kIn + kGen + kX + kP + kCoef + kR;
@@ -77,9 +78,10 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   double* phi_s = y_s + T;               // [T][JP]
   double* u_s = phi_s + T * JP;
   double* v_s = u_s + T * JP;
-  double* x_s = v_s + T * JP;            // [2][2*JP]
-  double* p_s = x_s + 4 * JP;            // [2][JJ]
-  double* cf_s = p_s + 2 * JJ;
+  double* ut_s = v_s + T * JP;           // [T][JP] phi o u
+  double* x_s = ut_s + T * JP;           // [2][2*JP]
+  double* p_s = x_s + 4 * JP;            // [RD][JJ]
+  double* cf_s = p_s + C::kP;
   double* r_s = cf_s + C::kCoef;         // [6][JP]
 
   const int N = a.N, Jr = a.Jr, Jc = a.Jc, Jg = a.Jg, J = Jr + 2 * Jc + Jg, P = 1 + 2 * Jr + 4 * Jc;
@@ -97,7 +99,7 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   {
     const double* row = a.coeffs + bb * a.coeff_stride;
     for (int i = k; i < P; i += L) cf_s[i] = row[i];
-    for (int i = k; i < 3 * T * JP; i += L) phi_s[i] = 0.0;
+    for (int i = k; i < 4 * T * JP; i += L) phi_s[i] = 0.0;
     for (int i = k; i < 4 * JP; i += L) x_s[i] = 0.0;
   }
   __syncwarp();
@@ -119,60 +121,141 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   int partner = kk;
   if (kk >= Jr && kk < Jr + 2 * Jc) partner = Jr + ((kk - Jr) ^ 1);
 
+  // the branch-free sincos needs |d t| < 1e9; t is sorted, so its two ends bound every argument
+  double dmax = 0.0;
+  for (int j = 0; j < Jc; ++j) dmax = fmax(dmax, fabs(d_comp[j]));
+  const bool fast_math =
+      __all_sync(kFull, dmax * fmax(fabs(__ldg(tp)), fabs(__ldg(tp + N - 1))) < kFastTrigLimit);
+
   // ---- tile set-up: inputs + generators of steps n0 .. n0+nt-1 (cholesky.h:127-152) ----------
-  auto load_tile = [&](int n0, int nt) {
-    if (k == 0) t_s[0] = __ldg(tp + (n0 > 0 ? n0 - 1 : 0));
-    for (int i = k; i < nt; i += L) {
-      const int n = n0 + i;
-      t_s[1 + i] = __ldg(tp + n);
-      d_s[i] = __ldg(dp + n) + (Ap ? __ldg(Ap + n) : 0.0);
-      y_s[i] = __ldg(yp + n);
+  // The inputs of a tile are fetched into registers one tile ahead (prefetch only issues the
+  // loads; nothing waits for them until the tile is needed), in either walking direction.
+  constexpr int PF = (T + L - 1) / L;
+  double pt[PF], pd[PF], py[PF], pt0 = 0.0;
+  int pf_n0 = -1;
+  auto prefetch = [&](int n0) {
+    pf_n0 = n0;
+    pt0 = __ldg(tp + max(n0 - 1, 0));
+#pragma unroll
+    for (int q = 0; q < PF; ++q) {
+      const int n = min(n0 + k + q * L, N - 1);
+      pt[q] = __ldg(tp + n);
+      pd[q] = __ldg(dp + n) + (Ap ? __ldg(Ap + n) : 0.0);
+      py[q] = __ldg(yp + n);
+    }
+  };
+  // next_n0 < 0: nothing to fetch ahead
+  auto load_tile = [&](int n0, int nt, int next_n0) {
+    if (pf_n0 != n0) prefetch(n0);
+    if (k == 0) t_s[0] = pt0;
+#pragma unroll
+    for (int q = 0; q < PF; ++q) {
+      const int i = k + q * L;
+      if (i < T) { t_s[1 + i] = pt[q]; d_s[i] = pd[q]; y_s[i] = py[q]; }
     }
     __syncwarp();
-    const int nterm = Jr + Jc;
-    for (int item = k; item < nt * nterm; item += L) {
-      const int i = item / nterm, term = item - i * nterm;
-      const double tn = t_s[1 + i], dx = tn - t_s[i];
-      if (term < Jr) {
-        phi_s[i * JP + term] = cel_exp(-c_real[term] * dx);
-        u_s[i * JP + term] = a_real[term];
-        v_s[i * JP + term] = 1.0;
-      } else {
-        const int q = term - Jr, r0 = Jr + 2 * q;
-        double sd, cd;
-        cel_sincos(d_comp[q] * tn, &sd, &cd);
-        const double e = cel_exp(-c_comp[q] * dx);
-        const double aa = a_comp[q], bq = b_comp[q];
-        phi_s[i * JP + r0] = e;
-        phi_s[i * JP + r0 + 1] = e;
-        u_s[i * JP + r0] = aa * cd + bq * sd;
-        u_s[i * JP + r0 + 1] = aa * sd - bq * cd;
-        v_s[i * JP + r0] = cd;
-        v_s[i * JP + r0 + 1] = sd;
+    pf_n0 = -1;
+    if (next_n0 >= 0) prefetch(next_n0);
+    if (fast_math) {   // four independent (step, term) items per lane, branch-free routines
+      const int nc = nt * Jc;
+      for (int item0 = k; item0 < nc; item0 += 4 * L) {
+        double sd[4], cd[4], e[4];
+        int ii[4], qq[4];
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+          const int item = min(item0 + m * L, nc - 1);
+          ii[m] = item / Jc; qq[m] = item - ii[m] * Jc;
+          const double tn = t_s[1 + ii[m]], dx = tn - t_s[ii[m]];
+          cel_sincos_core(d_comp[qq[m]] * tn, &sd[m], &cd[m]);
+          e[m] = cel_exp_clamped(-c_comp[qq[m]] * dx);
+        }
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+          if (item0 + m * L < nc) {
+            const int i = ii[m], q = qq[m], r0 = Jr + 2 * q;
+            const double aa = a_comp[q], bq = b_comp[q];
+            const double u0 = aa * cd[m] + bq * sd[m], u1 = aa * sd[m] - bq * cd[m];
+            phi_s[i * JP + r0] = e[m]; phi_s[i * JP + r0 + 1] = e[m];
+            u_s[i * JP + r0] = u0; u_s[i * JP + r0 + 1] = u1;
+            ut_s[i * JP + r0] = e[m] * u0; ut_s[i * JP + r0 + 1] = e[m] * u1;
+            v_s[i * JP + r0] = cd[m]; v_s[i * JP + r0 + 1] = sd[m];
+          }
+        }
+      }
+      const int nr = nt * Jr;
+      for (int item0 = k; item0 < nr; item0 += 4 * L) {
+        double e[4];
+        int ii[4], qq[4];
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+          const int item = min(item0 + m * L, nr - 1);
+          ii[m] = item / Jr; qq[m] = item - ii[m] * Jr;
+          e[m] = cel_exp_clamped(-c_real[qq[m]] * (t_s[1 + ii[m]] - t_s[ii[m]]));
+        }
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+          if (item0 + m * L < nr) {
+            const int i = ii[m], q = qq[m];
+            phi_s[i * JP + q] = e[m];
+            u_s[i * JP + q] = a_real[q];
+            ut_s[i * JP + q] = e[m] * a_real[q];
+            v_s[i * JP + q] = 1.0;
+          }
+        }
+      }
+    } else {
+      const int nterm = Jr + Jc;
+      for (int item = k; item < nt * nterm; item += L) {
+        const int i = item / nterm, term = item - i * nterm;
+        const double tn = t_s[1 + i], dx = tn - t_s[i];
+        if (term < Jr) {
+          const double e = cel_exp(-c_real[term] * dx);
+          phi_s[i * JP + term] = e;
+          u_s[i * JP + term] = a_real[term];
+          ut_s[i * JP + term] = e * a_real[term];
+          v_s[i * JP + term] = 1.0;
+        } else {
+          const int q = term - Jr, r0 = Jr + 2 * q;
+          double sd, cd;
+          cel_sincos(d_comp[q] * tn, &sd, &cd);
+          const double e = cel_exp(-c_comp[q] * dx);
+          const double aa = a_comp[q], bq = b_comp[q];
+          const double u0 = aa * cd + bq * sd, u1 = aa * sd - bq * cd;
+          phi_s[i * JP + r0] = e;
+          phi_s[i * JP + r0 + 1] = e;
+          u_s[i * JP + r0] = u0;
+          u_s[i * JP + r0 + 1] = u1;
+          ut_s[i * JP + r0] = e * u0;
+          ut_s[i * JP + r0 + 1] = e * u1;
+          v_s[i * JP + r0] = cd;
+          v_s[i * JP + r0 + 1] = sd;
+        }
       }
     }
     for (int item = k; item < nt * Jg; item += L) {
       const int i = item / Jg, q = item - i * Jg, r0 = Jr + 2 * Jc + q;
+      const double ug = __ldg(Up + (size_t)(n0 + i) * Jg + q);
       phi_s[i * JP + r0] = 1.0;
-      u_s[i * JP + r0] = __ldg(Up + (size_t)(n0 + i) * Jg + q);
+      u_s[i * JP + r0] = ug;
+      ut_s[i * JP + r0] = ug;
       v_s[i * JP + r0] = __ldg(Vp + (size_t)(n0 + i) * Jg + q);
     }
     __syncwarp();
   };
 
-  // ---- forward state -------------------------------------------------------------------------
+  // ---- forward state (the low-latency form of coop.cu: S, D W, 1/D, f, x/D) -------------------
   double S[JP];
-  double W_own, f_own, Dprev, xprev;
+  double dw_own, r_prev, f_own, s_prev, Dprev, xprev;
   auto reset_state = [&]() {
 #pragma unroll
     for (int j = 0; j < JP; ++j) S[j] = 0.0;
-    W_own = 0.0; f_own = 0.0; Dprev = 0.0; xprev = 0.0;
+    dw_own = 0.0; r_prev = 0.0; f_own = 0.0; s_prev = 0.0; Dprev = 0.0; xprev = 0.0;
   };
   auto store_state = [&](double* rec) {   // checkpoint: S in place of P
     if (row_ok) {
 #pragma unroll
       for (int j = 0; j < JP; ++j) rec[j * JP + kk] = S[j];
-      rec[JJ + kk] = W_own;
+      rec[JJ + kk] = dw_own * r_prev;
       rec[JJ + JP + kk] = f_own;
     }
     if (k == 0) { rec[JJ + 2 * JP] = Dprev; rec[JJ + 2 * JP + 1] = xprev; }
@@ -180,14 +263,17 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   auto load_state = [&](const double* rec) {
 #pragma unroll
     for (int j = 0; j < JP; ++j) S[j] = row_ok ? rec[j * JP + kk] : 0.0;
-    W_own = row_ok ? rec[JJ + kk] : 0.0;
+    const double Wk = row_ok ? rec[JJ + kk] : 0.0;
     f_own = row_ok ? rec[JJ + JP + kk] : 0.0;
     Dprev = rec[JJ + 2 * JP];
     xprev = rec[JJ + 2 * JP + 1];
+    r_prev = (Dprev != 0.0) ? 1.0 / Dprev : 0.0;      // the state before step 0 has D = 0
+    dw_own = Wk * Dprev;
+    s_prev = xprev * r_prev;
   };
 
   double quad = 0.0;
-  LogAcc ld;
+  LogAccFast ld;
   ld.init();
   int fail = 0;
 
@@ -196,52 +282,59 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
     for (int i = 0; i < nt; ++i) {
       const int n = n0 + i, par = n & 1;
       const double* ph = phi_s + i * JP;
-      const double* uu = u_s + i * JP;
-      double* xw = x_s + par * 2 * JP;                 // W_{n-1}, written by the previous step
+      const double* ut = ut_s + i * JP;
+      const double* xw = x_s + par * 2 * JP;           // (D W)_{n-1}, written by the previous step
       const double phk = row_ok ? ph[kk] : 0.0;
-      const double uk = row_ok ? uu[kk] : 0.0;
+      const double utk = row_ok ? ut[kk] : 0.0;
       const double vk = row_ok ? v_s[i * JP + kk] : 0.0;
-      const double dwk = Dprev * W_own;
+      const double dwr = dw_own * r_prev;              // W_{n-1}[k]
       double* trec = tape + (size_t)(n - tape0) * E;
-      double acc0 = 0.0, acc1 = 0.0;
+      double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
 #pragma unroll
       for (int j = 0; j < JP; j += 2) {
         const double2 p2 = *reinterpret_cast<const double2*>(ph + j);
-        const double2 w2 = *reinterpret_cast<const double2*>(xw + j);
-        const double2 u2 = *reinterpret_cast<const double2*>(uu + j);
-        const double P0 = fma(dwk, w2.x, S[j]), P1 = fma(dwk, w2.y, S[j + 1]);
+        const double2 x2 = *reinterpret_cast<const double2*>(xw + j);
+        const double2 u2 = *reinterpret_cast<const double2*>(ut + j);
+        const double s0 = S[j], s1 = S[j + 1];
+        if ((j & 2) == 0) { acc0 = fma(s0, u2.x, acc0); acc1 = fma(s1, u2.y, acc1); }
+        else { acc2 = fma(s0, u2.x, acc2); acc3 = fma(s1, u2.y, acc3); }
+        const double P0 = fma(dwr, x2.x, s0), P1 = fma(dwr, x2.y, s1);
         if (TAPE && row_ok) { trec[j * JP + kk] = P0; trec[(j + 1) * JP + kk] = P1; }
         S[j] = (phk * p2.x) * P0;
         S[j + 1] = (phk * p2.y) * P1;
-        acc0 = fma(S[j], u2.x, acc0);
-        acc1 = fma(S[j + 1], u2.y, acc1);
       }
-      const double su = acc0 + acc1;
-      f_own = phk * fma(W_own, xprev, f_own);
-      double red0 = uk * su, red1 = uk * f_own;
-      group_sum2<L>(red0, red1);
-      const double Dn = (d_s[i] + aconst) - red0;
-      const double x = y_s[i] - red1;
-      const double r = 1.0 / Dn;
-      W_own = (vk - su) * r;
-      if (row_ok) x_s[(par ^ 1) * 2 * JP + kk] = W_own;
+      const double av = (acc0 + acc1) + (acc2 + acc3);
+      double red_a = utk * av, red_f = utk * f_own, red_b = utk * dw_own;
+      group_sum2<L>(red_a, red_f);                     // known early: off the scalar chain
+      red_b = group_sum<L>(red_b);                     // the one reduction on the chain
+      const double tb = red_b * r_prev;
+      const double Dn = ((d_s[i] + aconst) - red_a) - red_b * tb;
+      const double x = (y_s[i] - red_f) - red_b * s_prev;
+      const double dw = vk - phk * fma(dw_own, tb, av);
+      f_own = phk * fma(dw_own, s_prev, f_own);
+      if (row_ok) x_s[(par ^ 1) * 2 * JP + kk] = dw;
+      const double r = fast_rcp_nocheck(Dn);
       if (TAPE) {
-        if (row_ok) { trec[JJ + kk] = W_own; trec[JJ + JP + kk] = f_own; }
+        if (row_ok) { trec[JJ + kk] = dw * r; trec[JJ + JP + kk] = f_own; }
         if (k == 0) { trec[JJ + 2 * JP] = Dn; trec[JJ + 2 * JP + 1] = x; }
       }
+      s_prev = r * x;
       if (ACCUM) {
-        if (Dn < 0.0 && fail == 0) fail = n + 1;       // cholesky.h:176
-        quad = fma(x * x, r, quad);
+        fail = (Dn < 0.0 && fail == 0) ? n + 1 : fail;   // cholesky.h:176
+        quad = fma(x, s_prev, quad);
         ld.add(Dn);
       }
+      dw_own = dw;
+      r_prev = r;
       Dprev = Dn;
       xprev = x;
       __syncwarp();
     }
+    if (ACCUM) ld.renorm();
   };
-  // make the exchange row hold W_{n-1} for the step that comes next (after a state reload)
+  // make the exchange row hold (D W)_{n-1} for the step that comes next (after a state reload)
   auto publish_W = [&](int n_next) {
-    if (row_ok) x_s[(n_next & 1) * 2 * JP + kk] = W_own;
+    if (row_ok) x_s[(n_next & 1) * 2 * JP + kk] = dw_own;
     __syncwarp();
   };
 
@@ -253,10 +346,10 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
     store_state(ckpt + (size_t)s * E);
     for (int n0 = seg0; n0 < seg1; n0 += T) {
       const int nt = min(T, seg1 - n0);
-      load_tile(n0, nt);
+      const int nx = n0 + T < seg1 ? n0 + T : (seg1 < N ? seg1 : -1);
+      load_tile(n0, nt, nx);
       forward_tile(n0, nt, false, 0, true);
     }
-    ld.renorm();
   }
 
   // =========================== phase B: segments in reverse =====================================
@@ -265,6 +358,8 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   for (int j = 0; j < JP; ++j) Pb[j] = 0.0;
   double gbar = 0.0, PbW = 0.0, sumA = 0.0;
   double R1 = 0.0, R2 = 0.0, R3 = 0.0, R4 = 0.0, R5 = 0.0, R6 = 0.0;
+  // tape scalars are fetched ahead of their use: two steps ahead while registers allow
+  constexpr bool DEEP = JP <= 16;
 
   __syncwarp();
   for (int s = nseg - 1; s >= 0; --s) {
@@ -274,40 +369,52 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
     __syncwarp();
     load_state(crec);
     publish_W(seg0);
+    int tile_n0 = -1;
     for (int n0 = seg0; n0 < seg1; n0 += T) {
       const int nt = min(T, seg1 - n0);
-      load_tile(n0, nt);
+      // ahead: the next tile; from the last tile, the one the adjoint walks into after it
+      const int nx = n0 + T < seg1 ? n0 + T : (n0 > seg0 ? n0 - T : (seg0 > 0 ? seg0 - Cseg : -1));
+      load_tile(n0, nt, nx);
       forward_tile(n0, nt, true, seg0, false);
+      tile_n0 = n0;                                    // the adjoint starts in this tile
     }
     __threadfence_block();
     __syncwarp();
 
     // ---- adjoint over the segment, n = seg1-1 .. seg0 ----
-    auto stage_block = [&](int n) {   // tape block of step n -> p_s[n & 1] (coalesced cp.async)
-      const double* src = tape + (size_t)(n - seg0) * E;
-      double* dst = p_s + (n & 1) * JJ;
-      for (int e = 2 * k; e < JJ; e += 2 * L) cp_async16(dst + e, src + e);
+    // tape block of step n -> ring slot n % RD (coalesced cp.async); one group per call, empty
+    // past the segment start so that the group count stays uniform
+    auto stage_block = [&](int n) {
+      if (n >= seg0) {
+        const double* src = tape + (size_t)(n - seg0) * E;
+        double* dst = p_s + (n & (C::RD - 1)) * JJ;
+        for (int e = 2 * k; e < JJ; e += 2 * L) cp_async16(dst + e, src + e);
+      }
       cp_async_commit();
     };
-    stage_block(seg1 - 1);
-    int tile_n0 = -1;
+    // record of step n: {W_n[k], f_n[k], D_n, x_n}; n = seg0-1 is the checkpoint
+    auto load_rec = [&](int n, double& Wv, double& fv, double& Dv, double& xv) {
+      const double* rec = n >= seg0 ? tape + (size_t)(n - seg0) * E : crec;
+      Wv = __ldcg(rec + JJ + kk);
+      fv = __ldcg(rec + JJ + JP + kk);
+      Dv = __ldcg(rec + JJ + 2 * JP);
+      xv = __ldcg(rec + JJ + 2 * JP + 1);
+    };
+    for (int q = 1; q < C::RD; ++q) stage_block(seg1 - q);
+    double Wn, fn, Dn, xn, Wm, fm, Dm, xm, Wq = 0.0, fq = 0.0, Dq = 0.0, xq = 0.0;
+    load_rec(seg1 - 1, Wn, fn, Dn, xn);
+    if (DEEP) load_rec(seg1 - 2, Wm, fm, Dm, xm);       // seg1-2 >= seg0-1
     for (int n = seg1 - 1; n >= seg0; --n) {
       // generators of the tile containing n (tiles are aligned to the segment start)
       const int tn0 = seg0 + ((n - seg0) / T) * T;
       if (tn0 != tile_n0) {
         tile_n0 = tn0;
-        load_tile(tn0, min(T, seg1 - tn0));
+        load_tile(tn0, min(T, seg1 - tn0), tn0 > seg0 ? tn0 - T : (seg0 > 0 ? seg0 - Cseg : -1));
       }
       const int i = n - tile_n0;
-      if (n > seg0) stage_block(n - 1);
-      const double* rec = tape + (size_t)(n - seg0) * E;
-      const double* prec = (n > seg0) ? rec - E : crec;   // record of step n-1 (checkpoint at the edge)
-      const double Wn = row_ok ? rec[JJ + kk] : 0.0;
-      const double fn = row_ok ? rec[JJ + JP + kk] : 0.0;
-      const double Dn = rec[JJ + 2 * JP], xn = rec[JJ + 2 * JP + 1];
-      const double Wm = row_ok ? prec[JJ + kk] : 0.0;     // W_{n-1}[k]
-      const double fm = row_ok ? prec[JJ + JP + kk] : 0.0;
-      const double xm = prec[JJ + 2 * JP + 1];
+      stage_block(n - (C::RD - 1));
+      if (DEEP) load_rec(max(n - 2, seg0 - 1), Wq, fq, Dq, xq);
+      else load_rec(n - 1, Wm, fm, Dm, xm);
       const double* ph = phi_s + i * JP;
       const double* uu = u_s + i * JP;
       const double phk = row_ok ? ph[kk] : 0.0;
@@ -315,32 +422,31 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
       const double vk = row_ok ? v_s[i * JP + kk] : 0.0;
       const double vpart = row_ok ? v_s[i * JP + partner] : 0.0;
       const double tn = t_s[1 + i], dxn = tn - t_s[i];
+      const double Wk = row_ok ? Wn : 0.0;
 
-      const double r = 1.0 / Dn;
-      double red0 = Wn * PbW, red1 = gbar * Wn;
+      const double r = fast_rcp_nocheck(Dn);
+      const double xr = xn * r;
+      double red0 = Wk * PbW, red1 = gbar * Wk;
       group_sum2<L>(red0, red1);
-      double Dbar = red0 + 0.5 * (xn * r) * (xn * r) - 0.5 * r;
-      const double xbar = red1 - xn * r;
+      // sum_k Wbar_k W_k = 2 D red0 + x red1: no third reduction
+      const double Dbar = fma(-xr, red1, fma(0.5 * xr, xr, -0.5 * r)) - red0;
+      const double xbar = red1 - xr;
       const double Wbar = 2.0 * Dn * PbW + gbar * xn;
-      const double red2 = group_sum<L>(Wbar * Wn);
-      Dbar -= red2 * r;
       const double w = Wbar * r;                          // also vbar_k
       R6 = fma(tn * w, vpart, R6);
       sumA += Dbar;
       const int par = n & 1;
       double* xch = x_s + par * 2 * JP;
       if (row_ok) { xch[kk] = w; xch[JP + kk] = Wm; }
-      if (n > seg0) cp_async_wait<1>(); else cp_async_wait<0>();
+      cp_async_wait<C::RD - 1>();                         // block n: requested RD-1 steps ago
       __syncwarp();
-      if (n > 0) {
+      if (n > 0) {                                        // step 0 has no generators (cholesky.h:118-124)
         const double fbar = gbar - xbar * uk;
-        double ubar = -xbar * fn;
-        const double gprev = fma(Wm, xm, fm);
-        double phibar = fbar * gprev;
+        const double gprev = row_ok ? fma(Wm, xm, fm) : 0.0;
         gbar = phk * fbar;
-        const double* pb = p_s + par * JJ;
+        const double* pb = p_s + (n & (C::RD - 1)) * JJ;
         const double hw = 0.5 * w, hu = 0.5 * uk, du = Dbar * uk;
-        double aSw = 0.0, aSu = 0.0, aphi = 0.0, aPbW = 0.0;
+        double aSw = 0.0, aSu = 0.0, aphi0 = 0.0, aphi1 = 0.0, aP0 = 0.0, aP1 = 0.0, aP2 = 0.0, aP3 = 0.0;
 #pragma unroll
         for (int j = 0; j < JP; ++j) {
           const double p = pb[j * JP + kk];
@@ -353,20 +459,25 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
           sb = fma(-hw, uj, sb);
           sb = fma(-hu, wj, sb);
           sb = fma(-du, uj, sb);
-          aphi = fma(sb * p, pj, aphi);
           const double pn = pp * sb;
           Pb[j] = row_ok ? pn : 0.0;
-          aPbW = fma(pn, wmj, aPbW);
+          if (j & 1) aphi1 = fma(sb * p, pj, aphi1); else aphi0 = fma(sb * p, pj, aphi0);
+          if ((j & 3) == 0) aP0 = fma(pn, wmj, aP0);
+          else if ((j & 3) == 1) aP1 = fma(pn, wmj, aP1);
+          else if ((j & 3) == 2) aP2 = fma(pn, wmj, aP2);
+          else aP3 = fma(pn, wmj, aP3);
         }
-        ubar -= aSw + 2.0 * Dbar * aSu;
-        phibar = fma(2.0, aphi, phibar);
-        PbW = row_ok ? aPbW : 0.0;
+        PbW = row_ok ? (aP0 + aP1) + (aP2 + aP3) : 0.0;
+        const double ubar = -xbar * (row_ok ? fn : 0.0) - (aSw + 2.0 * Dbar * aSu);
+        const double phibar = fma(2.0, aphi0 + aphi1, fbar * gprev);
         R1 = fma(ubar, vk, R1);
         R2 = fma(ubar, vpart, R2);
         R3 = fma(phibar, -dxn * phk, R3);
         R4 = fma(tn * ubar, vk, R4);
         R5 = fma(tn * ubar, vpart, R5);
       }
+      Wn = Wm; fn = fm; Dn = Dm; xn = xm;
+      if (DEEP) { Wm = Wq; fm = fq; Dm = Dq; xm = xq; }
       __syncwarp();
     }
   }
@@ -430,6 +541,36 @@ int grad_default_segment(int N) {
   int c = 16;
   while ((long long)c * c < (long long)N) c += 16;
   return c;
+}
+
+// Segment length for a batch: short enough that the tapes of the series in flight stay in L2
+// (each tape record is written once and read once; a tape that spills to DRAM costs 2 E doubles
+// of traffic per step), as long as the checkpoints that pays for fit in `kMaxScratch`.
+// Measured (profiles/README.md): B = 1024, N = 1e5, J = 8: 146 ms at sqrt(N), 120 ms at 64.
+int grad_tuned_segment(long long B, int N, int J, bool lockstep) {
+  const int seg_sqrt = grad_default_segment(N);
+  constexpr double kL2Budget = 48e6, kMaxScratch = 8e9;
+  double rec_bytes, ckpt_bytes;
+  long long resident;
+  int step;
+  if (lockstep) {
+    const int T3 = J * (J + 1) / 2, NP = J / 2;
+    rec_bytes = 8.0 * (T3 + 2 * J + 2 + 3 * NP + 2);
+    ckpt_bytes = 8.0 * (T3 + 3 * J + 2);
+    resident = 148LL * 8 * kWarp;
+    step = 8;
+  } else {
+    const int JP = grad_jp(J);
+    rec_bytes = ckpt_bytes = 8.0 * (JP * JP + 2 * JP + 2);
+    resident = 148LL * 8 * (kWarp / pow2ceil(JP));
+    step = 16;
+  }
+  if (resident > B) resident = B;
+  int seg = (int)(kL2Budget / (rec_bytes * (double)resident)) / step * step;
+  if (seg < step) seg = step;
+  // checkpoints: B * ceil(N / seg) records
+  while (seg < seg_sqrt && (double)B * ((N + seg - 1) / seg) * ckpt_bytes > kMaxScratch) seg += step;
+  return seg < seg_sqrt ? seg : seg_sqrt;
 }
 
 size_t grad_scratch_doubles(long long B, int N, int J, int seg) {

@@ -70,6 +70,7 @@ struct GradArgs {
   int seg;              // checkpoint distance (multiple of 16)
 };
 int grad_default_segment(int N);
+int grad_tuned_segment(long long B, int N, int J, bool lockstep);   // batch-aware (L2-resident tapes)
 size_t grad_scratch_doubles(long long B, int N, int J, int seg);
 cudaError_t launch_grad_coop(const GradArgs& a, cudaStream_t stream);
 
