@@ -8,12 +8,13 @@ namespace {
 
 inline size_t dbytes(size_t n) { return n * sizeof(double); }
 
-// chunk length that gives about 16 warps of groups per SM (148 SMs), never shorter than 256 steps
+// chunk length that gives one full wave of groups: 10 one-warp CTAs per SM (the staging ring of
+// scan.cu is ~20 KB per warp) on 148 SMs; never shorter than 256 steps
 void plan_chunks(cel_solver* s, int Nloc) {
   const int J = s->J > 0 ? s->J : 1;
   int L = 1;
   while (L < J && L < 32) L <<= 1;
-  const long long target = 148LL * 16 * (32 / L);
+  const long long target = 148LL * 10 * (32 / L);
   long long len = (Nloc + target - 1) / target;
   if (len < 256) len = 256;
   len = (len + 7) / 8 * 8;

@@ -87,6 +87,10 @@ __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.a
 __device__ __forceinline__ void cp_async_8(void* smem_dst, const void* gsrc) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
 }
+// 16-byte variant, L1-bypassing (streamed data)
+__device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit_group() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
@@ -101,6 +105,18 @@ __device__ __forceinline__ double group_sum(double v) {
 #pragma unroll
   for (int o = L / 2; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o, L);
   return v;
+}
+// same, naming only the lanes of the caller's group: groups of one warp may then follow
+// different control flow (chunks of different length in scan.cu)
+template <int L>
+__device__ __forceinline__ double group_sum_masked(double v, unsigned mask) {
+#pragma unroll
+  for (int o = L / 2; o > 0; o >>= 1) v += __shfl_xor_sync(mask, v, o, L);
+  return v;
+}
+template <int L>
+__device__ __forceinline__ unsigned group_mask(int g) {
+  return L >= 32 ? kFull : (((1u << (L & 31)) - 1u) << (g * L));
 }
 template <int L>
 __device__ __forceinline__ void group_sum2(double& a, double& b) {

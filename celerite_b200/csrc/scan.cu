@@ -26,14 +26,56 @@
 namespace cel {
 namespace {
 
-constexpr int TT = 8;
+constexpr int TT = 8;        // steps per staged tile
+constexpr int kStages = 3;   // tiles in the ring: two in flight while one is consumed
+
+// branch-free square root for normal positive d (a valid factor has D > 0): MUFU.RSQ64H seed,
+// two coupled Newton steps and a final residual correction
+__device__ __forceinline__ double fast_sqrt_nocheck(double d) {
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+  double g = d * y, h = 0.5 * y;
+  double r = fma(-h, g, 0.5);
+  g = fma(g, r, g); h = fma(h, r, h);
+  r = fma(-h, g, 0.5);
+  g = fma(g, r, g); h = fma(h, r, h);
+  return fma(fma(-g, g, d), h, g);
+}
 
 // --------------------------------------------------------------------------------------------
 // chunk sweeps
+//
+// The factor rows of a chunk are one contiguous range per array, so every tile of TT steps is
+// copied global -> shared as flat 16-byte cp.async units (8-byte units when J is odd and the rows
+// are only 8-byte aligned): a group asks for TT*J*8 contiguous bytes per array at once, which
+// keeps DRAM pages open, costs no registers, and lets the ring run two tiles (16 steps) ahead
+// of the serial recurrence.  The earlier version loaded row by row into a register double
+// buffer (40 scalar loads per tile and lane, 206 registers, 64-byte DRAM requests).
 // --------------------------------------------------------------------------------------------
 template <int L>
+struct ChunkSmem {
+  static constexpr int G = kWarp / L;
+  static constexpr int ROW = TT * L;                 // doubles per factor array per stage
+  static constexpr int STAGE = 3 * ROW + 2 * TT;     // phi | u | W | rhs | D
+  static constexpr int GROUP = kStages * STAGE;
+};
+
+// n doubles, contiguous, dst/src 16-byte aligned when vec16
+template <int L>
+__device__ __forceinline__ void copy_flat(double* dst, const double* src, int n, int k, bool vec16) {
+  if (vec16) {
+    for (int e = 2 * k; e < n; e += 2 * L) cp_async_16(dst + e, src + e);
+  } else {
+    for (int e = k; e < n; e += L) cp_async_8(dst + e, src + e);
+  }
+}
+
+// MODE 0: forward half of solve (writes x / D);  MODE 1: dot_L
+template <int L, int MODE>
 __global__ void __launch_bounds__(kWarp) k_chunk_forward(ScanArgs a) {
-  constexpr int G = kWarp / L;
+  using SM = ChunkSmem<L>;
+  constexpr int G = SM::G, ROW = SM::ROW;
+  __shared__ __align__(16) double sm[G * SM::GROUP];
   const int lane = threadIdx.x, g = lane / L, k = lane % L;
   const int ncols = a.nrhs + a.nbasis;
   const long long total = (long long)a.nchunks * ncols;
@@ -47,53 +89,89 @@ __global__ void __launch_bounds__(kWarp) k_chunk_forward(ScanArgs a) {
   const int kk = row_ok ? k : 0;
   const int n0 = chunk * a.chunk_len, n1 = min(N, n0 + a.chunk_len);
   const double* in = is_rhs ? a.in + (size_t)col * N : nullptr;
-  double* out = (is_rhs && a.out) ? a.out + (size_t)col * N : nullptr;
+  double* out = (is_rhs && a.out && active) ? a.out + (size_t)col * N : nullptr;
+  const bool vec16 = (J & 1) == 0;
+  // every warp-level primitive below names the group's own lanes only: chunks (and with them the
+  // trip counts) differ between the groups of a warp
+  const unsigned gmask = group_mask<L>(g);
+  double* base = sm + g * SM::GROUP;
 
   double f;
   if (a.init) f = row_ok ? a.init[((size_t)chunk * ncols + col) * J + kk] : 0.0;
   else if (is_rhs) f = 0.0;
   else f = (row_ok && (a.diag_basis || kk == col - a.nrhs)) ? 1.0 : 0.0;
 
-  struct Tile { double ph[TT], uu[TT], ww[TT], bn[TT], dn[TT]; };
-  auto load = [&](Tile& tl, int m0) {
-#pragma unroll
-    for (int i = 0; i < TT; ++i) {
-      const int n = min(m0 + i, n1 - 1), s = n + off;
-      const bool has_prev = (s >= 1) && row_ok;
-      tl.ph[i] = has_prev ? __ldg(a.phi + (size_t)(s - 1) * J + kk) : 0.0;
-      tl.uu[i] = has_prev ? __ldg(a.u + (size_t)(s - 1) * J + kk) : 0.0;
-      tl.ww[i] = row_ok ? __ldg(a.W + (size_t)s * J + kk) : 0.0;
-      tl.bn[i] = in ? __ldg(in + n) : 0.0;
-      tl.dn[i] = __ldg(a.D + s);
-    }
-  };
-  double wprev = 0.0, sprev = 0.0;
-  auto run = [&](const Tile& tl, int m0) {
-#pragma unroll
-    for (int i = 0; i < TT; ++i) {
-      if (m0 + i < n1) {
-        f = tl.ph[i] * fma(wprev, sprev, f);
-        const double red = group_sum<L>(tl.uu[i] * f);
-        if (a.mode == 1) {
-          const double tmp = sqrt(tl.dn[i]) * tl.bn[i];
-          if (out && k == 0 && active) out[m0 + i] = tmp + red;
-          sprev = tmp;
-        } else {
-          const double x = tl.bn[i] - red;
-          if (out && k == 0 && active) out[m0 + i] = x / tl.dn[i];
-          sprev = x;
-        }
-        wprev = tl.ww[i];
+  for (int e = k; e < SM::GROUP; e += L) base[e] = 0.0;   // basis columns keep a zero rhs
+  __syncwarp(gmask);
+
+  // tile of steps m0 .. m0+TT-1 -> ring slot st (a commit per call keeps the group count uniform)
+  auto issue = [&](int m0, int st) {
+    if (m0 < n1) {
+      const int cnt = min(TT, n1 - m0), s0 = m0 + off;
+      double* sp = base + st * SM::STAGE;
+      copy_flat<L>(sp + 2 * ROW, a.W + (size_t)s0 * J, cnt * J, k, vec16);
+      const int skip = (s0 == 0) ? 1 : 0;                 // the first step has no phi / u
+      if (cnt > skip) {
+        copy_flat<L>(sp + skip * J, a.phi + (size_t)(s0 - 1 + skip) * J, (cnt - skip) * J, k, vec16);
+        copy_flat<L>(sp + ROW + skip * J, a.u + (size_t)(s0 - 1 + skip) * J, (cnt - skip) * J, k, vec16);
+      }
+      if (skip && row_ok) { sp[kk] = 0.0; sp[ROW + kk] = 0.0; }
+      for (int i = k; i < cnt; i += L) {
+        if (in) cp_async_8(sp + 3 * ROW + i, in + m0 + i);
+        cp_async_8(sp + 3 * ROW + TT + i, a.D + s0 + i);
       }
     }
+    cp_async_commit_group();
   };
-  Tile ta, tb;
-  load(ta, n0);
-  for (int m0 = n0; m0 < n1; m0 += 2 * TT) {
-    if (m0 + TT < n1) load(tb, m0 + TT);
-    run(ta, m0);
-    if (m0 + 2 * TT < n1) load(ta, m0 + 2 * TT);
-    if (m0 + TT < n1) run(tb, m0 + TT);
+
+  double wprev = 0.0, sprev = 0.0;
+  auto step = [&](double* sp, int i) {
+    const double ph = row_ok ? sp[i * J + kk] : 0.0;
+    const double uu = row_ok ? sp[ROW + i * J + kk] : 0.0;
+    const double ww = row_ok ? sp[2 * ROW + i * J + kk] : 0.0;
+    const double bn = sp[3 * ROW + i], dn = sp[3 * ROW + TT + i];
+    f = ph * fma(wprev, sprev, f);
+    const double red = group_sum_masked<L>(uu * f, gmask);
+    double res;
+    if (MODE == 1) {
+      const double tmp = fast_sqrt_nocheck(dn) * bn;
+      res = tmp + red;
+      sprev = tmp;
+    } else {
+      const double x = bn - red;
+      res = x * fast_rcp_nocheck(dn);
+      sprev = x;
+    }
+    wprev = ww;
+    return res;
+  };
+
+  const int ntiles = (n1 - n0 + TT - 1) / TT;
+  for (int q = 0; q < kStages - 1; ++q) issue(n0 + q * TT, q);
+  for (int t = 0; t < ntiles; ++t) {
+    issue(n0 + (t + kStages - 1) * TT, (t + kStages - 1) % kStages);
+    cp_async_wait_group<kStages - 1>();
+    __syncwarp(gmask);
+    double* sp = base + (t % kStages) * SM::STAGE;
+    const int m0 = n0 + t * TT, cnt = min(TT, n1 - m0);
+    double mine = 0.0;                                   // lane k keeps the results of steps i = k (mod L)
+    if (cnt == TT) {
+#pragma unroll
+      for (int i = 0; i < TT; ++i) {
+        const double res = step(sp, i);
+        if ((i % L) == k) { if (L >= TT) mine = res; else if (out) sp[3 * ROW + i] = res; }
+      }
+    } else {
+      for (int i = 0; i < cnt; ++i) {
+        const double res = step(sp, i);
+        if ((i % L) == k) { if (L >= TT) mine = res; else if (out) sp[3 * ROW + i] = res; }
+      }
+    }
+    if (out) {
+      if (L >= TT) { if (k < cnt) out[m0 + k] = mine; }
+      else { __syncwarp(gmask); for (int i = k; i < cnt; i += L) out[m0 + i] = sp[3 * ROW + i]; }
+    }
+    __syncwarp(gmask);
   }
   if (a.carry && row_ok && active) a.carry[((size_t)chunk * ncols + col) * J + kk] = fma(wprev, sprev, f);
 }
@@ -101,7 +179,9 @@ __global__ void __launch_bounds__(kWarp) k_chunk_forward(ScanArgs a) {
 // backward half of solve; `in` holds x/D, chunks are independent given F at their upper edge
 template <int L>
 __global__ void __launch_bounds__(kWarp) k_chunk_backward(ScanArgs a) {
-  constexpr int G = kWarp / L;
+  using SM = ChunkSmem<L>;
+  constexpr int G = SM::G, ROW = SM::ROW;
+  __shared__ __align__(16) double sm[G * SM::GROUP];
   const int lane = threadIdx.x, g = lane / L, k = lane % L;
   const int ncols = a.nrhs + a.nbasis;
   const long long total = (long long)a.nchunks * ncols;
@@ -115,46 +195,75 @@ __global__ void __launch_bounds__(kWarp) k_chunk_backward(ScanArgs a) {
   const int kk = row_ok ? k : 0;
   const int n0 = chunk * a.chunk_len, n1 = min(N, n0 + a.chunk_len);
   const double* in = is_rhs ? a.in + (size_t)col * N : nullptr;
-  double* out = (is_rhs && a.out) ? a.out + (size_t)col * N : nullptr;
+  double* out = (is_rhs && a.out && active) ? a.out + (size_t)col * N : nullptr;
+  const bool vec16 = (J & 1) == 0;
+  // every warp-level primitive below names the group's own lanes only: chunks (and with them the
+  // trip counts) differ between the groups of a warp
+  const unsigned gmask = group_mask<L>(g);
+  double* base = sm + g * SM::GROUP;
 
   double f;  // F_n of the step about to be processed
   if (a.init) f = row_ok ? a.init[((size_t)chunk * ncols + col) * J + kk] : 0.0;
   else if (is_rhs) f = 0.0;
   else f = (row_ok && kk == col - a.nrhs) ? 1.0 : 0.0;
 
-  struct Tile { double ph[TT], uu[TT], ww[TT], xn[TT]; };
-  // m counts down from the chunk's upper edge: step m is n = n1-1-m
-  auto load = [&](Tile& tl, int m0) {
-#pragma unroll
-    for (int i = 0; i < TT; ++i) {
-      const int n = max(n1 - 1 - (m0 + i), n0), s = n + off;
-      const bool has_prev = (s >= 1) && row_ok;
-      tl.ph[i] = has_prev ? __ldg(a.phi + (size_t)(s - 1) * J + kk) : 0.0;   // phi_n
-      tl.uu[i] = has_prev ? __ldg(a.u + (size_t)(s - 1) * J + kk) : 0.0;     // u_n
-      tl.ww[i] = row_ok ? __ldg(a.W + (size_t)s * J + kk) : 0.0;
-      tl.xn[i] = in ? __ldg(in + n) : 0.0;
+  for (int e = k; e < SM::GROUP; e += L) base[e] = 0.0;
+  __syncwarp(gmask);
+
+  // Tiles are aligned to the chunk start (tile q = steps n0+q*TT ..) and walked from the last
+  // one down, so that every copy starts on a 16-byte boundary.
+  const int ntiles = (n1 - n0 + TT - 1) / TT;
+  auto issue = [&](int q, int st) {                       // q counts tiles from the top: tile ntiles-1-q
+    if (q < ntiles) {
+      const int m0 = n0 + (ntiles - 1 - q) * TT;
+      const int cnt = min(TT, n1 - m0), s0 = m0 + off;
+      double* sp = base + st * SM::STAGE;
+      copy_flat<L>(sp + 2 * ROW, a.W + (size_t)s0 * J, cnt * J, k, vec16);
+      const int skip = (s0 == 0) ? 1 : 0;
+      if (cnt > skip) {
+        copy_flat<L>(sp + skip * J, a.phi + (size_t)(s0 - 1 + skip) * J, (cnt - skip) * J, k, vec16);
+        copy_flat<L>(sp + ROW + skip * J, a.u + (size_t)(s0 - 1 + skip) * J, (cnt - skip) * J, k, vec16);
+      }
+      if (skip && row_ok) { sp[kk] = 0.0; sp[ROW + kk] = 0.0; }
+      if (in) for (int i = k; i < cnt; i += L) cp_async_8(sp + 3 * ROW + i, in + m0 + i);
     }
+    cp_async_commit_group();
   };
-  const int len = n1 - n0;
-  auto run = [&](const Tile& tl, int m0) {
+  auto step = [&](double* sp, int i) {
+    const double ph = row_ok ? sp[i * J + kk] : 0.0;
+    const double uu = row_ok ? sp[ROW + i * J + kk] : 0.0;
+    const double ww = row_ok ? sp[2 * ROW + i * J + kk] : 0.0;
+    const double red = group_sum_masked<L>(ww * f, gmask);
+    const double z = sp[3 * ROW + i] - red;
+    f = ph * fma(uu, z, f);   // F_{n-1}
+    return z;
+  };
+
+  for (int q = 0; q < kStages - 1; ++q) issue(q, q);
+  for (int t = 0; t < ntiles; ++t) {
+    issue(t + kStages - 1, (t + kStages - 1) % kStages);
+    cp_async_wait_group<kStages - 1>();
+    __syncwarp(gmask);
+    double* sp = base + (t % kStages) * SM::STAGE;
+    const int m0 = n0 + (ntiles - 1 - t) * TT, cnt = min(TT, n1 - m0);
+    double mine = 0.0;
+    if (cnt == TT) {
 #pragma unroll
-    for (int i = 0; i < TT; ++i) {
-      if (m0 + i < len) {
-        const int n = n1 - 1 - (m0 + i);
-        const double red = group_sum<L>(tl.ww[i] * f);
-        const double z = tl.xn[i] - red;
-        if (out && k == 0 && active) out[n] = z;
-        f = tl.ph[i] * fma(tl.uu[i], z, f);   // F_{n-1}
+      for (int i = TT - 1; i >= 0; --i) {
+        const double z = step(sp, i);
+        if ((i % L) == k) { if (L >= TT) mine = z; else if (out) sp[3 * ROW + i] = z; }
+      }
+    } else {
+      for (int i = cnt - 1; i >= 0; --i) {
+        const double z = step(sp, i);
+        if ((i % L) == k) { if (L >= TT) mine = z; else if (out) sp[3 * ROW + i] = z; }
       }
     }
-  };
-  Tile ta, tb;
-  load(ta, 0);
-  for (int m0 = 0; m0 < len; m0 += 2 * TT) {
-    if (m0 + TT < len) load(tb, m0 + TT);
-    run(ta, m0);
-    if (m0 + 2 * TT < len) load(ta, m0 + 2 * TT);
-    if (m0 + TT < len) run(tb, m0 + TT);
+    if (out) {
+      if (L >= TT) { if (k < cnt) out[m0 + k] = mine; }
+      else { __syncwarp(gmask); for (int i = k; i < cnt; i += L) out[m0 + i] = sp[3 * ROW + i]; }
+    }
+    __syncwarp(gmask);
   }
   if (a.carry && row_ok && active) a.carry[((size_t)chunk * ncols + col) * J + kk] = f;
 }
@@ -394,7 +503,8 @@ cudaError_t launch_chunk_sweep(const ScanArgs& a, cudaStream_t stream) {
     const int G = kWarp / LL;                                                     \
     const unsigned grid = (unsigned)((total + G - 1) / G);                        \
     if (a.mode == 2) k_chunk_backward<LL><<<grid, kWarp, 0, stream>>>(a);         \
-    else k_chunk_forward<LL><<<grid, kWarp, 0, stream>>>(a);                      \
+    else if (a.mode == 1) k_chunk_forward<LL, 1><<<grid, kWarp, 0, stream>>>(a);  \
+    else k_chunk_forward<LL, 0><<<grid, kWarp, 0, stream>>>(a);                   \
   }
   CEL_DISPATCH_L(a.J, CALL);
 #undef CALL
