@@ -59,7 +59,10 @@ int cel_destroy(cel_solver* s) {
                          &s->out0, &s->out1, &s->scratch0, &s->scratch1, &s->scratch2,
                          &s->stage_t[0], &s->stage_t[1], &s->stage_d[0], &s->stage_d[1], &s->stage_y[0],
                          &s->stage_y[1], &s->stage_c[0], &s->stage_c[1], &s->stage_o[0], &s->stage_o[1],
-                         &s->stage_s[0], &s->stage_s[1]};
+                         &s->stage_s[0], &s->stage_s[1],
+                         &s->maps[0], &s->maps[1], &s->maps[2], &s->pmaps[0], &s->pmaps[1], &s->pmaps[2],
+                         &s->smaps[0], &s->smaps[1], &s->smaps[2], &s->tmaps[0], &s->tmaps[1], &s->tmaps[2],
+                         &s->scan_vecs, &s->scan_h, &s->scan_cs, &s->scan_sg, &s->scan_total, &s->scan_tmp};
   for (auto* b : bufs) b->release();
   for (int i = 0; i < 2; ++i) {
     if (s->copy_stream[i]) cudaStreamDestroy(s->copy_stream[i]);

@@ -34,61 +34,68 @@ cel::ScanArgs base_args(cel_solver* s, int Nloc, int mode) {
 
 int nbasis_of(const cel_solver* s, int mode) { return mode == 1 ? 1 : s->J; }
 
-// chunk maps of one direction: depend on the factor only, computed once per compute()
+// chunk maps of one direction and what the middle stage derives from them (prefix maps inside the
+// super-chunks, super-chunk maps, map of the span): depend on the factor only, computed once per
+// compute()
 int ensure_maps(cel_solver* s, int Nloc, int mode) {
   if (s->maps_valid[mode]) return CEL_OK;
-  const int nb = nbasis_of(s, mode);
-  CEL_CUDA_TRY(s, s->maps[mode].reserve(dbytes((size_t)s->scan_nchunks * nb * s->J)));
+  const int nb = nbasis_of(s, mode), K = s->scan_nchunks, J = s->J;
+  int per_super = 0, nsuper = 0;
+  cel::middle_split(K, &per_super, &nsuper);
+  CEL_CUDA_TRY(s, s->maps[mode].reserve(dbytes((size_t)K * nb * J)));
+  CEL_CUDA_TRY(s, s->pmaps[mode].reserve(dbytes((size_t)K * nb * J)));
+  CEL_CUDA_TRY(s, s->smaps[mode].reserve(dbytes((size_t)nsuper * nb * J)));
+  CEL_CUDA_TRY(s, s->tmaps[mode].reserve(dbytes((size_t)nb * J)));
   cel::ScanArgs a = base_args(s, Nloc, mode);
   a.nrhs = 0; a.nbasis = nb;
   a.in = nullptr; a.out = nullptr; a.init = nullptr;
   a.carry = s->maps[mode].d();
   CEL_CUDA_TRY(s, cel::launch_chunk_sweep(a, s->stream));
-  s->launches += 1;
+  CEL_CUDA_TRY(s, cel::launch_middle_maps(J, nb, mode == 1, mode == 2, K, s->maps[mode].d(), s->pmaps[mode].d(),
+                                          s->smaps[mode].d(), s->tmaps[mode].d(), s->stream));
+  s->launches += 3;
   s->maps_valid[mode] = true;
   return CEL_OK;
 }
 
 // One sweep (mode) over the local span.
-//   d_total  != NULL : stop after the composition and write the span's map (summary);
+//   d_total  != NULL : stop after the middle stage and write the span's offset and map (summary);
 //   otherwise        : carry_in (may be NULL = zero) -> d_out.
-// reuse_vecs: pass 1 of the same (mode, input) was just done by a summary call.
+// reuse_vecs: pass 1 and the walk of the same (mode, input) were just done by a summary call.
 int scan_sweep(cel_solver* s, int mode, int nrhs, const double* d_in, const double* d_carry_in, double* d_out,
                double* d_total, bool reuse_vecs) {
   const int Nloc = s->N - s->n_off, J = s->J;
   if (s->scan_nchunks == 0) plan_chunks(s, Nloc);
-  const int K = s->scan_nchunks, nb = nbasis_of(s, mode), ncols = nrhs + nb;
-  const int nsuper = cel::middle_nsuper(K);
+  const int K = s->scan_nchunks, nb = nbasis_of(s, mode);
+  int per_super = 0, nsuper = 0;
+  cel::middle_split(K, &per_super, &nsuper);
   int rc = ensure_maps(s, Nloc, mode);
   if (rc != CEL_OK) return rc;
   CEL_CUDA_TRY(s, s->scan_vecs.reserve(dbytes((size_t)K * nrhs * J)));
-  CEL_CUDA_TRY(s, s->scan_rec.reserve(dbytes((size_t)K * ncols * J)));
-  CEL_CUDA_TRY(s, s->scan_srec.reserve(dbytes((size_t)nsuper * ncols * J)));
+  CEL_CUDA_TRY(s, s->scan_h.reserve(dbytes((size_t)K * nrhs * J)));
+  CEL_CUDA_TRY(s, s->scan_cs.reserve(dbytes((size_t)nsuper * nrhs * J)));
   CEL_CUDA_TRY(s, s->scan_sg.reserve(dbytes((size_t)nsuper * nrhs * J)));
-  CEL_CUDA_TRY(s, s->scan_gin.reserve(dbytes((size_t)K * nrhs * J)));
   cudaStream_t st = s->stream;
+  const int diag = (mode == 1), reverse = (mode == 2);
   if (!reuse_vecs) {
     // pass 1: offsets c of every chunk (zero incoming carry)
     cel::ScanArgs a = base_args(s, Nloc, mode);
     a.nrhs = nrhs; a.nbasis = 0; a.in = d_in; a.out = nullptr; a.init = nullptr;
     a.carry = s->scan_vecs.d();
     CEL_CUDA_TRY(s, cel::launch_chunk_sweep(a, st));
-    CEL_CUDA_TRY(s, cel::launch_pack_records(K, J, nrhs, nb, s->scan_vecs.d(), s->maps[mode].d(), s->scan_rec.d(), st));
-    s->launches += 2;
+    s->launches += 1;
   }
-  const int diag = (mode == 1), reverse = (mode == 2);
-  if (d_total) {
-    CEL_CUDA_TRY(s, cel::launch_middle(J, nrhs, nb, diag, reverse, K, s->scan_rec.d(), s->scan_srec.d(),
-                                       s->scan_sg.d(), nullptr, s->scan_gin.d(), d_total, 1, 0, st));
-    s->launches += 2;
-    return CEL_OK;
-  }
-  CEL_CUDA_TRY(s, cel::launch_middle(J, nrhs, nb, diag, reverse, K, s->scan_rec.d(), s->scan_srec.d(),
-                                     s->scan_sg.d(), d_carry_in, s->scan_gin.d(), nullptr, 0, reuse_vecs ? 1 : 0, st));
-  s->launches += reuse_vecs ? 2 : 3;
-  // pass 2: every chunk from its true carry
+  // middle: walk (unless a summary call already did it) and scan
+  CEL_CUDA_TRY(s, cel::launch_middle(J, nrhs, nb, diag, reverse, K, s->maps[mode].d(), s->scan_vecs.d(),
+                                     s->smaps[mode].d(), s->tmaps[mode].d(), s->scan_h.d(), s->scan_cs.d(),
+                                     d_total ? nullptr : d_carry_in, s->scan_sg.d(), d_total, reuse_vecs ? 0 : 1, 1,
+                                     st));
+  s->launches += reuse_vecs ? 1 : 2;
+  if (d_total) return CEL_OK;
+  // pass 2: every chunk from its true carry  h_i + P_i g_s
   cel::ScanArgs a = base_args(s, Nloc, mode);
-  a.nrhs = nrhs; a.nbasis = 0; a.in = d_in; a.out = d_out; a.init = s->scan_gin.d(); a.carry = nullptr;
+  a.nrhs = nrhs; a.nbasis = 0; a.in = d_in; a.out = d_out; a.init = s->scan_h.d(); a.carry = nullptr;
+  a.pmap = s->pmaps[mode].d(); a.sg = s->scan_sg.d(); a.per_super = per_super; a.walk_reverse = reverse;
   CEL_CUDA_TRY(s, cel::launch_chunk_sweep(a, st));
   s->launches += 1;
   return CEL_OK;

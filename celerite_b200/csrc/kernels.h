@@ -131,14 +131,20 @@ struct ScanArgs {
   double* carry;        // [nchunks][ncols][J] outgoing carries or NULL
   int mode;
   int diag_basis;       // the single basis column is the all-ones carry (diagonal maps: dot_L)
+  // pass 2 of a sweep: the carry entering chunk i is init[i] + pmap[i] * sg[super-chunk of i]
+  const double* pmap;   // [nchunks][J][J] (or [nchunks][J] when diag_basis) or NULL
+  const double* sg;     // [nsuper][ncols][J]
+  int per_super;        // chunks per super-chunk, counted in walk order
+  int walk_reverse;     // the walk runs from the last chunk to the first (backward sweep)
 };
 cudaError_t launch_chunk_sweep(const ScanArgs& a, cudaStream_t stream);
-cudaError_t launch_pack_records(int nchunks, int J, int nrhs, int nbasis, const double* vecs, const double* maps,
-                                double* rec, cudaStream_t stream);
-cudaError_t launch_middle(int J, int nrhs, int nbasis, int diag, int reverse, int nunits, const double* rec,
-                          double* srec, double* sg, const double* g0, double* gin, double* total,
-                          int compose_only, int skip_compose, cudaStream_t stream);
-int middle_nsuper(int nunits);
+cudaError_t launch_middle_maps(int J, int nbasis, int diag, int reverse, int nunits, const double* maps,
+                               double* pmaps, double* smaps, double* tmap, cudaStream_t stream);
+cudaError_t launch_middle(int J, int nrhs, int nbasis, int diag, int reverse, int nunits, const double* maps,
+                          const double* vecs, const double* smaps, const double* tmap, double* h, double* cs,
+                          const double* g0, double* sg, double* total, int do_walk, int do_scan,
+                          cudaStream_t stream);
+void middle_split(int nunits, int* per_super, int* nsuper);
 
 // predict (cholesky.h:599-698): merge sweeps over data times t[N] and sorted test points xs[M]
 struct PredictArgs {

@@ -70,6 +70,23 @@ __device__ __forceinline__ void copy_flat(double* dst, const double* src, int n,
   }
 }
 
+// carry entering chunk `chunk` in pass 2 (row kk of column col): h_i + P_i g_s, see "middle" below
+__device__ __forceinline__ double start_carry(const ScanArgs& a, int chunk, int col, int kk) {
+  const int J = a.J, ncols = a.nrhs + a.nbasis;
+  double f = a.init[((size_t)chunk * ncols + col) * J + kk];
+  if (a.pmap) {
+    const int q = a.walk_reverse ? a.nchunks - 1 - chunk : chunk;
+    const double* g = a.sg + ((size_t)(q / a.per_super) * ncols + col) * J;
+    if (a.diag_basis) {
+      f = fma(a.pmap[(size_t)chunk * J + kk], g[kk], f);
+    } else {
+      const double* P = a.pmap + (size_t)chunk * J * J;
+      for (int j = 0; j < J; ++j) f = fma(P[j * J + kk], g[j], f);
+    }
+  }
+  return f;
+}
+
 // MODE 0: forward half of solve (writes x / D);  MODE 1: dot_L
 template <int L, int MODE>
 __global__ void __launch_bounds__(kWarp) k_chunk_forward(ScanArgs a) {
@@ -97,7 +114,7 @@ __global__ void __launch_bounds__(kWarp) k_chunk_forward(ScanArgs a) {
   double* base = sm + g * SM::GROUP;
 
   double f;
-  if (a.init) f = row_ok ? a.init[((size_t)chunk * ncols + col) * J + kk] : 0.0;
+  if (a.init) f = row_ok ? start_carry(a, chunk, col, kk) : 0.0;
   else if (is_rhs) f = 0.0;
   else f = (row_ok && (a.diag_basis || kk == col - a.nrhs)) ? 1.0 : 0.0;
 
@@ -203,7 +220,7 @@ __global__ void __launch_bounds__(kWarp) k_chunk_backward(ScanArgs a) {
   double* base = sm + g * SM::GROUP;
 
   double f;  // F_n of the step about to be processed
-  if (a.init) f = row_ok ? a.init[((size_t)chunk * ncols + col) * J + kk] : 0.0;
+  if (a.init) f = row_ok ? start_carry(a, chunk, col, kk) : 0.0;
   else if (is_rhs) f = 0.0;
   else f = (row_ok && kk == col - a.nrhs) ? 1.0 : 0.0;
 
@@ -269,66 +286,78 @@ __global__ void __launch_bounds__(kWarp) k_chunk_backward(ScanArgs a) {
 }
 
 // --------------------------------------------------------------------------------------------
-// middle: compose / scan / distribute the chunk maps.  Records are [unit][col][J] with
-// col < nrhs the affine offsets c and col >= nrhs the columns of M (one column = all-ones image
-// when diag).  `reverse` walks the units from the last to the first (backward sweep).
-// One warp per super-chunk; lane k = row k (J <= 32).
+// middle: from the chunk maps to the carry entering every chunk.
+//
+// Chunks are grouped into ~sqrt(K) super-chunks (in WALK order: the backward sweep walks the
+// chunks from the last to the first).  Everything that depends on the factor only is computed
+// once per factor and cached in the handle:
+//     P_i   the map from the start of chunk i's super-chunk to the start of chunk i,
+//     M_s   the map of super-chunk s,  and the map of the whole span.
+// A sweep then needs two short serial walks of J-vectors (no matrix products):
+//     walk   per super-chunk (parallel): h_i = carry entering chunk i when the super-chunk starts
+//            from zero; its final value is the super-chunk's offset c_s
+//     scan   over the super-chunks (serial): carry g_s entering super-chunk s
+// and pass 2 starts chunk i from  h_i + P_i g_s  (evaluated inside the chunk kernel).
+// Records are [unit][col][J], column-major (entry (row k, column j) at [j*J + k]); diagonal maps
+// (dot_L) keep one column.  One warp per walk; lane k = row k (J <= 32).
 // --------------------------------------------------------------------------------------------
 struct MidArgs {
   int J, nrhs, nbasis, diag, reverse;
   int nunits, per_super, nsuper;
-  const double* rec;      // [nunits][ncols][J]  chunk maps
-  double* srec;           // [nsuper][ncols][J]  super-chunk maps (out of compose)
-  const double* g0;       // [nrhs][J] carry entering the first unit of the walk (or NULL = 0)
-  double* sg;             // [nsuper][nrhs][J] carries entering each super-chunk
-  double* gin;            // [nunits][ncols][J] carries entering each chunk (rhs columns only)
-  double* total;          // [ncols][J] composition of all super-chunks (optional)
+  const double* maps;     // [nunits][nbasis][J] chunk maps
+  const double* vecs;     // [nunits][nrhs][J]   chunk offsets (pass 1)
+  double* pmaps;          // [nunits][nbasis][J] P_i
+  double* smaps;          // [nsuper][nbasis][J] M_s
+  double* tmap;           // [nbasis][J]         map of the whole span
+  double* h;              // [nunits][nrhs][J]
+  double* cs;             // [nsuper][nrhs][J]
+  const double* g0;       // [nrhs][J] carry entering the span (or NULL = 0)
+  double* sg;             // [nsuper][nrhs][J]
+  double* total;          // [nrhs + nbasis][J]  offset and map of the whole span (optional)
 };
 
 constexpr int kMidMaxJ = 32;
 
-// The three middle kernels walk a sequence of records; records are copied into a 4-deep shared
-// memory ring with cp.async three steps ahead of their use (the walk is a chain of dependent
-// small matrix products, so a global-load latency per step would dominate it), and all loops over
-// J are unrolled at compile time (JT = J rounded up; rows/columns >= J are predicated off).
-constexpr int kRing = 4;
+// Records are copied into a shared-memory ring with cp.async several steps ahead of their use:
+// a walk is a chain of small dependent products, so a global-load latency per step would
+// dominate it.  A record has a map part (lenM doubles from srcM) and an offset part (lenC doubles
+// from srcC); either may be empty.
+constexpr int kRing = 8;
 struct RecStream {
-  const double* src;    // records, `len` doubles each
-  double* buf;          // [kRing][len] in shared memory
-  int len, first, count, nwalk, reverse;
+  const double* srcM;
+  const double* srcC;
+  double* buf;          // [kRing][lenM + lenC] in shared memory
+  int lenM, lenC, first, count, nwalk, reverse;
   __device__ __forceinline__ int unit(int q) const { return reverse ? nwalk - 1 - q : q; }
   __device__ __forceinline__ void fetch(int q, int lane) const {
     if (q < first + count) {
-      const double* s = src + (size_t)unit(q) * len;
-      double* d = buf + ((q - first) % kRing) * len;
-      for (int e = lane; e < len; e += kWarp) cp_async_8(d + e, s + e);
+      const int un = unit(q);
+      double* d = buf + ((q - first) % kRing) * (lenM + lenC);
+      const double* sM = srcM + (size_t)un * lenM;
+      for (int e = lane; e < lenM; e += kWarp) cp_async_8(d + e, sM + e);
+      const double* sC = srcC + (size_t)un * lenC;
+      for (int e = lane; e < lenC; e += kWarp) cp_async_8(d + lenM + e, sC + e);
     }
     cp_async_commit_group();
   }
   __device__ __forceinline__ void prime(int lane) const {
     for (int i = 0; i < kRing - 1; ++i) fetch(first + i, lane);
   }
-  // record of step q; also starts the fetch of step q + kRing - 1
+  // record of step q (map part first); also starts the fetch of step q + kRing - 1
   __device__ __forceinline__ const double* get(int q, int lane) const {
     fetch(q + kRing - 1, lane);
     cp_async_wait_group<kRing - 1>();
     __syncwarp();
-    return buf + ((q - first) % kRing) * len;
+    return buf + ((q - first) % kRing) * (lenM + lenC);
   }
 };
 
-// compose the running map (Mr[i][k] column i, cr[r][k]; shared memory) with one unit's map
+// running map (Mr[i][k] = column i, shared memory) <- (unit's map) o (running map)
 template <int JT>
-__device__ __forceinline__ void mid_compose(const MidArgs& m, const double* unit_rec, double* Mr, double* cr,
-                                            double* Mn, int k, bool row_ok) {
-  const int J = m.J, nrhs = m.nrhs;
-  const double* Mc = unit_rec + (size_t)nrhs * J;   // columns of the unit's M (or its diagonal)
-  if (m.diag) {
-    if (row_ok) {
-      const double d = Mc[k];
-      Mr[k] *= d;
-      for (int r = 0; r < nrhs; ++r) cr[r * J + k] = fma(d, cr[r * J + k], unit_rec[r * J + k]);
-    }
+__device__ __forceinline__ void mid_compose(int J, int diag, const double* Mc, double* Mr, double* Mn, int k,
+                                            bool row_ok) {
+  if (diag) {
+    if (row_ok) Mr[k] *= Mc[k];
     __syncwarp();
     return;
   }
@@ -342,144 +371,154 @@ __device__ __forceinline__ void mid_compose(const MidArgs& m, const double* unit
       for (int j = 0; j < JT; ++j) acc = fma(row[j], (j < J) ? Mr[i * J + j] : 0.0, acc);
       Mn[i * J + k] = acc;
     }
-    for (int r = 0; r < nrhs; ++r) {
-      double acc = unit_rec[r * J + k];
-#pragma unroll
-      for (int j = 0; j < JT; ++j) acc = fma(row[j], (j < J) ? cr[r * J + j] : 0.0, acc);
-      Mn[(J + r) * J + k] = acc;
-    }
   }
   __syncwarp();
-  if (row_ok) {
+  if (row_ok)
     for (int i = 0; i < J; ++i) Mr[i * J + k] = Mn[i * J + k];
-    for (int r = 0; r < nrhs; ++r) cr[r * J + k] = Mn[(J + r) * J + k];
-  }
   __syncwarp();
 }
 
-// apply one unit's map to carries g[r][k] held in shared memory
+// once per factor.  level 0: block s walks super-chunk s, stores P_i in front of every chunk and
+// M_s at the end;  level 1: one block composes the M_s into the map of the whole span.
 template <int JT>
-__device__ __forceinline__ void mid_apply(const MidArgs& m, const double* unit_rec, double* gs, double* gn, int k,
-                                          bool row_ok) {
-  const int J = m.J, nrhs = m.nrhs;
-  const double* Mc = unit_rec + (size_t)nrhs * J;
-  if (m.diag) {
-    if (row_ok)
-      for (int r = 0; r < nrhs; ++r) gs[r * J + k] = fma(Mc[k], gs[r * J + k], unit_rec[r * J + k]);
-    __syncwarp();
-    return;
-  }
-  double row[JT];
-#pragma unroll
-  for (int j = 0; j < JT; ++j) row[j] = (row_ok && j < J) ? Mc[j * J + k] : 0.0;
-  if (row_ok) {
-    for (int r = 0; r < nrhs; ++r) {
-      double acc = unit_rec[r * J + k];
-#pragma unroll
-      for (int j = 0; j < JT; ++j) acc = fma(row[j], (j < J) ? gs[r * J + j] : 0.0, acc);
-      gn[r * J + k] = acc;
-    }
-  }
-  __syncwarp();
-  if (row_ok) for (int r = 0; r < nrhs; ++r) gs[r * J + k] = gn[r * J + k];
-  __syncwarp();
-}
-
-template <int JT>
-__global__ void __launch_bounds__(kWarp) k_mid_compose(MidArgs m, int level_total) {
-  // level_total == 0: block b composes the chunks of super-chunk b into srec[b]
-  // level_total == 1: one block composes all super-chunk maps (srec) into total
+__global__ void __launch_bounds__(kWarp) k_mid_prefix(MidArgs m, int level) {
   extern __shared__ double sm[];
-  const int J = m.J, ncols = m.nrhs + m.nbasis, k = threadIdx.x, len = ncols * J;
+  const int J = m.J, nb = m.nbasis, k = threadIdx.x, len = nb * J;
   const bool row_ok = k < J;
   double* Mr = sm;                          // J*J (or J when diag)
-  double* cr = Mr + J * J;                  // nrhs*J
-  double* Mn = cr + m.nrhs * J;             // (J+nrhs)*J scratch
-  double* rb = Mn + (J + m.nrhs) * J;       // [kRing][len] record ring
+  double* Mn = Mr + J * J;
+  double* rb = Mn + J * J;                  // [kRing][len]
   for (int i = k; i < J * J; i += kWarp) Mr[i] = m.diag ? 1.0 : ((i / J) == (i % J) ? 1.0 : 0.0);
-  for (int i = k; i < m.nrhs * J; i += kWarp) cr[i] = 0.0;
   RecStream rs;
-  rs.buf = rb; rs.len = len;
-  if (level_total == 0) {
+  rs.buf = rb; rs.lenM = len; rs.lenC = 0; rs.srcC = nullptr;
+  if (level == 0) {
     rs.first = blockIdx.x * m.per_super; rs.count = min(m.per_super, m.nunits - rs.first);
-    rs.src = m.rec; rs.nwalk = m.nunits; rs.reverse = m.reverse;
-  } else {  // super-chunk records are indexed by position in the walk already
-    rs.first = 0; rs.count = m.nsuper; rs.src = m.srec; rs.nwalk = m.nsuper; rs.reverse = 0;
+    rs.srcM = m.maps; rs.nwalk = m.nunits; rs.reverse = m.reverse;
+  } else {  // super-chunk maps are stored in walk order already
+    rs.first = 0; rs.count = m.nsuper; rs.srcM = m.smaps; rs.nwalk = m.nsuper; rs.reverse = 0;
   }
   rs.prime(k);
   __syncwarp();
   for (int q = rs.first; q < rs.first + rs.count; ++q) {
     const double* rec = rs.get(q, k);
-    mid_compose<JT>(m, rec, Mr, cr, Mn, k, row_ok);
+    if (level == 0 && row_ok) {
+      double* dst = m.pmaps + (size_t)rs.unit(q) * len;
+      for (int i = 0; i < nb; ++i) dst[i * J + k] = Mr[i * J + k];
+    }
+    mid_compose<JT>(J, m.diag, rec, Mr, Mn, k, row_ok);
   }
-  double* dst = (level_total == 0) ? m.srec + (size_t)blockIdx.x * len : m.total;
-  if (row_ok) {
-    for (int r = 0; r < m.nrhs; ++r) dst[r * J + k] = cr[r * J + k];
-    if (m.diag) dst[m.nrhs * J + k] = Mr[k];
-    else for (int i = 0; i < J; ++i) dst[(m.nrhs + i) * J + k] = Mr[i * J + k];
-  }
+  double* dst = (level == 0) ? m.smaps + (size_t)blockIdx.x * len : m.tmap;
+  if (row_ok)
+    for (int i = 0; i < nb; ++i) dst[i * J + k] = Mr[i * J + k];
 }
 
+// g <- M g + c along `count` records; the carry BEFORE each record goes to before[unit], the
+// final one to final_out.  g lives in shared memory, double-buffered: one warp barrier per step.
+template <int JT>
+__device__ __forceinline__ void affine_walk(const MidArgs& m, const RecStream& rs, double* gs, const double* g_init,
+                                            double* before, double* final_out, int k, bool row_ok) {
+  const int J = m.J, nrhs = m.nrhs, lenM = rs.lenM;
+  for (int i = k; i < nrhs * J; i += kWarp) gs[i] = g_init ? g_init[i] : 0.0;
+  rs.prime(k);
+  __syncwarp();
+  int p = 0;
+  for (int q = rs.first; q < rs.first + rs.count; ++q) {
+    const double* rec = rs.get(q, k);
+    const double* cur = gs + p * nrhs * J;
+    double* nxt = gs + (p ^ 1) * nrhs * J;
+    double* bdst = before + (size_t)rs.unit(q) * nrhs * J;
+    if (m.diag) {
+      if (row_ok)
+        for (int r = 0; r < nrhs; ++r) {
+          const double g = cur[r * J + k];
+          bdst[r * J + k] = g;
+          nxt[r * J + k] = fma(rec[k], g, rec[lenM + r * J + k]);
+        }
+    } else {
+      double row[JT];
+#pragma unroll
+      for (int j = 0; j < JT; ++j) row[j] = (row_ok && j < J) ? rec[j * J + k] : 0.0;
+      if (row_ok)
+        for (int r = 0; r < nrhs; ++r) {
+          double acc0 = rec[lenM + r * J + k], acc1 = 0.0;
+#pragma unroll
+          for (int j = 0; j < JT; j += 2) {
+            acc0 = fma(row[j], (j < J) ? cur[r * J + j] : 0.0, acc0);
+            if (j + 1 < JT) acc1 = fma(row[j + 1], (j + 1 < J) ? cur[r * J + j + 1] : 0.0, acc1);
+          }
+          bdst[r * J + k] = cur[r * J + k];
+          nxt[r * J + k] = acc0 + acc1;
+        }
+    }
+    __syncwarp();
+    p ^= 1;
+  }
+  if (final_out && row_ok)
+    for (int r = 0; r < nrhs; ++r) final_out[r * J + k] = gs[p * nrhs * J + r * J + k];
+}
+
+// per sweep, block s: walk super-chunk s from a zero carry -> h_i of its chunks, c_s
+template <int JT>
+__global__ void __launch_bounds__(kWarp) k_mid_walk(MidArgs m) {
+  extern __shared__ double sm[];
+  const int k = threadIdx.x;
+  RecStream rs;
+  rs.buf = sm + 2 * m.nrhs * m.J;
+  rs.lenM = m.nbasis * m.J; rs.lenC = m.nrhs * m.J;
+  rs.srcM = m.maps; rs.srcC = m.vecs;
+  rs.first = blockIdx.x * m.per_super; rs.count = min(m.per_super, m.nunits - rs.first);
+  rs.nwalk = m.nunits; rs.reverse = m.reverse;
+  affine_walk<JT>(m, rs, sm, nullptr, m.h, m.cs + (size_t)blockIdx.x * m.nrhs * m.J, k, k < m.J);
+}
+
+// per sweep, one block: carries entering the super-chunks; optionally the span's offset and map
 template <int JT>
 __global__ void __launch_bounds__(kWarp) k_mid_scan(MidArgs m) {
-  // serial over the super-chunk maps: carry entering each super-chunk (walk order)
   extern __shared__ double sm[];
-  const int J = m.J, ncols = m.nrhs + m.nbasis, k = threadIdx.x, len = ncols * J;
-  const bool row_ok = k < J;
-  double* gs = sm;
-  double* gn = gs + m.nrhs * J;
-  double* rb = gn + m.nrhs * J;
-  for (int i = k; i < m.nrhs * J; i += kWarp) gs[i] = m.g0 ? m.g0[i] : 0.0;
+  const int k = threadIdx.x;
   RecStream rs;
-  rs.buf = rb; rs.len = len; rs.first = 0; rs.count = m.nsuper; rs.src = m.srec; rs.nwalk = m.nsuper; rs.reverse = 0;
-  rs.prime(k);
-  __syncwarp();
-  for (int q = 0; q < m.nsuper; ++q) {
-    const double* rec = rs.get(q, k);
-    if (row_ok) for (int r = 0; r < m.nrhs; ++r) m.sg[((size_t)q * m.nrhs + r) * J + k] = gs[r * J + k];
-    mid_apply<JT>(m, rec, gs, gn, k, row_ok);
-  }
+  rs.buf = sm + 2 * m.nrhs * m.J;
+  rs.lenM = m.nbasis * m.J; rs.lenC = m.nrhs * m.J;
+  rs.srcM = m.smaps; rs.srcC = m.cs;
+  rs.first = 0; rs.count = m.nsuper; rs.nwalk = m.nsuper; rs.reverse = 0;
+  affine_walk<JT>(m, rs, sm, m.g0, m.sg, m.total, k, k < m.J);
+  if (m.total)
+    for (int i = k; i < m.nbasis * m.J; i += kWarp) m.total[m.nrhs * m.J + i] = m.tmap[i];
+}
+
+inline void split_units(MidArgs& m) {
+  int ps = 1;
+  while ((long long)ps * ps < m.nunits) ++ps;
+  m.per_super = ps;
+  m.nsuper = (m.nunits + ps - 1) / ps;
+}
+
+template <typename K>
+inline cudaError_t opt_in_smem(K kern, size_t smem) {
+  if (smem <= 48 * 1024) return cudaSuccess;
+  return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 }
 
 template <int JT>
-__global__ void __launch_bounds__(kWarp) k_mid_distribute(MidArgs m) {
-  // block b walks super-chunk b (walk order) and hands every chunk its incoming carry
-  extern __shared__ double sm[];
-  const int J = m.J, ncols = m.nrhs + m.nbasis, k = threadIdx.x, len = ncols * J;
-  const bool row_ok = k < J;
-  double* gs = sm;
-  double* gn = gs + m.nrhs * J;
-  double* rb = gn + m.nrhs * J;
-  for (int i = k; i < m.nrhs * J; i += kWarp) gs[i] = m.sg[(size_t)blockIdx.x * m.nrhs * J + i];
-  RecStream rs;
-  rs.buf = rb; rs.len = len; rs.first = blockIdx.x * m.per_super; rs.count = min(m.per_super, m.nunits - rs.first);
-  rs.src = m.rec; rs.nwalk = m.nunits; rs.reverse = m.reverse;
-  rs.prime(k);
-  __syncwarp();
-  for (int q = rs.first; q < rs.first + rs.count; ++q) {
-    const double* rec = rs.get(q, k);
-    const int unit = rs.unit(q);
-    if (row_ok) for (int r = 0; r < m.nrhs; ++r) m.gin[((size_t)unit * m.nrhs + r) * J + k] = gs[r * J + k];
-    mid_apply<JT>(m, rec, gs, gn, k, row_ok);
-  }
+cudaError_t launch_prefix(const MidArgs& m, cudaStream_t stream) {
+  const size_t smem = (size_t)(2 * m.J * m.J + kRing * m.nbasis * m.J) * sizeof(double);
+  cudaError_t e = opt_in_smem(k_mid_prefix<JT>, smem);
+  if (e != cudaSuccess) return e;
+  k_mid_prefix<JT><<<m.nsuper, kWarp, smem, stream>>>(m, 0);
+  k_mid_prefix<JT><<<1, kWarp, smem, stream>>>(m, 1);
+  return cudaGetLastError();
 }
 
 template <int JT>
-void launch_mid(const MidArgs& m, size_t smem, size_t smem2, bool with_total, int compose_only, int skip_compose,
-                cudaStream_t stream) {
-  if (smem > 48 * 1024) {   // wide kernels with several right-hand sides: opt in to large shared memory
-    cudaFuncSetAttribute(k_mid_compose<JT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    cudaFuncSetAttribute(k_mid_scan<JT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
-    cudaFuncSetAttribute(k_mid_distribute<JT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
-  }
-  if (!skip_compose) {
-    k_mid_compose<JT><<<m.nsuper, kWarp, smem, stream>>>(m, 0);
-    if (with_total) k_mid_compose<JT><<<1, kWarp, smem, stream>>>(m, 1);
-  }
-  if (!compose_only) {
-    k_mid_scan<JT><<<1, kWarp, smem2, stream>>>(m);
-    k_mid_distribute<JT><<<m.nsuper, kWarp, smem2, stream>>>(m);
-  }
+cudaError_t launch_walks(const MidArgs& m, bool walk, bool scan, cudaStream_t stream) {
+  const size_t smem = (size_t)(2 * m.nrhs * m.J + kRing * (m.nbasis + m.nrhs) * m.J) * sizeof(double);
+  if (smem > 200 * 1024) return cudaErrorInvalidValue;   // too many right-hand sides for one middle pass
+  cudaError_t e = opt_in_smem(k_mid_walk<JT>, smem);
+  if (e == cudaSuccess) e = opt_in_smem(k_mid_scan<JT>, smem);
+  if (e != cudaSuccess) return e;
+  if (walk) k_mid_walk<JT><<<m.nsuper, kWarp, smem, stream>>>(m);
+  if (scan) k_mid_scan<JT><<<1, kWarp, smem, stream>>>(m);
+  return cudaGetLastError();
 }
 
 }  // namespace
@@ -511,64 +550,56 @@ cudaError_t launch_chunk_sweep(const ScanArgs& a, cudaStream_t stream) {
   return cudaGetLastError();
 }
 
-// Merge the basis columns of `maps` ([nchunks][nbasis][J]) and the offsets of `vecs`
-// ([nchunks][nrhs][J]) into one record array [nchunks][nrhs+nbasis][J].
-__global__ void k_pack_records(int nchunks, int J, int nrhs, int nbasis, const double* vecs, const double* maps,
-                               double* rec) {
-  const int ncols = nrhs + nbasis;
-  const long long total = (long long)nchunks * ncols * J;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int k = (int)(i % J);
-    const long long cc = i / J;
-    const int col = (int)(cc % ncols), chunk = (int)(cc / ncols);
-    rec[i] = (col < nrhs) ? vecs[((size_t)chunk * nrhs + col) * J + k]
-                          : maps[((size_t)chunk * nbasis + (col - nrhs)) * J + k];
-  }
-}
+#define CEL_DISPATCH_JT(J, CALL)       \
+  do {                                 \
+    if ((J) <= 2) { CALL(2); }         \
+    else if ((J) <= 4) { CALL(4); }    \
+    else if ((J) <= 8) { CALL(8); }    \
+    else if ((J) <= 16) { CALL(16); }  \
+    else { CALL(32); }                 \
+  } while (0)
 
-cudaError_t launch_pack_records(int nchunks, int J, int nrhs, int nbasis, const double* vecs, const double* maps,
-                                double* rec, cudaStream_t stream) {
-  const long long total = (long long)nchunks * (nrhs + nbasis) * J;
-  if (total == 0) return cudaSuccess;
-  const int threads = 256;
-  const long long want = (total + threads - 1) / threads;
-  const unsigned grid = (unsigned)(want < 148 * 8 ? want : 148 * 8);
-  k_pack_records<<<grid, threads, 0, stream>>>(nchunks, J, nrhs, nbasis, vecs, maps, rec);
-  return cudaGetLastError();
-}
-
-// middle stage driver.  Buffers: rec [nunits][ncols][J] in; srec [nsuper][ncols][J], sg
-// [nsuper][nrhs][J] scratch; gin [nunits][nrhs][J] out; total [ncols][J] out (optional);
-// g0 [nrhs][J] in (optional).  Set compose_only to stop after the total map (multi-GPU summary).
-cudaError_t launch_middle(int J, int nrhs, int nbasis, int diag, int reverse, int nunits, const double* rec,
-                          double* srec, double* sg, const double* g0, double* gin, double* total,
-                          int compose_only, int skip_compose, cudaStream_t stream) {
+// once per factor and direction: maps [nunits][nbasis][J] -> pmaps (same shape), smaps
+// [nsuper][nbasis][J], tmap [nbasis][J]
+cudaError_t launch_middle_maps(int J, int nbasis, int diag, int reverse, int nunits, const double* maps,
+                               double* pmaps, double* smaps, double* tmap, cudaStream_t stream) {
   if (J > kMidMaxJ || J < 1) return cudaErrorInvalidValue;
   MidArgs m{};
-  m.J = J; m.nrhs = nrhs; m.nbasis = nbasis; m.diag = diag; m.reverse = reverse;
-  m.nunits = nunits;
-  int ps = 1;
-  while ((long long)ps * ps < nunits) ++ps;
-  m.per_super = ps;
-  m.nsuper = (nunits + ps - 1) / ps;
-  m.rec = rec; m.srec = srec; m.g0 = g0; m.sg = sg; m.gin = gin; m.total = total;
-  const size_t ring = (size_t)kRing * (nrhs + nbasis) * J;
-  const size_t smem = (size_t)(J * J + nrhs * J + (J + nrhs) * J + ring) * sizeof(double);
-  const size_t smem2 = (size_t)(2 * nrhs * J + ring) * sizeof(double);
-  if (smem > 200 * 1024) return cudaErrorInvalidValue;   // too many right-hand sides for one middle pass
-  const bool wt = total != nullptr;
-  if (J <= 2) launch_mid<2>(m, smem, smem2, wt, compose_only, skip_compose, stream);
-  else if (J <= 4) launch_mid<4>(m, smem, smem2, wt, compose_only, skip_compose, stream);
-  else if (J <= 8) launch_mid<8>(m, smem, smem2, wt, compose_only, skip_compose, stream);
-  else if (J <= 16) launch_mid<16>(m, smem, smem2, wt, compose_only, skip_compose, stream);
-  else launch_mid<32>(m, smem, smem2, wt, compose_only, skip_compose, stream);
-  return cudaGetLastError();
+  m.J = J; m.nrhs = 0; m.nbasis = nbasis; m.diag = diag; m.reverse = reverse; m.nunits = nunits;
+  split_units(m);
+  m.maps = maps; m.pmaps = pmaps; m.smaps = smaps; m.tmap = tmap;
+  cudaError_t e = cudaSuccess;
+#define CALL(JT) e = launch_prefix<JT>(m, stream)
+  CEL_DISPATCH_JT(J, CALL);
+#undef CALL
+  return e;
 }
 
-int middle_nsuper(int nunits) {
-  int ps = 1;
-  while ((long long)ps * ps < nunits) ++ps;
-  return (nunits + ps - 1) / ps;
+// per sweep.  walk: vecs [nunits][nrhs][J] -> h (same shape), cs [nsuper][nrhs][J];
+// scan: g0 [nrhs][J] (optional) -> sg [nsuper][nrhs][J], total [nrhs+nbasis][J] (optional).
+cudaError_t launch_middle(int J, int nrhs, int nbasis, int diag, int reverse, int nunits, const double* maps,
+                          const double* vecs, const double* smaps, const double* tmap, double* h, double* cs,
+                          const double* g0, double* sg, double* total, int do_walk, int do_scan,
+                          cudaStream_t stream) {
+  if (J > kMidMaxJ || J < 1) return cudaErrorInvalidValue;
+  MidArgs m{};
+  m.J = J; m.nrhs = nrhs; m.nbasis = nbasis; m.diag = diag; m.reverse = reverse; m.nunits = nunits;
+  split_units(m);
+  m.maps = maps; m.vecs = vecs; m.smaps = const_cast<double*>(smaps); m.tmap = const_cast<double*>(tmap);
+  m.h = h; m.cs = cs; m.g0 = g0; m.sg = sg; m.total = total;
+  cudaError_t e = cudaSuccess;
+#define CALL(JT) e = launch_walks<JT>(m, do_walk != 0, do_scan != 0, stream)
+  CEL_DISPATCH_JT(J, CALL);
+#undef CALL
+  return e;
+}
+
+void middle_split(int nunits, int* per_super, int* nsuper) {
+  MidArgs m{};
+  m.nunits = nunits;
+  split_units(m);
+  *per_super = m.per_super;
+  *nsuper = m.nsuper;
 }
 
 }  // namespace cel

@@ -62,7 +62,8 @@ struct cel_solver {
   int scan_chunk_len = 0, scan_nchunks = 0;
   bool maps_valid[3] = {false, false, false};
   cel::DevBuf maps[3];             // [nchunks][nbasis][J] per mode
-  cel::DevBuf scan_vecs, scan_rec, scan_srec, scan_sg, scan_gin, scan_total, scan_tmp;
+  cel::DevBuf pmaps[3], smaps[3], tmaps[3];   // prefix / super-chunk / whole-span maps (scan.cu, "middle")
+  cel::DevBuf scan_vecs, scan_h, scan_cs, scan_sg, scan_total, scan_tmp;
 
   // ---- scratch ----
   cel::DevBuf in0, in1, in2, in3;  // single-series inputs / rhs
