@@ -157,6 +157,18 @@ int cel_span_apply(cel_solver* s, int op, int nrhs, const double* d_in, const do
   return scan_sweep(s, op, nrhs, d_in, d_carry_in, d_out, nullptr, reuse_summary != 0);
 }
 
+int cel_span_fold(cel_solver* s, int op, int nrhs, int world, int rank, const double* d_gathered,
+                  double* d_carry_out) {
+  int rc = check_ready(s, nrhs);
+  if (rc != CEL_OK) return rc;
+  if (op < 0 || op > 2 || !d_gathered || !d_carry_out) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "bad op or null pointer");
+  if (world < 1 || rank < 0 || rank >= world) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "rank outside [0, world)");
+  CEL_CUDA_TRY(s, cel::launch_span_fold(s->J, nrhs, nbasis_of(s, op), op == 1, op == 2, world, rank, d_gathered,
+                                        d_carry_out, s->stream));
+  s->launches += 1;
+  return CEL_OK;
+}
+
 int cel_span_dims(const cel_solver* s, int* n_local, int* J, int* nchunks, int* chunk_len) {
   if (!s) return CEL_INVALID_ARGUMENT;
   if (n_local) *n_local = s->N - s->n_off;

@@ -145,6 +145,8 @@ cudaError_t launch_middle(int J, int nrhs, int nbasis, int diag, int reverse, in
                           const double* g0, double* sg, double* total, int do_walk, int do_scan,
                           cudaStream_t stream);
 void middle_split(int nunits, int* per_super, int* nsuper);
+cudaError_t launch_span_fold(int J, int nrhs, int nbasis, int diag, int reverse, int world, int rank,
+                             const double* gathered, double* carry_out, cudaStream_t stream);
 
 // predict (cholesky.h:599-698): merge sweeps over data times t[N] and sorted test points xs[M]
 struct PredictArgs {

@@ -328,14 +328,15 @@ struct RecStream {
   const double* srcC;
   double* buf;          // [kRing][lenM + lenC] in shared memory
   int lenM, lenC, first, count, nwalk, reverse;
+  int strideM, strideC;   // doubles between consecutive units in srcM / srcC
   __device__ __forceinline__ int unit(int q) const { return reverse ? nwalk - 1 - q : q; }
   __device__ __forceinline__ void fetch(int q, int lane) const {
     if (q < first + count) {
       const int un = unit(q);
       double* d = buf + ((q - first) % kRing) * (lenM + lenC);
-      const double* sM = srcM + (size_t)un * lenM;
+      const double* sM = srcM + (size_t)un * strideM;
       for (int e = lane; e < lenM; e += kWarp) cp_async_8(d + e, sM + e);
-      const double* sC = srcC + (size_t)un * lenC;
+      const double* sC = srcC + (size_t)un * strideC;
       for (int e = lane; e < lenC; e += kWarp) cp_async_8(d + lenM + e, sC + e);
     }
     cp_async_commit_group();
@@ -390,7 +391,7 @@ __global__ void __launch_bounds__(kWarp) k_mid_prefix(MidArgs m, int level) {
   double* rb = Mn + J * J;                  // [kRing][len]
   for (int i = k; i < J * J; i += kWarp) Mr[i] = m.diag ? 1.0 : ((i / J) == (i % J) ? 1.0 : 0.0);
   RecStream rs;
-  rs.buf = rb; rs.lenM = len; rs.lenC = 0; rs.srcC = nullptr;
+  rs.buf = rb; rs.lenM = len; rs.lenC = 0; rs.srcC = nullptr; rs.strideM = len; rs.strideC = 0;
   if (level == 0) {
     rs.first = blockIdx.x * m.per_super; rs.count = min(m.per_super, m.nunits - rs.first);
     rs.srcM = m.maps; rs.nwalk = m.nunits; rs.reverse = m.reverse;
@@ -426,7 +427,7 @@ __device__ __forceinline__ void affine_walk(const MidArgs& m, const RecStream& r
     const double* rec = rs.get(q, k);
     const double* cur = gs + p * nrhs * J;
     double* nxt = gs + (p ^ 1) * nrhs * J;
-    double* bdst = before + (size_t)rs.unit(q) * nrhs * J;
+    double* bdst = before ? before + (size_t)rs.unit(q) * nrhs * J : nxt;   // no record wanted: a harmless target
     if (m.diag) {
       if (row_ok)
         for (int r = 0; r < nrhs; ++r) {
@@ -464,7 +465,7 @@ __global__ void __launch_bounds__(kWarp) k_mid_walk(MidArgs m) {
   const int k = threadIdx.x;
   RecStream rs;
   rs.buf = sm + 2 * m.nrhs * m.J;
-  rs.lenM = m.nbasis * m.J; rs.lenC = m.nrhs * m.J;
+  rs.lenM = m.nbasis * m.J; rs.lenC = m.nrhs * m.J; rs.strideM = rs.lenM; rs.strideC = rs.lenC;
   rs.srcM = m.maps; rs.srcC = m.vecs;
   rs.first = blockIdx.x * m.per_super; rs.count = min(m.per_super, m.nunits - rs.first);
   rs.nwalk = m.nunits; rs.reverse = m.reverse;
@@ -478,12 +479,28 @@ __global__ void __launch_bounds__(kWarp) k_mid_scan(MidArgs m) {
   const int k = threadIdx.x;
   RecStream rs;
   rs.buf = sm + 2 * m.nrhs * m.J;
-  rs.lenM = m.nbasis * m.J; rs.lenC = m.nrhs * m.J;
+  rs.lenM = m.nbasis * m.J; rs.lenC = m.nrhs * m.J; rs.strideM = rs.lenM; rs.strideC = rs.lenC;
   rs.srcM = m.smaps; rs.srcC = m.cs;
   rs.first = 0; rs.count = m.nsuper; rs.nwalk = m.nsuper; rs.reverse = 0;
   affine_walk<JT>(m, rs, sm, m.g0, m.sg, m.total, k, k < m.J);
   if (m.total)
     for (int i = k; i < m.nbasis * m.J; i += kWarp) m.total[m.nrhs * m.J + i] = m.tmap[i];
+}
+
+// multi-GPU: fold the gathered span summaries ([world][nrhs + nbasis][J], offsets first) of the
+// ranks this rank depends on into its incoming carry.  m.maps = gathered, m.nunits = world,
+// m.per_super = first rank of the walk (in walk order), m.nsuper = number of ranks to fold.
+template <int JT>
+__global__ void __launch_bounds__(kWarp) k_span_fold(MidArgs m) {
+  extern __shared__ double sm[];
+  const int k = threadIdx.x;
+  RecStream rs;
+  rs.buf = sm + 2 * m.nrhs * m.J;
+  rs.lenM = m.nbasis * m.J; rs.lenC = m.nrhs * m.J;
+  rs.strideM = rs.strideC = rs.lenM + rs.lenC;
+  rs.srcM = m.maps + rs.lenC; rs.srcC = m.maps;
+  rs.first = m.per_super; rs.count = m.nsuper; rs.nwalk = m.nunits; rs.reverse = m.reverse;
+  affine_walk<JT>(m, rs, sm, nullptr, nullptr, m.total, k, k < m.J);
 }
 
 inline void split_units(MidArgs& m) {
@@ -592,6 +609,27 @@ cudaError_t launch_middle(int J, int nrhs, int nbasis, int diag, int reverse, in
   CEL_DISPATCH_JT(J, CALL);
 #undef CALL
   return e;
+}
+
+cudaError_t launch_span_fold(int J, int nrhs, int nbasis, int diag, int reverse, int world, int rank,
+                             const double* gathered, double* carry_out, cudaStream_t stream) {
+  if (J > kMidMaxJ || J < 1 || rank < 0 || rank >= world) return cudaErrorInvalidValue;
+  MidArgs m{};
+  m.J = J; m.nrhs = nrhs; m.nbasis = nbasis; m.diag = diag; m.reverse = reverse; m.nunits = world;
+  m.per_super = 0;                                    // the walk starts at its first rank...
+  m.nsuper = reverse ? world - 1 - rank : rank;       // ...and stops in front of this one
+  m.maps = gathered; m.total = carry_out;
+  const size_t smem = (size_t)(2 * nrhs * J + kRing * (nbasis + nrhs) * J) * sizeof(double);
+  if (smem > 200 * 1024) return cudaErrorInvalidValue;
+  cudaError_t e = cudaSuccess;
+#define CALL(JT)                                              \
+  {                                                           \
+    e = opt_in_smem(k_span_fold<JT>, smem);                   \
+    if (e == cudaSuccess) k_span_fold<JT><<<1, kWarp, smem, stream>>>(m); \
+  }
+  CEL_DISPATCH_JT(J, CALL);
+#undef CALL
+  return e != cudaSuccess ? e : cudaGetLastError();
 }
 
 void middle_split(int nunits, int* per_super, int* nsuper) {

@@ -147,6 +147,17 @@ class LongSeries(object):
         _capi.check(rc, self._h)
         return out
 
+    def fold(self, op, gathered, nrhs, world, rank):
+        """Incoming carry of `rank` from the gathered summaries (world, nrhs + nb, J), on the device
+        (one small kernel; `fold_carries` is the same arithmetic in torch)."""
+        import torch
+        out = torch.empty((nrhs, self.J), dtype=torch.float64, device=gathered.device)
+        self._use_stream(gathered)
+        rc = self._lib.cel_span_fold(self._h, op, nrhs, world, rank, C.c_void_p(gathered.data_ptr()),
+                                     C.c_void_p(out.data_ptr()))
+        _capi.check(rc, self._h)
+        return out
+
     def launch_count(self):
         return int(self._lib.cel_launch_count(self._h))
 
@@ -178,8 +189,11 @@ class DistributedLongSeries(object):
         # concatenated along dim 0 (the form both NCCL and gloo accept), viewed per rank afterwards
         gathered = torch.empty((self.world * summ.shape[0], summ.shape[1]), dtype=summ.dtype, device=summ.device)
         self.dist.all_gather_into_tensor(gathered, summ, group=self.group)
-        gathered = gathered.view(self.world, summ.shape[0], summ.shape[1])
-        carry = fold_carries(gathered, self.rank, op, cols.shape[0], self.local.J)
+        if gathered.is_cuda:
+            carry = self.local.fold(op, gathered, cols.shape[0], self.world, self.rank)
+        else:
+            gathered = gathered.view(self.world, summ.shape[0], summ.shape[1])
+            carry = fold_carries(gathered, self.rank, op, cols.shape[0], self.local.J)
         return self.local.apply(op, cols, carry, reuse_summary=True)
 
     def solve(self, b_local):

@@ -176,6 +176,9 @@ int cel_dot_L_device(cel_solver* s, int nrhs, const double* d_z, double* d_out);
  *                                                     2 backward solve (in = x/D, out = K^-1 b)
  *     all-gather of the summaries (the only collective: (J^2+J)*8 bytes per rank), each rank
  *     folds the maps of the ranks before it (after it, for op 2) into its incoming carry
+ *     (cel_span_fold does that fold on the device: d_gathered[world][(nrhs + nb) * J] in rank
+ *     order -> d_carry_out[nrhs * J]; ranks 0..rank-1 in order for op 0 and 1, world-1..rank+1
+ *     for op 2)
  *     cel_span_apply      -> result for the span from that carry (d_carry_in: nrhs*J, NULL = 0;
  *                            reuse_summary != 0 skips pass 1 when it directly follows the
  *                            summarize call of the same op and input). */
@@ -183,6 +186,8 @@ int cel_span_trim(cel_solver* s, int halo);
 int cel_span_summarize(cel_solver* s, int op, int nrhs, const double* d_in, double* d_summary);
 int cel_span_apply(cel_solver* s, int op, int nrhs, const double* d_in, const double* d_carry_in,
                    double* d_out, int reuse_summary);
+int cel_span_fold(cel_solver* s, int op, int nrhs, int world, int rank, const double* d_gathered,
+                  double* d_carry_out);
 int cel_span_dims(const cel_solver* s, int* n_local, int* J, int* nchunks, int* chunk_len);
 
 /* ---- gradient without any allocation (no counterpart in the reference) ----------------------

@@ -74,6 +74,10 @@ def test_device_api_and_span_protocol_on_one_gpu():
         outs = []
         for r, (L, c) in enumerate(zip(locs, cols_per_rank)):
             carry = ls.fold_carries(summ, r, op, c.shape[0], L.J)
+            # the device-side fold (cel_span_fold) is the same arithmetic in one kernel
+            dev_carry = L.fold(op, summ.contiguous(), c.shape[0], world, r)
+            scale = max(1.0, float(carry.abs().max()))
+            assert float((dev_carry - carry).abs().max()) / scale < 1e-12
             # summaries of all ranks were taken before any apply: pass 1 must be redone per rank
             outs.append(L.apply(op, c, carry, reuse_summary=False))
         return outs
