@@ -285,6 +285,87 @@ __global__ void __launch_bounds__(kWarp) k_chunk_backward(ScanArgs a) {
   if (a.carry && row_ok && active) a.carry[((size_t)chunk * ncols + col) * J + kk] = f;
 }
 
+// Chunk maps M (once per factor): the J unit carries of a chunk share the chunk's factor tiles,
+// so ONE group carries all J columns through the chunk, J independent recurrences deep (the tiles
+// are read once and the reductions of the columns overlap).  BACKWARD: the map of the backward
+// half of solve (tiles walked from the top); otherwise the forward half.  The diagonal map of
+// dot_L is a single column and uses the ordinary sweep kernel.
+template <int L, bool BACKWARD>
+__global__ void __launch_bounds__(kWarp) k_chunk_maps(ScanArgs a) {
+  using SM = ChunkSmem<L>;
+  constexpr int G = SM::G, ROW = SM::ROW;
+  __shared__ __align__(16) double sm[G * SM::GROUP];
+  const int lane = threadIdx.x, g = lane / L, k = lane % L;
+  const long long gid0 = (long long)blockIdx.x * G + g;
+  const bool active = gid0 < a.nchunks;
+  const int chunk = (int)(active ? gid0 : a.nchunks - 1);
+  const int N = a.N, J = a.J, off = a.n_off;
+  const bool row_ok = k < J;
+  const int kk = row_ok ? k : 0;
+  const int n0 = chunk * a.chunk_len, n1 = min(N, n0 + a.chunk_len);
+  const bool vec16 = (J & 1) == 0;
+  const unsigned gmask = group_mask<L>(g);
+  double* base = sm + g * SM::GROUP;
+
+  double f[L], sprev[L];
+#pragma unroll
+  for (int c = 0; c < L; ++c) { f[c] = (row_ok && kk == c) ? 1.0 : 0.0; sprev[c] = 0.0; }
+  double wprev = 0.0;
+
+  const int ntiles = (n1 - n0 + TT - 1) / TT;
+  auto issue = [&](int q, int st) {                       // q-th tile of the walk
+    if (q < ntiles) {
+      const int m0 = n0 + (BACKWARD ? ntiles - 1 - q : q) * TT;
+      const int cnt = min(TT, n1 - m0), s0 = m0 + off;
+      double* sp = base + st * SM::STAGE;
+      copy_flat<L>(sp + 2 * ROW, a.W + (size_t)s0 * J, cnt * J, k, vec16);
+      const int skip = (s0 == 0) ? 1 : 0;
+      if (cnt > skip) {
+        copy_flat<L>(sp + skip * J, a.phi + (size_t)(s0 - 1 + skip) * J, (cnt - skip) * J, k, vec16);
+        copy_flat<L>(sp + ROW + skip * J, a.u + (size_t)(s0 - 1 + skip) * J, (cnt - skip) * J, k, vec16);
+      }
+      if (skip && row_ok) { sp[kk] = 0.0; sp[ROW + kk] = 0.0; }
+    }
+    cp_async_commit_group();
+  };
+  auto step = [&](const double* sp, int i) {
+    const double ph = row_ok ? sp[i * J + kk] : 0.0;
+    const double uu = row_ok ? sp[ROW + i * J + kk] : 0.0;
+    const double ww = row_ok ? sp[2 * ROW + i * J + kk] : 0.0;
+    if (BACKWARD) {
+#pragma unroll
+      for (int c = 0; c < L; ++c) {
+        const double z = -group_sum_masked<L>(ww * f[c], gmask);
+        f[c] = ph * fma(uu, z, f[c]);
+      }
+    } else {
+#pragma unroll
+      for (int c = 0; c < L; ++c) {
+        f[c] = ph * fma(wprev, sprev[c], f[c]);
+        sprev[c] = -group_sum_masked<L>(uu * f[c], gmask);
+      }
+      wprev = ww;
+    }
+  };
+
+  for (int q = 0; q < kStages - 1; ++q) issue(q, q);
+  for (int t = 0; t < ntiles; ++t) {
+    issue(t + kStages - 1, (t + kStages - 1) % kStages);
+    cp_async_wait_group<kStages - 1>();
+    __syncwarp(gmask);
+    const double* sp = base + (t % kStages) * SM::STAGE;
+    const int m0 = n0 + (BACKWARD ? ntiles - 1 - t : t) * TT, cnt = min(TT, n1 - m0);
+    if (BACKWARD) { for (int i = cnt - 1; i >= 0; --i) step(sp, i); }
+    else { for (int i = 0; i < cnt; ++i) step(sp, i); }
+    __syncwarp(gmask);
+  }
+  if (row_ok && active) {
+#pragma unroll
+    for (int c = 0; c < L; ++c)
+      if (c < J) a.carry[((size_t)chunk * J + c) * J + kk] = BACKWARD ? f[c] : fma(wprev, sprev[c], f[c]);
+  }
+}
+
 // --------------------------------------------------------------------------------------------
 // middle: from the chunk maps to the carry entering every chunk.
 //
@@ -554,6 +635,19 @@ cudaError_t launch_chunk_sweep(const ScanArgs& a, cudaStream_t stream) {
   if (a.J > kMidMaxJ || a.nchunks < 1) return cudaErrorInvalidValue;
   const long long total = (long long)a.nchunks * (a.nrhs + a.nbasis);
   if (total == 0) return cudaSuccess;
+  if (a.nrhs == 0 && a.nbasis == a.J && !a.diag_basis && a.mode != 1 && a.carry && !a.init) {
+    // the full chunk maps of a solve direction: one group per chunk carries all J columns
+#define CALLM(LL)                                                                    \
+  {                                                                                  \
+    const int G = kWarp / LL;                                                        \
+    const unsigned grid = (unsigned)((a.nchunks + G - 1) / G);                       \
+    if (a.mode == 2) k_chunk_maps<LL, true><<<grid, kWarp, 0, stream>>>(a);          \
+    else k_chunk_maps<LL, false><<<grid, kWarp, 0, stream>>>(a);                     \
+  }
+    CEL_DISPATCH_L(a.J, CALLM);
+#undef CALLM
+    return cudaGetLastError();
+  }
 #define CALL(LL)                                                                  \
   {                                                                               \
     const int G = kWarp / LL;                                                     \
