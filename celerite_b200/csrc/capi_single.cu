@@ -1,5 +1,6 @@
 // C ABI, part 2: the single-series entry points that mirror CholeskySolver<double>
 // (include/celerite_b200.h).  Host pointers in, host pointers out, synchronous.
+#include <algorithm>
 #include <cfloat>
 #include <cmath>
 #include <cstdlib>
@@ -8,6 +9,58 @@
 #include "solver_handle.h"
 
 namespace {
+
+// ---- time-segmented factorisation of one long series -------------------------------------------
+// The factorisation recursion forgets its past: two runs that differ in S at step m differ by a
+// factor ~prod(phi^2) <= exp(-2 c_min (t_n - t_m)) at step n (open-loop bound; the closed loop
+// contracts faster).  A segment that starts from S = 0 a time span
+// ln(1/kSegmentTol) / (2 c_min) before its first owned step therefore reproduces the serial factor
+// to round-off.  The bound is checked afterwards on the data: W and D of every segment's last
+// warm-up step must agree with the owner's values to kSegmentMismatchTol, else cel_compute redoes
+// the series serially.
+constexpr int kSegmentedMinN = 65536;
+constexpr double kSegmentTol = 1e-17;
+constexpr double kSegmentMismatchTol = 1e-12;
+
+// seg = [begin, first owned, end) per segment, or empty when segmenting does not pay
+void plan_segments(int J, int Jr, const double* c_real, int Jc, const double* c_comp, int N, const double* x,
+                   std::vector<int>& seg) {
+  seg.clear();
+  double c_min = INFINITY;
+  for (int j = 0; j < Jr; ++j) c_min = std::fmin(c_min, c_real[j]);
+  for (int j = 0; j < Jc; ++j) c_min = std::fmin(c_min, c_comp[j]);
+  if (!(c_min > 0.0) || !std::isfinite(c_min)) return;   // a term that never decays: no forgetting
+  double span = std::log(1.0 / kSegmentTol) / (2.0 * c_min);
+  // testing knob: shrink the halos until the a-posteriori check has to reject them
+  if (const char* e = getenv("CEL_SEGMENT_HALO_SCALE")) span *= atof(e);
+  int L = 1;
+  while (L < J && L < 32) L <<= 1;
+  const int slots = 148 * 8 * (32 / L);                  // resident groups of the cooperative kernel
+  // halo length (in steps) at the median sampling rate decides how finely the series can be cut
+  const double dt = (x[N - 1] - x[0]) / (double)(N - 1);
+  if (!(dt > 0.0)) return;
+  const double halo_steps = span / dt;
+  long long len = (N + slots - 1) / slots;
+  if (len < 1024) len = 1024;
+  if ((double)len < halo_steps) len = (long long)halo_steps;   // at most ~2x redundant work
+  len = (len + 15) / 16 * 16;
+  const int K = (int)((N + len - 1) / len);
+  if (K < 16) return;
+  seg.reserve(3 * (size_t)K);
+  long long work = 0;
+  for (int c = 0; c < K; ++c) {
+    const int own = (int)(c * len), end = (int)std::min<long long>(N, own + len);
+    int begin = 0;
+    if (own > 0) {
+      const double t0 = x[own] - span;
+      begin = (int)(std::lower_bound(x, x + own, t0) - x);
+      if (begin > 0) --begin;                            // one more step: the bound is met, not just approached
+    }
+    seg.push_back(begin); seg.push_back(own); seg.push_back(end);
+    work += end - begin;
+  }
+  if (work > 3LL * N) seg.clear();                       // uneven sampling made the halos long: not worth it
+}
 
 int pack_coeffs(cel_solver* s, double jitter, int Jr, const double* a_real, const double* c_real, int Jc,
                 const double* a_comp, const double* b_comp, const double* c_comp, const double* d_comp,
@@ -105,6 +158,51 @@ int cel_compute(cel_solver* s, double jitter, int Jr, const double* a_real, cons
     s->log_det = res[0];
     s->computed = true;
     return CEL_OK;
+  }
+
+  // Long series without general rows: factorise time segments side by side, each from a cold start
+  // behind a warm-up halo (plan_segments); falls through to the serial sweep when the kernel
+  // forgets too slowly for that, or when the check of the halos against their owners fails.
+  if (Jg == 0 && !A && N >= kSegmentedMinN) {
+    std::vector<int> seg;
+    plan_segments(J, Jr, c_real, Jc, c_comp, N, x, seg);
+    if (!seg.empty()) {
+      const int K = (int)(seg.size() / 3);
+      // scratch1: [K] logdet | [K][J+1] edge | [4] result | ints: [3K] seg, [K] status, [K] fail
+      const size_t nd = (size_t)K + (size_t)K * (J + 1) + 4;
+      CEL_CUDA_TRY(s, s->scratch1.reserve(dbytes(nd) + sizeof(int) * (size_t)5 * K));
+      double* d_ld = s->scratch1.d();
+      double* d_edge = d_ld + K;
+      double* d_res = d_edge + (size_t)K * (J + 1);
+      int* d_seg = reinterpret_cast<int*>(d_res + 4);
+      CEL_CUDA_TRY(s, cudaMemcpyAsync(d_seg, seg.data(), sizeof(int) * seg.size(), cudaMemcpyHostToDevice, st));
+      cel::BatchArgs sa{};
+      sa.B = K; sa.N = N; sa.stride = 0; sa.Jr = Jr; sa.Jc = Jc; sa.Jg = 0;
+      sa.coeffs = s->coeffs.d(); sa.coeff_stride = 0;
+      sa.t = s->t.d(); sa.diag = s->in0.d();
+      sa.out_logdet = d_ld; sa.status = d_seg + 3 * K; sa.fail_index = d_seg + 4 * K;
+      sa.phi = s->phi.d(); sa.u = s->u.d(); sa.W = s->W.d(); sa.D = s->D.d();
+      sa.seg = d_seg; sa.seg_edge = d_edge;
+      CEL_CUDA_TRY(s, cel::launch_factor_segments(sa, st));
+      CEL_CUDA_TRY(s, cel::launch_segment_finish(sa, d_res, st));
+      s->launches += 2;
+      CEL_CUDA_TRY(s, cudaMemcpyAsync(res, d_res, 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+      CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
+      const int* sres = reinterpret_cast<const int*>(res + 2);
+      if (res[1] <= kSegmentMismatchTol) {
+        s->N = N; s->J = J; s->Jr = Jr; s->Jc = Jc; s->Jg = Jg;
+        s->have_coeffs = true;
+        if (sres[0] != 0) {
+          char buf[128];
+          snprintf(buf, sizeof(buf), "failed to factorize or solve matrix (D_n < 0 at n = %d)", sres[1] - 1);
+          CEL_FAIL(s, CEL_NOT_POSITIVE_DEFINITE, buf);
+        }
+        s->log_det = res[0];
+        s->computed = true;
+        return CEL_OK;
+      }
+      // a halo had not converged onto its owner's state: redo the series serially
+    }
   }
 
   cel::BatchArgs a{};

@@ -115,6 +115,16 @@ __device__ __forceinline__ double group_sum_masked(double v, unsigned mask) {
   return v;
 }
 template <int L>
+__device__ __forceinline__ void group_sum2_masked(double& a, double& b, unsigned mask) {
+#pragma unroll
+  for (int o = L / 2; o > 0; o >>= 1) {
+    double ta = __shfl_xor_sync(mask, a, o, L);
+    double tb = __shfl_xor_sync(mask, b, o, L);
+    a += ta;
+    b += tb;
+  }
+}
+template <int L>
 __device__ __forceinline__ unsigned group_mask(int g) {
   return L >= 32 ? kFull : (((1u << (L & 31)) - 1u) << (g * L));
 }

@@ -53,7 +53,9 @@ struct CoopCfg {
   static constexpr size_t smem = (size_t)G * kGroup * sizeof(double);
 };
 
-template <int JP, bool STORE>
+// SEG: the groups are time segments of ONE series (BatchArgs::seg) instead of whole series; they
+// differ in length, so every warp-level primitive names the group's own lanes only.
+template <int JP, bool STORE, bool SEG = false>
 __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
   using C = CoopCfg<JP, STORE>;
   constexpr int L = C::L, G = C::G, T = C::T;
@@ -62,6 +64,8 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
   const long long b = (long long)blockIdx.x * G + g;
   const bool active = b < a.B;
   const long long bb = active ? b : a.B - 1;
+  const long long sb = SEG ? 0 : bb;            // series the group reads (segments share series 0)
+  const unsigned gmask = SEG ? group_mask<L>(g) : kFull;
 
   double* base = smem + (size_t)g * C::kGroup;
   double* t_s = base;                    // [T+1]  t_s[0] = previous time
@@ -77,21 +81,23 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
   double* cf_s = x_s + 2 * JP + C::kOut;  // coefficient row (w_s/dd_s exist only when STORE)
 
   const int N = a.N, Jr = a.Jr, Jc = a.Jc, Jg = a.Jg, J = Jr + 2 * Jc + Jg, P = 1 + 2 * Jr + 4 * Jc;
-  const double* tp = a.t + bb * a.stride;
-  const double* dp = a.diag + bb * a.stride;
-  const double* yp = a.y ? a.y + bb * a.stride : nullptr;
-  const double* Ap = a.A ? a.A + bb * a.stride : nullptr;
-  const double* Up = a.U ? a.U + bb * a.stride * Jg : nullptr;
-  const double* Vp = a.V ? a.V + bb * a.stride * Jg : nullptr;
+  const double* tp = a.t + sb * a.stride;
+  const double* dp = a.diag + sb * a.stride;
+  const double* yp = a.y ? a.y + sb * a.stride : nullptr;
+  const double* Ap = a.A ? a.A + sb * a.stride : nullptr;
+  const double* Up = a.U ? a.U + sb * a.stride * Jg : nullptr;
+  const double* Vp = a.V ? a.V + sb * a.stride * Jg : nullptr;
+  // steps [nb, ne) are swept, those from `no` on are owned (stored, accumulated)
+  const int nb = SEG ? a.seg[3 * bb] : 0, no = SEG ? a.seg[3 * bb + 1] : 0, ne = SEG ? a.seg[3 * bb + 2] : N;
 
   // coefficient row -> shared; zero the generator tiles once (padded columns stay zero)
   {
-    const double* row = a.coeffs + bb * a.coeff_stride;
+    const double* row = a.coeffs + sb * a.coeff_stride;
     for (int i = k; i < P; i += L) cf_s[i] = row[i];
     for (int i = k; i < 4 * T * JP; i += L) phi_s[i] = 0.0;
     for (int i = k; i < 2 * JP; i += L) x_s[i] = 0.0;
   }
-  __syncwarp();
+  __syncwarp(gmask);
   const double jitter = cf_s[0];
   const double* a_real = cf_s + 1;
   const double* c_real = a_real + Jr;
@@ -127,20 +133,20 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
 #pragma unroll
     for (int q = 0; q < PF; ++q) {
       const int i = k + q * L;
-      const int n = min(n0 + i, N - 1);
+      const int n = min(n0 + i, ne - 1);
       pt[q] = __ldg(tp + n);
       pd[q] = __ldg(dp + n);
       pa[q] = Ap ? __ldg(Ap + n) : 0.0;
       py[q] = yp ? __ldg(yp + n) : 0.0;
     }
   };
-  prefetch(0);
-  double t_last = __ldg(tp);             // time of the step before the tile
+  prefetch(nb);
+  double t_last = __ldg(tp + max(nb - 1, 0));   // time of the step before the tile
 
-  const int ntiles = (N + T - 1) / T;
+  const int ntiles = (ne - nb + T - 1) / T;
   for (int tile = 0; tile < ntiles; ++tile) {
-    const int n0 = tile * T;
-    const int nt = min(T, N - n0);
+    const int n0 = nb + tile * T;
+    const int nt = min(T, ne - n0);
     // ---- inputs of this tile -> shared; start fetching the next tile ----------------------
     if (k == 0) t_s[0] = t_last;
 #pragma unroll
@@ -148,7 +154,7 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
       const int i = k + q * L;
       if (i < T) { t_s[1 + i] = pt[q]; d_s[i] = pd[q] + pa[q]; y_s[i] = py[q]; }
     }
-    __syncwarp();
+    __syncwarp(gmask);
     t_last = t_s[nt];
     if (tile + 1 < ntiles) prefetch(n0 + T);
 
@@ -239,7 +245,7 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
       ut_s[i * JP + r0] = ug;
       v_s[i * JP + r0] = __ldg(Vp + (size_t)(n0 + i) * Jg + q);
     }
-    __syncwarp();
+    __syncwarp(gmask);
 
     // ---- serial phase ---------------------------------------------------------------------
     for (int i = 0; i < nt; ++i) {
@@ -266,43 +272,51 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
       }
       const double av = (acc0 + acc1) + (acc2 + acc3);
       double red_a = utk * av, red_f = utk * f_own, red_b = utk * dw_own;
-      group_sum2<L>(red_a, red_f);                   // known early: off the scalar chain
-      red_b = group_sum<L>(red_b);                   // the one reduction on the chain
+      group_sum2_masked<L>(red_a, red_f, gmask);     // known early: off the scalar chain
+      red_b = group_sum_masked<L>(red_b, gmask);     // the one reduction on the chain
       const double tb = red_b * r_prev;
       const double Dn = (((d_s[i] + sum_ar) + sum_ac) + jitter - red_a) - red_b * tb;
       const double x = (y_s[i] - red_f) - red_b * s_prev;
       const double dw = vk - phk * fma(dw_own, tb, av);
       f_own = phk * fma(dw_own, s_prev, f_own);
       if (row_ok) x_s[(par ^ 1) * JP + kk] = dw;
-      fail = (Dn < 0.0 && fail == 0) ? n0 + i + 1 : fail;   // cholesky.h:176
+      const bool own = !SEG || n0 + i >= no;
+      fail = (own && Dn < 0.0 && fail == 0) ? n0 + i + 1 : fail;   // cholesky.h:176
       const double r = fast_rcp_nocheck(Dn);
       if (STORE) {
         if (row_ok) w_s[i * JP + kk] = dw * r;
         if (k == 0) dd_s[i] = Dn;
       }
+      if (SEG && active && n0 + i == no - 1) {       // last warm-up step: kept for the consistency check
+        double* edge = a.seg_edge + (size_t)b * (J + 1);
+        if (k < J) edge[k] = dw * r;
+        if (k == 0) edge[J] = Dn;
+      }
       s_prev = r * x;
       quad = fma(x, s_prev, quad);
       dw_own = dw;
       r_prev = r;
-      ld.add(Dn);
-      __syncwarp();
+      ld.add(own ? Dn : 1.0);
+      __syncwarp(gmask);
     }
     ld.renorm();
 
     // ---- materialise (reference layout: J fastest, column n-1 of phi/u = time n) ------------
     if (STORE) {
       if (active) {
-        double* Wg = a.W + (size_t)b * N * J + (size_t)n0 * J;
-        for (int e = k; e < nt * J; e += L) {
+        const size_t fb = SEG ? 0 : (size_t)b;        // factor the group writes into
+        const int i_own = SEG ? max(no - n0, 0) : 0;  // first owned step of the tile
+        double* Wg = a.W + fb * N * J + (size_t)n0 * J;
+        for (int e = k + i_own * J; e < nt * J; e += L) {
           const int i = e / J, j = e - i * J;
           Wg[e] = w_s[i * JP + j];
         }
-        double* Dg = a.D + (size_t)b * N + n0;
-        for (int i = k; i < nt; i += L) Dg[i] = dd_s[i];
+        double* Dg = a.D + fb * N + n0;
+        for (int i = k + i_own; i < nt; i += L) Dg[i] = dd_s[i];
         if (N > 1) {
-          double* phg = a.phi + (size_t)b * (N - 1) * J;
-          double* ug = a.u + (size_t)b * (N - 1) * J;
-          const int i0 = (n0 == 0) ? 1 : 0;
+          double* phg = a.phi + fb * (N - 1) * J;
+          double* ug = a.u + fb * (N - 1) * J;
+          const int i0 = max(i_own, (n0 == 0) ? 1 : 0);
           for (int e = k + i0 * J; e < nt * J; e += L) {
             const int i = e / J, j = e - i * J;
             const size_t o = (size_t)(n0 + i - 1) * J + j;
@@ -311,7 +325,7 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
           }
         }
       }
-      __syncwarp();
+      __syncwarp(gmask);
     }
   }
 
@@ -352,7 +366,83 @@ cudaError_t dispatch(const BatchArgs& a, cudaStream_t stream) {
   return cudaErrorInvalidValue;
 }
 
+template <int JP>
+cudaError_t launch_seg(const BatchArgs& a, cudaStream_t stream) {
+  using C = CoopCfg<JP, true>;
+  auto kern = k_factor_coop<JP, true, true>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::smem);
+  if (e != cudaSuccess) return e;
+  const long long grid = (a.B + C::G - 1) / C::G;
+  kern<<<(unsigned)grid, kWarp, C::smem, stream>>>(a);
+  return cudaGetLastError();
+}
+
+// per-segment results -> log det (fixed summation order), worst halo mismatch, first failure
+__global__ void __launch_bounds__(256) k_segment_finish(BatchArgs a, double* result) {
+  __shared__ double s_sum[256], s_max[256];
+  __shared__ int s_fail[256];
+  const int J = a.Jr + 2 * a.Jc + a.Jg, tid = threadIdx.x;
+  const int K = (int)a.B;
+  // contiguous slices so that the summation order is the segment order
+  const int per = (K + 255) / 256, c0 = tid * per, c1 = min(K, c0 + per);
+  double sum = 0.0, worst = 0.0;
+  int fail = 0;
+  for (int c = c0; c < c1; ++c) {
+    sum += a.out_logdet[c];
+    const int f = a.fail_index[c];
+    if (f != 0 && (fail == 0 || f < fail)) fail = f;
+    const int nb = a.seg[3 * c], no = a.seg[3 * c + 1];
+    if (no > nb) {
+      const double* edge = a.seg_edge + (size_t)c * (J + 1);
+      const double* Wr = a.W + (size_t)(no - 1) * J;
+      double wmax = 0.0, dmax = 0.0;
+      for (int j = 0; j < J; ++j) { wmax = fmax(wmax, fabs(Wr[j])); dmax = fmax(dmax, fabs(edge[j] - Wr[j])); }
+      double rel = dmax / fmax(wmax, 1e-300);
+      const double Dr = a.D[no - 1];
+      rel = fmax(rel, fabs(edge[J] - Dr) / fmax(fabs(Dr), 1e-300));
+      if (!(rel <= worst)) worst = rel;               // nan counts as a mismatch
+    }
+  }
+  s_sum[tid] = sum; s_max[tid] = worst; s_fail[tid] = fail;
+  __syncthreads();
+  for (int o = 1; o < 256; o <<= 1) {                  // adjacent pairs first: keeps the order fixed
+    if ((tid & (2 * o - 1)) == 0) {
+      s_sum[tid] += s_sum[tid + o];
+      if (!(s_max[tid + o] <= s_max[tid])) s_max[tid] = s_max[tid + o];
+      const int f = s_fail[tid + o];
+      if (f != 0 && (s_fail[tid] == 0 || f < s_fail[tid])) s_fail[tid] = f;
+    }
+    __syncthreads();
+  }
+  if (tid == 0) {
+    const int f = s_fail[0];
+    result[0] = f ? __longlong_as_double(0x7ff8000000000000LL) : s_sum[0];
+    result[1] = s_max[0];
+    int* ir = reinterpret_cast<int*>(result + 2);
+    ir[0] = f ? 3 : 0;
+    ir[1] = f;
+  }
+}
+
 }  // namespace
+
+cudaError_t launch_factor_segments(const BatchArgs& a, cudaStream_t stream) {
+  const int J = a.Jr + 2 * a.Jc + a.Jg;
+  if (!a.seg || !a.seg_edge || !a.phi || a.Jg != 0 || J < 1 || J > kCoopMaxJ) return cudaErrorInvalidValue;
+  if (J <= 2) return launch_seg<2>(a, stream);
+  if (J <= 4) return launch_seg<4>(a, stream);
+  if (J <= 6) return launch_seg<6>(a, stream);
+  if (J <= 8) return launch_seg<8>(a, stream);
+  if (J <= 12) return launch_seg<12>(a, stream);
+  if (J <= 16) return launch_seg<16>(a, stream);
+  if (J <= 24) return launch_seg<24>(a, stream);
+  return launch_seg<32>(a, stream);
+}
+
+cudaError_t launch_segment_finish(const BatchArgs& a, double* result, cudaStream_t stream) {
+  k_segment_finish<<<1, 256, 0, stream>>>(a, result);
+  return cudaGetLastError();
+}
 
 cudaError_t launch_loglik_coop(const BatchArgs& a, cudaStream_t stream) {
   return a.phi ? dispatch<true>(a, stream) : dispatch<false>(a, stream);

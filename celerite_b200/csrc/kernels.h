@@ -31,12 +31,25 @@ struct BatchArgs {
   double* u;               // B x (N-1) x J
   double* W;               // B x N x J
   double* D;               // B x N
+  // Time-chunked factorisation of ONE series (launch_factor_segments): group b factorises steps
+  // [seg[3b], seg[3b+2]) from a cold start and owns (stores, accumulates) those from seg[3b+1] on;
+  // the steps before are its warm-up halo.  B = number of segments, stride = coeff_stride = 0.
+  const int* seg;          // NULL for batches of whole series
+  double* seg_edge;        // [B][J+1]: W and D of the last warm-up step, for the consistency check
 };
 
 // Thread-per-series lockstep sweep (fused log-likelihood), J = Jr + 2*Jc <= kLockstepMaxJ, Jg = 0.
 constexpr int kLockstepMaxJ = 6;
 constexpr int kLockstepFastJ = 6;   // beyond this the register state spills: use the cooperative kernel
 cudaError_t launch_loglik_lockstep(const BatchArgs& a, cudaStream_t stream);
+
+// One long series factorised in parallel segments with warm-up halos (coop.cu); a.seg, a.seg_edge,
+// a.phi.. set, a.out_logdet / a.status / a.fail_index per segment.  launch_segment_finish reduces
+// the per-segment results: result[0] = log det, result[1] = max relative difference between every
+// segment's last warm-up step and the same step as its owner computed it, and (as two ints in
+// result[2]) status and 1 + index of the first negative pivot.
+cudaError_t launch_factor_segments(const BatchArgs& a, cudaStream_t stream);
+cudaError_t launch_segment_finish(const BatchArgs& a, double* result, cudaStream_t stream);
 
 // Thread-per-series MATERIALISING compute with TMA stores (lockstep_store.cu); *used = false when
 // the batch does not qualify (then call launch_loglik_coop with a.phi set).

@@ -112,3 +112,80 @@ def test_full_size_properties_cfg4_like():
     kz = s.dot(p.jitter, p.a_real, p.c_real, p.a_comp, p.b_comp, p.c_comp, p.d_comp, E0, E2, E2, p.x, z)[:, 0]
     kz += p.diag * z
     assert rel_inf(kz, y) < 1e-8
+
+
+def _factor_diff(state, f):
+    comp, n, j, ld, phi, u, W, D = state
+    scale = lambda a: max(1e-300, float(np.max(np.abs(a))))  # noqa: E731
+    return max(np.max(np.abs(D - f.D)) / scale(f.D), np.max(np.abs(W.T - f.W)) / scale(f.W),
+               np.max(np.abs(phi.T - f.phi)) / scale(f.phi), np.max(np.abs(u.T - f.u)) / scale(f.u))
+
+
+@pytest.mark.parametrize("N,Jr,Jc,segmented", [(200000, 0, 4, True), (70001, 1, 1, True), (150000, 0, 1, True),
+                                               (100003, 2, 6, None)])
+def test_segmented_compute_matches_serial_factor(N, Jr, Jc, segmented):
+    """cel_compute on a long series factorises time segments side by side behind warm-up halos
+    (capi_single.cu: plan_segments).  The stored factor and log-determinant must be the serial ones."""
+    from celerite_b200 import solver
+    p, y = _problem(N, Jr, Jc, seed=N + 1)
+    chk = oracle.best()
+    f = chk.factor(p)
+    s = solver.CholeskySolver()
+    n0 = s.launch_count()
+    s.compute(p.jitter, p.a_real, p.c_real, p.a_comp, p.b_comp, p.c_comp, p.d_comp, E0, E2, E2, p.x, p.diag)
+    # segment sweep + finish; the serial path is one launch (segmented=None: the planner decides)
+    assert s.launch_count() - n0 == (2 if segmented else s.launch_count() - n0)
+    assert abs(s.log_determinant() - f.log_det) / N < 1e-12
+    assert _factor_diff(s.__getstate__(), f) < 1e-11
+    assert rel_inf(s.solve(y), chk.solve(f, y)) < RTOL_SOLVE
+
+
+def test_segmented_compute_falls_back_for_slow_kernels():
+    """A term that barely decays over the whole series leaves nothing to cut: serial sweep."""
+    from celerite_b200 import solver
+    N = 80000
+    p, y = _problem(N, 1, 1, seed=3)
+    span = p.x[-1] - p.x[0]
+    c_real = np.array(p.c_real, copy=True)
+    c_real[0] = 0.5 / span                      # a real term with a > 0 stays positive definite
+    pp = oracle.Problem(p.jitter, p.a_real, c_real, p.a_comp, p.b_comp, p.c_comp, p.d_comp, p.x, p.diag)
+    chk = oracle.best()
+    f = chk.factor(pp)
+    s = solver.CholeskySolver()
+    n0 = s.launch_count()
+    s.compute(pp.jitter, pp.a_real, pp.c_real, pp.a_comp, pp.b_comp, pp.c_comp, pp.d_comp, E0, E2, E2, pp.x, pp.diag)
+    assert s.launch_count() - n0 == 1
+    assert _factor_diff(s.__getstate__(), f) < 1e-11
+
+
+def test_segmented_compute_reports_the_first_negative_pivot():
+    """cholesky.h:176 — the failure index must be the serial one even when it lies deep in a segment."""
+    from celerite_b200 import solver
+    N = 120000
+    p, y = _problem(N, 0, 2, seed=9)
+    diag = np.array(p.diag, copy=True)
+    bad = 77777
+    diag[bad] = -50.0 * (np.sum(p.a_comp) + 1.0)
+    diag[bad + 20000] = diag[bad]
+    s = solver.CholeskySolver()
+    with pytest.raises(Exception) as ei:
+        s.compute(p.jitter, p.a_real, p.c_real, p.a_comp, p.b_comp, p.c_comp, p.d_comp, E0, E2, E2, p.x, diag)
+    assert "n = %d" % bad in str(ei.value)
+    assert not s.computed()
+
+
+def test_segmented_compute_rejects_halos_that_did_not_converge(monkeypatch):
+    """With the halos cut to 2 % of the bound the segments start from a wrong state; the check of
+    every halo against its owner must notice and the series is redone serially (3 launches)."""
+    from celerite_b200 import solver
+    N = 150000
+    p, y = _problem(N, 0, 2, seed=21)
+    chk = oracle.best()
+    f = chk.factor(p)
+    monkeypatch.setenv("CEL_SEGMENT_HALO_SCALE", "0.02")
+    s = solver.CholeskySolver()
+    n0 = s.launch_count()
+    s.compute(p.jitter, p.a_real, p.c_real, p.a_comp, p.b_comp, p.c_comp, p.d_comp, E0, E2, E2, p.x, p.diag)
+    assert s.launch_count() - n0 == 3
+    assert abs(s.log_determinant() - f.log_det) / N < 1e-12
+    assert _factor_diff(s.__getstate__(), f) < 1e-11

@@ -9,8 +9,10 @@ j, ar, cr, ac, bc, cc, dc = synth.split_row(b["coeffs"][0], 0, Jc)
 L = ls.LongSeries(0)
 rhs = torch.from_numpy(b["y"][0]).cuda()
 for rep in range(2):
+    t0 = time.perf_counter()
     L.compute(j, ar, cr, ac, bc, cc, dc, b["t"][0], b["diag"][0])
     torch.cuda.synchronize()
+    print("compute (host arrays in, factor resident): %.1f ms wall" % ((time.perf_counter() - t0) * 1e3))
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
     ev[0].record(); z = L.solve(rhs); ev[1].record(); z = L.solve(rhs); ev[2].record(); w = L.dot_L(rhs); ev[3].record()
     torch.cuda.synchronize()
