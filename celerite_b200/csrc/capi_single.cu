@@ -259,6 +259,19 @@ int cel_dot_solve(cel_solver* s, int N, const double* b, double* out) {
   cudaStream_t st = s->stream;
   CEL_CUDA_TRY(s, s->out0.reserve(64));
   double* res = static_cast<double*>(s->pinned);
+  if (s->J >= 1 && N >= kChunkedMinN && s->n_off == 0) {
+    // long series: the forward half of solve as a chunked scan (x / D), then sum (x/D)^2 D
+    CEL_CUDA_TRY(s, s->scan_tmp.reserve(dbytes((size_t)N)));
+    CEL_CUDA_TRY(s, s->scratch2.reserve(dbytes(cel::quad_scratch_doubles())));
+    rc = cel_span_apply(s, 0, 1, s->in0.d(), nullptr, s->scan_tmp.d(), 0);
+    if (rc != CEL_OK) return rc;
+    CEL_CUDA_TRY(s, cel::launch_quad(N, s->scan_tmp.d(), s->D.d(), s->scratch2.d(), s->out0.d(), st));
+    s->launches += 2;
+    CEL_CUDA_TRY(s, cudaMemcpyAsync(res, s->out0.p, sizeof(double), cudaMemcpyDeviceToHost, st));
+    CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
+    *out = res[0];
+    return CEL_OK;
+  }
   // J == 0 (cholesky.h:334-339) runs through the same kernel: no rows, x = b, sum b^2/D
   cel::SweepArgs a = sweep_args(s, 1);
   a.out = nullptr;

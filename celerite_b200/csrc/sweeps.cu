@@ -480,3 +480,49 @@ cudaError_t launch_predict(const PredictArgs& a, cudaStream_t stream) {
   return cudaGetLastError();
 }
 }  // namespace cel
+
+// sum_n xd_n^2 D_n for xd = x / D (the quadratic form y^T K^-1 y after a chunked forward sweep).
+// Two fixed-shape stages, so the summation order does not depend on scheduling.
+namespace cel {
+namespace {
+constexpr int kQuadBlocks = 592, kQuadThreads = 256;
+__device__ __forceinline__ double block_sum_ordered(double v, double* sh) {
+  sh[threadIdx.x] = v;
+  __syncthreads();
+  for (int o = 1; o < kQuadThreads; o <<= 1) {
+    if ((threadIdx.x & (2 * o - 1)) == 0) sh[threadIdx.x] += sh[threadIdx.x + o];
+    __syncthreads();
+  }
+  return sh[0];
+}
+__global__ void __launch_bounds__(kQuadThreads) k_quad_partial(int N, const double* xd, const double* D, double* part) {
+  __shared__ double sh[kQuadThreads];
+  // block b owns a contiguous slice; inside it the threads stride (coalesced)
+  const long long per = ((long long)N + gridDim.x - 1) / gridDim.x;
+  const long long lo = per * blockIdx.x, hi = lo + per < N ? lo + per : N;
+  double acc = 0.0;
+  for (long long n = lo + threadIdx.x; n < hi; n += kQuadThreads) {
+    const double v = xd[n];
+    acc = fma(v * v, D[n], acc);
+  }
+  const double tot = block_sum_ordered(acc, sh);
+  if (threadIdx.x == 0) part[blockIdx.x] = tot;
+}
+__global__ void __launch_bounds__(kQuadThreads) k_quad_final(int nparts, const double* part, double* out) {
+  __shared__ double sh[kQuadThreads];
+  const int per = (nparts + kQuadThreads - 1) / kQuadThreads;
+  double acc = 0.0;
+  for (int i = threadIdx.x * per; i < min(nparts, (threadIdx.x + 1) * per); ++i) acc += part[i];
+  const double tot = block_sum_ordered(acc, sh);
+  if (threadIdx.x == 0) out[0] = tot;
+}
+}  // namespace
+
+size_t quad_scratch_doubles() { return kQuadBlocks; }
+
+cudaError_t launch_quad(int N, const double* xd, const double* D, double* part, double* out, cudaStream_t stream) {
+  k_quad_partial<<<kQuadBlocks, kQuadThreads, 0, stream>>>(N, xd, D, part);
+  k_quad_final<<<1, kQuadThreads, 0, stream>>>(kQuadBlocks, part, out);
+  return cudaGetLastError();
+}
+}  // namespace cel

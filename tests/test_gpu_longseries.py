@@ -36,6 +36,11 @@ def test_host_api_uses_chunked_path(N, Jr, Jc, nrhs):
     assert rel_inf(s.dot_L(rhs), chk.dot_L(f, rhs)) < RTOL_SOLVE
     # second call reuses the cached chunk maps
     assert rel_inf(s.solve(rhs), chk.solve(f, rhs)) < RTOL_SOLVE
+    # y^T K^-1 y (cholesky.h:326-401): chunked forward sweep + ordered reduction
+    n1 = s.launch_count()
+    q, qref = s.dot_solve(y), chk.dot_solve(f, y)
+    assert s.launch_count() - n1 > 2
+    assert abs(q - qref) / max(abs(qref), N) < 1e-10
 
 
 def test_device_api_and_span_protocol_on_one_gpu():
