@@ -221,6 +221,37 @@ int cel_grad_log_likelihood_static_scratch(int N, int Jr, int Jc, const double* 
                                            double* d_val, double* d_grad, int32_t* d_status,
                                            void* cuda_stream);
 
+/* ---- kernel terms on the device --------------------------------------------
+ * Parameter vectors -> coefficient rows for a SUM of celerite terms (terms.py:280-324), and the
+ * transposed Jacobian that turns the coefficient gradient of cel_batched_grad_log_likelihood into
+ * the gradient with respect to the parameters (the reference: autograd, terms.py:197-215;
+ * celerite.py:290-297).  Parameters are the reference's, in its order:
+ *   CEL_TERM_JITTER   (log_sigma)                 terms.py:327-357   jitter += exp(2 log_sigma)
+ *   CEL_TERM_REAL     (log_a, log_c)              terms.py:360-391
+ *   CEL_TERM_COMPLEX3 (log_a, log_c, log_d)       terms.py:394-451, b = 0
+ *   CEL_TERM_COMPLEX4 (log_a, log_b, log_c, log_d)
+ *   CEL_TERM_SHO      (log_S0, log_Q, log_omega0) terms.py:464-517, Q >= 1/2: one complex term
+ *   CEL_TERM_SHO_OVERDAMPED (same parameters), Q < 1/2: two real terms
+ *   CEL_TERM_MATERN32 (log_sigma, log_rho), eps[t] terms.py:520-566
+ * A row is [jitter, a_real.., c_real.., a_comp.., b_comp.., c_comp.., d_comp..], terms in the order
+ * given.  The layout must be the same for the whole batch, so the two SHO regimes are two kinds; a
+ * series whose Q is on the other side gets d_status = 1 and NaN coefficients.  eps may be NULL
+ * (0.01 for every Matern term).  Device pointers; work is queued on the handle's stream. */
+#define CEL_TERM_JITTER 0
+#define CEL_TERM_REAL 1
+#define CEL_TERM_COMPLEX3 2
+#define CEL_TERM_COMPLEX4 3
+#define CEL_TERM_SHO 4
+#define CEL_TERM_SHO_OVERDAMPED 5
+#define CEL_TERM_MATERN32 6
+int cel_term_layout(int nterms, const int* kinds, int* n_params, int* Jr, int* Jc);
+int cel_term_coefficients(cel_solver* s, int nterms, const int* kinds, const double* eps, int64_t B,
+                          const double* d_params, int64_t param_stride, double* d_coeffs,
+                          int64_t coeff_stride, int32_t* d_status);
+int cel_term_backprop(cel_solver* s, int nterms, const int* kinds, const double* eps, int64_t B,
+                      const double* d_params, int64_t param_stride, const double* d_grad_coeffs,
+                      int64_t grad_coeff_stride, double* d_grad_params, int64_t grad_param_stride);
+
 /* Number of kernels this handle has launched since creation (bench.py's gpu_launches). */
 int64_t cel_launch_count(const cel_solver* s);
 
