@@ -21,6 +21,7 @@ namespace {
 constexpr int kSegmentedMinN = 65536;
 constexpr double kSegmentTol = 1e-17;
 constexpr double kSegmentMismatchTol = 1e-12;
+constexpr double kSpanMismatchTol = 1e-10;   // gradient spans: forward state and adjoint carries at the common edge
 
 // seg = [begin, first owned, end) per segment, or empty when segmenting does not pay
 void plan_segments(int J, int Jr, const double* c_real, int Jc, const double* c_comp, int N, const double* x,
@@ -60,6 +61,49 @@ void plan_segments(int J, int Jr, const double* c_real, int Jc, const double* c_
     work += end - begin;
   }
   if (work > 3LL * N) seg.clear();                       // uneven sampling made the halos long: not worth it
+}
+
+// spans for the gradient of one long series: [begin, first owned, end of owned, end).  The forward
+// solve vector f and the adjoint carry gbar forget like prod(phi) (not phi^2), so both halos span
+// ln(1/kSegmentTol) / c_min; the adjoint needs its halo on the right.
+void plan_grad_spans(int J, int Jr, const double* c_real, int Jc, const double* c_comp, int N, const double* x,
+                     std::vector<int>& span) {
+  span.clear();
+  double c_min = INFINITY;
+  for (int j = 0; j < Jr; ++j) c_min = std::fmin(c_min, c_real[j]);
+  for (int j = 0; j < Jc; ++j) c_min = std::fmin(c_min, c_comp[j]);
+  if (!(c_min > 0.0) || !std::isfinite(c_min)) return;
+  double reach = std::log(1.0 / kSegmentTol) / c_min;
+  if (const char* e = getenv("CEL_SEGMENT_HALO_SCALE")) reach *= atof(e);
+  int L = 1;
+  while (L < J && L < 32) L <<= 1;
+  const int slots = 148 * 8 * (32 / L);
+  const double dt = (x[N - 1] - x[0]) / (double)(N - 1);
+  if (!(dt > 0.0)) return;
+  const double halo_steps = reach / dt;
+  long long len = (N + slots - 1) / slots;
+  if (len < 1024) len = 1024;
+  if ((double)len < halo_steps) len = (long long)halo_steps;
+  len = (len + 15) / 16 * 16;
+  const int K = (int)((N + len - 1) / len);
+  if (K < 16) return;
+  span.reserve(4 * (size_t)K);
+  long long work = 0;
+  for (int c = 0; c < K; ++c) {
+    const int own0 = (int)(c * len), own1 = (int)std::min<long long>(N, own0 + len);
+    int begin = 0, end = N;
+    if (own0 > 0) {
+      begin = (int)(std::lower_bound(x, x + own0, x[own0] - reach) - x);
+      if (begin > 0) --begin;
+    }
+    if (own1 < N) {
+      end = (int)(std::upper_bound(x + own1, x + N, x[own1 - 1] + reach) - x);
+      if (end < N) ++end;
+    }
+    span.push_back(begin); span.push_back(own0); span.push_back(own1); span.push_back(end);
+    work += end - begin;
+  }
+  if (work > 4LL * N) span.clear();
 }
 
 int pack_coeffs(cel_solver* s, double jitter, int Jr, const double* a_real, const double* c_real, int Jc,
@@ -439,9 +483,7 @@ int cel_grad_log_likelihood(cel_solver* s, double jitter, int Jr, const double* 
   const int seg = cel::grad_default_segment(N);
   const size_t nscr = cel::grad_scratch_doubles(1, N, J, seg);
   const size_t nin = 3 * (size_t)N + (A ? N : 0) + 2 * (size_t)Jg * N + P;
-  CEL_CUDA_TRY(s, s->scratch0.reserve(dbytes(nscr)));
   CEL_CUDA_TRY(s, s->scratch1.reserve(dbytes(nin)));
-  CEL_CUDA_TRY(s, s->scratch2.reserve(dbytes((size_t)P + 8)));
   double* dx = s->scratch1.d();
   double* dy = dx + N;
   double* dd = dy + N;
@@ -458,11 +500,60 @@ int cel_grad_log_likelihood(cel_solver* s, double jitter, int Jr, const double* 
     CEL_CUDA_TRY(s, cudaMemcpyAsync(dU, U, dbytes((size_t)Jg * N), cudaMemcpyHostToDevice, st));
     CEL_CUDA_TRY(s, cudaMemcpyAsync(dV, V, dbytes((size_t)Jg * N), cudaMemcpyHostToDevice, st));
   }
+  // Long series without general rows: time spans side by side (grad.cu, SPAN), each behind a warm-up
+  // halo and in front of a cool-down halo; neighbouring spans are compared at their common edge
+  // and the series is redone serially if they disagree.
+  if (Jg == 0 && !A && N >= kSegmentedMinN) {
+    std::vector<int> span;
+    plan_grad_spans(J, Jr, c_real, Jc, c_comp, N, x, span);
+    if (!span.empty()) {
+      const int K = (int)(span.size() / 4);
+      int maxlen = 0;
+      for (int c = 0; c < K; ++c) maxlen = std::max(maxlen, span[4 * c + 3] - span[4 * c]);
+      const int sseg = cel::grad_tuned_segment(K, maxlen, J, false);
+      const size_t sscr = cel::grad_scratch_doubles(K, maxlen, J, sseg);
+      const int ER = 2 * J + 1;
+      // scratch2: [K] val | [K][P] grad | [K][4][ER] edges | [3+P] result | ints: [4K] span, [K] status
+      const size_t nd = (size_t)K * (1 + P + 4 * ER) + 3 + P;
+      CEL_CUDA_TRY(s, s->scratch0.reserve(dbytes(sscr)));
+      CEL_CUDA_TRY(s, s->scratch2.reserve(dbytes(nd) + sizeof(int) * (size_t)5 * K));
+      double* d_val = s->scratch2.d();
+      double* d_grad = d_val + K;
+      double* d_edge = d_grad + (size_t)K * P;
+      double* d_res = d_edge + (size_t)K * 4 * ER;
+      int* d_span = reinterpret_cast<int*>(d_res + 3 + P);
+      CEL_CUDA_TRY(s, cudaMemsetAsync(d_edge, 0, dbytes((size_t)K * 4 * ER), st));
+      CEL_CUDA_TRY(s, cudaMemcpyAsync(d_span, span.data(), sizeof(int) * span.size(), cudaMemcpyHostToDevice, st));
+      cel::GradArgs sa{};
+      sa.B = K; sa.N = N; sa.stride = 0; sa.Jr = Jr; sa.Jc = Jc; sa.Jg = 0;
+      sa.coeffs = dc; sa.coeff_stride = 0;
+      sa.t = dx; sa.diag = dd; sa.y = dy;
+      sa.out_val = d_val; sa.out_grad = d_grad; sa.status = d_span + 4 * K;
+      sa.scratch = s->scratch0.d(); sa.seg = sseg;
+      sa.span = d_span; sa.span_nseg_max = (maxlen + sseg - 1) / sseg; sa.span_edge = d_edge;
+      CEL_CUDA_TRY(s, cel::launch_grad_spans(sa, st));
+      CEL_CUDA_TRY(s, cel::launch_grad_span_finish(sa, d_res, st));
+      s->launches += 2;
+      if (s->pinned_cap < dbytes((size_t)P + 3)) CEL_FAIL(s, CEL_UNSUPPORTED, "too many coefficients");
+      CEL_CUDA_TRY(s, cudaMemcpyAsync(res, d_res, dbytes((size_t)P + 3), cudaMemcpyDeviceToHost, st));
+      CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
+      if (res[2] != 0.0) CEL_FAIL(s, CEL_NOT_POSITIVE_DEFINITE, "failed to factorize or solve matrix");
+      if (res[1] <= kSpanMismatchTol) {
+        *val = res[0];
+        for (int i = 0; i < P; ++i) grad[i] = res[3 + i];
+        return CEL_OK;
+      }
+      // the spans had not converged onto each other: serial sweep below
+    }
+  }
+
   cel::GradArgs a{};
   a.B = 1; a.N = N; a.stride = N; a.Jr = Jr; a.Jc = Jc; a.Jg = Jg;
   a.coeffs = dc; a.coeff_stride = P;
   a.t = dx; a.diag = dd; a.y = dy;
   a.A = A ? dA : nullptr; a.U = Jg > 0 ? dU : nullptr; a.V = Jg > 0 ? dV : nullptr;
+  CEL_CUDA_TRY(s, s->scratch0.reserve(dbytes(nscr)));
+  CEL_CUDA_TRY(s, s->scratch2.reserve(dbytes((size_t)P + 8)));
   double* dout = s->scratch2.d();
   a.out_val = dout; a.out_grad = dout + 2;
   a.status = reinterpret_cast<int*>(dout + 1);

@@ -61,7 +61,11 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-template <int JP>
+// SPAN: the groups are time spans of ONE series (GradArgs::span), each sweeping
+// [begin, end) forward from a cold start and the adjoint from `end` down to its first owned step;
+// only owned steps contribute to the value and the gradient sums.  Spans differ in length, so
+// every warp-level primitive names the group's own lanes.
+template <int JP, bool SPAN = false>
 __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   using C = GradCfg<JP>;
   constexpr int L = C::L, G = C::G, T = C::T, JJ = C::JJ, E = C::E;
@@ -70,6 +74,8 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   const long long b = (long long)blockIdx.x * G + g;
   const bool active = b < a.B;
   const long long bb = active ? b : a.B - 1;
+  const long long sb = SPAN ? 0 : bb;
+  const unsigned gmask = SPAN ? group_mask<L>(g) : kFull;
 
   double* base = smem + (size_t)g * C::kGroup;
   double* t_s = base;                    // [T+1]
@@ -85,24 +91,31 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   double* r_s = cf_s + C::kCoef;         // [6][JP]
 
   const int N = a.N, Jr = a.Jr, Jc = a.Jc, Jg = a.Jg, J = Jr + 2 * Jc + Jg, P = 1 + 2 * Jr + 4 * Jc;
-  const int Cseg = a.seg, nseg = (N + Cseg - 1) / Cseg;
-  const double* tp = a.t + bb * a.stride;
-  const double* dp = a.diag + bb * a.stride;
-  const double* yp = a.y + bb * a.stride;
-  const double* Ap = a.A ? a.A + bb * a.stride : nullptr;
-  const double* Up = a.U ? a.U + bb * a.stride * Jg : nullptr;
-  const double* Vp = a.V ? a.V + bb * a.stride * Jg : nullptr;
+  // steps [n_lo, n_hi) are swept; [own0, own1) contribute (whole series: everything)
+  const int n_lo = SPAN ? a.span[4 * bb] : 0, own0 = SPAN ? a.span[4 * bb + 1] : 0;
+  const int own1 = SPAN ? a.span[4 * bb + 2] : N, n_hi = SPAN ? a.span[4 * bb + 3] : N;
+  const int Cseg = a.seg, nseg = (n_hi - n_lo + Cseg - 1) / Cseg;
+  const int nseg_slot = SPAN ? a.span_nseg_max : nseg;   // scratch slots are sized for the longest span
+  const double* tp = a.t + sb * a.stride;
+  const double* dp = a.diag + sb * a.stride;
+  const double* yp = a.y + sb * a.stride;
+  const double* Ap = a.A ? a.A + sb * a.stride : nullptr;
+  const double* Up = a.U ? a.U + sb * a.stride * Jg : nullptr;
+  const double* Vp = a.V ? a.V + sb * a.stride * Jg : nullptr;
   // idle groups shadow the last series but must not share its scratch: give them their own slot
-  double* ckpt = a.scratch + (size_t)((long long)blockIdx.x * G + g) * ((size_t)(nseg + Cseg) * E);
-  double* tape = ckpt + (size_t)nseg * E;
+  double* ckpt = a.scratch + (size_t)((long long)blockIdx.x * G + g) * ((size_t)(nseg_slot + Cseg) * E);
+  double* tape = ckpt + (size_t)nseg_slot * E;
+  // span edges kept for the consistency check: 4 records of 2J+1 doubles (see launch_grad_spans)
+  const int ER = 2 * J + 1;
+  double* edge = SPAN ? a.span_edge + (size_t)bb * 4 * ER : nullptr;
 
   {
-    const double* row = a.coeffs + bb * a.coeff_stride;
+    const double* row = a.coeffs + sb * a.coeff_stride;
     for (int i = k; i < P; i += L) cf_s[i] = row[i];
     for (int i = k; i < 4 * T * JP; i += L) phi_s[i] = 0.0;
     for (int i = k; i < 4 * JP; i += L) x_s[i] = 0.0;
   }
-  __syncwarp();
+  __syncwarp(gmask);
   const double jitter = cf_s[0];
   const double* a_real = cf_s + 1;
   const double* c_real = a_real + Jr;
@@ -153,7 +166,7 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
       const int i = k + q * L;
       if (i < T) { t_s[1 + i] = pt[q]; d_s[i] = pd[q]; y_s[i] = py[q]; }
     }
-    __syncwarp();
+    __syncwarp(gmask);
     pf_n0 = -1;
     if (next_n0 >= 0) prefetch(next_n0);
     if (fast_math) {   // four independent (step, term) items per lane, branch-free routines
@@ -240,7 +253,7 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
       ut_s[i * JP + r0] = ug;
       v_s[i * JP + r0] = __ldg(Vp + (size_t)(n0 + i) * Jg + q);
     }
-    __syncwarp();
+    __syncwarp(gmask);
   };
 
   // ---- forward state (the low-latency form of coop.cu: S, D W, 1/D, f, x/D) -------------------
@@ -305,8 +318,8 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
       }
       const double av = (acc0 + acc1) + (acc2 + acc3);
       double red_a = utk * av, red_f = utk * f_own, red_b = utk * dw_own;
-      group_sum2<L>(red_a, red_f);                     // known early: off the scalar chain
-      red_b = group_sum<L>(red_b);                     // the one reduction on the chain
+      group_sum2_masked<L>(red_a, red_f, gmask);                     // known early: off the scalar chain
+      red_b = group_sum_masked<L>(red_b, gmask);                     // the one reduction on the chain
       const double tb = red_b * r_prev;
       const double Dn = ((d_s[i] + aconst) - red_a) - red_b * tb;
       const double x = (y_s[i] - red_f) - red_b * s_prev;
@@ -320,33 +333,39 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
       }
       s_prev = r * x;
       if (ACCUM) {
-        fail = (Dn < 0.0 && fail == 0) ? n + 1 : fail;   // cholesky.h:176
-        quad = fma(x, s_prev, quad);
-        ld.add(Dn);
+        const bool own = !SPAN || (n >= own0 && n < own1);
+        fail = (own && Dn < 0.0 && fail == 0) ? n + 1 : fail;   // cholesky.h:176
+        quad = fma(own ? x : 0.0, s_prev, quad);
+        ld.add(own ? Dn : 1.0);
+        if (SPAN && active && (n == own0 - 1 || n == own1 - 1)) {   // W, D at both edges of the owned range
+          double* er = edge + (n == own0 - 1 ? 0 : 1) * ER;
+          if (k < J) er[k] = dw * r;
+          if (k == 0) er[J] = Dn;
+        }
       }
       dw_own = dw;
       r_prev = r;
       Dprev = Dn;
       xprev = x;
-      __syncwarp();
+      __syncwarp(gmask);
     }
     if (ACCUM) ld.renorm();
   };
   // make the exchange row hold (D W)_{n-1} for the step that comes next (after a state reload)
   auto publish_W = [&](int n_next) {
     if (row_ok) x_s[(n_next & 1) * 2 * JP + kk] = dw_own;
-    __syncwarp();
+    __syncwarp(gmask);
   };
 
   // =========================== phase A: forward sweep, checkpoints =============================
   reset_state();
-  publish_W(0);
+  publish_W(n_lo);
   for (int s = 0; s < nseg; ++s) {
-    const int seg0 = s * Cseg, seg1 = min(N, seg0 + Cseg);
+    const int seg0 = n_lo + s * Cseg, seg1 = min(n_hi, seg0 + Cseg);
     store_state(ckpt + (size_t)s * E);
     for (int n0 = seg0; n0 < seg1; n0 += T) {
       const int nt = min(T, seg1 - n0);
-      const int nx = n0 + T < seg1 ? n0 + T : (seg1 < N ? seg1 : -1);
+      const int nx = n0 + T < seg1 ? n0 + T : (seg1 < n_hi ? seg1 : -1);
       load_tile(n0, nt, nx);
       forward_tile(n0, nt, false, 0, true);
     }
@@ -361,25 +380,27 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   // tape scalars are fetched ahead of their use: two steps ahead while registers allow
   constexpr bool DEEP = JP <= 16;
 
-  __syncwarp();
+  __syncwarp(gmask);
   for (int s = nseg - 1; s >= 0; --s) {
-    const int seg0 = s * Cseg, seg1 = min(N, seg0 + Cseg);
+    const int seg0 = n_lo + s * Cseg, seg1 = min(n_hi, seg0 + Cseg);
+    if (SPAN && seg1 <= own0) break;                   // warm-up only: nothing below contributes
+    const int adj_lo = SPAN ? max(seg0, own0) : seg0;  // the adjoint stops at the first owned step
     const double* crec = ckpt + (size_t)s * E;
     // ---- recompute the segment forward, taping every step ----
-    __syncwarp();
+    __syncwarp(gmask);
     load_state(crec);
     publish_W(seg0);
     int tile_n0 = -1;
     for (int n0 = seg0; n0 < seg1; n0 += T) {
       const int nt = min(T, seg1 - n0);
       // ahead: the next tile; from the last tile, the one the adjoint walks into after it
-      const int nx = n0 + T < seg1 ? n0 + T : (n0 > seg0 ? n0 - T : (seg0 > 0 ? seg0 - Cseg : -1));
+      const int nx = n0 + T < seg1 ? n0 + T : (n0 > seg0 ? n0 - T : (seg0 > n_lo ? seg0 - Cseg : -1));
       load_tile(n0, nt, nx);
       forward_tile(n0, nt, true, seg0, false);
       tile_n0 = n0;                                    // the adjoint starts in this tile
     }
     __threadfence_block();
-    __syncwarp();
+    __syncwarp(gmask);
 
     // ---- adjoint over the segment, n = seg1-1 .. seg0 ----
     // tape block of step n -> ring slot n % RD (coalesced cp.async); one group per call, empty
@@ -404,12 +425,12 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
     double Wn, fn, Dn, xn, Wm, fm, Dm, xm, Wq = 0.0, fq = 0.0, Dq = 0.0, xq = 0.0;
     load_rec(seg1 - 1, Wn, fn, Dn, xn);
     if (DEEP) load_rec(seg1 - 2, Wm, fm, Dm, xm);       // seg1-2 >= seg0-1
-    for (int n = seg1 - 1; n >= seg0; --n) {
+    for (int n = seg1 - 1; n >= adj_lo; --n) {
       // generators of the tile containing n (tiles are aligned to the segment start)
       const int tn0 = seg0 + ((n - seg0) / T) * T;
       if (tn0 != tile_n0) {
         tile_n0 = tn0;
-        load_tile(tn0, min(T, seg1 - tn0), tn0 > seg0 ? tn0 - T : (seg0 > 0 ? seg0 - Cseg : -1));
+        load_tile(tn0, min(T, seg1 - tn0), tn0 > seg0 ? tn0 - T : (seg0 > n_lo ? seg0 - Cseg : -1));
       }
       const int i = n - tile_n0;
       stage_block(n - (C::RD - 1));
@@ -423,23 +444,28 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
       const double vpart = row_ok ? v_s[i * JP + partner] : 0.0;
       const double tn = t_s[1 + i], dxn = tn - t_s[i];
       const double Wk = row_ok ? Wn : 0.0;
+      const bool own = !SPAN || (n >= own0 && n < own1);
+      const double om = own ? 1.0 : 0.0;               // cool-down steps feed the carries only
+      if (SPAN && active && n == own1 - 1 && k < J) {  // adjoint carries entering the last owned step
+        edge[2 * ER + k] = gbar; edge[2 * ER + J + k] = PbW;
+      }
 
       const double r = fast_rcp_nocheck(Dn);
       const double xr = xn * r;
       double red0 = Wk * PbW, red1 = gbar * Wk;
-      group_sum2<L>(red0, red1);
+      group_sum2_masked<L>(red0, red1, gmask);
       // sum_k Wbar_k W_k = 2 D red0 + x red1: no third reduction
       const double Dbar = fma(-xr, red1, fma(0.5 * xr, xr, -0.5 * r)) - red0;
       const double xbar = red1 - xr;
       const double Wbar = 2.0 * Dn * PbW + gbar * xn;
       const double w = Wbar * r;                          // also vbar_k
-      R6 = fma(tn * w, vpart, R6);
-      sumA += Dbar;
+      R6 = fma(om * tn * w, vpart, R6);
+      sumA = fma(om, Dbar, sumA);
       const int par = n & 1;
       double* xch = x_s + par * 2 * JP;
       if (row_ok) { xch[kk] = w; xch[JP + kk] = Wm; }
       cp_async_wait<C::RD - 1>();                         // block n: requested RD-1 steps ago
-      __syncwarp();
+      __syncwarp(gmask);
       if (n > 0) {                                        // step 0 has no generators (cholesky.h:118-124)
         const double fbar = gbar - xbar * uk;
         const double gprev = row_ok ? fma(Wm, xm, fm) : 0.0;
@@ -468,8 +494,8 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
           else aP3 = fma(pn, wmj, aP3);
         }
         PbW = row_ok ? (aP0 + aP1) + (aP2 + aP3) : 0.0;
-        const double ubar = -xbar * (row_ok ? fn : 0.0) - (aSw + 2.0 * Dbar * aSu);
-        const double phibar = fma(2.0, aphi0 + aphi1, fbar * gprev);
+        const double ubar = om * (-xbar * (row_ok ? fn : 0.0) - (aSw + 2.0 * Dbar * aSu));
+        const double phibar = om * fma(2.0, aphi0 + aphi1, fbar * gprev);
         R1 = fma(ubar, vk, R1);
         R2 = fma(ubar, vpart, R2);
         R3 = fma(phibar, -dxn * phk, R3);
@@ -478,8 +504,11 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
       }
       Wn = Wm; fn = fm; Dn = Dm; xn = xm;
       if (DEEP) { Wm = Wq; fm = fq; Dm = Dq; xm = xq; }
-      __syncwarp();
+      __syncwarp(gmask);
     }
+  }
+  if (SPAN && active && k < J) {                       // adjoint carries entering step own0 - 1
+    edge[3 * ER + k] = gbar; edge[3 * ER + J + k] = PbW;
   }
 
   // ---- combine the per-row sums into the reference's gradient vector (solver.cpp:392-434) ------
@@ -487,7 +516,7 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
     r_s[0 * JP + kk] = R1; r_s[1 * JP + kk] = R2; r_s[2 * JP + kk] = R3;
     r_s[3 * JP + kk] = R4; r_s[4 * JP + kk] = R5; r_s[5 * JP + kk] = R6;
   }
-  __syncwarp();
+  __syncwarp(gmask);
   if (active) {
     const double nan = __longlong_as_double(0x7ff8000000000000LL);
     double* gout = a.out_grad + (size_t)b * P;
@@ -531,6 +560,69 @@ cudaError_t launch_one(const GradArgs& a, cudaStream_t stream) {
   const long long grid = (a.B + C::G - 1) / C::G;
   kern<<<(unsigned)grid, kWarp, C::smem, stream>>>(a);
   return cudaGetLastError();
+}
+
+template <int JP>
+cudaError_t launch_span(const GradArgs& a, cudaStream_t stream) {
+  using C = GradCfg<JP>;
+  auto kern = k_grad_coop<JP, true>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::smem);
+  if (e != cudaSuccess) return e;
+  const long long grid = (a.B + C::G - 1) / C::G;
+  kern<<<(unsigned)grid, kWarp, C::smem, stream>>>(a);
+  return cudaGetLastError();
+}
+
+// partial results of the spans -> value, gradient (fixed summation order), worst edge mismatch
+__global__ void __launch_bounds__(256) k_grad_span_finish(GradArgs a, double* result) {
+  __shared__ double s_max[256];
+  const int J = a.Jr + 2 * a.Jc + a.Jg, P = 1 + 2 * a.Jr + 4 * a.Jc, tid = threadIdx.x;
+  const int K = (int)a.B, ER = 2 * J + 1;
+  // value and gradient entries: one thread each, spans added in order
+  for (int e = tid; e < P + 1; e += 256) {
+    double acc = 0.0;
+    if (e == 0) { for (int c = 0; c < K; ++c) acc += a.out_val[c]; result[0] = acc; }
+    else { for (int c = 0; c < K; ++c) acc += a.out_grad[(size_t)c * P + (e - 1)]; result[3 + e - 1] = acc; }
+  }
+  double worst = 0.0;
+  int fail = 0;
+  for (int c = tid; c < K; c += 256) {
+    if (a.status[c] != 0) fail = 1;
+    if (c + 1 < K) {
+      const double* me = a.span_edge + (size_t)c * 4 * ER;
+      const double* up = a.span_edge + (size_t)(c + 1) * 4 * ER;
+      // forward: my values at my last owned step (record 1) against my right neighbour's last
+      // warm-up step (its record 0) -- the same step, two histories
+      double wmax = 0.0, dmax = 0.0;
+      for (int j = 0; j < J; ++j) { wmax = fmax(wmax, fabs(me[ER + j])); dmax = fmax(dmax, fabs(up[j] - me[ER + j])); }
+      double rel = dmax / fmax(wmax, 1e-300);
+      rel = fmax(rel, fabs(up[J] - me[ER + J]) / fmax(fabs(me[ER + J]), 1e-300));
+      // adjoint: my carries entering my last owned step (record 2, behind my cool-down) against
+      // the neighbour's carries leaving its first owned step (its record 3)
+      double gmax = 0.0, gd = 0.0, pmax = 0.0, pd = 0.0;
+      for (int j = 0; j < J; ++j) {
+        gmax = fmax(gmax, fabs(up[3 * ER + j])); gd = fmax(gd, fabs(up[3 * ER + j] - me[2 * ER + j]));
+        pmax = fmax(pmax, fabs(up[3 * ER + J + j])); pd = fmax(pd, fabs(up[3 * ER + J + j] - me[2 * ER + J + j]));
+      }
+      rel = fmax(rel, gd / fmax(gmax, 1e-300));
+      rel = fmax(rel, pd / fmax(pmax, 1e-300));
+      if (!(rel <= worst)) worst = rel;
+    }
+  }
+  s_max[tid] = fail ? __longlong_as_double(0x7ff0000000000000LL) : worst;   // +inf marks a failed span
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (tid < o && !(s_max[tid + o] <= s_max[tid])) s_max[tid] = s_max[tid + o];
+    __syncthreads();
+  }
+  if (tid == 0) {
+    const bool failed = isinf(s_max[0]);
+    // a failed span (negative pivot in its owned range) is a failed series, not a mismatch
+    double w = 0.0;
+    if (!failed) w = s_max[0];
+    result[1] = w;
+    result[2] = failed ? 3.0 : 0.0;
+  }
 }
 
 int grad_jp(int J) { return J <= 2 ? 2 : J <= 4 ? 4 : J <= 6 ? 6 : J <= 8 ? 8 : J <= 12 ? 12 : J <= 16 ? 16 : J <= 24 ? 24 : 32; }
@@ -580,6 +672,26 @@ size_t grad_scratch_doubles(long long B, int N, int J, int seg) {
   const size_t E = (size_t)JP * JP + 2 * JP + 2;
   const size_t nseg = (size_t)(N + seg - 1) / seg;
   return (size_t)groups * (nseg + seg) * E;
+}
+
+cudaError_t launch_grad_spans(const GradArgs& a, cudaStream_t stream) {
+  const int J = a.Jr + 2 * a.Jc + a.Jg;
+  if (!a.span || !a.span_edge || a.Jg != 0 || J < 1 || J > kCoopMaxJ || a.seg < 1) return cudaErrorInvalidValue;
+  switch (grad_jp(J)) {
+    case 2: return launch_span<2>(a, stream);
+    case 4: return launch_span<4>(a, stream);
+    case 6: return launch_span<6>(a, stream);
+    case 8: return launch_span<8>(a, stream);
+    case 12: return launch_span<12>(a, stream);
+    case 16: return launch_span<16>(a, stream);
+    case 24: return launch_span<24>(a, stream);
+    default: return launch_span<32>(a, stream);
+  }
+}
+
+cudaError_t launch_grad_span_finish(const GradArgs& a, double* result, cudaStream_t stream) {
+  k_grad_span_finish<<<1, 256, 0, stream>>>(a, result);
+  return cudaGetLastError();
 }
 
 cudaError_t launch_grad_coop(const GradArgs& a, cudaStream_t stream) {

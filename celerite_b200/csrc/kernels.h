@@ -81,7 +81,19 @@ struct GradArgs {
   int* status;
   double* scratch;      // grad_scratch_doubles(B, N, J, seg) doubles
   int seg;              // checkpoint distance (multiple of 16)
+  // Time spans of ONE long series (launch_grad_spans): group b sweeps [span[4b], span[4b+3])
+  // forward from a cold start, runs the adjoint from the top down to span[4b+1], and counts only the
+  // steps [span[4b+1], span[4b+2]).  B = number of spans, stride = coeff_stride = 0; out_val,
+  // out_grad, out_logdet, out_quad, status hold per-span partial results.
+  const int* span;      // NULL for batches of whole series
+  int span_nseg_max;    // checkpoint slots per group = ceil(longest span / seg)
+  double* span_edge;    // [B][4][2J+1]: W,D at both edges of the owned range; adjoint carries at both
 };
+// One long series by time spans (grad.cu); launch_grad_span_finish adds the partial results up in
+// span order: result[0] = value, result[1] = worst relative mismatch between neighbouring spans
+// (forward state and adjoint carries), result[2] = status (as a double), result[3..3+P) = gradient.
+cudaError_t launch_grad_spans(const GradArgs& a, cudaStream_t stream);
+cudaError_t launch_grad_span_finish(const GradArgs& a, double* result, cudaStream_t stream);
 int grad_default_segment(int N);
 int grad_tuned_segment(long long B, int N, int J, bool lockstep);   // batch-aware (L2-resident tapes)
 size_t grad_scratch_doubles(long long B, int N, int J, int seg);

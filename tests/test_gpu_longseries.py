@@ -194,3 +194,32 @@ def test_segmented_compute_rejects_halos_that_did_not_converge(monkeypatch):
     assert s.launch_count() - n0 == 3
     assert abs(s.log_determinant() - f.log_det) / N < 1e-12
     assert _factor_diff(s.__getstate__(), f) < 1e-11
+
+
+def _grad_case(N, Jr, Jc, seed):
+    from celerite_b200 import solver
+    from tests.util import RTOL_GRAD, RTOL_SCALAR, rel_grad, rel_sum
+    p, y = _problem(N, Jr, Jc, seed=seed)
+    st, vref, gref = oracle.best().grad(p, y)
+    assert st == 0
+    s = solver.CholeskySolver()
+    n0 = s.launch_count()
+    val, g = s.grad_log_likelihood(p.jitter, p.a_real, p.c_real, p.a_comp, p.b_comp, p.c_comp, p.d_comp,
+                                   E0, E2, E2, p.x, y, p.diag)
+    assert rel_sum(val, vref, N) < RTOL_SCALAR
+    assert rel_grad(g, gref) < RTOL_GRAD, (g, gref)
+    return s.launch_count() - n0
+
+
+@pytest.mark.parametrize("N,Jr,Jc", [(150000, 0, 2), (100001, 1, 1), (200000, 0, 4)])
+def test_span_parallel_gradient_matches_reference(N, Jr, Jc):
+    """grad_log_likelihood of one long series runs as time spans side by side (grad.cu, SPAN):
+    value and gradient against the reference's automatic differentiation."""
+    assert _grad_case(N, Jr, Jc, seed=N + 7) == 2      # span sweep + finish
+
+
+def test_span_parallel_gradient_rejects_short_halos(monkeypatch):
+    """Halos cut to 2 % of the bound: neighbouring spans disagree at their common edge, the check
+    notices, and the serial sweep gives the answer (3 launches)."""
+    monkeypatch.setenv("CEL_SEGMENT_HALO_SCALE", "0.02")
+    assert _grad_case(120000, 0, 2, seed=31) == 3

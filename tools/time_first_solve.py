@@ -24,3 +24,7 @@ for rep in range(2):
     t0 = time.perf_counter(); S.compute(j, ar, cr, ac, bc, cc, dc, E0, E2, E2, b["t"][0], b["diag"][0]); t1 = time.perf_counter()
     q = S.dot_solve(b["y"][0]); t2 = time.perf_counter()
     print("host API: compute %.1f ms, dot_solve %.1f ms (log-likelihood of one N=%d series: %.1f ms)" % ((t1 - t0) * 1e3, (t2 - t1) * 1e3, N, (t2 - t0) * 1e3))
+for rep in range(2):
+    t0 = time.perf_counter()
+    v, g = S.grad_log_likelihood(j, ar, cr, ac, bc, cc, dc, E0, E2, E2, b["t"][0], b["y"][0], b["diag"][0])
+    print("host API: grad_log_likelihood of one N=%d series: %.1f ms (launches so far %d)" % (N, (time.perf_counter() - t0) * 1e3, S.launch_count()))
