@@ -57,6 +57,8 @@ SIGNATURES = {
     "cel_term_coefficients": (C.c_int, [_vp, C.c_int, _vp, _vp, C.c_int64, _vp, C.c_int64, _vp, C.c_int64, _vp]),
     "cel_term_backprop": (C.c_int, [_vp, C.c_int, _vp, _vp, C.c_int64, _vp, C.c_int64, _vp, C.c_int64, _vp, C.c_int64]),
     "cel_span_fold": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp]),
+    "cel_span_log_determinant": (C.c_int, [_vp, _vp]),
+    "cel_span_quad": (C.c_int, [_vp, _vp, _vp]),
     "cel_span_dims": (C.c_int, [_vp, _ip, _ip, _ip, _ip]),
     "cel_launch_count": (_i64, [_vp]),
 }

@@ -169,6 +169,28 @@ int cel_span_fold(cel_solver* s, int op, int nrhs, int world, int rank, const do
   return CEL_OK;
 }
 
+int cel_span_log_determinant(cel_solver* s, double* d_out) {
+  if (!s) return CEL_INVALID_ARGUMENT;
+  if (!s->computed) CEL_FAIL(s, CEL_NOT_COMPUTED, "you must call 'compute' first");
+  if (!d_out) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null pointer");
+  CEL_CUDA_TRY(s, cudaSetDevice(s->device));
+  CEL_CUDA_TRY(s, s->scratch2.reserve(dbytes(cel::quad_scratch_doubles())));
+  CEL_CUDA_TRY(s, cel::launch_quad(s->N - s->n_off, nullptr, s->D.d() + s->n_off, s->scratch2.d(), d_out, s->stream));
+  s->launches += 2;
+  return CEL_OK;
+}
+
+int cel_span_quad(cel_solver* s, const double* d_xd, double* d_out) {
+  if (!s) return CEL_INVALID_ARGUMENT;
+  if (!s->computed) CEL_FAIL(s, CEL_NOT_COMPUTED, "you must call 'compute' first");
+  if (!d_xd || !d_out) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null pointer");
+  CEL_CUDA_TRY(s, cudaSetDevice(s->device));
+  CEL_CUDA_TRY(s, s->scratch2.reserve(dbytes(cel::quad_scratch_doubles())));
+  CEL_CUDA_TRY(s, cel::launch_quad(s->N - s->n_off, d_xd, s->D.d() + s->n_off, s->scratch2.d(), d_out, s->stream));
+  s->launches += 2;
+  return CEL_OK;
+}
+
 int cel_span_dims(const cel_solver* s, int* n_local, int* J, int* nchunks, int* chunk_len) {
   if (!s) return CEL_INVALID_ARGUMENT;
   if (n_local) *n_local = s->N - s->n_off;

@@ -136,7 +136,8 @@ cudaError_t launch_dot(const DotArgs& a, cudaStream_t stream);
 cudaError_t launch_scale(int n, int N, const double* in, const double* D, double scalar, int mode, double* out,
                          cudaStream_t stream);
 // J == 0 "factorisation": D = diag + jitter (+A), logdet = sum log D   (cholesky.h:90-95)
-// sum_n xd_n^2 D_n (xd = x / D) in a fixed summation order; part: quad_scratch_doubles() doubles
+// sum_n xd_n^2 D_n (xd = x / D), or sum_n log D_n when xd is NULL, in a fixed summation order;
+// part: quad_scratch_doubles() doubles
 size_t quad_scratch_doubles();
 cudaError_t launch_quad(int N, const double* xd, const double* D, double* part, double* out, cudaStream_t stream);
 cudaError_t launch_jitter_only(int N, const double* diag, double jitter, double* D, double* logdet,

@@ -495,6 +495,7 @@ __device__ __forceinline__ double block_sum_ordered(double v, double* sh) {
   }
   return sh[0];
 }
+// xd == NULL: sum_n log D_n instead (the log-determinant of a span)
 __global__ void __launch_bounds__(kQuadThreads) k_quad_partial(int N, const double* xd, const double* D, double* part) {
   __shared__ double sh[kQuadThreads];
   // block b owns a contiguous slice; inside it the threads stride (coalesced)
@@ -502,8 +503,12 @@ __global__ void __launch_bounds__(kQuadThreads) k_quad_partial(int N, const doub
   const long long lo = per * blockIdx.x, hi = lo + per < N ? lo + per : N;
   double acc = 0.0;
   for (long long n = lo + threadIdx.x; n < hi; n += kQuadThreads) {
-    const double v = xd[n];
-    acc = fma(v * v, D[n], acc);
+    if (xd) {
+      const double v = xd[n];
+      acc = fma(v * v, D[n], acc);
+    } else {
+      acc += log(D[n]);
+    }
   }
   const double tot = block_sum_ordered(acc, sh);
   if (threadIdx.x == 0) part[blockIdx.x] = tot;

@@ -147,6 +147,35 @@ class LongSeries(object):
         _capi.check(rc, self._h)
         return out
 
+    def log_determinant(self, device=None):
+        """sum of log D over the span's own steps, as a 0-d device tensor (cholesky.h:208)."""
+        import torch
+        out = torch.empty((), dtype=torch.float64, device=device if device is not None else torch.device("cuda", torch.cuda.current_device()))
+        self._use_stream(out)
+        _capi.check(self._lib.cel_span_log_determinant(self._h, C.c_void_p(out.data_ptr())), self._h)
+        return out
+
+    def quad(self, xd):
+        """sum (x/D)^2 D over the span for xd = the result of a forward-solve sweep (1, N) or (N,)."""
+        import torch
+        xd = xd.reshape(-1).contiguous()
+        if xd.shape[0] != self.N:
+            raise RuntimeError("dimension mismatch")
+        out = torch.empty((), dtype=torch.float64, device=xd.device)
+        self._use_stream(xd)
+        _capi.check(self._lib.cel_span_quad(self._h, C.c_void_p(xd.data_ptr()), C.c_void_p(out.data_ptr())), self._h)
+        return out
+
+    def dot_solve(self, y):
+        """y^T K^-1 y (cholesky.h:326-401) for a device vector: forward sweep + ordered reduction."""
+        cols, _ = self._cols(y)
+        return self.quad(self.apply(OP_SOLVE_FORWARD, cols, None, reuse_summary=False))
+
+    def log_likelihood(self, y):
+        """-0.5 (y^T K^-1 y + log det K + N log 2 pi) as a 0-d device tensor (celerite.py:214-216)."""
+        import math
+        return -0.5 * (self.dot_solve(y) + self.log_determinant(y.device) + self.N * math.log(2.0 * math.pi))
+
     def fold(self, op, gathered, nrhs, world, rank):
         """Incoming carry of `rank` from the gathered summaries (world, nrhs + nb, J), on the device
         (one small kernel; `fold_carries` is the same arithmetic in torch)."""
@@ -207,3 +236,21 @@ class DistributedLongSeries(object):
         cols, squeeze = self.local._cols(z_local)
         out = self._sweep(OP_DOT_L, cols).transpose(0, 1)
         return out[:, 0] if squeeze else out
+
+    def log_determinant(self, device=None):
+        """log det K of the whole series: every rank's partial, added with one all-reduce."""
+        ld = self.local.log_determinant(device).reshape(1)
+        self.dist.all_reduce(ld, group=self.group)
+        return ld[0]
+
+    def dot_solve(self, y_local):
+        """y^T K^-1 y of the whole series: one forward sweep, partial sums added with one all-reduce."""
+        cols, _ = self.local._cols(y_local)
+        q = self.local.quad(self._sweep(OP_SOLVE_FORWARD, cols)).reshape(1)
+        self.dist.all_reduce(q, group=self.group)
+        return q[0]
+
+    def log_likelihood(self, y_local, N_total):
+        """celerite.py:214-216 for the whole series (N_total = its length over all ranks)."""
+        import math
+        return -0.5 * (self.dot_solve(y_local) + self.log_determinant(y_local.device) + N_total * math.log(2.0 * math.pi))

@@ -188,6 +188,12 @@ int cel_span_apply(cel_solver* s, int op, int nrhs, const double* d_in, const do
                    double* d_out, int reuse_summary);
 int cel_span_fold(cel_solver* s, int op, int nrhs, int world, int rank, const double* d_gathered,
                   double* d_carry_out);
+/* Scalars of a span, on the device (d_out: one double): sum of log D over the span's own steps
+ * (cholesky.h:208 restricted to the span), and sum (x/D)^2 D for d_xd = the output of a forward
+ * solve sweep (op 0) -- the span's share of y^T K^-1 y (cholesky.h:326-401).  Across ranks these
+ * are added with one all-reduce of a double each. */
+int cel_span_log_determinant(cel_solver* s, double* d_out);
+int cel_span_quad(cel_solver* s, const double* d_xd, double* d_out);
 int cel_span_dims(const cel_solver* s, int* n_local, int* J, int* nchunks, int* chunk_len);
 
 /* ---- gradient without any allocation (no counterpart in the reference) ----------------------

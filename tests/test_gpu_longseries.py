@@ -95,6 +95,14 @@ def test_device_api_and_span_protocol_on_one_gpu():
     lz = sweep(ls.OP_DOT_L, cols)
     ll = np.concatenate([t.cpu().numpy().T for t in lz], axis=0)
     assert rel_inf(ll, lref) < RTOL_SOLVE
+    # scalars: the spans' log-determinant partials and shares of y^T K^-1 y add up to the series'
+    ld = sum(float(L.log_determinant(dev)) for L in locs)
+    assert abs(ld - f.log_det) / N < 1e-12
+    quad = sum(float(L.quad(x[0])) for L, x in zip(locs, xd))
+    assert abs(quad - chk.dot_solve(f, y)) / N < 1e-10
+    assert abs(float(whole.log_determinant(dev)) - f.log_det) / N < 1e-12
+    llref = -0.5 * (chk.dot_solve(f, y) + f.log_det + N * np.log(2 * np.pi))
+    assert abs(float(whole.log_likelihood(bt[:, 0].contiguous())) - llref) / N < 1e-10
 
 
 def test_full_size_properties_cfg4_like():
