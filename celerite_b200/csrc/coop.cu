@@ -27,6 +27,8 @@
 // exchange -> update in sequence.
 //
 // For J <= 16 a warp carries 32/L series side by side.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "fastmath.cuh"
 #include "kernels.h"
@@ -49,14 +51,28 @@ struct CoopCfg {
   static constexpr int kX = 2 * JP;                 // D*W exchange, double buffered
   static constexpr int kOut = STORE ? T * JP + T : 0;  // W tile, D tile (materialising variant)
   static constexpr int kCoef = 4 * JP + 2;          // coefficient row (<= 1 + 4*Jc + 2*Jr <= 1 + 2J)
-  static constexpr int kGroup = kIn + kGen + kX + kOut + kCoef;
+  static constexpr int kSet = kIn + kGen;           // what the generator phase fills per tile
+  static constexpr int kGroup = kSet + kX + kOut + kCoef;
   static constexpr size_t smem = (size_t)G * kGroup * sizeof(double);
+  // producer/consumer variant: two tile sets
+  static constexpr int kGroupPC = 2 * kSet + kX + kOut + kCoef;
+  static constexpr size_t smemPC = (size_t)G * kGroupPC * sizeof(double);
 };
 
 // SEG: the groups are time segments of ONE series (BatchArgs::seg) instead of whole series; they
 // differ in length, so every warp-level primitive names the group's own lanes only.
-template <int JP, bool STORE, bool SEG = false>
-__global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
+//
+// PC: producer/consumer CTA of two warps.  With few series in flight the kernel is a chain of
+// latencies, and the generator phase (exp / sincos of a whole tile) was 37 % of it (ncu, J = 8);
+// warp 1 now fills tile i+1 (inputs + generators, double-buffered in shared memory) while warp 0
+// runs the serial recursion over tile i.  Hand-over through named barriers: full[buf] = 1 + buf,
+// empty[buf] = 3 + buf, 64 participants each.
+__device__ __forceinline__ void named_bar_sync(int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
+__device__ __forceinline__ void named_bar_arrive(int id) { asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory"); }
+
+template <int JP, bool STORE, bool SEG = false, bool PC = false>
+__global__ void __launch_bounds__(PC ? 2 * kWarp : kWarp) k_factor_coop(BatchArgs a) {
+  static_assert(!(SEG && PC), "segments differ in length: no CTA-wide barriers");
   using C = CoopCfg<JP, STORE>;
   constexpr int L = C::L, G = C::G, T = C::T;
   // (step, term) items a lane evaluates together in the generator phase: a tile holds 8 per lane
@@ -64,14 +80,16 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
   // J = 32 (registers)
   constexpr int kGenIlp = JP <= 16 ? 8 : 4;
   extern __shared__ __align__(16) double smem[];
-  const int lane = threadIdx.x, g = lane / L, k = lane % L;
+  const int lane = threadIdx.x & 31, g = lane / L, k = lane % L;
+  const bool do_fill = !PC || (threadIdx.x >> 5) == 1, do_serial = !PC || (threadIdx.x >> 5) == 0;
   const long long b = (long long)blockIdx.x * G + g;
   const bool active = b < a.B;
   const long long bb = active ? b : a.B - 1;
   const long long sb = SEG ? 0 : bb;            // series the group reads (segments share series 0)
   const unsigned gmask = SEG ? group_mask<L>(g) : kFull;
 
-  double* base = smem + (size_t)g * C::kGroup;
+  constexpr int NBUF = PC ? 2 : 1;
+  double* base = smem + (size_t)g * (PC ? C::kGroupPC : C::kGroup);
   double* t_s = base;                    // [T+1]  t_s[0] = previous time
   double* d_s = t_s + T + 2;             // [T]    diag + A
   double* y_s = d_s + T;                 // [T]
@@ -79,7 +97,7 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
   double* u_s = phi_s + T * JP;
   double* v_s = u_s + T * JP;
   double* ut_s = v_s + T * JP;           // [T][JP] phi o u
-  double* x_s = ut_s + T * JP;           // [2][JP] exchange of D*W
+  double* x_s = base + NBUF * C::kSet;   // [2][JP] exchange of D*W
   double* w_s = x_s + 2 * JP;            // [T][JP] W tile
   double* dd_s = w_s + T * JP;           // [T]     D tile
   double* cf_s = x_s + 2 * JP + C::kOut;  // coefficient row (w_s/dd_s exist only when STORE)
@@ -99,9 +117,10 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
     const double* row = a.coeffs + sb * a.coeff_stride;
     for (int i = k; i < P; i += L) cf_s[i] = row[i];
     for (int i = k; i < 4 * T * JP; i += L) phi_s[i] = 0.0;
+    if (PC) for (int i = k; i < 4 * T * JP; i += L) phi_s[C::kSet + i] = 0.0;
     for (int i = k; i < 2 * JP; i += L) x_s[i] = 0.0;
   }
-  __syncwarp(gmask);
+  if (PC) __syncthreads(); else __syncwarp(gmask);
   const double jitter = cf_s[0];
   const double* a_real = cf_s + 1;
   const double* c_real = a_real + Jr;
@@ -144,13 +163,20 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
       py[q] = yp ? __ldg(yp + n) : 0.0;
     }
   };
-  prefetch(nb);
+  if (do_fill) prefetch(nb);
   double t_last = __ldg(tp + max(nb - 1, 0));   // time of the step before the tile
 
   const int ntiles = (ne - nb + T - 1) / T;
   for (int tile = 0; tile < ntiles; ++tile) {
     const int n0 = nb + tile * T;
     const int nt = min(T, ne - n0);
+    if (PC) {                                          // this tile's set of buffers
+      const int off = (tile & 1) * C::kSet;
+      t_s = base + off; d_s = t_s + T + 2; y_s = d_s + T; phi_s = y_s + T;
+      u_s = phi_s + T * JP; v_s = u_s + T * JP; ut_s = v_s + T * JP;
+    }
+    if (do_fill) {
+    if (PC && tile >= 2) named_bar_sync(3 + (tile & 1));   // the consumer is done with this set
     // ---- inputs of this tile -> shared; start fetching the next tile ----------------------
     if (k == 0) t_s[0] = t_last;
 #pragma unroll
@@ -250,7 +276,11 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
       v_s[i * JP + r0] = __ldg(Vp + (size_t)(n0 + i) * Jg + q);
     }
     __syncwarp(gmask);
+    if (PC) { __threadfence_block(); named_bar_arrive(1 + (tile & 1)); }
+    }  // do_fill
 
+    if (do_serial) {
+    if (PC) named_bar_sync(1 + (tile & 1));            // the set is filled
     // ---- serial phase ---------------------------------------------------------------------
     for (int i = 0; i < nt; ++i) {
       const int par = (n0 + i) & 1;
@@ -331,9 +361,11 @@ __global__ void __launch_bounds__(kWarp) k_factor_coop(BatchArgs a) {
       }
       __syncwarp(gmask);
     }
+    if (PC && tile + 2 < ntiles) named_bar_arrive(3 + (tile & 1));
+    }  // do_serial
   }
 
-  if (active && k == 0) {
+  if (active && k == 0 && do_serial) {
     const double nan = __longlong_as_double(0x7ff8000000000000LL);
     const double logdet = fail ? nan : ld.value();
     const double q = fail ? nan : quad;
@@ -352,6 +384,16 @@ cudaError_t launch_one(const BatchArgs& a, cudaStream_t stream) {
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::smem);
   if (e != cudaSuccess) return e;
   const long long grid = (a.B + C::G - 1) / C::G;
+  // few series in flight (less than ~6 warps per SM): latency bound, split generator and recursion
+  static const bool no_pc = getenv("CEL_NO_PRODUCER_WARP") != nullptr;   // tuning knob
+  // (J <= 8: at J = 16 the two-warp form measured slower, 8.3 against 6.9 ms)
+  if (JP <= 8 && grid <= 148 * 6 && !no_pc) {
+    auto kpc = k_factor_coop<JP, STORE, false, true>;
+    e = cudaFuncSetAttribute(kpc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::smemPC);
+    if (e != cudaSuccess) return e;
+    kpc<<<(unsigned)grid, 2 * kWarp, C::smemPC, stream>>>(a);
+    return cudaGetLastError();
+  }
   kern<<<(unsigned)grid, kWarp, C::smem, stream>>>(a);
   return cudaGetLastError();
 }
