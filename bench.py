@@ -246,7 +246,22 @@ def run_cfg4(args):
     zb = torch.from_numpy(z[lo:hi]).to(dev)
     stream = torch.cuda.current_stream(dev)
 
+    # optional: the two calls recorded as CUDA graphs (one GPU only; measured 2.54 against 2.51 ms:
+    # nothing to gain when the sweeps themselves take 2 ms)
+    graphed = False
+    if getattr(args, "graph", False) and world == 1:
+        try:
+            g_solve = ls.CapturedSweep(eng, "solve", yb)
+            g_dotl = ls.CapturedSweep(eng, "dot_L", zb)
+            graphed = True
+        except Exception as e:   # noqa: BLE001
+            if rank == 0:
+                print("cuda graph capture failed (%s); timing plain calls" % e, file=sys.stderr)
+            torch.cuda.synchronize(dev)
+
     def step():
+        if graphed:
+            return g_solve(yb), g_dotl(zb)
         return eng.solve(yb), eng.dot_L(zb)
 
     def barrier():
@@ -273,7 +288,7 @@ def run_cfg4(args):
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
         ms = float(tms.item())
     clocks = sampler.stop() if rank == 0 else None
-    launches = (loc.launch_count() - l0)
+    launches = (g_solve.launches + g_dotl.launches) * args.steps if graphed else (loc.launch_count() - l0)
     value = 2.0 * N * J / (ms * 1e-3)
     # the dominant kernel alone: one chunk sweep (pass 1 of the forward solve; the call also runs
     # the two one-warp walk kernels of the middle stage, ~15 us)
@@ -298,7 +313,7 @@ def run_cfg4(args):
             "metric": metric, "value": value, "unit": "point-terms/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": desc, "N": N, "J": J, "halo": int(halo) if world > 1 else 0,
+            "config": {"workload": desc, "N": N, "J": J, "halo": int(halo) if world > 1 else 0, "cuda_graph": graphed,
                        "sharding": "time axis split into %d spans; one all-gather of (J^2+J) doubles per sweep" % world,
                        "inputs": "factor %.2f GB per rank, larger than the 126 MB L2" % ((hi - lo) * (3 * J + 1) * 8 / 1e9)},
             "roofline": {"bound": "hbm", "achieved": alg_sweep / (sweep_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
@@ -364,6 +379,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--jc", type=int, default=0, help="cfg3: number of SHO terms (J = 2*jc)")
     ap.add_argument("--no-grad", action="store_true", help="skip the extra log-lik+grad measurement")
+    ap.add_argument("--graph", action="store_true", help="cfg4, one GPU: time CUDA-graph replays of the two calls")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.workload == "cfg4":
