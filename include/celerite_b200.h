@@ -67,7 +67,14 @@ int cel_set_stream(cel_solver* s, void* cuda_stream);
 /* ---- CholeskySolver::compute (cholesky.h:41-210) ---------------------------------------------
  * Factorises K = L D L^T for one series and keeps phi,u,W,D on the device.  Returns
  * CEL_NOT_POSITIVE_DEFINITE as soon as some D_n < 0 was met; the handle is then "not computed"
- * exactly like the reference (cholesky.h:57). */
+ * exactly like the reference (cholesky.h:57).
+ * Long series (N >= 65536, no general rows) are factorised as time segments side by side, each
+ * from a cold start behind a warm-up halo of ln(1e17)/(2 c_min) in time; the result is checked
+ * against the neighbouring segment (1e-12) and the serial sweep is used instead when the check
+ * fails or when the terms decay too slowly for halos to pay.  cel_grad_log_likelihood does the
+ * same with halos on both sides (tolerance 1e-10); cel_solve, cel_dot_L and cel_dot_solve switch
+ * to chunked two-pass scans from N = 16384 on.  Results stay within the parity bars of the
+ * serial path (tests/test_gpu_longseries.py). */
 int cel_compute(cel_solver* s, double jitter,
                 int Jr, const double* a_real, const double* c_real,
                 int Jc, const double* a_comp, const double* b_comp,
