@@ -285,6 +285,126 @@ __global__ void __launch_bounds__(kWarp) k_chunk_backward(ScanArgs a) {
   if (a.carry && row_ok && active) a.carry[((size_t)chunk * ncols + col) * J + kk] = f;
 }
 
+// Several right-hand sides: ONE group carries NC columns of its chunk, so the factor tiles are read
+// once per NC columns instead of once per column and the NC reductions of a step overlap.  Same
+// staging and recurrences as the single-column kernels above; rhs sweeps only (no basis columns).
+// DIR 0: forward half of solve, 1: dot_L, 2: backward half of solve.
+template <int L, int DIR, int NC>
+__global__ void __launch_bounds__(kWarp) k_chunk_multi(ScanArgs a) {
+  constexpr int G = kWarp / L, ROW = TT * L, STAGE = 3 * ROW + (NC + 1) * TT, GROUP = kStages * STAGE;
+  constexpr bool BACK = DIR == 2;
+  __shared__ __align__(16) double sm[G * GROUP];
+  const int lane = threadIdx.x, g = lane / L, k = lane % L;
+  const int ncols = a.nrhs, ncg = (ncols + NC - 1) / NC;
+  const long long total = (long long)a.nchunks * ncg;
+  const long long gid0 = (long long)blockIdx.x * G + g;
+  const bool active = gid0 < total;
+  const long long gid = active ? gid0 : total - 1;
+  const int chunk = (int)(gid / ncg), col0 = (int)(gid % ncg) * NC;
+  const int N = a.N, J = a.J, off = a.n_off;
+  const bool row_ok = k < J;
+  const int kk = row_ok ? k : 0;
+  const int n0 = chunk * a.chunk_len, n1 = min(N, n0 + a.chunk_len);
+  const bool vec16 = (J & 1) == 0;
+  const unsigned gmask = group_mask<L>(g);
+  double* base = sm + g * GROUP;
+
+  bool cok[NC];
+  double f[NC], sprev[NC];
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    cok[c] = col0 + c < ncols;
+    f[c] = (a.init && row_ok && cok[c]) ? start_carry(a, chunk, col0 + c, kk) : 0.0;
+    sprev[c] = 0.0;
+  }
+  double wprev = 0.0;
+  for (int e = k; e < GROUP; e += L) base[e] = 0.0;      // absent columns keep a zero rhs
+  __syncwarp(gmask);
+
+  const int ntiles = (n1 - n0 + TT - 1) / TT;
+  auto issue = [&](int q, int st) {                       // q-th tile of the walk
+    if (q < ntiles) {
+      const int m0 = n0 + (BACK ? ntiles - 1 - q : q) * TT;
+      const int cnt = min(TT, n1 - m0), s0 = m0 + off;
+      double* sp = base + st * STAGE;
+      copy_flat<L>(sp + 2 * ROW, a.W + (size_t)s0 * J, cnt * J, k, vec16);
+      const int skip = (s0 == 0) ? 1 : 0;
+      if (cnt > skip) {
+        copy_flat<L>(sp + skip * J, a.phi + (size_t)(s0 - 1 + skip) * J, (cnt - skip) * J, k, vec16);
+        copy_flat<L>(sp + ROW + skip * J, a.u + (size_t)(s0 - 1 + skip) * J, (cnt - skip) * J, k, vec16);
+      }
+      if (skip && row_ok) { sp[kk] = 0.0; sp[ROW + kk] = 0.0; }
+      for (int i = k; i < cnt; i += L) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c)
+          if (cok[c]) cp_async_8(sp + 3 * ROW + c * TT + i, a.in + (size_t)(col0 + c) * N + m0 + i);
+        if (!BACK) cp_async_8(sp + 3 * ROW + NC * TT + i, a.D + s0 + i);
+      }
+    }
+    cp_async_commit_group();
+  };
+  // one step for all columns; results replace the rhs in shared memory (written by the lane that
+  // owns the slot: every lane has the reduced value)
+  auto step = [&](double* sp, int i) {
+    const double ph = row_ok ? sp[i * J + kk] : 0.0;
+    const double uu = row_ok ? sp[ROW + i * J + kk] : 0.0;
+    const double ww = row_ok ? sp[2 * ROW + i * J + kk] : 0.0;
+    double scale = 0.0;
+    if (DIR == 0) scale = fast_rcp_nocheck(sp[3 * ROW + NC * TT + i]);
+    if (DIR == 1) scale = fast_sqrt_nocheck(sp[3 * ROW + NC * TT + i]);
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      const double bn = sp[3 * ROW + c * TT + i];
+      double res;
+      if (BACK) {
+        res = bn - group_sum_masked<L>(ww * f[c], gmask);
+        f[c] = ph * fma(uu, res, f[c]);
+      } else {
+        f[c] = ph * fma(wprev, sprev[c], f[c]);
+        const double red = group_sum_masked<L>(uu * f[c], gmask);
+        if (DIR == 1) { sprev[c] = scale * bn; res = sprev[c] + red; }
+        else { sprev[c] = bn - red; res = sprev[c] * scale; }
+      }
+      if (a.out && (i % L) == k) sp[3 * ROW + c * TT + i] = res;
+    }
+    if (!BACK) wprev = ww;
+  };
+
+  for (int q = 0; q < kStages - 1; ++q) issue(q, q);
+  for (int t = 0; t < ntiles; ++t) {
+    issue(t + kStages - 1, (t + kStages - 1) % kStages);
+    cp_async_wait_group<kStages - 1>();
+    __syncwarp(gmask);
+    double* sp = base + (t % kStages) * STAGE;
+    const int m0 = n0 + (BACK ? ntiles - 1 - t : t) * TT, cnt = min(TT, n1 - m0);
+    if (cnt == TT) {
+      if (BACK) {
+#pragma unroll
+        for (int i = TT - 1; i >= 0; --i) step(sp, i);
+      } else {
+#pragma unroll
+        for (int i = 0; i < TT; ++i) step(sp, i);
+      }
+    } else {
+      if (BACK) { for (int i = cnt - 1; i >= 0; --i) step(sp, i); }
+      else { for (int i = 0; i < cnt; ++i) step(sp, i); }
+    }
+    if (a.out && active) {
+      __syncwarp(gmask);
+#pragma unroll
+      for (int c = 0; c < NC; ++c)
+        if (cok[c])
+          for (int i = k; i < cnt; i += L) a.out[(size_t)(col0 + c) * N + m0 + i] = sp[3 * ROW + c * TT + i];
+    }
+    __syncwarp(gmask);
+  }
+  if (a.carry && row_ok && active) {
+#pragma unroll
+    for (int c = 0; c < NC; ++c)
+      if (cok[c]) a.carry[((size_t)chunk * ncols + col0 + c) * J + kk] = BACK ? f[c] : fma(wprev, sprev[c], f[c]);
+  }
+}
+
 // Chunk maps M (once per factor): the J unit carries of a chunk share the chunk's factor tiles,
 // so ONE group carries all J columns through the chunk, J independent recurrences deep (the tiles
 // are read once and the reductions of the columns overlap).  BACKWARD: the map of the backward
@@ -635,6 +755,22 @@ cudaError_t launch_chunk_sweep(const ScanArgs& a, cudaStream_t stream) {
   if (a.J > kMidMaxJ || a.nchunks < 1) return cudaErrorInvalidValue;
   const long long total = (long long)a.nchunks * (a.nrhs + a.nbasis);
   if (total == 0) return cudaSuccess;
+  if (a.nbasis == 0 && a.nrhs >= 2) {
+    // several right-hand sides: NC columns per group share the factor tiles
+#define CALLMC(LL)                                                                             \
+  {                                                                                            \
+    constexpr int NCC = (LL) == 1 ? 2 : 4;                                                     \
+    const int G = kWarp / LL;                                                                  \
+    const long long groups = (long long)a.nchunks * ((a.nrhs + NCC - 1) / NCC);               \
+    const unsigned grid = (unsigned)((groups + G - 1) / G);                                    \
+    if (a.mode == 2) k_chunk_multi<LL, 2, NCC><<<grid, kWarp, 0, stream>>>(a);                 \
+    else if (a.mode == 1) k_chunk_multi<LL, 1, NCC><<<grid, kWarp, 0, stream>>>(a);            \
+    else k_chunk_multi<LL, 0, NCC><<<grid, kWarp, 0, stream>>>(a);                             \
+  }
+    CEL_DISPATCH_L(a.J, CALLMC);
+#undef CALLMC
+    return cudaGetLastError();
+  }
   if (a.nrhs == 0 && a.nbasis == a.J && !a.diag_basis && a.mode != 1 && a.carry && !a.init) {
     // the full chunk maps of a solve direction: one group per chunk carries all J columns
 #define CALLM(LL)                                                                    \

@@ -19,7 +19,7 @@ def _problem(N, Jr, Jc, seed):
 
 
 @pytest.mark.parametrize("N,Jr,Jc,nrhs", [(16384, 0, 1, 1), (50001, 1, 1, 2), (40000, 0, 4, 3), (20000, 2, 6, 1),
-                                          (17000, 0, 16, 1), (60160, 0, 1, 1), (20001, 1, 0, 2)])
+                                          (17000, 0, 16, 1), (60160, 0, 1, 1), (20001, 1, 0, 2), (30000, 0, 2, 5), (33000, 0, 4, 8)])
 def test_host_api_uses_chunked_path(N, Jr, Jc, nrhs):
     from celerite_b200 import solver
     p, y = _problem(N, Jr, Jc, seed=N)
