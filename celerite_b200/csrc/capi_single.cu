@@ -404,7 +404,20 @@ int cel_dot(cel_solver* s, double jitter, int Jr, const double* a_real, const do
     a.N = N; a.Jr = Jr; a.Jc = Jc; a.Jg = Jg; a.nrhs = nrhs;
     a.coeffs = dc; a.A = A ? dA : nullptr; a.U = Jg > 0 ? dU : nullptr; a.V = Jg > 0 ? dV : nullptr;
     a.x = dx; a.z = s->scratch0.d(); a.out = s->scratch1.d();
-    CEL_CUDA_TRY(s, cel::launch_dot(a, st));
+    if (N >= kChunkedMinN) {
+      // long series: chunks side by side (one wave of groups), carries passed on in closed form
+      int L = 1;
+      while (L < J && L < 32) L <<= 1;
+      const long long slots = 148LL * 16 * (32 / L);
+      long long len = ((long long)N * nrhs + slots - 1) / slots;
+      if (len < 256) len = 256;
+      const int K = (int)((N + len - 1) / len);
+      CEL_CUDA_TRY(s, s->out1.reserve(dbytes(4 * (size_t)K * nrhs * J)));
+      CEL_CUDA_TRY(s, cel::launch_dot_chunked(a, (int)len, K, s->out1.d(), st));
+      s->launches += 2;
+    } else {
+      CEL_CUDA_TRY(s, cel::launch_dot(a, st));
+    }
   }
   s->launches += 1;
   CEL_CUDA_TRY(s, cudaMemcpyAsync(out, s->scratch1.p, dbytes(nz), cudaMemcpyDeviceToHost, st));

@@ -131,6 +131,12 @@ struct DotArgs {
   double* out;
 };
 cudaError_t launch_dot(const DotArgs& a, cudaStream_t stream);
+// The same product on a long series, cut into `nchunks` chunks of `chunk_len` steps that are swept
+// side by side (both sweeps of cholesky.h:536-559 are linear recurrences with DIAGONAL transition
+// phi, so a chunk passes its incoming carry on scaled by exp(-c (t_hi - t_lo)) in closed form):
+// carries-only pass, a short scan over the chunks, then the full pass from the true carries.
+// carry: 4 * nchunks * nrhs * J doubles of scratch.
+cudaError_t launch_dot_chunked(const DotArgs& a, int chunk_len, int nchunks, double* carry, cudaStream_t stream);
 
 // elementwise helper for the J == 0 paths: mode 0 out=in/D, 1 out=scalar*in, 2 out=sqrt(D)*in
 cudaError_t launch_scale(int n, int N, const double* in, const double* D, double scalar, int mode, double* out,

@@ -233,6 +233,113 @@ __global__ void __launch_bounds__(kWarp) k_dot(DotArgs a) {
   }
 }
 
+// ---- K5 on long series: chunked ------------------------------------------------------------
+// Carries: G_n = f_n + u_n z_n of the upper sweep (entering a chunk from above, at time t_{n1}) and
+// H_n = f_n + v_n z_n of the lower sweep (entering from below, at time t_{n0-1}).
+// cu/cl: carries leaving a chunk (pass 0 output); gu/gl: carries entering it (pass 1 input).
+// FULL = false: carries only (no output);  FULL = true: start from gu/gl and write y.
+template <int L, bool FULL>
+__global__ void __launch_bounds__(kWarp) k_dot_chunk(DotArgs a, int chunk_len, int nchunks, double* cu, double* cl,
+                                                     const double* gu, const double* gl) {
+  constexpr int G = kWarp / L;
+  const int lane = threadIdx.x, g = lane / L, k = lane % L;
+  const long long total = (long long)nchunks * a.nrhs;
+  const long long gid0 = (long long)blockIdx.x * G + g;
+  const bool active = gid0 < total;
+  const long long gid = active ? gid0 : total - 1;
+  const int chunk = (int)(gid / a.nrhs), cc = (int)(gid % a.nrhs);
+  const unsigned gmask = group_mask<L>(g);
+  const int N = a.N, Jr = a.Jr, Jc = a.Jc, Jg = a.Jg, J = Jr + 2 * Jc + Jg;
+  const int n0 = chunk * chunk_len, n1 = min(N, n0 + chunk_len);
+  const RowGen rg = make_rowgen(a, k);
+  const int gq = (rg.type == 3) ? k - Jr - 2 * Jc : 0;
+  const double* z = a.z + (size_t)cc * N;
+  double* y = a.out + (size_t)cc * N;
+  const bool row_ok = k < J;
+  const size_t slot = ((size_t)chunk * a.nrhs + cc) * J + (row_ok ? k : 0);
+  double diag0 = a.coeffs[0];
+  {
+    double sr = 0.0, sc = 0.0;
+    for (int j = 0; j < Jr; ++j) sr += a.coeffs[1 + j];
+    for (int j = 0; j < Jc; ++j) sc += a.coeffs[1 + 2 * Jr + j];
+    diag0 = (sr + sc) + diag0;
+  }
+  // ---- upper sweep over the chunk, n = n1-1 .. n0 ----
+  {
+    const bool top = n1 >= N;                       // nothing above the last chunk
+    double f = (FULL && row_ok && !top) ? gu[slot] : 0.0;
+    double uprev = 0.0, zprev = 0.0, tnext = __ldg(a.x + (top ? N - 1 : n1));
+    bool first = top;
+    for (int n = n1 - 1; n >= n0; --n) {
+      const double tn = __ldg(a.x + n), zn = __ldg(z + n);
+      double Un = 0.0, Vn = 0.0;
+      if (rg.type == 3) { Un = __ldg(a.U + (size_t)n * Jg + gq); Vn = __ldg(a.V + (size_t)n * Jg + gq); }
+      double phi_next, un, vn;
+      rg.eval(tn, tnext - tn, Un, Vn, phi_next, un, vn);
+      if (first) phi_next = 0.0;
+      f = phi_next * fma(uprev, zprev, f);
+      if (FULL) {
+        const double red = group_sum_masked<L>(vn * f, gmask);
+        const double dg = diag0 + (a.A ? __ldg(a.A + n) : 0.0);
+        if (k == 0 && active) y[n] = dg * zn + red;
+      }
+      uprev = un; zprev = zn; tnext = tn; first = false;
+    }
+    if (!FULL && row_ok && active) cu[slot] = fma(uprev, zprev, f);     // G_{n0}
+  }
+  __syncwarp(gmask);
+  // ---- lower sweep over the chunk, n = n0 .. n1-1 ----
+  {
+    double f = (FULL && row_ok && n0 > 0) ? gl[slot] : 0.0;
+    double vprev = 0.0, zprev = 0.0, tprev = __ldg(a.x + (n0 > 0 ? n0 - 1 : 0));
+    for (int n = n0; n < n1; ++n) {
+      const double tn = __ldg(a.x + n), zn = __ldg(z + n);
+      double Un = 0.0, Vn = 0.0;
+      if (rg.type == 3) { Un = __ldg(a.U + (size_t)n * Jg + gq); Vn = __ldg(a.V + (size_t)n * Jg + gq); }
+      double phi_n, un, vn;
+      rg.eval(tn, tn - tprev, Un, Vn, phi_n, un, vn);
+      if (n == 0) phi_n = 0.0;
+      f = phi_n * fma(vprev, zprev, f);
+      if (FULL) {
+        const double red = group_sum_masked<L>(un * f, gmask);
+        if (k == 0 && active) y[n] += red;
+      }
+      vprev = vn; zprev = zn; tprev = tn;
+    }
+    if (!FULL && row_ok && active) cl[slot] = fma(vprev, zprev, f);     // H_{n1-1}
+  }
+}
+
+// carries entering every chunk: one thread per (column, row), serial over the chunks
+__global__ void k_dot_scan(DotArgs a, int chunk_len, int nchunks, const double* cu, const double* cl, double* gu,
+                           double* gl) {
+  const int J = a.Jr + 2 * a.Jc + a.Jg;
+  const int id = blockIdx.x * blockDim.x + threadIdx.x;
+  if (id >= a.nrhs * J) return;
+  const int cc = id / J, k = id % J;
+  const RowGen rg = make_rowgen(a, k);
+  const double c = (rg.type <= 2) ? rg.c : 0.0;      // general rows do not decay (phi = 1)
+  const int N = a.N;
+  auto slot = [&](int chunk) { return ((size_t)chunk * a.nrhs + cc) * J + k; };
+  // upper sweep: from the last chunk down; gu[chunk] = G at time t_{n1(chunk)}
+  double gcar = 0.0;
+  for (int ch = nchunks - 1; ch >= 0; --ch) {
+    gu[slot(ch)] = gcar;
+    const int n0 = ch * chunk_len, n1 = min(N, n0 + chunk_len);
+    // leaving the chunk at t_{n0}: own part + what came in, decayed over t_{n1} - t_{n0}
+    const double span = (n1 < N) ? a.x[n1] - a.x[n0] : 0.0;
+    gcar = fma(exp(-c * span), gcar, cu[slot(ch)]);
+  }
+  // lower sweep: from the first chunk up; gl[chunk] = H at time t_{n0(chunk)-1}
+  double hcar = 0.0;
+  for (int ch = 0; ch < nchunks; ++ch) {
+    gl[slot(ch)] = hcar;
+    const int n0 = ch * chunk_len, n1 = min(N, n0 + chunk_len);
+    const double span = (n0 > 0) ? a.x[n1 - 1] - a.x[n0 - 1] : 0.0;
+    hcar = fma(exp(-c * span), hcar, cl[slot(ch)]);
+  }
+}
+
 // J == 0 helpers (cholesky.h:90-95, 226-231, 334-339, 477-481)
 __global__ void k_scale(int n, int N, const double* in, const double* D, double scalar, int mode, double* out) {
   // n = N*nrhs elements.  mode 0: out = in / D   mode 1: out = scalar * in   mode 2: out = sqrt(D) * in
@@ -299,6 +406,25 @@ cudaError_t launch_dot(const DotArgs& a, cudaStream_t stream) {
   {                                                                                    \
     const int G = kWarp / LL, grid = (a.nrhs + G - 1) / G;                             \
     k_dot<LL><<<grid, kWarp, 0, stream>>>(a);                                          \
+  }
+  CEL_DISPATCH_L(J, CALL);
+#undef CALL
+  return cudaGetLastError();
+}
+
+cudaError_t launch_dot_chunked(const DotArgs& a, int chunk_len, int nchunks, double* carry, cudaStream_t stream) {
+  const int J = a.Jr + 2 * a.Jc + a.Jg;
+  if (J > kCoopMaxJ || J < 1 || nchunks < 1) return cudaErrorInvalidValue;
+  const size_t n = (size_t)nchunks * a.nrhs * J;
+  double* cu = carry; double* cl = cu + n; double* gu = cl + n; double* gl = gu + n;
+  const long long total = (long long)nchunks * a.nrhs;
+#define CALL(LL)                                                                                  \
+  {                                                                                               \
+    const int G = kWarp / LL;                                                                     \
+    const unsigned grid = (unsigned)((total + G - 1) / G);                                        \
+    k_dot_chunk<LL, false><<<grid, kWarp, 0, stream>>>(a, chunk_len, nchunks, cu, cl, nullptr, nullptr); \
+    k_dot_scan<<<(a.nrhs * J + 63) / 64, 64, 0, stream>>>(a, chunk_len, nchunks, cu, cl, gu, gl); \
+    k_dot_chunk<LL, true><<<grid, kWarp, 0, stream>>>(a, chunk_len, nchunks, nullptr, nullptr, gu, gl);  \
   }
   CEL_DISPATCH_L(J, CALL);
 #undef CALL

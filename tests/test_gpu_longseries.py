@@ -231,3 +231,17 @@ def test_span_parallel_gradient_rejects_short_halos(monkeypatch):
     notices, and the serial sweep gives the answer (3 launches)."""
     monkeypatch.setenv("CEL_SEGMENT_HALO_SCALE", "0.02")
     assert _grad_case(120000, 0, 2, seed=31) == 3
+
+
+@pytest.mark.parametrize("N,Jr,Jc,nrhs", [(50001, 1, 2, 2), (16384, 0, 1, 1), (40000, 2, 0, 3), (70000, 0, 8, 1)])
+def test_stateless_dot_on_long_series(N, Jr, Jc, nrhs):
+    """K z (cholesky.h:444-590) from N = 16384 on runs as chunks side by side with closed-form
+    carries (sweeps.cu: k_dot_chunk)."""
+    from celerite_b200 import solver
+    p, y = _problem(N, Jr, Jc, seed=N + 3)
+    z = np.random.default_rng(N).standard_normal((N, nrhs))
+    s = solver.CholeskySolver()
+    n0 = s.launch_count()
+    got = s.dot(p.jitter, p.a_real, p.c_real, p.a_comp, p.b_comp, p.c_comp, p.d_comp, E0, E2, E2, p.x, z)
+    assert s.launch_count() - n0 == 3
+    assert rel_inf(got, oracle.best().dot(p, z)) < RTOL_SOLVE
