@@ -454,8 +454,22 @@ int cel_predict(cel_solver* s, int N, const double* y, int M, const double* xs, 
   cel::PredictArgs a{};
   a.N = N; a.M = M; a.Jr = s->Jr; a.Jc = s->Jc;
   a.coeffs = s->coeffs.d(); a.t = s->t.d(); a.alpha = s->out1.d(); a.xs = dxs; a.out = dout;
-  CEL_CUDA_TRY(s, cel::launch_predict(a, st));
-  s->launches += 1;
+  const int Jp = s->Jr + 2 * s->Jc;
+  if (Jp >= 1 && N >= kChunkedMinN) {
+    // long series: the merge sweeps by chunks of data points (one wave of groups)
+    int L = 1;
+    while (L < Jp && L < 32) L <<= 1;
+    const long long slots = 148LL * 16 * (32 / L);
+    long long len = (N + slots - 1) / slots;
+    if (len < 256) len = 256;
+    const int K = (int)((N + len - 1) / len);
+    CEL_CUDA_TRY(s, s->scratch2.reserve(dbytes(4 * (size_t)K * Jp)));
+    CEL_CUDA_TRY(s, cel::launch_predict_chunked(a, (int)len, K, s->scratch2.d(), st));
+    s->launches += 4;
+  } else {
+    CEL_CUDA_TRY(s, cel::launch_predict(a, st));
+    s->launches += 1;
+  }
   CEL_CUDA_TRY(s, cudaMemcpyAsync(out, dout, dbytes(M), cudaMemcpyDeviceToHost, st));
   CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
   return CEL_OK;

@@ -193,6 +193,8 @@ struct PredictArgs {
   double* out;            // M
 };
 cudaError_t launch_predict(const PredictArgs& a, cudaStream_t stream);
+// the two merge sweeps by chunks of data points (long series); carry: 4 * nchunks * (Jr + 2 Jc) doubles
+cudaError_t launch_predict_chunked(const PredictArgs& a, int chunk_len, int nchunks, double* carry, cudaStream_t stream);
 
 // J == 0 value and d/djitter: out[0] = -0.5*sum(y^2/D + log D), out[1] = sum(0.5 y^2/D^2 - 0.5/D)
 cudaError_t launch_jitter_only_grad(int N, const double* diag, const double* y, double jitter, double* out2,

@@ -594,7 +594,168 @@ __global__ void __launch_bounds__(kWarp) k_predict(PredictArgs a) {
     }
   }
 }
+// ---- predict on long series: the merge sweeps by chunks of data points ----------------------
+// Q has diagonal transitions (exp(-c dt) per row), so an incoming carry crosses a chunk scaled by
+// exp(-c (t_hi - t_lo)).  PASS 0: every chunk's carries from zero (no test points); the scan hands
+// each chunk its true carries; PASS 1: forward sweep (writes pred); PASS 2: backward sweep (adds).
+// A chunk's test points are found by bisection: the forward sweep of chunk [n0, n1) consumes
+// xs in (t_{n0}, t_{n1}], the backward sweep xs in (t_{n0-1}, t_{n1-1}] (cholesky.h:614-695).
+__device__ __forceinline__ int upper_bound_d(const double* v, int n, double x) {   // first index with v[i] > x
+  int lo = 0, hi = n;
+  while (lo < hi) { const int mid = (lo + hi) >> 1; if (v[mid] <= x) lo = mid + 1; else hi = mid; }
+  return lo;
+}
+
+template <int L, int PASS>
+__global__ void __launch_bounds__(kWarp) k_predict_chunk(PredictArgs a, int chunk_len, int nchunks, double* cf, double* cb,
+                                                         const double* gf, const double* gb) {
+  constexpr int G = kWarp / L;
+  const int lane = threadIdx.x, g = lane / L, k = lane % L;
+  const int gid0 = blockIdx.x * G + g;
+  const bool active = gid0 < nchunks;
+  const int chunk = active ? gid0 : nchunks - 1;
+  const unsigned gmask = group_mask<L>(g);
+  const int N = a.N, M = a.M, Jr = a.Jr, Jc = a.Jc, Jp = Jr + 2 * Jc;
+  const int n0 = chunk * chunk_len, n1 = min(N, n0 + chunk_len);
+  const double* row = a.coeffs;
+  const double* a_real = row + 1;
+  const double* c_real = a_real + Jr;
+  const double* a_comp = c_real + Jr;
+  const double* b_comp = a_comp + Jc;
+  const double* c_comp = b_comp + Jc;
+  const double* d_comp = c_comp + Jc;
+  int type = 3;  // 0 real, 1 cos row, 2 sin row, 3 idle
+  double ca = 0.0, cb_ = 0.0, cc = 0.0, cd_ = 0.0;
+  if (k < Jr) { type = 0; ca = a_real[k]; cc = c_real[k]; }
+  else if (k < Jp) {
+    const int q = (k - Jr) >> 1;
+    type = 1 + ((k - Jr) & 1);
+    ca = a_comp[q]; cb_ = b_comp[q]; cc = c_comp[q]; cd_ = d_comp[q];
+  }
+  const double* t = a.t;
+  const double* xs = a.xs;
+  const double* alpha = a.alpha;
+  double* pred = a.out;
+  const bool lead = k == 0 && active;
+  const size_t slot = (size_t)chunk * Jp + (k < Jp ? k : 0);
+
+  if (PASS == 0 || PASS == 1) {   // ---- forward (614-653) ----
+    int m = 0;
+    if (PASS == 1) {
+      if (n0 == 0) { while (m < M && xs[m] <= t[0]) { if (lead) pred[m] = 0.0; ++m; } }
+      else m = upper_bound_d(xs, M, t[n0]);
+    }
+    double Q = (PASS == 1 && k < Jp) ? gf[slot] : 0.0;
+    for (int n = n0; n < n1; ++n) {
+      const double alphan = alpha[n];
+      const double tref = (n < N - 1) ? t[n + 1] : t[N - 1];
+      const double tn = t[n], dt = tref - tn;
+      if (type == 0) { Q += alphan; Q *= exp(-cc * dt); }
+      else if (type != 3) {
+        double sd, cd;
+        sincos(cd_ * tn, &sd, &cd);
+        Q += alphan * (type == 1 ? cd : sd);
+        Q *= exp(-cc * dt);
+      }
+      if (PASS == 1) {
+        while (m < M && (n == N - 1 || xs[m] <= tref)) {
+          const double xm = xs[m], dtm = xm - tref;
+          double term = 0.0;
+          if (type == 0) term = ca * exp(-cc * dtm) * Q;
+          else if (type != 3) {
+            double sd, cd;
+            sincos(cd_ * xm, &sd, &cd);
+            const double tmp = exp(-cc * dtm);
+            term = (type == 1 ? (ca * cd + cb_ * sd) : (ca * sd - cb_ * cd)) * tmp * Q;
+          }
+          term = group_sum_masked<L>(term, gmask);
+          if (lead) pred[m] = term;
+          ++m;
+        }
+      }
+    }
+    if (PASS == 0 && k < Jp && active) cf[slot] = Q;
+  }
+  if (PASS == 0 || PASS == 2) {   // ---- backward (655-695) ----
+    int m = (PASS == 2) ? upper_bound_d(xs, M, t[n1 - 1]) - 1 : -1;
+    double Q = (PASS == 2 && k < Jp) ? gb[slot] : 0.0;
+    for (int n = n1 - 1; n >= n0; --n) {
+      const double alphan = alpha[n];
+      const double tref = (n > 0) ? t[n - 1] : t[0];
+      const double tn = t[n], dt = tn - tref;
+      if (type == 0) { Q += alphan * ca; Q *= exp(-cc * dt); }
+      else if (type != 3) {
+        double sd, cd;
+        sincos(cd_ * tn, &sd, &cd);
+        Q += alphan * (type == 1 ? (ca * cd + cb_ * sd) : (ca * sd - cb_ * cd));
+        Q *= exp(-cc * dt);
+      }
+      if (PASS == 2) {
+        while (m >= 0 && (n == 0 || xs[m] > tref)) {
+          const double xm = xs[m], dtm = tref - xm;
+          double term = 0.0;
+          if (type == 0) term = exp(-cc * dtm) * Q;
+          else if (type != 3) {
+            double sd, cd;
+            sincos(cd_ * xm, &sd, &cd);
+            term = (type == 1 ? cd : sd) * exp(-cc * dtm) * Q;
+          }
+          term = group_sum_masked<L>(term, gmask);
+          if (lead) pred[m] += term;
+          --m;
+        }
+      }
+    }
+    if (PASS == 0 && k < Jp && active) cb[slot] = Q;
+  }
+}
+
+__global__ void k_predict_scan(PredictArgs a, int chunk_len, int nchunks, const double* cf, const double* cb, double* gf,
+                               double* gb) {
+  const int Jp = a.Jr + 2 * a.Jc, k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= Jp) return;
+  const double* c_real = a.coeffs + 1 + a.Jr;
+  const double* c_comp = a.coeffs + 1 + 2 * a.Jr + 2 * a.Jc;
+  const double c = k < a.Jr ? c_real[k] : c_comp[(k - a.Jr) >> 1];
+  const int N = a.N;
+  double q = 0.0;
+  for (int ch = 0; ch < nchunks; ++ch) {           // forward: carry at time t_{n0}
+    gf[(size_t)ch * Jp + k] = q;
+    const int n0 = ch * chunk_len, n1 = min(N, n0 + chunk_len);
+    q = fma(exp(-c * (a.t[min(n1, N - 1)] - a.t[n0])), q, cf[(size_t)ch * Jp + k]);
+  }
+  q = 0.0;
+  for (int ch = nchunks - 1; ch >= 0; --ch) {      // backward: carry at time t_{n1-1}
+    gb[(size_t)ch * Jp + k] = q;
+    const int n0 = ch * chunk_len, n1 = min(N, n0 + chunk_len);
+    q = fma(exp(-c * (a.t[n1 - 1] - a.t[max(n0 - 1, 0)])), q, cb[(size_t)ch * Jp + k]);
+  }
+}
 }  // namespace
+
+cudaError_t launch_predict_chunked(const PredictArgs& a, int chunk_len, int nchunks, double* carry, cudaStream_t stream) {
+  const int Jp = a.Jr + 2 * a.Jc;
+  if (Jp > kCoopMaxJ || Jp < 1 || nchunks < 1) return cudaErrorInvalidValue;
+  const size_t n = (size_t)nchunks * Jp;
+  double* cf = carry; double* cb = cf + n; double* gf = cb + n; double* gb = gf + n;
+#define CALLP(LL)                                                                                              \
+  {                                                                                                            \
+    const int G = kWarp / LL;                                                                                  \
+    const unsigned grid = (unsigned)((nchunks + G - 1) / G);                                                   \
+    k_predict_chunk<LL, 0><<<grid, kWarp, 0, stream>>>(a, chunk_len, nchunks, cf, cb, nullptr, nullptr);      \
+    k_predict_scan<<<1, 32, 0, stream>>>(a, chunk_len, nchunks, cf, cb, gf, gb);                              \
+    k_predict_chunk<LL, 1><<<grid, kWarp, 0, stream>>>(a, chunk_len, nchunks, nullptr, nullptr, gf, gb);      \
+    k_predict_chunk<LL, 2><<<grid, kWarp, 0, stream>>>(a, chunk_len, nchunks, nullptr, nullptr, gf, gb);      \
+  }
+  if (Jp <= 1) { CALLP(1); } else if (Jp <= 2) { CALLP(2); } else if (Jp <= 4) { CALLP(4); }
+  else if (Jp <= 8) { CALLP(8); } else if (Jp <= 16) { CALLP(16); } else { CALLP(32); }
+#undef CALLP
+  return cudaGetLastError();
+}
+
+namespace {
+// keeps the serial launcher's anonymous-namespace neighbours together
+}
 
 cudaError_t launch_predict(const PredictArgs& a, cudaStream_t stream) {
   const int Jp = a.Jr + 2 * a.Jc;

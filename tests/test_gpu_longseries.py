@@ -245,3 +245,25 @@ def test_stateless_dot_on_long_series(N, Jr, Jc, nrhs):
     got = s.dot(p.jitter, p.a_real, p.c_real, p.a_comp, p.b_comp, p.c_comp, p.d_comp, E0, E2, E2, p.x, z)
     assert s.launch_count() - n0 == 3
     assert rel_inf(got, oracle.best().dot(p, z)) < RTOL_SOLVE
+
+
+@pytest.mark.parametrize("N,Jr,Jc,M", [(40000, 1, 2, 25000), (16384, 0, 1, 7), (60001, 0, 4, 90000)])
+def test_predict_on_long_series(N, Jr, Jc, M):
+    """predict (cholesky.h:599-698) from N = 16384 on: chunked solve, then the two merge sweeps by
+    chunks of data points.  Test points before the first and after the last datum, on data times,
+    and repeated."""
+    from celerite_b200 import solver
+    p, y = _problem(N, Jr, Jc, seed=N + 5)
+    chk = oracle.best()
+    f = chk.factor(p)
+    rng = np.random.default_rng(M)
+    lo, hi = p.x[0], p.x[-1]
+    xs = rng.uniform(lo - 0.05 * (hi - lo), hi + 0.05 * (hi - lo), M)
+    k = min(M // 3, 1000)
+    xs[:k] = p.x[rng.integers(0, N, k)]                 # exactly on data times
+    if M > 4:
+        xs[-2] = xs[-1]                                  # a repeated test point
+    xs = np.sort(xs)
+    s = solver.CholeskySolver()
+    s.compute(p.jitter, p.a_real, p.c_real, p.a_comp, p.b_comp, p.c_comp, p.d_comp, E0, E2, E2, p.x, p.diag)
+    assert rel_inf(s.predict(y, xs), chk.predict(p, f, y, xs)) < RTOL_SOLVE
