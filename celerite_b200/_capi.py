@@ -42,6 +42,8 @@ SIGNATURES = {
     "cel_set_state": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_double, _vp, _vp, _vp, _vp]),
     "cel_batched_log_likelihood": (C.c_int, [_vp, _i64, C.c_int, _i64, C.c_int, C.c_int, _vp, _i64,
                                              _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_uint]),
+    "cel_batched_log_likelihood_ragged": (C.c_int, [_vp, _i64, C.c_int, _i64, C.c_int, C.c_int, _vp, _i64,
+                                                    _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_uint]),
     "cel_batched_grad_log_likelihood": (C.c_int, [_vp, _i64, C.c_int, _i64, C.c_int, C.c_int, _vp, _i64,
                                                   _vp, _vp, _vp, _vp, _vp, _vp, C.c_uint]),
     "cel_batched_compute": (C.c_int, [_vp, _i64, C.c_int, _i64, C.c_int, C.c_int, _vp, _i64,

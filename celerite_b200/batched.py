@@ -59,15 +59,19 @@ class BatchedSolver(object):
         B = Bt if Bt is not None else (Bc if Bc is not None else 1)
         return B, N, stride, cstride
 
-    def log_likelihood(self, coeffs, t, diag, y, Jr, Jc, return_parts=False):
+    def log_likelihood(self, coeffs, t, diag, y, Jr, Jc, return_parts=False, lengths=None):
         """-0.5*(y^T K^-1 y + log det K + N log 2pi) per series (celerite.py:214-216).
+
+        ``lengths`` (B int32, optional) makes the batch ragged: series b has ``lengths[b]`` points
+        and the rest of its row is padding (any finite values); N in the constant is then the
+        series' own length.
 
         Returns ``ll`` (and ``logdet, quad, status`` when ``return_parts``).  Series whose
         factorisation met D_n < 0 (cholesky.h:176) get ll = -inf and status = 3, the batched
         equivalent of ``GP.log_likelihood(quiet=True)`` (celerite.py:203-218).
         """
         if _is_torch(t):
-            return self._ll_torch(coeffs, t, diag, y, Jr, Jc, return_parts)
+            return self._ll_torch(coeffs, t, diag, y, Jr, Jc, return_parts, lengths)
         coeffs = np.ascontiguousarray(coeffs, dtype=np.float64)
         t = np.ascontiguousarray(t, dtype=np.float64)
         diag = np.ascontiguousarray(diag, dtype=np.float64)
@@ -78,14 +82,22 @@ class BatchedSolver(object):
         ll = np.empty(B); logdet = np.empty(B); quad = np.empty(B)
         status = np.empty(B, dtype=np.int32)
         p = lambda a: C.c_void_p(a.ctypes.data)  # noqa: E731
-        rc = self._lib.cel_batched_log_likelihood(self._h, B, N, stride, Jr, Jc, p(coeffs), cstride,
-                                                  p(t), p(diag), p(y), p(logdet), p(quad), p(ll), p(status),
-                                                  _capi.HOST_POINTERS)
+        if lengths is None:
+            rc = self._lib.cel_batched_log_likelihood(self._h, B, N, stride, Jr, Jc, p(coeffs), cstride,
+                                                      p(t), p(diag), p(y), p(logdet), p(quad), p(ll), p(status),
+                                                      _capi.HOST_POINTERS)
+        else:
+            lengths = np.ascontiguousarray(lengths, dtype=np.int32)
+            if lengths.shape != (B,):
+                raise RuntimeError("dimension mismatch: one length per series")
+            rc = self._lib.cel_batched_log_likelihood_ragged(self._h, B, N, stride, Jr, Jc, p(coeffs), cstride,
+                                                             p(t), p(diag), p(y), p(lengths), p(logdet), p(quad),
+                                                             p(ll), p(status), _capi.HOST_POINTERS)
         _capi.check(rc, self._h)
         ll[~np.isfinite(ll)] = -np.inf
         return (ll, logdet, quad, status) if return_parts else ll
 
-    def _ll_torch(self, coeffs, t, diag, y, Jr, Jc, return_parts):
+    def _ll_torch(self, coeffs, t, diag, y, Jr, Jc, return_parts, lengths=None):
         import torch
         for a in (coeffs, t, diag, y):
             if not (a.is_cuda and a.dtype == torch.float64 and a.is_contiguous()):
@@ -99,9 +111,16 @@ class BatchedSolver(object):
         # name the legacy default stream explicitly (cudaStreamLegacy == 0x1)
         self._lib.cel_set_stream(self._h, C.c_void_p(torch.cuda.current_stream(t.device).cuda_stream or 1))
         p = lambda a: C.c_void_p(a.data_ptr())  # noqa: E731
-        rc = self._lib.cel_batched_log_likelihood(self._h, B, N, stride, Jr, Jc, p(coeffs), cstride,
-                                                  p(t), p(diag), p(y), p(out[0]), p(out[1]), p(out[2]),
-                                                  p(status), 0)
+        if lengths is None:
+            rc = self._lib.cel_batched_log_likelihood(self._h, B, N, stride, Jr, Jc, p(coeffs), cstride,
+                                                      p(t), p(diag), p(y), p(out[0]), p(out[1]), p(out[2]),
+                                                      p(status), 0)
+        else:
+            if not (lengths.is_cuda and lengths.dtype == torch.int32 and lengths.is_contiguous() and lengths.shape == (B,)):
+                raise RuntimeError("lengths: contiguous int32 CUDA tensor of shape (B,)")
+            rc = self._lib.cel_batched_log_likelihood_ragged(self._h, B, N, stride, Jr, Jc, p(coeffs), cstride,
+                                                             p(t), p(diag), p(y), p(lengths), p(out[0]), p(out[1]),
+                                                             p(out[2]), p(status), 0)
         _capi.check(rc, self._h)
         ll = torch.where(torch.isfinite(out[2]), out[2], torch.full_like(out[2], float("-inf")))
         return (ll, out[0], out[1], status) if return_parts else ll

@@ -109,10 +109,11 @@ static int batched_loglik_device(cel_solver* s, const cel::BatchArgs& a) {
   return CEL_OK;
 }
 
-int cel_batched_log_likelihood(cel_solver* s, int64_t B, int N, int64_t stride, int Jr, int Jc,
-                               const double* coeffs, int64_t coeff_stride, const double* t, const double* diag,
-                               const double* y, double* out_logdet, double* out_quad, double* out_ll,
-                               int32_t* status, unsigned flags) {
+// lengths: NULL, or B per-series lengths (host or device like the other pointers)
+static int batched_ll_impl(cel_solver* s, int64_t B, int N, int64_t stride, int Jr, int Jc, const double* coeffs,
+                           int64_t coeff_stride, const double* t, const double* diag, const double* y,
+                           const int32_t* lengths, double* out_logdet, double* out_quad, double* out_ll,
+                           int32_t* status, unsigned flags) {
   if (s == nullptr) return CEL_INVALID_ARGUMENT;
   if (B < 0 || N < 1 || Jr < 0 || Jc < 0 || stride < 0 || coeff_stride < 0)
     CEL_FAIL(s, CEL_INVALID_ARGUMENT, "negative size");
@@ -129,9 +130,16 @@ int cel_batched_log_likelihood(cel_solver* s, int64_t B, int N, int64_t stride, 
   a.stride = stride; a.coeff_stride = coeff_stride;
 
   if (!(flags & CEL_HOST_POINTERS)) {
-    a.B = B; a.coeffs = coeffs; a.t = t; a.diag = diag; a.y = y;
+    a.B = B; a.coeffs = coeffs; a.t = t; a.diag = diag; a.y = y; a.lengths = lengths;
     a.out_logdet = out_logdet; a.out_quad = out_quad; a.out_ll = out_ll; a.status = status;
     return batched_loglik_device(s, a);
+  }
+  if (lengths && stride == 0) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "per-series lengths need per-series data (stride > 0)");
+  const int* d_len = nullptr;
+  if (lengths) {   // all lengths at once: B ints
+    CEL_CUDA_TRY(s, s->scratch2.reserve((size_t)B * sizeof(int)));
+    CEL_CUDA_TRY(s, cudaMemcpyAsync(s->scratch2.p, lengths, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, s->stream));
+    d_len = s->scratch2.i();
   }
 
   // ---- host buffers: stage the batch in chunks, copies of chunk i+1 overlap the sweep of chunk i
@@ -188,6 +196,7 @@ int cel_batched_log_likelihood(cel_solver* s, int64_t B, int N, int64_t stride, 
     double* o = s->stage_o[i].d();
     a.out_logdet = o; a.out_quad = o + chunk; a.out_ll = o + 2 * chunk;
     a.status = s->stage_s[i].i();
+    a.lengths = d_len ? d_len + b0 : nullptr;
     int rc = batched_loglik_device(s, a);
     if (rc != CEL_OK) return rc;
     if (out_logdet) CEL_CUDA_TRY(s, cudaMemcpyAsync(out_logdet + b0, a.out_logdet, nb * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
@@ -198,6 +207,24 @@ int cel_batched_log_likelihood(cel_solver* s, int64_t B, int N, int64_t stride, 
   }
   CEL_CUDA_TRY(s, cudaStreamSynchronize(s->stream));
   return CEL_OK;
+}
+
+int cel_batched_log_likelihood(cel_solver* s, int64_t B, int N, int64_t stride, int Jr, int Jc,
+                               const double* coeffs, int64_t coeff_stride, const double* t, const double* diag,
+                               const double* y, double* out_logdet, double* out_quad, double* out_ll,
+                               int32_t* status, unsigned flags) {
+  return batched_ll_impl(s, B, N, stride, Jr, Jc, coeffs, coeff_stride, t, diag, y, nullptr, out_logdet, out_quad,
+                         out_ll, status, flags);
+}
+
+int cel_batched_log_likelihood_ragged(cel_solver* s, int64_t B, int N, int64_t stride, int Jr, int Jc,
+                                      const double* coeffs, int64_t coeff_stride, const double* t,
+                                      const double* diag, const double* y, const int32_t* lengths,
+                                      double* out_logdet, double* out_quad, double* out_ll, int32_t* status,
+                                      unsigned flags) {
+  if (s && !lengths) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null lengths");
+  return batched_ll_impl(s, B, N, stride, Jr, Jc, coeffs, coeff_stride, t, diag, y, lengths, out_logdet, out_quad,
+                         out_ll, status, flags);
 }
 
 }  // extern "C"

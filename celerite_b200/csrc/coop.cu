@@ -111,6 +111,8 @@ __global__ void __launch_bounds__(PC ? 2 * kWarp : kWarp) k_factor_coop(BatchArg
   const double* Vp = a.V ? a.V + sb * a.stride * Jg : nullptr;
   // steps [nb, ne) are swept, those from `no` on are owned (stored, accumulated)
   const int nb = SEG ? a.seg[3 * bb] : 0, no = SEG ? a.seg[3 * bb + 1] : 0, ne = SEG ? a.seg[3 * bb + 2] : N;
+  // ragged batch: this series ends at len; the rest of its row is padding that is swept but not counted
+  const int len = (!SEG && a.lengths) ? min(max(a.lengths[bb], 0), N) : N;
 
   // coefficient row -> shared; zero the generator tiles once (padded columns stay zero)
   {
@@ -136,7 +138,7 @@ __global__ void __launch_bounds__(PC ? 2 * kWarp : kWarp) k_factor_coop(BatchArg
   double dmax = 0.0;
   for (int j = 0; j < Jc; ++j) dmax = fmax(dmax, fabs(d_comp[j]));
   const bool fast_math =
-      __all_sync(kFull, dmax * fmax(fabs(__ldg(tp)), fabs(__ldg(tp + N - 1))) < kFastTrigLimit);
+      __all_sync(kFull, dmax * fmax(fabs(__ldg(tp)), fabs(__ldg(tp + max(len, 1) - 1))) < kFastTrigLimit);
 
   const bool row_ok = k < JP;            // lanes JP..L-1 (JP not a power of two) carry zeros
   const int kk = row_ok ? k : JP - 1;
@@ -314,7 +316,7 @@ __global__ void __launch_bounds__(PC ? 2 * kWarp : kWarp) k_factor_coop(BatchArg
       const double dw = vk - phk * fma(dw_own, tb, av);
       f_own = phk * fma(dw_own, s_prev, f_own);
       if (row_ok) x_s[(par ^ 1) * JP + kk] = dw;
-      const bool own = !SEG || n0 + i >= no;
+      const bool own = SEG ? n0 + i >= no : n0 + i < len;
       fail = (own && Dn < 0.0 && fail == 0) ? n0 + i + 1 : fail;   // cholesky.h:176
       const double r = fast_rcp_nocheck(Dn);
       if (STORE) {
@@ -327,7 +329,7 @@ __global__ void __launch_bounds__(PC ? 2 * kWarp : kWarp) k_factor_coop(BatchArg
         if (k == 0) edge[J] = Dn;
       }
       s_prev = r * x;
-      quad = fma(x, s_prev, quad);
+      quad = own ? fma(x, s_prev, quad) : quad;
       dw_own = dw;
       r_prev = r;
       ld.add(own ? Dn : 1.0);
@@ -371,7 +373,7 @@ __global__ void __launch_bounds__(PC ? 2 * kWarp : kWarp) k_factor_coop(BatchArg
     const double q = fail ? nan : quad;
     if (a.out_logdet) a.out_logdet[b] = logdet;
     if (a.out_quad) a.out_quad[b] = q;
-    if (a.out_ll) a.out_ll[b] = -0.5 * (q + logdet + (double)N * kLog2Pi);
+    if (a.out_ll) a.out_ll[b] = -0.5 * (q + logdet + (double)len * kLog2Pi);
     if (a.status) a.status[b] = fail ? 3 : 0;
     if (a.fail_index) a.fail_index[b] = fail;
   }

@@ -21,6 +21,7 @@ struct BatchArgs {
   const double* A;         // general rows (cholesky.h:49-51): NULL or N per series
   const double* U;         // Jg x N per series, Jg fastest
   const double* V;
+  const int* lengths;      // NULL, or per series its own length <= N (ragged batch; the rest of the row is padding)
   double* out_logdet;      // any may be NULL
   double* out_quad;
   double* out_ll;

@@ -38,7 +38,7 @@ constexpr double kLog2Pi = 1.8378770664093454836;
 // lets cfg2's 2048 warps run as ONE wave on 148 SMs
 constexpr int lock_maxreg(int J) { return J <= 2 ? 128 : (J <= 4 ? 200 : 255); }
 
-template <int J, int G, int T, int STAGES, bool TMA, bool ALLC, int CAP, bool PIPE>
+template <int J, int G, int T, int STAGES, bool TMA, bool ALLC, int CAP, bool PIPE, bool RAG = false>
 __global__ void __launch_bounds__(kLockThreads) __maxnreg__(CAP)
 k_loglik_lockstep(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const __grid_constant__ CUtensorMap tm_d,
                   const __grid_constant__ CUtensorMap tm_y) {
@@ -58,6 +58,7 @@ k_loglik_lockstep(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const _
   const bool active = b < a.B;
   const long long bb = active ? b : a.B - 1;  // idle lanes shadow the last series, store nothing
   const int N = a.N;
+  const int len = RAG ? min(max(a.lengths[bb], 0), N) : N;   // this lane's own series length
   const double* tp = a.t + bb * a.stride;
   const double* dp = a.diag + bb * a.stride;
   const double* yp = a.y + bb * a.stride;
@@ -90,7 +91,7 @@ k_loglik_lockstep(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const _
   for (int j = 0; j < Jc; ++j) sum_ac += a_comp[j];
   const double asum = sum_ar + sum_ac;  // (diag + sum_ar) + sum_ac in the reference
   // The branch-free sincos is valid for |d*t| < 1e9; t is sorted, so the ends bound it.
-  const double tmax = fmax(fabs(__ldg(tp)), fabs(__ldg(tp + N - 1)));
+  const double tmax = fmax(fabs(__ldg(tp)), fabs(__ldg(tp + max(len, 1) - 1)));
   const bool warp_fast = __all_sync(kFull, dmax * tmax < kFastTrigLimit);
 
   // ---- staging ring ----------------------------------------------------------------------
@@ -178,7 +179,7 @@ k_loglik_lockstep(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const _
     // plain order: generators of G steps, then their recursion (lowest register pressure)
     for (int grp = 0; grp < nfull; ++grp) {
       lock_gen<J, G, true, ALLC>(ga, cf, Jc, ta, grp == 0 ? tprev : tb[G - 1]);
-      lock_rec<J, G, ALLC, false>(st, ga, asum, jitter, da, ya, grp * G, G);
+      lock_rec<J, G, ALLC, false, NoSink, RAG>(st, ga, asum, jitter, da, ya, grp * G, G, NoSink(), len);
       tb[G - 1] = ta[G - 1];
       fetch_or_zero((grp + 1) * G, ta, da, ya);
       if ((grp & 127) == 127) st.ld.renorm();
@@ -190,16 +191,16 @@ k_loglik_lockstep(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const _
     for (; grp + 1 < nfull; grp += 2) {
       fetch_or_zero((grp + 1) * G, tb, db, yb);
       lock_gen<J, G, true, ALLC>(gb, cf, Jc, tb, ta[G - 1]);
-      lock_rec<J, G, ALLC, false>(st, ga, asum, jitter, da, ya, grp * G, G);
+      lock_rec<J, G, ALLC, false, NoSink, RAG>(st, ga, asum, jitter, da, ya, grp * G, G, NoSink(), len);
       fetch_or_zero((grp + 2) * G, ta, da, ya);
       lock_gen<J, G, true, ALLC>(ga, cf, Jc, ta, tb[G - 1]);
-      lock_rec<J, G, ALLC, false>(st, gb, asum, jitter, db, yb, (grp + 1) * G, G);
+      lock_rec<J, G, ALLC, false, NoSink, RAG>(st, gb, asum, jitter, db, yb, (grp + 1) * G, G, NoSink(), len);
       if ((grp & 126) == 126) st.ld.renorm();
     }
     if (grp < nfull) {  // odd number of full groups
       fetch_or_zero((grp + 1) * G, tb, db, yb);
       lock_gen<J, G, true, ALLC>(gb, cf, Jc, tb, ta[G - 1]);
-      lock_rec<J, G, ALLC, false>(st, ga, asum, jitter, da, ya, grp * G, G);
+      lock_rec<J, G, ALLC, false, NoSink, RAG>(st, ga, asum, jitter, da, ya, grp * G, G, NoSink(), len);
       ga = gb;
 #pragma unroll
       for (int g = 0; g < G; ++g) { da[g] = db[g]; ya[g] = yb[g]; }
@@ -210,7 +211,7 @@ k_loglik_lockstep(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const _
     for (int grp = 0; grp < nfull; ++grp) {
       fetch_or_zero((grp + 1) * G, tb, db, yb);
       lock_gen<J, G, false, ALLC>(gb, cf, Jc, tb, ta[G - 1]);
-      lock_rec<J, G, ALLC, false>(st, ga, asum, jitter, da, ya, grp * G, G);
+      lock_rec<J, G, ALLC, false, NoSink, RAG>(st, ga, asum, jitter, da, ya, grp * G, G, NoSink(), len);
       ga = gb;
 #pragma unroll
       for (int g = 0; g < G; ++g) { ta[g] = tb[g]; da[g] = db[g]; ya[g] = yb[g]; }
@@ -219,7 +220,7 @@ k_loglik_lockstep(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const _
   }
   // ragged tail (< G steps): its generators are already in ga (out-of-range points were
   // zero-filled / clamped and are skipped by the guard)
-  if (nfull * G < N) lock_rec<J, G, ALLC, true>(st, ga, asum, jitter, da, ya, nfull * G, N - nfull * G);
+  if (nfull * G < N) lock_rec<J, G, ALLC, true, NoSink, RAG>(st, ga, asum, jitter, da, ya, nfull * G, N - nfull * G, NoSink(), len);
   st.ld.renorm();
 
   if (active) {
@@ -228,7 +229,7 @@ k_loglik_lockstep(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const _
     const double q = st.fail ? nan : st.quad;
     if (a.out_logdet) a.out_logdet[b] = logdet;
     if (a.out_quad) a.out_quad[b] = q;
-    if (a.out_ll) a.out_ll[b] = -0.5 * (q + logdet + (double)N * kLog2Pi);  // celerite.py:214-216
+    if (a.out_ll) a.out_ll[b] = -0.5 * (q + logdet + (double)len * kLog2Pi);  // celerite.py:214-216
     if (a.status) a.status[b] = st.fail ? 3 : 0;
     if (a.fail_index) a.fail_index[b] = st.fail;
   }
@@ -246,6 +247,22 @@ cudaError_t launch_one(const BatchArgs& a, cudaStream_t stream) {
                    make_series_map(&my, a.y, a.B, a.N, a.stride, T);
   constexpr bool kEven = (J % 2) == 0;
   const bool allc = kEven && a.Jr == 0;  // all rows are (cos,sin) pairs: SHO-type kernels
+  if (a.lengths) {   // ragged batch
+    if (tma) {
+      auto kern = allc ? k_loglik_lockstep<J, G, T, STAGES, true, kEven, CAP, PIPE, true>
+                       : k_loglik_lockstep<J, G, T, STAGES, true, false, CAP, PIPE, true>;
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return e;
+      kern<<<(unsigned)grid, kLockThreads, smem, stream>>>(a, mt, md, my);
+    } else {
+      memset(&mt, 0, sizeof(mt));
+      if (allc)
+        k_loglik_lockstep<J, G, T, STAGES, false, kEven, CAP, PIPE, true><<<(unsigned)grid, kLockThreads, 0, stream>>>(a, mt, mt, mt);
+      else
+        k_loglik_lockstep<J, G, T, STAGES, false, false, CAP, PIPE, true><<<(unsigned)grid, kLockThreads, 0, stream>>>(a, mt, mt, mt);
+    }
+    return cudaGetLastError();
+  }
   if (tma) {
     auto kern = allc ? k_loglik_lockstep<J, G, T, STAGES, true, kEven, CAP, PIPE> : k_loglik_lockstep<J, G, T, STAGES, true, false, CAP, PIPE>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -269,7 +286,7 @@ cudaError_t launch_loglik_lockstep(const BatchArgs& a, cudaStream_t stream) {
     case 1: return launch_one<1, 2, 8, 2>(a, stream);
     case 2: {
       static const char* g = getenv("CEL_LOCK_VARIANT");  // tuning knob for the J=2 kernel
-      const char v = g ? g[0] : 'a';
+      const char v = (g && !a.lengths) ? g[0] : 'a';
       if (v == 'b') return launch_one<2, 2, 8, 2, 168, true>(a, stream);
       if (v == 'e') return launch_one<2, 2, 8, 2, 128, true>(a, stream);
       if (v == 'c') return launch_one<2, 2, 8, 2, 128, false>(a, stream);

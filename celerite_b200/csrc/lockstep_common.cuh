@@ -100,10 +100,12 @@ struct NoSink {
 
 // `sink(g, D_n, W_n)` is called after every step (the materialising kernel stages the factor
 // through it; the fused kernels pass NoSink).
-template <int J, int G, bool ALLC, bool GUARD, typename Sink = NoSink>
+// RAG: the series of this lane ends at `len`; later steps (padding of a ragged batch) still run
+// but feed neither the sums nor the failure flag.
+template <int J, int G, bool ALLC, bool GUARD, typename Sink = NoSink, bool RAG = false>
 __device__ __forceinline__ void lock_rec(LockState<J>& st, const LockGen<J, G>& gn, const double asum,
                                          const double jitter, const double (&dd)[G], const double (&yy)[G],
-                                         const int n0, const int nvalid, Sink sink = Sink()) {
+                                         const int n0, const int nvalid, Sink sink = Sink(), const int len = 0) {
 #pragma unroll
   for (int g = 0; g < G; ++g) {
     if (!GUARD || g < nvalid) {
@@ -149,13 +151,15 @@ __device__ __forceinline__ void lock_rec(LockState<J>& st, const LockGen<J, G>& 
         Dn = fma(-gn.u[g][j], su, Dn);
         wn[j] = gn.v[g][j] - su;
       }
-      st.fail = (Dn < 0.0 && st.fail == 0) ? n0 + g + 1 : st.fail;  // cholesky.h:176
+      const bool live = !RAG || n0 + g < len;
+      st.fail = (live && Dn < 0.0 && st.fail == 0) ? n0 + g + 1 : st.fail;  // cholesky.h:176
       const double r = fast_rcp_nocheck(Dn);
 #pragma unroll
       for (int j = 0; j < J; ++j) { st.DW[j] = wn[j]; st.Wp[j] = wn[j] * r; }
-      st.quad = fma(x * x, r, st.quad);  // cholesky.h:356
+      const double q2 = fma(x * x, r, st.quad);  // cholesky.h:356
+      st.quad = live ? q2 : st.quad;
       st.xprev = x;
-      st.ld.add(Dn);                     // cholesky.h:208
+      st.ld.add(live ? Dn : 1.0);        // cholesky.h:208
       sink(g, Dn, st.Wp);
     }
   }

@@ -147,6 +147,15 @@ int cel_batched_log_likelihood(cel_solver* s, int64_t B, int N, int64_t stride,
                                double* out_logdet, double* out_quad, double* out_ll,
                                int32_t* status, unsigned flags);
 
+/* The same for a RAGGED batch: series b has lengths[b] <= N points (0 allowed: log-likelihood 0);
+ * the rest of its row in t/diag/y is padding of any finite content.  No counterpart in the
+ * reference (one series per call); lengths is a host or device array like the other pointers. */
+int cel_batched_log_likelihood_ragged(cel_solver* s, int64_t B, int N, int64_t stride, int Jr, int Jc,
+                                      const double* coeffs, int64_t coeff_stride, const double* t,
+                                      const double* diag, const double* y, const int32_t* lengths,
+                                      double* out_logdet, double* out_quad, double* out_ll,
+                                      int32_t* status, unsigned flags);
+
 /* Same sweep plus the reverse-mode gradient (solver.cpp:347-463 per series).
  * out_val[b] = -0.5*(quad+logdet) (no constant), out_grad[b*P + k], P = 1+2Jr+4Jc. */
 int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t stride,

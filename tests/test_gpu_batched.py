@@ -243,3 +243,45 @@ def test_argument_errors(bs):
     assert lib.cel_batched_log_likelihood(bs._h, 2, 8, 4, 0, 1, p, 5, p, p, p, p, p, p, p, 1) == _capi.DIMENSION_MISMATCH
     assert lib.cel_batched_log_likelihood(bs._h, 2, 8, 8, 0, 17, p, 69, p, p, p, p, p, p, p, 1) == _capi.UNSUPPORTED
     assert lib.cel_batched_log_likelihood(bs._h, 0, 8, 8, 0, 1, p, 5, p, p, p, p, p, p, p, 1) == _capi.OK
+
+
+@pytest.mark.parametrize("B,N,Jr,Jc,device", [(200, 700, 0, 1, True), (97, 403, 1, 1, False), (64, 300, 0, 2, True),
+                                              (20, 500, 0, 4, True), (20, 500, 2, 3, False)])
+def test_ragged_batch(bs, B, N, Jr, Jc, device):
+    """Series of different lengths in one padded batch (cel_batched_log_likelihood_ragged): every
+    series must get the log-likelihood of its own first lengths[b] points, whatever the padding
+    holds — here zeros, NaN-free garbage and a series of length 0 and of length N."""
+    from celerite_b200 import synth
+    b = synth.make_batch(B, N, Jr, Jc, seed=B + N)
+    rng = np.random.default_rng(B)
+    lengths = rng.integers(1, N + 1, B).astype(np.int32)
+    lengths[0], lengths[1], lengths[2] = N, 0, 1
+    t, d, y = b["t"].copy(), b["diag"].copy(), b["y"].copy()
+    for i in range(B):
+        n = lengths[i]
+        t[i, n:] = 0.0 if i % 2 else rng.uniform(-5, 5, N - n)      # padding: zeros or unsorted garbage
+        d[i, n:] = rng.uniform(-1, 1, N - n)
+        y[i, n:] = 1e6
+    P = b["coeffs"].shape[1]
+    chk = oracle.best()
+    if device:
+        import torch
+        tt = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to("cuda:0")  # noqa: E731
+        ll, logdet, quad, status = bs.log_likelihood(tt(b["coeffs"]), tt(t), tt(d), tt(y), Jr, Jc, return_parts=True,
+                                                     lengths=tt(lengths))
+        torch.cuda.synchronize()
+        ll, logdet, quad, status = (x.cpu().numpy() for x in (ll, logdet, quad, status))
+    else:
+        ll, logdet, quad, status = bs.log_likelihood(b["coeffs"], t, d, y, Jr, Jc, return_parts=True, lengths=lengths)
+    assert np.all(status == 0)
+    for i in range(B):
+        n = int(lengths[i])
+        if n == 0:
+            assert ll[i] == 0.0 and logdet[i] == 0.0 and quad[i] == 0.0
+            continue
+        ref = chk.batched_loglik(1, n, n, Jr, Jc, b["coeffs"][i:i + 1], P, b["t"][i:i + 1, :n].copy(),
+                                 b["diag"][i:i + 1, :n].copy(), b["y"][i:i + 1, :n].copy(), nthreads=1)
+        assert ref[0, 2] == 0
+        assert rel_sum(logdet[i], ref[0, 0], n) < RTOL_SCALAR
+        assert rel_sum(quad[i], ref[0, 1], n) < RTOL_SCALAR
+        assert rel_sum(ll[i], -0.5 * (ref[0, 0] + ref[0, 1] + n * np.log(2 * np.pi)), n) < RTOL_SCALAR
