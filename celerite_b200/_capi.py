@@ -46,6 +46,8 @@ SIGNATURES = {
                                                     _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_uint]),
     "cel_batched_grad_log_likelihood": (C.c_int, [_vp, _i64, C.c_int, _i64, C.c_int, C.c_int, _vp, _i64,
                                                   _vp, _vp, _vp, _vp, _vp, _vp, C.c_uint]),
+    "cel_batched_grad_log_likelihood_ragged": (C.c_int, [_vp, _i64, C.c_int, _i64, C.c_int, C.c_int, _vp, _i64,
+                                                         _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "cel_batched_compute": (C.c_int, [_vp, _i64, C.c_int, _i64, C.c_int, C.c_int, _vp, _i64,
                                       _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "cel_grad_log_likelihood_static_scratch": (C.c_int, [C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp,

@@ -125,6 +125,29 @@ class BatchedSolver(object):
         ll = torch.where(torch.isfinite(out[2]), out[2], torch.full_like(out[2], float("-inf")))
         return (ll, out[0], out[1], status) if return_parts else ll
 
+    def grad_log_likelihood_ragged(self, coeffs, t, diag, y, lengths, Jr, Jc):
+        """As ``grad_log_likelihood`` for a ragged batch: torch CUDA tensors only, ``t, diag, y`` of
+        shape (B, N) with series b occupying the first ``lengths[b]`` entries of its row."""
+        import torch
+        for a in (coeffs, t, diag, y):
+            if not (a.is_cuda and a.dtype == torch.float64 and a.is_contiguous()):
+                raise RuntimeError("expected contiguous float64 CUDA tensors")
+        if t.dim() != 2 or diag.shape != t.shape or y.shape != t.shape:
+            raise RuntimeError("dimension mismatch")
+        B, N, stride, cstride = self._shapes(coeffs, t, Jr, Jc)
+        if not (lengths.is_cuda and lengths.dtype == torch.int32 and lengths.is_contiguous() and lengths.shape == (B,)):
+            raise RuntimeError("lengths: contiguous int32 CUDA tensor of shape (B,)")
+        Pn = 1 + 2 * Jr + 4 * Jc
+        val = torch.empty(B, dtype=torch.float64, device=t.device)
+        grad = torch.empty((B, Pn), dtype=torch.float64, device=t.device)
+        status = torch.empty(B, dtype=torch.int32, device=t.device)
+        self._lib.cel_set_stream(self._h, C.c_void_p(torch.cuda.current_stream(t.device).cuda_stream or 1))
+        p = lambda a: C.c_void_p(a.data_ptr())  # noqa: E731
+        rc = self._lib.cel_batched_grad_log_likelihood_ragged(self._h, B, N, stride, Jr, Jc, p(coeffs), cstride, p(t),
+                                                              p(diag), p(y), p(lengths), p(val), p(grad), p(status))
+        _capi.check(rc, self._h)
+        return val, grad, status
+
     def grad_log_likelihood(self, coeffs, t, diag, y, Jr, Jc):
         """Per series: val = -0.5*(y^T K^-1 y + log det K) (no constant) and its gradient with
         respect to the coefficient row, in the layout of the reference's gradient vector

@@ -691,6 +691,38 @@ int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t str
   return CEL_OK;
 }
 
+int cel_batched_grad_log_likelihood_ragged(cel_solver* s, int64_t B, int N, int64_t stride, int Jr, int Jc,
+                                           const double* d_coeffs, int64_t coeff_stride, const double* d_t,
+                                           const double* d_diag, const double* d_y, const int32_t* d_lengths,
+                                           double* d_val, double* d_grad, int32_t* d_status) {
+  if (!s) return CEL_INVALID_ARGUMENT;
+  if (B < 0 || N < 1 || Jr < 0 || Jc < 0 || coeff_stride < 0) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "negative size");
+  if (stride < N) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "stride < N (a ragged batch has one row per series)");
+  const int J = Jr + 2 * Jc, P = 1 + 2 * Jr + 4 * Jc;
+  if (coeff_stride != 0 && coeff_stride < P) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "coeff_stride < 1+2Jr+4Jc");
+  if (J < 1 || J > cel::kCoopMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "batched gradient supports 1 <= J <= 32");
+  if (!d_coeffs || !d_t || !d_diag || !d_y || !d_lengths || !d_val || !d_grad)
+    CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null pointer");
+  if (B == 0) return CEL_OK;
+  CEL_CUDA_TRY(s, cudaSetDevice(s->device));
+  cudaStream_t st = s->stream;
+  // every series is one span [0, lengths[b]) of the cooperative gradient kernel (grad.cu, SPAN)
+  const int seg = cel::grad_tuned_segment(B, N, J, false);
+  CEL_CUDA_TRY(s, s->scratch0.reserve(dbytes(cel::grad_scratch_doubles(B, N, J, seg))));
+  CEL_CUDA_TRY(s, s->scratch2.reserve(sizeof(int) * 4 * (size_t)B));
+  CEL_CUDA_TRY(s, cel::launch_ragged_spans(B, N, d_lengths, s->scratch2.i(), st));
+  cel::GradArgs a{};
+  a.B = B; a.N = N; a.stride = stride; a.Jr = Jr; a.Jc = Jc; a.Jg = 0;
+  a.coeffs = d_coeffs; a.coeff_stride = coeff_stride;
+  a.t = d_t; a.diag = d_diag; a.y = d_y;
+  a.out_val = d_val; a.out_grad = d_grad; a.status = d_status;
+  a.scratch = s->scratch0.d(); a.seg = seg;
+  a.span = s->scratch2.i(); a.span_nseg_max = (N + seg - 1) / seg; a.span_edge = nullptr;
+  CEL_CUDA_TRY(s, cel::launch_grad_spans(a, st));
+  s->launches += 2;
+  return CEL_OK;
+}
+
 // ---- state (pickle) ---------------------------------------------------------------------------
 int cel_get_state(cel_solver* s, int* computed, int* N, int* J, double* log_det, double* phi, double* u, double* W,
                   double* D) {

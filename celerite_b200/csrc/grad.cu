@@ -75,7 +75,8 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   const long long b = (long long)blockIdx.x * G + g;
   const bool active = b < a.B;
   const long long bb = active ? b : a.B - 1;
-  const long long sb = SPAN ? 0 : bb;
+  // spans of ONE series share series 0 (stride 0); a ragged batch gives every series one span
+  const long long sb = (SPAN && a.stride == 0) ? 0 : bb;
   const unsigned gmask = SPAN ? group_mask<L>(g) : kFull;
 
   double* base = smem + (size_t)g * C::kGroup;
@@ -108,7 +109,7 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   double* tape = ckpt + (size_t)nseg_slot * E;
   // span edges kept for the consistency check: 4 records of 2J+1 doubles (see launch_grad_spans)
   const int ER = 2 * J + 1;
-  double* edge = SPAN ? a.span_edge + (size_t)bb * 4 * ER : nullptr;
+  double* edge = (SPAN && a.span_edge) ? a.span_edge + (size_t)bb * 4 * ER : nullptr;
 
   {
     const double* row = a.coeffs + sb * a.coeff_stride;
@@ -338,7 +339,7 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
         fail = (own && Dn < 0.0 && fail == 0) ? n + 1 : fail;   // cholesky.h:176
         quad = fma(own ? x : 0.0, s_prev, quad);
         ld.add(own ? Dn : 1.0);
-        if (SPAN && active && (n == own0 - 1 || n == own1 - 1)) {   // W, D at both edges of the owned range
+        if (SPAN && edge && active && (n == own0 - 1 || n == own1 - 1)) {   // W, D at both edges of the owned range
           double* er = edge + (n == own0 - 1 ? 0 : 1) * ER;
           if (k < J) er[k] = dw * r;
           if (k == 0) er[J] = Dn;
@@ -447,7 +448,7 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
       const double Wk = row_ok ? Wn : 0.0;
       const bool own = !SPAN || (n >= own0 && n < own1);
       const double om = own ? 1.0 : 0.0;               // cool-down steps feed the carries only
-      if (SPAN && active && n == own1 - 1 && k < J) {  // adjoint carries entering the last owned step
+      if (SPAN && edge && active && n == own1 - 1 && k < J) {  // adjoint carries entering the last owned step
         edge[2 * ER + k] = gbar; edge[2 * ER + J + k] = PbW;
       }
 
@@ -508,7 +509,7 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
       __syncwarp(gmask);
     }
   }
-  if (SPAN && active && k < J) {                       // adjoint carries entering step own0 - 1
+  if (SPAN && edge && active && k < J) {               // adjoint carries entering step own0 - 1
     edge[3 * ER + k] = gbar; edge[3 * ER + J + k] = PbW;
   }
 
@@ -677,7 +678,7 @@ size_t grad_scratch_doubles(long long B, int N, int J, int seg) {
 
 cudaError_t launch_grad_spans(const GradArgs& a, cudaStream_t stream) {
   const int J = a.Jr + 2 * a.Jc + a.Jg;
-  if (!a.span || !a.span_edge || a.Jg != 0 || J < 1 || J > kCoopMaxJ || a.seg < 1) return cudaErrorInvalidValue;
+  if (!a.span || a.Jg != 0 || J < 1 || J > kCoopMaxJ || a.seg < 1) return cudaErrorInvalidValue;
   switch (grad_jp(J)) {
     case 2: return launch_span<2>(a, stream);
     case 4: return launch_span<4>(a, stream);
@@ -688,6 +689,21 @@ cudaError_t launch_grad_spans(const GradArgs& a, cudaStream_t stream) {
     case 24: return launch_span<24>(a, stream);
     default: return launch_span<32>(a, stream);
   }
+}
+
+namespace {
+__global__ void k_ragged_spans(long long B, int N, const int* lengths, int* span) {
+  const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const int len = min(max(lengths[b], 0), N);
+  span[4 * b] = 0; span[4 * b + 1] = 0; span[4 * b + 2] = len; span[4 * b + 3] = len;
+}
+}  // namespace
+
+// ragged batch: every series is one span [0, lengths[b]) of its own row (a.stride > 0)
+cudaError_t launch_ragged_spans(long long B, int N, const int* lengths, int* span, cudaStream_t stream) {
+  k_ragged_spans<<<(unsigned)((B + 255) / 256), 256, 0, stream>>>(B, N, lengths, span);
+  return cudaGetLastError();
 }
 
 cudaError_t launch_grad_span_finish(const GradArgs& a, double* result, cudaStream_t stream) {

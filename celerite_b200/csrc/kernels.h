@@ -95,6 +95,8 @@ struct GradArgs {
 // (forward state and adjoint carries), result[2] = status (as a double), result[3..3+P) = gradient.
 cudaError_t launch_grad_spans(const GradArgs& a, cudaStream_t stream);
 cudaError_t launch_grad_span_finish(const GradArgs& a, double* result, cudaStream_t stream);
+// ragged batches: span[4b..] = {0, 0, len_b, len_b}; then launch_grad_spans with stride > 0, span_edge NULL
+cudaError_t launch_ragged_spans(long long B, int N, const int* lengths, int* span, cudaStream_t stream);
 int grad_default_segment(int N);
 int grad_tuned_segment(long long B, int N, int J, bool lockstep);   // batch-aware (L2-resident tapes)
 size_t grad_scratch_doubles(long long B, int N, int J, int seg);

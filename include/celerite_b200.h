@@ -164,6 +164,14 @@ int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t str
                                     double* out_val, double* out_grad,
                                     int32_t* status, unsigned flags);
 
+/* The gradient for a RAGGED batch (series b has d_lengths[b] <= N points, the rest of its row is
+ * padding).  Device pointers only; every series is swept over its own length by the cooperative
+ * kernel.  val carries no constant, as in cel_batched_grad_log_likelihood. */
+int cel_batched_grad_log_likelihood_ragged(cel_solver* s, int64_t B, int N, int64_t stride, int Jr, int Jc,
+                                           const double* d_coeffs, int64_t coeff_stride, const double* d_t,
+                                           const double* d_diag, const double* d_y, const int32_t* d_lengths,
+                                           double* d_val, double* d_grad, int32_t* d_status);
+
 /* Batched compute that DOES materialise the factor (cholesky.h:41-210 per series):
  * phi,u: B x (N-1) x J, W: B x N x J, D: B x N, logdet: B.  Device pointers only. */
 int cel_batched_compute(cel_solver* s, int64_t B, int N, int64_t stride,

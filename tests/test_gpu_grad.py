@@ -109,3 +109,37 @@ def test_batched_grad_lockstep_device(B, N, Jc):
         vref += 0.5 * np.pi * np.log(N)
         assert rel_sum(val[i], vref, N) < RTOL_SCALAR
         assert rel_grad(g[i], gref) < RTOL_GRAD, (i, g[i], gref)
+
+
+@pytest.mark.parametrize("B,N,Jr,Jc", [(40, 400, 0, 1), (21, 350, 1, 1), (12, 300, 0, 4)])
+def test_ragged_batched_grad(B, N, Jr, Jc):
+    """cel_batched_grad_log_likelihood_ragged: every series is differentiated over its own length,
+    whatever its padding holds (incl. a series of length 0, of length 1 and of length N)."""
+    import torch
+    from celerite_b200 import synth
+    from celerite_b200.batched import BatchedSolver
+    b = synth.make_batch(B, N, Jr, Jc, seed=5 * B + N)
+    rng = np.random.default_rng(B)
+    lengths = rng.integers(2, N + 1, B).astype(np.int32)
+    lengths[0], lengths[1], lengths[2] = N, 0, 1
+    t, d, y = b["t"].copy(), b["diag"].copy(), b["y"].copy()
+    for i in range(B):
+        n = lengths[i]
+        t[i, n:] = rng.uniform(-5, 5, N - n); d[i, n:] = -1.0; y[i, n:] = 1e6
+    tt = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to("cuda:0")  # noqa: E731
+    val, g, status = BatchedSolver().grad_log_likelihood_ragged(tt(b["coeffs"]), tt(t), tt(d), tt(y), tt(lengths), Jr, Jc)
+    torch.cuda.synchronize()
+    val, g, status = val.cpu().numpy(), g.cpu().numpy(), status.cpu().numpy()
+    assert np.all(status == 0)
+    chk = oracle.best()
+    for i in range(B):
+        n = int(lengths[i])
+        if n == 0:
+            assert val[i] == 0.0 and np.all(g[i] == 0.0)
+            continue
+        j, ar, cr, ac, bc, cc, dc = synth.split_row(b["coeffs"][i], Jr, Jc)
+        p = oracle.Problem(j, ar, cr, ac, bc, cc, dc, b["t"][i, :n].copy(), b["diag"][i, :n].copy())
+        st, vref, gref = chk.grad(p, b["y"][i, :n].copy())
+        vref += 0.5 * np.pi * np.log(n)   # batched value carries no constant
+        assert rel_sum(val[i], vref, n) < RTOL_SCALAR
+        assert rel_grad(g[i], gref) < RTOL_GRAD, (i, n, g[i], gref)
