@@ -18,7 +18,7 @@ namespace {
 // to round-off.  The bound is checked afterwards on the data: W and D of every segment's last
 // warm-up step must agree with the owner's values to kSegmentMismatchTol, else cel_compute redoes
 // the series serially.
-constexpr int kSegmentedMinN = 65536;
+constexpr int kSegmentedMinN = 16384;
 constexpr double kSegmentTol = 1e-17;
 constexpr double kSegmentMismatchTol = 1e-12;
 constexpr double kSpanMismatchTol = 1e-10;   // gradient spans: forward state and adjoint carries at the common edge
@@ -46,7 +46,7 @@ void plan_segments(int J, int Jr, const double* c_real, int Jc, const double* c_
   if ((double)len < halo_steps) len = (long long)halo_steps;   // at most ~2x redundant work
   len = (len + 15) / 16 * 16;
   const int K = (int)((N + len - 1) / len);
-  if (K < 16) return;
+  if (K < 8) return;
   seg.reserve(3 * (size_t)K);
   long long work = 0;
   for (int c = 0; c < K; ++c) {
@@ -86,7 +86,7 @@ void plan_grad_spans(int J, int Jr, const double* c_real, int Jc, const double* 
   if ((double)len < halo_steps) len = (long long)halo_steps;
   len = (len + 15) / 16 * 16;
   const int K = (int)((N + len - 1) / len);
-  if (K < 16) return;
+  if (K < 8) return;
   span.reserve(4 * (size_t)K);
   long long work = 0;
   for (int c = 0; c < K; ++c) {
@@ -126,9 +126,9 @@ int pack_coeffs(cel_solver* s, double jitter, int Jr, const double* a_real, cons
 
 inline size_t dbytes(size_t n) { return n * sizeof(double); }
 
-// from this length on, solve / dot_L run as chunked scans (6-7 short launches instead of one
-// serial sweep of N dependent steps)
-constexpr int kChunkedMinN = 16384;
+// from this length on, solve / dot_L / dot_solve / dot / predict run as chunked scans (a handful of
+// short launches instead of one serial sweep of N dependent steps at ~100 ns each)
+constexpr int kChunkedMinN = 4096;
 
 }  // namespace
 

@@ -68,12 +68,12 @@ int cel_set_stream(cel_solver* s, void* cuda_stream);
  * Factorises K = L D L^T for one series and keeps phi,u,W,D on the device.  Returns
  * CEL_NOT_POSITIVE_DEFINITE as soon as some D_n < 0 was met; the handle is then "not computed"
  * exactly like the reference (cholesky.h:57).
- * Long series (N >= 65536, no general rows) are factorised as time segments side by side, each
+ * Long series (N >= 16384, no general rows) are factorised as time segments side by side, each
  * from a cold start behind a warm-up halo of ln(1e17)/(2 c_min) in time; the result is checked
  * against the neighbouring segment (1e-12) and the serial sweep is used instead when the check
  * fails or when the terms decay too slowly for halos to pay.  cel_grad_log_likelihood does the
  * same with halos on both sides (tolerance 1e-10); cel_solve, cel_dot_L and cel_dot_solve switch
- * to chunked two-pass scans from N = 16384 on.  Results stay within the parity bars of the
+ * to chunked two-pass scans from N = 4096 on.  Results stay within the parity bars of the
  * serial path (tests/test_gpu_longseries.py). */
 int cel_compute(cel_solver* s, double jitter,
                 int Jr, const double* a_real, const double* c_real,
@@ -186,7 +186,7 @@ int cel_batched_compute(cel_solver* s, int64_t B, int N, int64_t stride,
  * right-hand sides (N_local x nrhs column-major): the time axis is cut into chunks swept
  * concurrently, chunk-to-chunk carries (J^2+J doubles) are composed in a short middle stage, and
  * a second pass writes the result.  cel_solve / cel_dot_L use the same path automatically for
- * N >= 16384.  d_out must not alias d_b. */
+ * N >= 4096.  d_out must not alias d_b. */
 int cel_solve_device(cel_solver* s, int nrhs, const double* d_b, double* d_out);   /* cholesky.h:218-318 */
 int cel_dot_L_device(cel_solver* s, int nrhs, const double* d_z, double* d_out);   /* cholesky.h:409-431 */
 

@@ -1,6 +1,6 @@
 """GPU parity of the chunked two-pass scans (scan.cu): solve and dot_L on long series against
 the CPU oracle, through the drop-in host API (cel_solve / cel_dot_L switch to the chunked path
-at N >= 16384), the device API, and the multi-GPU span protocol emulated on one GPU."""
+at N >= 4096), the device API, and the multi-GPU span protocol emulated on one GPU."""
 import numpy as np
 import pytest
 
@@ -18,7 +18,7 @@ def _problem(N, Jr, Jc, seed):
     return oracle.Problem(j, ar, cr, ac, bc, cc, dc, b["t"][0], b["diag"][0]), b["y"][0]
 
 
-@pytest.mark.parametrize("N,Jr,Jc,nrhs", [(16384, 0, 1, 1), (50001, 1, 1, 2), (40000, 0, 4, 3), (20000, 2, 6, 1),
+@pytest.mark.parametrize("N,Jr,Jc,nrhs", [(4096, 0, 2, 1), (5003, 1, 1, 2), (16384, 0, 1, 1), (50001, 1, 1, 2), (40000, 0, 4, 3), (20000, 2, 6, 1),
                                           (17000, 0, 16, 1), (60160, 0, 1, 1), (20001, 1, 0, 2), (30000, 0, 2, 5), (33000, 0, 4, 8)])
 def test_host_api_uses_chunked_path(N, Jr, Jc, nrhs):
     from celerite_b200 import solver
@@ -134,7 +134,7 @@ def _factor_diff(state, f):
                np.max(np.abs(phi.T - f.phi)) / scale(f.phi), np.max(np.abs(u.T - f.u)) / scale(f.u))
 
 
-@pytest.mark.parametrize("N,Jr,Jc,segmented", [(200000, 0, 4, True), (70001, 1, 1, True), (150000, 0, 1, True),
+@pytest.mark.parametrize("N,Jr,Jc,segmented", [(200000, 0, 4, True), (70001, 1, 1, True), (150000, 0, 1, True), (20000, 0, 2, None),
                                                (100003, 2, 6, None)])
 def test_segmented_compute_matches_serial_factor(N, Jr, Jc, segmented):
     """cel_compute on a long series factorises time segments side by side behind warm-up halos
@@ -226,6 +226,11 @@ def test_span_parallel_gradient_matches_reference(N, Jr, Jc):
     assert _grad_case(N, Jr, Jc, seed=N + 7) == 2      # span sweep + finish
 
 
+def test_gradient_just_above_the_span_threshold():
+    """N = 20000: whichever path the planner picks (spans or serial) must meet the bar."""
+    assert _grad_case(20000, 0, 2, seed=77) in (1, 2, 3)
+
+
 def test_span_parallel_gradient_rejects_short_halos(monkeypatch):
     """Halos cut to 2 % of the bound: neighbouring spans disagree at their common edge, the check
     notices, and the serial sweep gives the answer (3 launches)."""
@@ -233,9 +238,9 @@ def test_span_parallel_gradient_rejects_short_halos(monkeypatch):
     assert _grad_case(120000, 0, 2, seed=31) == 3
 
 
-@pytest.mark.parametrize("N,Jr,Jc,nrhs", [(50001, 1, 2, 2), (16384, 0, 1, 1), (40000, 2, 0, 3), (70000, 0, 8, 1)])
+@pytest.mark.parametrize("N,Jr,Jc,nrhs", [(50001, 1, 2, 2), (4096, 0, 1, 1), (40000, 2, 0, 3), (70000, 0, 8, 1)])
 def test_stateless_dot_on_long_series(N, Jr, Jc, nrhs):
-    """K z (cholesky.h:444-590) from N = 16384 on runs as chunks side by side with closed-form
+    """K z (cholesky.h:444-590) from N = 4096 on runs as chunks side by side with closed-form
     carries (sweeps.cu: k_dot_chunk)."""
     from celerite_b200 import solver
     p, y = _problem(N, Jr, Jc, seed=N + 3)
@@ -247,9 +252,9 @@ def test_stateless_dot_on_long_series(N, Jr, Jc, nrhs):
     assert rel_inf(got, oracle.best().dot(p, z)) < RTOL_SOLVE
 
 
-@pytest.mark.parametrize("N,Jr,Jc,M", [(40000, 1, 2, 25000), (16384, 0, 1, 7), (60001, 0, 4, 90000)])
+@pytest.mark.parametrize("N,Jr,Jc,M", [(40000, 1, 2, 25000), (4097, 0, 1, 7), (60001, 0, 4, 90000)])
 def test_predict_on_long_series(N, Jr, Jc, M):
-    """predict (cholesky.h:599-698) from N = 16384 on: chunked solve, then the two merge sweeps by
+    """predict (cholesky.h:599-698) from N = 4096 on: chunked solve, then the two merge sweeps by
     chunks of data points.  Test points before the first and after the last datum, on data times,
     and repeated."""
     from celerite_b200 import solver
