@@ -3,7 +3,7 @@
 // The factorisation needs one exp and one sincos per complex term and time step
 // (cholesky.h:130, 137-140); with the stock libdevice routines more issue slots went to
 // materialising 64-bit polynomial coefficients (UMOV pairs) than to arithmetic.  These versions
-// keep their coefficients in constant memory (uniform-register operands), use a 3-term
+// keep their coefficients in constant memory (uniform-register operands), use a two-term (fma)
 // Cody-Waite reduction that stays accurate up to |x| = 1e9 (no Payne-Hanek branch for the
 // d*t ~ 1e6 arguments of the N = 1e7 series) and fall back to libdevice outside their range.
 // Accuracy: <= ~1.5 ulp (polynomial error 2e-17, see math_tables.cuh), far inside the 1e-10
@@ -58,7 +58,6 @@ __device__ __forceinline__ void cel_sincos_core(double x, double* s, double* c) 
   const double kf = kd - kRintMagic;
   double r = fma(kf, tab::kTrigR[1], x);
   r = fma(kf, tab::kTrigR[2], r);
-  r = fma(kf, tab::kTrigR[3], r);
   const double z = r * r;
   const double ps = horner<6>(tab::kSinP, z);
   const double pc = horner<6>(tab::kCosP, z);
@@ -95,7 +94,6 @@ __device__ __forceinline__ void cel_sincos(double x, double* s, double* c) {
   const double kf = kd - kRintMagic;
   double r = fma(kf, tab::kTrigR[1], x);
   r = fma(kf, tab::kTrigR[2], r);
-  r = fma(kf, tab::kTrigR[3], r);
   const double z = r * r;
   const double ps = horner<6>(tab::kSinP, z);
   const double pc = horner<6>(tab::kCosP, z);

@@ -138,7 +138,7 @@ __device__ __forceinline__ void lock_rec(LockState<J>& st, const LockGen<J, G>& 
         x = fma(-gn.u[g][j], st.f[j], x);
       }
       // su = S u (symmetric matvec); D_n = A_n - u.su ; W_n = (v - su)/D_n — cholesky.h:98, 162-178
-      double Dn = (dd[g] + asum) + jitter;
+      double Dn = dd[g] + (asum + jitter);   // one add per step; the reference adds in the order (diag + sum a) + jitter
       double wn[J];
 #pragma unroll
       for (int j = 0; j < J; ++j) {
