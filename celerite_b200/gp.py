@@ -112,11 +112,13 @@ class BatchedGP(object):
             return torch.zeros_like(t)
         return (yerr * yerr).contiguous()                     # celerite.py:141: diag = yerr**2
 
-    def log_likelihood(self, params, t, y, yerr=None):
+    def log_likelihood(self, params, t, y, yerr=None, lengths=None):
         """-0.5*(r^T K^-1 r + log det K + N log 2 pi) per series (celerite.py:214-216); -inf where
-        the matrix is not positive definite (``quiet=True``, celerite.py:203-208)."""
+        the matrix is not positive definite (``quiet=True``, celerite.py:203-208).  ``lengths``
+        (int32 CUDA tensor, optional): series b uses only its first lengths[b] points."""
         rows, _ = self.coefficients(params)
-        return self.solver.log_likelihood(rows, t, self._diag(yerr, t), y, self.spec.Jr, self.spec.Jc)
+        return self.solver.log_likelihood(rows, t, self._diag(yerr, t), y, self.spec.Jr, self.spec.Jc,
+                                          lengths=lengths)
 
     def grad_log_likelihood(self, params, t, y, yerr=None):
         """(ll, grad) per series, grad with respect to the parameters (celerite.py:221-297).
