@@ -31,6 +31,8 @@ struct TermPlan {
   int real0[kMaxTerms];    // first real slot of the term
   int comp0[kMaxTerms];    // first complex slot of the term
   double eps[kMaxTerms];   // Matern32Term's eps
+  int k1[kMaxTerms], k2[kMaxTerms];   // factor kinds of a CEL_TERM_PRODUCT node
+  double eps2[kMaxTerms];             // eps of its second factor (eps: of its first)
 };
 
 __host__ __device__ inline int term_npar(int kind) {
@@ -48,6 +50,52 @@ __host__ __device__ inline int term_npar(int kind) {
 inline int term_nreal(int kind) { return kind == CEL_TERM_REAL ? 1 : kind == CEL_TERM_SHO_OVERDAMPED ? 2 : 0; }
 inline int term_ncomp(int kind) {
   return (kind == CEL_TERM_COMPLEX3 || kind == CEL_TERM_COMPLEX4 || kind == CEL_TERM_SHO || kind == CEL_TERM_MATERN32) ? 1 : 0;
+}
+
+// ---- factors of a product term (terms.py:218-277) ---------------------------------------------
+// A factor is a simple term with ONE coefficient set: real (a, c; b = d = 0) or complex (a, b, c, d).
+struct Fac { double a, b, c, d; int cplx; };
+
+__device__ __forceinline__ Fac fac_eval(int kind, const double* q, double eps, int& bad) {
+  Fac f; f.a = f.b = f.c = f.d = 0.0; f.cplx = 1;
+  switch (kind) {
+    case CEL_TERM_REAL: f.a = exp(q[0]); f.c = exp(q[1]); f.cplx = 0; break;
+    case CEL_TERM_COMPLEX3: f.a = exp(q[0]); f.c = exp(q[1]); f.d = exp(q[2]); break;
+    case CEL_TERM_COMPLEX4: f.a = exp(q[0]); f.b = exp(q[1]); f.c = exp(q[2]); f.d = exp(q[3]); break;
+    case CEL_TERM_SHO: {
+      const double S0 = exp(q[0]), Q = exp(q[1]), w0 = exp(q[2]);
+      if (!(Q >= 0.5)) bad = 1;
+      const double fq = sqrt(4.0 * Q * Q - 1.0);
+      f.a = S0 * w0 * Q; f.b = f.a / fq; f.c = 0.5 * w0 / Q; f.d = f.c * fq;
+    } break;
+    case CEL_TERM_MATERN32: {
+      const double w0 = sqrt(3.0) * exp(-q[1]), S0 = exp(2.0 * q[0]) / w0;
+      f.a = w0 * S0; f.b = w0 * w0 * S0 / eps; f.c = w0; f.d = eps;
+    } break;
+    default: bad = 1; break;
+  }
+  return f;
+}
+
+// o[i] = ga da/dp_i + gb db/dp_i + gc dc/dp_i + gd dd/dp_i for the factor's own parameters
+__device__ __forceinline__ void fac_back(int kind, const double* q, double eps, const Fac& f, double ga, double gb,
+                                         double gc, double gd, double* o) {
+  switch (kind) {
+    case CEL_TERM_REAL: o[0] = f.a * ga; o[1] = f.c * gc; break;
+    case CEL_TERM_COMPLEX3: o[0] = f.a * ga; o[1] = f.c * gc; o[2] = f.d * gd; break;
+    case CEL_TERM_COMPLEX4: o[0] = f.a * ga; o[1] = f.b * gb; o[2] = f.c * gc; o[3] = f.d * gd; break;
+    case CEL_TERM_SHO: {
+      const double Q = exp(q[1]), k = 4.0 * Q * Q / (4.0 * Q * Q - 1.0);
+      o[0] = f.a * ga + f.b * gb;
+      o[1] = f.a * ga + f.b * (1.0 - k) * gb - f.c * gc + f.d * (k - 1.0) * gd;
+      o[2] = f.a * ga + f.b * gb + f.c * gc + f.d * gd;
+    } break;
+    case CEL_TERM_MATERN32:
+      o[0] = 2.0 * f.a * ga + 2.0 * f.b * gb;
+      o[1] = -f.b * gb - f.c * gc;
+      break;
+    default: break;
+  }
 }
 
 // BACK = false: params -> coefficient row.   BACK = true: gp += J^T gc (gp zeroed here).
@@ -144,6 +192,47 @@ __global__ void __launch_bounds__(128) k_term_maps(TermPlan pl, long long B, con
           row[o_ac + c] = a; row[o_bc + c] = bb; row[o_cc + c] = w0; row[o_dc + c] = eps;
         }
       } break;
+      case CEL_TERM_PRODUCT: {                     // terms.py:236-277
+        const int ka = pl.k1[t], kb = pl.k2[t];
+        const double* qa = q;
+        const double* qb = q + term_npar(ka);
+        const Fac fa = fac_eval(ka, qa, pl.eps[t], bad), fb = fac_eval(kb, qb, pl.eps2[t], bad);
+        double ga1 = 0.0, gb1 = 0.0, gc1 = 0.0, gd1 = 0.0, ga2 = 0.0, gb2 = 0.0, gc2 = 0.0, gd2 = 0.0;
+        if (!fa.cplx && !fb.cplx) {                // real * real -> one real term
+          if (BACK) { ga1 = fb.a * g[o_ar + r]; ga2 = fa.a * g[o_ar + r]; gc1 = gc2 = g[o_cr + r]; }
+          else { row[o_ar + r] = fa.a * fb.a; row[o_cr + r] = fa.c + fb.c; }
+        } else if (fa.cplx != fb.cplx) {           // real * complex -> one complex term
+          const Fac& R = fa.cplx ? fb : fa;
+          const Fac& X = fa.cplx ? fa : fb;
+          if (BACK) {
+            const double gaR = X.a * g[o_ac + c] + X.b * g[o_bc + c], gcR = g[o_cc + c];
+            const double gaX = R.a * g[o_ac + c], gbX = R.a * g[o_bc + c], gcX = g[o_cc + c], gdX = g[o_dc + c];
+            if (fa.cplx) { ga1 = gaX; gb1 = gbX; gc1 = gcX; gd1 = gdX; ga2 = gaR; gc2 = gcR; }
+            else { ga1 = gaR; gc1 = gcR; ga2 = gaX; gb2 = gbX; gc2 = gcX; gd2 = gdX; }
+          } else {
+            row[o_ac + c] = R.a * X.a; row[o_bc + c] = R.a * X.b; row[o_cc + c] = R.c + X.c; row[o_dc + c] = X.d;
+          }
+        } else {                                   // complex * complex -> two complex terms
+          if (BACK) {
+            const double A0 = g[o_ac + c], B0 = g[o_bc + c], C0 = g[o_cc + c], D0 = g[o_dc + c];
+            const double A1 = g[o_ac + c + 1], B1 = g[o_bc + c + 1], C1 = g[o_cc + c + 1], D1 = g[o_dc + c + 1];
+            ga1 = 0.5 * (fb.a * A0 - fb.b * B0) + 0.5 * (fb.a * A1 + fb.b * B1);
+            gb1 = 0.5 * (fb.b * A0 + fb.a * B0) + 0.5 * (-fb.b * A1 + fb.a * B1);
+            ga2 = 0.5 * (fa.a * A0 + fa.b * B0) + 0.5 * (fa.a * A1 + fa.b * B1);
+            gb2 = 0.5 * (fa.b * A0 - fa.a * B0) + 0.5 * (-fa.b * A1 + fa.a * B1);
+            gc1 = gc2 = C0 + C1; gd1 = D0 + D1; gd2 = D1 - D0;
+          } else {
+            row[o_ac + c] = 0.5 * (fa.a * fb.a + fa.b * fb.b); row[o_bc + c] = 0.5 * (fa.b * fb.a - fa.a * fb.b);
+            row[o_cc + c] = fa.c + fb.c; row[o_dc + c] = fa.d - fb.d;
+            row[o_ac + c + 1] = 0.5 * (fa.a * fb.a - fa.b * fb.b); row[o_bc + c + 1] = 0.5 * (fa.b * fb.a + fa.a * fb.b);
+            row[o_cc + c + 1] = fa.c + fb.c; row[o_dc + c + 1] = fa.d + fb.d;
+          }
+        }
+        if (BACK) {
+          fac_back(ka, qa, pl.eps[t], fa, ga1, gb1, gc1, gd1, o);
+          fac_back(kb, qb, pl.eps2[t], fb, ga2, gb2, gc2, gd2, o + term_npar(ka));
+        }
+      } break;
       default: break;
     }
   }
@@ -151,19 +240,43 @@ __global__ void __launch_bounds__(128) k_term_maps(TermPlan pl, long long B, con
   if (status) status[b] = bad;
 }
 
-int make_plan(cel_solver* s, int nterms, const int* kinds, const double* eps, TermPlan& pl) {
-  if (nterms < 1 || nterms > kMaxTerms || !kinds) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "1 <= nterms <= 32");
+// a factor of a product: one coefficient set
+inline bool is_factor(int k) {
+  return k == CEL_TERM_REAL || k == CEL_TERM_COMPLEX3 || k == CEL_TERM_COMPLEX4 || k == CEL_TERM_SHO || k == CEL_TERM_MATERN32;
+}
+
+// kinds (product nodes take three entries) -> nodes; returns false on a malformed list
+bool parse_plan(int nlist, const int* kinds, const double* eps, TermPlan& pl) {
+  if (nlist < 1 || nlist > kMaxTerms || !kinds) return false;
   pl = TermPlan{};
-  pl.nterms = nterms;
-  int np = 0, jr = 0, jc = 0;
-  for (int t = 0; t < nterms; ++t) {
-    const int k = kinds[t];
-    if (term_npar(k) < 0) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "unknown term kind");
-    pl.kind[t] = k; pl.par0[t] = np; pl.real0[t] = jr; pl.comp0[t] = jc;
-    pl.eps[t] = eps ? eps[t] : 0.01;
-    np += term_npar(k); jr += term_nreal(k); jc += term_ncomp(k);
+  int np = 0, jr = 0, jc = 0, n = 0;
+  for (int i = 0; i < nlist; ++n) {
+    const int k = kinds[i];
+    pl.kind[n] = k; pl.par0[n] = np; pl.real0[n] = jr; pl.comp0[n] = jc;
+    pl.eps[n] = eps ? eps[i] : 0.01;
+    if (k == CEL_TERM_PRODUCT) {
+      if (i + 2 >= nlist || !is_factor(kinds[i + 1]) || !is_factor(kinds[i + 2])) return false;
+      const int ka = kinds[i + 1], kb = kinds[i + 2];
+      pl.k1[n] = ka; pl.k2[n] = kb;
+      pl.eps[n] = eps ? eps[i + 1] : 0.01; pl.eps2[n] = eps ? eps[i + 2] : 0.01;
+      np += term_npar(ka) + term_npar(kb);
+      const int ncx = term_ncomp(ka) + term_ncomp(kb);      // complex factors among the two
+      jr += (ncx == 0) ? 1 : 0;
+      jc += (ncx == 1) ? 1 : (ncx == 2 ? 2 : 0);
+      i += 3;
+    } else {
+      if (term_npar(k) < 0) return false;
+      np += term_npar(k); jr += term_nreal(k); jc += term_ncomp(k);
+      i += 1;
+    }
   }
-  pl.npar = np; pl.Jr = jr; pl.Jc = jc;
+  pl.nterms = n; pl.npar = np; pl.Jr = jr; pl.Jc = jc;
+  return true;
+}
+
+int make_plan(cel_solver* s, int nterms, const int* kinds, const double* eps, TermPlan& pl) {
+  if (!parse_plan(nterms, kinds, eps, pl))
+    CEL_FAIL(s, CEL_INVALID_ARGUMENT, "term list: 1..32 entries of known kinds; a product is followed by its two factors");
   return CEL_OK;
 }
 
@@ -173,15 +286,11 @@ int make_plan(cel_solver* s, int nterms, const int* kinds, const double* eps, Te
 extern "C" {
 
 int cel_term_layout(int nterms, const int* kinds, int* n_params, int* Jr, int* Jc) {
-  if (nterms < 1 || nterms > cel::kMaxTerms || !kinds) return CEL_INVALID_ARGUMENT;
-  int np = 0, jr = 0, jc = 0;
-  for (int t = 0; t < nterms; ++t) {
-    if (cel::term_npar(kinds[t]) < 0) return CEL_INVALID_ARGUMENT;
-    np += cel::term_npar(kinds[t]); jr += cel::term_nreal(kinds[t]); jc += cel::term_ncomp(kinds[t]);
-  }
-  if (n_params) *n_params = np;
-  if (Jr) *Jr = jr;
-  if (Jc) *Jc = jc;
+  cel::TermPlan pl;
+  if (!cel::parse_plan(nterms, kinds, nullptr, pl)) return CEL_INVALID_ARGUMENT;
+  if (n_params) *n_params = pl.npar;
+  if (Jr) *Jr = pl.Jr;
+  if (Jc) *Jc = pl.Jc;
   return CEL_OK;
 }
 

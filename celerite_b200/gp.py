@@ -31,11 +31,20 @@ _NAMES = {
 
 
 class TermSum(object):
-    """A sum of celerite terms, by kind (terms.py:280-324).  ``eps`` maps a term's position to the
-    Matern32Term approximation parameter (default 0.01, terms.py:549)."""
+    """A sum of celerite terms, by kind (terms.py:280-324); an entry ``("product", k1, k2)`` is the
+    product of two one-coefficient-set terms (terms.py:218-277).  ``eps`` maps a position in the
+    flattened kind list to the Matern32Term approximation parameter (default 0.01, terms.py:549)."""
 
     def __init__(self, kinds, eps=None):
-        self.kinds = np.array([KINDS[k] if isinstance(k, str) else int(k) for k in kinds], dtype=np.int32)
+        flat = []
+        for k in kinds:                                   # ("product", k1, k2) -> 7, k1, k2 (terms.py:218-277)
+            if isinstance(k, (tuple, list)):
+                if len(k) != 3 or k[0] != "product":
+                    raise ValueError('a product is written ("product", kind1, kind2)')
+                flat += [7, k[1], k[2]]
+            else:
+                flat.append(k)
+        self.kinds = np.array([KINDS[k] if isinstance(k, str) else int(k) for k in flat], dtype=np.int32)
         self.eps = np.full(len(self.kinds), 0.01)
         for i, v in (eps or {}).items():
             self.eps[i] = v
@@ -43,14 +52,25 @@ class TermSum(object):
         rc = _capi.lib().cel_term_layout(len(self.kinds), C.c_void_p(self.kinds.ctypes.data), C.byref(npar),
                                          C.byref(jr), C.byref(jc))
         if rc != _capi.OK:
-            raise ValueError("unknown term kind or more than 32 terms")
+            raise ValueError("unknown term kind, malformed product or more than 32 entries")
         self.n_params, self.Jr, self.Jc = npar.value, jr.value, jc.value
         self.n_coeffs = 1 + 2 * self.Jr + 4 * self.Jc
 
     @property
     def parameter_names(self):
         """Names in the reference's convention for sums: ``terms[i]:log_x`` (modeling.py)."""
-        return tuple("terms[%d]:%s" % (i, n) for i, k in enumerate(self.kinds) for n in _NAMES[int(k)])
+        names, i, node = [], 0, 0
+        while i < len(self.kinds):
+            k = int(self.kinds[i])
+            if k == 7:                                    # product: k1's parameters, then k2's
+                for tag, kk in (("k1", int(self.kinds[i + 1])), ("k2", int(self.kinds[i + 2]))):
+                    names += ["terms[%d]:%s:%s" % (node, tag, n) for n in _NAMES[kk]]
+                i += 3
+            else:
+                names += ["terms[%d]:%s" % (node, n) for n in _NAMES[k]]
+                i += 1
+            node += 1
+        return tuple(names)
 
     def _args(self):
         return len(self.kinds), C.c_void_p(self.kinds.ctypes.data), C.c_void_p(self.eps.ctypes.data)

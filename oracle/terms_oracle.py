@@ -11,11 +11,31 @@ order given, as TermSum.get_all_coefficients concatenates them (terms.py:305-314
 """
 import numpy as np
 
-NPAR = {0: 1, 1: 2, 2: 3, 3: 4, 4: 3, 5: 3, 6: 2}
+NPAR = {0: 1, 1: 2, 2: 3, 3: 4, 4: 3, 5: 3, 6: 2, 7: 0}
+PRODUCT = 7   # followed in the list by its two factor kinds (TermProduct, terms.py:218-277)
 
 
 def n_params(kinds):
     return sum(NPAR[k] for k in kinds)
+
+
+def _factor(k, q, eps):
+    """(a, b, c, d, is_complex) of a one-coefficient-set term."""
+    if k == 1:
+        return np.exp(q[0]), 0.0, np.exp(q[1]), 0.0, False
+    if k == 2:
+        return np.exp(q[0]), 0.0, np.exp(q[1]), np.exp(q[2]), True
+    if k == 3:
+        return np.exp(q[0]), np.exp(q[1]), np.exp(q[2]), np.exp(q[3]), True
+    if k == 4:
+        S0, Q, w0 = np.exp(q[0]), np.exp(q[1]), np.exp(q[2])
+        f = np.sqrt(4.0 * Q ** 2 - 1)
+        return S0 * w0 * Q, S0 * w0 * Q / f, 0.5 * w0 / Q, 0.5 * w0 / Q * f, True
+    if k == 6:
+        w0 = np.sqrt(3.0) * np.exp(-q[1])
+        S0 = np.exp(2.0 * q[0]) / w0
+        return w0 * S0, w0 * w0 * S0 / eps, w0, eps, True
+    raise ValueError("not a factor kind")
 
 
 def coefficients(kinds, eps, params):
@@ -23,7 +43,29 @@ def coefficients(kinds, eps, params):
     ar, cr, ac, bc, cc, dc = [], [], [], [], [], []
     jitter = 0.0
     o = 0
-    for t, k in enumerate(kinds):
+    t = -1
+    kinds = list(kinds)
+    while t + 1 < len(kinds):
+        t += 1
+        k = kinds[t]
+        if k == PRODUCT:                             # terms.py:236-277
+            k1, k2 = kinds[t + 1], kinds[t + 2]
+            q1 = params[o:o + NPAR[k1]]; o += NPAR[k1]
+            q2 = params[o:o + NPAR[k2]]; o += NPAR[k2]
+            a1, b1, c1, d1, x1 = _factor(k1, q1, eps[t + 1])
+            a2, b2, c2, d2, x2 = _factor(k2, q2, eps[t + 2])
+            if not x1 and not x2:
+                ar.append(a1 * a2); cr.append(c1 + c2)
+            elif x1 != x2:
+                (aR, cR), (aX, bX, cX, dX) = ((a1, c1), (a2, b2, c2, d2)) if x2 else ((a2, c2), (a1, b1, c1, d1))
+                ac.append(aR * aX); bc.append(aR * bX); cc.append(cR + cX); dc.append(dX)
+            else:
+                ac += [0.5 * (a1 * a2 + b1 * b2), 0.5 * (a1 * a2 - b1 * b2)]
+                bc += [0.5 * (b1 * a2 - a1 * b2), 0.5 * (b1 * a2 + a1 * b2)]
+                cc += [c1 + c2, c1 + c2]
+                dc += [d1 - d2, d1 + d2]
+            t += 2
+            continue
         q = params[o:o + NPAR[k]]
         o += NPAR[k]
         if k == 0:                                   # terms.py:356-357

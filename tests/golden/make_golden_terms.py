@@ -16,7 +16,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, os.path.join(ROOT, "baseline", "_ref"))
 from celerite import terms  # noqa: E402
 
-KINDS = {"jitter": 0, "real": 1, "complex3": 2, "complex4": 3, "sho": 4, "sho_over": 5, "matern32": 6}
+KINDS = {"jitter": 0, "real": 1, "complex3": 2, "complex4": 3, "sho": 4, "sho_over": 5, "matern32": 6, "product": 7}
 SPECS = [
     ["sho"],
     ["sho", "jitter"],
@@ -25,7 +25,18 @@ SPECS = [
     ["complex4", "complex3", "jitter", "real"],
     ["matern32", "sho", "jitter"],
     ["sho_over", "sho", "matern32", "complex4", "real", "jitter"],
+    [("product", "real", "real"), "jitter"],
+    [("product", "sho", "real"), ("product", "complex4", "sho")],
+    ["real", ("product", "real", "matern32"), ("product", "complex3", "complex4"), "sho"],
 ]
+NPAR = {"jitter": 1, "real": 2, "complex3": 3, "complex4": 4, "sho": 3, "sho_over": 3, "matern32": 2}
+
+
+def flatten(names):
+    out = []
+    for n in names:
+        out += (["product", n[1], n[2]] if isinstance(n, tuple) else [n])
+    return out
 
 
 def draw(rng, name):
@@ -47,10 +58,33 @@ def draw(rng, name):
     raise ValueError(name)
 
 
+def one(name, q, eps):
+    if name == "real":
+        return terms.RealTerm(log_a=q[0], log_c=q[1])
+    if name == "complex3":
+        return terms.ComplexTerm(log_a=q[0], log_c=q[1], log_d=q[2])
+    if name == "complex4":
+        return terms.ComplexTerm(log_a=q[0], log_b=q[1], log_c=q[2], log_d=q[3])
+    if name == "sho":
+        return terms.SHOTerm(log_S0=q[0], log_Q=q[1], log_omega0=q[2])
+    return terms.Matern32Term(log_sigma=q[0], log_rho=q[1], eps=eps)
+
+
 def build(names, params, epss):
-    ts, o = [], 0
-    for name, eps in zip(names, epss):
-        n = {"jitter": 1, "real": 2, "complex3": 3, "complex4": 4, "sho": 3, "sho_over": 3, "matern32": 2}[name]
+    """names: nested spec; epss: one value per FLATTENED position."""
+    ts, o, pos = [], 0, 0
+    for name in names:
+        if isinstance(name, tuple):
+            n1, n2 = NPAR[name[1]], NPAR[name[2]]
+            k1 = one(name[1], params[o:o + n1], epss[pos + 1])
+            k2 = one(name[2], params[o + n1:o + n1 + n2], epss[pos + 2])
+            ts.append(k1 * k2)
+            o += n1 + n2
+            pos += 3
+            continue
+        eps = epss[pos]
+        pos += 1
+        n = NPAR[name]
         q = params[o:o + n]
         o += n
         if name == "jitter":
@@ -85,7 +119,10 @@ def main():
         epss = None
         for w in range(5):
             ps, es = [], []
-            for name in names:
+            for name in flatten(names):
+                if name == "product":
+                    es.append(0.0)
+                    continue
                 q, e = draw(rng, name)
                 ps += q
                 es.append(e)
@@ -99,7 +136,7 @@ def main():
                 d[i] = 1e-6
                 jac.append((row_of(names, ps + d, epss) - row_of(names, ps - d, epss)) / 2e-6)
             P.append(ps); R.append(row); Jc.append(np.array(jac))
-        out["spec%d_kinds" % si] = np.array([KINDS[n] for n in names], dtype=np.int32)
+        out["spec%d_kinds" % si] = np.array([KINDS[n] for n in flatten(names)], dtype=np.int32)
         out["spec%d_eps" % si] = np.array([e if e else 0.01 for e in epss])
         out["spec%d_params" % si] = np.array(P)
         out["spec%d_rows" % si] = np.array(R)
