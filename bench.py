@@ -566,7 +566,7 @@ def main():
         alg_bytes = B * N * 24 + B * 28          # t, diag, y in; logdet, quad, ll, status out
         achieved = alg_bytes / (ms_step * 1e-3) / 1e9
         line = {
-            "metric": "GP log-likelihood point-terms/sec (N*J*batch / device time)",
+            "metric": "GP log-likelihood point-terms/sec (N*J*batch / time)",
             "value": value, "unit": "point-terms/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",

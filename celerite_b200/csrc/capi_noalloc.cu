@@ -12,6 +12,7 @@
 //
 // The price is a fixed ceiling: the scratch array below is 32 MiB, resident on every GPU that
 // loads the library until the process exits, and shared by all calls.
+#include <atomic>
 #include <cfloat>
 
 #include "../../include/celerite_b200.h"
@@ -26,8 +27,10 @@ static __device__ __align__(256) double g_static_scratch[kStaticScratchDoubles];
 
 // In host code `g_static_scratch` is only a stand-in symbol, not a device address; the address a
 // kernel can use has to be asked for, per device, with that device current.
+// The answer is remembered per device (relaxed atomics: racing first calls store the same value).
+// cudaDeviceReset() invalidates it together with everything else the library holds on that device.
 constexpr int kMaxDevices = 64;
-double* g_scratch_addr[kMaxDevices] = {nullptr};
+std::atomic<double*> g_scratch_addr[kMaxDevices];
 
 int scratch_for_current_device(double** out) {
   int dev = -1;
@@ -35,13 +38,14 @@ int scratch_for_current_device(double** out) {
     cudaGetLastError();
     return CEL_CUDA_ERROR;
   }
-  double* p = g_scratch_addr[dev];
-  if (p == nullptr) {  // first call on this device: one-time set-up (no allocation involved)
+  double* p = g_scratch_addr[dev].load(std::memory_order_relaxed);
+  if (p == nullptr) {  // first call on this device: one-time set-up (this is also when the driver loads the
+                       // library's device image, array included, if nothing of it ran on the device before)
     if (cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_static_scratch) != cudaSuccess || p == nullptr) {
       cudaGetLastError();
       return CEL_CUDA_ERROR;
     }
-    g_scratch_addr[dev] = p;  // racing first calls would both store the same value
+    g_scratch_addr[dev].store(p, std::memory_order_relaxed);
   }
   *out = p;
   return CEL_OK;

@@ -14,7 +14,7 @@ void plan_chunks(cel_solver* s, int Nloc) {
   const int J = s->J > 0 ? s->J : 1;
   int L = 1;
   while (L < J && L < 32) L <<= 1;
-  const long long target = 148LL * 10 * (32 / L);
+  const long long target = static_cast<long long>(cel::sm_count()) * 10 * (32 / L);
   long long len = (Nloc + target - 1) / target;
   if (len < 256) len = 256;
   len = (len + 7) / 8 * 8;

@@ -36,7 +36,7 @@ void plan_segments(int J, int Jr, const double* c_real, int Jc, const double* c_
   if (const char* e = getenv("CEL_SEGMENT_HALO_SCALE")) span *= atof(e);
   int L = 1;
   while (L < J && L < 32) L <<= 1;
-  const int slots = 148 * 8 * (32 / L);                  // resident groups of the cooperative kernel
+  const int slots = cel::sm_count() * 8 * (32 / L);                  // resident groups of the cooperative kernel
   // halo length (in steps) at the median sampling rate decides how finely the series can be cut
   const double dt = (x[N - 1] - x[0]) / (double)(N - 1);
   if (!(dt > 0.0)) return;
@@ -77,7 +77,7 @@ void plan_grad_spans(int J, int Jr, const double* c_real, int Jc, const double* 
   if (const char* e = getenv("CEL_SEGMENT_HALO_SCALE")) reach *= atof(e);
   int L = 1;
   while (L < J && L < 32) L <<= 1;
-  const int slots = 148 * 8 * (32 / L);
+  const int slots = cel::sm_count() * 8 * (32 / L);
   const double dt = (x[N - 1] - x[0]) / (double)(N - 1);
   if (!(dt > 0.0)) return;
   const double halo_steps = reach / dt;
@@ -282,6 +282,8 @@ static int sweep_prepare(cel_solver* s, int N, int nrhs, const double* in, const
   if (N != s->N && s->computed) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "dimension mismatch");  // cholesky.h:219
   if (!s->computed) CEL_FAIL(s, CEL_NOT_COMPUTED, "you must call 'compute' first");          // cholesky.h:220
   if (nrhs < 0 || !in || !out) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null right-hand side");
+  // after cel_span_trim the handle holds a span behind a warm-up halo: the host-array calls sweep whole series only
+  if (s->n_off != 0) CEL_FAIL(s, CEL_UNSUPPORTED, "trimmed span: use the *_device / cel_span_* calls");
   CEL_CUDA_TRY(s, cudaSetDevice(s->device));
   CEL_CUDA_TRY(s, s->in0.reserve(dbytes((size_t)N * (nrhs > 0 ? nrhs : 1))));
   CEL_CUDA_TRY(s, s->out1.reserve(dbytes((size_t)N * (nrhs > 0 ? nrhs : 1))));
@@ -408,7 +410,7 @@ int cel_dot(cel_solver* s, double jitter, int Jr, const double* a_real, const do
       // long series: chunks side by side (one wave of groups), carries passed on in closed form
       int L = 1;
       while (L < J && L < 32) L <<= 1;
-      const long long slots = 148LL * 16 * (32 / L);
+      const long long slots = static_cast<long long>(cel::sm_count()) * 16 * (32 / L);
       long long len = ((long long)N * nrhs + slots - 1) / slots;
       if (len < 256) len = 256;
       const int K = (int)((N + len - 1) / len);
@@ -459,7 +461,7 @@ int cel_predict(cel_solver* s, int N, const double* y, int M, const double* xs, 
     // long series: the merge sweeps by chunks of data points (one wave of groups)
     int L = 1;
     while (L < Jp && L < 32) L <<= 1;
-    const long long slots = 148LL * 16 * (32 / L);
+    const long long slots = static_cast<long long>(cel::sm_count()) * 16 * (32 / L);
     long long len = (N + slots - 1) / slots;
     if (len < 256) len = 256;
     const int K = (int)((N + len - 1) / len);
@@ -564,8 +566,11 @@ int cel_grad_log_likelihood(cel_solver* s, double jitter, int Jr, const double* 
       if (s->pinned_cap < dbytes((size_t)P + 3)) CEL_FAIL(s, CEL_UNSUPPORTED, "too many coefficients");
       CEL_CUDA_TRY(s, cudaMemcpyAsync(res, d_res, dbytes((size_t)P + 3), cudaMemcpyDeviceToHost, st));
       CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
-      if (res[2] != 0.0) CEL_FAIL(s, CEL_NOT_POSITIVE_DEFINITE, "failed to factorize or solve matrix");
-      if (res[1] <= kSpanMismatchTol) {
+      // a negative pivot inside a span is only believed when the spans agree at their edges: a cold-started
+      // halo that has not converged may fail where the whole series does not (the serial sweep below decides)
+      if (res[2] != 0.0 && res[1] <= kSpanMismatchTol)
+        CEL_FAIL(s, CEL_NOT_POSITIVE_DEFINITE, "failed to factorize or solve matrix");
+      if (res[2] == 0.0 && res[1] <= kSpanMismatchTol) {
         *val = res[0];
         for (int i = 0; i < P; ++i) grad[i] = res[3 + i];
         return CEL_OK;

@@ -389,7 +389,7 @@ cudaError_t launch_one(const BatchArgs& a, cudaStream_t stream) {
   // few series in flight (less than ~6 warps per SM): latency bound, split generator and recursion
   static const bool no_pc = getenv("CEL_NO_PRODUCER_WARP") != nullptr;   // tuning knob
   // (J <= 8: at J = 16 the two-warp form measured slower, 8.3 against 6.9 ms)
-  if (JP <= 8 && grid <= 148 * 6 && !no_pc) {
+  if (JP <= 8 && grid <= sm_count() * 6 && !no_pc) {
     auto kpc = k_factor_coop<JP, STORE, false, true>;
     e = cudaFuncSetAttribute(kpc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::smemPC);
     if (e != cudaSuccess) return e;

@@ -136,11 +136,12 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   int partner = kk;
   if (kk >= Jr && kk < Jr + 2 * Jc) partner = Jr + ((kk - Jr) ^ 1);
 
-  // the branch-free sincos needs |d t| < 1e9; t is sorted, so its two ends bound every argument
+  // the branch-free sincos needs |d t| < 1e9; t is sorted, so the two ends of the SWEPT range bound
+  // every argument (in a ragged batch t[N-1] is padding of any content, not part of the series)
   double dmax = 0.0;
   for (int j = 0; j < Jc; ++j) dmax = fmax(dmax, fabs(d_comp[j]));
-  const bool fast_math =
-      __all_sync(kFull, dmax * fmax(fabs(__ldg(tp)), fabs(__ldg(tp + N - 1))) < kFastTrigLimit);
+  const bool fast_math = __all_sync(
+      kFull, dmax * fmax(fabs(__ldg(tp + n_lo)), fabs(__ldg(tp + max(n_hi, 1) - 1))) < kFastTrigLimit);
 
   // ---- tile set-up: inputs + generators of steps n0 .. n0+nt-1 (cholesky.h:127-152) ----------
   // The inputs of a tile are fetched into registers one tile ahead (prefetch only issues the
@@ -651,12 +652,12 @@ int grad_tuned_segment(long long B, int N, int J, bool lockstep) {
     const int T3 = J * (J + 1) / 2, NP = J / 2;
     rec_bytes = 8.0 * (T3 + 2 * J + 2 + 3 * NP + 2);
     ckpt_bytes = 8.0 * (T3 + 3 * J + 2);
-    resident = 148LL * 8 * kWarp;
+    resident = static_cast<long long>(sm_count()) * 8 * kWarp;
     step = 8;
   } else {
     const int JP = grad_jp(J);
     rec_bytes = ckpt_bytes = 8.0 * (JP * JP + 2 * JP + 2);
-    resident = 148LL * 8 * (kWarp / pow2ceil(JP));
+    resident = static_cast<long long>(sm_count()) * 8 * (kWarp / pow2ceil(JP));
     step = 16;
   }
   if (resident > B) resident = B;

@@ -7,6 +7,20 @@
 
 namespace cel {
 
+// SMs of the current device (cudaDevAttrMultiProcessorCount; 148 on B200), cached per device.
+// Grids and segment plans are sized in multiples of this instead of a literal.
+inline int sm_count() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  int n = cached[dev];
+  if (n <= 0) {
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return n;
+}
+
 // One batch of independent series + kernels, all DEVICE pointers (see the C ABI for layout).
 struct BatchArgs {
   long long B;

@@ -434,7 +434,7 @@ cudaError_t launch_dot_chunked(const DotArgs& a, int chunk_len, int nchunks, dou
 cudaError_t launch_scale(int n, int N, const double* in, const double* D, double scalar, int mode, double* out,
                          cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
-  const int threads = 256, grid = min((n + threads - 1) / threads, 148 * 8);
+  const int threads = 256, grid = min((n + threads - 1) / threads, sm_count() * 8);
   k_scale<<<grid, threads, 0, stream>>>(n, N, in, D, scalar, mode, out);
   return cudaGetLastError();
 }

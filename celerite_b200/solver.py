@@ -201,6 +201,12 @@ class CholeskySolver(object):
         u = np.asfortranarray(u, dtype=np.float64)
         W = np.asfortranarray(W, dtype=np.float64)
         D = _vec(D)
+        n, j = int(n), int(j)
+        # cel_set_state copies j*(n-1), j*(n-1), j*n and n doubles from these pointers: a truncated or
+        # corrupted state must end here, not in an out-of-bounds read
+        if n < 0 or j < 0 or phi.shape != (j, max(n - 1, 0)) or u.shape != phi.shape \
+                or W.shape != (j, n) or D.size != n:
+            raise RuntimeError("Invalid state!")
         rc = self._lib.cel_set_state(self._h, int(bool(comp)), int(n), int(j), float(ld),
                                      _ptr(phi), _ptr(u), _ptr(W), _ptr(D))
         _capi.check(rc, self._h)

@@ -244,7 +244,11 @@ int cel_span_dims(const cel_solver* s, int* n_local, int* J, int* nchunks, int* 
  *     (different streams, different host threads) corrupt each other.  Serialise them.
  *   - Nothing has to be cleared between calls: every word is written before it is read.
  *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress,
- *     with that device current); make that first call before starting any stream capture. */
+ *     with that device current); make that first call before starting any stream capture.  It is
+ *     also the moment the driver loads the library's device image (the array included) if none of
+ *     its kernels ran on that device before, so "allocates nothing" holds from the second call on.
+ *     The address is remembered per device; cudaDeviceReset() makes it stale (as it does every
+ *     handle of this library). */
 #define CEL_STATIC_SCRATCH_BYTES (32u << 20)
 int cel_grad_log_likelihood_static_scratch(int N, int Jr, int Jc, const double* d_coeffs,
                                            const double* d_t, const double* d_diag, const double* d_y,
