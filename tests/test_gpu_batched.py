@@ -3,7 +3,7 @@ import numpy as np
 import pytest
 
 import oracle
-from tests.util import RTOL_SCALAR, rel_inf, rel_sum
+from tests.util import RTOL_SCALAR, rel_inf, rel_sum, scalar_parity
 
 pytestmark = pytest.mark.gpu
 
@@ -32,10 +32,13 @@ def _check(bs, B, N, Jr, Jc, seed, torch_path=False):
         ll, logdet, quad, status = bs.log_likelihood(b["coeffs"], b["t"], b["diag"], b["y"], Jr, Jc,
                                                      return_parts=True)
     assert np.all(status == 0)
-    assert rel_sum(logdet, ref[:, 0], N) < RTOL_SCALAR
-    assert rel_sum(quad, ref[:, 1], N) < RTOL_SCALAR
-    ll_ref = -0.5 * (ref[:, 1] + ref[:, 0] + N * np.log(2 * np.pi))
-    assert rel_sum(ll, ll_ref, N) < RTOL_SCALAR
+    # the other CPU build of the same algorithm gives the reference's own round-off floor per series
+    alt = oracle.Port().batched_loglik(B, N, N, Jr, Jc, b["coeffs"], P, b["t"], b["diag"], b["y"], nthreads=8)
+    c = 0.5 * N * np.log(2 * np.pi)
+    for got, r, a in ((logdet, ref[:, 0], alt[:, 0]), (quad, ref[:, 1], alt[:, 1]),
+                      (ll, -0.5 * (ref[:, 1] + ref[:, 0]) - c, -0.5 * (alt[:, 1] + alt[:, 0]) - c)):
+        worst, msg = scalar_parity(got, r, N, a)
+        assert worst <= 1.0, msg
 
 
 @pytest.mark.parametrize("B,N,Jr,Jc", [

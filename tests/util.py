@@ -35,6 +35,24 @@ def rel_sum(a, b, N, verbose=False):
     return float(np.max(out))
 
 
+def scalar_parity(got, ref, N, alt=None):
+    """(worst error / its tolerance, report string) for extensive scalars.  Error as in rel_sum (pure
+    relative for |ref| >= 1).  Tolerance: RTOL_SCALAR, except where the reference disagrees with ITSELF
+    by more: `alt` is the same quantity from the other CPU build of the same algorithm (the reference
+    compiled with FMA contraction against the plain-C restatement without), and a case whose two CPU
+    answers already differ by e (an ill-conditioned kernel) is held to max(1e-10, 3 e)."""
+    got, ref = np.atleast_1d(np.asarray(got, dtype=float)), np.atleast_1d(np.asarray(ref, dtype=float))
+    den = np.where(np.abs(ref) >= 1.0, np.abs(ref), np.maximum(np.abs(ref), float(N)))
+    err = np.abs(got - ref) / den
+    tol = np.full(ref.shape, RTOL_SCALAR)
+    noise = np.zeros(ref.shape)
+    if alt is not None:
+        noise = np.abs(np.atleast_1d(np.asarray(alt, dtype=float)) - ref) / den
+        tol = np.maximum(tol, 3.0 * noise)
+    i = int(np.argmax(err / tol))
+    return float(err[i] / tol[i]), "err %.3e tol %.3e (cpu-vs-cpu %.3e, ref %.6g)" % (err[i], tol[i], noise[i], ref[i])
+
+
 def rel_inf(a, b):
     """||a-b||_inf / ||b||_inf  (SURVEY.md §8c parity metric for vectors)."""
     a, b = np.asarray(a), np.asarray(b)
