@@ -144,9 +144,7 @@ static int batched_ll_impl(cel_solver* s, int64_t B, int N, int64_t stride, int 
 
   // ---- host buffers: stage the batch in chunks, copies of chunk i+1 overlap the sweep of chunk i
   const size_t series_bytes = (size_t)N * sizeof(double);
-  int64_t chunk = (int64_t)((size_t)(96u << 20) / (3 * series_bytes));
-  if (chunk < 64) chunk = 64;
-  if (chunk > B) chunk = B;
+  int64_t chunk = cel::staging_chunk(B, N, (size_t)96u << 20, 2);
   if (stride == 0) chunk = B;  // shared data: one series to copy, sweep everything at once
   const int64_t nchunks = (B + chunk - 1) / chunk;
   for (int i = 0; i < 2; ++i) {

@@ -652,9 +652,8 @@ int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t str
   }
   // host buffers: chunks of the batch, staged one after the other on the handle's stream
   const size_t series_bytes = dbytes(N);
-  int64_t chunk = (int64_t)((size_t)(256u << 20) / (3 * series_bytes));
-  if (chunk < 64) chunk = 64;
-  if (chunk > B) chunk = B;
+  int64_t chunk = cel::staging_chunk(B, N, (size_t)256u << 20, 1);
+  while (chunk > 64 && scratch_need(chunk) > ((size_t)24 << 30)) chunk /= 2;   // checkpoints + tape of the chunk
   if (stride == 0) chunk = B;
   const size_t ndata = (stride == 0 ? 1 : (size_t)chunk) * N;
   CEL_CUDA_TRY(s, s->scratch0.reserve(scratch_need(chunk)));

@@ -21,6 +21,23 @@ inline int sm_count() {
   return n;
 }
 
+// Series per staged chunk of a host-pointer batch.  A chunk's sweep lasts N dependent steps however
+// few series it holds, while its copy time grows with the series count: from about 2,048 series on
+// the copy (PCIe) is the longer of the two at every N, so chunks are at least that large -- and at
+// least `bytes_target` of input (copy efficiency) -- within a device-memory budget for the staging
+// buffers.  With fewer series than that the whole batch is one chunk.
+inline long long staging_chunk(long long B, int N, size_t bytes_target, int nbuffers) {
+  const size_t series_bytes = (size_t)N * sizeof(double) * 3;
+  long long chunk = (long long)(bytes_target / series_bytes);
+  if (chunk < 2048) chunk = 2048;
+  const size_t budget = (size_t)12 << 30;   // all staging buffers together
+  const long long cap = (long long)(budget / (series_bytes * (size_t)nbuffers));
+  if (chunk > cap) chunk = cap;
+  if (chunk < 64) chunk = 64;
+  if (chunk > B) chunk = B;
+  return chunk;
+}
+
 // One batch of independent series + kernels, all DEVICE pointers (see the C ABI for layout).
 struct BatchArgs {
   long long B;
