@@ -102,7 +102,8 @@ struct NoSink {
 // through it; the fused kernels pass NoSink).
 // RAG: the series of this lane ends at `len`; later steps (padding of a ragged batch) still run
 // but feed neither the sums nor the failure flag.
-template <int J, int G, bool ALLC, bool GUARD, typename Sink = NoSink, bool RAG = false>
+// SOLVE = false drops the forward substitution and the quadratic form (compute without a right-hand side).
+template <int J, int G, bool ALLC, bool GUARD, typename Sink = NoSink, bool RAG = false, bool SOLVE = true>
 __device__ __forceinline__ void lock_rec(LockState<J>& st, const LockGen<J, G>& gn, const double asum,
                                          const double jitter, const double (&dd)[G], const double (&yy)[G],
                                          const int n0, const int nvalid, Sink sink = Sink(), const int len = 0) {
@@ -132,10 +133,12 @@ __device__ __forceinline__ void lock_rec(LockState<J>& st, const LockGen<J, G>& 
       }
       // forward substitution with the previous column of W — cholesky.h:350-354
       double x = yy[g];
+      if constexpr (SOLVE) {
 #pragma unroll
-      for (int j = 0; j < J; ++j) {
-        st.f[j] = gn.phi[g][j] * fma(st.Wp[j], st.xprev, st.f[j]);
-        x = fma(-gn.u[g][j], st.f[j], x);
+        for (int j = 0; j < J; ++j) {
+          st.f[j] = gn.phi[g][j] * fma(st.Wp[j], st.xprev, st.f[j]);
+          x = fma(-gn.u[g][j], st.f[j], x);
+        }
       }
       // su = S u (symmetric matvec); D_n = A_n - u.su ; W_n = (v - su)/D_n — cholesky.h:98, 162-178
       double Dn = dd[g] + (asum + jitter);   // one add per step; the reference adds in the order (diag + sum a) + jitter
@@ -156,9 +159,11 @@ __device__ __forceinline__ void lock_rec(LockState<J>& st, const LockGen<J, G>& 
       const double r = fast_rcp_nocheck(Dn);
 #pragma unroll
       for (int j = 0; j < J; ++j) { st.DW[j] = wn[j]; st.Wp[j] = wn[j] * r; }
-      const double q2 = fma(x * x, r, st.quad);  // cholesky.h:356
-      st.quad = live ? q2 : st.quad;
-      st.xprev = x;
+      if constexpr (SOLVE) {
+        const double q2 = fma(x * x, r, st.quad);  // cholesky.h:356
+        st.quad = live ? q2 : st.quad;
+        st.xprev = x;
+      }
       st.ld.add(live ? Dn : 1.0);        // cholesky.h:208
       sink(g, Dn, st.Wp);
     }
