@@ -64,8 +64,17 @@ SIGNATURES = {
     "cel_span_log_determinant": (C.c_int, [_vp, _vp]),
     "cel_span_quad": (C.c_int, [_vp, _vp, _vp]),
     "cel_span_dims": (C.c_int, [_vp, _ip, _ip, _ip, _ip]),
+    "cel_comm_unique_id": (C.c_int, [_vp]),
+    "cel_comm_init": (C.c_int, [_vp, C.c_int, C.c_int, _vp]),
+    "cel_comm_destroy": (C.c_int, [_vp]),
+    "cel_mgpu_bounds": (C.c_int, [_i64, C.c_int, C.c_int, C.POINTER(_i64), C.POINTER(_i64)]),
+    "cel_compute_mgpu": (C.c_int, [_vp, C.c_double, C.c_int, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _i64]),
+    "cel_solve_mgpu": (C.c_int, [_vp, C.c_int, _vp, _vp]),
+    "cel_dot_L_mgpu": (C.c_int, [_vp, C.c_int, _vp, _vp]),
+    "cel_log_likelihood_mgpu": (C.c_int, [_vp, _vp, _dp]),
     "cel_launch_count": (_i64, [_vp]),
 }
+COMM_ID_BYTES = 128
 
 _lib = None
 

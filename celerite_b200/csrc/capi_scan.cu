@@ -1,5 +1,9 @@
 // C ABI, part 4: long-series variants of solve / dot_L (chunked two-pass scans, scan.cu) on
 // device-resident data, and their multi-GPU "span" form.
+#include <dlfcn.h>
+#include <math.h>
+#include <nccl.h>      // types only: the library is loaded at run time (see nccl_api)
+
 #include <vector>
 
 #include "solver_handle.h"
@@ -110,9 +114,207 @@ int check_ready(cel_solver* s, int nrhs) {
   return CEL_OK;
 }
 
+// ---- NCCL, resolved at run time ------------------------------------------------------------------
+// The shared library must load on machines without NCCL (single-GPU users never touch it), and inside
+// a PyTorch process it must use the NCCL that process already holds rather than a second copy: so no
+// link-time dependency, dlopen by soname when the first communicator is asked for.
+struct NcclApi {
+  void* lib = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+  std::string err;
+};
+
+NcclApi& nccl_api() {
+  static NcclApi api;
+  static bool tried = false;
+  if (tried) return api;
+  tried = true;
+  const char* names[] = {"libnccl.so.2", "libnccl.so"};
+  for (const char* n : names) {
+    api.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+    if (api.lib) break;
+  }
+  if (!api.lib) {
+    api.err = std::string("NCCL not found (dlopen libnccl.so.2): ") + (dlerror() ? dlerror() : "");
+    return api;
+  }
+  auto sym = [&](const char* name) -> void* {
+    void* p = dlsym(api.lib, name);
+    if (!p && api.err.empty()) api.err = std::string("NCCL symbol missing: ") + name;
+    return p;
+  };
+  api.GetUniqueId = reinterpret_cast<decltype(api.GetUniqueId)>(sym("ncclGetUniqueId"));
+  api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(sym("ncclCommInitRank"));
+  api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
+  api.AllGather = reinterpret_cast<decltype(api.AllGather)>(sym("ncclAllGather"));
+  api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(sym("ncclAllReduce"));
+  api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
+  return api;
+}
+
+#define CEL_NCCL_TRY(s, expr)                                                                    \
+  do {                                                                                           \
+    ncclResult_t _r = (expr);                                                                    \
+    if (_r != ncclSuccess) {                                                                     \
+      char _buf[512];                                                                            \
+      snprintf(_buf, sizeof(_buf), "%s failed: %s (%s:%d)", #expr,                               \
+               nccl_api().GetErrorString ? nccl_api().GetErrorString(_r) : "?", __FILE__, __LINE__); \
+      (s)->err = _buf;                                                                           \
+      return CEL_CUDA_ERROR;                                                                     \
+    }                                                                                            \
+  } while (0)
+
+// One sweep over the whole series: every rank summarises its span, the summaries are all-gathered,
+// every rank folds the maps of the ranks before it (after it, for the backward sweep) into its
+// incoming carry, and the second pass writes the span's result.  All on the handle's stream.
+int mgpu_sweep(cel_solver* s, int op, int nrhs, const double* d_in, double* d_out) {
+  const int J = s->J, nb = nbasis_of(s, op);
+  const size_t count = (size_t)(nrhs + nb) * J;
+  if (s->world == 1) return scan_sweep(s, op, nrhs, d_in, nullptr, d_out, nullptr, false);
+  NcclApi& nc = nccl_api();
+  CEL_CUDA_TRY(s, s->mg_summary.reserve(dbytes(count)));
+  CEL_CUDA_TRY(s, s->mg_gathered.reserve(dbytes(count * s->world)));
+  CEL_CUDA_TRY(s, s->mg_carry.reserve(dbytes((size_t)nrhs * J)));
+  int rc = scan_sweep(s, op, nrhs, d_in, nullptr, nullptr, s->mg_summary.d(), false);
+  if (rc != CEL_OK) return rc;
+  CEL_NCCL_TRY(s, nc.AllGather(s->mg_summary.p, s->mg_gathered.p, count, ncclDouble,
+                               static_cast<ncclComm_t>(s->nccl_comm), s->stream));
+  CEL_CUDA_TRY(s, cel::launch_span_fold(J, nrhs, nb, op == 1, op == 2, s->world, s->rank, s->mg_gathered.d(),
+                                        s->mg_carry.d(), s->stream));
+  s->launches += 1;
+  return scan_sweep(s, op, nrhs, d_in, s->mg_carry.d(), d_out, nullptr, true);
+}
+
+int mgpu_ready(cel_solver* s, int nrhs) {
+  int rc = check_ready(s, nrhs);
+  if (rc != CEL_OK) return rc;
+  if (s->world > 1 && !s->nccl_comm) CEL_FAIL(s, CEL_NOT_COMPUTED, "call cel_comm_init first");
+  if (s->mg_N == 0) CEL_FAIL(s, CEL_NOT_COMPUTED, "call cel_compute_mgpu first");
+  return CEL_OK;
+}
+
 }  // namespace
 
 extern "C" {
+
+int cel_comm_unique_id(void* id_bytes) {
+  if (!id_bytes) return CEL_INVALID_ARGUMENT;
+  static_assert(sizeof(ncclUniqueId) == CEL_COMM_ID_BYTES, "ncclUniqueId is 128 bytes");
+  NcclApi& nc = nccl_api();
+  if (!nc.err.empty() || !nc.GetUniqueId) return CEL_CUDA_ERROR;
+  ncclUniqueId id;
+  if (nc.GetUniqueId(&id) != ncclSuccess) return CEL_CUDA_ERROR;
+  memcpy(id_bytes, &id, sizeof(id));
+  return CEL_OK;
+}
+
+int cel_comm_init(cel_solver* s, int world, int rank, const void* id_bytes) {
+  if (!s) return CEL_INVALID_ARGUMENT;
+  if (world < 1 || rank < 0 || rank >= world) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "rank outside [0, world)");
+  cel_comm_destroy(s);
+  s->world = world; s->rank = rank;
+  if (world == 1) return CEL_OK;
+  if (!id_bytes) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null communicator id");
+  NcclApi& nc = nccl_api();
+  if (!nc.err.empty()) CEL_FAIL(s, CEL_CUDA_ERROR, nc.err);
+  CEL_CUDA_TRY(s, cudaSetDevice(s->device));
+  ncclUniqueId id;
+  memcpy(&id, id_bytes, sizeof(id));
+  ncclComm_t comm = nullptr;
+  CEL_NCCL_TRY(s, nc.CommInitRank(&comm, world, id, rank));
+  s->nccl_comm = comm;
+  return CEL_OK;
+}
+
+int cel_comm_destroy(cel_solver* s) {
+  if (!s) return CEL_INVALID_ARGUMENT;
+  if (s->nccl_comm) {
+    NcclApi& nc = nccl_api();
+    if (nc.CommDestroy) nc.CommDestroy(static_cast<ncclComm_t>(s->nccl_comm));
+    s->nccl_comm = nullptr;
+  }
+  s->world = 1; s->rank = 0;
+  return CEL_OK;
+}
+
+int cel_mgpu_bounds(int64_t N, int world, int rank, int64_t* lo, int64_t* hi) {
+  if (N < 0 || world < 1 || rank < 0 || rank >= world || !lo || !hi) return CEL_INVALID_ARGUMENT;
+  const int64_t base = N / world, rem = N % world;
+  *lo = rank * base + (rank < rem ? rank : rem);
+  *hi = *lo + base + (rank < rem ? 1 : 0);
+  return CEL_OK;
+}
+
+int cel_compute_mgpu(cel_solver* s, double jitter, int Jr, const double* a_real, const double* c_real, int Jc,
+                     const double* a_comp, const double* b_comp, const double* c_comp, const double* d_comp,
+                     int64_t N, const double* x, const double* diag, int64_t halo) {
+  if (!s) return CEL_INVALID_ARGUMENT;
+  if (N < s->world || !x || !diag || halo < 0) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "series shorter than the number of ranks, or null input");
+  int64_t lo = 0, hi = 0;
+  cel_mgpu_bounds(N, s->world, s->rank, &lo, &hi);
+  if (halo > lo) halo = lo;
+  const int64_t s0 = lo - halo, n = hi - s0;
+  if (n > 0x7fffffffLL) CEL_FAIL(s, CEL_UNSUPPORTED, "span longer than 2^31 steps");
+  s->mg_N = 0;
+  int rc = cel_compute(s, jitter, Jr, a_real, c_real, Jc, a_comp, b_comp, c_comp, d_comp, 0, nullptr, nullptr,
+                       nullptr, (int)n, x + s0, diag + s0);
+  if (rc != CEL_OK) return rc;
+  if (halo > 0) {
+    rc = cel_span_trim(s, (int)halo);
+    if (rc != CEL_OK) return rc;
+  }
+  s->mg_N = N; s->mg_lo = lo; s->mg_hi = hi;
+  return CEL_OK;
+}
+
+int cel_solve_mgpu(cel_solver* s, int nrhs, const double* d_b, double* d_out) {
+  int rc = mgpu_ready(s, nrhs);
+  if (rc != CEL_OK) return rc;
+  if (!d_b || !d_out) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null pointer");
+  const int Nloc = s->N - s->n_off;
+  CEL_CUDA_TRY(s, s->scan_tmp.reserve(dbytes((size_t)Nloc * nrhs)));
+  rc = mgpu_sweep(s, 0, nrhs, d_b, s->scan_tmp.d());         // x / D
+  if (rc != CEL_OK) return rc;
+  return mgpu_sweep(s, 2, nrhs, s->scan_tmp.d(), d_out);     // K^-1 b
+}
+
+int cel_dot_L_mgpu(cel_solver* s, int nrhs, const double* d_z, double* d_out) {
+  int rc = mgpu_ready(s, nrhs);
+  if (rc != CEL_OK) return rc;
+  if (!d_z || !d_out) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null pointer");
+  return mgpu_sweep(s, 1, nrhs, d_z, d_out);
+}
+
+int cel_log_likelihood_mgpu(cel_solver* s, const double* d_y, double* out3) {
+  int rc = mgpu_ready(s, 1);
+  if (rc != CEL_OK) return rc;
+  if (!d_y || !out3) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null pointer");
+  const int Nloc = s->N - s->n_off;
+  CEL_CUDA_TRY(s, s->scan_tmp.reserve(dbytes((size_t)Nloc)));
+  CEL_CUDA_TRY(s, s->mg_scalars.reserve(dbytes(2)));
+  CEL_CUDA_TRY(s, s->scratch2.reserve(dbytes(cel::quad_scratch_doubles())));
+  rc = mgpu_sweep(s, 0, 1, d_y, s->scan_tmp.d());
+  if (rc != CEL_OK) return rc;
+  double* sc = s->mg_scalars.d();
+  // this span's share of log det K and of y^T K^-1 y (fixed summation order), then one all-reduce
+  CEL_CUDA_TRY(s, cel::launch_quad(Nloc, nullptr, s->D.d() + s->n_off, s->scratch2.d(), sc, s->stream));
+  CEL_CUDA_TRY(s, cel::launch_quad(Nloc, s->scan_tmp.d(), s->D.d() + s->n_off, s->scratch2.d(), sc + 1, s->stream));
+  s->launches += 4;
+  if (s->world > 1)
+    CEL_NCCL_TRY(s, nccl_api().AllReduce(sc, sc, 2, ncclDouble, ncclSum, static_cast<ncclComm_t>(s->nccl_comm), s->stream));
+  double* res = static_cast<double*>(s->pinned);
+  CEL_CUDA_TRY(s, cudaMemcpyAsync(res, sc, dbytes(2), cudaMemcpyDeviceToHost, s->stream));
+  CEL_CUDA_TRY(s, cudaStreamSynchronize(s->stream));
+  out3[0] = res[0];
+  out3[1] = res[1];
+  out3[2] = -0.5 * (res[1] + res[0] + (double)s->mg_N * 1.8378770664093454836);
+  return CEL_OK;
+}
 
 int cel_solve_device(cel_solver* s, int nrhs, const double* d_b, double* d_out) {
   int rc = check_ready(s, nrhs);

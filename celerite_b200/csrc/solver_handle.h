@@ -65,6 +65,12 @@ struct cel_solver {
   cel::DevBuf pmaps[3], smaps[3], tmaps[3];   // prefix / super-chunk / whole-span maps (scan.cu, "middle")
   cel::DevBuf scan_vecs, scan_h, scan_cs, scan_sg, scan_total, scan_tmp;
 
+  // ---- several GPUs, one span of a long series per rank (capi_scan.cu: cel_comm_*, cel_*_mgpu) ----
+  void* nccl_comm = nullptr;       // ncclComm_t, created by cel_comm_init on this handle's device
+  int world = 1, rank = 0;
+  long long mg_N = 0, mg_lo = 0, mg_hi = 0;    // length of the whole series and this rank's span [lo, hi)
+  cel::DevBuf mg_summary, mg_gathered, mg_carry, mg_scalars;
+
   // ---- scratch ----
   cel::DevBuf in0, in1, in2, in3;  // single-series inputs / rhs
   cel::DevBuf out0, out1;

@@ -192,9 +192,15 @@ class LongSeries(object):
 
 
 class DistributedLongSeries(object):
-    """One long series split by time over the ranks of ``torch.distributed`` (one GPU each)."""
+    """One long series split by time over the ranks of ``torch.distributed`` (one GPU each).
 
-    def __init__(self, device=-1, group=None):
+    On CUDA the whole exchange lives in the C library (cel_comm_init / cel_*_mgpu: summarize ->
+    ncclAllGather -> fold -> apply enqueued from C++ on one stream, one host call per operation);
+    torch.distributed only carries the 128-byte NCCL id from rank 0 to the others once.  With
+    ``use_c_abi=False`` (and in the CPU tests of the host logic, gloo backend) the all-gather goes
+    through torch.distributed instead and the fold is the torch statement `fold_carries`."""
+
+    def __init__(self, device=-1, group=None, use_c_abi=True):
         import torch.distributed as dist
         self.dist = dist
         self.group = group
@@ -202,15 +208,52 @@ class DistributedLongSeries(object):
         self.world = dist.get_world_size(group)
         self.local = LongSeries(device)
         self.lo = self.hi = self.halo = 0
+        self.c_abi = False
+        self.collective_backend = "torch.distributed all_gather_into_tensor"
+        if use_c_abi and self.world > 1:
+            self._init_comm()
+
+    def _init_comm(self):
+        import torch
+        lib, h = self.local._lib, self.local._h
+        dev = torch.device("cuda", torch.cuda.current_device())
+        backend = self.dist.get_backend(self.group)
+        ident = torch.zeros(_capi.COMM_ID_BYTES, dtype=torch.uint8)
+        if self.rank == 0:
+            buf = (C.c_ubyte * _capi.COMM_ID_BYTES)()
+            _capi.check(lib.cel_comm_unique_id(buf), h)
+            ident = torch.frombuffer(bytearray(buf), dtype=torch.uint8).clone()
+        if backend == "nccl":
+            ident = ident.to(dev)
+        src = self.dist.get_global_rank(self.group, 0) if self.group is not None else 0
+        self.dist.broadcast(ident, src=src, group=self.group)
+        raw = bytes(ident.cpu().numpy().tobytes())
+        _capi.check(lib.cel_comm_init(h, self.world, self.rank, C.c_char_p(raw)), h)
+        self.c_abi = True
+        self.collective_backend = "ncclAllGather / ncclAllReduce inside the C ABI (cel_*_mgpu)"
 
     def compute(self, jitter, a_real, c_real, a_comp, b_comp, c_comp, d_comp, x, diag, halo):
         """x, diag: the FULL host arrays (every rank slices its own span + halo)."""
         N = len(x)
         self.lo, self.hi = span_bounds(N, self.world, self.rank)
         self.halo = min(int(halo), self.lo)
+        if self.c_abi:
+            v = lambda a: np.ascontiguousarray(np.asarray(a, dtype=np.float64).reshape(-1))  # noqa: E731
+            a_real, c_real, a_comp, b_comp, c_comp, d_comp, x, diag = map(v, (a_real, c_real, a_comp, b_comp, c_comp,
+                                                                              d_comp, x, diag))
+            p = lambda a: C.c_void_p(a.ctypes.data)  # noqa: E731
+            lib, h = self.local._lib, self.local._h
+            rc = lib.cel_compute_mgpu(h, float(jitter), a_real.size, p(a_real), p(c_real), a_comp.size, p(a_comp),
+                                      p(b_comp), p(c_comp), p(d_comp), N, p(x), p(diag), int(halo))
+            _capi.check(rc, h)
+            self.local.N = self.hi - self.lo
+            self.local.J = a_real.size + 2 * a_comp.size
+            self.N_total = N
+            return
         s0 = self.lo - self.halo
         self.local.compute(jitter, a_real, c_real, a_comp, b_comp, c_comp, d_comp, x[s0:self.hi], diag[s0:self.hi],
                            halo=self.halo)
+        self.N_total = N
 
     def _sweep(self, op, cols):
         import torch
@@ -225,7 +268,19 @@ class DistributedLongSeries(object):
             carry = fold_carries(gathered, self.rank, op, cols.shape[0], self.local.J)
         return self.local.apply(op, cols, carry, reuse_summary=True)
 
+    def _mgpu(self, fn, b_local):
+        import torch
+        cols, squeeze = self.local._cols(b_local)
+        out = torch.empty_like(cols)
+        self.local._use_stream(b_local)
+        h = self.local._h
+        _capi.check(fn(h, cols.shape[0], C.c_void_p(cols.data_ptr()), C.c_void_p(out.data_ptr())), h)
+        out = out.transpose(0, 1)
+        return out[:, 0] if squeeze else out
+
     def solve(self, b_local):
+        if self.c_abi:
+            return self._mgpu(self.local._lib.cel_solve_mgpu, b_local)
         cols, squeeze = self.local._cols(b_local)
         xd = self._sweep(OP_SOLVE_FORWARD, cols)
         z = self._sweep(OP_SOLVE_BACKWARD, xd)
@@ -233,6 +288,8 @@ class DistributedLongSeries(object):
         return z[:, 0] if squeeze else z
 
     def dot_L(self, z_local):
+        if self.c_abi:
+            return self._mgpu(self.local._lib.cel_dot_L_mgpu, z_local)
         cols, squeeze = self.local._cols(z_local)
         out = self._sweep(OP_DOT_L, cols).transpose(0, 1)
         return out[:, 0] if squeeze else out
@@ -250,10 +307,21 @@ class DistributedLongSeries(object):
         self.dist.all_reduce(q, group=self.group)
         return q[0]
 
-    def log_likelihood(self, y_local, N_total):
+    def log_likelihood(self, y_local, N_total=None):
         """celerite.py:214-216 for the whole series (N_total = its length over all ranks)."""
         import math
-        return -0.5 * (self.dot_solve(y_local) + self.log_determinant(y_local.device) + N_total * math.log(2.0 * math.pi))
+        if self.c_abi:
+            cols, _ = self.local._cols(y_local)
+            self.local._use_stream(y_local)
+            out = (C.c_double * 3)()
+            h = self.local._h
+            _capi.check(self.local._lib.cel_log_likelihood_mgpu(h, C.c_void_p(cols.data_ptr()), out), h)
+            return float(out[2])
+        N_total = self.N_total if N_total is None else N_total
+        return -0.5 * (self.dist_solve_logdet(y_local) + N_total * math.log(2.0 * math.pi))
+
+    def dist_solve_logdet(self, y_local):
+        return self.dot_solve(y_local) + self.log_determinant(y_local.device)
 
 
 class CapturedSweep(object):

@@ -220,6 +220,40 @@ int cel_span_log_determinant(cel_solver* s, double* d_out);
 int cel_span_quad(cel_solver* s, const double* d_xd, double* d_out);
 int cel_span_dims(const cel_solver* s, int* n_local, int* J, int* nchunks, int* chunk_len);
 
+/* ---- one long series over several GPUs, collectives inside the library ------------------------
+ * (no counterpart in the reference, whose sweeps are N serial steps on one core: cholesky.h:218-431)
+ * One process per GPU, one handle per process.  The time axis is cut into `world` contiguous spans;
+ * rank r owns [lo_r, hi_r) (cel_mgpu_bounds).  The only data that crosses NVLink is what the scans
+ * carry from span to span -- (J^2 + J) doubles per rank and sweep, J for dot_L -- exchanged with
+ * ncclAllGather on the handle's stream, plus one ncclAllReduce of two doubles for the
+ * log-likelihood.  Everything is enqueued from C++ on the handle's stream: one host call per
+ * operation, no synchronisation in between (cel_log_likelihood_mgpu synchronises to return scalars).
+ * NCCL is loaded at run time (dlopen "libnccl.so.2": in a process that already holds PyTorch's
+ * NCCL that copy is used); without it cel_comm_* return CEL_CUDA_ERROR and a message.
+ *
+ *   rank 0:      cel_comm_unique_id(id)           -> CEL_COMM_ID_BYTES bytes, handed to every rank by the caller
+ *                                                    (MPI, a socket, torch.distributed.broadcast, a file ...)
+ *   every rank:  cel_comm_init(h, world, rank, id)   collective (ncclCommInitRank on the handle's device)
+ *                cel_compute_mgpu(h, ..., N, x, diag, halo)   x, diag: the WHOLE host arrays; the rank
+ *                     factorises [lo - halo, hi) (the halo warms the recursion up, see cel_span_trim)
+ *                cel_solve_mgpu / cel_dot_L_mgpu   d_in, d_out: this rank's span, device memory,
+ *                     (hi - lo) x nrhs column-major
+ *                cel_log_likelihood_mgpu           d_y: this rank's span; out[3] (host) = log det K,
+ *                     y^T K^-1 y, -0.5 (quad + logdet + N log 2 pi) of the whole series, on every rank */
+#define CEL_COMM_ID_BYTES 128
+int cel_comm_unique_id(void* id_bytes);
+int cel_comm_init(cel_solver* s, int world, int rank, const void* id_bytes);
+int cel_comm_destroy(cel_solver* s);
+int cel_mgpu_bounds(int64_t N, int world, int rank, int64_t* lo, int64_t* hi);
+int cel_compute_mgpu(cel_solver* s, double jitter,
+                     int Jr, const double* a_real, const double* c_real,
+                     int Jc, const double* a_comp, const double* b_comp,
+                     const double* c_comp, const double* d_comp,
+                     int64_t N, const double* x, const double* diag, int64_t halo);
+int cel_solve_mgpu(cel_solver* s, int nrhs, const double* d_b, double* d_out);    /* cholesky.h:218-318 */
+int cel_dot_L_mgpu(cel_solver* s, int nrhs, const double* d_z, double* d_out);    /* cholesky.h:409-431 */
+int cel_log_likelihood_mgpu(cel_solver* s, const double* d_y, double* out3);      /* celerite.py:211-216 */
+
 /* ---- gradient without any allocation (no counterpart in the reference) ----------------------
  * For callers that must not allocate: applications that gave the whole GPU to their own pool
  * allocator and forbid cudaMalloc/cudaFree once running (both synchronise the device), fixed

@@ -27,6 +27,20 @@ def test_span_bounds_cover_everything():
             assert max(h - l for l, h in b) - min(h - l for l, h in b) <= 1
 
 
+def test_c_abi_span_bounds_agree_with_the_python_statement():
+    """cel_mgpu_bounds (the split cel_compute_mgpu uses) is plain integer arithmetic: callable without a GPU."""
+    import ctypes as C
+    from celerite_b200 import _capi, longseries as ls
+    lib = _capi.lib()
+    for N in (8, 1000, 10**7 + 3, 2**33 + 5):
+        for world in (1, 2, 3, 8):
+            for r in range(world):
+                lo, hi = C.c_int64(), C.c_int64()
+                assert lib.cel_mgpu_bounds(N, world, r, C.byref(lo), C.byref(hi)) == _capi.OK
+                assert (lo.value, hi.value) == ls.span_bounds(N, world, r)
+    assert lib.cel_mgpu_bounds(10, 2, 2, C.byref(lo), C.byref(hi)) == _capi.INVALID_ARGUMENT
+
+
 def test_fold_carries_gloo_world2():
     import subprocess
     import sys
