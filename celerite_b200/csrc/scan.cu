@@ -20,6 +20,8 @@
 // Mapping: one group of L = pow2ceil(J) lanes per (chunk, column); lane k owns row k; the factor
 // rows of a step are J contiguous doubles, so a group's loads are coalesced; a register ring
 // keeps one 8-step tile of loads in flight ahead of the recurrence.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -515,6 +517,7 @@ struct MidArgs {
   const double* g0;       // [nrhs][J] carry entering the span (or NULL = 0)
   double* sg;             // [nsuper][nrhs][J]
   double* total;          // [nrhs + nbasis][J]  offset and map of the whole span (optional)
+  int fast;               // the records of one walk fit in shared memory: affine_walk_fast
 };
 
 constexpr int kMidMaxJ = 32;
@@ -614,11 +617,102 @@ __global__ void __launch_bounds__(kWarp) k_mid_prefix(MidArgs m, int level) {
     for (int i = 0; i < nb; ++i) dst[i * J + k] = Mr[i * J + k];
 }
 
+// flat global -> shared copy of n doubles by one warp (16-byte units when both ends allow it)
+__device__ __forceinline__ void warp_copy_async(double* dst, const double* src, int n, int lane) {
+  if (((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15u) == 0 && (n & 1) == 0) {
+    for (int e = 2 * lane; e < n; e += 2 * kWarp) cp_async_16(dst + e, src + e);
+  } else {
+    for (int e = lane; e < n; e += kWarp) cp_async_8(dst + e, src + e);
+  }
+}
+
+// The same walk when all its records fit in shared memory (the usual case: ~sqrt(K) records of
+// (nbasis + nrhs) J doubles): they are brought in with a few wide copies, the carry lives in
+// registers (lane k = row k, the other rows come by shuffle) and a step is one short dependent chain
+// -- no copy, wait or barrier per step.  At K = 4,883 chunks, J = 8 a walk of 70 records went from
+// 41 us to a few us.  nrhs <= 4.
+template <int JT>
+__device__ __forceinline__ void affine_walk_fast(const MidArgs& m, const RecStream& rs, double* buf,
+                                                 const double* g_init, double* before, double* final_out, int k,
+                                                 bool row_ok) {
+  constexpr int NR = 4;
+  const int J = m.J, nrhs = m.nrhs, lenM = rs.lenM, lenC = rs.lenC;
+  if (rs.count <= 0) {
+    if (final_out && row_ok)
+      for (int r = 0; r < nrhs; ++r) final_out[r * J + k] = g_init ? g_init[r * J + k] : 0.0;
+    return;
+  }
+  // units of this walk in memory order
+  const int ua = rs.unit(rs.first), ub = rs.unit(rs.first + rs.count - 1);
+  const int u0 = min(ua, ub);
+  const bool interleaved = (rs.srcM == rs.srcC + lenC) && rs.strideM == rs.strideC;
+  double* bufM;
+  double* bufC;
+  if (interleaved) {
+    warp_copy_async(buf, rs.srcC + (size_t)u0 * rs.strideC, rs.count * rs.strideC, k);
+    bufC = buf; bufM = buf + lenC;
+  } else {
+    warp_copy_async(buf, rs.srcM + (size_t)u0 * rs.strideM, rs.count * rs.strideM, k);
+    bufM = buf;
+    bufC = buf + (((size_t)rs.count * rs.strideM + 1) & ~(size_t)1);
+    if (lenC > 0) warp_copy_async(bufC, rs.srcC + (size_t)u0 * rs.strideC, rs.count * rs.strideC, k);
+  }
+  cp_async_commit_group();
+  double g[NR];
+#pragma unroll
+  for (int r = 0; r < NR; ++r) g[r] = (g_init && row_ok && r < nrhs) ? g_init[r * J + k] : 0.0;
+  cp_async_wait_group<0>();
+  __syncwarp();
+  const int kk = row_ok ? k : 0;
+  for (int q = rs.first; q < rs.first + rs.count; ++q) {
+    const int un = rs.unit(q);
+    const double* Mp = bufM + (size_t)(un - u0) * rs.strideM;
+    const double* Cp = bufC + (size_t)(un - u0) * rs.strideC;
+    if (before && row_ok) {
+      double* bdst = before + (size_t)un * nrhs * J;
+#pragma unroll
+      for (int r = 0; r < NR; ++r)
+        if (r < nrhs) bdst[r * J + k] = g[r];
+    }
+    if (m.diag) {
+      const double mk = Mp[kk];
+#pragma unroll
+      for (int r = 0; r < NR; ++r)
+        if (r < nrhs) g[r] = fma(mk, g[r], Cp[r * J + kk]);
+    } else {
+      double row[JT];
+#pragma unroll
+      for (int j = 0; j < JT; ++j) row[j] = (j < J) ? Mp[j * J + kk] : 0.0;
+#pragma unroll
+      for (int r = 0; r < NR; ++r) {
+        if (r < nrhs) {      // warp-uniform
+          double acc0 = Cp[r * J + kk], acc1 = 0.0;
+#pragma unroll
+          for (int j = 0; j < JT; j += 2) {
+            acc0 = fma(row[j], __shfl_sync(kFull, g[r], j), acc0);
+            if (j + 1 < JT) acc1 = fma(row[j + 1], __shfl_sync(kFull, g[r], j + 1), acc1);
+          }
+          g[r] = acc0 + acc1;
+        }
+      }
+    }
+  }
+  if (final_out && row_ok) {
+#pragma unroll
+    for (int r = 0; r < NR; ++r)
+      if (r < nrhs) final_out[r * J + k] = g[r];
+  }
+}
+
 // g <- M g + c along `count` records; the carry BEFORE each record goes to before[unit], the
 // final one to final_out.  g lives in shared memory, double-buffered: one warp barrier per step.
 template <int JT>
 __device__ __forceinline__ void affine_walk(const MidArgs& m, const RecStream& rs, double* gs, const double* g_init,
                                             double* before, double* final_out, int k, bool row_ok) {
+  if (m.fast) {
+    affine_walk_fast<JT>(m, rs, gs, g_init, before, final_out, k, row_ok);
+    return;
+  }
   const int J = m.J, nrhs = m.nrhs, lenM = rs.lenM;
   for (int i = k; i < nrhs * J; i += kWarp) gs[i] = g_init ? g_init[i] : 0.0;
   rs.prime(k);
@@ -727,9 +821,21 @@ cudaError_t launch_prefix(const MidArgs& m, cudaStream_t stream) {
   return cudaGetLastError();
 }
 
+// shared memory of the walk kernels when a whole walk of `nrec` records is held at once (0: does not apply)
+inline size_t fast_walk_smem(const MidArgs& m, int nrec) {
+  static const bool off = getenv("CEL_NO_FAST_WALK") != nullptr;   // debugging knob
+  if (off || m.nrhs > 4) return 0;
+  const size_t n = (size_t)nrec * (m.nbasis + m.nrhs) * m.J + 2;
+  return n * sizeof(double) <= 160 * 1024 ? n * sizeof(double) : 0;
+}
+
 template <int JT>
-cudaError_t launch_walks(const MidArgs& m, bool walk, bool scan, cudaStream_t stream) {
-  const size_t smem = (size_t)(2 * m.nrhs * m.J + kRing * (m.nbasis + m.nrhs) * m.J) * sizeof(double);
+cudaError_t launch_walks(const MidArgs& m_in, bool walk, bool scan, cudaStream_t stream) {
+  MidArgs m = m_in;
+  size_t smem = (size_t)(2 * m.nrhs * m.J + kRing * (m.nbasis + m.nrhs) * m.J) * sizeof(double);
+  const size_t fs = fast_walk_smem(m, m.per_super > m.nsuper ? m.per_super : m.nsuper);
+  m.fast = fs != 0;
+  if (m.fast) smem = fs;
   if (smem > 200 * 1024) return cudaErrorInvalidValue;   // too many right-hand sides for one middle pass
   cudaError_t e = opt_in_smem(k_mid_walk<JT>, smem);
   if (e == cudaSuccess) e = opt_in_smem(k_mid_scan<JT>, smem);
@@ -849,7 +955,10 @@ cudaError_t launch_span_fold(int J, int nrhs, int nbasis, int diag, int reverse,
   m.per_super = 0;                                    // the walk starts at its first rank...
   m.nsuper = reverse ? world - 1 - rank : rank;       // ...and stops in front of this one
   m.maps = gathered; m.total = carry_out;
-  const size_t smem = (size_t)(2 * nrhs * J + kRing * (nbasis + nrhs) * J) * sizeof(double);
+  size_t smem = (size_t)(2 * nrhs * J + kRing * (nbasis + nrhs) * J) * sizeof(double);
+  const size_t fs = fast_walk_smem(m, world);
+  m.fast = fs != 0;
+  if (m.fast) smem = fs;
   if (smem > 200 * 1024) return cudaErrorInvalidValue;
   cudaError_t e = cudaSuccess;
 #define CALL(JT)                                              \
