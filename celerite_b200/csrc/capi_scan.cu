@@ -184,10 +184,28 @@ int mgpu_sweep(cel_solver* s, int op, int nrhs, const double* d_in, double* d_ou
   if (rc != CEL_OK) return rc;
   CEL_NCCL_TRY(s, nc.AllGather(s->mg_summary.p, s->mg_gathered.p, count, ncclDouble,
                                static_cast<ncclComm_t>(s->nccl_comm), s->stream));
-  CEL_CUDA_TRY(s, cel::launch_span_fold(J, nrhs, nb, op == 1, op == 2, s->world, s->rank, s->mg_gathered.d(),
-                                        s->mg_carry.d(), s->stream));
+  // the scan stage again, this time from the true incoming carry, which the same kernel folds from the
+  // gathered summaries; then pass 2
+  const int K = s->scan_nchunks;
+  int per_super = 0, nsuper = 0;
+  cel::middle_split(K, &per_super, &nsuper);
+  bool fused = false;
+  CEL_CUDA_TRY(s, cel::launch_middle_scan_folded(J, nrhs, nb, op == 1, op == 2, K, s->smaps[op].d(), s->tmaps[op].d(),
+                                                 s->scan_cs.d(), s->scan_sg.d(), s->mg_gathered.d(), s->world,
+                                                 s->rank, &fused, s->stream));
+  if (!fused) {
+    CEL_CUDA_TRY(s, cel::launch_span_fold(J, nrhs, nb, op == 1, op == 2, s->world, s->rank, s->mg_gathered.d(),
+                                          s->mg_carry.d(), s->stream));
+    s->launches += 1;
+    return scan_sweep(s, op, nrhs, d_in, s->mg_carry.d(), d_out, nullptr, true);
+  }
   s->launches += 1;
-  return scan_sweep(s, op, nrhs, d_in, s->mg_carry.d(), d_out, nullptr, true);
+  cel::ScanArgs a = base_args(s, s->N - s->n_off, op);
+  a.nrhs = nrhs; a.nbasis = 0; a.in = d_in; a.out = d_out; a.init = s->scan_h.d(); a.carry = nullptr;
+  a.pmap = s->pmaps[op].d(); a.sg = s->scan_sg.d(); a.per_super = per_super; a.walk_reverse = (op == 2);
+  CEL_CUDA_TRY(s, cel::launch_chunk_sweep(a, s->stream));
+  s->launches += 1;
+  return CEL_OK;
 }
 
 int mgpu_ready(cel_solver* s, int nrhs) {

@@ -213,6 +213,12 @@ cudaError_t launch_middle(int J, int nrhs, int nbasis, int diag, int reverse, in
                           const double* vecs, const double* smaps, const double* tmap, double* h, double* cs,
                           const double* g0, double* sg, double* total, int do_walk, int do_scan,
                           cudaStream_t stream);
+// scan stage alone, with the incoming carry folded from the all-gathered span summaries of `world`
+// ranks inside the same kernel (multi-GPU sweeps: saves the separate fold launch).  *fused = false
+// when the records do not fit the fast path: the caller then folds with launch_span_fold.
+cudaError_t launch_middle_scan_folded(int J, int nrhs, int nbasis, int diag, int reverse, int nunits,
+                                      const double* smaps, const double* tmap, const double* cs, double* sg,
+                                      const double* gathered, int world, int rank, bool* fused, cudaStream_t stream);
 void middle_split(int nunits, int* per_super, int* nsuper);
 cudaError_t launch_span_fold(int J, int nrhs, int nbasis, int diag, int reverse, int world, int rank,
                              const double* gathered, double* carry_out, cudaStream_t stream);

@@ -518,6 +518,10 @@ struct MidArgs {
   double* sg;             // [nsuper][nrhs][J]
   double* total;          // [nrhs + nbasis][J]  offset and map of the whole span (optional)
   int fast;               // the records of one walk fit in shared memory: affine_walk_fast
+  // scan stage of a multi-GPU sweep: fold the gathered span summaries [world][nrhs + nbasis][J] of the
+  // ranks in front of this one (behind it, for the backward sweep) into the incoming carry first
+  const double* fold_src;
+  int fold_world, fold_count, g0_off;   // g0_off: doubles into shared memory where the folded carry is kept
 };
 
 constexpr int kMidMaxJ = 32;
@@ -777,7 +781,19 @@ __global__ void __launch_bounds__(kWarp) k_mid_scan(MidArgs m) {
   rs.lenM = m.nbasis * m.J; rs.lenC = m.nrhs * m.J; rs.strideM = rs.lenM; rs.strideC = rs.lenC;
   rs.srcM = m.smaps; rs.srcC = m.cs;
   rs.first = 0; rs.count = m.nsuper; rs.nwalk = m.nsuper; rs.reverse = 0;
-  affine_walk<JT>(m, rs, sm, m.g0, m.sg, m.total, k, k < m.J);
+  const double* g_init = m.g0;
+  if (m.fold_src) {   // fast path only (launch_middle_scan_folded)
+    RecStream fr;
+    fr.buf = sm;
+    fr.lenM = rs.lenM; fr.lenC = rs.lenC; fr.strideM = fr.strideC = rs.lenM + rs.lenC;
+    fr.srcM = m.fold_src + fr.lenC; fr.srcC = m.fold_src;
+    fr.first = 0; fr.count = m.fold_count; fr.nwalk = m.fold_world; fr.reverse = m.reverse;
+    double* g0s = sm + m.g0_off;
+    affine_walk_fast<JT>(m, fr, sm, nullptr, nullptr, g0s, k, k < m.J);
+    __syncwarp();
+    g_init = g0s;
+  }
+  affine_walk<JT>(m, rs, sm, g_init, m.sg, m.total, k, k < m.J);
   if (m.total)
     for (int i = k; i < m.nbasis * m.J; i += kWarp) m.total[m.nrhs * m.J + i] = m.tmap[i];
 }
@@ -945,6 +961,36 @@ cudaError_t launch_middle(int J, int nrhs, int nbasis, int diag, int reverse, in
   CEL_DISPATCH_JT(J, CALL);
 #undef CALL
   return e;
+}
+
+cudaError_t launch_middle_scan_folded(int J, int nrhs, int nbasis, int diag, int reverse, int nunits,
+                                      const double* smaps, const double* tmap, const double* cs, double* sg,
+                                      const double* gathered, int world, int rank, bool* fused, cudaStream_t stream) {
+  *fused = false;
+  if (J > kMidMaxJ || J < 1 || rank < 0 || rank >= world) return cudaErrorInvalidValue;
+  MidArgs m{};
+  m.J = J; m.nrhs = nrhs; m.nbasis = nbasis; m.diag = diag; m.reverse = reverse; m.nunits = nunits;
+  split_units(m);
+  m.smaps = const_cast<double*>(smaps); m.tmap = const_cast<double*>(tmap); m.cs = const_cast<double*>(cs);
+  m.sg = sg; m.g0 = nullptr; m.total = nullptr;
+  const int nrec = m.nsuper > world ? m.nsuper : world;
+  const size_t fs = fast_walk_smem(m, nrec);
+  if (fs == 0) return cudaSuccess;
+  m.fast = 1;
+  m.fold_src = gathered; m.fold_world = world; m.fold_count = reverse ? world - 1 - rank : rank;
+  m.g0_off = (int)(fs / sizeof(double));
+  const size_t smem = fs + (size_t)nrhs * J * sizeof(double);
+  cudaError_t e = cudaSuccess;
+#define CALL(JT)                                                           \
+  {                                                                        \
+    e = opt_in_smem(k_mid_scan<JT>, smem);                                 \
+    if (e == cudaSuccess) k_mid_scan<JT><<<1, kWarp, smem, stream>>>(m);   \
+  }
+  CEL_DISPATCH_JT(J, CALL);
+#undef CALL
+  if (e != cudaSuccess) return e;
+  *fused = true;
+  return cudaGetLastError();
 }
 
 cudaError_t launch_span_fold(int J, int nrhs, int nbasis, int diag, int reverse, int world, int rank,
