@@ -22,6 +22,7 @@
 // row-indexed leaves the kernel in the fused variant.
 #include <cuda.h>
 #include <cstdlib>
+#include <type_traits>
 
 #include "lockstep_common.cuh"
 
@@ -234,6 +235,239 @@ k_loglik_lockstep(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const _
   }
 }
 
+// ---- second generation of the hot loop --------------------------------------------------------------
+// The kernel above is bound by instruction issue (profiles/r01i: 75 fp64 + 65 other instructions per
+// point, an fp64 instruction holding the dispatch port for two cycles), so this one removes
+// instructions that are not arithmetic of the recursion:
+//  * a loop iteration is a whole 8-point tile: barrier wait, slot address, refill and the tile index
+//    arithmetic happen once per tile, and the shared-memory loads use four per-lane offsets computed
+//    before the loop;
+//  * pivot bookkeeping works on PAIRS of pivots and is optimistic: one unsigned compare per pivot
+//    checks that D_n is a normal number in [2^-500, 2^500] (which also excludes zero, negative,
+//    infinite and NaN pivots), the log-determinant takes exponent and mantissa of the product
+//    D_n D_n+1 (no overflow possible in that range), and nothing else is tracked.  A lane that
+//    ever fails the check, and every lane of a warp whose trigonometric arguments leave the range
+//    of the branch-free sincos, recomputes its series at the end in careful_series() -- stock
+//    exp/sincos, IEEE division, a log per pivot, the first negative pivot recorded -- so the
+//    reference's semantics (cholesky.h:176, :208) hold for every input, at full speed for ordinary ones.
+template <int J, bool ALLC>
+__device__ __noinline__ void careful_series(const BatchArgs& a, long long bb, int len, const double (&cf)[(J + 1) / 2][4],
+                                            double asum, double jitter, double* logdet, double* quad, int* fail) {
+  const double* tp = a.t + bb * a.stride;
+  const double* dp = a.diag + bb * a.stride;
+  const double* yp = a.y + bb * a.stride;
+  LockState<J> st;
+#pragma unroll
+  for (int i = 0; i < J * (J + 1) / 2; ++i) st.S[i] = 0.0;
+#pragma unroll
+  for (int j = 0; j < J; ++j) { st.Wp[j] = 0.0; st.DW[j] = 0.0; st.f[j] = 0.0; }
+  st.xprev = 0.0; st.quad = 0.0; st.fail = 0;
+  double lsum = 0.0, tprev = __ldg(tp);
+  int bad_at = 0;
+#pragma unroll 1
+  for (int n = 0; n < len && bad_at == 0; ++n) {
+    const double tt[1] = {__ldg(tp + n)}, dd[1] = {__ldg(dp + n)}, yy[1] = {__ldg(yp + n)};
+    LockGen<J, 1> gn;
+    lock_gen<J, 1, false, ALLC>(gn, cf, a.Jc, tt, tprev);
+    auto sink = [&](int, double Dn, const double*) {
+      if (Dn < 0.0) bad_at = n + 1;          // cholesky.h:176: strictly negative, the sweep stops here
+      lsum += log(Dn);                       // cholesky.h:208
+    };
+    lock_rec<J, 1, ALLC, false, decltype(sink), false, true, false, true>(st, gn, asum, jitter, dd, yy, n, 1, sink);
+    tprev = tt[0];
+  }
+  *logdet = lsum; *quad = st.quad; *fail = bad_at;
+}
+
+template <int J, bool ALLC, int CAP>
+__global__ void __launch_bounds__(kLockThreads) __maxnreg__(CAP)
+k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const __grid_constant__ CUtensorMap tm_d,
+                   const __grid_constant__ CUtensorMap tm_y) {
+  constexpr int G = 2, T = 8, STAGES = 2;
+  constexpr int NP = (J + 1) / 2;
+  constexpr int WARPS = kLockThreads / kWarp;
+  constexpr int kTile = kWarp * T * 8;  // bytes of one [32 x T] box
+  extern __shared__ unsigned char smem_dyn[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned char* smem_al = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
+  unsigned char* wbuf = smem_al + (size_t)warp * (STAGES * 3 * kTile);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_al + (size_t)WARPS * (STAGES * 3 * kTile)) + warp * STAGES;
+
+  const long long b0 = (long long)blockIdx.x * kLockThreads + warp * kWarp;
+  const long long b = b0 + lane;
+  const bool active = b < a.B;
+  const long long bb = active ? b : a.B - 1;  // idle lanes shadow the last series, store nothing
+  const int N = a.N;
+  const double* tp = a.t + bb * a.stride;
+
+  const int Jr = a.Jr, Jc = a.Jc;
+  const double* row = a.coeffs + bb * a.coeff_stride;
+  const double jitter = row[0];
+  const double* a_real = row + 1;
+  const double* c_real = a_real + Jr;
+  const double* a_comp = c_real + Jr;
+  const double* b_comp = a_comp + Jc;
+  const double* c_comp = b_comp + Jc;
+  const double* d_comp = c_comp + Jc;
+  double cf[NP][4];
+  double sum_ar = 0.0, sum_ac = 0.0, dmax = 0.0;
+#pragma unroll
+  for (int p = 0; p < NP; ++p) {
+    if (p < Jc) {
+      cf[p][0] = a_comp[p]; cf[p][1] = b_comp[p]; cf[p][2] = c_comp[p]; cf[p][3] = d_comp[p];
+      dmax = fmax(dmax, fabs(cf[p][3]));
+    } else {
+      int r0 = 2 * (p - Jc), r1 = r0 + 1;
+      cf[p][0] = a_real[r0]; cf[p][1] = c_real[r0];
+      cf[p][2] = (r1 < Jr) ? a_real[r1] : 0.0;
+      cf[p][3] = (r1 < Jr) ? c_real[r1] : 0.0;
+    }
+  }
+  for (int j = 0; j < Jr; ++j) sum_ar += a_real[j];
+  for (int j = 0; j < Jc; ++j) sum_ac += a_comp[j];
+  const double asum = sum_ar + sum_ac;
+  const double tmax = fmax(fabs(__ldg(tp)), fabs(__ldg(tp + N - 1)));
+  const bool warp_fast = __all_sync(kFull, dmax * tmax < kFastTrigLimit);
+
+  const int ntiles = (N + T - 1) / T;
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) mbar_init(&bars[s], 1);
+    mbar_fence_init();
+  }
+  __syncwarp();
+  auto issue = [&](int k) {
+    if (lane == 0) {
+      const int s = k % STAGES;
+      unsigned char* dst = wbuf + (size_t)s * 3 * kTile;
+      fence_async_smem();   // generic-proxy reads of the slot before the async-proxy refill
+      mbar_arrive_expect_tx(&bars[s], 3u * kTile);
+      tma_load_2d(dst, &tm_t, k * T, (int)b0, &bars[s]);
+      tma_load_2d(dst + kTile, &tm_d, k * T, (int)b0, &bars[s]);
+      tma_load_2d(dst + 2 * kTile, &tm_y, k * T, (int)b0, &bars[s]);
+    }
+  };
+  if (warp_fast) {
+#pragma unroll
+    for (int k = 0; k < STAGES; ++k)
+      if (k < ntiles) issue(k);
+  }
+
+  LockState<J> st;
+#pragma unroll
+  for (int i = 0; i < J * (J + 1) / 2; ++i) st.S[i] = 0.0;
+#pragma unroll
+  for (int j = 0; j < J; ++j) { st.Wp[j] = 0.0; st.DW[j] = 0.0; st.f[j] = 0.0; }
+  st.xprev = 0.0; st.quad = 0.0; st.fail = 0;
+  double mant = 1.0;        // product of the pair mantissas since the last renormalisation, in [1, 2^256)
+  int e32 = 0;              // their unbiased exponents
+  long long expo = 0;
+  unsigned bad = warp_fast ? 0u : 1u;
+
+  if (warp_fast) {
+    const int swz = (lane >> 1) & 3;  // 64B swizzle: 16-byte chunk index ^= bits 7..8 of the address
+    const unsigned char* lbase = wbuf + lane * (T * 8);
+    int offc[T / 2];
+#pragma unroll
+    for (int c = 0; c < T / 2; ++c) offc[c] = (c ^ swz) << 4;
+    double tlast = __ldg(tp);
+
+    // one pair of steps: loads, generators, recursion, optimistic bookkeeping
+    auto pair = [&](const unsigned char* src, int c, auto guard, int nvalid) {
+      constexpr bool GUARD = decltype(guard)::value;
+      const double2 v0 = *reinterpret_cast<const double2*>(src + offc[c]);
+      const double2 v1 = *reinterpret_cast<const double2*>(src + kTile + offc[c]);
+      const double2 v2 = *reinterpret_cast<const double2*>(src + 2 * kTile + offc[c]);
+      const double tt[G] = {v0.x, v0.y}, dd[G] = {v1.x, v1.y}, yy[G] = {v2.x, v2.y};
+      LockGen<J, G> gn;
+      lock_gen<J, G, true, ALLC>(gn, cf, Jc, tt, tlast);
+      tlast = tt[G - 1];
+      double Dg[G] = {1.0, 1.0};
+      auto sink = [&](int g, double Dn, const double*) { Dg[g] = Dn; };
+      lock_rec<J, G, ALLC, GUARD, decltype(sink), false, true, false, false>(st, gn, asum, jitter, dd, yy, 0, nvalid, sink);
+      // normal and inside [2^-500, 2^500]: one unsigned compare on the high word (negative numbers,
+      // zero, denormals, inf and nan all land outside)
+      bad |= (unsigned)((unsigned)(__double2hiint(Dg[0]) - 0x20b00000) >= 0x3e800000u);
+      bad |= (unsigned)((unsigned)(__double2hiint(Dg[1]) - 0x20b00000) >= 0x3e800000u);
+      const double P = Dg[0] * Dg[1];
+      const int hp = __double2hiint(P);
+      e32 += (hp >> 20) - 1023;
+      mant *= __hiloint2double((hp & 0x000fffff) | 0x3ff00000, __double2loint(P));
+    };
+    auto renorm = [&]() {
+      const int hi = __double2hiint(mant);
+      expo += e32 + (((hi >> 20) & 0x7ff) - 1023);
+      e32 = 0;
+      mant = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(mant));
+    };
+
+    const int nfull = N / T;
+#pragma unroll 1
+    for (int k = 0; k < nfull; ++k) {
+      const int s = k & (STAGES - 1);
+      mbar_wait(&bars[s], (k / STAGES) & 1);
+      const unsigned char* src = lbase + s * (3 * kTile);
+#pragma unroll
+      for (int c = 0; c < T / 2; ++c) {
+        pair(src, c, std::false_type(), G);
+        if (c == T / 2 - 1) {      // the tile is in registers on every lane: refill its slot
+          __syncwarp();
+          if (k + STAGES < ntiles) issue(k + STAGES);
+        }
+      }
+      if ((k & 63) == 63) renorm();
+    }
+    if (nfull < ntiles) {          // ragged tail: fewer than 8 points, zero-filled by the TMA unit
+      const int s = nfull & (STAGES - 1);
+      mbar_wait(&bars[s], (nfull / STAGES) & 1);
+      const unsigned char* src = lbase + s * (3 * kTile);
+      const int left = N - nfull * T;
+#pragma unroll
+      for (int c = 0; c < T / 2; ++c)
+        if (2 * c < left) pair(src, c, std::true_type(), left - 2 * c);
+    }
+    renorm();
+  }
+
+  double logdet = log(mant) + 0.6931471805599453094 * static_cast<double>(expo);
+  double q = st.quad;
+  int fail = 0;
+  if (bad) careful_series<J, ALLC>(a, bb, N, cf, asum, jitter, &logdet, &q, &fail);
+
+  if (active) {
+    const double nan = __longlong_as_double(0x7ff8000000000000LL);
+    if (fail) { logdet = nan; q = nan; }
+    if (a.out_logdet) a.out_logdet[b] = logdet;
+    if (a.out_quad) a.out_quad[b] = q;
+    if (a.out_ll) a.out_ll[b] = -0.5 * (q + logdet + (double)N * kLog2Pi);  // celerite.py:214-216
+    if (a.status) a.status[b] = fail ? 3 : 0;
+    if (a.fail_index) a.fail_index[b] = fail;
+  }
+}
+
+template <int J, int CAP>
+cudaError_t launch_v2(const BatchArgs& a, cudaStream_t stream, bool* used) {
+  constexpr int T = 8, STAGES = 2;
+  constexpr int WARPS = kLockThreads / kWarp;
+  constexpr size_t smem = (size_t)WARPS * STAGES * 3 * kWarp * T * 8 + WARPS * STAGES * sizeof(uint64_t) + 1024;
+  *used = false;
+  static const bool off = getenv("CEL_LOCK_V1") != nullptr;    // A/B knob: the first-generation loop
+  if (off || a.lengths || a.N < 1) return cudaSuccess;
+  alignas(64) CUtensorMap mt, md, my;
+  if (!(make_series_map(&mt, a.t, a.B, a.N, a.stride, T) && make_series_map(&md, a.diag, a.B, a.N, a.stride, T) &&
+        make_series_map(&my, a.y, a.B, a.N, a.stride, T)))
+    return cudaSuccess;
+  constexpr bool kEven = (J % 2) == 0;
+  const bool allc = kEven && a.Jr == 0;
+  auto kern = allc ? k_loglik_lockstep2<J, kEven, CAP> : k_loglik_lockstep2<J, false, CAP>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  const long long grid = (a.B + kLockThreads - 1) / kLockThreads;
+  kern<<<(unsigned)grid, kLockThreads, smem, stream>>>(a, mt, md, my);
+  *used = true;
+  return cudaGetLastError();
+}
+
 template <int J, int G, int T, int STAGES, int CAP = lock_maxreg(J), bool PIPE = false>
 cudaError_t launch_one(const BatchArgs& a, cudaStream_t stream) {
   constexpr int WARPS = kLockThreads / kWarp;
@@ -281,6 +515,16 @@ cudaError_t launch_one(const BatchArgs& a, cudaStream_t stream) {
 
 cudaError_t launch_loglik_lockstep(const BatchArgs& a, cudaStream_t stream) {
   const int J = a.Jr + 2 * a.Jc;
+  {
+    bool used = false;
+    cudaError_t e = cudaSuccess;
+    switch (J) {
+      case 2: e = launch_v2<2, lock_maxreg(2)>(a, stream, &used); break;
+      case 4: e = launch_v2<4, lock_maxreg(4)>(a, stream, &used); break;
+      default: break;
+    }
+    if (e != cudaSuccess || used) return e;
+  }
   switch (J) {
     case 1: return launch_one<1, 2, 8, 2>(a, stream);
     case 2: {

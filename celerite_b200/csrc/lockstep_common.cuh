@@ -103,7 +103,11 @@ struct NoSink {
 // RAG: the series of this lane ends at `len`; later steps (padding of a ragged batch) still run
 // but feed neither the sums nor the failure flag.
 // SOLVE = false drops the forward substitution and the quadratic form (compute without a right-hand side).
-template <int J, int G, bool ALLC, bool GUARD, typename Sink = NoSink, bool RAG = false, bool SOLVE = true>
+// BOOK = false leaves the pivot bookkeeping (failure flag, log-determinant accumulator) to the caller,
+// who sees every D_n through the sink.  EXACT divides by D_n instead of multiplying by the fast
+// reciprocal (which is only good for normal, finite pivots).
+template <int J, int G, bool ALLC, bool GUARD, typename Sink = NoSink, bool RAG = false, bool SOLVE = true,
+          bool BOOK = true, bool EXACT = false>
 __device__ __forceinline__ void lock_rec(LockState<J>& st, const LockGen<J, G>& gn, const double asum,
                                          const double jitter, const double (&dd)[G], const double (&yy)[G],
                                          const int n0, const int nvalid, Sink sink = Sink(), const int len = 0) {
@@ -155,8 +159,8 @@ __device__ __forceinline__ void lock_rec(LockState<J>& st, const LockGen<J, G>& 
         wn[j] = gn.v[g][j] - su;
       }
       const bool live = !RAG || n0 + g < len;
-      st.fail = (live && Dn < 0.0 && st.fail == 0) ? n0 + g + 1 : st.fail;  // cholesky.h:176
-      const double r = fast_rcp_nocheck(Dn);
+      if constexpr (BOOK) st.fail = (live && Dn < 0.0 && st.fail == 0) ? n0 + g + 1 : st.fail;  // cholesky.h:176
+      const double r = EXACT ? 1.0 / Dn : fast_rcp_nocheck(Dn);
 #pragma unroll
       for (int j = 0; j < J; ++j) { st.DW[j] = wn[j]; st.Wp[j] = wn[j] * r; }
       if constexpr (SOLVE) {
@@ -164,7 +168,7 @@ __device__ __forceinline__ void lock_rec(LockState<J>& st, const LockGen<J, G>& 
         st.quad = live ? q2 : st.quad;
         st.xprev = x;
       }
-      st.ld.add(live ? Dn : 1.0);        // cholesky.h:208
+      if constexpr (BOOK) st.ld.add(live ? Dn : 1.0);        // cholesky.h:208
       sink(g, Dn, st.Wp);
     }
   }
