@@ -471,6 +471,12 @@ def bench_batched(ctx, wl, steps, warmup, e2e_steps, data=None, cpu=True, with_g
             line["cpu_baseline"] = {"value": sample * N * J / cdt, "unit": UNIT, "cores": cores, "kind": chk.kind,
                                     "sample": "first %d of %d series, %d threads, one series per task" % (sample, B, cores),
                                     "max_rel_diff_vs_gpu": max(pure_rel(got[0], ref[:, 0]), pure_rel(got[1], ref[:, 1]))}
+            try:   # the reference's own round-off floor on the same sample: FMA-contracted build against the plain-C restatement
+                alt = oracle.Port().batched_loglik(sample, N, N, Jr, Jc, coeffs_np[:sample], P, ht.numpy()[:sample],
+                                                   hd.numpy()[:sample], hy.numpy()[:sample], nthreads=cores)
+                line["cpu_baseline"]["max_rel_diff_cpu_vs_cpu"] = max(pure_rel(alt[:, 0], ref[:, 0]), pure_rel(alt[:, 1], ref[:, 1]))
+            except Exception:   # noqa: BLE001
+                pass
     return line
 
 

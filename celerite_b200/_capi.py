@@ -72,6 +72,7 @@ SIGNATURES = {
     "cel_solve_mgpu": (C.c_int, [_vp, C.c_int, _vp, _vp]),
     "cel_dot_L_mgpu": (C.c_int, [_vp, C.c_int, _vp, _vp]),
     "cel_log_likelihood_mgpu": (C.c_int, [_vp, _vp, _dp]),
+    "cel_debug_math": (C.c_int, [C.c_int, _i64, _vp, _vp, _vp, _vp]),
     "cel_launch_count": (_i64, [_vp]),
 }
 COMM_ID_BYTES = 128

@@ -71,6 +71,64 @@ __device__ __forceinline__ void cel_sincos_core(double x, double* s, double* c) 
 }
 constexpr double kFastTrigLimit = 1.0e9;
 
+// ----------------------------------------------------------------------------------------------
+// Table-driven variants for the hottest loop (lockstep.cu, second generation): a finer argument
+// reduction (pi/64 and ln2/32 instead of pi/2 and ln2) against small shared-memory tables makes
+// the polynomials short Taylor sums and removes the quadrant logic of sincos altogether:
+//   sincos: 16 fp64 instructions + one 16-byte table load      (core above: 20 + ~10 integer/select)
+//   exp   : 11 fp64 instructions + one  8-byte table load      (core above: 15)
+// Truncation errors: sin 9e-21, cos 3e-18, exp 4e-18 (|r| <= pi/128, ln2/64); the table entries are
+// correctly rounded doubles, so results are good to about 1 ulp of max(|sin|, |cos|), resp. of exp.
+// Same validity range as the cores: |x| < 1e9 for sincos, clamped exponent for exp.
+// ----------------------------------------------------------------------------------------------
+constexpr int kTrigTabN = 128;   // (sin, cos)(j pi/64), j = 0..127
+constexpr int kExpTabN = 32;     // 2^(j/32),           j = 0..31
+namespace tab {
+static __constant__ double kTrigR64[3] = {20.371832715762604, -0.04908738521234052, -1.9135106236677394e-18};
+static __constant__ double kExpR32[3] = {46.16624130844683, -0.02166084939249829, -7.247021293269686e-19};
+static __constant__ double kSinT[3] = {-1.0 / 6.0, 1.0 / 120.0, -1.0 / 5040.0};
+static __constant__ double kCosT[3] = {-0.5, 1.0 / 24.0, -1.0 / 720.0};
+static __constant__ double kExpT[5] = {0.5, 1.0 / 6.0, 1.0 / 24.0, 1.0 / 120.0, 1.0 / 720.0};
+}  // namespace tab
+
+// every thread of the block helps; call __syncthreads()/__syncwarp() afterwards as appropriate
+__device__ __forceinline__ void cel_fill_tables(double2* trig_tab, double* exp_tab, int tid, int nthreads) {
+  for (int j = tid; j < kTrigTabN; j += nthreads) {
+    double sj, cj;
+    sincospi(j * (1.0 / 64.0), &sj, &cj);
+    trig_tab[j] = make_double2(sj, cj);
+  }
+  for (int j = tid; j < kExpTabN; j += nthreads) exp_tab[j] = exp2(j * (1.0 / 32.0));
+}
+
+__device__ __forceinline__ void cel_sincos_tab(double x, double* s, double* c, const double2* trig_tab) {
+  const double kd = fma(x, tab::kTrigR64[0], kRintMagic);
+  const int j = __double2loint(kd) & (kTrigTabN - 1);
+  const double kf = kd - kRintMagic;
+  double r = fma(kf, tab::kTrigR64[1], x);
+  r = fma(kf, tab::kTrigR64[2], r);
+  const double2 T = trig_tab[j];                  // (S, C) of the table angle
+  const double z = r * r;
+  const double sr = fma(r * z, fma(z, fma(z, tab::kSinT[2], tab::kSinT[1]), tab::kSinT[0]), r);   // sin r
+  const double cm = z * fma(z, fma(z, tab::kCosT[2], tab::kCosT[1]), tab::kCosT[0]);               // cos r - 1
+  *s = fma(T.y, sr, fma(T.x, cm, T.x));           // S cos r + C sin r
+  *c = fma(-T.x, sr, fma(T.y, cm, T.y));          // C cos r - S sin r
+}
+
+__device__ __forceinline__ double cel_exp_tab(double x, const double* exp_tab) {
+  const double kd = fma(x, tab::kExpR32[0], kRintMagic);
+  const int k = __double2loint(kd);
+  const double kf = kd - kRintMagic;
+  double r = fma(kf, tab::kExpR32[1], x);
+  r = fma(kf, tab::kExpR32[2], r);
+  const double Tj = exp_tab[k & (kExpTabN - 1)];
+  const double q = fma(r, fma(r, fma(r, fma(r, tab::kExpT[4], tab::kExpT[3]), tab::kExpT[2]), tab::kExpT[1]), tab::kExpT[0]);
+  const double p = fma(r * r, q, r);              // exp(r) - 1
+  const double v = fma(Tj, p, Tj);                // in [0.98, 2.03]
+  const int m = min(max(k >> 5, -1022), 1022);    // clamped like cel_exp_clamped: tiny instead of denormal/zero
+  return __hiloint2double(__double2hiint(v) + (m << 20), __double2loint(v));
+}
+
 // Out-of-line stock routines for the rare slow paths (keeps the hot loops small).
 static __device__ __noinline__ double slow_exp(double x) { return exp(x); }
 static __device__ __noinline__ void slow_sincos(double x, double* s, double* c) { sincos(x, s, c); }

@@ -279,7 +279,7 @@ __device__ __noinline__ void careful_series(const BatchArgs& a, long long bb, in
   *logdet = lsum; *quad = st.quad; *fail = bad_at;
 }
 
-template <int J, bool ALLC, int CAP>
+template <int J, bool ALLC, int CAP, bool TAB>
 __global__ void __launch_bounds__(kLockThreads) __maxnreg__(CAP)
 k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const __grid_constant__ CUtensorMap tm_d,
                    const __grid_constant__ CUtensorMap tm_y) {
@@ -292,6 +292,13 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
   unsigned char* smem_al = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
   unsigned char* wbuf = smem_al + (size_t)warp * (STAGES * 3 * kTile);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_al + (size_t)WARPS * (STAGES * 3 * kTile)) + warp * STAGES;
+  // tables of the table-driven exp / sincos, one copy per CTA behind the barriers
+  double2* trig_tab = reinterpret_cast<double2*>(smem_al + (size_t)WARPS * (STAGES * 3 * kTile) + 64);
+  double* exp_tab = reinterpret_cast<double*>(trig_tab + kTrigTabN);
+  if (TAB) {
+    cel_fill_tables(trig_tab, exp_tab, threadIdx.x, kLockThreads);
+    __syncthreads();
+  }
 
   const long long b0 = (long long)blockIdx.x * kLockThreads + warp * kWarp;
   const long long b = b0 + lane;
@@ -380,7 +387,8 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
       const double2 v2 = *reinterpret_cast<const double2*>(src + 2 * kTile + offc[c]);
       const double tt[G] = {v0.x, v0.y}, dd[G] = {v1.x, v1.y}, yy[G] = {v2.x, v2.y};
       LockGen<J, G> gn;
-      lock_gen<J, G, true, ALLC>(gn, cf, Jc, tt, tlast);
+      if (TAB) lock_gen_tab<J, G, ALLC>(gn, cf, Jc, tt, tlast, trig_tab, exp_tab);
+      else lock_gen<J, G, true, ALLC>(gn, cf, Jc, tt, tlast);
       tlast = tt[G - 1];
       double Dg[G] = {1.0, 1.0};
       auto sink = [&](int g, double Dn, const double*) { Dg[g] = Dn; };
@@ -449,9 +457,10 @@ template <int J, int CAP>
 cudaError_t launch_v2(const BatchArgs& a, cudaStream_t stream, bool* used) {
   constexpr int T = 8, STAGES = 2;
   constexpr int WARPS = kLockThreads / kWarp;
-  constexpr size_t smem = (size_t)WARPS * STAGES * 3 * kWarp * T * 8 + WARPS * STAGES * sizeof(uint64_t) + 1024;
+  constexpr size_t smem = (size_t)WARPS * STAGES * 3 * kWarp * T * 8 + 64 + kTrigTabN * 16 + kExpTabN * 8 + 1024;
   *used = false;
   static const bool off = getenv("CEL_LOCK_V1") != nullptr;    // A/B knob: the first-generation loop
+  static const bool notab = getenv("CEL_LOCK_NOTAB") != nullptr;   // A/B knob: polynomial-only exp / sincos
   if (off || a.lengths || a.N < 1) return cudaSuccess;
   alignas(64) CUtensorMap mt, md, my;
   if (!(make_series_map(&mt, a.t, a.B, a.N, a.stride, T) && make_series_map(&md, a.diag, a.B, a.N, a.stride, T) &&
@@ -459,7 +468,8 @@ cudaError_t launch_v2(const BatchArgs& a, cudaStream_t stream, bool* used) {
     return cudaSuccess;
   constexpr bool kEven = (J % 2) == 0;
   const bool allc = kEven && a.Jr == 0;
-  auto kern = allc ? k_loglik_lockstep2<J, kEven, CAP> : k_loglik_lockstep2<J, false, CAP>;
+  auto kern = allc ? (notab ? k_loglik_lockstep2<J, kEven, CAP, false> : k_loglik_lockstep2<J, kEven, CAP, true>)
+                   : (notab ? k_loglik_lockstep2<J, false, CAP, false> : k_loglik_lockstep2<J, false, CAP, true>);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   const long long grid = (a.B + kLockThreads - 1) / kLockThreads;

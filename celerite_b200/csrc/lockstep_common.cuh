@@ -91,6 +91,44 @@ __device__ __forceinline__ void lock_gen(LockGen<J, G>& o, const double (&cf)[(J
   }
 }
 
+// lock_gen<.., FAST = true> with the table-driven exp / sincos of fastmath.cuh
+template <int J, int G, bool ALLC>
+__device__ __forceinline__ void lock_gen_tab(LockGen<J, G>& o, const double (&cf)[(J + 1) / 2][4], const int Jc,
+                                             const double (&tt)[G], const double tprev, const double2* trig_tab,
+                                             const double* exp_tab) {
+  constexpr int NP = (J + 1) / 2;
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    const double tn = tt[g];
+    const double dx = tn - (g == 0 ? tprev : tt[g == 0 ? 0 : g - 1]);
+#pragma unroll
+    for (int p = 0; p < NP; ++p) {
+      if (ALLC || p < Jc) {
+        double sd, cd;
+        cel_sincos_tab(cf[p][3] * tn, &sd, &cd, trig_tab);
+        const double e = cel_exp_tab(-cf[p][2] * dx, exp_tab);
+        o.phi[g][2 * p] = e;
+        o.u[g][2 * p] = fma(cf[p][0], cd, cf[p][1] * sd);
+        o.v[g][2 * p] = cd;
+        if (2 * p + 1 < J) {
+          o.phi[g][2 * p + 1] = e;
+          o.u[g][2 * p + 1] = fma(cf[p][0], sd, -(cf[p][1] * cd));
+          o.v[g][2 * p + 1] = sd;
+        }
+      } else {
+        o.phi[g][2 * p] = cel_exp_tab(-cf[p][1] * dx, exp_tab);
+        o.u[g][2 * p] = cf[p][0];
+        o.v[g][2 * p] = 1.0;
+        if (2 * p + 1 < J) {
+          o.phi[g][2 * p + 1] = cel_exp_tab(-cf[p][3] * dx, exp_tab);
+          o.u[g][2 * p + 1] = cf[p][2];
+          o.v[g][2 * p + 1] = 1.0;
+        }
+      }
+    }
+  }
+}
+
 // The serial part: G steps of cholesky.h:154-178 fused with the forward substitution of
 // dot_solve (cholesky.h:350-356).  ALLC: every row belongs to a complex pair, whose two rows
 // share phi, so the products phi_q*phi_j are formed once per pair of pairs.

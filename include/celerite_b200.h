@@ -322,6 +322,12 @@ int cel_term_backprop(cel_solver* s, int nterms, const int* kinds, const double*
                       const double* d_params, int64_t param_stride, const double* d_grad_coeffs,
                       int64_t grad_coeff_stride, double* d_grad_params, int64_t grad_param_stride);
 
+/* Diagnostic: the kernels' own exp / sincos (csrc/fastmath.cuh) evaluated on n device doubles, so that
+ * tests can measure their error against libm.  which: 0 polynomial cores (out1 = exp(x); or, with
+ * out2 != NULL, out1 = sin(x), out2 = cos(x)), 1 the table-driven variants of the fused batched
+ * log-likelihood.  Arguments must lie in the routines' range (|x| < 700 for exp, < 1e9 for sincos). */
+int cel_debug_math(int which, int64_t n, const double* d_x, double* d_out1, double* d_out2, void* cuda_stream);
+
 /* Number of kernels this handle has launched since creation (bench.py's gpu_launches). */
 int64_t cel_launch_count(const cel_solver* s);
 
