@@ -279,7 +279,7 @@ __device__ __noinline__ void careful_series(const BatchArgs& a, long long bb, in
   *logdet = lsum; *quad = st.quad; *fail = bad_at;
 }
 
-template <int J, bool ALLC, int CAP, bool TAB>
+template <int J, bool ALLC, int CAP, bool TAB, bool PIPE = false>
 __global__ void __launch_bounds__(kLockThreads) __maxnreg__(CAP)
 k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const __grid_constant__ CUtensorMap tm_d,
                    const __grid_constant__ CUtensorMap tm_y) {
@@ -409,18 +409,55 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
       mant = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(mant));
     };
 
+    // the two halves of `pair`, for the software-pipelined loop: the generators of pair c+1 (independent
+    // chains) are written before the recursion of pair c (one serial chain), so that they fill its bubbles
+    struct PairIn { LockGen<J, G> gn; double dd[G], yy[G]; };
+    auto load_gen = [&](const unsigned char* src, int c, PairIn& o) {
+      const double2 v0 = *reinterpret_cast<const double2*>(src + offc[c]);
+      const double2 v1 = *reinterpret_cast<const double2*>(src + kTile + offc[c]);
+      const double2 v2 = *reinterpret_cast<const double2*>(src + 2 * kTile + offc[c]);
+      const double tt[G] = {v0.x, v0.y};
+      o.dd[0] = v1.x; o.dd[1] = v1.y; o.yy[0] = v2.x; o.yy[1] = v2.y;
+      if (TAB) lock_gen_tab<J, G, ALLC>(o.gn, cf, Jc, tt, tlast, trig_tab, exp_tab);
+      else lock_gen<J, G, true, ALLC>(o.gn, cf, Jc, tt, tlast);
+      tlast = tt[G - 1];
+    };
+    auto rec_book = [&](const PairIn& in) {
+      double Dg[G] = {1.0, 1.0};
+      auto sink = [&](int g, double Dn, const double*) { Dg[g] = Dn; };
+      lock_rec<J, G, ALLC, false, decltype(sink), false, true, false, false>(st, in.gn, asum, jitter, in.dd, in.yy, 0, G, sink);
+      bad |= (unsigned)((unsigned)(__double2hiint(Dg[0]) - 0x20b00000) >= 0x3e800000u);
+      bad |= (unsigned)((unsigned)(__double2hiint(Dg[1]) - 0x20b00000) >= 0x3e800000u);
+      const double P = Dg[0] * Dg[1];
+      const int hp = __double2hiint(P);
+      e32 += (hp >> 20) - 1023;
+      mant *= __hiloint2double((hp & 0x000fffff) | 0x3ff00000, __double2loint(P));
+    };
+
     const int nfull = N / T;
 #pragma unroll 1
     for (int k = 0; k < nfull; ++k) {
       const int s = k & (STAGES - 1);
       mbar_wait(&bars[s], (k / STAGES) & 1);
       const unsigned char* src = lbase + s * (3 * kTile);
+      if (PIPE) {
+        PairIn pa, pb;
+        load_gen(src, 0, pa);
+        load_gen(src, 1, pb); rec_book(pa);
+        load_gen(src, 2, pa); rec_book(pb);
+        load_gen(src, 3, pb);
+        __syncwarp();              // the tile is in registers on every lane: refill its slot
+        if (k + STAGES < ntiles) issue(k + STAGES);
+        rec_book(pa);
+        rec_book(pb);
+      } else {
 #pragma unroll
-      for (int c = 0; c < T / 2; ++c) {
-        pair(src, c, std::false_type(), G);
-        if (c == T / 2 - 1) {      // the tile is in registers on every lane: refill its slot
-          __syncwarp();
-          if (k + STAGES < ntiles) issue(k + STAGES);
+        for (int c = 0; c < T / 2; ++c) {
+          pair(src, c, std::false_type(), G);
+          if (c == T / 2 - 1) {      // the tile is in registers on every lane: refill its slot
+            __syncwarp();
+            if (k + STAGES < ntiles) issue(k + STAGES);
+          }
         }
       }
       if ((k & 63) == 63) renorm();
@@ -461,6 +498,8 @@ cudaError_t launch_v2(const BatchArgs& a, cudaStream_t stream, bool* used) {
   *used = false;
   static const bool off = getenv("CEL_LOCK_V1") != nullptr;    // A/B knob: the first-generation loop
   static const bool notab = getenv("CEL_LOCK_NOTAB") != nullptr;   // A/B knob: polynomial-only exp / sincos
+  // software-pipelined tile loop: 0.803 -> 0.792 ms on cfg2 (J = 2), nothing at J = 4; CEL_LOCK_NOPIPE turns it off
+  static const bool pipe = J <= 2 && getenv("CEL_LOCK_NOPIPE") == nullptr;
   if (off || a.lengths || a.N < 1) return cudaSuccess;
   alignas(64) CUtensorMap mt, md, my;
   if (!(make_series_map(&mt, a.t, a.B, a.N, a.stride, T) && make_series_map(&md, a.diag, a.B, a.N, a.stride, T) &&
@@ -470,6 +509,7 @@ cudaError_t launch_v2(const BatchArgs& a, cudaStream_t stream, bool* used) {
   const bool allc = kEven && a.Jr == 0;
   auto kern = allc ? (notab ? k_loglik_lockstep2<J, kEven, CAP, false> : k_loglik_lockstep2<J, kEven, CAP, true>)
                    : (notab ? k_loglik_lockstep2<J, false, CAP, false> : k_loglik_lockstep2<J, false, CAP, true>);
+  if (pipe && !notab) kern = allc ? k_loglik_lockstep2<J, kEven, CAP, true, true> : k_loglik_lockstep2<J, false, CAP, true, true>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   const long long grid = (a.B + kLockThreads - 1) / kLockThreads;
