@@ -102,8 +102,8 @@ __device__ __forceinline__ void fwd_step(FwdState<J>& st, const double (&cf)[J /
   x_out = x;
 }
 
-template <int J>
-__global__ void __launch_bounds__(kWarp) __maxnreg__(J <= 2 ? 168 : 255)
+template <int J, int REGS>
+__global__ void __launch_bounds__(kWarp) __maxnreg__(REGS)
 k_grad_lockstep(GradArgs a, const __grid_constant__ CUtensorMap tm_t, const __grid_constant__ CUtensorMap tm_d,
                 const __grid_constant__ CUtensorMap tm_y) {
   using C = LG<J>;
@@ -415,7 +415,7 @@ k_grad_lockstep(GradArgs a, const __grid_constant__ CUtensorMap tm_t, const __gr
   }
 }
 
-template <int J>
+template <int J, int REGS>
 cudaError_t launch_one(const GradArgs& a, cudaStream_t stream, bool* used) {
   using C = LG<J>;
   alignas(64) CUtensorMap mt, md, my;
@@ -423,7 +423,7 @@ cudaError_t launch_one(const GradArgs& a, cudaStream_t stream, bool* used) {
                   make_series_map(&my, a.y, a.B, a.N, a.stride, T);
   *used = ok;
   if (!ok) return cudaSuccess;
-  auto kern = k_grad_lockstep<J>;
+  auto kern = k_grad_lockstep<J, REGS>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::smem);
   if (e != cudaSuccess) return e;
   const long long grid = (a.B + kWarp - 1) / kWarp;
@@ -450,7 +450,11 @@ size_t grad_lockstep_scratch_doubles(long long B, int N, int Jc, int seg) {
 cudaError_t launch_grad_lockstep(const GradArgs& a, cudaStream_t stream, bool* used) {
   *used = false;
   if (!grad_lockstep_applies(a.Jr, a.Jc, a.Jg, a.stride) || (a.seg % T) != 0) return cudaSuccess;
-  return a.Jc == 1 ? launch_one<2>(a, stream, used) : launch_one<4>(a, stream, used);
+  if (a.Jc == 2) return launch_one<4, 255>(a, stream, used);
+  // J = 2: 144 registers keep 14 warps per SM resident, so that 2,048 warps (65,536 series) run as one wave
+  static const char* re = getenv("CEL_GRAD_REGS");   // A/B knob
+  if (re && atoi(re) == 168) return launch_one<2, 168>(a, stream, used);
+  return launch_one<2, 144>(a, stream, used);
 }
 
 }  // namespace cel
