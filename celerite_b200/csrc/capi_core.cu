@@ -122,7 +122,7 @@ static int batched_ll_impl(cel_solver* s, int64_t B, int N, int64_t stride, int 
   if (stride != 0 && stride < N) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "stride < N");
   const int P = 1 + 2 * Jr + 4 * Jc;
   if (coeff_stride != 0 && coeff_stride < P) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "coeff_stride < 1+2Jr+4Jc");
-  if (Jr + 2 * Jc > cel::kCoopMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "batched kernels support J <= 32");
+  if (Jr + 2 * Jc > cel::kWideMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "batched kernels support J <= 96");
   if (!coeffs || !t || !diag || !y) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null input");
   if (B == 0) return CEL_OK;
   CEL_CUDA_TRY(s, cudaSetDevice(s->device));

@@ -164,7 +164,7 @@ int cel_compute(cel_solver* s, double jitter, int Jr, const double* a_real, cons
   int rc = pack_coeffs(s, jitter, Jr, a_real, c_real, Jc, a_comp, b_comp, c_comp, d_comp, row);
   if (rc != CEL_OK) return rc;
   const int J = Jr + 2 * Jc + Jg;
-  if (J > cel::kCoopMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "J > 32 is not supported yet");
+  if (J > cel::kWideMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "J > 96 is not supported");
   CEL_CUDA_TRY(s, cudaSetDevice(s->device));
   cudaStream_t st = s->stream;
 
@@ -207,7 +207,7 @@ int cel_compute(cel_solver* s, double jitter, int Jr, const double* a_real, cons
   // Long series without general rows: factorise time segments side by side, each from a cold start
   // behind a warm-up halo (plan_segments); falls through to the serial sweep when the kernel
   // forgets too slowly for that, or when the check of the halos against their owners fails.
-  if (Jg == 0 && !A && N >= kSegmentedMinN) {
+  if (Jg == 0 && !A && N >= kSegmentedMinN && J <= cel::kCoopMaxJ) {
     std::vector<int> seg;
     plan_segments(J, Jr, c_real, Jc, c_comp, N, x, seg);
     if (!seg.empty()) {
@@ -305,7 +305,7 @@ int cel_dot_solve(cel_solver* s, int N, const double* b, double* out) {
   cudaStream_t st = s->stream;
   CEL_CUDA_TRY(s, s->out0.reserve(64));
   double* res = static_cast<double*>(s->pinned);
-  if (s->J >= 1 && N >= kChunkedMinN && s->n_off == 0) {
+  if (s->J >= 1 && s->J <= cel::kCoopMaxJ && N >= kChunkedMinN && s->n_off == 0) {
     // long series: the forward half of solve as a chunked scan (x / D), then sum (x/D)^2 D
     CEL_CUDA_TRY(s, s->scan_tmp.reserve(dbytes((size_t)N)));
     CEL_CUDA_TRY(s, s->scratch2.reserve(dbytes(cel::quad_scratch_doubles())));
@@ -335,7 +335,7 @@ int cel_solve(cel_solver* s, int N, int nrhs, const double* b, double* out) {
   if (rc != CEL_OK) return rc;
   if (nrhs == 0) return CEL_OK;
   cudaStream_t st = s->stream;
-  if (s->J >= 1 && N >= kChunkedMinN) {
+  if (s->J >= 1 && s->J <= cel::kCoopMaxJ && N >= kChunkedMinN) {
     // long series: chunked two-pass scans (scan.cu) instead of one serial sweep
     rc = cel_solve_device(s, nrhs, s->in0.d(), s->out1.d());
     if (rc != CEL_OK) return rc;
@@ -354,7 +354,7 @@ int cel_dot_L(cel_solver* s, int N, int nrhs, const double* z, double* out) {
   if (rc != CEL_OK) return rc;
   if (nrhs == 0) return CEL_OK;
   cudaStream_t st = s->stream;
-  if (s->J >= 1 && N >= kChunkedMinN) {
+  if (s->J >= 1 && s->J <= cel::kCoopMaxJ && N >= kChunkedMinN) {
     rc = cel_dot_L_device(s, nrhs, s->in0.d(), s->out1.d());
     if (rc != CEL_OK) return rc;
   } else {
@@ -377,7 +377,7 @@ int cel_dot(cel_solver* s, double jitter, int Jr, const double* a_real, const do
   int rc = pack_coeffs(s, jitter, Jr, a_real, c_real, Jc, a_comp, b_comp, c_comp, d_comp, row);
   if (rc != CEL_OK) return rc;
   const int J = Jr + 2 * Jc + Jg;
-  if (J > cel::kCoopMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "J > 32 is not supported yet");
+  if (J > cel::kWideMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "J > 96 is not supported");
   if (nrhs == 0) return CEL_OK;
   CEL_CUDA_TRY(s, cudaSetDevice(s->device));
   cudaStream_t st = s->stream;
@@ -406,7 +406,7 @@ int cel_dot(cel_solver* s, double jitter, int Jr, const double* a_real, const do
     a.N = N; a.Jr = Jr; a.Jc = Jc; a.Jg = Jg; a.nrhs = nrhs;
     a.coeffs = dc; a.A = A ? dA : nullptr; a.U = Jg > 0 ? dU : nullptr; a.V = Jg > 0 ? dV : nullptr;
     a.x = dx; a.z = s->scratch0.d(); a.out = s->scratch1.d();
-    if (N >= kChunkedMinN) {
+    if (N >= kChunkedMinN && J <= cel::kCoopMaxJ) {
       // long series: chunks side by side (one wave of groups), carries passed on in closed form
       int L = 1;
       while (L < J && L < 32) L <<= 1;
@@ -442,7 +442,7 @@ int cel_predict(cel_solver* s, int N, const double* y, int M, const double* xs, 
   int rc = sweep_prepare(s, N, 1, y, dummy);
   if (rc != CEL_OK) return rc;
   cudaStream_t st = s->stream;
-  if (s->J >= 1 && N >= kChunkedMinN) {
+  if (s->J >= 1 && s->J <= cel::kCoopMaxJ && N >= kChunkedMinN) {
     rc = cel_solve_device(s, 1, s->in0.d(), s->out1.d());
     if (rc != CEL_OK) return rc;
   } else {
@@ -457,7 +457,7 @@ int cel_predict(cel_solver* s, int N, const double* y, int M, const double* xs, 
   a.N = N; a.M = M; a.Jr = s->Jr; a.Jc = s->Jc;
   a.coeffs = s->coeffs.d(); a.t = s->t.d(); a.alpha = s->out1.d(); a.xs = dxs; a.out = dout;
   const int Jp = s->Jr + 2 * s->Jc;
-  if (Jp >= 1 && N >= kChunkedMinN) {
+  if (Jp >= 1 && Jp <= cel::kCoopMaxJ && N >= kChunkedMinN) {
     // long series: the merge sweeps by chunks of data points (one wave of groups)
     int L = 1;
     while (L < Jp && L < 32) L <<= 1;
@@ -489,7 +489,7 @@ int cel_grad_log_likelihood(cel_solver* s, double jitter, int Jr, const double* 
   int rc = pack_coeffs(s, jitter, Jr, a_real, c_real, Jc, a_comp, b_comp, c_comp, d_comp, row);
   if (rc != CEL_OK) return rc;
   const int J = Jr + 2 * Jc + Jg, P = (int)row.size();
-  if (J > cel::kCoopMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "J > 32 is not supported yet");
+  if (J > cel::kWideMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "J > 96 is not supported");
   CEL_CUDA_TRY(s, cudaSetDevice(s->device));
   cudaStream_t st = s->stream;
   double* res = static_cast<double*>(s->pinned);
@@ -532,7 +532,7 @@ int cel_grad_log_likelihood(cel_solver* s, double jitter, int Jr, const double* 
   // Long series without general rows: time spans side by side (grad.cu, SPAN), each behind a warm-up
   // halo and in front of a cool-down halo; neighbouring spans are compared at their common edge
   // and the series is redone serially if they disagree.
-  if (Jg == 0 && !A && N >= kSegmentedMinN) {
+  if (Jg == 0 && !A && N >= kSegmentedMinN && J <= cel::kCoopMaxJ) {
     std::vector<int> span;
     plan_grad_spans(J, Jr, c_real, Jc, c_comp, N, x, span);
     if (!span.empty()) {
@@ -612,7 +612,7 @@ int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t str
   if (stride != 0 && stride < N) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "stride < N");
   const int J = Jr + 2 * Jc, P = 1 + 2 * Jr + 4 * Jc;
   if (coeff_stride != 0 && coeff_stride < P) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "coeff_stride < 1+2Jr+4Jc");
-  if (J < 1 || J > cel::kCoopMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "batched gradient supports 1 <= J <= 32");
+  if (J < 1 || J > cel::kWideMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "batched gradient supports 1 <= J <= 96");
   if (!coeffs || !t || !diag || !y || !out_val || !out_grad) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null pointer");
   if (B == 0) return CEL_OK;
   CEL_CUDA_TRY(s, cudaSetDevice(s->device));
@@ -704,7 +704,7 @@ int cel_batched_grad_log_likelihood_ragged(cel_solver* s, int64_t B, int N, int6
   if (stride < N) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "stride < N (a ragged batch has one row per series)");
   const int J = Jr + 2 * Jc, P = 1 + 2 * Jr + 4 * Jc;
   if (coeff_stride != 0 && coeff_stride < P) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "coeff_stride < 1+2Jr+4Jc");
-  if (J < 1 || J > cel::kCoopMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "batched gradient supports 1 <= J <= 32");
+  if (J < 1 || J > cel::kCoopMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "the ragged batched gradient supports 1 <= J <= 32");
   if (!d_coeffs || !d_t || !d_diag || !d_y || !d_lengths || !d_val || !d_grad)
     CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null pointer");
   if (B == 0) return CEL_OK;
@@ -751,7 +751,7 @@ int cel_set_state(cel_solver* s, int computed, int N, int J, double log_det, con
                   const double* W, const double* D) {
   if (!s) return CEL_INVALID_ARGUMENT;
   if (N < 0 || J < 0) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "negative size");
-  if (J > cel::kCoopMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "J > 32 is not supported yet");
+  if (J > cel::kWideMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "J > 96 is not supported");
   s->computed = false;
   s->n_off = 0;
   s->scan_nchunks = 0;
@@ -788,7 +788,7 @@ int cel_batched_compute(cel_solver* s, int64_t B, int N, int64_t stride, int Jr,
   if (B < 0 || N < 1 || Jr < 0 || Jc < 0 || stride < 0 || coeff_stride < 0)
     CEL_FAIL(s, CEL_INVALID_ARGUMENT, "negative size");
   const int J = Jr + 2 * Jc;
-  if (J < 1 || J > cel::kCoopMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "batched compute supports 1 <= J <= 32");
+  if (J < 1 || J > cel::kWideMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "batched compute supports 1 <= J <= 96");
   if (!coeffs || !t || !diag || !phi || !u || !W || !D) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null pointer");
   if (B == 0) return CEL_OK;
   CEL_CUDA_TRY(s, cudaSetDevice(s->device));

@@ -493,6 +493,7 @@ cudaError_t launch_segment_finish(const BatchArgs& a, double* result, cudaStream
 }
 
 cudaError_t launch_loglik_coop(const BatchArgs& a, cudaStream_t stream) {
+  if (a.Jr + 2 * a.Jc + a.Jg > kCoopMaxJ) return launch_wide_factor(a, stream);   // widej.cu
   return a.phi ? dispatch<true>(a, stream) : dispatch<false>(a, stream);
 }
 

@@ -669,6 +669,7 @@ int grad_tuned_segment(long long B, int N, int J, bool lockstep) {
 }
 
 size_t grad_scratch_doubles(long long B, int N, int J, int seg) {
+  if (J > kCoopMaxJ) return wide_grad_scratch_doubles(B, N, J);
   const int JP = grad_jp(J);
   const int L = pow2ceil(JP), G = kWarp / L;
   const long long groups = ((B + G - 1) / G) * G;       // idle groups own a slot too
@@ -714,7 +715,8 @@ cudaError_t launch_grad_span_finish(const GradArgs& a, double* result, cudaStrea
 
 cudaError_t launch_grad_coop(const GradArgs& a, cudaStream_t stream) {
   const int J = a.Jr + 2 * a.Jc + a.Jg;
-  if (J < 1 || J > kCoopMaxJ || a.seg < 1) return cudaErrorInvalidValue;
+  if (J > kCoopMaxJ) return launch_wide_grad(a, stream);   // widej.cu: full tape, no checkpoints
+  if (J < 1 || a.seg < 1) return cudaErrorInvalidValue;
   switch (grad_jp(J)) {
     case 2: return launch_one<2>(a, stream);
     case 4: return launch_one<4>(a, stream);

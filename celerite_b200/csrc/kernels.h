@@ -88,8 +88,10 @@ cudaError_t launch_segment_finish(const BatchArgs& a, double* result, cudaStream
 cudaError_t launch_compute_lockstep(const BatchArgs& a, cudaStream_t stream, bool* used);
 
 // Cooperative sweep: L = pow2ceil(J) lanes per series, one row of S per lane.  Fused
-// log-likelihood when a.phi == NULL, materialising compute otherwise.  J <= kCoopMaxJ.
+// log-likelihood when a.phi == NULL, materialising compute otherwise.  J <= kCoopMaxJ; wider
+// kernels go to the wide family (widej.cu) from inside the same launchers.
 constexpr int kCoopMaxJ = 32;
+constexpr int kWideMaxJ = 96;    // widest kernel the library takes: state and adjoint in 220 KB of shared memory
 cudaError_t launch_loglik_coop(const BatchArgs& a, cudaStream_t stream);
 
 // Fused log-likelihood + reverse-mode gradient (celerite/solver.cpp:347-463), DEVICE pointers.
@@ -171,6 +173,16 @@ cudaError_t launch_dot(const DotArgs& a, cudaStream_t stream);
 // carries-only pass, a short scan over the chunks, then the full pass from the true carries.
 // carry: 4 * nchunks * nrhs * J doubles of scratch.
 cudaError_t launch_dot_chunked(const DotArgs& a, int chunk_len, int nchunks, double* carry, cudaStream_t stream);
+
+// Wide kernels, 32 < J <= kWideMaxJ (widej.cu): one warp per series / right-hand side, state in shared
+// memory.  sweep mode: 0 solve, 1 dot_solve, 2 dot_L.  The gradient tapes N (J^2 + 2J + 2) doubles per series.
+struct PredictArgs;
+cudaError_t launch_wide_factor(const BatchArgs& a, cudaStream_t stream);
+cudaError_t launch_wide_sweep(const SweepArgs& a, int mode, cudaStream_t stream);
+cudaError_t launch_wide_dot(const DotArgs& a, cudaStream_t stream);
+cudaError_t launch_wide_predict(const PredictArgs& a, cudaStream_t stream);
+size_t wide_grad_scratch_doubles(long long B, int N, int J);
+cudaError_t launch_wide_grad(const GradArgs& a, cudaStream_t stream);
 
 // elementwise helper for the J == 0 paths: mode 0 out=in/D, 1 out=scalar*in, 2 out=sqrt(D)*in
 cudaError_t launch_scale(int n, int N, const double* in, const double* D, double scalar, int mode, double* out,

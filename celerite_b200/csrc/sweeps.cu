@@ -363,7 +363,7 @@ __global__ void k_scale(int n, int N, const double* in, const double* D, double 
   } while (0)
 
 cudaError_t launch_solve(const SweepArgs& a, cudaStream_t stream) {
-  if (a.J > kCoopMaxJ) return cudaErrorInvalidValue;
+  if (a.J > kCoopMaxJ) return launch_wide_sweep(a, 0, stream);   // widej.cu
 #define CALL(LL)                                                                       \
   {                                                                                    \
     const int G = kWarp / LL, grid = (a.nrhs + G - 1) / G;                             \
@@ -376,7 +376,7 @@ cudaError_t launch_solve(const SweepArgs& a, cudaStream_t stream) {
 }
 
 cudaError_t launch_dot_solve(const SweepArgs& a, cudaStream_t stream) {
-  if (a.J > kCoopMaxJ) return cudaErrorInvalidValue;
+  if (a.J > kCoopMaxJ) return launch_wide_sweep(a, 1, stream);
 #define CALL(LL)                                                                       \
   {                                                                                    \
     const int G = kWarp / LL, grid = (a.nrhs + G - 1) / G;                             \
@@ -388,7 +388,7 @@ cudaError_t launch_dot_solve(const SweepArgs& a, cudaStream_t stream) {
 }
 
 cudaError_t launch_dot_L(const SweepArgs& a, cudaStream_t stream) {
-  if (a.J > kCoopMaxJ) return cudaErrorInvalidValue;
+  if (a.J > kCoopMaxJ) return launch_wide_sweep(a, 2, stream);
 #define CALL(LL)                                                                       \
   {                                                                                    \
     const int G = kWarp / LL, grid = (a.nrhs + G - 1) / G;                             \
@@ -401,7 +401,7 @@ cudaError_t launch_dot_L(const SweepArgs& a, cudaStream_t stream) {
 
 cudaError_t launch_dot(const DotArgs& a, cudaStream_t stream) {
   const int J = a.Jr + 2 * a.Jc + a.Jg;
-  if (J > kCoopMaxJ) return cudaErrorInvalidValue;
+  if (J > kCoopMaxJ) return launch_wide_dot(a, stream);
 #define CALL(LL)                                                                       \
   {                                                                                    \
     const int G = kWarp / LL, grid = (a.nrhs + G - 1) / G;                             \
@@ -759,7 +759,7 @@ namespace {
 
 cudaError_t launch_predict(const PredictArgs& a, cudaStream_t stream) {
   const int Jp = a.Jr + 2 * a.Jc;
-  if (Jp > kCoopMaxJ) return cudaErrorInvalidValue;
+  if (Jp > kCoopMaxJ) return launch_wide_predict(a, stream);
 #define CALL(LL) { k_predict<LL><<<1, LL < 32 ? 32 : LL, 0, stream>>>(a); }
   if (Jp <= 1) { CALL(1); } else if (Jp <= 2) { CALL(2); } else if (Jp <= 4) { CALL(4); }
   else if (Jp <= 8) { CALL(8); } else if (Jp <= 16) { CALL(16); } else { CALL(32); }

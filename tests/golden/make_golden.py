@@ -75,6 +75,24 @@ def cases():
     # not positive definite: negative amplitude drives D_n < 0 (cholesky.h:176)
     x, d, y = series(64)
     out["npd_j1"] = (Problem(0.0, [-1.0], [0.5], [], [], [], [], x, 1e-3 * np.ones(64)), y)
+    # wider than one row per lane (J > 32: cholesky.h:181-204 takes its dynamic branch): 8 real + 16 complex
+    # (J=40), the same with three general rows on top of 2 real + 16 complex (J=37), and 32 SHO terms (J=64).
+    # Appended last so that the random streams of the cases above stay what they were.
+    x, d, y = series(160, 16.0)
+    out["wider_j40"] = (Problem(0.01, rng.uniform(0.5, 1.5, 8), rng.uniform(0.1, 2, 8),
+                                rng.uniform(0.5, 1.5, 16), rng.uniform(0, 0.05, 16),
+                                rng.uniform(0.2, 2, 16), rng.uniform(0.5, 8, 16), x, d), y)
+    x, d, y = series(96)
+    Jg = 3
+    U = 0.1 * rng.standard_normal((Jg, 96))
+    V = 0.1 * rng.standard_normal((Jg, 96))
+    A = 1.0 + np.sum(U * U + V * V, axis=0)
+    out["wider_general_j37"] = (Problem(0.02, rng.uniform(0.5, 1.5, 2), rng.uniform(0.1, 2, 2),
+                                        rng.uniform(0.5, 1.5, 16), rng.uniform(0, 0.05, 16),
+                                        rng.uniform(0.2, 2, 16), rng.uniform(0.5, 8, 16), x, d, A=A, U=U, V=V), y)
+    b = synth.make_batch(1, 64, 0, 32, seed=10)
+    j, ar, cr, ac, bc, cc, dc = synth.split_row(b["coeffs"][0], 0, 32)
+    out["wider_sho_j64"] = (Problem(j, ar, cr, ac, bc, cc, dc, b["t"][0], b["diag"][0]), b["y"][0])
     return out
 
 

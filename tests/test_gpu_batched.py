@@ -53,6 +53,8 @@ def _check(bs, B, N, Jr, Jc, seed, torch_path=False):
     (3, 800, 0, 8),       # J=16
     (3, 640, 4, 11),      # J=26 (the widest kernel of tests/test_celerite.py)
     (2, 700, 0, 16),      # J=32
+    (3, 300, 4, 18),      # J=40: wider than one row per lane, the wide kernels (widej.cu)
+    (2, 200, 0, 40),      # J=80
 ])
 def test_batched_loglik_host(bs, B, N, Jr, Jc):
     _check(bs, B, N, Jr, Jc, seed=B + N)
@@ -163,7 +165,7 @@ def test_repeatable_at_full_size(bs):
 
 
 @pytest.mark.parametrize("B,N,Jr,Jc", [(100, 500, 0, 1), (70, 403, 0, 2), (40, 300, 0, 3), (33, 200, 1, 1),
-                                       (5, 333, 0, 1), (3, 150, 0, 8)])
+                                       (5, 333, 0, 1), (3, 150, 0, 8), (3, 120, 3, 17)])
 def test_batched_compute_materialises_reference_factor(bs, B, N, Jr, Jc):
     """cel_batched_compute: phi,u,W,D of every series vs the oracle's factor (the TMA-store
     lockstep kernel for all-complex even J <= 6 with aligned rows, the cooperative kernel else)."""
@@ -188,6 +190,26 @@ def test_batched_compute_materialises_reference_factor(bs, B, N, Jr, Jc):
         assert rel_sum(float(logdet[i]), f.log_det, N) < RTOL_SCALAR
         if hasattr(chk, "release"):
             chk.release(f)
+
+
+def test_wide_kernels_batched_gradient_and_limit(bs):
+    """J = 37 (3 real + 17 complex): value and all 1 + 2*3 + 4*17 derivatives of a small batch against the
+    reference's forward-mode AD; and the width the library refuses (J > 96)."""
+    from celerite_b200 import synth, _capi
+    from tests.util import RTOL_GRAD, rel_grad
+    B, N, Jr, Jc = 3, 150, 3, 17
+    b = synth.make_batch(B, N, Jr, Jc, seed=91)
+    P = b["coeffs"].shape[1]
+    val, grad, status = bs.grad_log_likelihood(b["coeffs"], b["t"], b["diag"], b["y"], Jr, Jc)
+    gv, gg, gs = oracle.best().batched_grad(B, N, N, Jr, Jc, b["coeffs"], P, b["t"], b["diag"], b["y"], nthreads=4)
+    assert np.all(status == 0) and np.all(gs == 0)
+    const = 0.5 * np.pi * np.log(N)                      # solver.cpp:415, carried by the reference's value only
+    assert np.max(np.abs((val - const) - gv) / np.abs(gv)) < RTOL_SCALAR
+    for i in range(B):
+        assert rel_grad(grad[i], gg[i]) < RTOL_GRAD
+    wide = synth.make_batch(1, 16, 0, 49, seed=1)        # J = 98
+    with pytest.raises(_capi.CeleriteB200Error):
+        bs.log_likelihood(wide["coeffs"], wide["t"], wide["diag"], wide["y"], 0, 49)
 
 
 def test_jitter_only_batch(bs):
@@ -244,7 +266,7 @@ def test_argument_errors(bs):
     p = C.c_void_p(a.ctypes.data)
     assert lib.cel_batched_log_likelihood(bs._h, 1, 0, 0, 0, 1, p, 5, p, p, p, p, p, p, p, 1) == _capi.INVALID_ARGUMENT
     assert lib.cel_batched_log_likelihood(bs._h, 2, 8, 4, 0, 1, p, 5, p, p, p, p, p, p, p, 1) == _capi.DIMENSION_MISMATCH
-    assert lib.cel_batched_log_likelihood(bs._h, 2, 8, 8, 0, 17, p, 69, p, p, p, p, p, p, p, 1) == _capi.UNSUPPORTED
+    assert lib.cel_batched_log_likelihood(bs._h, 2, 8, 8, 0, 49, p, 197, p, p, p, p, p, p, p, 1) == _capi.UNSUPPORTED   # J = 98 > 96
     assert lib.cel_batched_log_likelihood(bs._h, 0, 8, 8, 0, 1, p, 5, p, p, p, p, p, p, p, 1) == _capi.OK
 
 
