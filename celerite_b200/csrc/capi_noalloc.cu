@@ -21,7 +21,7 @@
 namespace {
 
 // 32 MiB of scratch for the checkpoints and the segment tape of ONE series
-// (see grad.cu: (ceil(N/C) + C) * (JP^2 + 2 JP + 2) doubles with C ~ sqrt(N)).
+// (see grad.cu: (ceil(N/C) + C) * (JP (JP+1)/2 + 2 JP + 2) doubles with C ~ sqrt(N)).
 constexpr size_t kStaticScratchDoubles = CEL_STATIC_SCRATCH_BYTES / sizeof(double);
 static __device__ __align__(256) double g_static_scratch[kStaticScratchDoubles];
 

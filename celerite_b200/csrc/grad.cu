@@ -18,7 +18,7 @@
 // (8.7 KB at J = 32), so the sweep is CHECKPOINTED: the forward pass stores its state every C
 // steps; the reverse pass re-runs one segment forward from its checkpoint, taping the C states
 // into a per-series scratch area that stays L2-resident, then consumes the tape backwards.
-// Scratch per series: (ceil(N/C) + C) * (JP^2 + 2 JP + 2) doubles, C ~ sqrt(N).
+// Scratch per series: (ceil(N/C) + C) * (JP (JP+1)/2 + 2 JP + 2) doubles, C ~ sqrt(N).
 //
 // Mapping: as in coop.cu — L = pow2ceil(J) lanes per series, lane k owns row k of S, Pbar, P.
 // Tape blocks are stored transposed ([j][k], k fastest) so that each lane's row is read and
@@ -41,7 +41,12 @@ struct GradCfg {
   static constexpr int G = kWarp / L;
   static constexpr int T = 16;
   static constexpr int JJ = JP * JP;
-  static constexpr int E = JJ + 2 * JP + 2;          // one tape / checkpoint record, in doubles
+  // The J x J blocks of the records (P_n on the tape, S in a checkpoint) are symmetric: only the upper
+  // triangle is kept, packed by columns (entry (k, j), k <= j, at j(j+1)/2 + k; lanes 0..j write column j
+  // as one coalesced row).  At J = 32 the tape was 8.7 KB per step and bound the kernel (1.7 TB of DRAM
+  // traffic per 1,024 x 1e5 batch, profiles/r02_grad_coop_j32.txt); now 4.6 KB.
+  static constexpr int BLK = (JP * (JP + 1) / 2 + 1) & ~1;   // even: records stay 16-byte aligned
+  static constexpr int E = BLK + 2 * JP + 2;         // one tape / checkpoint record, in doubles
   static constexpr int kIn = 3 * T + 2;
   static constexpr int kGen = 4 * T * JP;          // phi, u, v, phi o u
   static constexpr int kX = 4 * JP;                  // [2][2*JP] exchange rows
@@ -68,7 +73,7 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 template <int JP, bool SPAN = false>
 __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   using C = GradCfg<JP>;
-  constexpr int L = C::L, G = C::G, T = C::T, JJ = C::JJ, E = C::E;
+  constexpr int L = C::L, G = C::G, T = C::T, JJ = C::JJ, E = C::E, BLK = C::BLK;
   constexpr int kGenIlp = 4;   // generator items per lane evaluated together (8 spills here: 23.8 -> 25.4 ms at J = 8)
   extern __shared__ __align__(16) double smem[];
   const int lane = threadIdx.x, g = lane / L, k = lane % L;
@@ -267,22 +272,26 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
     for (int j = 0; j < JP; ++j) S[j] = 0.0;
     dw_own = 0.0; r_prev = 0.0; f_own = 0.0; s_prev = 0.0; Dprev = 0.0; xprev = 0.0;
   };
+  const int tk = kk * (kk + 1) / 2;
+  // entry (kk, j) of a packed symmetric block
+  auto pidx = [&](int j) { return j >= kk ? j * (j + 1) / 2 + kk : tk + j; };
   auto store_state = [&](double* rec) {   // checkpoint: S in place of P
     if (row_ok) {
 #pragma unroll
-      for (int j = 0; j < JP; ++j) rec[j * JP + kk] = S[j];
-      rec[JJ + kk] = dw_own * r_prev;
-      rec[JJ + JP + kk] = f_own;
+      for (int j = 0; j < JP; ++j)
+        if (j >= kk) rec[j * (j + 1) / 2 + kk] = S[j];
+      rec[BLK + kk] = dw_own * r_prev;
+      rec[BLK + JP + kk] = f_own;
     }
-    if (k == 0) { rec[JJ + 2 * JP] = Dprev; rec[JJ + 2 * JP + 1] = xprev; }
+    if (k == 0) { rec[BLK + 2 * JP] = Dprev; rec[BLK + 2 * JP + 1] = xprev; }
   };
   auto load_state = [&](const double* rec) {
 #pragma unroll
-    for (int j = 0; j < JP; ++j) S[j] = row_ok ? rec[j * JP + kk] : 0.0;
-    const double Wk = row_ok ? rec[JJ + kk] : 0.0;
-    f_own = row_ok ? rec[JJ + JP + kk] : 0.0;
-    Dprev = rec[JJ + 2 * JP];
-    xprev = rec[JJ + 2 * JP + 1];
+    for (int j = 0; j < JP; ++j) S[j] = row_ok ? rec[pidx(j)] : 0.0;
+    const double Wk = row_ok ? rec[BLK + kk] : 0.0;
+    f_own = row_ok ? rec[BLK + JP + kk] : 0.0;
+    Dprev = rec[BLK + 2 * JP];
+    xprev = rec[BLK + 2 * JP + 1];
     r_prev = (Dprev != 0.0) ? 1.0 / Dprev : 0.0;      // the state before step 0 has D = 0
     dw_own = Wk * Dprev;
     s_prev = xprev * r_prev;
@@ -315,7 +324,10 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
         if ((j & 2) == 0) { acc0 = fma(s0, u2.x, acc0); acc1 = fma(s1, u2.y, acc1); }
         else { acc2 = fma(s0, u2.x, acc2); acc3 = fma(s1, u2.y, acc3); }
         const double P0 = fma(dwr, x2.x, s0), P1 = fma(dwr, x2.y, s1);
-        if (TAPE && row_ok) { trec[j * JP + kk] = P0; trec[(j + 1) * JP + kk] = P1; }
+        if (TAPE && row_ok) {
+          if (j >= kk) trec[j * (j + 1) / 2 + kk] = P0;
+          if (j + 1 >= kk) trec[(j + 1) * (j + 2) / 2 + kk] = P1;
+        }
         S[j] = (phk * p2.x) * P0;
         S[j + 1] = (phk * p2.y) * P1;
       }
@@ -331,8 +343,8 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
       if (row_ok) x_s[(par ^ 1) * 2 * JP + kk] = dw;
       const double r = fast_rcp_nocheck(Dn);
       if (TAPE) {
-        if (row_ok) { trec[JJ + kk] = dw * r; trec[JJ + JP + kk] = f_own; }
-        if (k == 0) { trec[JJ + 2 * JP] = Dn; trec[JJ + 2 * JP + 1] = x; }
+        if (row_ok) { trec[BLK + kk] = dw * r; trec[BLK + JP + kk] = f_own; }
+        if (k == 0) { trec[BLK + 2 * JP] = Dn; trec[BLK + 2 * JP + 1] = x; }
       }
       s_prev = r * x;
       if (ACCUM) {
@@ -412,17 +424,17 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
       if (n >= seg0) {
         const double* src = tape + (size_t)(n - seg0) * E;
         double* dst = p_s + (n & (C::RD - 1)) * JJ;
-        for (int e = 2 * k; e < JJ; e += 2 * L) cp_async16(dst + e, src + e);
+        for (int e = 2 * k; e < BLK; e += 2 * L) cp_async16(dst + e, src + e);
       }
       cp_async_commit();
     };
     // record of step n: {W_n[k], f_n[k], D_n, x_n}; n = seg0-1 is the checkpoint
     auto load_rec = [&](int n, double& Wv, double& fv, double& Dv, double& xv) {
       const double* rec = n >= seg0 ? tape + (size_t)(n - seg0) * E : crec;
-      Wv = __ldcg(rec + JJ + kk);
-      fv = __ldcg(rec + JJ + JP + kk);
-      Dv = __ldcg(rec + JJ + 2 * JP);
-      xv = __ldcg(rec + JJ + 2 * JP + 1);
+      Wv = __ldcg(rec + BLK + kk);
+      fv = __ldcg(rec + BLK + JP + kk);
+      Dv = __ldcg(rec + BLK + 2 * JP);
+      xv = __ldcg(rec + BLK + 2 * JP + 1);
     };
     for (int q = 1; q < C::RD; ++q) stage_block(seg1 - q);
     double Wn, fn, Dn, xn, Wm, fm, Dm, xm, Wq = 0.0, fq = 0.0, Dq = 0.0, xq = 0.0;
@@ -478,7 +490,7 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
         double aSw = 0.0, aSu = 0.0, aphi0 = 0.0, aphi1 = 0.0, aP0 = 0.0, aP1 = 0.0, aP2 = 0.0, aP3 = 0.0;
 #pragma unroll
         for (int j = 0; j < JP; ++j) {
-          const double p = pb[j * JP + kk];
+          const double p = pb[pidx(j)];
           const double pj = ph[j], uj = uu[j], wj = xch[j], wmj = xch[JP + j];
           const double pp = phk * pj;
           const double sv = pp * p;
@@ -656,7 +668,7 @@ int grad_tuned_segment(long long B, int N, int J, bool lockstep) {
     step = 8;
   } else {
     const int JP = grad_jp(J);
-    rec_bytes = ckpt_bytes = 8.0 * (JP * JP + 2 * JP + 2);
+    rec_bytes = ckpt_bytes = 8.0 * (((JP * (JP + 1) / 2 + 1) & ~1) + 2 * JP + 2);
     resident = static_cast<long long>(sm_count()) * 8 * (kWarp / pow2ceil(JP));
     step = 16;
   }
@@ -673,7 +685,7 @@ size_t grad_scratch_doubles(long long B, int N, int J, int seg) {
   const int JP = grad_jp(J);
   const int L = pow2ceil(JP), G = kWarp / L;
   const long long groups = ((B + G - 1) / G) * G;       // idle groups own a slot too
-  const size_t E = (size_t)JP * JP + 2 * JP + 2;
+  const size_t E = (((size_t)JP * (JP + 1) / 2 + 1) & ~(size_t)1) + 2 * JP + 2;
   const size_t nseg = (size_t)(N + seg - 1) / seg;
   return (size_t)groups * (nseg + seg) * E;
 }

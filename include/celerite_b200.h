@@ -271,9 +271,9 @@ int cel_log_likelihood_mgpu(cel_solver* s, const double* d_y, double* out3);    
  * The checkpoint/tape scratch of the reverse sweep lives in a fixed array inside the library
  * image: CEL_STATIC_SCRATCH_BYTES (32 MiB) on every GPU that loads the library, until exit.
  *   - Problems needing more are refused with CEL_EXCEEDS_STATIC_SCRATCH and nothing is launched.
- *     Need = G*(ceil(N/C) + C)*(JP^2 + 2*JP + 2)*8 bytes with C = 16*ceil(sqrt(N)/16), JP = J
- *     rounded up to {2,4,6,8,12,16,24,32}, G = 32/pow2ceil(JP): e.g. J = 8 fits up to N ~ 3e7,
- *     J = 32 up to N ~ 3e6.
+ *     Need = G*(ceil(N/C) + C)*(JP*(JP+1)/2 + 2*JP + 2)*8 bytes with C = 16*ceil(sqrt(N)/16), JP = J
+ *     rounded up to {2,4,6,8,12,16,24,32}, G = 32/pow2ceil(JP): e.g. J = 8 fits up to N ~ 9e7,
+ *     J = 32 up to N ~ 1.2e7.
  *   - All calls on a GPU share the one array: two calls whose kernels overlap on the device
  *     (different streams, different host threads) corrupt each other.  Serialise them.
  *   - Nothing has to be cleared between calls: every word is written before it is read.

@@ -82,12 +82,12 @@ def test_static_scratch_refuses_what_does_not_fit():
     lib = _capi.lib()
     dev = torch.device("cuda:0")
     torch.cuda.set_device(dev)
-    # J = 32 at N = 1e7 needs ~53 MiB of checkpoints + tape: more than the 32 MiB array.  The call
+    # J = 32 at N = 3e7 needs ~52 MiB of checkpoints + tape: more than the 32 MiB array.  The call
     # must say so before touching any of its arguments, so small dummy buffers are enough.
     dummy = torch.zeros(128, dtype=torch.float64, device=dev)
     st = torch.zeros(1, dtype=torch.int32, device=dev)
     p = lambda a: C.c_void_p(a.data_ptr())  # noqa: E731
-    rc = lib.cel_grad_log_likelihood_static_scratch(10_000_000, 0, 16, p(dummy), p(dummy), p(dummy), p(dummy),
+    rc = lib.cel_grad_log_likelihood_static_scratch(30_000_000, 0, 16, p(dummy), p(dummy), p(dummy), p(dummy),
                                                     p(dummy), p(dummy), p(st), None)
     assert rc == _capi.EXCEEDS_STATIC_SCRATCH
     rc = lib.cel_grad_log_likelihood_static_scratch(100, 0, 17, p(dummy), p(dummy), p(dummy), p(dummy),
