@@ -656,7 +656,15 @@ int grad_default_segment(int N) {
 // Measured (profiles/README.md): B = 1024, N = 1e5, J = 8: 146 ms at sqrt(N), 120 ms at 64.
 int grad_tuned_segment(long long B, int N, int J, bool lockstep) {
   const int seg_sqrt = grad_default_segment(N);
-  constexpr double kL2Budget = 48e6, kMaxScratch = 8e9;
+  constexpr double kL2Budget = 48e6;
+  // checkpoints may take up to 40 % of the free device memory (B200: 180 GB; J = 32, B = 1,024, N = 1e5
+  // wants 30 GB of them at segment 16, which runs in 500 ms against 545 ms at segment 64), at least 8 GB
+  double kMaxScratch = 8e9;
+  {
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && 0.4 * (double)free_b > kMaxScratch) kMaxScratch = 0.4 * (double)free_b;
+    else cudaGetLastError();
+  }
   double rec_bytes, ckpt_bytes;
   long long resident;
   int step;
