@@ -65,7 +65,8 @@ int cel_destroy(cel_solver* s) {
                          &s->maps[0], &s->maps[1], &s->maps[2], &s->pmaps[0], &s->pmaps[1], &s->pmaps[2],
                          &s->smaps[0], &s->smaps[1], &s->smaps[2], &s->tmaps[0], &s->tmaps[1], &s->tmaps[2],
                          &s->scan_vecs, &s->scan_h, &s->scan_cs, &s->scan_sg, &s->scan_total, &s->scan_tmp,
-                         &s->mg_summary, &s->mg_gathered, &s->mg_carry, &s->mg_scalars};
+                         &s->mg_summary, &s->mg_gathered, &s->mg_carry, &s->mg_scalars,
+                         &s->resp[0], &s->resp[1], &s->resp[2], &s->scan_x0};
   cel_comm_destroy(s);
   for (auto* b : bufs) b->release();
   for (int i = 0; i < 2; ++i) {

@@ -2,6 +2,7 @@
 // device-resident data, and their multi-GPU "span" form.
 #include <dlfcn.h>
 #include <math.h>
+#include <stdlib.h>
 #include <nccl.h>      // types only: the library is loaded at run time (see nccl_api)
 
 #include <vector>
@@ -54,11 +55,43 @@ int ensure_maps(cel_solver* s, int Nloc, int mode) {
   a.nrhs = 0; a.nbasis = nb;
   a.in = nullptr; a.out = nullptr; a.init = nullptr;
   a.carry = s->maps[mode].d();
+  // per-step responses for the elementwise pass 2 (launch_chunk_correct): N*J doubles per direction, kept
+  // only while they are a modest share of the free memory (the two-pass form needs none)
+  s->resp_valid[mode] = false;
+  {
+    static const bool off = getenv("CEL_NO_RESPONSES") != nullptr;   // A/B knob: recurrence in pass 2
+    size_t free_b = 0, total_b = 0;
+    const size_t need = dbytes((size_t)Nloc * J);
+    if (!off && cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && (need <= s->resp[mode].cap || 8 * need <= free_b) &&
+        s->resp[mode].reserve(need) == cudaSuccess) {
+      a.emit = s->resp[mode].d();
+      s->resp_valid[mode] = true;
+    } else {
+      cudaGetLastError();
+    }
+  }
   CEL_CUDA_TRY(s, cel::launch_chunk_sweep(a, s->stream));
   CEL_CUDA_TRY(s, cel::launch_middle_maps(J, nb, mode == 1, mode == 2, K, s->maps[mode].d(), s->pmaps[mode].d(),
                                           s->smaps[mode].d(), s->tmaps[mode].d(), s->stream));
   s->launches += 3;
   s->maps_valid[mode] = true;
+  return CEL_OK;
+}
+
+// pass 2: every chunk from its true carry  h_i + P_i g_s  -- as an elementwise correction of pass 1's
+// output x0 when the responses of this direction are cached, as a second recurrence otherwise
+int scan_pass2(cel_solver* s, int mode, int nrhs, const double* d_in, const double* x0, double* d_out, int per_super) {
+  cel::ScanArgs a = base_args(s, s->N - s->n_off, mode);
+  a.nrhs = nrhs; a.nbasis = 0; a.out = d_out; a.init = s->scan_h.d(); a.carry = nullptr;
+  a.pmap = s->pmaps[mode].d(); a.sg = s->scan_sg.d(); a.per_super = per_super; a.walk_reverse = (mode == 2);
+  if (s->resp_valid[mode] && x0) {
+    a.in = x0;
+    CEL_CUDA_TRY(s, cel::launch_chunk_correct(a, s->resp[mode].d(), s->stream));
+  } else {
+    a.in = d_in;
+    CEL_CUDA_TRY(s, cel::launch_chunk_sweep(a, s->stream));
+  }
+  s->launches += 1;
   return CEL_OK;
 }
 
@@ -81,10 +114,22 @@ int scan_sweep(cel_solver* s, int mode, int nrhs, const double* d_in, const doub
   CEL_CUDA_TRY(s, s->scan_sg.reserve(dbytes((size_t)nsuper * nrhs * J)));
   cudaStream_t st = s->stream;
   const int diag = (mode == 1), reverse = (mode == 2);
+  // With the per-step responses cached, pass 1 also writes its output (zero incoming carries) and pass 2
+  // is an elementwise correction of it; a summary call parks that output in the handle.
+  const bool corr = s->resp_valid[mode];
+  double* x0 = nullptr;
+  if (corr) {
+    if (d_total || reuse_vecs) {
+      CEL_CUDA_TRY(s, s->scan_x0.reserve(dbytes((size_t)Nloc * nrhs)));
+      x0 = s->scan_x0.d();
+    } else {
+      x0 = d_out;
+    }
+  }
   if (!reuse_vecs) {
     // pass 1: offsets c of every chunk (zero incoming carry)
     cel::ScanArgs a = base_args(s, Nloc, mode);
-    a.nrhs = nrhs; a.nbasis = 0; a.in = d_in; a.out = nullptr; a.init = nullptr;
+    a.nrhs = nrhs; a.nbasis = 0; a.in = d_in; a.out = x0; a.init = nullptr;
     a.carry = s->scan_vecs.d();
     CEL_CUDA_TRY(s, cel::launch_chunk_sweep(a, st));
     s->launches += 1;
@@ -96,13 +141,7 @@ int scan_sweep(cel_solver* s, int mode, int nrhs, const double* d_in, const doub
                                      st));
   s->launches += reuse_vecs ? 1 : 2;
   if (d_total) return CEL_OK;
-  // pass 2: every chunk from its true carry  h_i + P_i g_s
-  cel::ScanArgs a = base_args(s, Nloc, mode);
-  a.nrhs = nrhs; a.nbasis = 0; a.in = d_in; a.out = d_out; a.init = s->scan_h.d(); a.carry = nullptr;
-  a.pmap = s->pmaps[mode].d(); a.sg = s->scan_sg.d(); a.per_super = per_super; a.walk_reverse = reverse;
-  CEL_CUDA_TRY(s, cel::launch_chunk_sweep(a, st));
-  s->launches += 1;
-  return CEL_OK;
+  return scan_pass2(s, mode, nrhs, d_in, x0, d_out, per_super);
 }
 
 int check_ready(cel_solver* s, int nrhs) {
@@ -200,12 +239,7 @@ int mgpu_sweep(cel_solver* s, int op, int nrhs, const double* d_in, double* d_ou
     return scan_sweep(s, op, nrhs, d_in, s->mg_carry.d(), d_out, nullptr, true);
   }
   s->launches += 1;
-  cel::ScanArgs a = base_args(s, s->N - s->n_off, op);
-  a.nrhs = nrhs; a.nbasis = 0; a.in = d_in; a.out = d_out; a.init = s->scan_h.d(); a.carry = nullptr;
-  a.pmap = s->pmaps[op].d(); a.sg = s->scan_sg.d(); a.per_super = per_super; a.walk_reverse = (op == 2);
-  CEL_CUDA_TRY(s, cel::launch_chunk_sweep(a, s->stream));
-  s->launches += 1;
-  return CEL_OK;
+  return scan_pass2(s, op, nrhs, d_in, s->resp_valid[op] ? s->scan_x0.d() : nullptr, d_out, per_super);
 }
 
 int mgpu_ready(cel_solver* s, int nrhs) {

@@ -217,8 +217,17 @@ struct ScanArgs {
   const double* sg;     // [nsuper][ncols][J]
   int per_super;        // chunks per super-chunk, counted in walk order
   int walk_reverse;     // the walk runs from the last chunk to the first (backward sweep)
+  // map-building sweeps only (nrhs == 0): also write, per step n and row c, the response of the sweep's
+  // output at step n to a unit incoming carry in row c of the step's chunk -- [N][J] doubles.  With
+  // these, pass 2 of a sweep is an elementwise correction (launch_chunk_correct) instead of a second
+  // recurrence over the factor.
+  double* emit;
 };
 cudaError_t launch_chunk_sweep(const ScanArgs& a, cudaStream_t stream);
+// out[n] = x0[n] + sum_c resp[n][c] * carry_chunk(n)[c] for every right-hand side: pass 2 of a sweep when the
+// responses are cached.  a.in = x0 (pass-1 output, zero incoming carries), a.out (may alias a.in), a.init /
+// a.pmap / a.sg / a.per_super / a.walk_reverse / a.diag_basis as for pass 2 of launch_chunk_sweep.
+cudaError_t launch_chunk_correct(const ScanArgs& a, const double* resp, cudaStream_t stream);
 cudaError_t launch_middle_maps(int J, int nbasis, int diag, int reverse, int nunits, const double* maps,
                                double* pmaps, double* smaps, double* tmap, cudaStream_t stream);
 cudaError_t launch_middle(int J, int nrhs, int nbasis, int diag, int reverse, int nunits, const double* maps,

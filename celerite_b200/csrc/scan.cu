@@ -144,12 +144,15 @@ __global__ void __launch_bounds__(kWarp) k_chunk_forward(ScanArgs a) {
   };
 
   double wprev = 0.0, sprev = 0.0;
+  double* emit_row = (MODE == 1 && a.emit && !is_rhs && row_ok && active) ? a.emit + kk : nullptr;
+  int emit_m0 = 0;
   auto step = [&](double* sp, int i) {
     const double ph = row_ok ? sp[i * J + kk] : 0.0;
     const double uu = row_ok ? sp[ROW + i * J + kk] : 0.0;
     const double ww = row_ok ? sp[2 * ROW + i * J + kk] : 0.0;
     const double bn = sp[3 * ROW + i], dn = sp[3 * ROW + TT + i];
     f = ph * fma(wprev, sprev, f);
+    if (MODE == 1 && emit_row) emit_row[(size_t)(emit_m0 + i) * J] = uu * f;   // response of y_n to a unit carry in this row
     const double red = group_sum_masked<L>(uu * f, gmask);
     double res;
     if (MODE == 1) {
@@ -173,6 +176,7 @@ __global__ void __launch_bounds__(kWarp) k_chunk_forward(ScanArgs a) {
     __syncwarp(gmask);
     double* sp = base + (t % kStages) * SM::STAGE;
     const int m0 = n0 + t * TT, cnt = min(TT, n1 - m0);
+    emit_m0 = m0;
     double mine = 0.0;                                   // lane k keeps the results of steps i = k (mod L)
     if (cnt == TT) {
 #pragma unroll
@@ -450,23 +454,32 @@ __global__ void __launch_bounds__(kWarp) k_chunk_maps(ScanArgs a) {
     }
     cp_async_commit_group();
   };
-  auto step = [&](const double* sp, int i) {
+  // step i of the tile starting at m0; with a.emit, lane c also records the response of the sweep's output
+  // at this step to a unit carry in row c (forward: x_n / D_n, backward: z_n)
+  auto step = [&](const double* sp, int i, int m0) {
     const double ph = row_ok ? sp[i * J + kk] : 0.0;
     const double uu = row_ok ? sp[ROW + i * J + kk] : 0.0;
     const double ww = row_ok ? sp[2 * ROW + i * J + kk] : 0.0;
+    double mine = 0.0;
     if (BACKWARD) {
 #pragma unroll
       for (int c = 0; c < L; ++c) {
         const double z = -group_sum_masked<L>(ww * f[c], gmask);
         f[c] = ph * fma(uu, z, f[c]);
+        if (c == kk) mine = z;
       }
     } else {
 #pragma unroll
       for (int c = 0; c < L; ++c) {
         f[c] = ph * fma(wprev, sprev[c], f[c]);
         sprev[c] = -group_sum_masked<L>(uu * f[c], gmask);
+        if (c == kk) mine = sprev[c];
       }
       wprev = ww;
+    }
+    if (a.emit && row_ok && active) {
+      const int n = m0 + i;
+      a.emit[(size_t)n * J + kk] = BACKWARD ? mine : mine * fast_rcp_nocheck(__ldg(a.D + n + off));
     }
   };
 
@@ -477,14 +490,46 @@ __global__ void __launch_bounds__(kWarp) k_chunk_maps(ScanArgs a) {
     __syncwarp(gmask);
     const double* sp = base + (t % kStages) * SM::STAGE;
     const int m0 = n0 + (BACKWARD ? ntiles - 1 - t : t) * TT, cnt = min(TT, n1 - m0);
-    if (BACKWARD) { for (int i = cnt - 1; i >= 0; --i) step(sp, i); }
-    else { for (int i = 0; i < cnt; ++i) step(sp, i); }
+    if (BACKWARD) { for (int i = cnt - 1; i >= 0; --i) step(sp, i, m0); }
+    else { for (int i = 0; i < cnt; ++i) step(sp, i, m0); }
     __syncwarp(gmask);
   }
   if (row_ok && active) {
 #pragma unroll
     for (int c = 0; c < L; ++c)
       if (c < J) a.carry[((size_t)chunk * J + c) * J + kk] = BACKWARD ? f[c] : fma(wprev, sprev[c], f[c]);
+  }
+}
+
+// --------------------------------------------------------------------------------------------
+// pass 2 as an elementwise correction.  The sweeps are affine in the carry that enters a chunk, so
+// (output from the true carry) = (output from a zero carry, written by pass 1) + resp_n . carry, with
+// resp_n the per-step responses recorded once per factor by the map-building sweeps.  No recurrence
+// and no factor: 8 (J + 2) bytes per point and right-hand side instead of 8 (3J + 3).
+// One CTA per (chunk, right-hand side); its first J threads form the chunk's incoming carry
+// h_i + P_i g_s (start_carry), then every thread corrects its steps.
+// --------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_chunk_correct(ScanArgs a, const double* __restrict__ resp) {
+  __shared__ double carry[kCoopMaxJ];
+  const int chunk = blockIdx.x, col = blockIdx.y, J = a.J, N = a.N;
+  const int n0 = chunk * a.chunk_len, n1 = min(N, n0 + a.chunk_len);
+  if (threadIdx.x < J) carry[threadIdx.x] = start_carry(a, chunk, col, threadIdx.x);
+  __syncthreads();
+  const double* x0 = a.in + (size_t)col * N;
+  double* out = a.out + (size_t)col * N;
+  for (int n = n0 + threadIdx.x; n < n1; n += blockDim.x) {
+    const double* r = resp + (size_t)n * J;
+    double acc0 = x0[n], acc1 = 0.0;
+    if ((J & 1) == 0) {
+      for (int c = 0; c < J; c += 2) {
+        const double2 v = __ldg(reinterpret_cast<const double2*>(r + c));
+        acc0 = fma(v.x, carry[c], acc0);
+        acc1 = fma(v.y, carry[c + 1], acc1);
+      }
+    } else {
+      for (int c = 0; c < J; ++c) acc0 = fma(__ldg(r + c), carry[c], acc0);
+    }
+    out[n] = acc0 + acc1;
   }
 }
 
@@ -916,6 +961,13 @@ cudaError_t launch_chunk_sweep(const ScanArgs& a, cudaStream_t stream) {
   }
   CEL_DISPATCH_L(a.J, CALL);
 #undef CALL
+  return cudaGetLastError();
+}
+
+cudaError_t launch_chunk_correct(const ScanArgs& a, const double* resp, cudaStream_t stream) {
+  if (a.J > kMidMaxJ || a.J < 1 || a.nchunks < 1 || a.nrhs < 1 || !a.init || !resp) return cudaErrorInvalidValue;
+  dim3 grid((unsigned)a.nchunks, (unsigned)a.nrhs);
+  k_chunk_correct<<<grid, 128, 0, stream>>>(a, resp);
   return cudaGetLastError();
 }
 

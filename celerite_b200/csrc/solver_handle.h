@@ -63,6 +63,9 @@ struct cel_solver {
   bool maps_valid[3] = {false, false, false};
   cel::DevBuf maps[3];             // [nchunks][nbasis][J] per mode
   cel::DevBuf pmaps[3], smaps[3], tmaps[3];   // prefix / super-chunk / whole-span maps (scan.cu, "middle")
+  cel::DevBuf resp[3];             // [N][J] per mode: response of the sweep's output to a unit carry entering the chunk
+  bool resp_valid[3] = {false, false, false};
+  cel::DevBuf scan_x0;             // pass-1 output kept between cel_span_summarize and cel_span_apply
   cel::DevBuf scan_vecs, scan_h, scan_cs, scan_sg, scan_total, scan_tmp;
 
   // ---- several GPUs, one span of a long series per rank (capi_scan.cu: cel_comm_*, cel_*_mgpu) ----
