@@ -45,7 +45,8 @@ struct FwdState {
 template <int J, bool TAPE>
 __device__ __forceinline__ void fwd_step(FwdState<J>& st, const double (&cf)[J / 2][4], const double (&e)[J / 2],
                                          const double (&cd)[J / 2], const double (&sd)[J / 2], double An, double yn,
-                                         double tn, double dx, double* rec, double& Dn_out, double& x_out) {
+                                         double tn, double dx, double* rec, double& Dn_out, double& x_out,
+                                         double& r_out) {
   constexpr int NP = J / 2, T3 = J * (J + 1) / 2;
   double u[J], v[J];
 #pragma unroll
@@ -79,7 +80,7 @@ __device__ __forceinline__ void fwd_step(FwdState<J>& st, const double (&cf)[J /
     Dn = fma(-u[j], su, Dn);
     wn[j] = v[j] - su;
   }
-  const double r = 1.0 / Dn;
+  const double r = fast_rcp(Dn);    // MUFU seed + two Newton steps; IEEE division outside the normal range
 #pragma unroll
   for (int j = 0; j < J; ++j) { st.DW[j] = wn[j]; st.W[j] = wn[j] * r; }
   st.xprev = x;
@@ -100,9 +101,12 @@ __device__ __forceinline__ void fwd_step(FwdState<J>& st, const double (&cf)[J /
   }
   Dn_out = Dn;
   x_out = x;
+  r_out = r;
 }
 
-template <int J, int REGS>
+// STAPE: the tape of a segment lives in shared memory (segments of 8 steps only) instead of in global
+// memory behind L1/L2
+template <int J, int REGS, bool STAPE = false>
 __global__ void __launch_bounds__(kWarp) __maxnreg__(REGS)
 k_grad_lockstep(GradArgs a, const __grid_constant__ CUtensorMap tm_t, const __grid_constant__ CUtensorMap tm_d,
                 const __grid_constant__ CUtensorMap tm_y) {
@@ -123,6 +127,7 @@ k_grad_lockstep(GradArgs a, const __grid_constant__ CUtensorMap tm_t, const __gr
   const double* tp = a.t + bb * a.stride;
   double* ckpt = a.scratch + (size_t)blockIdx.x * ((size_t)nseg * EC + (size_t)Cseg * E) * kWarp + lane;
   double* tape = ckpt + (size_t)nseg * EC * kWarp;
+  if (STAPE) tape = reinterpret_cast<double*>(smem_al + (size_t)STAGES * 3 * C::kTile + 64) + lane;
 
   const double* row = a.coeffs + bb * a.coeff_stride;
   const double jitter = row[0];
@@ -233,13 +238,13 @@ k_grad_lockstep(GradArgs a, const __grid_constant__ CUtensorMap tm_t, const __gr
 #pragma unroll
     for (int i = 0; i < T; ++i) {
       if (k * T + i < N) {
-        double e[NP], cd[NP], sd[NP], Dn, x;
+        double e[NP], cd[NP], sd[NP], Dn, x, r;
         const double dx = rt[i] - tprev;
         gen1(rt[i], dx, e, cd, sd);
-        fwd_step<J, false>(st, cf, e, cd, sd, rd[i] + aconst, ry[i], rt[i], dx, nullptr, Dn, x);
+        fwd_step<J, false>(st, cf, e, cd, sd, rd[i] + aconst, ry[i], rt[i], dx, nullptr, Dn, x, r);
         tprev = rt[i];
         fail = (Dn < 0.0 && fail == 0) ? k * T + i + 1 : fail;
-        quad = fma(x * x, 1.0 / Dn, quad);
+        quad = fma(x * x, r, quad);
         ld.add(Dn);
       }
     }
@@ -268,11 +273,11 @@ k_grad_lockstep(GradArgs a, const __grid_constant__ CUtensorMap tm_t, const __gr
       for (int i = 0; i < T; ++i) {
         const int n = k * T + i;
         if (n < seg1) {
-          double e[NP], cd[NP], sd[NP], Dn, x;
+          double e[NP], cd[NP], sd[NP], Dn, x, r;
           const double dx = rt[i] - tprev;
           gen1(rt[i], dx, e, cd, sd);
           fwd_step<J, true>(st, cf, e, cd, sd, rd[i] + aconst, ry[i], rt[i], dx,
-                            tape + (size_t)(n - seg0) * E * kWarp, Dn, x);
+                            tape + (size_t)(n - seg0) * E * kWarp, Dn, x, r);
           tprev = rt[i];
         }
       }
@@ -315,7 +320,7 @@ k_grad_lockstep(GradArgs a, const __grid_constant__ CUtensorMap tm_t, const __gr
         v[2 * p] = cd[p]; v[2 * p + 1] = sd[p];
         vp[2 * p] = sd[p]; vp[2 * p + 1] = cd[p];
       }
-      const double r = 1.0 / Dn;
+      const double r = fast_rcp(Dn);
       double PbW[J], Dbar = 0.5 * (xn * r) * (xn * r) - 0.5 * r, xbar = -xn * r;
 #pragma unroll
       for (int k = 0; k < J; ++k) {
@@ -415,19 +420,20 @@ k_grad_lockstep(GradArgs a, const __grid_constant__ CUtensorMap tm_t, const __gr
   }
 }
 
-template <int J, int REGS>
+template <int J, int REGS, bool STAPE = false>
 cudaError_t launch_one(const GradArgs& a, cudaStream_t stream, bool* used) {
   using C = LG<J>;
+  const size_t smem_bytes = C::smem + (STAPE ? (size_t)8 * C::E * kWarp * sizeof(double) + 64 : 0);
   alignas(64) CUtensorMap mt, md, my;
   const bool ok = make_series_map(&mt, a.t, a.B, a.N, a.stride, T) && make_series_map(&md, a.diag, a.B, a.N, a.stride, T) &&
                   make_series_map(&my, a.y, a.B, a.N, a.stride, T);
   *used = ok;
   if (!ok) return cudaSuccess;
-  auto kern = k_grad_lockstep<J, REGS>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::smem);
+  auto kern = k_grad_lockstep<J, REGS, STAPE>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return e;
   const long long grid = (a.B + kWarp - 1) / kWarp;
-  kern<<<(unsigned)grid, kWarp, C::smem, stream>>>(a, mt, md, my);
+  kern<<<(unsigned)grid, kWarp, smem_bytes, stream>>>(a, mt, md, my);
   return cudaGetLastError();
 }
 
@@ -451,10 +457,18 @@ cudaError_t launch_grad_lockstep(const GradArgs& a, cudaStream_t stream, bool* u
   *used = false;
   if (!grad_lockstep_applies(a.Jr, a.Jc, a.Jg, a.stride) || (a.seg % T) != 0) return cudaSuccess;
   if (a.Jc == 2) return launch_one<4, 255>(a, stream, used);
-  // J = 2: 144 registers keep 14 warps per SM resident, so that 2,048 warps (65,536 series) run as one wave
+  // J = 2.  The tape of a segment (8 steps x 14 doubles x 32 lanes = 28 KB per warp) is written to global
+  // memory and read back a few hundred cycles later: the kernel lives on L1 hits, and how many warps an
+  // SM holds decides whether the tapes fit.  Measured on cfg2 (65,536 x 2,000, round 2): 8 warps per SM
+  // (255 registers) 5.05 ms; 12 warps (168) 5.4-5.5 ms; 14 warps (144, one wave) 5.43 ms; 10 warps (200)
+  // 11.7 ms (the tapes thrash); tape in shared memory at the 5 warps per SM that leaves: 5.79 ms;
+  // shared-memory tables for exp/sincos (2.3 KB less L1 per warp): 6.1 ms.  CEL_GRAD_REGS selects.
   static const char* re = getenv("CEL_GRAD_REGS");   // A/B knob
-  if (re && atoi(re) == 168) return launch_one<2, 168>(a, stream, used);
-  return launch_one<2, 144>(a, stream, used);
+  const int rv = re ? atoi(re) : 0;
+  if (rv == 144) return launch_one<2, 144>(a, stream, used);
+  if (rv == 168) return launch_one<2, 168>(a, stream, used);
+  if (rv == 1255 && a.seg == 8) return launch_one<2, 255, true>(a, stream, used);
+  return launch_one<2, 255>(a, stream, used);
 }
 
 }  // namespace cel
