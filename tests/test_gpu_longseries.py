@@ -272,3 +272,54 @@ def test_predict_on_long_series(N, Jr, Jc, M):
     s = solver.CholeskySolver()
     s.compute(p.jitter, p.a_real, p.c_real, p.a_comp, p.b_comp, p.c_comp, p.d_comp, E0, E2, E2, p.x, p.diag)
     assert rel_inf(s.predict(y, xs), chk.predict(p, f, y, xs)) < RTOL_SOLVE
+
+
+def test_mgpu_entry_points_with_a_world_of_one():
+    """cel_comm_init / cel_compute_mgpu / cel_solve_mgpu / cel_dot_L_mgpu / cel_log_likelihood_mgpu through
+    the C ABI with world = 1 (no NCCL needed: the collectives degenerate, the rest of the path is the one
+    every rank of a larger world runs) against the reference.  tests/test_gpu_multi.py does two GPUs."""
+    import ctypes as C
+    import torch
+    from celerite_b200 import _capi
+    N, Jr, Jc = 50_000, 1, 2
+    p, y = _problem(N, Jr, Jc, seed=123)
+    chk = oracle.best()
+    f = chk.factor(p)
+    lib = _capi.lib()
+    h = _capi.create(0)
+    try:
+        dev = torch.device("cuda:0")
+        ptr = lambda a: C.c_void_p(a.ctypes.data)  # noqa: E731
+        lo, hi = C.c_int64(), C.c_int64()
+        assert lib.cel_mgpu_bounds(N, 1, 0, C.byref(lo), C.byref(hi)) == _capi.OK and (lo.value, hi.value) == (0, N)
+        _capi.check(lib.cel_comm_init(h, 1, 0, None), h)
+        ar, cr, ac, bc, cc, dc = (np.ascontiguousarray(v, dtype=np.float64) for v in
+                                  (p.a_real, p.c_real, p.a_comp, p.b_comp, p.c_comp, p.d_comp))
+        _capi.check(lib.cel_compute_mgpu(h, float(p.jitter), Jr, ptr(ar), ptr(cr), Jc, ptr(ac), ptr(bc), ptr(cc), ptr(dc),
+                                         N, ptr(p.x), ptr(p.diag), 0), h)
+        rhs = np.stack([y, np.random.default_rng(5).standard_normal(N)], axis=0)      # two columns, column-major N x 2
+        d_in = torch.from_numpy(rhs).to(dev)
+        d_out = torch.empty_like(d_in)
+        v = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
+        lib.cel_set_stream(h, C.c_void_p(torch.cuda.current_stream(dev).cuda_stream or 1))
+        _capi.check(lib.cel_solve_mgpu(h, 2, v(d_in), v(d_out)), h)
+        torch.cuda.synchronize(dev)
+        assert rel_inf(d_out.cpu().numpy().T, chk.solve(f, rhs.T.copy())) < RTOL_SOLVE
+        _capi.check(lib.cel_dot_L_mgpu(h, 2, v(d_in), v(d_out)), h)
+        torch.cuda.synchronize(dev)
+        assert rel_inf(d_out.cpu().numpy().T, chk.dot_L(f, rhs.T.copy())) < RTOL_SOLVE
+        out3 = (C.c_double * 3)()
+        _capi.check(lib.cel_log_likelihood_mgpu(h, v(d_in[0].contiguous()), out3), h)
+        quad = chk.dot_solve(f, y)
+        ll = -0.5 * (quad + f.log_det + N * np.log(2 * np.pi))
+        assert abs(out3[0] - f.log_det) / abs(f.log_det) < 1e-10
+        assert abs(out3[1] - quad) / abs(quad) < 1e-10
+        assert abs(out3[2] - ll) / abs(ll) < 1e-10
+        # a sweep before cel_compute_mgpu is refused, not run
+        h2 = _capi.create(0)
+        assert lib.cel_solve_mgpu(h2, 1, v(d_in), v(d_out)) == _capi.NOT_COMPUTED
+        lib.cel_destroy(h2)
+    finally:
+        lib.cel_destroy(h)
+        if hasattr(chk, "release"):
+            chk.release(f)
