@@ -73,7 +73,29 @@ def build(force=False, verbose=False):
             print("linked", LIB)
     elif verbose:
         print("up to date:", LIB)
+    _build_examples(verbose)
     return LIB
+
+
+def _build_examples(verbose=False):
+    """examples/*.cu -> build/bin/ (C++ programs over the C ABI alone; run by the GPU tests)."""
+    exdir = os.path.join(ROOT, "examples")
+    bindir = os.path.join(ROOT, "build", "bin")
+    if not os.path.isdir(exdir):
+        return
+    os.makedirs(bindir, exist_ok=True)
+    for src in sorted(f for f in os.listdir(exdir) if f.endswith(".cu")):
+        path = os.path.join(exdir, src)
+        out = os.path.join(bindir, src[:-3])
+        if os.path.exists(out) and os.path.getmtime(out) >= max(os.path.getmtime(path), os.path.getmtime(LIB)):
+            continue
+        cmd = [NVCC, "-O2", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-I", os.path.join(ROOT, "include"),
+               path, "-o", out, "-L", HERE, "-lcelerite_b200", "-Xlinker", "-rpath,$ORIGIN/../../celerite_b200"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("example build failed for %s:\n%s\n%s" % (src, r.stdout, r.stderr))
+        if verbose:
+            print("built", out)
 
 
 if __name__ == "__main__":

@@ -32,3 +32,15 @@ def test_long_series_over_two_gpus(N):
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "OK" in r.stdout, (r.stdout + r.stderr)[-3000:]
     assert "inside the C ABI" in r.stdout
+
+
+def test_cpp_program_over_the_c_abi_alone():
+    """examples/mgpu_long_series.cu: one host thread per visible GPU, no Python and no PyTorch in the
+    process -- cel_comm_unique_id / cel_comm_init / cel_compute_mgpu / cel_solve_mgpu / cel_dot_L_mgpu /
+    cel_log_likelihood_mgpu against one GPU holding the whole series (with one GPU the world is 1 and
+    the collectives degenerate; with more, NCCL carries the span summaries)."""
+    exe = os.path.join(ROOT, "build", "bin", "mgpu_long_series")
+    if not os.path.exists(exe):
+        pytest.skip("build/bin/mgpu_long_series is not built (python -m celerite_b200.build)")
+    r = subprocess.run([exe, "600000"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "OK" in r.stdout, (r.stdout + r.stderr)[-2000:]
