@@ -198,7 +198,7 @@ __device__ __forceinline__ void lock_rec(LockState<J>& st, const LockGen<J, G>& 
       }
       const bool live = !RAG || n0 + g < len;
       if constexpr (BOOK) st.fail = (live && Dn < 0.0 && st.fail == 0) ? n0 + g + 1 : st.fail;  // cholesky.h:176
-      const double r = EXACT ? 1.0 / Dn : fast_rcp_nocheck(Dn);
+      const double r = EXACT ? 1.0 / Dn : fast_rcp_cubic(Dn);
 #pragma unroll
       for (int j = 0; j < J; ++j) { st.DW[j] = wn[j]; st.Wp[j] = wn[j] * r; }
       if constexpr (SOLVE) {

@@ -336,6 +336,7 @@ int cel_term_backprop(cel_solver* s, int nterms, const int* kinds, const double*
 }  // extern "C"
 
 // ---- diagnostic: the kernels' own exp / sincos on plain arrays (cel_debug_math) ------------------
+#include "common.cuh"
 #include "fastmath.cuh"
 namespace {
 __global__ void k_debug_math(int which, long long n, const double* x, double* o1, double* o2) {
@@ -345,7 +346,9 @@ __global__ void k_debug_math(int which, long long n, const double* x, double* o1
   __syncthreads();
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const double v = x[i];
-    if (o2) {
+    if (which == 2) {          // the hot loops' reciprocal
+      o1[i] = cel::fast_rcp_cubic(v);
+    } else if (o2) {
       double s, c;
       if (which == 1) cel::cel_sincos_tab(v, &s, &c, trig_tab);
       else cel::cel_sincos_core(v, &s, &c);
@@ -358,7 +361,7 @@ __global__ void k_debug_math(int which, long long n, const double* x, double* o1
 }  // namespace
 
 extern "C" int cel_debug_math(int which, int64_t n, const double* d_x, double* d_out1, double* d_out2, void* cuda_stream) {
-  if (n < 0 || !d_x || !d_out1 || which < 0 || which > 1) return CEL_INVALID_ARGUMENT;
+  if (n < 0 || !d_x || !d_out1 || which < 0 || which > 2) return CEL_INVALID_ARGUMENT;
   if (n == 0) return CEL_OK;
   k_debug_math<<<296, 256, 0, static_cast<cudaStream_t>(cuda_stream)>>>(which, n, d_x, d_out1, d_out2);
   return cudaGetLastError() == cudaSuccess ? CEL_OK : CEL_CUDA_ERROR;

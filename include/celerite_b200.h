@@ -325,7 +325,8 @@ int cel_term_backprop(cel_solver* s, int nterms, const int* kinds, const double*
 /* Diagnostic: the kernels' own exp / sincos (csrc/fastmath.cuh) evaluated on n device doubles, so that
  * tests can measure their error against libm.  which: 0 polynomial cores (out1 = exp(x); or, with
  * out2 != NULL, out1 = sin(x), out2 = cos(x)), 1 the table-driven variants of the fused batched
- * log-likelihood.  Arguments must lie in the routines' range (|x| < 700 for exp, < 1e9 for sincos). */
+ * log-likelihood, 2 the hot loops' reciprocal (out1 = 1/x, normal positive x).  Arguments must lie in the
+ * routines' range (|x| < 700 for exp, < 1e9 for sincos). */
 int cel_debug_math(int which, int64_t n, const double* d_x, double* d_out1, double* d_out2, void* cuda_stream);
 
 /* Number of kernels this handle has launched since creation (bench.py's gpu_launches). */

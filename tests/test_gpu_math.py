@@ -49,3 +49,12 @@ def test_sincos(which):
     assert max(es.max(), ec.max()) < 2.0 * ULP
     # the pair stays on the unit circle
     assert np.max(np.abs(s * s + c * c - 1.0)) < 4.0 * ULP
+
+
+def test_reciprocal_of_the_hot_loops():
+    rng = np.random.default_rng(3)
+    x = np.concatenate([10.0 ** rng.uniform(-150, 150, 300000), rng.uniform(0.5, 2.0, 300000)])
+    got, _ = _run(2, x, False)
+    err = np.abs(got * x - 1.0)
+    print("fast_rcp_cubic: max |x r - 1| = %.2f ulp" % (err.max() / ULP))
+    assert err.max() < 2.0 * ULP
