@@ -202,17 +202,11 @@ struct LogAccFast {
   }
 };
 
-// reciprocal without the range guard: two Newton steps on the MUFU.RCP64H seed.  Only valid for
+// reciprocal without the range guard: a third-order step on the MUFU.RCP64H seed (fast_rcp_cubic
+// below; round 1 used two Newton steps, one dependent instruction more).  Only valid for
 // normal finite d; the hot loops pair it with LogAccFast, whose flags catch everything else.
-__device__ __forceinline__ double fast_rcp_nocheck(double d) {
-  double r;
-  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
-  double err = fma(-d, r, 1.0);
-  r = fma(r, err, r);
-  err = fma(-d, r, 1.0);
-  r = fma(r, err, r);
-  return r;
-}
+__device__ __forceinline__ double fast_rcp_cubic(double d);
+__device__ __forceinline__ double fast_rcp_nocheck(double d) { return fast_rcp_cubic(d); }
 
 // same contract as fast_rcp_nocheck with one instruction less: a third-order step on the MUFU seed,
 // r = r0 + r0 (e + e^2) with e = 1 - d r0.  The seed is good to ~2^-20, so the remaining error ~e^3 is
@@ -225,18 +219,12 @@ __device__ __forceinline__ double fast_rcp_cubic(double d) {
   return fma(r, t, r);
 }
 
-// reciprocal: MUFU.RCP64H seed (about 20 bits) + two Newton steps; falls back to an IEEE
+// reciprocal: MUFU.RCP64H seed (about 20 bits) + the third-order step; falls back to an IEEE
 // division outside the normal range.  Relative error <= ~1 ulp, far inside the 1e-10 bar.
 __device__ __forceinline__ double fast_rcp(double d) {
   int e = (__double2hiint(d) >> 20) & 0x7ff;
   if (e < 2 || e > 0x7fc) return 1.0 / d;
-  double r;
-  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
-  double err = fma(-d, r, 1.0);
-  r = fma(r, err, r);
-  err = fma(-d, r, 1.0);
-  r = fma(r, err, r);
-  return r;
+  return fast_rcp_cubic(d);
 }
 
 }  // namespace cel
