@@ -55,7 +55,9 @@ struct GradCfg {
   static constexpr int kCoef = 4 * JP + 2;
   static constexpr int kR = 6 * JP;
   static constexpr int kGroup = kIn + kGen + kX + kP + kCoef + kR;
-  static constexpr size_t smem = (size_t)G * kGroup * sizeof(double);
+  static constexpr int kTab = 2 * kTrigTabN + kExpTabN;       // tables of the table-driven exp / sincos
+  static constexpr int kTabOff = (G * kGroup + 1) & ~1;        // 16-byte aligned
+  static constexpr size_t smem = ((size_t)kTabOff + kTab) * sizeof(double);
 };
 
 // 16-byte global->shared copy that bypasses L1 (the tape was written moments ago by other lanes)
@@ -84,6 +86,9 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   const long long sb = (SPAN && a.stride == 0) ? 0 : bb;
   const unsigned gmask = SPAN ? group_mask<L>(g) : kFull;
 
+  double2* trig_tab = reinterpret_cast<double2*>(smem + C::kTabOff);
+  double* exp_tab = smem + C::kTabOff + 2 * kTrigTabN;
+  cel_fill_tables(trig_tab, exp_tab, lane, kWarp);
   double* base = smem + (size_t)g * C::kGroup;
   double* t_s = base;                    // [T+1]
   double* d_s = t_s + T + 2;             // [T]  diag (+A)
@@ -187,8 +192,8 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
           const int item = min(item0 + m * L, nc - 1);
           ii[m] = item / Jc; qq[m] = item - ii[m] * Jc;
           const double tn = t_s[1 + ii[m]], dx = tn - t_s[ii[m]];
-          cel_sincos_core(d_comp[qq[m]] * tn, &sd[m], &cd[m]);
-          e[m] = cel_exp_clamped(-c_comp[qq[m]] * dx);
+          cel_sincos_tab(d_comp[qq[m]] * tn, &sd[m], &cd[m], trig_tab);
+          e[m] = cel_exp_tab(-c_comp[qq[m]] * dx, exp_tab);
         }
 #pragma unroll
         for (int m = 0; m < kGenIlp; ++m) {
@@ -211,7 +216,7 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
         for (int m = 0; m < kGenIlp; ++m) {
           const int item = min(item0 + m * L, nr - 1);
           ii[m] = item / Jr; qq[m] = item - ii[m] * Jr;
-          e[m] = cel_exp_clamped(-c_real[qq[m]] * (t_s[1 + ii[m]] - t_s[ii[m]]));
+          e[m] = cel_exp_tab(-c_real[qq[m]] * (t_s[1 + ii[m]] - t_s[ii[m]]), exp_tab);
         }
 #pragma unroll
         for (int m = 0; m < kGenIlp; ++m) {
