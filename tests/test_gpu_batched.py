@@ -212,6 +212,39 @@ def test_wide_kernels_batched_gradient_and_limit(bs):
         bs.log_likelihood(wide["coeffs"], wide["t"], wide["diag"], wide["y"], 0, 49)
 
 
+def test_unusual_series_take_the_careful_path(bs):
+    """The second-generation fused kernel is optimistic: pivots outside [2^-500, 2^500] and trigonometric
+    arguments beyond 1e9 send a lane (resp. a warp) to careful_series().  Both must still match the reference:
+    a batch in which some series are scaled by 1e160 (pivots ~1e160), and one whose time stamps are offset
+    by 1e9 days (d*t ~ 1e10).  The same inputs run through the ragged entry point (first-generation kernel)."""
+    from celerite_b200 import synth
+    B, N, Jr, Jc = 70, 400, 0, 1
+    b = synth.make_batch(B, N, Jr, Jc, seed=77)
+    coeffs, t, diag, y = b["coeffs"].copy(), b["t"].copy(), b["diag"].copy(), b["y"].copy()
+    big = [3, 40, 69]
+    for i in big:                       # K -> s K, y -> sqrt(s) y: same quadratic form, log det + N log s
+        s = 1e160
+        coeffs[i, 0] *= s               # jitter
+        coeffs[i, 1] *= s               # a
+        coeffs[i, 2] *= s               # b
+        diag[i] *= s
+        y[i] *= 1e80
+    P = coeffs.shape[1]
+    ref = oracle.best().batched_loglik(B, N, N, Jr, Jc, coeffs, P, t, diag, y, nthreads=4)
+    ll, logdet, quad, status = bs.log_likelihood(coeffs, t, diag, y, Jr, Jc, return_parts=True)
+    assert np.all(status == 0) and np.all(ref[:, 2] == 0)
+    assert np.max(np.abs(logdet - ref[:, 0]) / np.abs(ref[:, 0])) < RTOL_SCALAR
+    assert np.max(np.abs(quad - ref[:, 1]) / np.abs(ref[:, 1])) < RTOL_SCALAR
+    assert logdet[3] > 0.9 * N * np.log(1e160)                    # the scaled series really are huge
+    # time stamps far from zero: sin/cos of d*t with |d*t| ~ 1e10 (stock range reduction on the GPU as on the CPU)
+    t2 = t + 1.0e9
+    ref2 = oracle.best().batched_loglik(B, N, N, Jr, Jc, b["coeffs"], P, t2, b["diag"], b["y"], nthreads=4)
+    ll2, logdet2, quad2, status2 = bs.log_likelihood(b["coeffs"], t2, b["diag"], b["y"], Jr, Jc, return_parts=True)
+    assert np.all(status2 == 0)
+    assert np.max(np.abs(logdet2 - ref2[:, 0]) / np.maximum(np.abs(ref2[:, 0]), 1.0)) < 1e-9
+    assert np.max(np.abs(quad2 - ref2[:, 1]) / np.abs(ref2[:, 1])) < 1e-9
+
+
 def test_jitter_only_batch(bs):
     """J = 0 (cholesky.h:90-95, 334-339): K = diag(sigma^2 + jitter)."""
     rng = np.random.default_rng(0)
