@@ -635,10 +635,12 @@ int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t str
   };
   auto launch = [&](cel::GradArgs& ga) -> cudaError_t {
     bool used = false;
+    int nl = 0;
     if (lock) {
-      cudaError_t e = cel::launch_grad_lockstep(ga, st, &used);
+      cudaError_t e = cel::launch_grad_lockstep(ga, st, &used, &nl);
       if (e != cudaSuccess) return e;
     }
+    s->launches += used ? nl : 1;
     return used ? cudaSuccess : cel::launch_grad_coop(ga, st);
   };
   if (!(flags & CEL_HOST_POINTERS)) {
@@ -647,7 +649,6 @@ int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t str
     a.t = t; a.diag = diag; a.y = y;
     a.out_val = out_val; a.out_grad = out_grad; a.status = status; a.scratch = s->scratch0.d();
     CEL_CUDA_TRY(s, launch(a));
-    s->launches += 1;
     return CEL_OK;
   }
   // host buffers: chunks of the batch, staged one after the other on the handle's stream
@@ -686,7 +687,6 @@ int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t str
     a.out_val = s->stage_o[0].d(); a.out_grad = s->stage_o[0].d() + chunk;
     a.status = s->stage_s[0].i(); a.scratch = s->scratch0.d();
     CEL_CUDA_TRY(s, launch(a));
-    s->launches += 1;
     CEL_CUDA_TRY(s, cudaMemcpyAsync(out_val + b0, a.out_val, dbytes(nb), cudaMemcpyDeviceToHost, st));
     CEL_CUDA_TRY(s, cudaMemcpyAsync(out_grad + b0 * P, a.out_grad, dbytes((size_t)nb * P), cudaMemcpyDeviceToHost, st));
     if (status) CEL_CUDA_TRY(s, cudaMemcpyAsync(status + b0, a.status, nb * sizeof(int), cudaMemcpyDeviceToHost, st));

@@ -68,6 +68,12 @@ struct BatchArgs {
   // the steps before are its warm-up halo.  B = number of segments, stride = coeff_stride = 0.
   const int* seg;          // NULL for batches of whole series
   double* seg_edge;        // [B][J+1]: W and D of the last warm-up step, for the consistency check
+  // Forward half of the two-kernel gradient (lockstep_grad2.cu; launch_loglik_lockstep_ckpt only):
+  // the recursion state before every 4th step, [warp of 32 series][segment][10][32] doubles, and per
+  // series whether it left the fast path (then its outputs are not final: the caller re-does it)
+  double* ckpt;
+  int* flags;
+  double* out_half;        // -0.5 * (quad + logdet), no constant (the gradient entry points' value)
 };
 
 // Thread-per-series lockstep sweep (fused log-likelihood), J = Jr + 2*Jc <= kLockstepMaxJ, Jg = 0.
@@ -113,6 +119,7 @@ struct GradArgs {
   double* out_logdet;   // optional
   double* out_quad;     // optional
   int* status;
+  const int* only;      // lockstep kernel: NULL, or per series non-zero = wanted (warps with none leave at once)
   double* scratch;      // grad_scratch_doubles(B, N, J, seg) doubles
   int seg;              // checkpoint distance (multiple of 16)
   // Time spans of ONE long series (launch_grad_spans): group b sweeps [span[4b], span[4b+3])
@@ -138,7 +145,16 @@ cudaError_t launch_grad_coop(const GradArgs& a, cudaStream_t stream);
 // Thread-per-series variant of the same sweep (lockstep_grad.cu) for all-complex J = 2, 4.
 bool grad_lockstep_applies(int Jr, int Jc, int Jg, long long stride);
 size_t grad_lockstep_scratch_doubles(long long B, int N, int Jc, int seg);
-cudaError_t launch_grad_lockstep(const GradArgs& a, cudaStream_t stream, bool* used);
+cudaError_t launch_grad_lockstep(const GradArgs& a, cudaStream_t stream, bool* used, int* launches = nullptr);
+// J = 2 (one complex term): forward sweep of the fused log-likelihood kernel that also leaves checkpoints
+// (lockstep.cu), and the reverse sweep over them (lockstep_grad2.cu)
+constexpr int kGrad2Seg = 4;      // steps between checkpoints
+constexpr int kGrad2Ckpt = 10;    // doubles per checkpoint: S00 S01 S11 DW0 DW1 D f0 f1 x t
+cudaError_t launch_loglik_lockstep_ckpt(const BatchArgs& a, cudaStream_t stream, bool* used);
+size_t grad2_scratch_doubles(long long B, int N, int seg_v1);
+size_t grad_lockstep_v1_scratch_doubles(long long B, int N, int Jc, int seg);
+cudaError_t launch_grad_lockstep_v1(const GradArgs& a, cudaStream_t stream, bool* used);
+cudaError_t launch_grad2(const GradArgs& a, cudaStream_t stream, bool* used, int* launches);
 
 // One stored factor (reference layout) applied to nrhs right-hand sides, DEVICE pointers.
 struct SweepArgs {

@@ -279,7 +279,9 @@ __device__ __noinline__ void careful_series(const BatchArgs& a, long long bb, in
   *logdet = lsum; *quad = st.quad; *fail = bad_at;
 }
 
-template <int J, bool ALLC, int CAP, bool TAB, bool PIPE = false>
+// CKPT (forward half of the two-kernel gradient, J = 2): the state before every kGrad2Seg-th step goes to
+// a.ckpt, series that left the fast path are flagged in a.flags instead of being redone here
+template <int J, bool ALLC, int CAP, bool TAB, bool PIPE = false, bool CKPT = false>
 __global__ void __launch_bounds__(kLockThreads) __maxnreg__(CAP)
 k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const __grid_constant__ CUtensorMap tm_d,
                    const __grid_constant__ CUtensorMap tm_y) {
@@ -378,6 +380,18 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
 #pragma unroll
     for (int c = 0; c < T / 2; ++c) offc[c] = (c ^ swz) << 4;
     double tlast = __ldg(tp);
+    double Dlast = 1.0;
+    // checkpoint s = the state before step kGrad2Seg * s: S, D W and D of the step before, f, x, t
+    const int nckpt = (N + kGrad2Seg - 1) / kGrad2Seg;
+    double* ckp = CKPT ? a.ckpt + ((size_t)(b0 / kWarp) * nckpt * kGrad2Ckpt) * kWarp + lane : nullptr;
+    auto checkpoint = [&](int s) {
+      if constexpr (CKPT && J == 2) {
+        double* q = ckp + (size_t)s * (kGrad2Ckpt * kWarp);
+        q[0] = st.S[0]; q[kWarp] = st.S[1]; q[2 * kWarp] = st.S[2];
+        q[3 * kWarp] = st.DW[0]; q[4 * kWarp] = st.DW[1]; q[5 * kWarp] = Dlast;
+        q[6 * kWarp] = st.f[0]; q[7 * kWarp] = st.f[1]; q[8 * kWarp] = st.xprev; q[9 * kWarp] = tlast;
+      }
+    };
 
     // one pair of steps: loads, generators, recursion, optimistic bookkeeping
     auto pair = [&](const unsigned char* src, int c, auto guard, int nvalid) {
@@ -401,6 +415,7 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
       const int hp = __double2hiint(P);
       e32 += (hp >> 20) - 1023;
       mant *= __hiloint2double((hp & 0x000fffff) | 0x3ff00000, __double2loint(P));
+      if (CKPT) Dlast = Dg[1];
     };
     auto renorm = [&]() {
       const int hi = __double2hiint(mant);
@@ -458,6 +473,7 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
             __syncwarp();
             if (k + STAGES < ntiles) issue(k + STAGES);
           }
+          if (CKPT && (c & 1) && k * T + 2 * c + 2 < N) checkpoint((k * T + 2 * c + 2) / kGrad2Seg);
         }
       }
       if ((k & 63) == 63) renorm();
@@ -469,7 +485,10 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
       const int left = N - nfull * T;
 #pragma unroll
       for (int c = 0; c < T / 2; ++c)
-        if (2 * c < left) pair(src, c, std::true_type(), left - 2 * c);
+        if (2 * c < left) {
+          pair(src, c, std::true_type(), left - 2 * c);
+          if (CKPT && (c & 1) && 2 * c + 2 < left) checkpoint((nfull * T + 2 * c + 2) / kGrad2Seg);
+        }
     }
     renorm();
   }
@@ -477,11 +496,15 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
   double logdet = log(mant) + 0.6931471805599453094 * static_cast<double>(expo);
   double q = st.quad;
   int fail = 0;
-  if (bad) careful_series<J, ALLC>(a, bb, N, cf, asum, jitter, &logdet, &q, &fail);
+  if (bad && !CKPT) careful_series<J, ALLC>(a, bb, N, cf, asum, jitter, &logdet, &q, &fail);
 
   if (active) {
     const double nan = __longlong_as_double(0x7ff8000000000000LL);
     if (fail) { logdet = nan; q = nan; }
+    if (CKPT) {
+      a.flags[b] = bad ? 1 : 0;
+      if (a.out_half) a.out_half[b] = -0.5 * (q + logdet);
+    }
     if (a.out_logdet) a.out_logdet[b] = logdet;
     if (a.out_quad) a.out_quad[b] = q;
     if (a.out_ll) a.out_ll[b] = -0.5 * (q + logdet + (double)N * kLog2Pi);  // celerite.py:214-216
@@ -517,6 +540,30 @@ cudaError_t launch_v2(const BatchArgs& a, cudaStream_t stream, bool* used) {
   *used = true;
   return cudaGetLastError();
 }
+
+}  // namespace
+
+// forward half of the two-kernel gradient (J = 2, all complex): the fused kernel, leaving checkpoints
+cudaError_t launch_loglik_lockstep_ckpt(const BatchArgs& a, cudaStream_t stream, bool* used) {
+  constexpr int T = 8, STAGES = 2, J = 2;
+  constexpr int WARPS = kLockThreads / kWarp;
+  constexpr size_t smem = (size_t)WARPS * STAGES * 3 * kWarp * T * 8 + 64 + kTrigTabN * 16 + kExpTabN * 8 + 1024;
+  *used = false;
+  if (a.Jr != 0 || a.Jc != 1 || a.Jg != 0 || a.lengths || a.N < 1 || !a.ckpt || !a.flags) return cudaSuccess;
+  alignas(64) CUtensorMap mt, md, my;
+  if (!(make_series_map(&mt, a.t, a.B, a.N, a.stride, T) && make_series_map(&md, a.diag, a.B, a.N, a.stride, T) &&
+        make_series_map(&my, a.y, a.B, a.N, a.stride, T)))
+    return cudaSuccess;
+  auto kern = k_loglik_lockstep2<J, true, lock_maxreg(J), true, false, true>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  const long long grid = (a.B + kLockThreads - 1) / kLockThreads;
+  kern<<<(unsigned)grid, kLockThreads, smem, stream>>>(a, mt, md, my);
+  *used = true;
+  return cudaGetLastError();
+}
+
+namespace {
 
 template <int J, int G, int T, int STAGES, int CAP = lock_maxreg(J), bool PIPE = false>
 cudaError_t launch_one(const BatchArgs& a, cudaStream_t stream) {

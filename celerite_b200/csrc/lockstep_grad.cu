@@ -122,6 +122,7 @@ k_grad_lockstep(GradArgs a, const __grid_constant__ CUtensorMap tm_t, const __gr
   const long long b = b0 + lane;
   const bool active = b < a.B;
   const long long bb = active ? b : a.B - 1;
+  if (a.only && !__any_sync(kFull, active && a.only[bb] != 0)) return;   // redo pass: nothing flagged in this warp
   const int N = a.N, Jc = a.Jc, Pn = 1 + 4 * Jc;
   const int Cseg = a.seg, nseg = (N + Cseg - 1) / Cseg;
   const double* tp = a.t + bb * a.stride;
@@ -446,6 +447,13 @@ bool grad_lockstep_applies(int Jr, int Jc, int Jg, long long stride) {
 }
 
 size_t grad_lockstep_scratch_doubles(long long B, int N, int Jc, int seg) {
+  const size_t v1 = grad_lockstep_v1_scratch_doubles(B, N, Jc, seg);   // also what the fallback of Jc = 1 uses
+  if (Jc != 1) return v1;
+  const size_t v2 = grad2_scratch_doubles(B, N, seg);
+  return v2 > v1 ? v2 : v1;
+}
+
+size_t grad_lockstep_v1_scratch_doubles(long long B, int N, int Jc, int seg) {
   const int J = 2 * Jc, NP = Jc, T3 = J * (J + 1) / 2;
   const size_t E = T3 + 2 * J + 2 + 3 * NP + 2, EC = T3 + 3 * J + 2;
   const size_t nseg = (size_t)(N + seg - 1) / seg;
@@ -453,7 +461,18 @@ size_t grad_lockstep_scratch_doubles(long long B, int N, int Jc, int seg) {
   return warps * (nseg * EC + (size_t)seg * E) * kWarp;
 }
 
-cudaError_t launch_grad_lockstep(const GradArgs& a, cudaStream_t stream, bool* used) {
+cudaError_t launch_grad_lockstep(const GradArgs& a, cudaStream_t stream, bool* used, int* launches) {
+  *used = false;
+  if (a.Jc == 1 && !a.only) {      // one complex term: the two-kernel form (lockstep_grad2.cu)
+    cudaError_t e = launch_grad2(a, stream, used, launches);
+    if (e != cudaSuccess || *used) return e;
+  }
+  cudaError_t e = launch_grad_lockstep_v1(a, stream, used);
+  if (e == cudaSuccess && *used && launches) *launches += 1;
+  return e;
+}
+
+cudaError_t launch_grad_lockstep_v1(const GradArgs& a, cudaStream_t stream, bool* used) {
   *used = false;
   if (!grad_lockstep_applies(a.Jr, a.Jc, a.Jg, a.stride) || (a.seg % T) != 0) return cudaSuccess;
   if (a.Jc == 2) return launch_one<4, 255>(a, stream, used);

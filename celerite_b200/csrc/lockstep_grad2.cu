@@ -1,0 +1,302 @@
+// K6b — value + reverse-mode gradient for batches with ONE complex term (J = 2: a single SHO-type term,
+// the shape of BASELINE config 2), second generation: two kernels instead of one.
+//
+// Same mathematics as lockstep_grad.cu (celerite/solver.cpp:347-463 differentiated by hand, a lane per
+// series), but organised around what bounded the first generation.  That kernel kept a thread's forward
+// state, adjoint state and an 8-step tape behind L1 at ~180 registers, i.e. two warps per scheduler, and
+// spent its time waiting on fixed-latency dependencies (profiles/r02_grad_lockstep_before.txt: 1.8 warps
+// active, 0.39 eligible per scheduler, issue slots 33 % busy).  Here:
+//
+//  forward  (lockstep.cu, k_loglik_lockstep2<..., CKPT>): the fused log-likelihood kernel at its usual
+//           128 registers, which additionally stores the recursion state before every 4th step
+//           (10 doubles per series and segment, lane-contiguous 256-byte rows);
+//  reverse  (below): segments of 4 steps from the last to the first: load the checkpoint, recompute the
+//           4 steps writing what the adjoint needs (12 doubles per step) to SHARED memory, then run the
+//           adjoint of the 4 steps reading it back.  Inputs arrive as [32 series x 4 points] TMA boxes,
+//           the box of the next segment in flight while this one is worked on.  One CTA of 14 warps per
+//           SM (one copy of the exp / sincos tables, 15 KB of tape + tile per warp = 212 KB), 128
+//           registers: all 2,048 warps of config 2 are resident at once, 3.5 per scheduler.
+//
+// The adjoint step is also leaner than the first generation's: the tape holds S_n (already scaled by
+// phi phi^T), 1/D_n and x_n/D_n, so the step needs no reciprocal, no record of step n-1 (phi-bar times
+// phi is formed directly: fbar . f_n + 2 sum sb o S_n) and only the five sums the gradient is made of.
+//
+// Series that leave the fast path of the forward kernel (pivot outside [2^-500, 2^500] or not finite,
+// negative pivots, |d t| >= 1e9) are flagged there and redone by the first-generation kernel, which
+// carries the guarded arithmetic and the reference's failure semantics (launch_grad2 below).
+#include <cfloat>
+#include <cstdlib>
+#include <type_traits>
+
+#include "lockstep_common.cuh"
+
+namespace cel {
+namespace {
+
+using namespace lockstep;
+
+constexpr int kSeg = kGrad2Seg;          // steps per segment = points per TMA box
+constexpr int kRows = 12;                // tape rows per step: S00 S01 S11 W0 W1 f0 f1 r xr e cd sd
+constexpr int kRevWarps = 14;
+constexpr int kRevThreads = kRevWarps * kWarp;
+constexpr int kTileB = kWarp * kSeg * 8;                       // one [32 x 4] box: 1 KB
+constexpr int kWarpBytes = 3 * kTileB + kRows * kSeg * kWarp * 8;   // 3 KB of boxes + 12 KB of tape
+constexpr int kBarBytes = 128;                                 // 14 mbarriers, padded
+constexpr size_t kRevSmem = (size_t)kRevWarps * kWarpBytes + kBarBytes + kTrigTabN * 16 + kExpTabN * 8 + 1024;
+static_assert(kWarpBytes % 1024 == 0 && kRevWarps * 8 <= kBarBytes, "shared-memory layout");
+
+__global__ void __maxnreg__(128)
+k_grad2_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_constant__ CUtensorMap tm_t,
+                const __grid_constant__ CUtensorMap tm_d, const __grid_constant__ CUtensorMap tm_y) {
+  extern __shared__ unsigned char smem_dyn[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned char* smem_al = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
+  unsigned char* wtile = smem_al + (size_t)warp * kWarpBytes;
+  double* tape = reinterpret_cast<double*>(wtile + 3 * kTileB) + lane;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem_al + (size_t)kRevWarps * kWarpBytes) + warp;
+  double2* trig_tab = reinterpret_cast<double2*>(smem_al + (size_t)kRevWarps * kWarpBytes + kBarBytes);
+  double* exp_tab = reinterpret_cast<double*>(trig_tab + kTrigTabN);
+  cel_fill_tables(trig_tab, exp_tab, threadIdx.x, kRevThreads);
+  __syncthreads();
+
+  const long long wg = (long long)blockIdx.x * kRevWarps + warp;   // 32 series per warp
+  const long long b0 = wg * kWarp;
+  if (b0 >= a.B) return;
+  const long long b = b0 + lane;
+  const bool active = b < a.B;
+  const long long bb = active ? b : a.B - 1;
+  const int N = a.N;
+  const int nseg = (N + kSeg - 1) / kSeg;
+
+  const double* row = a.coeffs + bb * a.coeff_stride;
+  const double jitter = row[0];
+  const double ca = row[1], cb = row[2], cc = row[3], cd_ = row[4];
+  const double aconst = ca + jitter;
+  const double ncc = -cc;
+
+  if (lane == 0) {
+    mbar_init(bar, 1);
+    mbar_fence_init();
+  }
+  __syncwarp();
+  auto issue = [&](int s) {
+    if (lane == 0) {
+      fence_async_smem();
+      mbar_arrive_expect_tx(bar, 3u * kTileB);
+      tma_load_2d(wtile, &tm_t, s * kSeg, (int)b0, bar);
+      tma_load_2d(wtile + kTileB, &tm_d, s * kSeg, (int)b0, bar);
+      tma_load_2d(wtile + 2 * kTileB, &tm_y, s * kSeg, (int)b0, bar);
+    }
+  };
+  issue(nseg - 1);
+
+  const double* ck = ckpt_base + ((size_t)wg * nseg * kGrad2Ckpt) * kWarp + lane;
+  const unsigned char* lrow = wtile + lane * (kSeg * 8);
+
+  // adjoint state: Pb = adjoint of P_{n+1} (symmetric), g = adjoint of f_{n+1} scaled back by phi
+  double Pb00 = 0.0, Pb01 = 0.0, Pb11 = 0.0, g0 = 0.0, g1 = 0.0;
+  double ga = 0.0, gb = 0.0, gc = 0.0, gd = 0.0, sumA = 0.0;
+  unsigned phase = 0;
+
+  auto segment = [&](const int s, auto guard, const int nv) {
+    constexpr bool GUARD = decltype(guard)::value;
+    // ---- state before step kSeg*s (zero before the first step: cholesky.h:104-124 as one more step) ----
+    double S00 = 0.0, S01 = 0.0, S11 = 0.0, DW0 = 0.0, DW1 = 0.0, Dp = 1.0, f0 = 0.0, f1 = 0.0, xp = 0.0, tprev = 0.0;
+    if (s > 0) {
+      const double* q = ck + (size_t)s * (kGrad2Ckpt * kWarp);
+      S00 = q[0]; S01 = q[kWarp]; S11 = q[2 * kWarp];
+      DW0 = q[3 * kWarp]; DW1 = q[4 * kWarp]; Dp = q[5 * kWarp];
+      f0 = q[6 * kWarp]; f1 = q[7 * kWarp]; xp = q[8 * kWarp]; tprev = q[9 * kWarp];
+    }
+    // ---- this segment's inputs into registers, then the box of the next one may land in the slot ----
+    mbar_wait(bar, phase);
+    phase ^= 1u;
+    double rt[kSeg], rd[kSeg], ry[kSeg];
+#pragma unroll
+    for (int c = 0; c < kSeg / 2; ++c) {
+      const double2 v0 = *reinterpret_cast<const double2*>(lrow + 16 * c);
+      const double2 v1 = *reinterpret_cast<const double2*>(lrow + kTileB + 16 * c);
+      const double2 v2 = *reinterpret_cast<const double2*>(lrow + 2 * kTileB + 16 * c);
+      rt[2 * c] = v0.x; rt[2 * c + 1] = v0.y;
+      rd[2 * c] = v1.x; rd[2 * c + 1] = v1.y;
+      ry[2 * c] = v2.x; ry[2 * c + 1] = v2.y;
+    }
+    __syncwarp();
+    if (s > 0) issue(s - 1);
+    if (s == 0) tprev = rt[0];
+    const double t_in = tprev;
+    const double rp = fast_rcp_cubic(Dp);
+    double W0 = DW0 * rp, W1 = DW1 * rp;
+
+    // ---- recompute the segment, taping what the adjoint needs ----
+#pragma unroll
+    for (int i = 0; i < kSeg; ++i) {
+      if (!GUARD || i < nv) {
+        const double tn = rt[i];
+        const double dx = tn - tprev;
+        double sd, cd;
+        cel_sincos_tab(cd_ * tn, &sd, &cd, trig_tab);
+        const double e = cel_exp_tab(ncc * dx, exp_tab);
+        const double u0 = fma(ca, cd, cb * sd), u1 = fma(ca, sd, -(cb * cd));
+        const double e2 = e * e;
+        S00 = e2 * fma(DW0, W0, S00);
+        S01 = e2 * fma(DW1, W0, S01);
+        S11 = e2 * fma(DW1, W1, S11);
+        f0 = e * fma(W0, xp, f0);
+        f1 = e * fma(W1, xp, f1);
+        const double x = fma(-u1, f1, fma(-u0, f0, ry[i]));
+        const double su0 = fma(S01, u1, S00 * u0), su1 = fma(S11, u1, S01 * u0);
+        const double D = fma(-u1, su1, fma(-u0, su0, rd[i] + aconst));
+        DW0 = cd - su0; DW1 = sd - su1;
+        const double r = fast_rcp_cubic(D);
+        W0 = DW0 * r; W1 = DW1 * r;
+        xp = x; tprev = tn;
+        double* q = tape + i * (kRows * kWarp);
+        q[0] = S00; q[kWarp] = S01; q[2 * kWarp] = S11;
+        q[3 * kWarp] = W0; q[4 * kWarp] = W1;
+        q[5 * kWarp] = f0; q[6 * kWarp] = f1;
+        q[7 * kWarp] = r; q[8 * kWarp] = x * r;
+        q[9 * kWarp] = e; q[10 * kWarp] = cd; q[11 * kWarp] = sd;
+      }
+    }
+    // ---- adjoint of the segment, last step first ----
+#pragma unroll
+    for (int i = kSeg - 1; i >= 0; --i) {
+      if (!GUARD || i < nv) {
+        const double* q = tape + i * (kRows * kWarp);
+        const double s00 = q[0], s01 = q[kWarp], s11 = q[2 * kWarp];
+        const double w0 = q[3 * kWarp], w1 = q[4 * kWarp];
+        const double ff0 = q[5 * kWarp], ff1 = q[6 * kWarp];
+        const double r = q[7 * kWarp], xr = q[8 * kWarp];
+        const double e = q[9 * kWarp], cd = q[10 * kWarp], sd = q[11 * kWarp];
+        const double tn = rt[i];
+        const double ndx = (i == 0 ? t_in : rt[i == 0 ? 0 : i - 1]) - tn;
+        const double u0 = fma(ca, cd, cb * sd), u1 = fma(ca, sd, -(cb * cd));
+        const double PbW0 = fma(Pb01, w1, Pb00 * w0), PbW1 = fma(Pb11, w1, Pb01 * w0);
+        // wb = W-bar / D_n (D_n / D_n = 1 in 2 D_n PbW / D_n)
+        const double wb0 = fma(g0, xr, PbW0 + PbW0), wb1 = fma(g1, xr, PbW1 + PbW1);
+        double Dbar = fma(0.5 * xr, xr, -0.5 * r);
+        Dbar = fma(w0, PbW0 - wb0, Dbar);
+        Dbar = fma(w1, PbW1 - wb1, Dbar);
+        const double xbar = fma(g1, w1, fma(g0, w0, -xr));
+        sumA += Dbar;
+        const double fb0 = fma(-xbar, u0, g0), fb1 = fma(-xbar, u1, g1);
+        const double Su0 = fma(s01, u1, s00 * u0), Su1 = fma(s11, u1, s01 * u0);
+        const double Sw0 = fma(s01, wb1, s00 * wb0), Sw1 = fma(s11, wb1, s01 * wb0);
+        const double D2 = Dbar + Dbar;
+        const double ub0 = fma(-D2, Su0, fma(-xbar, ff0, -Sw0));
+        const double ub1 = fma(-D2, Su1, fma(-xbar, ff1, -Sw1));
+        const double du0 = -Dbar * u0, du1 = -Dbar * u1;
+        const double hw0 = -0.5 * wb0, hw1 = -0.5 * wb1;
+        const double sb00 = fma(du0 - wb0, u0, Pb00);
+        const double sb11 = fma(du1 - wb1, u1, Pb11);
+        const double sb01 = fma(hw0 + du0, u1, fma(hw1, u0, Pb01));
+        // (phi-bar . phi) summed over the pair: fbar . f_n + 2 sum_kj sb_kj S_kj
+        double qq = (sb01 + sb01) * s01;
+        qq = fma(sb00, s00, qq);
+        qq = fma(sb11, s11, qq);
+        const double pe = fma(2.0, qq, fma(fb1, ff1, fb0 * ff0));
+        gc = fma(ndx, pe, gc);
+        g0 = e * fb0; g1 = e * fb1;
+        const double e2 = e * e;
+        Pb00 = e2 * sb00; Pb01 = e2 * sb01; Pb11 = e2 * sb11;
+        ga = fma(ub1, sd, fma(ub0, cd, ga));
+        gb = fma(-ub1, cd, fma(ub0, sd, gb));
+        const double gq = fma(wb1, cd, fma(-wb0, sd, fma(ub1, u0, -(ub0 * u1))));
+        gd = fma(tn, gq, gd);
+      }
+    }
+  };
+
+  const int nfull = N / kSeg;
+  if (nfull < nseg) segment(nseg - 1, std::true_type(), N - nfull * kSeg);
+#pragma unroll 1
+  for (int s = nfull - 1; s >= 0; --s) segment(s, std::false_type(), kSeg);
+
+  if (active) {
+    double* g = a.out_grad + (size_t)b * 5;
+    g[0] = (jitter > DBL_EPSILON) ? sumA : 0.0;   // solver.cpp:377-389, 418-426
+    g[1] = ga + sumA;
+    g[2] = gb;
+    g[3] = gc;
+    g[4] = gd;
+  }
+}
+
+}  // namespace
+
+// The batch goes through in pieces of at most this many series, so that the checkpoints of a piece
+// (20 bytes per point) stay below ~6 GB whatever the batch
+static long long grad2_piece(long long B, int N) {
+  const double per_series = 8.0 * kGrad2Ckpt * ((N + kSeg - 1) / kSeg);
+  long long piece = (long long)(6.0e9 / per_series) / (kRevWarps * kWarp) * (kRevWarps * kWarp);
+  if (piece < 64 * kRevWarps * kWarp) piece = 64 * kRevWarps * kWarp;
+  return B < piece ? B : piece;
+}
+static size_t flag_doubles(long long piece) { return ((size_t)piece / 2 + 32) & ~(size_t)31; }
+
+// flags of a piece + the larger of its checkpoints and what the first-generation kernel wants for the redo
+size_t grad2_scratch_doubles(long long B, int N, int seg_v1) {
+  const long long piece = grad2_piece(B, N);
+  const size_t warps = (size_t)((piece + kWarp - 1) / kWarp);
+  const size_t nseg = (size_t)(N + kSeg - 1) / kSeg;
+  const size_t ck = warps * nseg * kGrad2Ckpt * kWarp;
+  const size_t v1 = grad_lockstep_v1_scratch_doubles(piece, N, 1, seg_v1);
+  return flag_doubles(piece) + (ck > v1 ? ck : v1);
+}
+
+cudaError_t launch_grad2(const GradArgs& a, cudaStream_t stream, bool* used, int* launches) {
+  *used = false;
+  static const bool off = getenv("CEL_GRAD_V1") != nullptr;   // A/B knob: the first-generation kernel
+  if (off || a.Jr != 0 || a.Jc != 1 || a.Jg != 0 || a.stride <= 0 || a.span || a.only || a.N < 1 || a.B < 1)
+    return cudaSuccess;
+  if ((a.seg % 8) != 0 || a.seg < 8) return cudaSuccess;
+  const long long piece = grad2_piece(a.B, a.N);
+  int* flags = reinterpret_cast<int*>(a.scratch);
+  double* region = a.scratch + flag_doubles(piece);
+  auto kern = k_grad2_reverse;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRevSmem);
+  if (e != cudaSuccess) return e;
+  for (long long off0 = 0; off0 < a.B; off0 += piece) {
+    const long long nb = (off0 + piece <= a.B) ? piece : a.B - off0;
+    GradArgs g = a;
+    g.B = nb;
+    g.coeffs = a.coeffs + off0 * a.coeff_stride;
+    g.t = a.t + off0 * a.stride; g.diag = a.diag + off0 * a.stride; g.y = a.y + off0 * a.stride;
+    g.out_val = a.out_val ? a.out_val + off0 : nullptr;
+    g.out_grad = a.out_grad + off0 * 5;
+    g.out_logdet = a.out_logdet ? a.out_logdet + off0 : nullptr;
+    g.out_quad = a.out_quad ? a.out_quad + off0 : nullptr;
+    g.status = a.status ? a.status + off0 : nullptr;
+    alignas(64) CUtensorMap mt, md, my;
+    if (!(make_rows_map(&mt, g.t, nb, a.N, a.stride, kSeg, false) && make_rows_map(&md, g.diag, nb, a.N, a.stride, kSeg, false) &&
+          make_rows_map(&my, g.y, nb, a.N, a.stride, kSeg, false)))
+      return off0 == 0 ? cudaSuccess : cudaErrorInvalidValue;
+    BatchArgs f{};
+    f.B = nb; f.N = a.N; f.stride = a.stride; f.Jr = 0; f.Jc = 1; f.Jg = 0;
+    f.coeffs = g.coeffs; f.coeff_stride = a.coeff_stride;
+    f.t = g.t; f.diag = g.diag; f.y = g.y;
+    f.out_logdet = g.out_logdet; f.out_quad = g.out_quad; f.out_half = g.out_val; f.status = g.status;
+    f.ckpt = region; f.flags = flags;
+    bool fwd = false;
+    e = launch_loglik_lockstep_ckpt(f, stream, &fwd);
+    if (e != cudaSuccess) return e;
+    if (!fwd) return off0 == 0 ? cudaSuccess : cudaErrorInvalidValue;   // (cannot differ between pieces)
+    const long long warps = (nb + kWarp - 1) / kWarp;
+    kern<<<(unsigned)((warps + kRevWarps - 1) / kRevWarps), kRevThreads, kRevSmem, stream>>>(g, region, mt, md, my);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    // flagged series again, by the first-generation kernel (its warps leave at once where nothing is flagged)
+    GradArgs r = g;
+    r.only = flags; r.scratch = region;
+    bool redo = false;
+    e = launch_grad_lockstep_v1(r, stream, &redo);
+    if (e != cudaSuccess) return e;
+    if (!redo) return cudaErrorInvalidValue;
+    if (launches) *launches += 3;
+  }
+  *used = true;
+  return cudaSuccess;
+}
+
+}  // namespace cel
