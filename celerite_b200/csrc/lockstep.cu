@@ -380,16 +380,19 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
 #pragma unroll
     for (int c = 0; c < T / 2; ++c) offc[c] = (c ^ swz) << 4;
     double tlast = __ldg(tp);
-    double Dlast = 1.0;
-    // checkpoint s = the state before step kGrad2Seg * s: S, D W and D of the step before, f, x, t
+    // checkpoint s = the state before step kGrad2Seg * s, in the form the next step consumes it:
+    // S + D W W^T (cholesky.h:154-160 before the scaling by phi phi^T), f + W x (cholesky.h:350-354), t
     const int nckpt = (N + kGrad2Seg - 1) / kGrad2Seg;
     double* ckp = CKPT ? a.ckpt + ((size_t)(b0 / kWarp) * nckpt * kGrad2Ckpt) * kWarp + lane : nullptr;
     auto checkpoint = [&](int s) {
       if constexpr (CKPT && J == 2) {
         double* q = ckp + (size_t)s * (kGrad2Ckpt * kWarp);
-        q[0] = st.S[0]; q[kWarp] = st.S[1]; q[2 * kWarp] = st.S[2];
-        q[3 * kWarp] = st.DW[0]; q[4 * kWarp] = st.DW[1]; q[5 * kWarp] = Dlast;
-        q[6 * kWarp] = st.f[0]; q[7 * kWarp] = st.f[1]; q[8 * kWarp] = st.xprev; q[9 * kWarp] = tlast;
+        q[0] = fma(st.DW[0], st.Wp[0], st.S[0]);
+        q[kWarp] = fma(st.DW[1], st.Wp[0], st.S[1]);
+        q[2 * kWarp] = fma(st.DW[1], st.Wp[1], st.S[2]);
+        q[3 * kWarp] = fma(st.Wp[0], st.xprev, st.f[0]);
+        q[4 * kWarp] = fma(st.Wp[1], st.xprev, st.f[1]);
+        q[5 * kWarp] = tlast;
       }
     };
 
@@ -415,7 +418,6 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
       const int hp = __double2hiint(P);
       e32 += (hp >> 20) - 1023;
       mant *= __hiloint2double((hp & 0x000fffff) | 0x3ff00000, __double2loint(P));
-      if (CKPT) Dlast = Dg[1];
     };
     auto renorm = [&]() {
       const int hi = __double2hiint(mant);

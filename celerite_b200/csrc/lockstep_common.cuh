@@ -234,7 +234,7 @@ inline EncodeTiledFn encode_fn() {
 }
 
 // 2-D view [B rows][rowlen doubles] of a batch, rows `stride` doubles apart, fetched/stored in
-// boxes of [32 rows x box_inner doubles] (box_inner 8 -> 64-byte swizzle, 16 -> 128-byte swizzle)
+// boxes of [32 rows x box_inner doubles] (box_inner 4 -> 32-byte swizzle, 8 -> 64-byte, 16 -> 128-byte)
 inline bool make_rows_map(CUtensorMap* map, const double* base, long long B, long long rowlen, long long stride,
                           int box_inner, bool swizzle = true) {
   EncodeTiledFn fn = encode_fn();
@@ -248,7 +248,8 @@ inline bool make_rows_map(CUtensorMap* map, const double* base, long long B, lon
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double*>(base), dims, strides, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE,
                   !swizzle ? CU_TENSOR_MAP_SWIZZLE_NONE
-                           : (box_inner == 16 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B),
+                           : (box_inner == 16 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                              : (box_inner == 4 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_64B)),
                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS;
 }

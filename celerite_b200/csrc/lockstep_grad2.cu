@@ -91,46 +91,55 @@ k_grad2_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
   issue(nseg - 1);
 
   const double* ck = ckpt_base + ((size_t)wg * nseg * kGrad2Ckpt) * kWarp + lane;
+  // 32-byte swizzle of the boxes: the 16-byte half of a row is exchanged where address bit 7 is set
   const unsigned char* lrow = wtile + lane * (kSeg * 8);
+  const int h0 = ((lane >> 2) & 1) << 4, h1 = h0 ^ 16;
 
   // adjoint state: Pb = adjoint of P_{n+1} (symmetric), g = adjoint of f_{n+1} scaled back by phi
   double Pb00 = 0.0, Pb01 = 0.0, Pb11 = 0.0, g0 = 0.0, g1 = 0.0;
   double ga = 0.0, gb = 0.0, gc = 0.0, gd = 0.0, sumA = 0.0;
   unsigned phase = 0;
 
-  auto segment = [&](const int s, auto guard, const int nv) {
-    constexpr bool GUARD = decltype(guard)::value;
-    // ---- state before step kSeg*s (zero before the first step: cholesky.h:104-124 as one more step) ----
-    double S00 = 0.0, S01 = 0.0, S11 = 0.0, DW0 = 0.0, DW1 = 0.0, Dp = 1.0, f0 = 0.0, f1 = 0.0, xp = 0.0, tprev = 0.0;
+  // state before the segment that is processed next, in the form of the checkpoints (lockstep.cu):
+  // Sp = S + D W W^T, fp = f + W x of the step before, and its time; all zero before step 0
+  double Sp00 = 0.0, Sp01 = 0.0, Sp11 = 0.0, fp0 = 0.0, fp1 = 0.0, tprev = 0.0;
+  auto load_state = [&](int s) {
     if (s > 0) {
       const double* q = ck + (size_t)s * (kGrad2Ckpt * kWarp);
-      S00 = q[0]; S01 = q[kWarp]; S11 = q[2 * kWarp];
-      DW0 = q[3 * kWarp]; DW1 = q[4 * kWarp]; Dp = q[5 * kWarp];
-      f0 = q[6 * kWarp]; f1 = q[7 * kWarp]; xp = q[8 * kWarp]; tprev = q[9 * kWarp];
+      Sp00 = q[0]; Sp01 = q[kWarp]; Sp11 = q[2 * kWarp];
+      fp0 = q[3 * kWarp]; fp1 = q[4 * kWarp]; tprev = q[5 * kWarp];
+    } else {
+      Sp00 = Sp01 = Sp11 = fp0 = fp1 = 0.0;
     }
-    // ---- this segment's inputs into registers, then the box of the next one may land in the slot ----
+  };
+  load_state(nseg - 1);
+
+  auto segment = [&](const int s, auto guard, const int nv) {
+    constexpr bool GUARD = decltype(guard)::value;
     mbar_wait(bar, phase);
     phase ^= 1u;
-    double rt[kSeg], rd[kSeg], ry[kSeg];
-#pragma unroll
-    for (int c = 0; c < kSeg / 2; ++c) {
-      const double2 v0 = *reinterpret_cast<const double2*>(lrow + 16 * c);
-      const double2 v1 = *reinterpret_cast<const double2*>(lrow + kTileB + 16 * c);
-      const double2 v2 = *reinterpret_cast<const double2*>(lrow + 2 * kTileB + 16 * c);
-      rt[2 * c] = v0.x; rt[2 * c + 1] = v0.y;
-      rd[2 * c] = v1.x; rd[2 * c + 1] = v1.y;
-      ry[2 * c] = v2.x; ry[2 * c + 1] = v2.y;
+    double rt[kSeg];
+    {
+      const double2 v0 = *reinterpret_cast<const double2*>(lrow + h0);
+      const double2 v1 = *reinterpret_cast<const double2*>(lrow + h1);
+      rt[0] = v0.x; rt[1] = v0.y; rt[2] = v1.x; rt[3] = v1.y;
     }
-    __syncwarp();
-    if (s > 0) issue(s - 1);
     if (s == 0) tprev = rt[0];
     const double t_in = tprev;
-    const double rp = fast_rcp_cubic(Dp);
-    double W0 = DW0 * rp, W1 = DW1 * rp;
 
     // ---- recompute the segment, taping what the adjoint needs ----
+    double dd[2], yy[2];
 #pragma unroll
     for (int i = 0; i < kSeg; ++i) {
+      if ((i & 1) == 0) {       // diag and y of two steps at a time; after the second pair the slot is free
+        const double2 v1 = *reinterpret_cast<const double2*>(lrow + kTileB + (i == 0 ? h0 : h1));
+        const double2 v2 = *reinterpret_cast<const double2*>(lrow + 2 * kTileB + (i == 0 ? h0 : h1));
+        dd[0] = v1.x; dd[1] = v1.y; yy[0] = v2.x; yy[1] = v2.y;
+        if (i == kSeg - 2) {
+          __syncwarp();
+          if (s > 0) issue(s - 1);
+        }
+      }
       if (!GUARD || i < nv) {
         const double tn = rt[i];
         const double dx = tn - tprev;
@@ -139,18 +148,17 @@ k_grad2_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
         const double e = cel_exp_tab(ncc * dx, exp_tab);
         const double u0 = fma(ca, cd, cb * sd), u1 = fma(ca, sd, -(cb * cd));
         const double e2 = e * e;
-        S00 = e2 * fma(DW0, W0, S00);
-        S01 = e2 * fma(DW1, W0, S01);
-        S11 = e2 * fma(DW1, W1, S11);
-        f0 = e * fma(W0, xp, f0);
-        f1 = e * fma(W1, xp, f1);
-        const double x = fma(-u1, f1, fma(-u0, f0, ry[i]));
+        const double S00 = e2 * Sp00, S01 = e2 * Sp01, S11 = e2 * Sp11;   // cholesky.h:154-160
+        const double f0 = e * fp0, f1 = e * fp1;                          // cholesky.h:350-354
+        const double x = fma(-u1, f1, fma(-u0, f0, yy[i & 1]));
         const double su0 = fma(S01, u1, S00 * u0), su1 = fma(S11, u1, S01 * u0);
-        const double D = fma(-u1, su1, fma(-u0, su0, rd[i] + aconst));
-        DW0 = cd - su0; DW1 = sd - su1;
+        const double D = fma(-u1, su1, fma(-u0, su0, dd[i & 1] + aconst));
+        const double DW0 = cd - su0, DW1 = sd - su1;
         const double r = fast_rcp_cubic(D);
-        W0 = DW0 * r; W1 = DW1 * r;
-        xp = x; tprev = tn;
+        const double W0 = DW0 * r, W1 = DW1 * r;
+        Sp00 = fma(DW0, W0, S00); Sp01 = fma(DW1, W0, S01); Sp11 = fma(DW1, W1, S11);
+        fp0 = fma(W0, x, f0); fp1 = fma(W1, x, f1);
+        tprev = tn;
         double* q = tape + i * (kRows * kWarp);
         q[0] = S00; q[kWarp] = S01; q[2 * kWarp] = S11;
         q[3 * kWarp] = W0; q[4 * kWarp] = W1;
@@ -159,6 +167,9 @@ k_grad2_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
         q[9 * kWarp] = e; q[10 * kWarp] = cd; q[11 * kWarp] = sd;
       }
     }
+    // the forward state is dead now: fetch that of the segment below while the adjoint runs
+    load_state(s - 1);
+
     // ---- adjoint of the segment, last step first ----
 #pragma unroll
     for (int i = kSeg - 1; i >= 0; --i) {
@@ -269,8 +280,8 @@ cudaError_t launch_grad2(const GradArgs& a, cudaStream_t stream, bool* used, int
     g.out_quad = a.out_quad ? a.out_quad + off0 : nullptr;
     g.status = a.status ? a.status + off0 : nullptr;
     alignas(64) CUtensorMap mt, md, my;
-    if (!(make_rows_map(&mt, g.t, nb, a.N, a.stride, kSeg, false) && make_rows_map(&md, g.diag, nb, a.N, a.stride, kSeg, false) &&
-          make_rows_map(&my, g.y, nb, a.N, a.stride, kSeg, false)))
+    if (!(make_rows_map(&mt, g.t, nb, a.N, a.stride, kSeg) && make_rows_map(&md, g.diag, nb, a.N, a.stride, kSeg) &&
+          make_rows_map(&my, g.y, nb, a.N, a.stride, kSeg)))
       return off0 == 0 ? cudaSuccess : cudaErrorInvalidValue;
     BatchArgs f{};
     f.B = nb; f.N = a.N; f.stride = a.stride; f.Jr = 0; f.Jc = 1; f.Jg = 0;
