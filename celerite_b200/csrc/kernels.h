@@ -69,7 +69,7 @@ struct BatchArgs {
   const int* seg;          // NULL for batches of whole series
   double* seg_edge;        // [B][J+1]: W and D of the last warm-up step, for the consistency check
   // Forward half of the two-kernel gradient (lockstep_grad2.cu; launch_loglik_lockstep_ckpt only):
-  // the recursion state before every 4th step, [warp of 32 series][segment][6][32] doubles, and per
+  // the recursion state before every 4th step, [warp of 32 series][segment][5][32] doubles, and per
   // series whether it left the fast path (then its outputs are not final: the caller re-does it)
   double* ckpt;
   int* flags;
@@ -149,7 +149,7 @@ cudaError_t launch_grad_lockstep(const GradArgs& a, cudaStream_t stream, bool* u
 // J = 2 (one complex term): forward sweep of the fused log-likelihood kernel that also leaves checkpoints
 // (lockstep.cu), and the reverse sweep over them (lockstep_grad2.cu)
 constexpr int kGrad2Seg = 4;      // steps between checkpoints
-constexpr int kGrad2Ckpt = 6;     // doubles per checkpoint: (S + D W W^T) 00 01 11, (f + W x) 0 1, t
+constexpr int kGrad2Ckpt = 5;     // doubles per checkpoint: (S + D W W^T) 00 01 11, (f + W x) 0 1
 cudaError_t launch_loglik_lockstep_ckpt(const BatchArgs& a, cudaStream_t stream, bool* used);
 size_t grad2_scratch_doubles(long long B, int N, int seg_v1);
 size_t grad_lockstep_v1_scratch_doubles(long long B, int N, int Jc, int seg);

@@ -381,7 +381,7 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
     for (int c = 0; c < T / 2; ++c) offc[c] = (c ^ swz) << 4;
     double tlast = __ldg(tp);
     // checkpoint s = the state before step kGrad2Seg * s, in the form the next step consumes it:
-    // S + D W W^T (cholesky.h:154-160 before the scaling by phi phi^T), f + W x (cholesky.h:350-354), t
+    // S + D W W^T (cholesky.h:154-160 before the scaling by phi phi^T), f + W x (cholesky.h:350-354)
     const int nckpt = (N + kGrad2Seg - 1) / kGrad2Seg;
     double* ckp = CKPT ? a.ckpt + ((size_t)(b0 / kWarp) * nckpt * kGrad2Ckpt) * kWarp + lane : nullptr;
     auto checkpoint = [&](int s) {
@@ -392,7 +392,6 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
         q[2 * kWarp] = fma(st.DW[1], st.Wp[1], st.S[2]);
         q[3 * kWarp] = fma(st.Wp[0], st.xprev, st.f[0]);
         q[4 * kWarp] = fma(st.Wp[1], st.xprev, st.f[1]);
-        q[5 * kWarp] = tlast;
       }
     };
 

@@ -42,19 +42,22 @@ constexpr int kRevThreads = kRevWarps * kWarp;
 constexpr int kTileB = kWarp * kSeg * 8;                       // one [32 x 4] box: 1 KB
 constexpr int kWarpBytes = 3 * kTileB + kRows * kSeg * kWarp * 8;   // 3 KB of boxes + 12 KB of tape
 constexpr int kBarBytes = 128;                                 // 14 mbarriers, padded
-constexpr size_t kRevSmem = (size_t)kRevWarps * kWarpBytes + kBarBytes + kTrigTabN * 16 + kExpTabN * 8 + 1024;
+constexpr int kPrevB = kWarp * 16;                             // one [32 x 2] box of t: the two points before a segment
+constexpr size_t kRevSmem = (size_t)kRevWarps * (kWarpBytes + kPrevB) + kBarBytes + kTrigTabN * 16 + kExpTabN * 8 + 1024;
 static_assert(kWarpBytes % 1024 == 0 && kRevWarps * 8 <= kBarBytes, "shared-memory layout");
 
 __global__ void __maxnreg__(128)
 k_grad2_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_constant__ CUtensorMap tm_t,
-                const __grid_constant__ CUtensorMap tm_d, const __grid_constant__ CUtensorMap tm_y) {
+                const __grid_constant__ CUtensorMap tm_d, const __grid_constant__ CUtensorMap tm_y,
+                const __grid_constant__ CUtensorMap tm_p) {
   extern __shared__ unsigned char smem_dyn[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   unsigned char* smem_al = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
   unsigned char* wtile = smem_al + (size_t)warp * kWarpBytes;
   double* tape = reinterpret_cast<double*>(wtile + 3 * kTileB) + lane;
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem_al + (size_t)kRevWarps * kWarpBytes) + warp;
-  double2* trig_tab = reinterpret_cast<double2*>(smem_al + (size_t)kRevWarps * kWarpBytes + kBarBytes);
+  unsigned char* wprev = smem_al + (size_t)kRevWarps * kWarpBytes + kBarBytes + warp * kPrevB;
+  double2* trig_tab = reinterpret_cast<double2*>(smem_al + (size_t)kRevWarps * (kWarpBytes + kPrevB) + kBarBytes);
   double* exp_tab = reinterpret_cast<double*>(trig_tab + kTrigTabN);
   cel_fill_tables(trig_tab, exp_tab, threadIdx.x, kRevThreads);
   __syncthreads();
@@ -82,7 +85,8 @@ k_grad2_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
   auto issue = [&](int s) {
     if (lane == 0) {
       fence_async_smem();
-      mbar_arrive_expect_tx(bar, 3u * kTileB);
+      mbar_arrive_expect_tx(bar, 3u * kTileB + kPrevB);
+      tma_load_2d(wprev, &tm_p, s * kSeg - 2, (int)b0, bar);   // (zero-filled before the series begins)
       tma_load_2d(wtile, &tm_t, s * kSeg, (int)b0, bar);
       tma_load_2d(wtile + kTileB, &tm_d, s * kSeg, (int)b0, bar);
       tma_load_2d(wtile + 2 * kTileB, &tm_y, s * kSeg, (int)b0, bar);
@@ -102,12 +106,12 @@ k_grad2_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
 
   // state before the segment that is processed next, in the form of the checkpoints (lockstep.cu):
   // Sp = S + D W W^T, fp = f + W x of the step before, and its time; all zero before step 0
-  double Sp00 = 0.0, Sp01 = 0.0, Sp11 = 0.0, fp0 = 0.0, fp1 = 0.0, tprev = 0.0;
+  double Sp00 = 0.0, Sp01 = 0.0, Sp11 = 0.0, fp0 = 0.0, fp1 = 0.0;
   auto load_state = [&](int s) {
     if (s > 0) {
       const double* q = ck + (size_t)s * (kGrad2Ckpt * kWarp);
       Sp00 = q[0]; Sp01 = q[kWarp]; Sp11 = q[2 * kWarp];
-      fp0 = q[3 * kWarp]; fp1 = q[4 * kWarp]; tprev = q[5 * kWarp];
+      fp0 = q[3 * kWarp]; fp1 = q[4 * kWarp];
     } else {
       Sp00 = Sp01 = Sp11 = fp0 = fp1 = 0.0;
     }
@@ -124,7 +128,8 @@ k_grad2_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
       const double2 v1 = *reinterpret_cast<const double2*>(lrow + h1);
       rt[0] = v0.x; rt[1] = v0.y; rt[2] = v1.x; rt[3] = v1.y;
     }
-    if (s == 0) tprev = rt[0];
+    // time of the step before the segment (dt = 0 at the very first step: cholesky.h:104-124 as one more step)
+    double tprev = s == 0 ? rt[0] : *reinterpret_cast<const double*>(wprev + lane * 16 + 8);
     const double t_in = tprev;
 
     // ---- recompute the segment, taping what the adjoint needs ----
@@ -279,9 +284,9 @@ cudaError_t launch_grad2(const GradArgs& a, cudaStream_t stream, bool* used, int
     g.out_logdet = a.out_logdet ? a.out_logdet + off0 : nullptr;
     g.out_quad = a.out_quad ? a.out_quad + off0 : nullptr;
     g.status = a.status ? a.status + off0 : nullptr;
-    alignas(64) CUtensorMap mt, md, my;
+    alignas(64) CUtensorMap mt, md, my, mp;
     if (!(make_rows_map(&mt, g.t, nb, a.N, a.stride, kSeg) && make_rows_map(&md, g.diag, nb, a.N, a.stride, kSeg) &&
-          make_rows_map(&my, g.y, nb, a.N, a.stride, kSeg)))
+          make_rows_map(&my, g.y, nb, a.N, a.stride, kSeg) && make_rows_map(&mp, g.t, nb, a.N, a.stride, 2, false)))
       return off0 == 0 ? cudaSuccess : cudaErrorInvalidValue;
     BatchArgs f{};
     f.B = nb; f.N = a.N; f.stride = a.stride; f.Jr = 0; f.Jc = 1; f.Jg = 0;
@@ -294,7 +299,7 @@ cudaError_t launch_grad2(const GradArgs& a, cudaStream_t stream, bool* used, int
     if (e != cudaSuccess) return e;
     if (!fwd) return off0 == 0 ? cudaSuccess : cudaErrorInvalidValue;   // (cannot differ between pieces)
     const long long warps = (nb + kWarp - 1) / kWarp;
-    kern<<<(unsigned)((warps + kRevWarps - 1) / kRevWarps), kRevThreads, kRevSmem, stream>>>(g, region, mt, md, my);
+    kern<<<(unsigned)((warps + kRevWarps - 1) / kRevWarps), kRevThreads, kRevSmem, stream>>>(g, region, mt, md, my, mp);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     // flagged series again, by the first-generation kernel (its warps leave at once where nothing is flagged)
