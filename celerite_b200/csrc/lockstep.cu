@@ -386,6 +386,7 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
     double* ckp = CKPT ? a.ckpt + ((size_t)(b0 / kWarp) * nckpt * kGrad2Ckpt) * kWarp + lane : nullptr;
     auto checkpoint = [&](int s) {
       if constexpr (CKPT && J == 2) {
+        if (b0 >= a.B) return;     // a warp of idle lanes only (the last CTA): it owns no checkpoint rows
         double* q = ckp + (size_t)s * (kGrad2Ckpt * kWarp);
         q[0] = fma(st.DW[0], st.Wp[0], st.S[0]);
         q[kWarp] = fma(st.DW[1], st.Wp[0], st.S[1]);
