@@ -106,6 +106,52 @@ void plan_grad_spans(int J, int Jr, const double* c_real, int Jc, const double* 
   if (work > 4LL * N) span.clear();
 }
 
+// spans for the exact time-parallel adjoint (grad.cu, scan modes): [begin, first owned, end of owned, end of
+// owned].  Only the forward state needs a warm-up (f forgets like prod(phi): ln(1/kSegmentTol) / c_min); with
+// `halo` false the spans are cut at multiples of `seg` and carry none (the forward sweep is serial then).
+void plan_scan_spans(int J, int Jr, const double* c_real, int Jc, const double* c_comp, int N, const double* x,
+                     bool halo, int seg, std::vector<int>& span, int* span_len) {
+  span.clear();
+  int L = 1;
+  while (L < J && L < 32) L <<= 1;
+  const int slots = cel::sm_count() * 8 * (32 / L);
+  long long len = (N + slots - 1) / slots;
+  if (len < 1024) len = 1024;
+  double reach = 0.0;
+  if (halo) {
+    double c_min = INFINITY;
+    for (int j = 0; j < Jr; ++j) c_min = std::fmin(c_min, c_real[j]);
+    for (int j = 0; j < Jc; ++j) c_min = std::fmin(c_min, c_comp[j]);
+    if (!(c_min > 0.0) || !std::isfinite(c_min)) return;
+    reach = std::log(1.0 / kSegmentTol) / c_min;
+    if (const char* e = getenv("CEL_SEGMENT_HALO_SCALE")) reach *= atof(e);
+    const double dt = (x[N - 1] - x[0]) / (double)(N - 1);
+    if (!(dt > 0.0)) return;
+    // only the forward sweep pays for the warm-up (the two adjoint passes do not), and a span's latency is
+    // what bounds a series that cannot fill the GPU: owned ranges down to a quarter of the halo
+    if ((double)len < 0.25 * reach / dt) len = (long long)(0.25 * reach / dt);
+    len = (len + 15) / 16 * 16;
+  } else {
+    len = (len + seg - 1) / seg * seg;
+  }
+  const int K = (int)((N + len - 1) / len);
+  if (halo && K < 8) return;
+  span.reserve(4 * (size_t)K);
+  long long work = 0;
+  for (int c = 0; c < K; ++c) {
+    const int own0 = (int)(c * len), own1 = (int)std::min<long long>(N, own0 + len);
+    int begin = own0;
+    if (halo && own0 > 0) {
+      begin = (int)(std::lower_bound(x, x + own0, x[own0] - reach) - x);
+      if (begin > 0) --begin;
+    }
+    span.push_back(begin); span.push_back(own0); span.push_back(own1); span.push_back(own1);
+    work += own1 - begin;
+  }
+  if (halo && work > 6LL * N) span.clear();
+  *span_len = (int)len;
+}
+
 int pack_coeffs(cel_solver* s, double jitter, int Jr, const double* a_real, const double* c_real, int Jc,
                 const double* a_comp, const double* b_comp, const double* c_comp, const double* d_comp,
                 std::vector<double>& row) {
@@ -532,7 +578,75 @@ int cel_grad_log_likelihood(cel_solver* s, double jitter, int Jr, const double* 
   // Long series without general rows: time spans side by side (grad.cu, SPAN), each behind a warm-up
   // halo and in front of a cool-down halo; neighbouring spans are compared at their common edge
   // and the series is redone serially if they disagree.
-  if (Jg == 0 && !A && N >= kSegmentedMinN && J <= cel::kCoopMaxJ) {
+  const bool spans_v1 = getenv("CEL_GRAD_SPANS_V1") != nullptr;   // A/B knob: warm-up + cool-down halos
+  if (!spans_v1 && Jg == 0 && !A && N >= kSegmentedMinN && J <= cel::kCoopMaxJ) {
+    // The exact time-parallel adjoint (grad.cu, scan modes).  Attempt 0: the spans' forward sweeps run side
+    // by side behind warm-up halos, checked at the common edges afterwards (W, D and f of the same step, two
+    // histories).  Attempt 1, when the factorisation does not forget fast enough for that: ONE forward
+    // sweep over the series leaves the checkpoints.  Either way the adjoint -- the linear recursions -- is
+    // an exact two-pass scan over the spans: probe, fold, final.
+    const bool no_halo = getenv("CEL_GRAD_SCAN_SERIAL_FORWARD") != nullptr;   // testing knob: attempt 1 only
+    for (int attempt = no_halo ? 1 : 0; attempt < 2; ++attempt) {
+      const bool halo = attempt == 0;
+      std::vector<int> span;
+      int len = 0;
+      int sseg = cel::grad_tuned_segment(cel::sm_count() * 8, std::max(1024, N / (cel::sm_count() * 8)), J, false);
+      plan_scan_spans(J, Jr, c_real, Jc, c_comp, N, x, halo, sseg, span, &len);
+      if (span.empty()) continue;
+      const int K = (int)(span.size() / 4);
+      int maxlen = 0;
+      for (int c = 0; c < K; ++c) maxlen = std::max(maxlen, span[4 * c + 3] - span[4 * c]);
+      if (halo) sseg = cel::grad_tuned_segment(K, maxlen, J, false);
+      if (const char* e = getenv("CEL_GRAD_SCAN_SEG")) { const int v = atoi(e); if (halo && v >= 16 && v % 16 == 0) sseg = v; }   // tuning knob
+      if (!halo) maxlen = len;                                   // every span owns len / sseg checkpoint slots
+      const size_t sscr = cel::grad_scratch_doubles(K, maxlen, J, sseg);
+      const size_t nadj = cel::grad_scan_adj_doubles(K, J);
+      const int ER = 2 * J + 1;
+      // scratch2: [K] val | [K][P] grad | [K][4][ER] edges | [3+P] result | adj | ints: [4K] span, [K] status
+      const size_t nd = (size_t)K * (1 + P + 4 * ER) + 3 + P + nadj;
+      CEL_CUDA_TRY(s, s->scratch0.reserve(dbytes(sscr)));
+      CEL_CUDA_TRY(s, s->scratch2.reserve(dbytes(nd) + sizeof(int) * (size_t)5 * K));
+      double* d_val = s->scratch2.d();
+      double* d_grad = d_val + K;
+      double* d_edge = d_grad + (size_t)K * P;
+      double* d_res = d_edge + (size_t)K * 4 * ER;
+      double* d_adj = d_res + 3 + P;
+      int* d_span = reinterpret_cast<int*>(d_adj + nadj);
+      CEL_CUDA_TRY(s, cudaMemsetAsync(d_val, 0, dbytes((size_t)K * (1 + P + 4 * ER)), st));
+      CEL_CUDA_TRY(s, cudaMemsetAsync(d_span + 4 * K, 0, sizeof(int) * (size_t)K, st));
+      CEL_CUDA_TRY(s, cudaMemcpyAsync(d_span, span.data(), sizeof(int) * span.size(), cudaMemcpyHostToDevice, st));
+      cel::GradArgs sa{};
+      sa.B = K; sa.N = N; sa.stride = 0; sa.Jr = Jr; sa.Jc = Jc; sa.Jg = 0;
+      sa.coeffs = dc; sa.coeff_stride = 0;
+      sa.t = dx; sa.diag = dd; sa.y = dy;
+      sa.out_val = d_val; sa.out_grad = d_grad; sa.status = d_span + 4 * K;
+      sa.scratch = s->scratch0.d(); sa.seg = sseg;
+      sa.span = d_span; sa.span_nseg_max = (maxlen + sseg - 1) / sseg; sa.span_edge = d_edge;
+      sa.adj = d_adj; sa.have_ckpt = halo ? 0 : 1;
+      if (!halo) {                                         // the forward sweep, serial: value, status, checkpoints
+        cel::GradArgs fa = sa;
+        fa.B = 1; fa.stride = N; fa.coeff_stride = P; fa.span = nullptr; fa.span_edge = nullptr; fa.adj = nullptr;
+        CEL_CUDA_TRY(s, cel::launch_grad_scan(fa, 3, st));
+        s->launches += 1;
+      }
+      CEL_CUDA_TRY(s, cel::launch_grad_scan(sa, 1, st));
+      CEL_CUDA_TRY(s, cel::launch_grad_scan_fold(K, J, d_adj, st));
+      CEL_CUDA_TRY(s, cel::launch_grad_scan(sa, 2, st));
+      CEL_CUDA_TRY(s, cel::launch_grad_span_finish(sa, d_res, st));
+      s->launches += 4;
+      if (s->pinned_cap < dbytes((size_t)P + 3)) CEL_FAIL(s, CEL_UNSUPPORTED, "too many coefficients");
+      CEL_CUDA_TRY(s, cudaMemcpyAsync(res, d_res, dbytes((size_t)P + 3), cudaMemcpyDeviceToHost, st));
+      CEL_CUDA_TRY(s, cudaStreamSynchronize(st));
+      // (a negative pivot behind a warm-up halo is only believed when the spans agree at their edges)
+      if (res[1] <= kSpanMismatchTol || !halo) {
+        if (res[2] != 0.0) CEL_FAIL(s, CEL_NOT_POSITIVE_DEFINITE, "failed to factorize or solve matrix");
+        *val = res[0];
+        for (int i = 0; i < P; ++i) grad[i] = res[3 + i];
+        return CEL_OK;
+      }
+    }
+  }
+  if (spans_v1 && Jg == 0 && !A && N >= kSegmentedMinN && J <= cel::kCoopMaxJ) {
     std::vector<int> span;
     plan_grad_spans(J, Jr, c_real, Jc, c_comp, N, x, span);
     if (!span.empty()) {

@@ -30,6 +30,8 @@
 #include "fastmath.cuh"
 #include "kernels.h"
 
+#pragma nv_diag_suppress 128   // "loop is not reachable": the forward-only instantiation (MODE 3) returns before the adjoint
+
 namespace cel {
 namespace {
 
@@ -54,7 +56,10 @@ struct GradCfg {
   static constexpr int kP = RD * JJ;
   static constexpr int kCoef = 4 * JP + 2;
   static constexpr int kR = 6 * JP;
-  static constexpr int kGroup = kIn + kGen + kX + kP + kCoef + kR;
+  static constexpr int kM = JP * JP;                 // transfer matrix of a span (scan modes only)
+  static constexpr int kGroup = kIn + kGen + kX + kP + kCoef + kR + kM;
+  // per span, exchanged between the scan passes (GradArgs::adj): M | P0 | g0 | P_in | g_in
+  static constexpr int kAdj = 3 * JP * JP + 2 * JP;
   static constexpr int kTab = 2 * kTrigTabN + kExpTabN;       // tables of the table-driven exp / sincos
   static constexpr int kTabOff = (G * kGroup + 1) & ~1;        // 16-byte aligned
   static constexpr size_t smem = ((size_t)kTabOff + kTab) * sizeof(double);
@@ -72,7 +77,22 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // [begin, end) forward from a cold start and the adjoint from `end` down to its first owned step;
 // only owned steps contribute to the value and the gradient sums.  Spans differ in length, so
 // every warp-level primitive names the group's own lanes.
-template <int JP, bool SPAN = false>
+//
+// MODE (the EXACT time-parallel adjoint; tools/proto_adjoint_scan.py states it in numpy): the adjoint
+// recursion is affine in its carries (Pbar, gbar) and its homogeneous part is a congruence,
+//     gbar_out = M gbar_in + g0,   Pbar_out = M Pbar_in M^T - 1/2 ((M gbar_in) g0^T + g0 (M gbar_in)^T) + P0,
+// with M = prod_n Phi_n (I - u_n W_n^T) over the steps of a span (the J x J map of the backward solve) and
+// (g0, P0) the carries a sweep leaves that entered the span with zero carries.  So:
+//   MODE 1 (probe)  forward sweep of the span (unless its checkpoints already exist, a.have_ckpt), then the
+//                   adjoint from its last owned step down with ZERO carries, forming M on the way; leaves
+//                   M, P0, g0 in a.adj.  No gradient sums.
+//   k_adj_fold      folds the spans from the last to the first: every span's true incoming carries.
+//   MODE 2 (final)  no forward sweep (the checkpoints of MODE 1 are still in the scratch): the adjoint again,
+//                   from the true incoming carries, with the gradient sums.
+//   MODE 3 (forward) SPAN = false, one series: the forward sweep only, its checkpoints stored where the spans
+//                   of MODE 1/2 (aligned to the segment length, no warm-up) expect them -- the serial
+//                   fall-back when the factorisation does not forget fast enough for warm-up halos.
+template <int JP, bool SPAN = false, int MODE = 0>
 __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   using C = GradCfg<JP>;
   constexpr int L = C::L, G = C::G, T = C::T, JJ = C::JJ, E = C::E, BLK = C::BLK;
@@ -101,6 +121,7 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   double* p_s = x_s + 4 * JP;            // [RD][JJ]
   double* cf_s = p_s + C::kP;
   double* r_s = cf_s + C::kCoef;         // [6][JP]
+  double* m_s = r_s + C::kR;             // [JP][JP] M, entry (j, c) at j*JP + c (lane c owns column c)
 
   const int N = a.N, Jr = a.Jr, Jc = a.Jc, Jg = a.Jg, J = Jr + 2 * Jc + Jg, P = 1 + 2 * Jr + 4 * Jc;
   // steps [n_lo, n_hi) are swept; [own0, own1) contribute (whole series: everything)
@@ -117,6 +138,14 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   // idle groups shadow the last series but must not share its scratch: give them their own slot
   double* ckpt = a.scratch + (size_t)((long long)blockIdx.x * G + g) * ((size_t)(nseg_slot + Cseg) * E);
   double* tape = ckpt + (size_t)nseg_slot * E;
+  // MODE 3: segment s of the series is segment s % spg of span s / spg (spans of spg segments, no warm-up)
+  auto ckpt_rec = [&](int s) -> double* {
+    if (MODE == 3) {
+      const int spg = a.span_nseg_max;
+      return a.scratch + (size_t)(s / spg) * ((size_t)(spg + Cseg) * E) + (size_t)(s % spg) * E;
+    }
+    return ckpt + (size_t)s * E;
+  };
   // span edges kept for the consistency check: 4 records of 2J+1 doubles (see launch_grad_spans)
   const int ER = 2 * J + 1;
   double* edge = (SPAN && a.span_edge) ? a.span_edge + (size_t)bb * 4 * ER : nullptr;
@@ -361,6 +390,9 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
           double* er = edge + (n == own0 - 1 ? 0 : 1) * ER;
           if (k < J) er[k] = dw * r;
           if (k == 0) er[J] = Dn;
+          // scan modes: the adjoint is exact, so records 2 / 3 carry the forward vector f instead of the
+          // adjoint carries (k_grad_span_finish compares a span's record 2 with its neighbour's record 3)
+          if (MODE == 1 && k < J) edge[(n == own0 - 1 ? 3 : 2) * ER + k] = f_own;
         }
       }
       dw_own = dw;
@@ -378,17 +410,32 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   };
 
   // =========================== phase A: forward sweep, checkpoints =============================
-  reset_state();
-  publish_W(n_lo);
-  for (int s = 0; s < nseg; ++s) {
-    const int seg0 = n_lo + s * Cseg, seg1 = min(n_hi, seg0 + Cseg);
-    store_state(ckpt + (size_t)s * E);
-    for (int n0 = seg0; n0 < seg1; n0 += T) {
-      const int nt = min(T, seg1 - n0);
-      const int nx = n0 + T < seg1 ? n0 + T : (seg1 < n_hi ? seg1 : -1);
-      load_tile(n0, nt, nx);
-      forward_tile(n0, nt, false, 0, true);
+  const bool sweep_forward = MODE == 0 || MODE == 3 || (MODE == 1 && !a.have_ckpt);
+  if (sweep_forward) {
+    reset_state();
+    publish_W(n_lo);
+    for (int s = 0; s < nseg; ++s) {
+      const int seg0 = n_lo + s * Cseg, seg1 = min(n_hi, seg0 + Cseg);
+      if (MODE != 3 || active) store_state(ckpt_rec(s));   // (MODE 3: idle groups own no slot)
+      for (int n0 = seg0; n0 < seg1; n0 += T) {
+        const int nt = min(T, seg1 - n0);
+        const int nx = n0 + T < seg1 ? n0 + T : (seg1 < n_hi ? seg1 : -1);
+        load_tile(n0, nt, nx);
+        forward_tile(n0, nt, false, 0, true);
+      }
     }
+  }
+  if (MODE == 3) {
+    if (active && k == 0) {
+      const double nan = __longlong_as_double(0x7ff8000000000000LL);
+      const double logdet = fail ? nan : ld.value();
+      const double q = fail ? nan : quad;
+      if (a.out_val) a.out_val[b] = -0.5 * (q + logdet);
+      if (a.out_logdet) a.out_logdet[b] = logdet;
+      if (a.out_quad) a.out_quad[b] = q;
+      if (a.status) a.status[b] = fail ? 3 : 0;
+    }
+    return;
   }
 
   // =========================== phase B: segments in reverse =====================================
@@ -397,6 +444,18 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   for (int j = 0; j < JP; ++j) Pb[j] = 0.0;
   double gbar = 0.0, PbW = 0.0, sumA = 0.0;
   double R1 = 0.0, R2 = 0.0, R3 = 0.0, R4 = 0.0, R5 = 0.0, R6 = 0.0;
+  double* adj = (MODE == 1 || MODE == 2) ? a.adj + (size_t)bb * C::kAdj : nullptr;
+  bool carries_in = false;
+  if (MODE == 1 && row_ok) {                         // M = I
+    for (int j = 0; j < JP; ++j) m_s[j * JP + kk] = (j == kk) ? 1.0 : 0.0;
+  }
+  if (MODE == 2) {                                   // the span's true incoming carries (k_adj_fold)
+    const double* pin = adj + 2 * JP * JP + JP;
+#pragma unroll
+    for (int j = 0; j < JP; ++j) Pb[j] = row_ok ? pin[kk * JP + j] : 0.0;
+    gbar = row_ok ? pin[JP * JP + kk] : 0.0;
+    carries_in = true;                               // PbW = Pbar W of the first step: formed below
+  }
   // tape scalars are fetched ahead of their use: two steps ahead while registers allow
   constexpr bool DEEP = JP <= 16;
 
@@ -445,6 +504,16 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
     double Wn, fn, Dn, xn, Wm, fm, Dm, xm, Wq = 0.0, fq = 0.0, Dq = 0.0, xq = 0.0;
     load_rec(seg1 - 1, Wn, fn, Dn, xn);
     if (DEEP) load_rec(seg1 - 2, Wm, fm, Dm, xm);       // seg1-2 >= seg0-1
+    if (MODE == 2 && carries_in) {                      // PbW = Pbar_in W_n of the step the adjoint starts at
+      carries_in = false;
+      if (row_ok) r_s[kk] = Wn;
+      __syncwarp(gmask);
+      double acc = 0.0;
+#pragma unroll
+      for (int j = 0; j < JP; ++j) acc = fma(Pb[j], r_s[j], acc);
+      PbW = row_ok ? acc : 0.0;
+      __syncwarp(gmask);
+    }
     for (int n = seg1 - 1; n >= adj_lo; --n) {
       // generators of the tile containing n (tiles are aligned to the segment start)
       const int tn0 = seg0 + ((n - seg0) / T) * T;
@@ -464,9 +533,9 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
       const double vpart = row_ok ? v_s[i * JP + partner] : 0.0;
       const double tn = t_s[1 + i], dxn = tn - t_s[i];
       const double Wk = row_ok ? Wn : 0.0;
-      const bool own = !SPAN || (n >= own0 && n < own1);
-      const double om = own ? 1.0 : 0.0;               // cool-down steps feed the carries only
-      if (SPAN && edge && active && n == own1 - 1 && k < J) {  // adjoint carries entering the last owned step
+      const bool own = MODE != 1 && (!SPAN || (n >= own0 && n < own1));
+      const double om = own ? 1.0 : 0.0;               // cool-down steps (and the probe pass) feed the carries only
+      if (MODE == 0 && SPAN && edge && active && n == own1 - 1 && k < J) {  // adjoint carries entering the last owned step
         edge[2 * ER + k] = gbar; edge[2 * ER + J + k] = PbW;
       }
 
@@ -484,6 +553,7 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
       const int par = n & 1;
       double* xch = x_s + par * 2 * JP;
       if (row_ok) { xch[kk] = w; xch[JP + kk] = Wm; }
+      if (MODE == 1 && row_ok) r_s[kk] = Wk;              // W_n for the transfer matrix
       cp_async_wait<C::RD - 1>();                         // block n: requested RD-1 steps ago
       __syncwarp(gmask);
       if (n > 0) {                                        // step 0 has no generators (cholesky.h:118-124)
@@ -521,14 +591,44 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
         R3 = fma(phibar, -dxn * phk, R3);
         R4 = fma(tn * ubar, vk, R4);
         R5 = fma(tn * ubar, vpart, R5);
+        if (MODE == 1 && row_ok) {                        // M <- Phi_n (I - u_n W_n^T) M, lane k owns column k
+          double dot = 0.0;
+#pragma unroll
+          for (int j = 0; j < JP; ++j) dot = fma(r_s[j], m_s[j * JP + kk], dot);
+#pragma unroll
+          for (int j = 0; j < JP; ++j) m_s[j * JP + kk] = ph[j] * fma(-uu[j], dot, m_s[j * JP + kk]);
+        }
       }
       Wn = Wm; fn = fm; Dn = Dm; xn = xm;
       if (DEEP) { Wm = Wq; fm = fq; Dm = Dq; xm = xq; }
       __syncwarp(gmask);
     }
   }
-  if (SPAN && edge && active && k < J) {               // adjoint carries entering step own0 - 1
+  if (MODE == 0 && SPAN && edge && active && k < J) {  // adjoint carries entering step own0 - 1
     edge[3 * ER + k] = gbar; edge[3 * ER + J + k] = PbW;
+  }
+  if (MODE == 1) {                                     // what the fold needs: M, and the carries left from zero
+    __syncwarp(gmask);
+    if (active) {
+      if (row_ok) {
+#pragma unroll
+        for (int j = 0; j < JP; ++j) {
+          adj[j * JP + kk] = m_s[j * JP + kk];            // M (j, k)
+          adj[JP * JP + kk * JP + j] = Pb[j];             // P0 (k, j)
+        }
+        adj[2 * JP * JP + kk] = gbar;
+      }
+      if (k == 0 && sweep_forward) {
+        const double nan = __longlong_as_double(0x7ff8000000000000LL);
+        const double logdet = fail ? nan : ld.value();
+        const double q = fail ? nan : quad;
+        if (a.out_val) a.out_val[b] = -0.5 * (q + logdet);
+        if (a.out_logdet) a.out_logdet[b] = logdet;
+        if (a.out_quad) a.out_quad[b] = q;
+        if (a.status) a.status[b] = fail ? 3 : 0;
+      }
+    }
+    return;
   }
 
   // ---- combine the per-row sums into the reference's gradient vector (solver.cpp:392-434) ------
@@ -560,7 +660,7 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
       }
       gout[e] = fail ? nan : gval;
     }
-    if (k == 0) {
+    if (k == 0 && MODE != 2) {
       const double logdet = fail ? nan : ld.value();
       const double q = fail ? nan : quad;
       if (a.out_val) a.out_val[b] = -0.5 * (q + logdet);
@@ -590,6 +690,71 @@ cudaError_t launch_span(const GradArgs& a, cudaStream_t stream) {
   if (e != cudaSuccess) return e;
   const long long grid = (a.B + C::G - 1) / C::G;
   kern<<<(unsigned)grid, kWarp, C::smem, stream>>>(a);
+  return cudaGetLastError();
+}
+
+template <int JP, int MODE>
+cudaError_t launch_scan_mode(const GradArgs& a, cudaStream_t stream) {
+  using C = GradCfg<JP>;
+  auto kern = k_grad_coop<JP, MODE != 3, MODE>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::smem);
+  if (e != cudaSuccess) return e;
+  const long long grid = (a.B + C::G - 1) / C::G;
+  kern<<<(unsigned)grid, kWarp, C::smem, stream>>>(a);
+  return cudaGetLastError();
+}
+
+// The fold between the two adjoint passes: spans from the last to the first, a thread per matrix entry.
+//   carries into span c = carries out of span c+1;   out = M in M^T - 1/2 ((M g) g0^T + g0 (M g)^T) + P0,  M g + g0
+template <int JP>
+__global__ void __launch_bounds__(JP * JP) k_adj_fold(int K, double* adj) {
+  constexpr int JJ = JP * JP, kAdj = GradCfg<JP>::kAdj;
+  __shared__ double Ms[JJ], Ps[JJ], Ts[JJ], gs[JP], g0s[JP], Mg[JP];
+  const int tid = threadIdx.x, i = tid / JP, j = tid % JP;
+  Ps[tid] = 0.0;
+  if (tid < JP) gs[tid] = 0.0;
+  // records are read one span ahead of their use
+  double m_next = adj[(size_t)(K - 1) * kAdj + tid], p0_next = adj[(size_t)(K - 1) * kAdj + JJ + tid];
+  double g0_next = tid < JP ? adj[(size_t)(K - 1) * kAdj + 2 * JJ + tid] : 0.0;
+  __syncthreads();
+  for (int c = K - 1; c >= 0; --c) {
+    double* rec = adj + (size_t)c * kAdj;
+    rec[2 * JJ + JP + tid] = Ps[tid];                       // P_in
+    if (tid < JP) rec[3 * JJ + JP + tid] = gs[tid];         // g_in
+    const double p0 = p0_next;
+    Ms[tid] = m_next;
+    if (tid < JP) g0s[tid] = g0_next;
+    if (c > 0) {
+      const double* nx = adj + (size_t)(c - 1) * kAdj;
+      m_next = nx[tid]; p0_next = nx[JJ + tid];
+      if (tid < JP) g0_next = nx[2 * JJ + tid];
+    }
+    __syncthreads();
+    double t = 0.0;
+#pragma unroll
+    for (int q = 0; q < JP; ++q) t = fma(Ms[i * JP + q], Ps[q * JP + j], t);     // T = M P
+    Ts[tid] = t;
+    if (tid < JP) {
+      double v = 0.0;
+#pragma unroll
+      for (int q = 0; q < JP; ++q) v = fma(Ms[tid * JP + q], gs[q], v);
+      Mg[tid] = v;
+    }
+    __syncthreads();
+    double pn = p0;
+#pragma unroll
+    for (int q = 0; q < JP; ++q) pn = fma(Ts[i * JP + q], Ms[j * JP + q], pn);   // + T M^T
+    pn -= 0.5 * (Mg[i] * g0s[j] + g0s[i] * Mg[j]);
+    __syncthreads();
+    Ps[tid] = pn;
+    if (tid < JP) gs[tid] = Mg[tid] + g0s[tid];
+    __syncthreads();
+  }
+}
+
+template <int JP>
+cudaError_t launch_fold(int K, double* adj, cudaStream_t stream) {
+  k_adj_fold<JP><<<1, JP * JP, 0, stream>>>(K, adj);
   return cudaGetLastError();
 }
 
@@ -715,6 +880,41 @@ cudaError_t launch_grad_spans(const GradArgs& a, cudaStream_t stream) {
     case 16: return launch_span<16>(a, stream);
     case 24: return launch_span<24>(a, stream);
     default: return launch_span<32>(a, stream);
+  }
+}
+
+// the exact time-parallel adjoint: mode 1 (probe), 2 (final) over spans; 3: forward sweep of the whole series
+cudaError_t launch_grad_scan(const GradArgs& a, int mode, cudaStream_t stream) {
+  const int J = a.Jr + 2 * a.Jc + a.Jg;
+  if (a.Jg != 0 || J < 1 || J > kCoopMaxJ || a.seg < 1 || mode < 1 || mode > 3) return cudaErrorInvalidValue;
+  if (mode != 3 && (!a.span || !a.adj)) return cudaErrorInvalidValue;
+#define CEL_SCAN_CASE(JPV)                                                        \
+  case JPV:                                                                       \
+    return mode == 1 ? launch_scan_mode<JPV, 1>(a, stream)                        \
+                     : (mode == 2 ? launch_scan_mode<JPV, 2>(a, stream) : launch_scan_mode<JPV, 3>(a, stream));
+  switch (grad_jp(J)) {
+    CEL_SCAN_CASE(2) CEL_SCAN_CASE(4) CEL_SCAN_CASE(6) CEL_SCAN_CASE(8) CEL_SCAN_CASE(12) CEL_SCAN_CASE(16) CEL_SCAN_CASE(24)
+    default: return mode == 1 ? launch_scan_mode<32, 1>(a, stream)
+                              : (mode == 2 ? launch_scan_mode<32, 2>(a, stream) : launch_scan_mode<32, 3>(a, stream));
+  }
+#undef CEL_SCAN_CASE
+}
+
+size_t grad_scan_adj_doubles(int K, int J) {
+  const int JP = grad_jp(J);
+  return (size_t)K * (3 * JP * JP + 2 * JP);
+}
+
+cudaError_t launch_grad_scan_fold(int K, int J, double* adj, cudaStream_t stream) {
+  switch (grad_jp(J)) {
+    case 2: return launch_fold<2>(K, adj, stream);
+    case 4: return launch_fold<4>(K, adj, stream);
+    case 6: return launch_fold<6>(K, adj, stream);
+    case 8: return launch_fold<8>(K, adj, stream);
+    case 12: return launch_fold<12>(K, adj, stream);
+    case 16: return launch_fold<16>(K, adj, stream);
+    case 24: return launch_fold<24>(K, adj, stream);
+    default: return launch_fold<32>(K, adj, stream);
   }
 }
 

@@ -129,11 +129,17 @@ struct GradArgs {
   const int* span;      // NULL for batches of whole series
   int span_nseg_max;    // checkpoint slots per group = ceil(longest span / seg)
   double* span_edge;    // [B][4][2J+1]: W,D at both edges of the owned range; adjoint carries at both
+  // the exact time-parallel adjoint (launch_grad_scan): per span M | P0 | g0 | P_in | g_in, grad_scan_adj_doubles
+  double* adj;
+  int have_ckpt;        // mode 1: the forward sweep (mode 3) has already left the checkpoints
 };
 // One long series by time spans (grad.cu); launch_grad_span_finish adds the partial results up in
 // span order: result[0] = value, result[1] = worst relative mismatch between neighbouring spans
 // (forward state and adjoint carries), result[2] = status (as a double), result[3..3+P) = gradient.
 cudaError_t launch_grad_spans(const GradArgs& a, cudaStream_t stream);
+cudaError_t launch_grad_scan(const GradArgs& a, int mode, cudaStream_t stream);
+size_t grad_scan_adj_doubles(int K, int J);
+cudaError_t launch_grad_scan_fold(int K, int J, double* adj, cudaStream_t stream);
 cudaError_t launch_grad_span_finish(const GradArgs& a, double* result, cudaStream_t stream);
 // ragged batches: span[4b..] = {0, 0, len_b, len_b}; then launch_grad_spans with stride > 0, span_edge NULL
 cudaError_t launch_ragged_spans(long long B, int N, const int* lengths, int* span, cudaStream_t stream);

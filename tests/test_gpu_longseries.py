@@ -221,21 +221,37 @@ def _grad_case(N, Jr, Jc, seed):
 
 @pytest.mark.parametrize("N,Jr,Jc", [(150000, 0, 2), (100001, 1, 1), (200000, 0, 4)])
 def test_span_parallel_gradient_matches_reference(N, Jr, Jc):
-    """grad_log_likelihood of one long series runs as time spans side by side (grad.cu, SPAN):
-    value and gradient against the reference's automatic differentiation."""
-    assert _grad_case(N, Jr, Jc, seed=N + 7) == 2      # span sweep + finish
+    """grad_log_likelihood of one long series runs as time spans side by side with the adjoint as an exact
+    two-pass scan (grad.cu, scan modes: probe, fold, final, finish): value and gradient against the
+    reference's automatic differentiation."""
+    assert _grad_case(N, Jr, Jc, seed=N + 7) == 4
 
 
 def test_gradient_just_above_the_span_threshold():
-    """N = 20000: whichever path the planner picks (spans or serial) must meet the bar."""
-    assert _grad_case(20000, 0, 2, seed=77) in (1, 2, 3)
+    """N = 20000: whichever path the planner picks must meet the bar."""
+    assert _grad_case(20000, 0, 2, seed=77) in (1, 4, 5, 9)
 
 
 def test_span_parallel_gradient_rejects_short_halos(monkeypatch):
-    """Halos cut to 2 % of the bound: neighbouring spans disagree at their common edge, the check
-    notices, and the serial sweep gives the answer (3 launches)."""
+    """Warm-up halos cut to 2 % of the bound: neighbouring spans disagree at their common edge (W, D, f of
+    the same step), the check notices, and the second attempt -- ONE forward sweep over the series for the
+    checkpoints, the adjoint scan as before -- gives the answer (4 + 5 launches)."""
     monkeypatch.setenv("CEL_SEGMENT_HALO_SCALE", "0.02")
-    assert _grad_case(120000, 0, 2, seed=31) == 3
+    assert _grad_case(120000, 0, 2, seed=31) == 9
+
+
+@pytest.mark.parametrize("N,Jr,Jc", [(90000, 0, 2), (70001, 2, 1), (50000, 0, 8), (40000, 0, 13)])
+def test_adjoint_scan_behind_a_serial_forward_sweep(monkeypatch, N, Jr, Jc):
+    """The path for kernels that forget too slowly for warm-up halos, forced: forward sweep of the whole
+    series (mode 3), then probe, fold, final, finish.  No halo anywhere, so nothing is approximate."""
+    monkeypatch.setenv("CEL_GRAD_SCAN_SERIAL_FORWARD", "1")
+    assert _grad_case(N, Jr, Jc, seed=N + 3) == 5
+
+
+def test_halo_and_cool_down_spans_of_round_one_still_agree(monkeypatch):
+    """CEL_GRAD_SPANS_V1: the span sweep with warm-up and cool-down halos (kept as an A/B knob)."""
+    monkeypatch.setenv("CEL_GRAD_SPANS_V1", "1")
+    assert _grad_case(150000, 0, 2, seed=150007) == 2
 
 
 @pytest.mark.parametrize("N,Jr,Jc,nrhs", [(50001, 1, 2, 2), (4096, 0, 1, 1), (40000, 2, 0, 3), (70000, 0, 8, 1)])
