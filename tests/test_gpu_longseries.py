@@ -339,3 +339,27 @@ def test_mgpu_entry_points_with_a_world_of_one():
         lib.cel_destroy(h)
         if hasattr(chk, "release"):
             chk.release(f)
+
+
+def test_high_q_oscillator_takes_the_serial_forward_sweep_by_itself():
+    """Two SHO terms of quality factor 300 and 1,500 (c = w0 / 2Q ~ 1e-3): the factorisation forgets over
+    ~4e4 time units, far longer than the series, so no warm-up halo can be planned; the gradient must come
+    out of the forward sweep + adjoint scan (5 launches) and match the reference's AD."""
+    from celerite_b200 import solver, synth
+    from tests.util import RTOL_GRAD, RTOL_SCALAR, rel_grad, rel_sum
+    N = 60000
+    b = synth.make_batch(1, N, 0, 2, seed=5)
+    a0, b0, c0, d0 = synth.sho_coefficients(1.3, 300.0, 0.9)
+    a1, b1, c1, d1 = synth.sho_coefficients(0.6, 1500.0, 4.0)
+    p = oracle.Problem(synth.JITTER, E0, E0, np.array([a0, a1]), np.array([b0, b1]), np.array([c0, c1]),
+                       np.array([d0, d1]), b["t"][0], b["diag"][0])
+    y = b["y"][0]
+    st, vref, gref = oracle.best().grad(p, y)
+    assert st == 0
+    s = solver.CholeskySolver()
+    n0 = s.launch_count()
+    val, g = s.grad_log_likelihood(p.jitter, p.a_real, p.c_real, p.a_comp, p.b_comp, p.c_comp, p.d_comp,
+                                   E0, E2, E2, p.x, y, p.diag)
+    assert s.launch_count() - n0 == 5
+    assert rel_sum(val, vref, N) < RTOL_SCALAR
+    assert rel_grad(g, gref) < RTOL_GRAD, (g, gref)
