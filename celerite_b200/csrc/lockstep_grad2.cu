@@ -46,10 +46,21 @@ constexpr int kPrevB = kWarp * 16;                             // one [32 x 2] b
 constexpr size_t kRevSmem = (size_t)kRevWarps * (kWarpBytes + kPrevB) + kBarBytes + kTrigTabN * 16 + kExpTabN * 8 + 1024;
 static_assert(kWarpBytes % 1024 == 0 && kRevWarps * 8 <= kBarBytes, "shared-memory layout");
 
+// MODE 0: a warp sweeps its 32 series from the last segment to the first.
+// MODE 1 / 2 (batches too small to fill the GPU that way: few, long series): the EXACT time-parallel adjoint of
+// grad.cu (see there, and tools/proto_adjoint_scan.py) with a thread per series -- the segments of a series are
+// cut into K spans, a warp sweeps ONE span of its 32 series; MODE 1 (probe) starts from zero carries and forms
+// the span's 2 x 2 transfer map M = prod e_n (I - u_n W_n^T) on the way, k_grad2_fold gives every span its true
+// incoming carries, MODE 2 (final) sweeps again from those with the gradient sums; k_grad2_finish adds the
+// spans' sums up.  xch: per (warp of series, span) 19 rows of 32 doubles:
+//   0-3 M, 4-5 g0, 6-8 P0 (probe) | 9-13 carries in: P00 P01 P11 g0 g1 (fold) | 14-18 sumA ga gb gc gd (final)
+constexpr int kXchRows = 19;
+
+template <int MODE>
 __global__ void __maxnreg__(128)
 k_grad2_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_constant__ CUtensorMap tm_t,
                 const __grid_constant__ CUtensorMap tm_d, const __grid_constant__ CUtensorMap tm_y,
-                const __grid_constant__ CUtensorMap tm_p) {
+                const __grid_constant__ CUtensorMap tm_p, const int K, const int span_segs, double* __restrict__ xch) {
   extern __shared__ unsigned char smem_dyn[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   unsigned char* smem_al = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
@@ -62,7 +73,9 @@ k_grad2_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
   cel_fill_tables(trig_tab, exp_tab, threadIdx.x, kRevThreads);
   __syncthreads();
 
-  const long long wg = (long long)blockIdx.x * kRevWarps + warp;   // 32 series per warp
+  const long long unit = (long long)blockIdx.x * kRevWarps + warp;
+  const long long wg = MODE == 0 ? unit : unit / K;      // 32 series per warp
+  const int span = MODE == 0 ? 0 : (int)(unit - wg * K);
   const long long b0 = wg * kWarp;
   if (b0 >= a.B) return;
   const long long b = b0 + lane;
@@ -92,7 +105,11 @@ k_grad2_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
       tma_load_2d(wtile + 2 * kTileB, &tm_y, s * kSeg, (int)b0, bar);
     }
   };
-  issue(nseg - 1);
+  // segments [s_lo, s_hi) are this warp's
+  const int s_lo = MODE == 0 ? 0 : span * span_segs;
+  const int s_hi = MODE == 0 ? nseg : min(nseg, s_lo + span_segs);
+  if (s_lo >= s_hi) return;                              // (K * span_segs >= nseg: only trailing spans can be empty)
+  issue(s_hi - 1);
 
   const double* ck = ckpt_base + ((size_t)wg * nseg * kGrad2Ckpt) * kWarp + lane;
   // 32-byte swizzle of the boxes: the 16-byte half of a row is exchanged where address bit 7 is set
@@ -102,7 +119,12 @@ k_grad2_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
   // adjoint state: Pb = adjoint of P_{n+1} (symmetric), g = adjoint of f_{n+1} scaled back by phi
   double Pb00 = 0.0, Pb01 = 0.0, Pb11 = 0.0, g0 = 0.0, g1 = 0.0;
   double ga = 0.0, gb = 0.0, gc = 0.0, gd = 0.0, sumA = 0.0;
-  unsigned phase = 0;
+  double m00 = 1.0, m01 = 0.0, m10 = 0.0, m11 = 1.0;    // MODE 1: the span's transfer map
+  auto xrow = [&]() { return xch + (size_t)(blockIdx.x * kRevWarps + (threadIdx.x >> 5)) * (kXchRows * kWarp) + (threadIdx.x & 31); };
+  if (MODE == 2) {
+    const double* xu = xrow();
+    Pb00 = xu[9 * kWarp]; Pb01 = xu[10 * kWarp]; Pb11 = xu[11 * kWarp]; g0 = xu[12 * kWarp]; g1 = xu[13 * kWarp];
+  }
 
   // state before the segment that is processed next, in the form of the checkpoints (lockstep.cu):
   // Sp = S + D W W^T, fp = f + W x of the step before, and its time; all zero before step 0
@@ -116,12 +138,11 @@ k_grad2_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
       Sp00 = Sp01 = Sp11 = fp0 = fp1 = 0.0;
     }
   };
-  load_state(nseg - 1);
+  load_state(s_hi - 1);
 
   auto segment = [&](const int s, auto guard, const int nv) {
     constexpr bool GUARD = decltype(guard)::value;
-    mbar_wait(bar, phase);
-    phase ^= 1u;
+    mbar_wait(bar, (unsigned)((s_hi - 1 - s) & 1));        // one box per segment, from the top
     double rt[kSeg];
     {
       const double2 v0 = *reinterpret_cast<const double2*>(lrow + h0);
@@ -142,7 +163,7 @@ k_grad2_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
         dd[0] = v1.x; dd[1] = v1.y; yy[0] = v2.x; yy[1] = v2.y;
         if (i == kSeg - 2) {
           __syncwarp();
-          if (s > 0) issue(s - 1);
+          if (s > s_lo) issue(s - 1);
         }
       }
       if (!GUARD || i < nv) {
@@ -173,7 +194,7 @@ k_grad2_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
       }
     }
     // the forward state is dead now: fetch that of the segment below while the adjoint runs
-    load_state(s - 1);
+    if (MODE == 0 || s > s_lo) load_state(s - 1);
 
     // ---- adjoint of the segment, last step first ----
 #pragma unroll
@@ -220,15 +241,39 @@ k_grad2_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
         gb = fma(-ub1, cd, fma(ub0, sd, gb));
         const double gq = fma(wb1, cd, fma(-wb0, sd, fma(ub1, u0, -(ub0 * u1))));
         gd = fma(tn, gq, gd);
+        if (MODE == 1) {                                  // M <- e (I - u W_n^T) M
+          const double d0 = fma(w1, m10, w0 * m00), d1 = fma(w1, m11, w0 * m01);
+          m00 = e * fma(-u0, d0, m00); m01 = e * fma(-u0, d1, m01);
+          m10 = e * fma(-u1, d0, m10); m11 = e * fma(-u1, d1, m11);
+        }
       }
     }
   };
 
   const int nfull = N / kSeg;
-  if (nfull < nseg) segment(nseg - 1, std::true_type(), N - nfull * kSeg);
+  if (MODE == 0) {
+    if (nfull < nseg) segment(nseg - 1, std::true_type(), N - nfull * kSeg);   // the ragged last segment
 #pragma unroll 1
-  for (int s = nfull - 1; s >= 0; --s) segment(s, std::false_type(), kSeg);
+    for (int s = nfull - 1; s >= 0; --s) segment(s, std::false_type(), kSeg);
+  } else {
+    int s_top = s_hi - 1;
+    if (s_top >= nfull) { segment(s_top, std::true_type(), N - nfull * kSeg); --s_top; }
+#pragma unroll 1
+    for (int s = s_top; s >= s_lo; --s) segment(s, std::false_type(), kSeg);
+  }
 
+  if (MODE == 1) {
+    double* xu = xrow();
+    xu[0] = m00; xu[kWarp] = m01; xu[2 * kWarp] = m10; xu[3 * kWarp] = m11;
+    xu[4 * kWarp] = g0; xu[5 * kWarp] = g1;
+    xu[6 * kWarp] = Pb00; xu[7 * kWarp] = Pb01; xu[8 * kWarp] = Pb11;
+    return;
+  }
+  if (MODE == 2) {
+    double* xu = xrow();
+    xu[14 * kWarp] = sumA; xu[15 * kWarp] = ga; xu[16 * kWarp] = gb; xu[17 * kWarp] = gc; xu[18 * kWarp] = gd;
+    return;
+  }
   if (active) {
     double* g = a.out_grad + (size_t)b * 5;
     g[0] = (jitter > DBL_EPSILON) ? sumA : 0.0;   // solver.cpp:377-389, 418-426
@@ -239,10 +284,50 @@ k_grad2_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
   }
 }
 
+// carries into span c = carries out of span c+1 (a thread per series; the 2 x 2 case of k_adj_fold in grad.cu)
+__global__ void __launch_bounds__(128) k_grad2_fold(long long B, int K, double* xch) {
+  const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  double* x0 = xch + (size_t)(b / kWarp) * K * (kXchRows * kWarp) + (b % kWarp);
+  double p00 = 0.0, p01 = 0.0, p11 = 0.0, g0 = 0.0, g1 = 0.0;
+  for (int c = K - 1; c >= 0; --c) {
+    double* x = x0 + (size_t)c * (kXchRows * kWarp);
+    x[9 * kWarp] = p00; x[10 * kWarp] = p01; x[11 * kWarp] = p11; x[12 * kWarp] = g0; x[13 * kWarp] = g1;
+    const double m00 = x[0], m01 = x[kWarp], m10 = x[2 * kWarp], m11 = x[3 * kWarp];
+    const double q0 = x[4 * kWarp], q1 = x[5 * kWarp];
+    const double mg0 = fma(m01, g1, m00 * g0), mg1 = fma(m11, g1, m10 * g0);
+    const double a00 = fma(m01, p01, m00 * p00), a01 = fma(m01, p11, m00 * p01);      // M P
+    const double a10 = fma(m11, p01, m10 * p00), a11 = fma(m11, p11, m10 * p01);
+    p00 = fma(a01, m01, a00 * m00) - mg0 * q0 + x[6 * kWarp];
+    p01 = fma(a01, m11, a00 * m10) - 0.5 * fma(mg0, q1, q0 * mg1) + x[7 * kWarp];
+    p11 = fma(a11, m11, a10 * m10) - mg1 * q1 + x[8 * kWarp];
+    g0 = mg0 + q0; g1 = mg1 + q1;
+  }
+}
+
+// the spans' sums in span order -> the reference's gradient vector (solver.cpp:392-434)
+__global__ void __launch_bounds__(128) k_grad2_finish(GradArgs a, int K, const double* xch) {
+  const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= a.B) return;
+  const double* x0 = xch + (size_t)(b / kWarp) * K * (kXchRows * kWarp) + (b % kWarp);
+  double sumA = 0.0, ga = 0.0, gb = 0.0, gc = 0.0, gd = 0.0;
+  for (int c = 0; c < K; ++c) {
+    const double* x = x0 + (size_t)c * (kXchRows * kWarp);
+    sumA += x[14 * kWarp]; ga += x[15 * kWarp]; gb += x[16 * kWarp]; gc += x[17 * kWarp]; gd += x[18 * kWarp];
+  }
+  const double jitter = a.coeffs[b * a.coeff_stride];
+  double* g = a.out_grad + (size_t)b * 5;
+  g[0] = (jitter > DBL_EPSILON) ? sumA : 0.0;
+  g[1] = ga + sumA;
+  g[2] = gb;
+  g[3] = gc;
+  g[4] = gd;
+}
+
 }  // namespace
 
 // The batch goes through in pieces of at most this many series, so that the checkpoints of a piece
-// (20 bytes per point) stay below ~6 GB whatever the batch
+// (10 bytes per point) stay below ~6 GB whatever the batch
 static long long grad2_piece(long long B, int N) {
   const double per_series = 8.0 * kGrad2Ckpt * ((N + kSeg - 1) / kSeg);
   long long piece = (long long)(6.0e9 / per_series) / (kRevWarps * kWarp) * (kRevWarps * kWarp);
@@ -251,6 +336,22 @@ static long long grad2_piece(long long B, int N) {
 }
 static size_t flag_doubles(long long piece) { return ((size_t)piece / 2 + 32) & ~(size_t)31; }
 
+// Spans per series for the time-parallel form: as many as fill one wave of reverse-kernel warps, at least 16
+// segments (64 steps) each; 1 = the whole series per warp (MODE 0)
+static int grad2_spans(long long B, int N, int* span_segs) {
+  static const bool off = getenv("CEL_GRAD2_NO_SPANS") != nullptr;   // A/B knob
+  const long long warps = (B + kWarp - 1) / kWarp;
+  const int nseg = (N + kSeg - 1) / kSeg;
+  const long long wave = (long long)sm_count() * kRevWarps;
+  long long K = wave / warps;
+  if (K > nseg / 16) K = nseg / 16;
+  if (K > 1024) K = 1024;
+  if (off || K < 2) { *span_segs = nseg; return 1; }
+  const int segs = (int)((nseg + K - 1) / K);
+  *span_segs = segs;
+  return (nseg + segs - 1) / segs;
+}
+
 // flags of a piece + the larger of its checkpoints and what the first-generation kernel wants for the redo
 size_t grad2_scratch_doubles(long long B, int N, int seg_v1) {
   const long long piece = grad2_piece(B, N);
@@ -258,7 +359,10 @@ size_t grad2_scratch_doubles(long long B, int N, int seg_v1) {
   const size_t nseg = (size_t)(N + kSeg - 1) / kSeg;
   const size_t ck = warps * nseg * kGrad2Ckpt * kWarp;
   const size_t v1 = grad_lockstep_v1_scratch_doubles(piece, N, 1, seg_v1);
-  return flag_doubles(piece) + (ck > v1 ? ck : v1);
+  int segs = 0;
+  const int K = grad2_spans(piece, N, &segs);
+  const size_t xch = K > 1 ? warps * K * kXchRows * kWarp : 0;
+  return flag_doubles(piece) + (ck > v1 ? ck : v1) + xch;
 }
 
 cudaError_t launch_grad2(const GradArgs& a, cudaStream_t stream, bool* used, int* launches) {
@@ -270,9 +374,18 @@ cudaError_t launch_grad2(const GradArgs& a, cudaStream_t stream, bool* used, int
   const long long piece = grad2_piece(a.B, a.N);
   int* flags = reinterpret_cast<int*>(a.scratch);
   double* region = a.scratch + flag_doubles(piece);
-  auto kern = k_grad2_reverse;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRevSmem);
+  cudaError_t e = cudaFuncSetAttribute(k_grad2_reverse<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRevSmem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_grad2_reverse<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRevSmem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_grad2_reverse<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRevSmem);
   if (e != cudaSuccess) return e;
+  // the spans' exchange rows sit behind the larger of (checkpoints, scratch of the redo pass)
+  size_t region_doubles;
+  {
+    const size_t pw = (size_t)((piece + kWarp - 1) / kWarp), nsg = (size_t)(a.N + kSeg - 1) / kSeg;
+    const size_t ck = pw * nsg * kGrad2Ckpt * kWarp, v1 = grad_lockstep_v1_scratch_doubles(piece, a.N, 1, a.seg);
+    region_doubles = ck > v1 ? ck : v1;
+  }
+  double* xch = region + region_doubles;
   for (long long off0 = 0; off0 < a.B; off0 += piece) {
     const long long nb = (off0 + piece <= a.B) ? piece : a.B - off0;
     GradArgs g = a;
@@ -299,7 +412,19 @@ cudaError_t launch_grad2(const GradArgs& a, cudaStream_t stream, bool* used, int
     if (e != cudaSuccess) return e;
     if (!fwd) return off0 == 0 ? cudaSuccess : cudaErrorInvalidValue;   // (cannot differ between pieces)
     const long long warps = (nb + kWarp - 1) / kWarp;
-    kern<<<(unsigned)((warps + kRevWarps - 1) / kRevWarps), kRevThreads, kRevSmem, stream>>>(g, region, mt, md, my, mp);
+    int span_segs = 0;
+    const int K = grad2_spans(nb, a.N, &span_segs);
+    if (K == 1) {
+      k_grad2_reverse<0><<<(unsigned)((warps + kRevWarps - 1) / kRevWarps), kRevThreads, kRevSmem, stream>>>(
+          g, region, mt, md, my, mp, 1, span_segs, nullptr);
+    } else {                                             // few long series: probe, fold, final, finish over K spans
+      const unsigned grid = (unsigned)((warps * K + kRevWarps - 1) / kRevWarps), gb = (unsigned)((nb + 127) / 128);
+      k_grad2_reverse<1><<<grid, kRevThreads, kRevSmem, stream>>>(g, region, mt, md, my, mp, K, span_segs, xch);
+      k_grad2_fold<<<gb, 128, 0, stream>>>(nb, K, xch);
+      k_grad2_reverse<2><<<grid, kRevThreads, kRevSmem, stream>>>(g, region, mt, md, my, mp, K, span_segs, xch);
+      k_grad2_finish<<<gb, 128, 0, stream>>>(g, K, xch);
+      if (launches) *launches += 3;
+    }
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     // flagged series again, by the first-generation kernel (its warps leave at once where nothing is flagged)

@@ -85,7 +85,8 @@ def test_batched_grad(B, N, Jr, Jc):
         assert rel_grad(g[i], gref) < RTOL_GRAD
 
 
-@pytest.mark.parametrize("B,N,Jc", [(100, 500, 1), (33, 2000, 1), (70, 403, 2), (5, 1000, 2), (40, 17, 1), (3, 1, 1)])
+@pytest.mark.parametrize("B,N,Jc", [(100, 500, 1), (33, 2000, 1), (70, 403, 2), (5, 1000, 2), (40, 17, 1), (3, 1, 1),
+                                    (40, 20000, 1), (300, 4098, 1), (2, 262, 1)])
 def test_batched_grad_lockstep_device(B, N, Jc):
     """The thread-per-series gradient kernel (all-complex J = 2, 4; device-resident, TMA path) must
     agree with the reference gradient and with the cooperative kernel."""
