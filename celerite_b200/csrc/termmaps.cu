@@ -15,24 +15,42 @@
 // either under-damped for the whole batch (CEL_TERM_SHO, Q >= 1/2: one complex term) or
 // over-damped for the whole batch (CEL_TERM_SHO_OVERDAMPED, Q < 1/2: two real terms); a series
 // on the wrong side gets status 1 and NaN coefficients.
+//
+// Products (terms.py:218-277) of anything: the kind list is a PREFIX expression -- CEL_TERM_PRODUCT and
+// CEL_TERM_SUM are followed by their two operands, each a simple term or again a product / sum -- which
+// the host flattens once into a straight-line program over "slots" (one coefficient set (a, b, c, d) each):
+// a leaf evaluates its term into one slot (two for an over-damped SHO), a product node multiplies every
+// set of one operand with every set of the other in the reference's order (real x real; real1 x complex2,
+// real2 x complex1; complex x complex giving two sets), a sum node concatenates.  A thread runs the
+// program forward (slots in local memory) and, for the transposed Jacobian, once more backward with one
+// adjoint per slot.
 #include <cmath>
+#include <vector>
 
 #include "solver_handle.h"
 
 namespace cel {
 namespace {
 
-constexpr int kMaxTerms = 32;
+constexpr int kMaxList = 64;     // entries of the kind list
+constexpr int kMaxOps = 96;
+constexpr int kMaxSlots = 96;
+constexpr int kMaxLeaves = 32;
+
+enum : unsigned char { OP_LEAF = 0, OP_JITTER = 1, OP_MUL_RR = 2, OP_MUL_RC = 3, OP_MUL_CC = 4 };
+
+struct TermOp {
+  unsigned char type, kind;      // kind: the term kind of a leaf
+  short a, b;                    // leaf: first parameter, index into eps[];  products: operand slots (RC: real, complex)
+  short out;                     // first slot written (an over-damped SHO and a complex x complex product write two)
+};
 
 struct TermPlan {
-  int nterms, npar, Jr, Jc;
-  int kind[kMaxTerms];
-  int par0[kMaxTerms];     // first parameter of the term
-  int real0[kMaxTerms];    // first real slot of the term
-  int comp0[kMaxTerms];    // first complex slot of the term
-  double eps[kMaxTerms];   // Matern32Term's eps
-  int k1[kMaxTerms], k2[kMaxTerms];   // factor kinds of a CEL_TERM_PRODUCT node
-  double eps2[kMaxTerms];             // eps of its second factor (eps: of its first)
+  int nops, nslots, npar, Jr, Jc;
+  TermOp ops[kMaxOps];
+  short real_out[kMaxSlots];     // slot of the i-th real / complex set of the row
+  short comp_out[kMaxSlots];
+  double eps[kMaxLeaves];
 };
 
 __host__ __device__ inline int term_npar(int kind) {
@@ -47,26 +65,32 @@ __host__ __device__ inline int term_npar(int kind) {
     default: return -1;
   }
 }
-inline int term_nreal(int kind) { return kind == CEL_TERM_REAL ? 1 : kind == CEL_TERM_SHO_OVERDAMPED ? 2 : 0; }
-inline int term_ncomp(int kind) {
-  return (kind == CEL_TERM_COMPLEX3 || kind == CEL_TERM_COMPLEX4 || kind == CEL_TERM_SHO || kind == CEL_TERM_MATERN32) ? 1 : 0;
-}
 
-// ---- factors of a product term (terms.py:218-277) ---------------------------------------------
-// A factor is a simple term with ONE coefficient set: real (a, c; b = d = 0) or complex (a, b, c, d).
-struct Fac { double a, b, c, d; int cplx; };
+struct Set { double a, b, c, d; };
 
-__device__ __forceinline__ Fac fac_eval(int kind, const double* q, double eps, int& bad) {
-  Fac f; f.a = f.b = f.c = f.d = 0.0; f.cplx = 1;
+// a leaf: parameters -> its coefficient set(s)   (terms.py:389-391, 431-439, 490-517, 562-566)
+__device__ __forceinline__ void leaf_eval(int kind, const double* q, double eps, Set* o, int& bad) {
+  const double nan = __longlong_as_double(0x7ff8000000000000LL);
+  Set f; f.a = f.b = f.c = f.d = 0.0;
   switch (kind) {
-    case CEL_TERM_REAL: f.a = exp(q[0]); f.c = exp(q[1]); f.cplx = 0; break;
+    case CEL_TERM_REAL: f.a = exp(q[0]); f.c = exp(q[1]); break;
     case CEL_TERM_COMPLEX3: f.a = exp(q[0]); f.c = exp(q[1]); f.d = exp(q[2]); break;
     case CEL_TERM_COMPLEX4: f.a = exp(q[0]); f.b = exp(q[1]); f.c = exp(q[2]); f.d = exp(q[3]); break;
-    case CEL_TERM_SHO: {
+    case CEL_TERM_SHO: {                             // Q >= 1/2
       const double S0 = exp(q[0]), Q = exp(q[1]), w0 = exp(q[2]);
-      if (!(Q >= 0.5)) bad = 1;
       const double fq = sqrt(4.0 * Q * Q - 1.0);
       f.a = S0 * w0 * Q; f.b = f.a / fq; f.c = 0.5 * w0 / Q; f.d = f.c * fq;
+      if (!(Q >= 0.5)) { bad = 1; f.a = f.b = f.c = f.d = nan; }
+    } break;
+    case CEL_TERM_SHO_OVERDAMPED: {                  // Q < 1/2: two real sets
+      const double S0 = exp(q[0]), Q = exp(q[1]), w0 = exp(q[2]);
+      const double fq = sqrt(1.0 - 4.0 * Q * Q);
+      const double h = 0.5 * S0 * w0 * Q, e = 0.5 * w0 / Q;
+      Set g; g.b = g.d = 0.0;
+      f.a = h * (1.0 + 1.0 / fq); f.c = e * (1.0 - fq);
+      g.a = h * (1.0 - 1.0 / fq); g.c = e * (1.0 + fq);
+      if (!(Q < 0.5)) { bad = 1; f.a = f.c = g.a = g.c = nan; }
+      o[1] = g;
     } break;
     case CEL_TERM_MATERN32: {
       const double w0 = sqrt(3.0) * exp(-q[1]), S0 = exp(2.0 * q[0]) / w0;
@@ -74,209 +98,219 @@ __device__ __forceinline__ Fac fac_eval(int kind, const double* q, double eps, i
     } break;
     default: bad = 1; break;
   }
-  return f;
+  o[0] = f;
 }
 
-// o[i] = ga da/dp_i + gb db/dp_i + gc dc/dp_i + gd dd/dp_i for the factor's own parameters
-__device__ __forceinline__ void fac_back(int kind, const double* q, double eps, const Fac& f, double ga, double gb,
-                                         double gc, double gd, double* o) {
+// transposed Jacobian of a leaf: o[i] = sum over its sets of (ga da/dp_i + gb db/dp_i + gc dc/dp_i + gd dd/dp_i)
+__device__ __forceinline__ void leaf_back(int kind, const double* q, const Set* f, const Set* g, double* o) {
   switch (kind) {
-    case CEL_TERM_REAL: o[0] = f.a * ga; o[1] = f.c * gc; break;
-    case CEL_TERM_COMPLEX3: o[0] = f.a * ga; o[1] = f.c * gc; o[2] = f.d * gd; break;
-    case CEL_TERM_COMPLEX4: o[0] = f.a * ga; o[1] = f.b * gb; o[2] = f.c * gc; o[3] = f.d * gd; break;
+    case CEL_TERM_REAL: o[0] = f[0].a * g[0].a; o[1] = f[0].c * g[0].c; break;
+    case CEL_TERM_COMPLEX3: o[0] = f[0].a * g[0].a; o[1] = f[0].c * g[0].c; o[2] = f[0].d * g[0].d; break;
+    case CEL_TERM_COMPLEX4:
+      o[0] = f[0].a * g[0].a; o[1] = f[0].b * g[0].b; o[2] = f[0].c * g[0].c; o[3] = f[0].d * g[0].d;
+      break;
     case CEL_TERM_SHO: {
+      // d/dlogQ: f' = 4 Q^2 / f;  a' = a, b' = b (1 - 4Q^2/f^2), c' = -c, d' = c (4Q^2/f - f)
       const double Q = exp(q[1]), k = 4.0 * Q * Q / (4.0 * Q * Q - 1.0);
-      o[0] = f.a * ga + f.b * gb;
-      o[1] = f.a * ga + f.b * (1.0 - k) * gb - f.c * gc + f.d * (k - 1.0) * gd;
-      o[2] = f.a * ga + f.b * gb + f.c * gc + f.d * gd;
+      o[0] = f[0].a * g[0].a + f[0].b * g[0].b;
+      o[1] = f[0].a * g[0].a + f[0].b * (1.0 - k) * g[0].b - f[0].c * g[0].c + f[0].d * (k - 1.0) * g[0].d;
+      o[2] = f[0].a * g[0].a + f[0].b * g[0].b + f[0].c * g[0].c + f[0].d * g[0].d;
+    } break;
+    case CEL_TERM_SHO_OVERDAMPED: {
+      // dlogQ: f' = -4Q^2/f; (1/f)' = 4Q^2/f^3
+      const double S0 = exp(q[0]), Q = exp(q[1]), w0 = exp(q[2]);
+      const double f2 = 1.0 - 4.0 * Q * Q, fq = sqrt(f2), h = 0.5 * S0 * w0 * Q, e = 0.5 * w0 / Q;
+      const double k = 4.0 * Q * Q / f2;
+      const double da0 = f[0].a + h * k / fq, da1 = f[1].a - h * k / fq;
+      const double dc0 = -f[0].c + e * k * fq, dc1 = -f[1].c - e * k * fq;
+      o[0] = f[0].a * g[0].a + f[1].a * g[1].a;
+      o[1] = da0 * g[0].a + da1 * g[1].a + dc0 * g[0].c + dc1 * g[1].c;
+      o[2] = f[0].a * g[0].a + f[1].a * g[1].a + f[0].c * g[0].c + f[1].c * g[1].c;
     } break;
     case CEL_TERM_MATERN32:
-      o[0] = 2.0 * f.a * ga + 2.0 * f.b * gb;
-      o[1] = -f.b * gb - f.c * gc;
+      // a = sigma^2: da/dlogsigma = 2a; b = w0 sigma^2/eps: 2b and -b; c = w0: -w0; d = eps: const
+      o[0] = 2.0 * f[0].a * g[0].a + 2.0 * f[0].b * g[0].b;
+      o[1] = -f[0].b * g[0].b - f[0].c * g[0].c;
       break;
     default: break;
   }
 }
 
-// BACK = false: params -> coefficient row.   BACK = true: gp += J^T gc (gp zeroed here).
+// BACK = false: params -> coefficient row.   BACK = true: gp = J^T gc.
 template <bool BACK>
-__global__ void __launch_bounds__(128) k_term_maps(TermPlan pl, long long B, const double* params, long long pstride,
-                                                   double* coeffs, long long cstride, const double* gc, long long gcstride,
-                                                   double* gp, long long gpstride, int* status) {
+__global__ void __launch_bounds__(64) k_term_maps(const __grid_constant__ TermPlan pl, long long B, const double* params,
+                                                  long long pstride, double* coeffs, long long cstride, const double* gc,
+                                                  long long gcstride, double* gp, long long gpstride, int* status) {
   const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
   const double* p = params + b * pstride;
   const int Jr = pl.Jr, Jc = pl.Jc;
-  // slots of the row
   const int o_ar = 1, o_cr = 1 + Jr, o_ac = 1 + 2 * Jr, o_bc = o_ac + Jc, o_cc = o_bc + Jc, o_dc = o_cc + Jc;
-  double* row = BACK ? nullptr : coeffs + b * cstride;
-  const double* g = BACK ? gc + b * gcstride : nullptr;
-  double* out = BACK ? gp + b * gpstride : nullptr;
-  const double nan = __longlong_as_double(0x7ff8000000000000LL);
+  Set slot[kMaxSlots];
   double jitter = 0.0;
   int bad = 0;
-  for (int t = 0; t < pl.nterms; ++t) {
-    const double* q = p + pl.par0[t];
-    double* o = BACK ? out + pl.par0[t] : nullptr;
-    const int r = pl.real0[t], c = pl.comp0[t];
-    switch (pl.kind[t]) {
-      case CEL_TERM_JITTER: {                      // terms.py:356-357
-        const double j = exp(2.0 * q[0]);
-        if (BACK) o[0] = 2.0 * j * g[0];
-        else jitter += j;
+  // ---- forward: the program, op by op ----
+  for (int i = 0; i < pl.nops; ++i) {
+    const TermOp op = pl.ops[i];
+    switch (op.type) {
+      case OP_JITTER: jitter += exp(2.0 * p[op.a]); break;                    // terms.py:356-357
+      case OP_LEAF: leaf_eval(op.kind, p + op.a, pl.eps[op.b], slot + op.out, bad); break;
+      case OP_MUL_RR: {                                                       // terms.py:246-252
+        const Set x = slot[op.a], y = slot[op.b];
+        Set r; r.a = x.a * y.a; r.b = 0.0; r.c = x.c + y.c; r.d = 0.0;
+        slot[op.out] = r;
       } break;
-      case CEL_TERM_REAL: {                        // terms.py:389-391
-        const double a = exp(q[0]), cc = exp(q[1]);
-        if (BACK) { o[0] = a * g[o_ar + r]; o[1] = cc * g[o_cr + r]; }
-        else { row[o_ar + r] = a; row[o_cr + r] = cc; }
+      case OP_MUL_RC: {                                                       // terms.py:260-267
+        const Set x = slot[op.a], y = slot[op.b];
+        Set r; r.a = x.a * y.a; r.b = x.a * y.b; r.c = x.c + y.c; r.d = y.d;
+        slot[op.out] = r;
       } break;
-      case CEL_TERM_COMPLEX3: {                    // terms.py:431-435 (b = 0)
-        const double a = exp(q[0]), cc = exp(q[1]), d = exp(q[2]);
-        if (BACK) { o[0] = a * g[o_ac + c]; o[1] = cc * g[o_cc + c]; o[2] = d * g[o_dc + c]; }
-        else { row[o_ac + c] = a; row[o_bc + c] = 0.0; row[o_cc + c] = cc; row[o_dc + c] = d; }
+      default: {                                                              // OP_MUL_CC, terms.py:269-280
+        const Set x = slot[op.a], y = slot[op.b];
+        Set r0, r1;
+        r0.a = 0.5 * (x.a * y.a + x.b * y.b); r0.b = 0.5 * (x.b * y.a - x.a * y.b); r0.c = x.c + y.c; r0.d = x.d - y.d;
+        r1.a = 0.5 * (x.a * y.a - x.b * y.b); r1.b = 0.5 * (x.b * y.a + x.a * y.b); r1.c = x.c + y.c; r1.d = x.d + y.d;
+        slot[op.out] = r0; slot[op.out + 1] = r1;
       } break;
-      case CEL_TERM_COMPLEX4: {                    // terms.py:436-439
-        const double a = exp(q[0]), bb = exp(q[1]), cc = exp(q[2]), d = exp(q[3]);
-        if (BACK) { o[0] = a * g[o_ac + c]; o[1] = bb * g[o_bc + c]; o[2] = cc * g[o_cc + c]; o[3] = d * g[o_dc + c]; }
-        else { row[o_ac + c] = a; row[o_bc + c] = bb; row[o_cc + c] = cc; row[o_dc + c] = d; }
-      } break;
-      case CEL_TERM_SHO: {                         // terms.py:503-517, Q >= 1/2
-        const double S0 = exp(q[0]), Q = exp(q[1]), w0 = exp(q[2]);
-        const double f2 = 4.0 * Q * Q - 1.0;
-        if (!(Q >= 0.5)) bad = 1;
-        const double f = sqrt(f2);
-        const double a = S0 * w0 * Q, bb = a / f, cc = 0.5 * w0 / Q, d = cc * f;
-        if (BACK) {
-          // d/dlogQ: f' = 4 Q^2 / f;  a' = a, b' = b (1 - 4Q^2/f^2), c' = -c, d' = c (4Q^2/f - f)
-          const double ga = g[o_ac + c], gb = g[o_bc + c], gcc = g[o_cc + c], gd = g[o_dc + c];
-          const double k = 4.0 * Q * Q / f2;
-          o[0] = a * ga + bb * gb;
-          o[1] = a * ga + bb * (1.0 - k) * gb - cc * gcc + d * (k - 1.0) * gd;
-          o[2] = a * ga + bb * gb + cc * gcc + d * gd;
-        } else {
-          row[o_ac + c] = bad ? nan : a; row[o_bc + c] = bad ? nan : bb;
-          row[o_cc + c] = bad ? nan : cc; row[o_dc + c] = bad ? nan : d;
-        }
-      } break;
-      case CEL_TERM_SHO_OVERDAMPED: {              // terms.py:490-501, Q < 1/2
-        const double S0 = exp(q[0]), Q = exp(q[1]), w0 = exp(q[2]);
-        const double f2 = 1.0 - 4.0 * Q * Q;
-        if (!(Q < 0.5)) bad = 1;
-        const double f = sqrt(f2);
-        const double h = 0.5 * S0 * w0 * Q, e = 0.5 * w0 / Q;
-        const double a0 = h * (1.0 + 1.0 / f), a1 = h * (1.0 - 1.0 / f), c0 = e * (1.0 - f), c1 = e * (1.0 + f);
-        if (BACK) {
-          // dlogQ: f' = -4Q^2/f; (1/f)' = 4Q^2/f^3
-          const double ga0 = g[o_ar + r], ga1 = g[o_ar + r + 1], gc0 = g[o_cr + r], gc1 = g[o_cr + r + 1];
-          const double k = 4.0 * Q * Q / f2;                 // = -f'/f
-          const double da0 = a0 + h * k / f, da1 = a1 - h * k / f;
-          const double dc0 = -c0 + e * k * f, dc1 = -c1 - e * k * f;
-          o[0] = a0 * ga0 + a1 * ga1;
-          o[1] = da0 * ga0 + da1 * ga1 + dc0 * gc0 + dc1 * gc1;
-          o[2] = a0 * ga0 + a1 * ga1 + c0 * gc0 + c1 * gc1;
-        } else {
-          row[o_ar + r] = bad ? nan : a0; row[o_ar + r + 1] = bad ? nan : a1;
-          row[o_cr + r] = bad ? nan : c0; row[o_cr + r + 1] = bad ? nan : c1;
-        }
-      } break;
-      case CEL_TERM_MATERN32: {                    // terms.py:562-566
-        const double eps = pl.eps[t];
-        const double w0 = sqrt(3.0) * exp(-q[1]);
-        const double S0 = exp(2.0 * q[0]) / w0;
-        const double a = w0 * S0, bb = w0 * w0 * S0 / eps;
-        if (BACK) {
-          // a = sigma^2: da/dlogsigma = 2a; b = w0 sigma^2/eps: 2b and -b; c = w0: -w0; d = eps: const
-          o[0] = 2.0 * a * g[o_ac + c] + 2.0 * bb * g[o_bc + c];
-          o[1] = -bb * g[o_bc + c] - w0 * g[o_cc + c];
-        } else {
-          row[o_ac + c] = a; row[o_bc + c] = bb; row[o_cc + c] = w0; row[o_dc + c] = eps;
-        }
-      } break;
-      case CEL_TERM_PRODUCT: {                     // terms.py:236-277
-        const int ka = pl.k1[t], kb = pl.k2[t];
-        const double* qa = q;
-        const double* qb = q + term_npar(ka);
-        const Fac fa = fac_eval(ka, qa, pl.eps[t], bad), fb = fac_eval(kb, qb, pl.eps2[t], bad);
-        double ga1 = 0.0, gb1 = 0.0, gc1 = 0.0, gd1 = 0.0, ga2 = 0.0, gb2 = 0.0, gc2 = 0.0, gd2 = 0.0;
-        if (!fa.cplx && !fb.cplx) {                // real * real -> one real term
-          if (BACK) { ga1 = fb.a * g[o_ar + r]; ga2 = fa.a * g[o_ar + r]; gc1 = gc2 = g[o_cr + r]; }
-          else { row[o_ar + r] = fa.a * fb.a; row[o_cr + r] = fa.c + fb.c; }
-        } else if (fa.cplx != fb.cplx) {           // real * complex -> one complex term
-          const Fac& R = fa.cplx ? fb : fa;
-          const Fac& X = fa.cplx ? fa : fb;
-          if (BACK) {
-            const double gaR = X.a * g[o_ac + c] + X.b * g[o_bc + c], gcR = g[o_cc + c];
-            const double gaX = R.a * g[o_ac + c], gbX = R.a * g[o_bc + c], gcX = g[o_cc + c], gdX = g[o_dc + c];
-            if (fa.cplx) { ga1 = gaX; gb1 = gbX; gc1 = gcX; gd1 = gdX; ga2 = gaR; gc2 = gcR; }
-            else { ga1 = gaR; gc1 = gcR; ga2 = gaX; gb2 = gbX; gc2 = gcX; gd2 = gdX; }
-          } else {
-            row[o_ac + c] = R.a * X.a; row[o_bc + c] = R.a * X.b; row[o_cc + c] = R.c + X.c; row[o_dc + c] = X.d;
-          }
-        } else {                                   // complex * complex -> two complex terms
-          if (BACK) {
-            const double A0 = g[o_ac + c], B0 = g[o_bc + c], C0 = g[o_cc + c], D0 = g[o_dc + c];
-            const double A1 = g[o_ac + c + 1], B1 = g[o_bc + c + 1], C1 = g[o_cc + c + 1], D1 = g[o_dc + c + 1];
-            ga1 = 0.5 * (fb.a * A0 - fb.b * B0) + 0.5 * (fb.a * A1 + fb.b * B1);
-            gb1 = 0.5 * (fb.b * A0 + fb.a * B0) + 0.5 * (-fb.b * A1 + fb.a * B1);
-            ga2 = 0.5 * (fa.a * A0 + fa.b * B0) + 0.5 * (fa.a * A1 + fa.b * B1);
-            gb2 = 0.5 * (fa.b * A0 - fa.a * B0) + 0.5 * (-fa.b * A1 + fa.a * B1);
-            gc1 = gc2 = C0 + C1; gd1 = D0 + D1; gd2 = D1 - D0;
-          } else {
-            row[o_ac + c] = 0.5 * (fa.a * fb.a + fa.b * fb.b); row[o_bc + c] = 0.5 * (fa.b * fb.a - fa.a * fb.b);
-            row[o_cc + c] = fa.c + fb.c; row[o_dc + c] = fa.d - fb.d;
-            row[o_ac + c + 1] = 0.5 * (fa.a * fb.a - fa.b * fb.b); row[o_bc + c + 1] = 0.5 * (fa.b * fb.a + fa.a * fb.b);
-            row[o_cc + c + 1] = fa.c + fb.c; row[o_dc + c + 1] = fa.d + fb.d;
-          }
-        }
-        if (BACK) {
-          fac_back(ka, qa, pl.eps[t], fa, ga1, gb1, gc1, gd1, o);
-          fac_back(kb, qb, pl.eps2[t], fb, ga2, gb2, gc2, gd2, o + term_npar(ka));
-        }
-      } break;
-      default: break;
     }
   }
-  if (!BACK) row[0] = jitter;
-  if (status) status[b] = bad;
+  if (!BACK) {
+    double* row = coeffs + b * cstride;
+    row[0] = jitter;
+    for (int i = 0; i < Jr; ++i) { const Set s = slot[pl.real_out[i]]; row[o_ar + i] = s.a; row[o_cr + i] = s.c; }
+    for (int i = 0; i < Jc; ++i) {
+      const Set s = slot[pl.comp_out[i]];
+      row[o_ac + i] = s.a; row[o_bc + i] = s.b; row[o_cc + i] = s.c; row[o_dc + i] = s.d;
+    }
+    if (status) status[b] = bad;
+    return;
+  }
+  // ---- backward: one adjoint per slot, seeded from the row's gradient ----
+  const double* g = gc + b * gcstride;
+  double* out = gp + b * gpstride;
+  Set gs[kMaxSlots];
+  for (int i = 0; i < pl.nslots; ++i) { gs[i].a = 0.0; gs[i].b = 0.0; gs[i].c = 0.0; gs[i].d = 0.0; }
+  for (int i = 0; i < Jr; ++i) { Set& s = gs[pl.real_out[i]]; s.a += g[o_ar + i]; s.c += g[o_cr + i]; }
+  for (int i = 0; i < Jc; ++i) {
+    Set& s = gs[pl.comp_out[i]];
+    s.a += g[o_ac + i]; s.b += g[o_bc + i]; s.c += g[o_cc + i]; s.d += g[o_dc + i];
+  }
+  for (int i = pl.nops - 1; i >= 0; --i) {
+    const TermOp op = pl.ops[i];
+    switch (op.type) {
+      case OP_JITTER: out[op.a] = 2.0 * exp(2.0 * p[op.a]) * g[0]; break;
+      case OP_LEAF: leaf_back(op.kind, p + op.a, slot + op.out, gs + op.out, out + op.a); break;
+      case OP_MUL_RR: {
+        const Set x = slot[op.a], y = slot[op.b], r = gs[op.out];
+        gs[op.a].a += y.a * r.a; gs[op.a].c += r.c;
+        gs[op.b].a += x.a * r.a; gs[op.b].c += r.c;
+      } break;
+      case OP_MUL_RC: {
+        const Set x = slot[op.a], y = slot[op.b], r = gs[op.out];
+        gs[op.a].a += y.a * r.a + y.b * r.b; gs[op.a].c += r.c;
+        gs[op.b].a += x.a * r.a; gs[op.b].b += x.a * r.b; gs[op.b].c += r.c; gs[op.b].d += r.d;
+      } break;
+      default: {
+        const Set x = slot[op.a], y = slot[op.b], r0 = gs[op.out], r1 = gs[op.out + 1];
+        gs[op.a].a += 0.5 * (y.a * r0.a - y.b * r0.b) + 0.5 * (y.a * r1.a + y.b * r1.b);
+        gs[op.a].b += 0.5 * (y.b * r0.a + y.a * r0.b) + 0.5 * (-y.b * r1.a + y.a * r1.b);
+        gs[op.b].a += 0.5 * (x.a * r0.a + x.b * r0.b) + 0.5 * (x.a * r1.a + x.b * r1.b);
+        gs[op.b].b += 0.5 * (x.b * r0.a - x.a * r0.b) + 0.5 * (-x.b * r1.a + x.a * r1.b);
+        gs[op.a].c += r0.c + r1.c; gs[op.b].c += r0.c + r1.c;
+        gs[op.a].d += r0.d + r1.d; gs[op.b].d += r1.d - r0.d;
+      } break;
+    }
+  }
 }
 
-// a factor of a product: one coefficient set
-inline bool is_factor(int k) {
-  return k == CEL_TERM_REAL || k == CEL_TERM_COMPLEX3 || k == CEL_TERM_COMPLEX4 || k == CEL_TERM_SHO || k == CEL_TERM_MATERN32;
-}
+// ---- host: the prefix kind list -> the program ---------------------------------------------------
+struct Node { std::vector<short> real, comp; };
 
-// kinds (product nodes take three entries) -> nodes; returns false on a malformed list
-bool parse_plan(int nlist, const int* kinds, const double* eps, TermPlan& pl) {
-  if (nlist < 1 || nlist > kMaxTerms || !kinds) return false;
-  pl = TermPlan{};
-  int np = 0, jr = 0, jc = 0, n = 0;
-  for (int i = 0; i < nlist; ++n) {
-    const int k = kinds[i];
-    pl.kind[n] = k; pl.par0[n] = np; pl.real0[n] = jr; pl.comp0[n] = jc;
-    pl.eps[n] = eps ? eps[i] : 0.01;
-    if (k == CEL_TERM_PRODUCT) {
-      if (i + 2 >= nlist || !is_factor(kinds[i + 1]) || !is_factor(kinds[i + 2])) return false;
-      const int ka = kinds[i + 1], kb = kinds[i + 2];
-      pl.k1[n] = ka; pl.k2[n] = kb;
-      pl.eps[n] = eps ? eps[i + 1] : 0.01; pl.eps2[n] = eps ? eps[i + 2] : 0.01;
-      np += term_npar(ka) + term_npar(kb);
-      const int ncx = term_ncomp(ka) + term_ncomp(kb);      // complex factors among the two
-      jr += (ncx == 0) ? 1 : 0;
-      jc += (ncx == 1) ? 1 : (ncx == 2 ? 2 : 0);
-      i += 3;
+struct Builder {
+  TermPlan& pl;
+  const int* kinds;
+  const double* eps;
+  int n, pos = 0, nleaf = 0;
+  bool ok = true;
+  bool push(const TermOp& op, int nout) {
+    if (pl.nops >= kMaxOps || pl.nslots + nout > kMaxSlots) return ok = false;
+    pl.ops[pl.nops++] = op;
+    pl.nslots += nout;
+    return true;
+  }
+  // one operand of a product / sum, or a top-level entry (jitter only there: terms.py:221-224)
+  Node expr(bool top) {
+    Node r;
+    if (!ok || pos >= n) { ok = false; return r; }
+    const int at = pos, k = kinds[pos++];
+    if (k == CEL_TERM_PRODUCT || k == CEL_TERM_SUM) {
+      const Node x = expr(false), y = expr(false);
+      if (!ok) return r;
+      if (k == CEL_TERM_SUM) {                         // terms.py:305-314: array by array
+        r.real = x.real; r.real.insert(r.real.end(), y.real.begin(), y.real.end());
+        r.comp = x.comp; r.comp.insert(r.comp.end(), y.comp.begin(), y.comp.end());
+        return r;
+      }
+      for (short i : x.real)                           // real x real
+        for (short j : y.real) {
+          if (!push(TermOp{OP_MUL_RR, 0, i, j, (short)pl.nslots}, 1)) return r;
+          r.real.push_back((short)(pl.nslots - 1));
+        }
+      for (int pass = 0; pass < 2; ++pass) {           // real1 x complex2, then real2 x complex1
+        const Node& R = pass == 0 ? x : y;
+        const Node& X = pass == 0 ? y : x;
+        for (short i : R.real)
+          for (short j : X.comp) {
+            if (!push(TermOp{OP_MUL_RC, 0, i, j, (short)pl.nslots}, 1)) return r;
+            r.comp.push_back((short)(pl.nslots - 1));
+          }
+      }
+      for (short i : x.comp)                           // complex x complex: two sets each
+        for (short j : y.comp) {
+          if (!push(TermOp{OP_MUL_CC, 0, i, j, (short)pl.nslots}, 2)) return r;
+          r.comp.push_back((short)(pl.nslots - 2)); r.comp.push_back((short)(pl.nslots - 1));
+        }
+      return r;
+    }
+    const int np = term_npar(k);
+    if (np < 0 || (k == CEL_TERM_JITTER && !top) || nleaf >= kMaxLeaves) { ok = false; return r; }
+    if (k == CEL_TERM_JITTER) {
+      if (!push(TermOp{OP_JITTER, (unsigned char)k, (short)pl.npar, 0, 0}, 0)) return r;
     } else {
-      if (term_npar(k) < 0) return false;
-      np += term_npar(k); jr += term_nreal(k); jc += term_ncomp(k);
-      i += 1;
+      pl.eps[nleaf] = eps ? eps[at] : 0.01;
+      const int nout = k == CEL_TERM_SHO_OVERDAMPED ? 2 : 1;
+      if (!push(TermOp{OP_LEAF, (unsigned char)k, (short)pl.npar, (short)nleaf, (short)pl.nslots}, nout)) return r;
+      ++nleaf;
+      const bool cplx = k != CEL_TERM_REAL && k != CEL_TERM_SHO_OVERDAMPED;
+      for (int q = 0; q < nout; ++q) (cplx ? r.comp : r.real).push_back((short)(pl.nslots - nout + q));
     }
+    pl.npar += np;
+    return r;
   }
-  pl.nterms = n; pl.npar = np; pl.Jr = jr; pl.Jc = jc;
+};
+
+// returns false on a malformed list (unknown kind, operand missing, jitter inside a product, too large)
+bool parse_plan(int nlist, const int* kinds, const double* eps, TermPlan& pl) {
+  if (nlist < 1 || nlist > kMaxList || !kinds) return false;
+  pl = TermPlan{};
+  Builder bd{pl, kinds, eps, nlist};
+  std::vector<short> real, comp;
+  while (bd.ok && bd.pos < nlist) {
+    const Node t = bd.expr(true);
+    real.insert(real.end(), t.real.begin(), t.real.end());
+    comp.insert(comp.end(), t.comp.begin(), t.comp.end());
+  }
+  if (!bd.ok || real.size() > (size_t)kMaxSlots || comp.size() > (size_t)kMaxSlots) return false;
+  pl.Jr = (int)real.size(); pl.Jc = (int)comp.size();
+  for (int i = 0; i < pl.Jr; ++i) pl.real_out[i] = real[i];
+  for (int i = 0; i < pl.Jc; ++i) pl.comp_out[i] = comp[i];
   return true;
 }
 
 int make_plan(cel_solver* s, int nterms, const int* kinds, const double* eps, TermPlan& pl) {
   if (!parse_plan(nterms, kinds, eps, pl))
-    CEL_FAIL(s, CEL_INVALID_ARGUMENT, "term list: 1..32 entries of known kinds; a product is followed by its two factors");
+    CEL_FAIL(s, CEL_INVALID_ARGUMENT,
+             "term list: 1..64 entries of known kinds in prefix order; a product / sum is followed by its two operands");
   return CEL_OK;
 }
 
@@ -305,9 +339,9 @@ int cel_term_coefficients(cel_solver* s, int nterms, const int* kinds, const dou
   if (param_stride < pl.npar || coeff_stride < 1 + 2 * pl.Jr + 4 * pl.Jc) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "stride too short");
   if (B == 0) return CEL_OK;
   CEL_CUDA_TRY(s, cudaSetDevice(s->device));
-  const unsigned grid = (unsigned)((B + 127) / 128);
-  cel::k_term_maps<false><<<grid, 128, 0, s->stream>>>(pl, B, d_params, param_stride, d_coeffs, coeff_stride, nullptr, 0,
-                                                       nullptr, 0, d_status);
+  const unsigned grid = (unsigned)((B + 63) / 64);
+  cel::k_term_maps<false><<<grid, 64, 0, s->stream>>>(pl, B, d_params, param_stride, d_coeffs, coeff_stride, nullptr, 0,
+                                                      nullptr, 0, d_status);
   CEL_CUDA_TRY(s, cudaGetLastError());
   s->launches += 1;
   return CEL_OK;
@@ -325,9 +359,9 @@ int cel_term_backprop(cel_solver* s, int nterms, const int* kinds, const double*
     CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "stride too short");
   if (B == 0) return CEL_OK;
   CEL_CUDA_TRY(s, cudaSetDevice(s->device));
-  const unsigned grid = (unsigned)((B + 127) / 128);
-  cel::k_term_maps<true><<<grid, 128, 0, s->stream>>>(pl, B, d_params, param_stride, nullptr, 0, d_grad_coeffs,
-                                                      grad_coeff_stride, d_grad_params, grad_param_stride, nullptr);
+  const unsigned grid = (unsigned)((B + 63) / 64);
+  cel::k_term_maps<true><<<grid, 64, 0, s->stream>>>(pl, B, d_params, param_stride, nullptr, 0, d_grad_coeffs,
+                                                     grad_coeff_stride, d_grad_params, grad_param_stride, nullptr);
   CEL_CUDA_TRY(s, cudaGetLastError());
   s->launches += 1;
   return CEL_OK;

@@ -22,7 +22,8 @@ import numpy as np
 from . import _capi
 from .batched import BatchedSolver
 
-KINDS = {"jitter": 0, "real": 1, "complex3": 2, "complex4": 3, "sho": 4, "sho_overdamped": 5, "matern32": 6}
+KINDS = {"jitter": 0, "real": 1, "complex3": 2, "complex4": 3, "sho": 4, "sho_overdamped": 5, "matern32": 6,
+         "product": 7, "sum": 8}
 _NAMES = {
     0: ("log_sigma",), 1: ("log_a", "log_c"), 2: ("log_a", "log_c", "log_d"),
     3: ("log_a", "log_b", "log_c", "log_d"), 4: ("log_S0", "log_Q", "log_omega0"),
@@ -31,20 +32,28 @@ _NAMES = {
 
 
 class TermSum(object):
-    """A sum of celerite terms, by kind (terms.py:280-324); an entry ``("product", k1, k2)`` is the
-    product of two one-coefficient-set terms (terms.py:218-277).  ``eps`` maps a position in the
-    flattened kind list to the Matern32Term approximation parameter (default 0.01, terms.py:549)."""
+    """A sum of celerite terms, by kind (terms.py:280-324).  An entry ``("product", x, y)`` is the product
+    ``x * y`` (terms.py:218-277) of two operands, each a kind, another product, or ``("sum", x, y)`` for
+    ``(x + y)``; every coefficient set of ``x`` meets every set of ``y`` as in the reference.  The kind list
+    may also be given already flattened to prefix order (7 = product, 8 = sum, each followed by its two
+    operands).  ``eps`` maps a position in the flattened list to the Matern32Term approximation parameter
+    (default 0.01, terms.py:549)."""
 
     def __init__(self, kinds, eps=None):
-        flat = []
-        for k in kinds:                                   # ("product", k1, k2) -> 7, k1, k2 (terms.py:218-277)
+        def flat(k):
             if isinstance(k, (tuple, list)):
-                if len(k) != 3 or k[0] != "product":
-                    raise ValueError('a product is written ("product", kind1, kind2)')
-                flat += [7, k[1], k[2]]
-            else:
-                flat.append(k)
-        self.kinds = np.array([KINDS[k] if isinstance(k, str) else int(k) for k in flat], dtype=np.int32)
+                if len(k) != 3 or k[0] not in ("product", "sum"):
+                    raise ValueError('a product is written ("product", x, y), a sum inside it ("sum", x, y)')
+                return [KINDS[k[0]]] + flat(k[1]) + flat(k[2])
+            if isinstance(k, str):
+                if k not in KINDS:
+                    raise ValueError("unknown term kind %r" % (k,))
+                return [KINDS[k]]
+            return [int(k)]
+        out = []
+        for k in kinds:
+            out += flat(k)
+        self.kinds = np.array(out, dtype=np.int32)
         self.eps = np.full(len(self.kinds), 0.01)
         for i, v in (eps or {}).items():
             self.eps[i] = v
@@ -52,23 +61,31 @@ class TermSum(object):
         rc = _capi.lib().cel_term_layout(len(self.kinds), C.c_void_p(self.kinds.ctypes.data), C.byref(npar),
                                          C.byref(jr), C.byref(jc))
         if rc != _capi.OK:
-            raise ValueError("unknown term kind, malformed product or more than 32 entries")
+            raise ValueError("unknown term kind, malformed product / sum, jitter inside a product, or too many entries")
         self.n_params, self.Jr, self.Jc = npar.value, jr.value, jc.value
         self.n_coeffs = 1 + 2 * self.Jr + 4 * self.Jc
 
     @property
     def parameter_names(self):
-        """Names in the reference's convention for sums: ``terms[i]:log_x`` (modeling.py)."""
-        names, i, node = [], 0, 0
-        while i < len(self.kinds):
-            k = int(self.kinds[i])
-            if k == 7:                                    # product: k1's parameters, then k2's
-                for tag, kk in (("k1", int(self.kinds[i + 1])), ("k2", int(self.kinds[i + 2]))):
-                    names += ["terms[%d]:%s:%s" % (node, tag, n) for n in _NAMES[kk]]
-                i += 3
-            else:
-                names += ["terms[%d]:%s" % (node, n) for n in _NAMES[k]]
-                i += 1
+        """Names in the reference's convention (modeling.py): ``terms[i]:log_x`` for the i-th term of the
+        sum, ``terms[i]:k1:log_x`` / ``:k2:`` inside a product, ``:terms[j]:`` inside a sum."""
+        names = []
+        kinds = [int(k) for k in self.kinds]
+
+        def walk(pos, prefix):
+            k = kinds[pos]
+            if k == 7:
+                pos = walk(pos + 1, prefix + "k1:")
+                return walk(pos, prefix + "k2:")
+            if k == 8:
+                pos = walk(pos + 1, prefix + "terms[0]:")
+                return walk(pos, prefix + "terms[1]:")
+            names.extend(prefix + n for n in _NAMES[k])
+            return pos + 1
+
+        pos = node = 0
+        while pos < len(kinds):
+            pos = walk(pos, "terms[%d]:" % node)
             node += 1
         return tuple(names)
 

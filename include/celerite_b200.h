@@ -312,8 +312,12 @@ int cel_grad_log_likelihood_static_scratch(int N, int Jr, int Jc, const double* 
 #define CEL_TERM_SHO 4
 #define CEL_TERM_SHO_OVERDAMPED 5
 #define CEL_TERM_MATERN32 6
-#define CEL_TERM_PRODUCT 7   /* k1 * k2 (terms.py:218-277): followed in `kinds` by its two factor kinds, each one
-                              of REAL, COMPLEX3, COMPLEX4, SHO, MATERN32; parameters: those of k1, then of k2 */
+#define CEL_TERM_PRODUCT 7   /* k1 * k2 (TermProduct, terms.py:218-277): `kinds` is a PREFIX expression, a product is
+                              followed by its two operands, each a term without jitter, another product or a
+                              CEL_TERM_SUM; parameters: those of k1, then of k2; every coefficient set of k1 is
+                              multiplied with every set of k2 in the reference's order */
+#define CEL_TERM_SUM 8       /* k1 + k2 as an operand of a product ((k1 + k2) * k3); at the top level terms are
+                              simply listed.  At most 64 entries, 96 coefficient sets in flight. */
 int cel_term_layout(int nterms, const int* kinds, int* n_params, int* Jr, int* Jc);
 int cel_term_coefficients(cel_solver* s, int nterms, const int* kinds, const double* eps, int64_t B,
                           const double* d_params, int64_t param_stride, double* d_coeffs,

@@ -16,7 +16,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, os.path.join(ROOT, "baseline", "_ref"))
 from celerite import terms  # noqa: E402
 
-KINDS = {"jitter": 0, "real": 1, "complex3": 2, "complex4": 3, "sho": 4, "sho_over": 5, "matern32": 6, "product": 7}
+KINDS = {"jitter": 0, "real": 1, "complex3": 2, "complex4": 3, "sho": 4, "sho_over": 5, "matern32": 6, "product": 7,
+         "sum": 8}
 SPECS = [
     ["sho"],
     ["sho", "jitter"],
@@ -28,14 +29,24 @@ SPECS = [
     [("product", "real", "real"), "jitter"],
     [("product", "sho", "real"), ("product", "complex4", "sho")],
     ["real", ("product", "real", "matern32"), ("product", "complex3", "complex4"), "sho"],
+    # nested products, sums inside products, factors with two coefficient sets
+    [("product", "sho_over", "sho")],
+    [("product", "sho_over", "sho_over"), "jitter"],
+    [("product", ("product", "real", "sho"), "complex3"), "real"],
+    [("product", ("sum", "real", "sho"), "sho_over"), "jitter"],
+    ["sho", ("product", ("sum", "real", "real"), ("sum", "sho", ("product", "matern32", "complex4")))],
 ]
 NPAR = {"jitter": 1, "real": 2, "complex3": 3, "complex4": 4, "sho": 3, "sho_over": 3, "matern32": 2}
 
 
 def flatten(names):
+    """nested spec -> prefix list of names"""
     out = []
     for n in names:
-        out += (["product", n[1], n[2]] if isinstance(n, tuple) else [n])
+        if isinstance(n, tuple):
+            out += [n[0]] + flatten([n[1]]) + flatten([n[2]])
+        else:
+            out.append(n)
     return out
 
 
@@ -72,33 +83,26 @@ def one(name, q, eps):
 
 def build(names, params, epss):
     """names: nested spec; epss: one value per FLATTENED position."""
-    ts, o, pos = [], 0, 0
-    for name in names:
+    state = {"o": 0, "pos": 0}
+
+    def node(name):
         if isinstance(name, tuple):
-            n1, n2 = NPAR[name[1]], NPAR[name[2]]
-            k1 = one(name[1], params[o:o + n1], epss[pos + 1])
-            k2 = one(name[2], params[o + n1:o + n1 + n2], epss[pos + 2])
-            ts.append(k1 * k2)
-            o += n1 + n2
-            pos += 3
-            continue
-        eps = epss[pos]
-        pos += 1
+            state["pos"] += 1
+            k1 = node(name[1])
+            k2 = node(name[2])
+            return k1 * k2 if name[0] == "product" else k1 + k2
+        eps = epss[state["pos"]]
+        state["pos"] += 1
         n = NPAR[name]
-        q = params[o:o + n]
-        o += n
+        q = params[state["o"]:state["o"] + n]
+        state["o"] += n
         if name == "jitter":
-            ts.append(terms.JitterTerm(log_sigma=q[0]))
-        elif name == "real":
-            ts.append(terms.RealTerm(log_a=q[0], log_c=q[1]))
-        elif name == "complex3":
-            ts.append(terms.ComplexTerm(log_a=q[0], log_c=q[1], log_d=q[2]))
-        elif name == "complex4":
-            ts.append(terms.ComplexTerm(log_a=q[0], log_b=q[1], log_c=q[2], log_d=q[3]))
-        elif name in ("sho", "sho_over"):
-            ts.append(terms.SHOTerm(log_S0=q[0], log_Q=q[1], log_omega0=q[2]))
-        else:
-            ts.append(terms.Matern32Term(log_sigma=q[0], log_rho=q[1], eps=eps))
+            return terms.JitterTerm(log_sigma=q[0])
+        if name in ("sho", "sho_over"):
+            return terms.SHOTerm(log_S0=q[0], log_Q=q[1], log_omega0=q[2])
+        return one(name, q, eps)
+
+    ts = [node(name) for name in names]
     k = ts[0]
     for t in ts[1:]:
         k = k + t
@@ -120,7 +124,7 @@ def main():
         for w in range(5):
             ps, es = [], []
             for name in flatten(names):
-                if name == "product":
+                if name in ("product", "sum"):
                     es.append(0.0)
                     continue
                 q, e = draw(rng, name)

@@ -38,6 +38,14 @@ def test_term_layout_without_a_gpu(gold):
         assert len(spec.parameter_names) == spec.n_params
     with pytest.raises(ValueError):
         TermSum([99])
+    with pytest.raises(ValueError):                      # products are not implemented for terms with jitter (terms.py:221-224)
+        TermSum([("product", "jitter", "real")])
+    with pytest.raises(ValueError):                      # a product needs two operands
+        TermSum([7, 1])
+    nested = TermSum([("product", ("sum", "real", "sho"), "sho_overdamped"), "jitter"])
+    assert (nested.n_params, nested.Jr, nested.Jc) == (9, 2, 2)
+    assert nested.parameter_names[:3] == ("terms[0]:k1:terms[0]:log_a", "terms[0]:k1:terms[0]:log_c", "terms[0]:k1:terms[1]:log_S0")
+    assert nested.parameter_names[-1] == "terms[1]:log_sigma"
 
 
 @pytest.mark.gpu
