@@ -50,6 +50,8 @@ SIGNATURES = {
                                                          _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "cel_batched_compute": (C.c_int, [_vp, _i64, C.c_int, _i64, C.c_int, C.c_int, _vp, _i64,
                                       _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "cel_batched_compute_ragged": (C.c_int, [_vp, _i64, C.c_int, _i64, C.c_int, C.c_int, _vp, _i64,
+                                             _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "cel_grad_log_likelihood_static_scratch": (C.c_int, [C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp,
                                                          _vp, _vp, _vp, _vp]),
     "cel_solve_device": (C.c_int, [_vp, C.c_int, _vp, _vp]),

@@ -182,15 +182,20 @@ class BatchedSolver(object):
         _capi.check(rc, self._h)
         return val, grad, status
 
-    def compute(self, coeffs, t, diag, Jr, Jc):
+    def compute(self, coeffs, t, diag, Jr, Jc, lengths=None):
         """Batched CholeskySolver::compute (cholesky.h:41-210) on torch CUDA tensors: returns
         (phi, u, W, D, logdet, status) with phi,u: (B, N-1, J), W: (B, N, J), D: (B, N) — per
-        series the reference's factor layout (J fastest)."""
+        series the reference's factor layout (J fastest).  ``lengths`` (int32, shape (B,)): a ragged
+        batch, series b being the first lengths[b] entries of its row; its factor is valid in those
+        columns, the log-determinant and the status count its own steps only."""
         import torch
         for a in (coeffs, t, diag):
             if not (a.is_cuda and a.dtype == torch.float64 and a.is_contiguous()):
                 raise RuntimeError("expected contiguous float64 CUDA tensors")
         B, N, stride, cstride = self._shapes(coeffs, t, Jr, Jc)
+        if lengths is not None and not (lengths.is_cuda and lengths.dtype == torch.int32 and lengths.is_contiguous()
+                                        and lengths.shape == (B,)):
+            raise RuntimeError("lengths: contiguous int32 CUDA tensor of shape (B,)")
         J = Jr + 2 * Jc
         dev = t.device
         phi = torch.empty((B, max(N - 1, 0), J), dtype=torch.float64, device=dev)
@@ -201,8 +206,12 @@ class BatchedSolver(object):
         status = torch.empty(B, dtype=torch.int32, device=dev)
         self._lib.cel_set_stream(self._h, C.c_void_p(torch.cuda.current_stream(dev).cuda_stream or 1))
         p = lambda a: C.c_void_p(a.data_ptr())  # noqa: E731
-        rc = self._lib.cel_batched_compute(self._h, B, N, stride, Jr, Jc, p(coeffs), cstride, p(t), p(diag),
-                                           p(phi), p(u), p(W), p(D), p(logdet), p(status))
+        if lengths is not None:
+            rc = self._lib.cel_batched_compute_ragged(self._h, B, N, stride, Jr, Jc, p(coeffs), cstride, p(t), p(diag),
+                                                      p(lengths), p(phi), p(u), p(W), p(D), p(logdet), p(status))
+        else:
+            rc = self._lib.cel_batched_compute(self._h, B, N, stride, Jr, Jc, p(coeffs), cstride, p(t), p(diag),
+                                               p(phi), p(u), p(W), p(D), p(logdet), p(status))
         _capi.check(rc, self._h)
         return phi, u, W, D, logdet, status
 

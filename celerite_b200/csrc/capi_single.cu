@@ -919,4 +919,28 @@ int cel_batched_compute(cel_solver* s, int64_t B, int N, int64_t stride, int Jr,
   return CEL_OK;
 }
 
+// ragged batch: series b occupies the first lengths[b] entries of its row (cooperative kernel, J <= 32)
+int cel_batched_compute_ragged(cel_solver* s, int64_t B, int N, int64_t stride, int Jr, int Jc, const double* d_coeffs,
+                               int64_t coeff_stride, const double* d_t, const double* d_diag, const int32_t* d_lengths,
+                               double* phi, double* u, double* W, double* D, double* out_logdet, int32_t* status) {
+  if (!s) return CEL_INVALID_ARGUMENT;
+  if (B < 0 || N < 1 || Jr < 0 || Jc < 0 || stride < 0 || coeff_stride < 0)
+    CEL_FAIL(s, CEL_INVALID_ARGUMENT, "negative size");
+  if (stride != 0 && stride < N) CEL_FAIL(s, CEL_DIMENSION_MISMATCH, "stride < N");
+  const int J = Jr + 2 * Jc;
+  if (J < 1 || J > cel::kCoopMaxJ) CEL_FAIL(s, CEL_UNSUPPORTED, "ragged batched compute supports 1 <= J <= 32");
+  if (!d_coeffs || !d_t || !d_diag || !d_lengths || !phi || !u || !W || !D) CEL_FAIL(s, CEL_INVALID_ARGUMENT, "null pointer");
+  if (B == 0) return CEL_OK;
+  CEL_CUDA_TRY(s, cudaSetDevice(s->device));
+  cel::BatchArgs a{};
+  a.B = B; a.N = N; a.stride = stride; a.Jr = Jr; a.Jc = Jc; a.Jg = 0;
+  a.coeffs = d_coeffs; a.coeff_stride = coeff_stride;
+  a.t = d_t; a.diag = d_diag; a.y = nullptr; a.lengths = d_lengths;
+  a.out_logdet = out_logdet; a.status = status;
+  a.phi = phi; a.u = u; a.W = W; a.D = D;
+  CEL_CUDA_TRY(s, cel::launch_loglik_coop(a, s->stream));
+  s->launches += 1;
+  return CEL_OK;
+}
+
 }  // extern "C"

@@ -179,6 +179,14 @@ int cel_batched_compute(cel_solver* s, int64_t B, int N, int64_t stride,
                         const double* t, const double* diag,
                         double* phi, double* u, double* W, double* D, double* out_logdet,
                         int32_t* status);
+/* The same for a ragged batch (rows padded to N, series b = the first d_lengths[b] entries of its row; J <= 32):
+ * the factor of series b is valid in columns [0, d_lengths[b]) of its blocks, the rest is unspecified;
+ * log-determinant and status count the series' own steps only (cholesky.h:176, :208). */
+int cel_batched_compute_ragged(cel_solver* s, int64_t B, int N, int64_t stride,
+                               int Jr, int Jc, const double* d_coeffs, int64_t coeff_stride,
+                               const double* d_t, const double* d_diag, const int32_t* d_lengths,
+                               double* phi, double* u, double* W, double* D, double* out_logdet,
+                               int32_t* status);
 
 /* ---- long single series: chunked two-pass scans on device-resident data -------------------
  * (no counterpart in the reference, whose sweeps are N dependent steps on one thread,

@@ -192,6 +192,42 @@ def test_batched_compute_materialises_reference_factor(bs, B, N, Jr, Jc):
             chk.release(f)
 
 
+@pytest.mark.parametrize("B,N,Jr,Jc", [(40, 300, 0, 1), (21, 257, 1, 2), (9, 200, 2, 7)])
+def test_ragged_batched_compute(bs, B, N, Jr, Jc):
+    """cel_batched_compute_ragged: every series is factorised over its own length whatever its padding holds
+    (a negative diagonal there included); log-determinant and status count the series' own steps; lengths
+    N, 1 and 2 among them.  Factor columns beyond a series' length are unspecified and not looked at."""
+    import torch
+    from celerite_b200 import synth
+    from tests.util import RTOL_SOLVE
+    b = synth.make_batch(B, N, Jr, Jc, seed=7 * B + N)
+    rng = np.random.default_rng(B + N)
+    lengths = rng.integers(3, N + 1, B).astype(np.int32)
+    lengths[0], lengths[1], lengths[2] = N, 1, 2
+    for i in range(B):
+        b["diag"][i, lengths[i]:] = -1.0e3           # padding that would fail the factorisation if it counted
+        b["t"][i, lengths[i]:] = 0.0                 # ... and is not even sorted
+    dev = torch.device("cuda:0")
+    tt = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)  # noqa: E731
+    phi, u, W, D, logdet, status = bs.compute(tt(b["coeffs"]), tt(b["t"]), tt(b["diag"]), Jr, Jc, lengths=tt(lengths))
+    torch.cuda.synchronize()
+    assert int(status.sum()) == 0
+    chk = oracle.best()
+    for i in range(B):
+        n = int(lengths[i])
+        j, ar, cr, ac, bc, cc, dc = synth.split_row(b["coeffs"][i], Jr, Jc)
+        p = oracle.Problem(j, ar, cr, ac, bc, cc, dc, b["t"][i, :n].copy(), b["diag"][i, :n].copy())
+        f = chk.factor(p)
+        if n > 1:
+            assert rel_inf(phi[i, :n - 1].cpu().numpy(), f.phi) < RTOL_SOLVE
+            assert rel_inf(u[i, :n - 1].cpu().numpy(), f.u) < RTOL_SOLVE
+        assert rel_inf(W[i, :n].cpu().numpy(), f.W) < RTOL_SOLVE
+        assert rel_inf(D[i, :n].cpu().numpy(), f.D) < RTOL_SOLVE
+        assert rel_sum(float(logdet[i]), f.log_det, n) < RTOL_SCALAR
+        if hasattr(chk, "release"):
+            chk.release(f)
+
+
 def test_wide_kernels_batched_gradient_and_limit(bs):
     """J = 37 (3 real + 17 complex): value and all 1 + 2*3 + 4*17 derivatives of a small batch against the
     reference's forward-mode AD; and the width the library refuses (J > 96)."""
