@@ -37,11 +37,15 @@ namespace {
 
 constexpr int pow2ceil(int x) { return x <= 1 ? 1 : x <= 2 ? 2 : x <= 4 ? 4 : x <= 8 ? 8 : x <= 16 ? 16 : 32; }
 
-template <int JP>
+// MODE: see k_grad_coop (only the probe pass of the adjoint scan, MODE 1, keeps a transfer matrix in shared memory)
+template <int JP, int MODE = 0>
 struct GradCfg {
   static constexpr int L = pow2ceil(JP);
   static constexpr int G = kWarp / L;
-  static constexpr int T = 16;
+  // Shared memory decides how many warps an SM holds (255 registers allow 8): at J > 16 a warp is ONE series,
+  // and config 3 (1,024 series) wants all of them resident at once -- 7 per SM -- instead of a second, nearly
+  // empty wave.  Tiles of 8 steps and ring slots of the packed triangle (not J x J) keep J = 32 at 31 KB.
+  static constexpr int T = JP >= 24 ? 8 : 16;
   static constexpr int JJ = JP * JP;
   // The J x J blocks of the records (P_n on the tape, S in a checkpoint) are symmetric: only the upper
   // triangle is kept, packed by columns (entry (k, j), k <= j, at j(j+1)/2 + k; lanes 0..j write column j
@@ -52,11 +56,12 @@ struct GradCfg {
   static constexpr int kIn = 3 * T + 2;
   static constexpr int kGen = 4 * T * JP;          // phi, u, v, phi o u
   static constexpr int kX = 4 * JP;                  // [2][2*JP] exchange rows
-  static constexpr int RD = JP >= 24 ? 2 : 4;        // cp.async ring: tape blocks staged RD-1 steps ahead
-  static constexpr int kP = RD * JJ;
+  static constexpr int RD = 4;                       // cp.async ring: tape blocks staged RD-1 steps ahead
+  static constexpr int kSlot = BLK;                  // one ring slot: the packed triangle of a tape record
+  static constexpr int kP = RD * kSlot;
   static constexpr int kCoef = 4 * JP + 2;
   static constexpr int kR = 6 * JP;
-  static constexpr int kM = JP * JP;                 // transfer matrix of a span (scan modes only)
+  static constexpr int kM = MODE == 1 ? JP * JP : 0; // transfer matrix of a span (probe pass of the adjoint scan)
   static constexpr int kGroup = kIn + kGen + kX + kP + kCoef + kR + kM;
   // per span, exchanged between the scan passes (GradArgs::adj): M | P0 | g0 | P_in | g_in
   static constexpr int kAdj = 3 * JP * JP + 2 * JP;
@@ -94,8 +99,8 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 //                   fall-back when the factorisation does not forget fast enough for warm-up halos.
 template <int JP, bool SPAN = false, int MODE = 0>
 __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
-  using C = GradCfg<JP>;
-  constexpr int L = C::L, G = C::G, T = C::T, JJ = C::JJ, E = C::E, BLK = C::BLK;
+  using C = GradCfg<JP, MODE>;
+  constexpr int L = C::L, G = C::G, T = C::T, E = C::E, BLK = C::BLK;
   constexpr int kGenIlp = 4;   // generator items per lane evaluated together (8 spills here: 23.8 -> 25.4 ms at J = 8)
   extern __shared__ __align__(16) double smem[];
   const int lane = threadIdx.x, g = lane / L, k = lane % L;
@@ -487,7 +492,7 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
     auto stage_block = [&](int n) {
       if (n >= seg0) {
         const double* src = tape + (size_t)(n - seg0) * E;
-        double* dst = p_s + (n & (C::RD - 1)) * JJ;
+        double* dst = p_s + (n & (C::RD - 1)) * C::kSlot;
         for (int e = 2 * k; e < BLK; e += 2 * L) cp_async16(dst + e, src + e);
       }
       cp_async_commit();
@@ -560,29 +565,41 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
         const double fbar = gbar - xbar * uk;
         const double gprev = row_ok ? fma(Wm, xm, fm) : 0.0;
         gbar = phk * fbar;
-        const double* pb = p_s + (n & (C::RD - 1)) * JJ;
-        const double hw = 0.5 * w, hu = 0.5 * uk, du = Dbar * uk;
-        double aSw = 0.0, aSu = 0.0, aphi0 = 0.0, aphi1 = 0.0, aP0 = 0.0, aP1 = 0.0, aP2 = 0.0, aP3 = 0.0;
+        const double* pb = p_s + (n & (C::RD - 1)) * C::kSlot;
+        // sb_kj = Pb_kj - 1/2 (w_k u_j + u_k w_j) - Dbar u_k u_j = Pb_kj - (w_k / 2 + Dbar u_k) u_j - (u_k / 2) w_j
+        const double hu = 0.5 * uk, hwdu = fma(Dbar, uk, 0.5 * w);
+        constexpr bool kAllRows = (JP == L);             // no idle lanes in a group: nothing to mask
+        double aSw0 = 0.0, aSw1 = 0.0, aSu0 = 0.0, aSu1 = 0.0, aphi0 = 0.0, aphi1 = 0.0;
+        double aP0 = 0.0, aP1 = 0.0, aP2 = 0.0, aP3 = 0.0;
 #pragma unroll
-        for (int j = 0; j < JP; ++j) {
-          const double p = pb[pidx(j)];
-          const double pj = ph[j], uj = uu[j], wj = xch[j], wmj = xch[JP + j];
-          const double pp = phk * pj;
-          const double sv = pp * p;
-          aSw = fma(sv, wj, aSw);
-          aSu = fma(sv, uj, aSu);
-          double sb = Pb[j];
-          sb = fma(-hw, uj, sb);
-          sb = fma(-hu, wj, sb);
-          sb = fma(-du, uj, sb);
-          const double pn = pp * sb;
-          Pb[j] = row_ok ? pn : 0.0;
-          if (j & 1) aphi1 = fma(sb * p, pj, aphi1); else aphi0 = fma(sb * p, pj, aphi0);
-          if ((j & 3) == 0) aP0 = fma(pn, wmj, aP0);
-          else if ((j & 3) == 1) aP1 = fma(pn, wmj, aP1);
-          else if ((j & 3) == 2) aP2 = fma(pn, wmj, aP2);
-          else aP3 = fma(pn, wmj, aP3);
+        for (int j = 0; j < JP; j += 2) {
+          const double2 ph2 = *reinterpret_cast<const double2*>(ph + j);
+          const double2 uu2 = *reinterpret_cast<const double2*>(uu + j);
+          const double2 w2 = *reinterpret_cast<const double2*>(xch + j);
+          const double2 wm2 = *reinterpret_cast<const double2*>(xch + JP + j);
+          const double pa = pb[pidx(j)], pc = pb[pidx(j + 1)];
+          {
+            const double pp = phk * ph2.x, q = pa * ph2.x, sv = phk * q;
+            aSw0 = fma(sv, w2.x, aSw0);
+            aSu0 = fma(sv, uu2.x, aSu0);
+            const double sb = fma(-hwdu, uu2.x, fma(-hu, w2.x, Pb[j]));
+            const double pn = pp * sb;
+            Pb[j] = (kAllRows || row_ok) ? pn : 0.0;
+            aphi0 = fma(sb, q, aphi0);
+            if ((j & 2) == 0) aP0 = fma(pn, wm2.x, aP0); else aP2 = fma(pn, wm2.x, aP2);
+          }
+          {
+            const double pp = phk * ph2.y, q = pc * ph2.y, sv = phk * q;
+            aSw1 = fma(sv, w2.y, aSw1);
+            aSu1 = fma(sv, uu2.y, aSu1);
+            const double sb = fma(-hwdu, uu2.y, fma(-hu, w2.y, Pb[j + 1]));
+            const double pn = pp * sb;
+            Pb[j + 1] = (kAllRows || row_ok) ? pn : 0.0;
+            aphi1 = fma(sb, q, aphi1);
+            if ((j & 2) == 0) aP1 = fma(pn, wm2.y, aP1); else aP3 = fma(pn, wm2.y, aP3);
+          }
         }
+        const double aSw = aSw0 + aSw1, aSu = aSu0 + aSu1;
         PbW = row_ok ? (aP0 + aP1) + (aP2 + aP3) : 0.0;
         const double ubar = om * (-xbar * (row_ok ? fn : 0.0) - (aSw + 2.0 * Dbar * aSu));
         const double phibar = om * fma(2.0, aphi0 + aphi1, fbar * gprev);
@@ -695,7 +712,7 @@ cudaError_t launch_span(const GradArgs& a, cudaStream_t stream) {
 
 template <int JP, int MODE>
 cudaError_t launch_scan_mode(const GradArgs& a, cudaStream_t stream) {
-  using C = GradCfg<JP>;
+  using C = GradCfg<JP, MODE>;
   auto kern = k_grad_coop<JP, MODE != 3, MODE>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::smem);
   if (e != cudaSuccess) return e;
