@@ -745,6 +745,7 @@ int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t str
   auto scratch_need = [&](int64_t nb) {
     size_t n = cel::grad_scratch_doubles(nb, N, J, seg);
     if (lock) { const size_t m = cel::grad_lockstep_scratch_doubles(nb, N, Jc, seg); if (m > n) n = m; }
+    else { const size_t m = cel::grad_batch_scan_scratch_doubles(nb, N, J); if (m > n) n = m; }
     return dbytes(n);
   };
   auto launch = [&](cel::GradArgs& ga) -> cudaError_t {
@@ -752,6 +753,10 @@ int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t str
     int nl = 0;
     if (lock) {
       cudaError_t e = cel::launch_grad_lockstep(ga, st, &used, &nl);
+      if (e != cudaSuccess) return e;
+    }
+    if (!used && !lock) {       // few long series on the cooperative kernel: forward sweep + adjoint scan over spans
+      cudaError_t e = cel::launch_grad_batch_scan(ga, st, &used, &nl);
       if (e != cudaSuccess) return e;
     }
     s->launches += used ? nl : 1;

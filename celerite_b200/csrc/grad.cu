@@ -25,6 +25,7 @@
 // written with fully coalesced accesses; in the reverse pass the next block is staged into
 // shared memory with cp.async while the current step computes.
 #include <cfloat>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "fastmath.cuh"
@@ -107,8 +108,10 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   const long long b = (long long)blockIdx.x * G + g;
   const bool active = b < a.B;
   const long long bb = active ? b : a.B - 1;
-  // spans of ONE series share series 0 (stride 0); a ragged batch gives every series one span
-  const long long sb = (SPAN && a.stride == 0) ? 0 : bb;
+  // spans of ONE series share series 0 (stride 0); a ragged batch gives every series one span; the scan over
+  // a batch cuts every series into spans_per_series spans
+  const long long sb = (SPAN && a.spans_per_series > 0 && a.stride != 0) ? bb / a.spans_per_series
+                                                                          : ((SPAN && a.stride == 0) ? 0 : bb);
   const unsigned gmask = SPAN ? group_mask<L>(g) : kFull;
 
   double2* trig_tab = reinterpret_cast<double2*>(smem + C::kTabOff);
@@ -147,7 +150,8 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   auto ckpt_rec = [&](int s) -> double* {
     if (MODE == 3) {
       const int spg = a.span_nseg_max;
-      return a.scratch + (size_t)(s / spg) * ((size_t)(spg + Cseg) * E) + (size_t)(s % spg) * E;
+      const size_t unit = (size_t)bb * (a.spans_per_series > 0 ? a.spans_per_series : 0) + (size_t)(s / spg);
+      return a.scratch + unit * ((size_t)(spg + Cseg) * E) + (size_t)(s % spg) * E;
     }
     return ckpt + (size_t)s * E;
   };
@@ -726,6 +730,7 @@ cudaError_t launch_scan_mode(const GradArgs& a, cudaStream_t stream) {
 template <int JP>
 __global__ void __launch_bounds__(JP * JP) k_adj_fold(int K, double* adj) {
   constexpr int JJ = JP * JP, kAdj = GradCfg<JP>::kAdj;
+  adj += (size_t)blockIdx.x * K * kAdj;                 // a batch: one CTA per series
   __shared__ double Ms[JJ], Ps[JJ], Ts[JJ], gs[JP], g0s[JP], Mg[JP];
   const int tid = threadIdx.x, i = tid / JP, j = tid % JP;
   Ps[tid] = 0.0;
@@ -770,8 +775,8 @@ __global__ void __launch_bounds__(JP * JP) k_adj_fold(int K, double* adj) {
 }
 
 template <int JP>
-cudaError_t launch_fold(int K, double* adj, cudaStream_t stream) {
-  k_adj_fold<JP><<<1, JP * JP, 0, stream>>>(K, adj);
+cudaError_t launch_fold(int K, double* adj, cudaStream_t stream, long long nseries) {
+  k_adj_fold<JP><<<(unsigned)nseries, JP * JP, 0, stream>>>(K, adj);
   return cudaGetLastError();
 }
 
@@ -922,17 +927,106 @@ size_t grad_scan_adj_doubles(int K, int J) {
   return (size_t)K * (3 * JP * JP + 2 * JP);
 }
 
-cudaError_t launch_grad_scan_fold(int K, int J, double* adj, cudaStream_t stream) {
+cudaError_t launch_grad_scan_fold(int K, int J, double* adj, cudaStream_t stream, long long nseries) {
   switch (grad_jp(J)) {
-    case 2: return launch_fold<2>(K, adj, stream);
-    case 4: return launch_fold<4>(K, adj, stream);
-    case 6: return launch_fold<6>(K, adj, stream);
-    case 8: return launch_fold<8>(K, adj, stream);
-    case 12: return launch_fold<12>(K, adj, stream);
-    case 16: return launch_fold<16>(K, adj, stream);
-    case 24: return launch_fold<24>(K, adj, stream);
-    default: return launch_fold<32>(K, adj, stream);
+    case 2: return launch_fold<2>(K, adj, stream, nseries);
+    case 4: return launch_fold<4>(K, adj, stream, nseries);
+    case 6: return launch_fold<6>(K, adj, stream, nseries);
+    case 8: return launch_fold<8>(K, adj, stream, nseries);
+    case 12: return launch_fold<12>(K, adj, stream, nseries);
+    case 16: return launch_fold<16>(K, adj, stream, nseries);
+    case 24: return launch_fold<24>(K, adj, stream, nseries);
+    default: return launch_fold<32>(K, adj, stream, nseries);
   }
+}
+
+// ---- batches of few long series: forward sweep per series, adjoint scan over K spans of each ----------------
+namespace {
+struct BatchScanPlan { int K, len, seg; size_t ck, adj, part; };
+
+// K spans per series so that the spans fill the warps the GPU holds (8 per SM at 255 registers).  The scan
+// costs a second adjoint pass and throughput grows only like ~warps^0.45 (measured, 1,024 x 1e5: J = 4, 128
+// warps: 97 ms whole series, 106 ms at K = 4, 79 ms at K = 9; J = 8, 256 warps: 116 ms against 131 ms at
+// K = 4), so it is used from K = 6 on: batches of a few dozen long series gain 3-4x.  1 = not worth it
+BatchScanPlan plan_batch_scan(long long B, int N, int J) {
+  BatchScanPlan p{1, N, 0, 0, 0, 0};
+  static const bool off = getenv("CEL_GRAD_NO_BATCH_SCAN") != nullptr;   // A/B knob
+  if (off || J < 1 || J > 16 || N < 4096) return p;                      // (J > 16: a warp per series, B warps fill the GPU)
+  const int JP = grad_jp(J), G = kWarp / pow2ceil(JP);
+  const long long warps = (B + G - 1) / G, slots = (long long)sm_count() * 8;
+  long long K = slots / warps;
+  if (K < 6) return p;
+  const int seg = 64;
+  long long len = ((N + K - 1) / K + seg - 1) / seg * seg;
+  if (len < 8 * seg) len = 8 * seg;
+  K = (N + len - 1) / len;
+  if (K < 6) return p;
+  const size_t E = (((size_t)JP * (JP + 1) / 2 + 1) & ~(size_t)1) + 2 * JP + 2;
+  p.K = (int)K; p.len = (int)len; p.seg = seg;
+  const size_t units = (((size_t)B * K + G - 1) / G) * G;
+  p.ck = units * ((size_t)(len / seg) + seg) * E;
+  p.adj = (size_t)B * K * (3 * JP * JP + 2 * JP);
+  p.part = (size_t)B * K * (1 + 2 * (size_t)J + 1);   // >= P = 1 + 2Jr + 4Jc doubles per span
+  return p;
+}
+
+__global__ void k_uniform_spans(long long units, int K, int len, int N, int* span) {
+  const long long u = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= units) return;
+  const int c = (int)(u % K), own0 = c * len, own1 = min(N, own0 + len);
+  span[4 * u] = own0; span[4 * u + 1] = own0; span[4 * u + 2] = own1; span[4 * u + 3] = own1;
+}
+
+// the spans' gradient sums in span order; failed series (status from the forward sweep) get NaN
+__global__ void k_grad_batch_finish(long long B, int K, int P, const double* part, const int* st, double* out_grad, int* status) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * P) return;
+  const long long b = i / P;
+  const int e = (int)(i - b * P);
+  double acc = 0.0;
+  for (int c = 0; c < K; ++c) acc += part[((size_t)b * K + c) * P + e];
+  out_grad[i] = st[b] ? __longlong_as_double(0x7ff8000000000000LL) : acc;
+  if (e == 0 && status) status[b] = st[b];
+}
+}  // namespace
+
+size_t grad_batch_scan_scratch_doubles(long long B, int N, int J) {
+  const BatchScanPlan p = plan_batch_scan(B, N, J);
+  if (p.K < 2) return 0;
+  return p.ck + p.adj + p.part + ((size_t)B * p.K * 4 + (size_t)B + 2) / 2 + 8;
+}
+
+cudaError_t launch_grad_batch_scan(const GradArgs& a, cudaStream_t stream, bool* used, int* launches) {
+  *used = false;
+  const int J = a.Jr + 2 * a.Jc, P = 1 + 2 * a.Jr + 4 * a.Jc;
+  if (a.Jg != 0 || a.A || a.span || a.stride <= 0) return cudaSuccess;
+  const BatchScanPlan p = plan_batch_scan(a.B, a.N, J);
+  if (p.K < 2) return cudaSuccess;
+  const long long units = a.B * p.K;
+  double* d_adj = a.scratch + p.ck;
+  double* d_part = d_adj + p.adj;
+  int* d_span = reinterpret_cast<int*>(d_part + p.part);
+  int* d_st = d_span + 4 * units;
+  k_uniform_spans<<<(unsigned)((units + 255) / 256), 256, 0, stream>>>(units, p.K, p.len, a.N, d_span);
+  GradArgs f = a;                                      // forward sweep: values, status, checkpoints
+  f.seg = p.seg; f.span = nullptr; f.span_nseg_max = p.len / p.seg; f.spans_per_series = p.K; f.status = d_st;
+  cudaError_t e = launch_grad_scan(f, 3, stream);
+  if (e != cudaSuccess) return e;
+  GradArgs sa = f;
+  sa.B = units; sa.span = d_span; sa.span_edge = nullptr; sa.adj = d_adj; sa.have_ckpt = 1;
+  sa.out_val = nullptr; sa.out_logdet = nullptr; sa.out_quad = nullptr; sa.status = nullptr; sa.out_grad = d_part;
+  e = launch_grad_scan(sa, 1, stream);
+  if (e != cudaSuccess) return e;
+  e = launch_grad_scan_fold(p.K, J, d_adj, stream, a.B);
+  if (e != cudaSuccess) return e;
+  e = launch_grad_scan(sa, 2, stream);
+  if (e != cudaSuccess) return e;
+  k_grad_batch_finish<<<(unsigned)((a.B * P + 255) / 256), 256, 0, stream>>>(a.B, p.K, P, d_part, d_st, a.out_grad, a.status);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  if (launches) *launches += 6;
+  *used = true;
+  return cudaSuccess;
 }
 
 namespace {

@@ -132,6 +132,7 @@ struct GradArgs {
   // the exact time-parallel adjoint (launch_grad_scan): per span M | P0 | g0 | P_in | g_in, grad_scan_adj_doubles
   double* adj;
   int have_ckpt;        // mode 1: the forward sweep (mode 3) has already left the checkpoints
+  int spans_per_series; // scan modes over a BATCH: span u belongs to series u / spans_per_series (0: see `span`)
 };
 // One long series by time spans (grad.cu); launch_grad_span_finish adds the partial results up in
 // span order: result[0] = value, result[1] = worst relative mismatch between neighbouring spans
@@ -139,7 +140,12 @@ struct GradArgs {
 cudaError_t launch_grad_spans(const GradArgs& a, cudaStream_t stream);
 cudaError_t launch_grad_scan(const GradArgs& a, int mode, cudaStream_t stream);
 size_t grad_scan_adj_doubles(int K, int J);
-cudaError_t launch_grad_scan_fold(int K, int J, double* adj, cudaStream_t stream);
+cudaError_t launch_grad_scan_fold(int K, int J, double* adj, cudaStream_t stream, long long nseries = 1);
+// Batches of FEW LONG series on the cooperative kernel: forward sweep per series (mode 3), then the exact
+// time-parallel adjoint over spans_per_series spans of every series.  `a` as for launch_grad_coop, with
+// a.scratch of grad_batch_scan_scratch_doubles; *used = false when the shape does not call for it.
+size_t grad_batch_scan_scratch_doubles(long long B, int N, int J);
+cudaError_t launch_grad_batch_scan(const GradArgs& a, cudaStream_t stream, bool* used, int* launches);
 cudaError_t launch_grad_span_finish(const GradArgs& a, double* result, cudaStream_t stream);
 // ragged batches: span[4b..] = {0, 0, len_b, len_b}; then launch_grad_spans with stride > 0, span_edge NULL
 cudaError_t launch_ragged_spans(long long B, int N, const int* lengths, int* span, cudaStream_t stream);

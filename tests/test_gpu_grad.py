@@ -197,3 +197,37 @@ def test_two_kernel_gradient_redoes_series_that_leave_the_fast_path():
             continue
         assert rel_grad(g[i], gref) < tol_g, (i, g[i], gref)
     assert g[nojit, 0] == 0.0 and g[0, 0] != 0.0
+
+
+@pytest.mark.parametrize("B,N,Jr,Jc", [(40, 30000, 1, 1), (100, 8192, 0, 3), (17, 20001, 2, 0), (6, 50000, 0, 8)])
+def test_few_long_series_take_the_batched_adjoint_scan(B, N, Jr, Jc):
+    """Batches that leave most of the GPU empty with a group of lanes per whole series (few series, N >= 4096,
+    J <= 16) run as a forward sweep per series followed by the exact adjoint scan over spans of every series
+    (grad.cu, launch_grad_batch_scan: 6 launches); value, gradient and status against the reference, with one
+    series that is not positive definite."""
+    import torch
+    from celerite_b200 import synth
+    from celerite_b200.batched import BatchedSolver
+    b = synth.make_batch(B, N, Jr, Jc, seed=B + N)
+    bad = B // 2
+    b["diag"][bad, N // 3] = -80.0
+    dev = torch.device("cuda:0")
+    tt = lambda a: torch.from_numpy(a).to(dev)  # noqa: E731
+    bs = BatchedSolver()
+    n0 = bs._lib.cel_launch_count(bs._h)
+    val, g, status = bs.grad_log_likelihood(tt(b["coeffs"]), tt(b["t"]), tt(b["diag"]), tt(b["y"]), Jr, Jc)
+    torch.cuda.synchronize()
+    assert bs._lib.cel_launch_count(bs._h) - n0 == 6
+    val, g, status = val.cpu().numpy(), g.cpu().numpy(), status.cpu().numpy()
+    chk = oracle.best()
+    for i in sorted(set([0, 1, bad, B - 1] + list(range(0, B, max(1, B // 5))))):
+        j, ar, cr, ac, bc, cc, dc = synth.split_row(b["coeffs"][i], Jr, Jc)
+        p = oracle.Problem(j, ar, cr, ac, bc, cc, dc, b["t"][i], b["diag"][i])
+        st, vref, gref = chk.grad(p, b["y"][i])
+        if i == bad:
+            assert st != 0 and status[i] == 3 and np.isnan(val[i]) and np.all(np.isnan(g[i]))
+            continue
+        assert st == 0 and status[i] == 0
+        vref += 0.5 * np.pi * np.log(N)
+        assert rel_sum(val[i], vref, N) < RTOL_SCALAR
+        assert rel_grad(g[i], gref) < RTOL_GRAD, (i, g[i], gref)
