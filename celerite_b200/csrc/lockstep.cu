@@ -462,11 +462,13 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
         load_gen(src, 0, pa);
         load_gen(src, 1, pb); rec_book(pa);
         load_gen(src, 2, pa); rec_book(pb);
+        if (CKPT && k * T + 4 < N) checkpoint((k * T + 4) / kGrad2Seg);
         load_gen(src, 3, pb);
         __syncwarp();              // the tile is in registers on every lane: refill its slot
         if (k + STAGES < ntiles) issue(k + STAGES);
         rec_book(pa);
         rec_book(pb);
+        if (CKPT && k * T + 8 < N) checkpoint((k * T + 8) / kGrad2Seg);
       } else {
 #pragma unroll
         for (int c = 0; c < T / 2; ++c) {
@@ -556,7 +558,8 @@ cudaError_t launch_loglik_lockstep_ckpt(const BatchArgs& a, cudaStream_t stream,
   if (!(make_series_map(&mt, a.t, a.B, a.N, a.stride, T) && make_series_map(&md, a.diag, a.B, a.N, a.stride, T) &&
         make_series_map(&my, a.y, a.B, a.N, a.stride, T)))
     return cudaSuccess;
-  auto kern = k_loglik_lockstep2<J, true, lock_maxreg(J), true, false, true>;
+  static const bool nopipe = getenv("CEL_LOCK_NOPIPE") != nullptr;
+  auto kern = nopipe ? k_loglik_lockstep2<J, true, lock_maxreg(J), true, false, true> : k_loglik_lockstep2<J, true, lock_maxreg(J), true, true, true>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   const long long grid = (a.B + kLockThreads - 1) / kLockThreads;
