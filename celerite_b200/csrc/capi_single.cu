@@ -776,7 +776,11 @@ int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t str
   while (chunk > 64 && scratch_need(chunk) > ((size_t)24 << 30)) chunk /= 2;   // checkpoints + tape of the chunk
   if (stride == 0) chunk = B;
   const size_t ndata = (stride == 0 ? 1 : (size_t)chunk) * N;
-  CEL_CUDA_TRY(s, s->scratch0.reserve(scratch_need(chunk)));
+  {   // the last chunk is shorter, and the span plans of the scan paths depend on the batch size
+    size_t need = scratch_need(chunk);
+    if (B % chunk != 0) need = std::max(need, scratch_need(B % chunk));
+    CEL_CUDA_TRY(s, s->scratch0.reserve(need));
+  }
   CEL_CUDA_TRY(s, s->stage_t[0].reserve(dbytes(ndata)));
   CEL_CUDA_TRY(s, s->stage_d[0].reserve(dbytes(ndata)));
   CEL_CUDA_TRY(s, s->stage_y[0].reserve(dbytes(ndata)));

@@ -332,6 +332,7 @@ static long long grad2_piece(long long B, int N) {
   const double per_series = 8.0 * kGrad2Ckpt * ((N + kSeg - 1) / kSeg);
   long long piece = (long long)(6.0e9 / per_series) / (kRevWarps * kWarp) * (kRevWarps * kWarp);
   if (piece < 64 * kRevWarps * kWarp) piece = 64 * kRevWarps * kWarp;
+  if (const char* e = getenv("CEL_GRAD2_PIECE")) { const long long v = atoll(e); if (v >= kWarp) piece = v / kWarp * kWarp; }   // testing knob
   return B < piece ? B : piece;
 }
 static size_t flag_doubles(long long piece) { return ((size_t)piece / 2 + 32) & ~(size_t)31; }
@@ -343,7 +344,7 @@ static int grad2_spans(long long B, int N, int* span_segs) {
   const long long warps = (B + kWarp - 1) / kWarp;
   const int nseg = (N + kSeg - 1) / kSeg;
   const long long wave = (long long)sm_count() * kRevWarps;
-  long long K = wave / warps;
+  long long K = wave / warps;                           // warps * K <= wave: xch_doubles() relies on it
   if (K > nseg / 16) K = nseg / 16;
   if (K > 1024) K = 1024;
   if (off || K < 2) { *span_segs = nseg; return 1; }
@@ -353,16 +354,17 @@ static int grad2_spans(long long B, int N, int* span_segs) {
 }
 
 // flags of a piece + the larger of its checkpoints and what the first-generation kernel wants for the redo
+// exchange rows of the time-parallel form: K >= 2 only when warps * K fits one wave, so one wave of units bounds it
+// (whatever the size of the last piece of a batch)
+static size_t xch_doubles() { return ((size_t)sm_count() * kRevWarps + kRevWarps) * kXchRows * kWarp; }
+
 size_t grad2_scratch_doubles(long long B, int N, int seg_v1) {
   const long long piece = grad2_piece(B, N);
   const size_t warps = (size_t)((piece + kWarp - 1) / kWarp);
   const size_t nseg = (size_t)(N + kSeg - 1) / kSeg;
   const size_t ck = warps * nseg * kGrad2Ckpt * kWarp;
   const size_t v1 = grad_lockstep_v1_scratch_doubles(piece, N, 1, seg_v1);
-  int segs = 0;
-  const int K = grad2_spans(piece, N, &segs);
-  const size_t xch = K > 1 ? warps * K * kXchRows * kWarp : 0;
-  return flag_doubles(piece) + (ck > v1 ? ck : v1) + xch;
+  return flag_doubles(piece) + (ck > v1 ? ck : v1) + xch_doubles();
 }
 
 cudaError_t launch_grad2(const GradArgs& a, cudaStream_t stream, bool* used, int* launches) {

@@ -231,3 +231,26 @@ def test_few_long_series_take_the_batched_adjoint_scan(B, N, Jr, Jc):
         vref += 0.5 * np.pi * np.log(N)
         assert rel_sum(val[i], vref, N) < RTOL_SCALAR
         assert rel_grad(g[i], gref) < RTOL_GRAD, (i, g[i], gref)
+
+
+def test_two_kernel_gradient_in_pieces(monkeypatch):
+    """The J = 2 gradient goes through a large batch in pieces that share one scratch area (checkpoints,
+    flags, exchange rows); forced here to pieces of 448 series, the last one shorter and -- being small --
+    swept in spans where the full pieces are not.  Every series against the reference."""
+    import torch
+    from celerite_b200 import synth
+    from celerite_b200.batched import BatchedSolver
+    monkeypatch.setenv("CEL_GRAD2_PIECE", "448")
+    B, N = 1000, 1200
+    b = synth.make_batch(B, N, 0, 1, seed=99)
+    dev = torch.device("cuda:0")
+    tt = lambda a: torch.from_numpy(a).to(dev)  # noqa: E731
+    bs = BatchedSolver()
+    val, g, status = bs.grad_log_likelihood(tt(b["coeffs"]), tt(b["t"]), tt(b["diag"]), tt(b["y"]), 0, 1)
+    torch.cuda.synchronize()
+    val, g, status = val.cpu().numpy(), g.cpu().numpy(), status.cpu().numpy()
+    assert np.all(status == 0)
+    rv, rg, rs = oracle.best().batched_grad(B, N, N, 0, 1, b["coeffs"], b["coeffs"].shape[1], b["t"], b["diag"], b["y"], 8)
+    rv = rv + 0.5 * np.pi * np.log(N)
+    assert np.max(np.abs(val - rv) / np.maximum(np.abs(rv), 1.0)) < RTOL_SCALAR
+    assert max(rel_grad(g[i], rg[i]) for i in range(B)) < RTOL_GRAD
