@@ -75,6 +75,7 @@ SIGNATURES = {
     "cel_dot_L_mgpu": (C.c_int, [_vp, C.c_int, _vp, _vp]),
     "cel_log_likelihood_mgpu": (C.c_int, [_vp, _vp, _dp]),
     "cel_debug_math": (C.c_int, [C.c_int, _i64, _vp, _vp, _vp, _vp]),
+    "cel_debug_guards_intact": (C.c_int, [_vp]),
     "cel_launch_count": (_i64, [_vp]),
 }
 COMM_ID_BYTES = 128

@@ -93,6 +93,28 @@ int cel_set_stream(cel_solver* s, void* cuda_stream) {
 
 int64_t cel_launch_count(const cel_solver* s) { return s ? s->launches : 0; }
 
+// Debugging aid: with CEL_DEBUG_GUARD set in the environment every internal device buffer is allocated at exactly
+// the size asked for plus a guard band; returns 1 when all bands of the handle's scratch buffers are untouched,
+// 0 when a kernel wrote behind a buffer, -1 without the environment variable.  Synchronises the device.
+int cel_debug_guards_intact(cel_solver* s) {
+  if (!s || !cel::DevBuf::guarded()) return -1;
+  if (cudaSetDevice(s->device) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) { cudaGetLastError(); return 0; }
+  const cel::DevBuf* bufs[] = {&s->scratch0, &s->scratch1, &s->scratch2, &s->in0, &s->in1, &s->in2, &s->in3, &s->out0, &s->out1,
+                               &s->stage_t[0], &s->stage_d[0], &s->stage_y[0], &s->stage_c[0], &s->stage_o[0], &s->stage_s[0],
+                               &s->phi, &s->u, &s->W, &s->D};
+  static unsigned char host[cel::DevBuf::kGuardBytes];
+  for (const cel::DevBuf* b : bufs) {
+    if (!b->p) continue;
+    if (cudaMemcpy(host, static_cast<const char*>(b->p) + b->cap, cel::DevBuf::kGuardBytes, cudaMemcpyDeviceToHost) != cudaSuccess) {
+      cudaGetLastError();
+      return 0;
+    }
+    for (size_t i = 0; i < cel::DevBuf::kGuardBytes; ++i)
+      if (host[i] != 0xA5) return 0;
+  }
+  return 1;
+}
+
 // ------------------------------------------------------------------------------------------
 // batched log-likelihood
 // ------------------------------------------------------------------------------------------

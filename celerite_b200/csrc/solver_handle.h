@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include <string>
 
@@ -17,7 +18,25 @@ namespace cel {
 struct DevBuf {
   void* p = nullptr;
   size_t cap = 0;
+  size_t guard_at = 0;             // CEL_DEBUG_GUARD: offset of the guard band behind the bytes asked for
+  static constexpr size_t kGuardBytes = 4096;
+  static bool guarded() {
+    static const bool on = getenv("CEL_DEBUG_GUARD") != nullptr;
+    return on;
+  }
   cudaError_t reserve(size_t bytes) {
+    if (guarded()) {
+      // debugging aid (cel_debug_guards_intact): exactly the bytes asked for, then a band of 0xA5 that nothing
+      // may touch; re-made on every change of size so that the band always sits right behind the request
+      if (p && bytes == guard_at) return cudaSuccess;
+      if (p) cudaFree(p);
+      p = nullptr; cap = 0;
+      const size_t at = (bytes + 15) & ~(size_t)15;
+      cudaError_t e = cudaMalloc(&p, at + kGuardBytes);
+      if (e != cudaSuccess) return e;
+      cap = at; guard_at = bytes;
+      return cudaMemset(static_cast<char*>(p) + at, 0xA5, kGuardBytes);
+    }
     if (bytes <= cap) return cudaSuccess;
     if (p) cudaFree(p);
     p = nullptr;

@@ -341,6 +341,12 @@ int cel_term_backprop(cel_solver* s, int nterms, const int* kinds, const double*
  * routines' range (|x| < 700 for exp, < 1e9 for sincos). */
 int cel_debug_math(int which, int64_t n, const double* d_x, double* d_out1, double* d_out2, void* cuda_stream);
 
+/* Diagnostic: with CEL_DEBUG_GUARD set in the environment when the library is first used, every internal device
+ * buffer of a handle is allocated at exactly the size asked for, followed by a 4 KB guard band.  Returns 1 when
+ * the bands behind the handle's buffers are untouched, 0 when something wrote behind a buffer, -1 when the
+ * variable is not set.  Synchronises the device; for tests. */
+int cel_debug_guards_intact(cel_solver* s);
+
 /* Number of kernels this handle has launched since creation (bench.py's gpu_launches). */
 int64_t cel_launch_count(const cel_solver* s);
 

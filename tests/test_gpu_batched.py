@@ -379,3 +379,18 @@ def test_ragged_batch(bs, B, N, Jr, Jc, device):
         assert rel_sum(logdet[i], ref[0, 0], n) < RTOL_SCALAR
         assert rel_sum(quad[i], ref[0, 1], n) < RTOL_SCALAR
         assert rel_sum(ll[i], -0.5 * (ref[0, 0] + ref[0, 1] + n * np.log(2 * np.pi)), n) < RTOL_SCALAR
+
+
+def test_no_kernel_writes_behind_its_scratch():
+    """CEL_DEBUG_GUARD: internal device buffers at exactly the requested size with a guard band behind each;
+    tools/guard_check.py drives the gradient paths (two-kernel, spans, pieces, cooperative scan over a batch and
+    over one long series), the term maps and the ragged compute at small sizes and asks
+    cel_debug_guards_intact after every call.  A fresh process, since the variable is read once."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, CEL_DEBUG_GUARD="1")
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "guard_check.py")], cwd=root, env=env,
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "guards intact" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
