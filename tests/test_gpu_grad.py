@@ -254,3 +254,32 @@ def test_two_kernel_gradient_in_pieces(monkeypatch):
     rv = rv + 0.5 * np.pi * np.log(N)
     assert np.max(np.abs(val - rv) / np.maximum(np.abs(rv), 1.0)) < RTOL_SCALAR
     assert max(rel_grad(g[i], rg[i]) for i in range(B)) < RTOL_GRAD
+
+
+@pytest.mark.parametrize("B,N,Jc,device", [(100, 600, 1, True), (100, 600, 1, False), (40, 4096, 1, True), (12, 500, 2, True)])
+def test_batched_grad_with_one_coefficient_row_for_all(B, N, Jc, device):
+    """coeff_stride = 0: one kernel for every series of the batch (one MCMC walker, many light curves), through the
+    two-kernel gradient (J = 2; whole series and, for (40, 4096), spans) and the one-kernel form (J = 4)."""
+    import torch
+    from celerite_b200 import synth
+    from celerite_b200.batched import BatchedSolver
+    b = synth.make_batch(B, N, 0, Jc, seed=B + N + Jc)
+    row = np.ascontiguousarray(b["coeffs"][3])
+    bs = BatchedSolver()
+    if device:
+        dev = torch.device("cuda:0")
+        tt = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)  # noqa: E731
+        val, g, status = bs.grad_log_likelihood(tt(row), tt(b["t"]), tt(b["diag"]), tt(b["y"]), 0, Jc)
+        torch.cuda.synchronize()
+        val, g, status = val.cpu().numpy(), g.cpu().numpy(), status.cpu().numpy()
+    else:
+        val, g, status = bs.grad_log_likelihood(row, b["t"], b["diag"], b["y"], 0, Jc)
+    assert np.all(status == 0) and val.shape == (B,) and g.shape == (B, 1 + 4 * Jc)
+    chk = oracle.best()
+    j, ar, cr, ac, bc, cc, dc = synth.split_row(row, 0, Jc)
+    for i in sorted(set(list(range(0, B, max(1, B // 6))) + [B - 1])):
+        p = oracle.Problem(j, ar, cr, ac, bc, cc, dc, b["t"][i], b["diag"][i])
+        st, vref, gref = chk.grad(p, b["y"][i])
+        vref += 0.5 * np.pi * np.log(N)
+        assert rel_sum(val[i], vref, N) < RTOL_SCALAR
+        assert rel_grad(g[i], gref) < RTOL_GRAD, (i, g[i], gref)
