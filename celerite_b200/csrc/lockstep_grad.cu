@@ -61,8 +61,8 @@ __device__ __forceinline__ void fwd_step(FwdState<J>& st, const double (&cf)[J /
 #pragma unroll
     for (int q = 0; q <= j; ++q) {
       const double P = fma(st.DW[j], st.W[q], st.S[tr<J>(q, j)]);
-      if (TAPE) rec[tr<J>(q, j) * kWarp] = P;
       st.S[tr<J>(q, j)] = (e[q / 2] * e[j / 2]) * P;
+      if (TAPE) rec[tr<J>(q, j) * kWarp] = st.S[tr<J>(q, j)];     // S_n, already scaled by phi phi^T
     }
   double x = yn;
 #pragma unroll
@@ -92,7 +92,7 @@ __device__ __forceinline__ void fwd_step(FwdState<J>& st, const double (&cf)[J /
 #pragma unroll
     for (int j = 0; j < J; ++j) q[j * kWarp] = st.f[j];
     q += J * kWarp;
-    q[0] = Dn; q[kWarp] = x;
+    q[0] = r; q[kWarp] = x * r;                                   // 1/D_n and x_n/D_n: the adjoint needs no division
     q += 2 * kWarp;
 #pragma unroll
     for (int p = 0; p < NP; ++p) { q[p * kWarp] = e[p]; q[(NP + p) * kWarp] = cd[p]; q[(2 * NP + p) * kWarp] = sd[p]; }
@@ -254,11 +254,13 @@ k_grad_lockstep(GradArgs a, const __grid_constant__ CUtensorMap tm_t, const __gr
   ld.renorm();
 
   // ================= phase B: segments in reverse: recompute + tape, then adjoint ===============
-  double Pb[T3], gbar[J], R1[J], R2[J], R3[J], R4[J], R5[J], R6[J];
+  double Pb[T3], gbar[J], Ga[NP], Gb[NP], Gc[NP], Gd[NP];
 #pragma unroll
   for (int i = 0; i < T3; ++i) Pb[i] = 0.0;
 #pragma unroll
-  for (int j = 0; j < J; ++j) { gbar[j] = 0.0; R1[j] = R2[j] = R3[j] = R4[j] = R5[j] = R6[j] = 0.0; }
+  for (int j = 0; j < J; ++j) gbar[j] = 0.0;
+#pragma unroll
+  for (int p = 0; p < NP; ++p) { Ga[p] = 0.0; Gb[p] = 0.0; Gc[p] = 0.0; Gd[p] = 0.0; }
   double sumA = 0.0;
 
   for (int s = nseg - 1; s >= 0; --s) {
@@ -284,114 +286,79 @@ k_grad_lockstep(GradArgs a, const __grid_constant__ CUtensorMap tm_t, const __gr
       }
     }
     // ---- adjoint, n = seg1-1 .. seg0 (tape only) ----
-    const double* ck = ckpt + (size_t)s * EC * kWarp;
+    // The same algebra as lockstep_grad2.cu: with S_n (scaled), r = 1/D_n and xr = x_n/D_n on the tape the step
+    // needs no reciprocal and no record of step n-1 (phi-bar . phi = fbar . f_n + 2 sum sb o S_n), and only four
+    // sums per complex pair (the d-derivative collapses to t_n (ub1 u0 - ub0 u1 - wb0 sin + wb1 cos)).
     for (int n = seg1 - 1; n >= seg0; --n) {
       const double* rec = tape + (size_t)(n - seg0) * E * kWarp;
-      double P[T3], W[J], f[J], e[NP], cd[NP], sd[NP];
+      double S[T3], W[J], f[J], e[NP], cd[NP], sd[NP];
 #pragma unroll
-      for (int i = 0; i < T3; ++i) P[i] = rec[i * kWarp];
+      for (int i = 0; i < T3; ++i) S[i] = rec[i * kWarp];
       const double* q = rec + T3 * kWarp;
 #pragma unroll
       for (int j = 0; j < J; ++j) { W[j] = q[j * kWarp]; f[j] = q[(J + j) * kWarp]; }
       q += 2 * J * kWarp;
-      const double Dn = q[0], xn = q[kWarp];
+      const double r = q[0], xr = q[kWarp];
       q += 2 * kWarp;
 #pragma unroll
       for (int p = 0; p < NP; ++p) { e[p] = q[p * kWarp]; cd[p] = q[(NP + p) * kWarp]; sd[p] = q[(2 * NP + p) * kWarp]; }
       q += 3 * NP * kWarp;
-      const double tn = q[0], dxn = q[kWarp];
-      // W, f, x of step n-1: previous tape record, or the checkpoint at the segment edge
-      double Wm[J], fm[J], xm;
-      if (n > seg0) {
-        const double* pr = rec - E * kWarp + T3 * kWarp;
-#pragma unroll
-        for (int j = 0; j < J; ++j) { Wm[j] = pr[j * kWarp]; fm[j] = pr[(J + j) * kWarp]; }
-        xm = pr[(2 * J + 1) * kWarp];
-      } else {
-        const double* pr = ck + T3 * kWarp;
-#pragma unroll
-        for (int j = 0; j < J; ++j) { Wm[j] = pr[j * kWarp]; fm[j] = pr[(2 * J + j) * kWarp]; }
-        xm = pr[3 * J * kWarp];
-      }
-      double u[J], v[J], vp[J];
+      const double tn = q[0], ndx = -q[kWarp];
+      double u[J];
 #pragma unroll
       for (int p = 0; p < NP; ++p) {
         u[2 * p] = fma(cf[p][0], cd[p], cf[p][1] * sd[p]);
         u[2 * p + 1] = fma(cf[p][0], sd[p], -(cf[p][1] * cd[p]));
-        v[2 * p] = cd[p]; v[2 * p + 1] = sd[p];
-        vp[2 * p] = sd[p]; vp[2 * p + 1] = cd[p];
       }
-      const double r = fast_rcp(Dn);
-      double PbW[J], Dbar = 0.5 * (xn * r) * (xn * r) - 0.5 * r, xbar = -xn * r;
+      double wb[J], Dbar = fma(0.5 * xr, xr, -0.5 * r), xbar = -xr;
 #pragma unroll
       for (int k = 0; k < J; ++k) {
         double acc = 0.0;
 #pragma unroll
         for (int j = 0; j < J; ++j) acc = fma(Pb[tr<J>(k, j)], W[j], acc);
-        PbW[k] = acc;
-        Dbar = fma(W[k], acc, Dbar);
+        wb[k] = fma(gbar[k], xr, acc + acc);              // W-bar / D_n
+        Dbar = fma(W[k], acc - wb[k], Dbar);
         xbar = fma(gbar[k], W[k], xbar);
       }
-      double w[J], WbW = 0.0;
+      sumA += Dbar;
+      double fb[J], ub[J];
+      const double D2 = Dbar + Dbar;
 #pragma unroll
       for (int k = 0; k < J; ++k) {
-        const double Wbar = fma(2.0 * Dn, PbW[k], gbar[k] * xn);
-        WbW = fma(Wbar, W[k], WbW);
-        w[k] = Wbar * r;
+        fb[k] = fma(-xbar, u[k], gbar[k]);
+        double su = 0.0, sw = 0.0;
+#pragma unroll
+        for (int j = 0; j < J; ++j) {
+          su = fma(S[tr<J>(k, j)], u[j], su);
+          sw = fma(S[tr<J>(k, j)], wb[j], sw);
+        }
+        ub[k] = fma(-D2, su, fma(-xbar, f[k], -sw));
       }
-      Dbar = fma(-WbW, r, Dbar);
+      // sb = Pb - 1/2 (wb u^T + u wb^T) - Dbar u u^T;  pe_k = fb_k f_k + 2 sum_j sb_kj S_kj;  Pb <- phi phi^T o sb
+      //   sb_kj = Pb_kj - (wb_k / 2) u_j - u_k (wb_j / 2 + Dbar u_j)
+      double pe[J], hw[J], hv[J];
 #pragma unroll
-      for (int k = 0; k < J; ++k) R6[k] = fma(tn * w[k], vp[k], R6[k]);
-      sumA += Dbar;
-      if (n > 0) {
-        double ubar[J], phibar[J], Su[J], Sw[J], sb[T3];
+      for (int k = 0; k < J; ++k) { pe[k] = fb[k] * f[k]; hw[k] = -0.5 * wb[k]; hv[k] = fma(Dbar, u[k], 0.5 * wb[k]); }
 #pragma unroll
-        for (int k = 0; k < J; ++k) {
-          const double fbar = fma(-xbar, u[k], gbar[k]);
-          ubar[k] = -xbar * f[k];
-          phibar[k] = fbar * fma(Wm[k], xm, fm[k]);
-          gbar[k] = e[k / 2] * fbar;
-          Su[k] = 0.0; Sw[k] = 0.0;
+      for (int j = 0; j < J; ++j)
+#pragma unroll
+        for (int k = 0; k <= j; ++k) {
+          const double t0 = fma(-u[k], hv[j], fma(hw[k], u[j], Pb[tr<J>(k, j)]));
+          const double ss = t0 * S[tr<J>(k, j)];
+          pe[k] = fma(2.0, ss, pe[k]);
+          if (k != j) pe[j] = fma(2.0, ss, pe[j]);
+          Pb[tr<J>(k, j)] = (e[k / 2] * e[j / 2]) * t0;
         }
 #pragma unroll
-        for (int k = 0; k < J; ++k)
+      for (int k = 0; k < J; ++k) gbar[k] = e[k / 2] * fb[k];
 #pragma unroll
-          for (int j = 0; j < J; ++j) {
-            const double sv = (e[k / 2] * e[j / 2]) * P[tr<J>(k, j)];
-            Su[k] = fma(sv, u[j], Su[k]);
-            Sw[k] = fma(sv, w[j], Sw[k]);
-          }
-#pragma unroll
-        for (int k = 0; k < J; ++k) ubar[k] -= fma(2.0 * Dbar, Su[k], Sw[k]);
-#pragma unroll
-        for (int j = 0; j < J; ++j)
-#pragma unroll
-          for (int k = 0; k <= j; ++k) {
-            double t0 = Pb[tr<J>(k, j)];
-            t0 = fma(-0.5 * w[k], u[j], t0);
-            t0 = fma(-0.5 * u[k], w[j], t0);
-            t0 = fma(-Dbar * u[k], u[j], t0);
-            sb[tr<J>(k, j)] = t0;
-          }
-#pragma unroll
-        for (int k = 0; k < J; ++k) {
-          double acc = 0.0;
-#pragma unroll
-          for (int j = 0; j < J; ++j) acc = fma(sb[tr<J>(k, j)] * P[tr<J>(k, j)], e[j / 2], acc);
-          phibar[k] = fma(2.0, acc, phibar[k]);
-        }
-#pragma unroll
-        for (int j = 0; j < J; ++j)
-#pragma unroll
-          for (int k = 0; k <= j; ++k) Pb[tr<J>(k, j)] = (e[k / 2] * e[j / 2]) * sb[tr<J>(k, j)];
-#pragma unroll
-        for (int k = 0; k < J; ++k) {
-          R1[k] = fma(ubar[k], v[k], R1[k]);
-          R2[k] = fma(ubar[k], vp[k], R2[k]);
-          R3[k] = fma(phibar[k], -dxn * e[k / 2], R3[k]);
-          R4[k] = fma(tn * ubar[k], v[k], R4[k]);
-          R5[k] = fma(tn * ubar[k], vp[k], R5[k]);
-        }
+      for (int p = 0; p < NP; ++p) {
+        const int k = 2 * p;
+        Ga[p] = fma(ub[k + 1], sd[p], fma(ub[k], cd[p], Ga[p]));
+        Gb[p] = fma(-ub[k + 1], cd[p], fma(ub[k], sd[p], Gb[p]));
+        Gc[p] = fma(ndx, pe[k] + pe[k + 1], Gc[p]);
+        const double gq = fma(wb[k + 1], cd[p], fma(-wb[k], sd[p], fma(ub[k + 1], u[k], -(ub[k] * u[k + 1]))));
+        Gd[p] = fma(tn, gq, Gd[p]);
       }
     }
   }
@@ -402,15 +369,10 @@ k_grad_lockstep(GradArgs a, const __grid_constant__ CUtensorMap tm_t, const __gr
     g[0] = fail ? nan : ((jitter > DBL_EPSILON) ? sumA : 0.0);   // solver.cpp:377-389, 418-426
 #pragma unroll
     for (int p = 0; p < NP; ++p) {
-      const int k = 2 * p;
-      const double ga = R1[k] + R1[k + 1] + sumA;
-      const double gb = R2[k] - R2[k + 1];
-      const double gc = R3[k] + R3[k + 1];
-      const double gd = -cf[p][0] * R5[k] + cf[p][1] * R4[k] + cf[p][0] * R5[k + 1] + cf[p][1] * R4[k + 1] - R6[k] + R6[k + 1];
-      g[1 + p] = fail ? nan : ga;
-      g[1 + Jc + p] = fail ? nan : gb;
-      g[1 + 2 * Jc + p] = fail ? nan : gc;
-      g[1 + 3 * Jc + p] = fail ? nan : gd;
+      g[1 + p] = fail ? nan : Ga[p] + sumA;
+      g[1 + Jc + p] = fail ? nan : Gb[p];
+      g[1 + 2 * Jc + p] = fail ? nan : Gc[p];
+      g[1 + 3 * Jc + p] = fail ? nan : Gd[p];
     }
     const double logdet = fail ? nan : ld.value();
     const double qv = fail ? nan : quad;
