@@ -19,6 +19,9 @@ namespace {
 // warm-up step must agree with the owner's values to kSegmentMismatchTol, else cel_compute redoes
 // the series serially.
 constexpr int kSegmentedMinN = 16384;
+// the gradient's adjoint scan behind ONE serial forward sweep pays much earlier: the reverse sweep is two thirds
+// of the serial gradient (N = 4,096, J = 3: 3.6 ms serial, forward sweep + scan over 16 spans 1.6 ms)
+constexpr int kGradScanMinN = 1024;
 constexpr double kSegmentTol = 1e-17;
 constexpr double kSegmentMismatchTol = 1e-12;
 constexpr double kSpanMismatchTol = 1e-10;   // gradient spans: forward state and adjoint carries at the common edge
@@ -116,7 +119,8 @@ void plan_scan_spans(int J, int Jr, const double* c_real, int Jc, const double* 
   while (L < J && L < 32) L <<= 1;
   const int slots = cel::sm_count() * 8 * (32 / L);
   long long len = (N + slots - 1) / slots;
-  if (len < 1024) len = 1024;
+  const long long min_len = halo ? 1024 : std::max(256, 4 * seg);
+  if (len < min_len) len = min_len;
   double reach = 0.0;
   if (halo) {
     double c_min = INFINITY;
@@ -135,7 +139,7 @@ void plan_scan_spans(int J, int Jr, const double* c_real, int Jc, const double* 
     len = (len + seg - 1) / seg * seg;
   }
   const int K = (int)((N + len - 1) / len);
-  if (halo && K < 8) return;
+  if (halo ? K < 8 : K < 4) return;                      // too few spans to pay for the second adjoint pass
   span.reserve(4 * (size_t)K);
   long long work = 0;
   for (int c = 0; c < K; ++c) {
@@ -579,14 +583,14 @@ int cel_grad_log_likelihood(cel_solver* s, double jitter, int Jr, const double* 
   // halo and in front of a cool-down halo; neighbouring spans are compared at their common edge
   // and the series is redone serially if they disagree.
   const bool spans_v1 = getenv("CEL_GRAD_SPANS_V1") != nullptr;   // A/B knob: warm-up + cool-down halos
-  if (!spans_v1 && Jg == 0 && !A && N >= kSegmentedMinN && J <= cel::kCoopMaxJ) {
+  if (!spans_v1 && Jg == 0 && !A && N >= kGradScanMinN && J <= cel::kCoopMaxJ) {
     // The exact time-parallel adjoint (grad.cu, scan modes).  Attempt 0: the spans' forward sweeps run side
     // by side behind warm-up halos, checked at the common edges afterwards (W, D and f of the same step, two
     // histories).  Attempt 1, when the factorisation does not forget fast enough for that: ONE forward
     // sweep over the series leaves the checkpoints.  Either way the adjoint -- the linear recursions -- is
     // an exact two-pass scan over the spans: probe, fold, final.
     const bool no_halo = getenv("CEL_GRAD_SCAN_SERIAL_FORWARD") != nullptr;   // testing knob: attempt 1 only
-    for (int attempt = no_halo ? 1 : 0; attempt < 2; ++attempt) {
+    for (int attempt = (no_halo || N < kSegmentedMinN) ? 1 : 0; attempt < 2; ++attempt) {
       const bool halo = attempt == 0;
       std::vector<int> span;
       int len = 0;
