@@ -196,3 +196,48 @@ def test_factor_file_round_trip_and_residual(tmp_path):
     assert s2.log_determinant() == s.log_determinant()
     assert np.array_equal(s2.solve(y), s.solve(y))
     assert audit.residual(s, j, ar, cr, ac, bc, cc, dc, t, d, y) < 1e-9
+
+
+def test_factor_file_crosses_over_to_the_reference_solver_and_back(tmp_path):
+    """SURVEY.md §8f-4, both directions: a factor computed on the GPU, written with audit.save_factor, is installed
+    in the REFERENCE's CPU CholeskySolver (its own __setstate__, solver.cpp:644-663) and solves there; a factor
+    the reference computed and pickled is installed in the GPU solver and solves here.  Same answers to 1e-10."""
+    import os
+    import pickle
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    ref_dir = os.path.join(root, "baseline", "_ref")
+    if not os.path.isdir(os.path.join(ref_dir, "celerite")):
+        pytest.skip("baseline/_ref (pip install of the reference) is not present")
+    sys.path.insert(0, ref_dir)
+    try:
+        from celerite import solver as ref_solver
+    finally:
+        sys.path.remove(ref_dir)
+    from celerite_b200 import audit, solver, synth
+    from tests.util import RTOL_SOLVE
+    N, Jr, Jc = 2500, 2, 1
+    b = synth.make_batch(1, N, Jr, Jc, seed=21)
+    j, ar, cr, ac, bc, cc, dc = synth.split_row(b["coeffs"][0], Jr, Jc)
+    t, d, y = b["t"][0], b["diag"][0], b["y"][0]
+    E0, E2 = np.empty(0), np.empty((0, 0))
+    gpu = solver.CholeskySolver()
+    gpu.compute(j, ar, cr, ac, bc, cc, dc, E0, E2, E2, t, d)
+    cpu = ref_solver.CholeskySolver()
+    cpu.compute(j, ar, cr, ac, bc, cc, dc, E0, E2, E2, t, d)
+    z_cpu, z_gpu = cpu.solve(y), gpu.solve(y)
+    # GPU factor -> file -> reference solver
+    path = str(tmp_path / "gpu_factor.npz")
+    audit.save_factor(gpu, path)
+    cpu2 = ref_solver.CholeskySolver.__new__(ref_solver.CholeskySolver)   # what unpickling does (pybind11 py::pickle)
+    cpu2.__setstate__(audit.load_factor(path))
+    assert cpu2.computed() and abs(cpu2.log_determinant() - cpu.log_determinant()) < 1e-10 * abs(cpu.log_determinant())
+    assert rel_inf(np.asarray(cpu2.solve(y)), np.asarray(z_cpu)) < RTOL_SOLVE
+    assert abs(cpu2.dot_solve(y) - cpu.dot_solve(y)) < 1e-10 * abs(cpu.dot_solve(y))
+    # reference factor -> pickle -> GPU solver
+    gpu2 = solver.CholeskySolver()
+    gpu2.__setstate__(pickle.loads(pickle.dumps(cpu, -1)).__getstate__())
+    assert gpu2.computed() and abs(gpu2.log_determinant() - cpu.log_determinant()) < 1e-10 * abs(cpu.log_determinant())
+    assert rel_inf(np.asarray(gpu2.solve(y)), np.asarray(z_cpu)) < RTOL_SOLVE
+    assert rel_inf(np.asarray(gpu2.dot_L(y)), np.asarray(cpu.dot_L(y))) < RTOL_SOLVE
+    assert rel_inf(np.asarray(z_gpu), np.asarray(z_cpu)) < RTOL_SOLVE
