@@ -621,8 +621,12 @@ cudaError_t launch_loglik_lockstep(const BatchArgs& a, cudaStream_t stream) {
     bool used = false;
     cudaError_t e = cudaSuccess;
     switch (J) {
+      case 1: e = launch_v2<1, lock_maxreg(1)>(a, stream, &used); break;
       case 2: e = launch_v2<2, lock_maxreg(2)>(a, stream, &used); break;
+      case 3: e = launch_v2<3, lock_maxreg(3)>(a, stream, &used); break;
       case 4: e = launch_v2<4, lock_maxreg(4)>(a, stream, &used); break;
+      case 5: e = launch_v2<5, lock_maxreg(5)>(a, stream, &used); break;
+      case 6: e = launch_v2<6, lock_maxreg(6)>(a, stream, &used); break;
       default: break;
     }
     if (e != cudaSuccess || used) return e;
