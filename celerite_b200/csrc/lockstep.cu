@@ -281,7 +281,9 @@ __device__ __noinline__ void careful_series(const BatchArgs& a, long long bb, in
 
 // CKPT (forward half of the two-kernel gradient, J = 2): the state before every kGrad2Seg-th step goes to
 // a.ckpt, series that left the fast path are flagged in a.flags instead of being redone here
-template <int J, bool ALLC, int CAP, bool TAB, bool PIPE = false, bool CKPT = false>
+// RAG: a ragged batch (a.lengths): a lane's series ends at its own length; the steps behind it (padding of any
+// content) still run but feed neither the sums nor the range check.
+template <int J, bool ALLC, int CAP, bool TAB, bool PIPE = false, bool CKPT = false, bool RAG = false>
 __global__ void __launch_bounds__(kLockThreads) __maxnreg__(CAP)
 k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const __grid_constant__ CUtensorMap tm_d,
                    const __grid_constant__ CUtensorMap tm_y) {
@@ -307,6 +309,7 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
   const bool active = b < a.B;
   const long long bb = active ? b : a.B - 1;  // idle lanes shadow the last series, store nothing
   const int N = a.N;
+  const int len = RAG ? min(max(a.lengths[bb], 0), N) : N;   // this lane's own series length
   const double* tp = a.t + bb * a.stride;
 
   const int Jr = a.Jr, Jc = a.Jc;
@@ -335,7 +338,7 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
   for (int j = 0; j < Jr; ++j) sum_ar += a_real[j];
   for (int j = 0; j < Jc; ++j) sum_ac += a_comp[j];
   const double asum = sum_ar + sum_ac;
-  const double tmax = fmax(fabs(__ldg(tp)), fabs(__ldg(tp + N - 1)));
+  const double tmax = fmax(fabs(__ldg(tp)), fabs(__ldg(tp + max(len, 1) - 1)));   // (behind len: padding)
   const bool warp_fast = __all_sync(kFull, dmax * tmax < kFastTrigLimit);
 
   const int ntiles = (N + T - 1) / T;
@@ -397,7 +400,7 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
     };
 
     // one pair of steps: loads, generators, recursion, optimistic bookkeeping
-    auto pair = [&](const unsigned char* src, int c, auto guard, int nvalid) {
+    auto pair = [&](const unsigned char* src, int c, auto guard, int nvalid, int n0) {
       constexpr bool GUARD = decltype(guard)::value;
       const double2 v0 = *reinterpret_cast<const double2*>(src + offc[c]);
       const double2 v1 = *reinterpret_cast<const double2*>(src + kTile + offc[c]);
@@ -409,7 +412,8 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
       tlast = tt[G - 1];
       double Dg[G] = {1.0, 1.0};
       auto sink = [&](int g, double Dn, const double*) { Dg[g] = Dn; };
-      lock_rec<J, G, ALLC, GUARD, decltype(sink), false, true, false, false>(st, gn, asum, jitter, dd, yy, 0, nvalid, sink);
+      lock_rec<J, G, ALLC, GUARD, decltype(sink), RAG, true, false, false>(st, gn, asum, jitter, dd, yy, n0, nvalid, sink, len);
+      if (RAG) { Dg[0] = n0 < len ? Dg[0] : 1.0; Dg[1] = n0 + 1 < len ? Dg[1] : 1.0; }
       // normal and inside [2^-500, 2^500]: one unsigned compare on the high word (negative numbers,
       // zero, denormals, inf and nan all land outside)
       bad |= (unsigned)((unsigned)(__double2hiint(Dg[0]) - 0x20b00000) >= 0x3e800000u);
@@ -428,8 +432,9 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
 
     // the two halves of `pair`, for the software-pipelined loop: the generators of pair c+1 (independent
     // chains) are written before the recursion of pair c (one serial chain), so that they fill its bubbles
-    struct PairIn { LockGen<J, G> gn; double dd[G], yy[G]; };
-    auto load_gen = [&](const unsigned char* src, int c, PairIn& o) {
+    struct PairIn { LockGen<J, G> gn; double dd[G], yy[G]; int n0; };
+    auto load_gen = [&](const unsigned char* src, int c, PairIn& o, int n0 = 0) {
+      o.n0 = n0;
       const double2 v0 = *reinterpret_cast<const double2*>(src + offc[c]);
       const double2 v1 = *reinterpret_cast<const double2*>(src + kTile + offc[c]);
       const double2 v2 = *reinterpret_cast<const double2*>(src + 2 * kTile + offc[c]);
@@ -442,7 +447,8 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
     auto rec_book = [&](const PairIn& in) {
       double Dg[G] = {1.0, 1.0};
       auto sink = [&](int g, double Dn, const double*) { Dg[g] = Dn; };
-      lock_rec<J, G, ALLC, false, decltype(sink), false, true, false, false>(st, in.gn, asum, jitter, in.dd, in.yy, 0, G, sink);
+      lock_rec<J, G, ALLC, false, decltype(sink), RAG, true, false, false>(st, in.gn, asum, jitter, in.dd, in.yy, in.n0, G, sink, len);
+      if (RAG) { Dg[0] = in.n0 < len ? Dg[0] : 1.0; Dg[1] = in.n0 + 1 < len ? Dg[1] : 1.0; }
       bad |= (unsigned)((unsigned)(__double2hiint(Dg[0]) - 0x20b00000) >= 0x3e800000u);
       bad |= (unsigned)((unsigned)(__double2hiint(Dg[1]) - 0x20b00000) >= 0x3e800000u);
       const double P = Dg[0] * Dg[1];
@@ -459,11 +465,11 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
       const unsigned char* src = lbase + s * (3 * kTile);
       if (PIPE) {
         PairIn pa, pb;
-        load_gen(src, 0, pa);
-        load_gen(src, 1, pb); rec_book(pa);
-        load_gen(src, 2, pa); rec_book(pb);
+        load_gen(src, 0, pa, k * T);
+        load_gen(src, 1, pb, k * T + 2); rec_book(pa);
+        load_gen(src, 2, pa, k * T + 4); rec_book(pb);
         if (CKPT && k * T + 4 < N) checkpoint((k * T + 4) / kGrad2Seg);
-        load_gen(src, 3, pb);
+        load_gen(src, 3, pb, k * T + 6);
         __syncwarp();              // the tile is in registers on every lane: refill its slot
         if (k + STAGES < ntiles) issue(k + STAGES);
         rec_book(pa);
@@ -472,7 +478,7 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
       } else {
 #pragma unroll
         for (int c = 0; c < T / 2; ++c) {
-          pair(src, c, std::false_type(), G);
+          pair(src, c, std::false_type(), G, k * T + 2 * c);
           if (c == T / 2 - 1) {      // the tile is in registers on every lane: refill its slot
             __syncwarp();
             if (k + STAGES < ntiles) issue(k + STAGES);
@@ -490,7 +496,7 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
 #pragma unroll
       for (int c = 0; c < T / 2; ++c)
         if (2 * c < left) {
-          pair(src, c, std::true_type(), left - 2 * c);
+          pair(src, c, std::true_type(), left - 2 * c, nfull * T + 2 * c);
           if (CKPT && (c & 1) && 2 * c + 2 < left) checkpoint((nfull * T + 2 * c + 2) / kGrad2Seg);
         }
     }
@@ -500,7 +506,7 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
   double logdet = log(mant) + 0.6931471805599453094 * static_cast<double>(expo);
   double q = st.quad;
   int fail = 0;
-  if (bad && !CKPT) careful_series<J, ALLC>(a, bb, N, cf, asum, jitter, &logdet, &q, &fail);
+  if (bad && !CKPT) careful_series<J, ALLC>(a, bb, len, cf, asum, jitter, &logdet, &q, &fail);
 
   if (active) {
     const double nan = __longlong_as_double(0x7ff8000000000000LL);
@@ -511,7 +517,7 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
     }
     if (a.out_logdet) a.out_logdet[b] = logdet;
     if (a.out_quad) a.out_quad[b] = q;
-    if (a.out_ll) a.out_ll[b] = -0.5 * (q + logdet + (double)N * kLog2Pi);  // celerite.py:214-216
+    if (a.out_ll) a.out_ll[b] = -0.5 * (q + logdet + (double)len * kLog2Pi);  // celerite.py:214-216
     if (a.status) a.status[b] = fail ? 3 : 0;
     if (a.fail_index) a.fail_index[b] = fail;
   }
@@ -527,7 +533,7 @@ cudaError_t launch_v2(const BatchArgs& a, cudaStream_t stream, bool* used) {
   static const bool notab = getenv("CEL_LOCK_NOTAB") != nullptr;   // A/B knob: polynomial-only exp / sincos
   // software-pipelined tile loop: 0.803 -> 0.792 ms on cfg2 (J = 2), nothing at J = 4; CEL_LOCK_NOPIPE turns it off
   static const bool pipe = J <= 2 && getenv("CEL_LOCK_NOPIPE") == nullptr;
-  if (off || a.lengths || a.N < 1) return cudaSuccess;
+  if (off || a.N < 1) return cudaSuccess;
   alignas(64) CUtensorMap mt, md, my;
   if (!(make_series_map(&mt, a.t, a.B, a.N, a.stride, T) && make_series_map(&md, a.diag, a.B, a.N, a.stride, T) &&
         make_series_map(&my, a.y, a.B, a.N, a.stride, T)))
@@ -537,6 +543,10 @@ cudaError_t launch_v2(const BatchArgs& a, cudaStream_t stream, bool* used) {
   auto kern = allc ? (notab ? k_loglik_lockstep2<J, kEven, CAP, false> : k_loglik_lockstep2<J, kEven, CAP, true>)
                    : (notab ? k_loglik_lockstep2<J, false, CAP, false> : k_loglik_lockstep2<J, false, CAP, true>);
   if (pipe && !notab) kern = allc ? k_loglik_lockstep2<J, kEven, CAP, true, true> : k_loglik_lockstep2<J, false, CAP, true, true>;
+  if (a.lengths) {                  // ragged batch: the table-driven loop with per-lane lengths
+    if (notab) return cudaSuccess;  // (A/B knob only without lengths: the first-generation kernel takes it)
+    kern = allc ? k_loglik_lockstep2<J, kEven, CAP, true, false, false, true> : k_loglik_lockstep2<J, false, CAP, true, false, false, true>;
+  }
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   const long long grid = (a.B + kLockThreads - 1) / kLockThreads;
