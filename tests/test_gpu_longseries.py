@@ -363,3 +363,15 @@ def test_high_q_oscillator_takes_the_serial_forward_sweep_by_itself():
     assert s.launch_count() - n0 == 5
     assert rel_sum(val, vref, N) < RTOL_SCALAR
     assert rel_grad(g, gref) < RTOL_GRAD, (g, gref)
+
+
+@pytest.mark.parametrize("N,Jr,Jc", [(1024, 0, 1), (1500, 1, 2), (4096, 1, 1), (6000, 0, 13)])
+def test_short_series_gradient_is_a_forward_sweep_and_an_adjoint_scan(N, Jr, Jc):
+    """From N = 1,024 on the single-series gradient runs as ONE forward sweep (mode 3) and the exact adjoint scan
+    over spans of >= 256 steps (probe, fold, final, finish: 5 launches); N = 4,096 with one real and one complex
+    term is BASELINE config 1."""
+    assert _grad_case(N, Jr, Jc, seed=N + 11) == 5
+
+
+def test_series_below_the_scan_threshold_take_the_serial_sweep():
+    assert _grad_case(1000, 1, 1, seed=5) == 1
