@@ -72,6 +72,7 @@ struct BatchArgs {
   // the recursion state before every 4th step, [warp of 32 series][segment][5][32] doubles, and per
   // series whether it left the fast path (then its outputs are not final: the caller re-does it)
   double* ckpt;
+  int ckpt_seg;            // steps between checkpoints (2 or 4); J (J+1)/2 + J doubles each
   int* flags;
   double* out_half;        // -0.5 * (quad + logdet), no constant (the gradient entry points' value)
 };
@@ -160,10 +161,11 @@ size_t grad_lockstep_scratch_doubles(long long B, int N, int Jc, int seg);
 cudaError_t launch_grad_lockstep(const GradArgs& a, cudaStream_t stream, bool* used, int* launches = nullptr);
 // J = 2 (one complex term): forward sweep of the fused log-likelihood kernel that also leaves checkpoints
 // (lockstep.cu), and the reverse sweep over them (lockstep_grad2.cu)
-constexpr int kGrad2Seg = 4;      // steps between checkpoints
-constexpr int kGrad2Ckpt = 5;     // doubles per checkpoint: (S + D W W^T) 00 01 11, (f + W x) 0 1
+constexpr int kGrad2Seg = 4;      // steps between checkpoints (J = 2)
+constexpr int kGrad2Ckpt = 5;     // doubles per checkpoint at J = 2: (S + D W W^T) 00 01 11, (f + W x) 0 1
+constexpr int kGrad4Seg = 2;      // J = 4 (two complex terms): 10 + 4 doubles per checkpoint
 cudaError_t launch_loglik_lockstep_ckpt(const BatchArgs& a, cudaStream_t stream, bool* used);
-size_t grad2_scratch_doubles(long long B, int N, int seg_v1);
+size_t grad2_scratch_doubles(long long B, int N, int seg_v1, int Jc = 1);
 size_t grad_lockstep_v1_scratch_doubles(long long B, int N, int Jc, int seg);
 cudaError_t launch_grad_lockstep_v1(const GradArgs& a, cudaStream_t stream, bool* used);
 cudaError_t launch_grad2(const GradArgs& a, cudaStream_t stream, bool* used, int* launches);

@@ -383,19 +383,22 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
 #pragma unroll
     for (int c = 0; c < T / 2; ++c) offc[c] = (c ^ swz) << 4;
     double tlast = __ldg(tp);
-    // checkpoint s = the state before step kGrad2Seg * s, in the form the next step consumes it:
+    // checkpoint s = the state before step a.ckpt_seg * s, in the form the next step consumes it:
     // S + D W W^T (cholesky.h:154-160 before the scaling by phi phi^T), f + W x (cholesky.h:350-354)
-    const int nckpt = (N + kGrad2Seg - 1) / kGrad2Seg;
-    double* ckp = CKPT ? a.ckpt + ((size_t)(b0 / kWarp) * nckpt * kGrad2Ckpt) * kWarp + lane : nullptr;
+    constexpr int kCkD = J * (J + 1) / 2 + J;
+    const int cseg = CKPT ? a.ckpt_seg : 4;
+    const int nckpt = (N + cseg - 1) / cseg;
+    double* ckp = CKPT ? a.ckpt + ((size_t)(b0 / kWarp) * nckpt * kCkD) * kWarp + lane : nullptr;
     auto checkpoint = [&](int s) {
-      if constexpr (CKPT && J == 2) {
+      if constexpr (CKPT && ALLC) {
         if (b0 >= a.B) return;     // a warp of idle lanes only (the last CTA): it owns no checkpoint rows
-        double* q = ckp + (size_t)s * (kGrad2Ckpt * kWarp);
-        q[0] = fma(st.DW[0], st.Wp[0], st.S[0]);
-        q[kWarp] = fma(st.DW[1], st.Wp[0], st.S[1]);
-        q[2 * kWarp] = fma(st.DW[1], st.Wp[1], st.S[2]);
-        q[3 * kWarp] = fma(st.Wp[0], st.xprev, st.f[0]);
-        q[4 * kWarp] = fma(st.Wp[1], st.xprev, st.f[1]);
+        double* q = ckp + (size_t)s * (kCkD * kWarp);
+#pragma unroll
+        for (int j = 0; j < J; ++j) {
+#pragma unroll
+          for (int r = 0; r <= j; ++r) q[tri<J>(r, j) * kWarp] = fma(st.DW[j], st.Wp[r], st.S[tri<J>(r, j)]);
+          q[(J * (J + 1) / 2 + j) * kWarp] = fma(st.Wp[j], st.xprev, st.f[j]);
+        }
       }
     };
 
@@ -468,13 +471,13 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
         load_gen(src, 0, pa, k * T);
         load_gen(src, 1, pb, k * T + 2); rec_book(pa);
         load_gen(src, 2, pa, k * T + 4); rec_book(pb);
-        if (CKPT && k * T + 4 < N) checkpoint((k * T + 4) / kGrad2Seg);
+        if (CKPT && k * T + 4 < N) checkpoint((k * T + 4) / 4);          // (the pipelined loop: J = 2, segments of 4)
         load_gen(src, 3, pb, k * T + 6);
         __syncwarp();              // the tile is in registers on every lane: refill its slot
         if (k + STAGES < ntiles) issue(k + STAGES);
         rec_book(pa);
         rec_book(pb);
-        if (CKPT && k * T + 8 < N) checkpoint((k * T + 8) / kGrad2Seg);
+        if (CKPT && k * T + 8 < N) checkpoint((k * T + 8) / 4);
       } else {
 #pragma unroll
         for (int c = 0; c < T / 2; ++c) {
@@ -483,7 +486,7 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
             __syncwarp();
             if (k + STAGES < ntiles) issue(k + STAGES);
           }
-          if (CKPT && (c & 1) && k * T + 2 * c + 2 < N) checkpoint((k * T + 2 * c + 2) / kGrad2Seg);
+          if (CKPT && ((c & 1) || cseg == 2) && k * T + 2 * c + 2 < N) checkpoint((k * T + 2 * c + 2) / cseg);
         }
       }
       if ((k & 63) == 63) renorm();
@@ -497,7 +500,7 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
       for (int c = 0; c < T / 2; ++c)
         if (2 * c < left) {
           pair(src, c, std::true_type(), left - 2 * c, nfull * T + 2 * c);
-          if (CKPT && (c & 1) && 2 * c + 2 < left) checkpoint((nfull * T + 2 * c + 2) / kGrad2Seg);
+          if (CKPT && ((c & 1) || cseg == 2) && 2 * c + 2 < left) checkpoint((nfull * T + 2 * c + 2) / cseg);
         }
     }
     renorm();
@@ -557,25 +560,33 @@ cudaError_t launch_v2(const BatchArgs& a, cudaStream_t stream, bool* used) {
 
 }  // namespace
 
-// forward half of the two-kernel gradient (J = 2, all complex): the fused kernel, leaving checkpoints
-cudaError_t launch_loglik_lockstep_ckpt(const BatchArgs& a, cudaStream_t stream, bool* used) {
-  constexpr int T = 8, STAGES = 2, J = 2;
+// forward half of the two-kernel gradient (J = 2 or 4, all complex): the fused kernel, leaving checkpoints
+template <int J>
+static cudaError_t launch_ckpt(const BatchArgs& a, cudaStream_t stream, bool* used) {
+  constexpr int T = 8, STAGES = 2;
   constexpr int WARPS = kLockThreads / kWarp;
   constexpr size_t smem = (size_t)WARPS * STAGES * 3 * kWarp * T * 8 + 64 + kTrigTabN * 16 + kExpTabN * 8 + 1024;
-  *used = false;
-  if (a.Jr != 0 || a.Jc != 1 || a.Jg != 0 || a.lengths || a.N < 1 || !a.ckpt || !a.flags) return cudaSuccess;
   alignas(64) CUtensorMap mt, md, my;
   if (!(make_series_map(&mt, a.t, a.B, a.N, a.stride, T) && make_series_map(&md, a.diag, a.B, a.N, a.stride, T) &&
         make_series_map(&my, a.y, a.B, a.N, a.stride, T)))
     return cudaSuccess;
   static const bool nopipe = getenv("CEL_LOCK_NOPIPE") != nullptr;
-  auto kern = nopipe ? k_loglik_lockstep2<J, true, lock_maxreg(J), true, false, true> : k_loglik_lockstep2<J, true, lock_maxreg(J), true, true, true>;
+  auto kern = (nopipe || J > 2) ? k_loglik_lockstep2<J, true, lock_maxreg(J), true, false, true>
+                                : k_loglik_lockstep2<J, true, lock_maxreg(J), true, true, true>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   const long long grid = (a.B + kLockThreads - 1) / kLockThreads;
   kern<<<(unsigned)grid, kLockThreads, smem, stream>>>(a, mt, md, my);
   *used = true;
   return cudaGetLastError();
+}
+
+cudaError_t launch_loglik_lockstep_ckpt(const BatchArgs& a, cudaStream_t stream, bool* used) {
+  *used = false;
+  if (a.Jr != 0 || a.Jg != 0 || a.lengths || a.N < 1 || !a.ckpt || !a.flags) return cudaSuccess;
+  if (a.Jc == 1 && a.ckpt_seg == 4) return launch_ckpt<2>(a, stream, used);
+  if (a.Jc == 2 && (a.ckpt_seg == 2 || a.ckpt_seg == 4)) return launch_ckpt<4>(a, stream, used);
+  return cudaSuccess;
 }
 
 namespace {

@@ -410,8 +410,8 @@ bool grad_lockstep_applies(int Jr, int Jc, int Jg, long long stride) {
 
 size_t grad_lockstep_scratch_doubles(long long B, int N, int Jc, int seg) {
   const size_t v1 = grad_lockstep_v1_scratch_doubles(B, N, Jc, seg);   // also what the fallback of Jc = 1 uses
-  if (Jc != 1) return v1;
-  const size_t v2 = grad2_scratch_doubles(B, N, seg);
+  if (Jc != 1 && Jc != 2) return v1;
+  const size_t v2 = grad2_scratch_doubles(B, N, seg, Jc);
   return v2 > v1 ? v2 : v1;
 }
 
@@ -425,7 +425,7 @@ size_t grad_lockstep_v1_scratch_doubles(long long B, int N, int Jc, int seg) {
 
 cudaError_t launch_grad_lockstep(const GradArgs& a, cudaStream_t stream, bool* used, int* launches) {
   *used = false;
-  if (a.Jc == 1 && !a.only) {      // one complex term: the two-kernel form (lockstep_grad2.cu)
+  if ((a.Jc == 1 || a.Jc == 2) && !a.only) {      // one or two complex terms: the two-kernel form (lockstep_grad2.cu)
     cudaError_t e = launch_grad2(a, stream, used, launches);
     if (e != cudaSuccess || *used) return e;
   }

@@ -284,6 +284,265 @@ k_grad2_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
   }
 }
 
+// ---- the same reverse sweep for two complex terms (J = 4), written over arrays --------------------------------
+// 26 tape rows per step instead of 12 and a 14-double checkpoint: segments of KSEG steps (the forward kernel leaves
+// a checkpoint at each), WARPS warps per CTA at up to 255 registers.  Whole series per warp only (few long J = 4
+// series go to the cooperative kernel and its batched adjoint scan).
+template <int J, int KSEG>
+struct RevN {
+  static constexpr int NP = J / 2, T3 = J * (J + 1) / 2;
+  static constexpr int kRowsN = T3 + 2 * J + 2 + 3 * NP;      // S, W, f, r, xr, e, cd, sd
+  static constexpr int kCk = T3 + J;                          // S + D W W^T (triangle), f + W x
+  static constexpr int kTile = kWarp * KSEG * 8;
+  static constexpr int kWarpB = ((3 * kTile + kPrevB + kRowsN * KSEG * kWarp * 8) + 1023) & ~1023;
+  static constexpr int WARPS = (int)((227 * 1024 - 4096) / kWarpB) < 8 ? (int)((227 * 1024 - 4096) / kWarpB) : 8;
+  static constexpr size_t smem = (size_t)WARPS * kWarpB + kBarBytes + kTrigTabN * 16 + kExpTabN * 8 + 1024;
+};
+template <int J>
+__device__ __forceinline__ constexpr int trn(int k, int j) { return k <= j ? j * (j + 1) / 2 + k : k * (k + 1) / 2 + j; }
+
+template <int J, int KSEG>
+__global__ void __maxnreg__(255)
+k_gradN_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_constant__ CUtensorMap tm_t,
+                const __grid_constant__ CUtensorMap tm_d, const __grid_constant__ CUtensorMap tm_y,
+                const __grid_constant__ CUtensorMap tm_p) {
+  using C = RevN<J, KSEG>;
+  constexpr int NP = C::NP, T3 = C::T3, NR = C::kRowsN, WARPS = C::WARPS;
+  static_assert(KSEG == 2 || KSEG == 4, "boxes of 2 or 4 points");
+  extern __shared__ unsigned char smem_dyn[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned char* smem_al = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
+  unsigned char* wtile = smem_al + (size_t)warp * C::kWarpB;
+  unsigned char* wprev = wtile + 3 * C::kTile;
+  double* tape = reinterpret_cast<double*>(wprev + kPrevB) + lane;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem_al + (size_t)WARPS * C::kWarpB) + warp;
+  double2* trig_tab = reinterpret_cast<double2*>(smem_al + (size_t)WARPS * C::kWarpB + kBarBytes);
+  double* exp_tab = reinterpret_cast<double*>(trig_tab + kTrigTabN);
+  cel_fill_tables(trig_tab, exp_tab, threadIdx.x, WARPS * kWarp);
+  __syncthreads();
+
+  const long long wg = (long long)blockIdx.x * WARPS + warp;
+  const long long b0 = wg * kWarp;
+  if (b0 >= a.B) return;
+  const long long b = b0 + lane;
+  const bool active = b < a.B;
+  const long long bb = active ? b : a.B - 1;
+  const int N = a.N, Jc = a.Jc;
+  const int nseg = (N + KSEG - 1) / KSEG;
+  const double* row = a.coeffs + bb * a.coeff_stride;
+  const double jitter = row[0];
+  double cf[NP][4], asum = 0.0;
+#pragma unroll
+  for (int p = 0; p < NP; ++p) {
+    cf[p][0] = row[1 + p]; cf[p][1] = row[1 + Jc + p]; cf[p][2] = -row[1 + 2 * Jc + p]; cf[p][3] = row[1 + 3 * Jc + p];
+    asum += cf[p][0];
+  }
+  const double aconst = asum + jitter;
+
+  if (lane == 0) {
+    mbar_init(bar, 1);
+    mbar_fence_init();
+  }
+  __syncwarp();
+  auto issue = [&](int s) {
+    if (lane == 0) {
+      fence_async_smem();
+      mbar_arrive_expect_tx(bar, 3u * C::kTile + kPrevB);
+      tma_load_2d(wprev, &tm_p, s * KSEG - 2, (int)b0, bar);
+      tma_load_2d(wtile, &tm_t, s * KSEG, (int)b0, bar);
+      tma_load_2d(wtile + C::kTile, &tm_d, s * KSEG, (int)b0, bar);
+      tma_load_2d(wtile + 2 * C::kTile, &tm_y, s * KSEG, (int)b0, bar);
+    }
+  };
+  issue(nseg - 1);
+  const double* ck = ckpt_base + ((size_t)wg * nseg * C::kCk) * kWarp + lane;
+  const unsigned char* lrow = wtile + lane * (KSEG * 8);
+  const int h0 = KSEG == 4 ? ((lane >> 2) & 1) << 4 : 0, h1 = h0 ^ 16;      // 32-byte swizzle of [32 x 4] boxes
+
+  double Pb[T3], gb_[J], Ga[NP], Gb[NP], Gc[NP], Gd[NP], sumA = 0.0;
+#pragma unroll
+  for (int i = 0; i < T3; ++i) Pb[i] = 0.0;
+#pragma unroll
+  for (int j = 0; j < J; ++j) gb_[j] = 0.0;
+#pragma unroll
+  for (int p = 0; p < NP; ++p) { Ga[p] = 0.0; Gb[p] = 0.0; Gc[p] = 0.0; Gd[p] = 0.0; }
+
+  double Sp[T3], fp[J];
+  auto load_state = [&](int s) {
+    if (s > 0) {
+      const double* q = ck + (size_t)s * (C::kCk * kWarp);
+#pragma unroll
+      for (int i = 0; i < T3; ++i) Sp[i] = q[i * kWarp];
+#pragma unroll
+      for (int j = 0; j < J; ++j) fp[j] = q[(T3 + j) * kWarp];
+    } else {
+#pragma unroll
+      for (int i = 0; i < T3; ++i) Sp[i] = 0.0;
+#pragma unroll
+      for (int j = 0; j < J; ++j) fp[j] = 0.0;
+    }
+  };
+  load_state(nseg - 1);
+
+  auto segment = [&](const int s, auto guard, const int nv) {
+    constexpr bool GUARD = decltype(guard)::value;
+    mbar_wait(bar, (unsigned)((nseg - 1 - s) & 1));
+    double rt[KSEG], rd[KSEG], ry[KSEG];
+#pragma unroll
+    for (int c = 0; c < KSEG / 2; ++c) {
+      const int off = KSEG == 4 ? (c == 0 ? h0 : h1) : 0;
+      const double2 v0 = *reinterpret_cast<const double2*>(lrow + off);
+      const double2 v1 = *reinterpret_cast<const double2*>(lrow + C::kTile + off);
+      const double2 v2 = *reinterpret_cast<const double2*>(lrow + 2 * C::kTile + off);
+      rt[2 * c] = v0.x; rt[2 * c + 1] = v0.y; rd[2 * c] = v1.x; rd[2 * c + 1] = v1.y; ry[2 * c] = v2.x; ry[2 * c + 1] = v2.y;
+    }
+    double tprev = s == 0 ? rt[0] : *reinterpret_cast<const double*>(wprev + lane * 16 + 8);
+    const double t_in = tprev;
+    __syncwarp();
+    if (s > 0) issue(s - 1);
+
+    // ---- recompute the segment, taping what the adjoint needs ----
+#pragma unroll
+    for (int i = 0; i < KSEG; ++i) {
+      if (!GUARD || i < nv) {
+        const double tn = rt[i], dx = tn - tprev;
+        double e[NP], cd[NP], sd[NP], u[J], S[T3], f[J];
+#pragma unroll
+        for (int p = 0; p < NP; ++p) {
+          cel_sincos_tab(cf[p][3] * tn, &sd[p], &cd[p], trig_tab);
+          e[p] = cel_exp_tab(cf[p][2] * dx, exp_tab);
+          u[2 * p] = fma(cf[p][0], cd[p], cf[p][1] * sd[p]);
+          u[2 * p + 1] = fma(cf[p][0], sd[p], -(cf[p][1] * cd[p]));
+        }
+        double ee[NP][NP];
+#pragma unroll
+        for (int p = 0; p < NP; ++p)
+#pragma unroll
+          for (int q = p; q < NP; ++q) ee[p][q] = e[p] * e[q];
+#pragma unroll
+        for (int j = 0; j < J; ++j)
+#pragma unroll
+          for (int q = 0; q <= j; ++q) S[trn<J>(q, j)] = ee[q / 2][j / 2] * Sp[trn<J>(q, j)];     // cholesky.h:154-160
+        double x = ry[i];
+#pragma unroll
+        for (int j = 0; j < J; ++j) { f[j] = e[j / 2] * fp[j]; x = fma(-u[j], f[j], x); }          // cholesky.h:350-354
+        double D = rd[i] + aconst, DW[J];
+#pragma unroll
+        for (int j = 0; j < J; ++j) {
+          double su = 0.0;
+#pragma unroll
+          for (int q = 0; q < J; ++q) su = (q == 0) ? S[trn<J>(0, j)] * u[0] : fma(S[trn<J>(q, j)], u[q], su);
+          D = fma(-u[j], su, D);
+          DW[j] = ((j & 1) ? sd[j / 2] : cd[j / 2]) - su;
+        }
+        const double r = fast_rcp_cubic(D);
+        double W[J];
+#pragma unroll
+        for (int j = 0; j < J; ++j) W[j] = DW[j] * r;
+#pragma unroll
+        for (int j = 0; j < J; ++j) {
+#pragma unroll
+          for (int q = 0; q <= j; ++q) Sp[trn<J>(q, j)] = fma(DW[j], W[q], S[trn<J>(q, j)]);
+          fp[j] = fma(W[j], x, f[j]);
+        }
+        tprev = tn;
+        double* q = tape + i * (NR * kWarp);
+#pragma unroll
+        for (int k = 0; k < T3; ++k) q[k * kWarp] = S[k];
+#pragma unroll
+        for (int j = 0; j < J; ++j) { q[(T3 + j) * kWarp] = W[j]; q[(T3 + J + j) * kWarp] = f[j]; }
+        q[(T3 + 2 * J) * kWarp] = r; q[(T3 + 2 * J + 1) * kWarp] = x * r;
+#pragma unroll
+        for (int p = 0; p < NP; ++p) {
+          q[(T3 + 2 * J + 2 + p) * kWarp] = e[p]; q[(T3 + 2 * J + 2 + NP + p) * kWarp] = cd[p];
+          q[(T3 + 2 * J + 2 + 2 * NP + p) * kWarp] = sd[p];
+        }
+      }
+    }
+    load_state(s - 1);     // the forward state is dead: the checkpoint of the segment below arrives during the adjoint
+
+    // ---- adjoint of the segment, last step first (the algebra of k_grad2_reverse, over arrays) ----
+#pragma unroll
+    for (int i = KSEG - 1; i >= 0; --i) {
+      if (!GUARD || i < nv) {
+        const double* q = tape + i * (NR * kWarp);
+        double S[T3], W[J], f[J], e[NP], cd[NP], sd[NP], u[J];
+#pragma unroll
+        for (int k = 0; k < T3; ++k) S[k] = q[k * kWarp];
+#pragma unroll
+        for (int j = 0; j < J; ++j) { W[j] = q[(T3 + j) * kWarp]; f[j] = q[(T3 + J + j) * kWarp]; }
+        const double r = q[(T3 + 2 * J) * kWarp], xr = q[(T3 + 2 * J + 1) * kWarp];
+#pragma unroll
+        for (int p = 0; p < NP; ++p) {
+          e[p] = q[(T3 + 2 * J + 2 + p) * kWarp]; cd[p] = q[(T3 + 2 * J + 2 + NP + p) * kWarp];
+          sd[p] = q[(T3 + 2 * J + 2 + 2 * NP + p) * kWarp];
+          u[2 * p] = fma(cf[p][0], cd[p], cf[p][1] * sd[p]);
+          u[2 * p + 1] = fma(cf[p][0], sd[p], -(cf[p][1] * cd[p]));
+        }
+        const double tn = rt[i];
+        const double ndx = (i == 0 ? t_in : rt[i == 0 ? 0 : i - 1]) - tn;
+        double wb[J], Dbar = fma(0.5 * xr, xr, -0.5 * r), xbar = -xr;
+#pragma unroll
+        for (int k = 0; k < J; ++k) {
+          double acc = 0.0;
+#pragma unroll
+          for (int j = 0; j < J; ++j) acc = fma(Pb[trn<J>(k, j)], W[j], acc);
+          wb[k] = fma(gb_[k], xr, acc + acc);
+          Dbar = fma(W[k], acc - wb[k], Dbar);
+          xbar = fma(gb_[k], W[k], xbar);
+        }
+        sumA += Dbar;
+        const double D2 = Dbar + Dbar;
+        double fb[J], ub[J], pe[J], hw[J], hv[J];
+#pragma unroll
+        for (int k = 0; k < J; ++k) {
+          fb[k] = fma(-xbar, u[k], gb_[k]);
+          double su = 0.0, sw = 0.0;
+#pragma unroll
+          for (int j = 0; j < J; ++j) { su = fma(S[trn<J>(k, j)], u[j], su); sw = fma(S[trn<J>(k, j)], wb[j], sw); }
+          ub[k] = fma(-D2, su, fma(-xbar, f[k], -sw));
+          pe[k] = fb[k] * f[k]; hw[k] = -0.5 * wb[k]; hv[k] = fma(Dbar, u[k], 0.5 * wb[k]);
+        }
+#pragma unroll
+        for (int j = 0; j < J; ++j)
+#pragma unroll
+          for (int k = 0; k <= j; ++k) {
+            const double t0 = fma(-u[k], hv[j], fma(hw[k], u[j], Pb[trn<J>(k, j)]));
+            const double ss = t0 * S[trn<J>(k, j)];
+            pe[k] = fma(2.0, ss, pe[k]);
+            if (k != j) pe[j] = fma(2.0, ss, pe[j]);
+            Pb[trn<J>(k, j)] = (e[k / 2] * e[j / 2]) * t0;
+          }
+#pragma unroll
+        for (int k = 0; k < J; ++k) gb_[k] = e[k / 2] * fb[k];
+#pragma unroll
+        for (int p = 0; p < NP; ++p) {
+          const int k = 2 * p;
+          Ga[p] = fma(ub[k + 1], sd[p], fma(ub[k], cd[p], Ga[p]));
+          Gb[p] = fma(-ub[k + 1], cd[p], fma(ub[k], sd[p], Gb[p]));
+          Gc[p] = fma(ndx, pe[k] + pe[k + 1], Gc[p]);
+          const double gq = fma(wb[k + 1], cd[p], fma(-wb[k], sd[p], fma(ub[k + 1], u[k], -(ub[k] * u[k + 1]))));
+          Gd[p] = fma(tn, gq, Gd[p]);
+        }
+      }
+    }
+  };
+
+  const int nfull = N / KSEG;
+  if (nfull < nseg) segment(nseg - 1, std::true_type(), N - nfull * KSEG);
+#pragma unroll 1
+  for (int s = nfull - 1; s >= 0; --s) segment(s, std::false_type(), KSEG);
+
+  if (active) {
+    double* g = a.out_grad + (size_t)b * (1 + 4 * Jc);
+    g[0] = (jitter > DBL_EPSILON) ? sumA : 0.0;
+#pragma unroll
+    for (int p = 0; p < NP; ++p) {
+      g[1 + p] = Ga[p] + sumA; g[1 + Jc + p] = Gb[p]; g[1 + 2 * Jc + p] = Gc[p]; g[1 + 3 * Jc + p] = Gd[p];
+    }
+  }
+}
+
 // carries into span c = carries out of span c+1 (a thread per series; the 2 x 2 case of k_adj_fold in grad.cu)
 __global__ void __launch_bounds__(128) k_grad2_fold(long long B, int K, double* xch) {
   const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -327,10 +586,12 @@ __global__ void __launch_bounds__(128) k_grad2_finish(GradArgs a, int K, const d
 }  // namespace
 
 // The batch goes through in pieces of at most this many series, so that the checkpoints of a piece
-// (10 bytes per point) stay below ~6 GB whatever the batch
-static long long grad2_piece(long long B, int N) {
-  const double per_series = 8.0 * kGrad2Ckpt * ((N + kSeg - 1) / kSeg);
-  long long piece = (long long)(6.0e9 / per_series) / (kRevWarps * kWarp) * (kRevWarps * kWarp);
+// (10 bytes per point at J = 2, 56 at J = 4) stay below ~12 GB whatever the batch
+static int ck_doubles(int Jc) { return Jc == 1 ? kGrad2Ckpt : 14; }
+static int ck_seg(int Jc) { return Jc == 1 ? kSeg : kGrad4Seg; }
+static long long grad2_piece(long long B, int N, int Jc = 1) {
+  const double per_series = 8.0 * ck_doubles(Jc) * ((N + ck_seg(Jc) - 1) / ck_seg(Jc));
+  long long piece = (long long)(12.0e9 / per_series) / (kRevWarps * kWarp) * (kRevWarps * kWarp);
   if (piece < 64 * kRevWarps * kWarp) piece = 64 * kRevWarps * kWarp;
   if (const char* e = getenv("CEL_GRAD2_PIECE")) { const long long v = atoll(e); if (v >= kWarp) piece = v / kWarp * kWarp; }   // testing knob
   return B < piece ? B : piece;
@@ -358,33 +619,38 @@ static int grad2_spans(long long B, int N, int* span_segs) {
 // (whatever the size of the last piece of a batch)
 static size_t xch_doubles() { return ((size_t)sm_count() * kRevWarps + kRevWarps) * kXchRows * kWarp; }
 
-size_t grad2_scratch_doubles(long long B, int N, int seg_v1) {
-  const long long piece = grad2_piece(B, N);
+size_t grad2_scratch_doubles(long long B, int N, int seg_v1, int Jc) {
+  const long long piece = grad2_piece(B, N, Jc);
   const size_t warps = (size_t)((piece + kWarp - 1) / kWarp);
-  const size_t nseg = (size_t)(N + kSeg - 1) / kSeg;
-  const size_t ck = warps * nseg * kGrad2Ckpt * kWarp;
-  const size_t v1 = grad_lockstep_v1_scratch_doubles(piece, N, 1, seg_v1);
-  return flag_doubles(piece) + (ck > v1 ? ck : v1) + xch_doubles();
+  const size_t nseg = (size_t)(N + ck_seg(Jc) - 1) / ck_seg(Jc);
+  const size_t ck = warps * nseg * ck_doubles(Jc) * kWarp;
+  const size_t v1 = grad_lockstep_v1_scratch_doubles(piece, N, Jc, seg_v1);
+  return flag_doubles(piece) + (ck > v1 ? ck : v1) + (Jc == 1 ? xch_doubles() : 0);
 }
 
 cudaError_t launch_grad2(const GradArgs& a, cudaStream_t stream, bool* used, int* launches) {
   *used = false;
   static const bool off = getenv("CEL_GRAD_V1") != nullptr;   // A/B knob: the first-generation kernel
-  if (off || a.Jr != 0 || a.Jc != 1 || a.Jg != 0 || a.stride <= 0 || a.span || a.only || a.N < 1 || a.B < 1)
+  static const bool off4 = getenv("CEL_GRAD4_V1") != nullptr;  // A/B knob: the same at J = 4
+  if (off || a.Jr != 0 || (a.Jc != 1 && a.Jc != 2) || a.Jg != 0 || a.stride <= 0 || a.span || a.only || a.N < 1 || a.B < 1)
     return cudaSuccess;
+  if (a.Jc == 2 && off4) return cudaSuccess;
   if ((a.seg % 8) != 0 || a.seg < 8) return cudaSuccess;
-  const long long piece = grad2_piece(a.B, a.N);
+  const int Jc = a.Jc, Pn = 1 + 4 * Jc, cseg = ck_seg(Jc);
+  using R4 = RevN<4, kGrad4Seg>;
+  const long long piece = grad2_piece(a.B, a.N, Jc);
   int* flags = reinterpret_cast<int*>(a.scratch);
   double* region = a.scratch + flag_doubles(piece);
   cudaError_t e = cudaFuncSetAttribute(k_grad2_reverse<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRevSmem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_grad2_reverse<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRevSmem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_grad2_reverse<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRevSmem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gradN_reverse<4, kGrad4Seg>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)R4::smem);
   if (e != cudaSuccess) return e;
   // the spans' exchange rows sit behind the larger of (checkpoints, scratch of the redo pass)
   size_t region_doubles;
   {
-    const size_t pw = (size_t)((piece + kWarp - 1) / kWarp), nsg = (size_t)(a.N + kSeg - 1) / kSeg;
-    const size_t ck = pw * nsg * kGrad2Ckpt * kWarp, v1 = grad_lockstep_v1_scratch_doubles(piece, a.N, 1, a.seg);
+    const size_t pw = (size_t)((piece + kWarp - 1) / kWarp), nsg = (size_t)(a.N + cseg - 1) / cseg;
+    const size_t ck = pw * nsg * ck_doubles(Jc) * kWarp, v1 = grad_lockstep_v1_scratch_doubles(piece, a.N, Jc, a.seg);
     region_doubles = ck > v1 ? ck : v1;
   }
   double* xch = region + region_doubles;
@@ -395,16 +661,17 @@ cudaError_t launch_grad2(const GradArgs& a, cudaStream_t stream, bool* used, int
     g.coeffs = a.coeffs + off0 * a.coeff_stride;
     g.t = a.t + off0 * a.stride; g.diag = a.diag + off0 * a.stride; g.y = a.y + off0 * a.stride;
     g.out_val = a.out_val ? a.out_val + off0 : nullptr;
-    g.out_grad = a.out_grad + off0 * 5;
+    g.out_grad = a.out_grad + off0 * Pn;
     g.out_logdet = a.out_logdet ? a.out_logdet + off0 : nullptr;
     g.out_quad = a.out_quad ? a.out_quad + off0 : nullptr;
     g.status = a.status ? a.status + off0 : nullptr;
     alignas(64) CUtensorMap mt, md, my, mp;
-    if (!(make_rows_map(&mt, g.t, nb, a.N, a.stride, kSeg) && make_rows_map(&md, g.diag, nb, a.N, a.stride, kSeg) &&
-          make_rows_map(&my, g.y, nb, a.N, a.stride, kSeg) && make_rows_map(&mp, g.t, nb, a.N, a.stride, 2, false)))
+    const bool swz = cseg == 4;      // [32 x 4] boxes are 32-byte swizzled, [32 x 2] boxes are plain 16-byte rows
+    if (!(make_rows_map(&mt, g.t, nb, a.N, a.stride, cseg, swz) && make_rows_map(&md, g.diag, nb, a.N, a.stride, cseg, swz) &&
+          make_rows_map(&my, g.y, nb, a.N, a.stride, cseg, swz) && make_rows_map(&mp, g.t, nb, a.N, a.stride, 2, false)))
       return off0 == 0 ? cudaSuccess : cudaErrorInvalidValue;
     BatchArgs f{};
-    f.B = nb; f.N = a.N; f.stride = a.stride; f.Jr = 0; f.Jc = 1; f.Jg = 0;
+    f.B = nb; f.N = a.N; f.stride = a.stride; f.Jr = 0; f.Jc = Jc; f.Jg = 0; f.ckpt_seg = cseg;
     f.coeffs = g.coeffs; f.coeff_stride = a.coeff_stride;
     f.t = g.t; f.diag = g.diag; f.y = g.y;
     f.out_logdet = g.out_logdet; f.out_quad = g.out_quad; f.out_half = g.out_val; f.status = g.status;
@@ -415,8 +682,11 @@ cudaError_t launch_grad2(const GradArgs& a, cudaStream_t stream, bool* used, int
     if (!fwd) return off0 == 0 ? cudaSuccess : cudaErrorInvalidValue;   // (cannot differ between pieces)
     const long long warps = (nb + kWarp - 1) / kWarp;
     int span_segs = 0;
-    const int K = grad2_spans(nb, a.N, &span_segs);
-    if (K == 1) {
+    const int K = Jc == 1 ? grad2_spans(nb, a.N, &span_segs) : 1;
+    if (Jc == 2) {
+      k_gradN_reverse<4, kGrad4Seg><<<(unsigned)((warps + R4::WARPS - 1) / R4::WARPS), R4::WARPS * kWarp, R4::smem, stream>>>(
+          g, region, mt, md, my, mp);
+    } else if (K == 1) {
       k_grad2_reverse<0><<<(unsigned)((warps + kRevWarps - 1) / kRevWarps), kRevThreads, kRevSmem, stream>>>(
           g, region, mt, md, my, mp, 1, span_segs, nullptr);
     } else {                                             // few long series: probe, fold, final, finish over K spans
