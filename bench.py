@@ -414,7 +414,7 @@ def bench_batched(ctx, wl, steps, warmup, e2e_steps, data=None, cpu=True, with_g
         grad_extra = {"value": world * B * N * J / (g_ms * 1e-3), "unit": UNIT, "ms_per_step": g_ms,
                       "roofline": {"achieved": alg_g / (g_ms * 1e-3) / 1e9, "frac": alg_g / (g_ms * 1e-3) / 1e9 / peak,
                                    "traffic": ncu_traffic(workload_key + "_grad"), "algorithmic_bytes_per_launch": alg_g,
-                                   "kernel": ("k_loglik_lockstep2<CKPT> + k_grad2_reverse" if J == 2 else "k_grad_lockstep") if J <= 4 else "k_grad_coop"},
+                                   "kernel": ("k_loglik_lockstep2<CKPT> + " + ("k_grad2_reverse" if J == 2 else "k_gradN_reverse")) if J <= 4 else "k_grad_coop"},
                       "what": "cel_batched_grad_log_likelihood on the same batch (value + 1+2Jr+4Jc derivatives per series)"}
 
     if rank != 0:
