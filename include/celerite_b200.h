@@ -110,7 +110,10 @@ int cel_predict(cel_solver* s, int N, const double* y, int M, const double* xs, 
  * constant: the binding layer adds the reference's -0.5*M_PI*log(N) (solver.cpp:415).
  * grad[0 .. 2Jr+4Jc] = d val / d [jitter, a_real, c_real, a_comp, b_comp, c_comp, d_comp]; the
  * jitter slot is forced to 0 when jitter <= DBL_EPSILON (solver.cpp:377-389, 418-426).
- * Computed by a reverse-mode sweep (one forward + one adjoint pass), not forward-mode AD. */
+ * Computed by a reverse-mode sweep (one forward + one adjoint pass), not forward-mode AD; from
+ * N = 1,024 on (no general rows, J <= 32) the adjoint pass runs as an exact two-pass scan over time
+ * spans behind the forward sweep, which itself is cut into spans behind warm-up halos from N = 16,384
+ * on when the kernel forgets fast enough (checked at the span edges, else one serial forward sweep). */
 int cel_grad_log_likelihood(cel_solver* s, double jitter,
                             int Jr, const double* a_real, const double* c_real,
                             int Jc, const double* a_comp, const double* b_comp,
@@ -157,7 +160,11 @@ int cel_batched_log_likelihood_ragged(cel_solver* s, int64_t B, int N, int64_t s
                                       int32_t* status, unsigned flags);
 
 /* Same sweep plus the reverse-mode gradient (solver.cpp:347-463 per series).
- * out_val[b] = -0.5*(quad+logdet) (no constant), out_grad[b*P + k], P = 1+2Jr+4Jc. */
+ * out_val[b] = -0.5*(quad+logdet) (no constant), out_grad[b*P + k], P = 1+2Jr+4Jc.
+ * One or two complex terms (Jr = 0, Jc <= 2) take the thread-per-series two-kernel form (forward sweep
+ * leaving checkpoints, reverse sweep over them); everything else the cooperative kernel.  The handle's
+ * scratch grows with the batch (checkpoints: 10 bytes per point at J = 2, 56 at J = 4, at most ~12 GB
+ * at a time; larger batches go through in pieces). */
 int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t stride,
                                     int Jr, int Jc, const double* coeffs, int64_t coeff_stride,
                                     const double* t, const double* diag, const double* y,
