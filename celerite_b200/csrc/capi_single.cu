@@ -750,6 +750,9 @@ int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t str
     size_t n = cel::grad_scratch_doubles(nb, N, J, seg);
     if (lock) { const size_t m = cel::grad_lockstep_scratch_doubles(nb, N, Jc, seg); if (m > n) n = m; }
     else { const size_t m = cel::grad_batch_scan_scratch_doubles(nb, N, J); if (m > n) n = m; }
+    if (cel::grad_mixed_applies(nb, N, Jr, Jc, stride == 0 ? 0 : (flags & CEL_HOST_POINTERS ? N : stride))) {
+      const size_t m = cel::grad_mixed_scratch_doubles(nb, N, Jr, Jc); if (m > n) n = m;
+    }
     return dbytes(n);
   };
   auto launch = [&](cel::GradArgs& ga) -> cudaError_t {
@@ -757,6 +760,10 @@ int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t str
     int nl = 0;
     if (lock) {
       cudaError_t e = cel::launch_grad_lockstep(ga, st, &used, &nl);
+      if (e != cudaSuccess) return e;
+    }
+    if (!used && !lock) {       // real + complex terms, J <= 4, thousands of series: thread-per-series two-kernel form
+      cudaError_t e = cel::launch_grad_mixed(ga, st, &used, &nl);
       if (e != cudaSuccess) return e;
     }
     if (!used && !lock) {       // few long series on the cooperative kernel: forward sweep + adjoint scan over spans

@@ -102,6 +102,7 @@ template <int JP, bool SPAN = false, int MODE = 0>
 __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   using C = GradCfg<JP, MODE>;
   constexpr int L = C::L, G = C::G, T = C::T, E = C::E, BLK = C::BLK;
+  if (a.run_if && *a.run_if == 0) return;        // a redo pass nobody asked for (uniform over the grid)
   constexpr int kGenIlp = 4;   // generator items per lane evaluated together (8 spills here: 23.8 -> 25.4 ms at J = 8)
   extern __shared__ __align__(16) double smem[];
   const int lane = threadIdx.x, g = lane / L, k = lane % L;

@@ -74,6 +74,7 @@ struct BatchArgs {
   double* ckpt;
   int ckpt_seg;            // steps between checkpoints (2 or 4); J (J+1)/2 + J doubles each
   int* flags;
+  int* any_flag;           // optional: set to 1 when any series of the batch is flagged
   double* out_half;        // -0.5 * (quad + logdet), no constant (the gradient entry points' value)
 };
 
@@ -121,6 +122,7 @@ struct GradArgs {
   double* out_quad;     // optional
   int* status;
   const int* only;      // lockstep kernel: NULL, or per series non-zero = wanted (warps with none leave at once)
+  const int* run_if;    // cooperative kernel: NULL, or a device flag; the whole launch leaves at once when it is 0
   double* scratch;      // grad_scratch_doubles(B, N, J, seg) doubles
   int seg;              // checkpoint distance (multiple of 16)
   // Time spans of ONE long series (launch_grad_spans): group b sweeps [span[4b], span[4b+3])
@@ -169,6 +171,11 @@ size_t grad2_scratch_doubles(long long B, int N, int seg_v1, int Jc = 1);
 size_t grad_lockstep_v1_scratch_doubles(long long B, int N, int Jc, int seg);
 cudaError_t launch_grad_lockstep_v1(const GradArgs& a, cudaStream_t stream, bool* used);
 cudaError_t launch_grad2(const GradArgs& a, cudaStream_t stream, bool* used, int* launches);
+// Mixed real + complex terms, J = Jr + 2 Jc <= 4 with Jr >= 1 (e.g. RealTerm + ComplexTerm, BASELINE config 1's kernel,
+// as a batch): the same two kernels; when ANY series leaves the fast path the cooperative kernel redoes the batch.
+bool grad_mixed_applies(long long B, int N, int Jr, int Jc, long long stride);
+size_t grad_mixed_scratch_doubles(long long B, int N, int Jr, int Jc);
+cudaError_t launch_grad_mixed(const GradArgs& a, cudaStream_t stream, bool* used, int* launches);
 
 // One stored factor (reference layout) applied to nrhs right-hand sides, DEVICE pointers.
 struct SweepArgs {

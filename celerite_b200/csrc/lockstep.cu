@@ -390,7 +390,7 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
     const int nckpt = (N + cseg - 1) / cseg;
     double* ckp = CKPT ? a.ckpt + ((size_t)(b0 / kWarp) * nckpt * kCkD) * kWarp + lane : nullptr;
     auto checkpoint = [&](int s) {
-      if constexpr (CKPT && ALLC) {
+      if constexpr (CKPT) {
         if (b0 >= a.B) return;     // a warp of idle lanes only (the last CTA): it owns no checkpoint rows
         double* q = ckp + (size_t)s * (kCkD * kWarp);
 #pragma unroll
@@ -516,6 +516,7 @@ k_loglik_lockstep2(BatchArgs a, const __grid_constant__ CUtensorMap tm_t, const 
     if (fail) { logdet = nan; q = nan; }
     if (CKPT) {
       a.flags[b] = bad ? 1 : 0;
+      if (bad && a.any_flag) atomicOr(a.any_flag, 1);
       if (a.out_half) a.out_half[b] = -0.5 * (q + logdet);
     }
     if (a.out_logdet) a.out_logdet[b] = logdet;
@@ -561,7 +562,7 @@ cudaError_t launch_v2(const BatchArgs& a, cudaStream_t stream, bool* used) {
 }  // namespace
 
 // forward half of the two-kernel gradient (J = 2 or 4, all complex): the fused kernel, leaving checkpoints
-template <int J>
+template <int J, bool ALLC>
 static cudaError_t launch_ckpt(const BatchArgs& a, cudaStream_t stream, bool* used) {
   constexpr int T = 8, STAGES = 2;
   constexpr int WARPS = kLockThreads / kWarp;
@@ -571,8 +572,8 @@ static cudaError_t launch_ckpt(const BatchArgs& a, cudaStream_t stream, bool* us
         make_series_map(&my, a.y, a.B, a.N, a.stride, T)))
     return cudaSuccess;
   static const bool nopipe = getenv("CEL_LOCK_NOPIPE") != nullptr;
-  auto kern = (nopipe || J > 2) ? k_loglik_lockstep2<J, true, lock_maxreg(J), true, false, true>
-                                : k_loglik_lockstep2<J, true, lock_maxreg(J), true, true, true>;
+  auto kern = (nopipe || J > 2 || !ALLC) ? k_loglik_lockstep2<J, ALLC, lock_maxreg(J), true, false, true>
+                                         : k_loglik_lockstep2<J, ALLC, lock_maxreg(J), true, true, true>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   const long long grid = (a.B + kLockThreads - 1) / kLockThreads;
@@ -583,10 +584,21 @@ static cudaError_t launch_ckpt(const BatchArgs& a, cudaStream_t stream, bool* us
 
 cudaError_t launch_loglik_lockstep_ckpt(const BatchArgs& a, cudaStream_t stream, bool* used) {
   *used = false;
-  if (a.Jr != 0 || a.Jg != 0 || a.lengths || a.N < 1 || !a.ckpt || !a.flags) return cudaSuccess;
-  if (a.Jc == 1 && a.ckpt_seg == 4) return launch_ckpt<2>(a, stream, used);
-  if (a.Jc == 2 && (a.ckpt_seg == 2 || a.ckpt_seg == 4)) return launch_ckpt<4>(a, stream, used);
-  return cudaSuccess;
+  if (a.Jg != 0 || a.lengths || a.N < 1 || !a.ckpt || !a.flags) return cudaSuccess;
+  const int J = a.Jr + 2 * a.Jc;
+  if (a.Jr == 0) {
+    if (a.Jc == 1 && a.ckpt_seg == 4) return launch_ckpt<2, true>(a, stream, used);
+    if (a.Jc == 2 && (a.ckpt_seg == 2 || a.ckpt_seg == 4)) return launch_ckpt<4, true>(a, stream, used);
+    return cudaSuccess;
+  }
+  if (a.ckpt_seg != 2) return cudaSuccess;      // real rows present: segments of 2 steps (lockstep_grad2.cu, launch_grad_mixed)
+  switch (J) {
+    case 1: return launch_ckpt<1, false>(a, stream, used);
+    case 2: return launch_ckpt<2, false>(a, stream, used);
+    case 3: return launch_ckpt<3, false>(a, stream, used);
+    case 4: return launch_ckpt<4, false>(a, stream, used);
+    default: return cudaSuccess;
+  }
 }
 
 namespace {

@@ -287,14 +287,15 @@ k_grad2_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
   }
 }
 
-// ---- the same reverse sweep for two complex terms (J = 4), written over arrays --------------------------------
-// 26 tape rows per step instead of 12 and a 14-double checkpoint: segments of KSEG steps (the forward kernel leaves
-// a checkpoint at each), WARPS warps per CTA at up to 255 registers.  Whole series per warp only (few long J = 4
-// series go to the cooperative kernel and its batched adjoint scan).
-template <int J, int KSEG>
+// ---- the same reverse sweep written over arrays: two complex terms (J = 4), and mixed real + complex terms ------
+// JC complex pairs (rows 2p, 2p+1) followed by JR real rows, J = 2 JC + JR <= 4 -- the row order of lockstep.cu, whose
+// checkpoints are read here.  At J = 4: 26 tape rows per step instead of 12 and a 14-double checkpoint, so segments of
+// KSEG = 2 steps, WARPS warps per CTA at up to 255 registers.  Whole series per warp only (few long series go to the
+// cooperative kernel and its batched adjoint scan).
+template <int JC, int JR, int KSEG>
 struct RevN {
-  static constexpr int NP = J / 2, T3 = J * (J + 1) / 2;
-  static constexpr int kRowsN = T3 + 2 * J + 2 + 3 * NP;      // S, W, f, r, xr, e, cd, sd
+  static constexpr int J = 2 * JC + JR, T3 = J * (J + 1) / 2;
+  static constexpr int kRowsN = T3 + 2 * J + 2 + 3 * JC + JR;  // S, W, f, r, xr, e, cd, sd of the pairs, e of the real rows
   static constexpr int kCk = T3 + J;                          // S + D W W^T (triangle), f + W x
   static constexpr int kTile = kWarp * KSEG * 8;
   static constexpr int kWarpB = ((3 * kTile + kPrevB + kRowsN * KSEG * kWarp * 8) + 1023) & ~1023;
@@ -304,13 +305,14 @@ struct RevN {
 template <int J>
 __device__ __forceinline__ constexpr int trn(int k, int j) { return k <= j ? j * (j + 1) / 2 + k : k * (k + 1) / 2 + j; }
 
-template <int J, int KSEG>
+template <int JC, int JR, int KSEG>
 __global__ void __maxnreg__(255)
 k_gradN_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_constant__ CUtensorMap tm_t,
                 const __grid_constant__ CUtensorMap tm_d, const __grid_constant__ CUtensorMap tm_y,
                 const __grid_constant__ CUtensorMap tm_p) {
-  using C = RevN<J, KSEG>;
-  constexpr int NP = C::NP, T3 = C::T3, NR = C::kRowsN, WARPS = C::WARPS;
+  using C = RevN<JC, JR, KSEG>;
+  constexpr int J = C::J, NP = JC, T3 = C::T3, NR = C::kRowsN, WARPS = C::WARPS;
+  constexpr int NPA = JC > 0 ? JC : 1, NRA = JR > 0 ? JR : 1;     // array extents (no zero-length arrays)
   static_assert(KSEG == 2 || KSEG == 4, "boxes of 2 or 4 points");
   extern __shared__ unsigned char smem_dyn[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -330,14 +332,17 @@ k_gradN_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
   const long long b = b0 + lane;
   const bool active = b < a.B;
   const long long bb = active ? b : a.B - 1;
-  const int N = a.N, Jc = a.Jc;
+  const int N = a.N, Jr = a.Jr, Jc = a.Jc;
   const int nseg = (N + KSEG - 1) / KSEG;
-  const double* row = a.coeffs + bb * a.coeff_stride;
+  const double* row = a.coeffs + bb * a.coeff_stride;      // [jitter, a_real, c_real, a_comp, b_comp, c_comp, d_comp]
   const double jitter = row[0];
-  double cf[NP][4], asum = 0.0;
+  double cf[NPA][4], ar[NRA], ncr[NRA], asum = 0.0;
+#pragma unroll
+  for (int r = 0; r < JR; ++r) { ar[r] = row[1 + r]; ncr[r] = -row[1 + Jr + r]; asum += ar[r]; }
 #pragma unroll
   for (int p = 0; p < NP; ++p) {
-    cf[p][0] = row[1 + p]; cf[p][1] = row[1 + Jc + p]; cf[p][2] = -row[1 + 2 * Jc + p]; cf[p][3] = row[1 + 3 * Jc + p];
+    const double* q = row + 1 + 2 * Jr;
+    cf[p][0] = q[p]; cf[p][1] = q[Jc + p]; cf[p][2] = -q[2 * Jc + p]; cf[p][3] = q[3 * Jc + p];
     asum += cf[p][0];
   }
   const double aconst = asum + jitter;
@@ -362,13 +367,15 @@ k_gradN_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
   const unsigned char* lrow = wtile + lane * (KSEG * 8);
   const int h0 = KSEG == 4 ? ((lane >> 2) & 1) << 4 : 0, h1 = h0 ^ 16;      // 32-byte swizzle of [32 x 4] boxes
 
-  double Pb[T3], gb_[J], Ga[NP], Gb[NP], Gc[NP], Gd[NP], sumA = 0.0;
+  double Pb[T3], gb_[J], Ga[NPA], Gb[NPA], Gc[NPA], Gd[NPA], Ra[NRA], Rc[NRA], sumA = 0.0;
 #pragma unroll
   for (int i = 0; i < T3; ++i) Pb[i] = 0.0;
 #pragma unroll
   for (int j = 0; j < J; ++j) gb_[j] = 0.0;
 #pragma unroll
-  for (int p = 0; p < NP; ++p) { Ga[p] = 0.0; Gb[p] = 0.0; Gc[p] = 0.0; Gd[p] = 0.0; }
+  for (int p = 0; p < NPA; ++p) { Ga[p] = 0.0; Gb[p] = 0.0; Gc[p] = 0.0; Gd[p] = 0.0; }
+#pragma unroll
+  for (int r = 0; r < NRA; ++r) { Ra[r] = 0.0; Rc[r] = 0.0; }
 
   double Sp[T3], fp[J];
   auto load_state = [&](int s) {
@@ -386,6 +393,8 @@ k_gradN_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
     }
   };
   load_state(nseg - 1);
+  // tape rows behind S, W, f, r, xr: e, cos, sin of every pair, then e of every real row
+  constexpr int kGen = T3 + 2 * J + 2;
 
   auto segment = [&](const int s, auto guard, const int nv) {
     constexpr bool GUARD = decltype(guard)::value;
@@ -409,26 +418,28 @@ k_gradN_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
     for (int i = 0; i < KSEG; ++i) {
       if (!GUARD || i < nv) {
         const double tn = rt[i], dx = tn - tprev;
-        double e[NP], cd[NP], sd[NP], u[J], S[T3], f[J];
+        double e[NPA], cd[NPA], sd[NPA], er[NRA], ph[J], u[J], v[J], S[T3], f[J];
 #pragma unroll
         for (int p = 0; p < NP; ++p) {
           cel_sincos_tab(cf[p][3] * tn, &sd[p], &cd[p], trig_tab);
           e[p] = cel_exp_tab(cf[p][2] * dx, exp_tab);
           u[2 * p] = fma(cf[p][0], cd[p], cf[p][1] * sd[p]);
           u[2 * p + 1] = fma(cf[p][0], sd[p], -(cf[p][1] * cd[p]));
+          v[2 * p] = cd[p]; v[2 * p + 1] = sd[p];
+          ph[2 * p] = e[p]; ph[2 * p + 1] = e[p];
         }
-        double ee[NP][NP];
 #pragma unroll
-        for (int p = 0; p < NP; ++p)
-#pragma unroll
-          for (int q = p; q < NP; ++q) ee[p][q] = e[p] * e[q];
+        for (int r = 0; r < JR; ++r) {                       // cholesky.h:129-133
+          er[r] = cel_exp_tab(ncr[r] * dx, exp_tab);
+          u[2 * JC + r] = ar[r]; v[2 * JC + r] = 1.0; ph[2 * JC + r] = er[r];
+        }
 #pragma unroll
         for (int j = 0; j < J; ++j)
 #pragma unroll
-          for (int q = 0; q <= j; ++q) S[trn<J>(q, j)] = ee[q / 2][j / 2] * Sp[trn<J>(q, j)];     // cholesky.h:154-160
+          for (int q = 0; q <= j; ++q) S[trn<J>(q, j)] = (ph[q] * ph[j]) * Sp[trn<J>(q, j)];        // cholesky.h:154-160
         double x = ry[i];
 #pragma unroll
-        for (int j = 0; j < J; ++j) { f[j] = e[j / 2] * fp[j]; x = fma(-u[j], f[j], x); }          // cholesky.h:350-354
+        for (int j = 0; j < J; ++j) { f[j] = ph[j] * fp[j]; x = fma(-u[j], f[j], x); }               // cholesky.h:350-354
         double D = rd[i] + aconst, DW[J];
 #pragma unroll
         for (int j = 0; j < J; ++j) {
@@ -436,7 +447,7 @@ k_gradN_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
 #pragma unroll
           for (int q = 0; q < J; ++q) su = (q == 0) ? S[trn<J>(0, j)] * u[0] : fma(S[trn<J>(q, j)], u[q], su);
           D = fma(-u[j], su, D);
-          DW[j] = ((j & 1) ? sd[j / 2] : cd[j / 2]) - su;
+          DW[j] = v[j] - su;
         }
         const double r = fast_rcp_cubic(D);
         double W[J];
@@ -457,9 +468,10 @@ k_gradN_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
         q[(T3 + 2 * J) * kWarp] = r; q[(T3 + 2 * J + 1) * kWarp] = x * r;
 #pragma unroll
         for (int p = 0; p < NP; ++p) {
-          q[(T3 + 2 * J + 2 + p) * kWarp] = e[p]; q[(T3 + 2 * J + 2 + NP + p) * kWarp] = cd[p];
-          q[(T3 + 2 * J + 2 + 2 * NP + p) * kWarp] = sd[p];
+          q[(kGen + p) * kWarp] = e[p]; q[(kGen + NP + p) * kWarp] = cd[p]; q[(kGen + 2 * NP + p) * kWarp] = sd[p];
         }
+#pragma unroll
+        for (int r2 = 0; r2 < JR; ++r2) q[(kGen + 3 * NP + r2) * kWarp] = er[r2];
       }
     }
     load_state(s - 1);     // the forward state is dead: the checkpoint of the segment below arrives during the adjoint
@@ -469,7 +481,7 @@ k_gradN_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
     for (int i = KSEG - 1; i >= 0; --i) {
       if (!GUARD || i < nv) {
         const double* q = tape + i * (NR * kWarp);
-        double S[T3], W[J], f[J], e[NP], cd[NP], sd[NP], u[J];
+        double S[T3], W[J], f[J], cd[NPA], sd[NPA], ph[J], u[J];
 #pragma unroll
         for (int k = 0; k < T3; ++k) S[k] = q[k * kWarp];
 #pragma unroll
@@ -477,11 +489,14 @@ k_gradN_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
         const double r = q[(T3 + 2 * J) * kWarp], xr = q[(T3 + 2 * J + 1) * kWarp];
 #pragma unroll
         for (int p = 0; p < NP; ++p) {
-          e[p] = q[(T3 + 2 * J + 2 + p) * kWarp]; cd[p] = q[(T3 + 2 * J + 2 + NP + p) * kWarp];
-          sd[p] = q[(T3 + 2 * J + 2 + 2 * NP + p) * kWarp];
+          const double e = q[(kGen + p) * kWarp];
+          cd[p] = q[(kGen + NP + p) * kWarp]; sd[p] = q[(kGen + 2 * NP + p) * kWarp];
           u[2 * p] = fma(cf[p][0], cd[p], cf[p][1] * sd[p]);
           u[2 * p + 1] = fma(cf[p][0], sd[p], -(cf[p][1] * cd[p]));
+          ph[2 * p] = e; ph[2 * p + 1] = e;
         }
+#pragma unroll
+        for (int r2 = 0; r2 < JR; ++r2) { ph[2 * JC + r2] = q[(kGen + 3 * NP + r2) * kWarp]; u[2 * JC + r2] = ar[r2]; }
         const double tn = rt[i];
         const double ndx = (i == 0 ? t_in : rt[i == 0 ? 0 : i - 1]) - tn;
         double wb[J], Dbar = fma(0.5 * xr, xr, -0.5 * r), xbar = -xr;
@@ -514,10 +529,10 @@ k_gradN_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
             const double ss = t0 * S[trn<J>(k, j)];
             pe[k] = fma(2.0, ss, pe[k]);
             if (k != j) pe[j] = fma(2.0, ss, pe[j]);
-            Pb[trn<J>(k, j)] = (e[k / 2] * e[j / 2]) * t0;
+            Pb[trn<J>(k, j)] = (ph[k] * ph[j]) * t0;
           }
 #pragma unroll
-        for (int k = 0; k < J; ++k) gb_[k] = e[k / 2] * fb[k];
+        for (int k = 0; k < J; ++k) gb_[k] = ph[k] * fb[k];
 #pragma unroll
         for (int p = 0; p < NP; ++p) {
           const int k = 2 * p;
@@ -526,6 +541,11 @@ k_gradN_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
           Gc[p] = fma(ndx, pe[k] + pe[k + 1], Gc[p]);
           const double gq = fma(wb[k + 1], cd[p], fma(-wb[k], sd[p], fma(ub[k + 1], u[k], -(ub[k] * u[k + 1]))));
           Gd[p] = fma(tn, gq, Gd[p]);
+        }
+#pragma unroll
+        for (int r2 = 0; r2 < JR; ++r2) {                    // real rows: v = 1, u = a (solver.cpp:392-404)
+          Ra[r2] += ub[2 * JC + r2];
+          Rc[r2] = fma(ndx, pe[2 * JC + r2], Rc[r2]);
         }
       }
     }
@@ -537,11 +557,14 @@ k_gradN_reverse(GradArgs a, const double* __restrict__ ckpt_base, const __grid_c
   for (int s = nfull - 1; s >= 0; --s) segment(s, std::false_type(), KSEG);
 
   if (active) {
-    double* g = a.out_grad + (size_t)b * (1 + 4 * Jc);
+    double* g = a.out_grad + (size_t)b * (1 + 2 * Jr + 4 * Jc);
     g[0] = (jitter > DBL_EPSILON) ? sumA : 0.0;
 #pragma unroll
+    for (int r = 0; r < JR; ++r) { g[1 + r] = Ra[r] + sumA; g[1 + Jr + r] = Rc[r]; }
+#pragma unroll
     for (int p = 0; p < NP; ++p) {
-      g[1 + p] = Ga[p] + sumA; g[1 + Jc + p] = Gb[p]; g[1 + 2 * Jc + p] = Gc[p]; g[1 + 3 * Jc + p] = Gd[p];
+      double* q = g + 1 + 2 * Jr;
+      q[p] = Ga[p] + sumA; q[Jc + p] = Gb[p]; q[2 * Jc + p] = Gc[p]; q[3 * Jc + p] = Gd[p];
     }
   }
 }
@@ -640,14 +663,14 @@ cudaError_t launch_grad2(const GradArgs& a, cudaStream_t stream, bool* used, int
   if (a.Jc == 2 && off4) return cudaSuccess;
   if ((a.seg % 8) != 0 || a.seg < 8) return cudaSuccess;
   const int Jc = a.Jc, Pn = 1 + 4 * Jc, cseg = ck_seg(Jc);
-  using R4 = RevN<4, kGrad4Seg>;
+  using R4 = RevN<2, 0, kGrad4Seg>;
   const long long piece = grad2_piece(a.B, a.N, Jc);
   int* flags = reinterpret_cast<int*>(a.scratch);
   double* region = a.scratch + flag_doubles(piece);
   cudaError_t e = cudaFuncSetAttribute(k_grad2_reverse<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRevSmem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_grad2_reverse<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRevSmem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_grad2_reverse<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRevSmem);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gradN_reverse<4, kGrad4Seg>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)R4::smem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gradN_reverse<2, 0, kGrad4Seg>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)R4::smem);
   if (e != cudaSuccess) return e;
   // the spans' exchange rows sit behind the larger of (checkpoints, scratch of the redo pass)
   size_t region_doubles;
@@ -687,7 +710,7 @@ cudaError_t launch_grad2(const GradArgs& a, cudaStream_t stream, bool* used, int
     int span_segs = 0;
     const int K = Jc == 1 ? grad2_spans(nb, a.N, &span_segs) : 1;
     if (Jc == 2) {
-      k_gradN_reverse<4, kGrad4Seg><<<(unsigned)((warps + R4::WARPS - 1) / R4::WARPS), R4::WARPS * kWarp, R4::smem, stream>>>(
+      k_gradN_reverse<2, 0, kGrad4Seg><<<(unsigned)((warps + R4::WARPS - 1) / R4::WARPS), R4::WARPS * kWarp, R4::smem, stream>>>(
           g, region, mt, md, my, mp);
     } else if (K == 1) {
       k_grad2_reverse<0><<<(unsigned)((warps + kRevWarps - 1) / kRevWarps), kRevThreads, kRevSmem, stream>>>(
@@ -711,6 +734,82 @@ cudaError_t launch_grad2(const GradArgs& a, cudaStream_t stream, bool* used, int
     if (!redo) return cudaErrorInvalidValue;
     if (launches) *launches += 3;
   }
+  *used = true;
+  return cudaSuccess;
+}
+
+// ---- mixed real + complex terms (J = Jr + 2 Jc <= 4, Jr >= 1) ---------------------------------------------------------
+namespace {
+constexpr int kMixSeg = 2;
+
+template <int JC, int JR>
+cudaError_t launch_mixed_reverse(const GradArgs& g, const double* ckpt, const CUtensorMap& mt, const CUtensorMap& md,
+                                 const CUtensorMap& my, const CUtensorMap& mp, cudaStream_t stream) {
+  using R = RevN<JC, JR, kMixSeg>;
+  auto kern = k_gradN_reverse<JC, JR, kMixSeg>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)R::smem);
+  if (e != cudaSuccess) return e;
+  const long long warps = (g.B + kWarp - 1) / kWarp;
+  kern<<<(unsigned)((warps + R::WARPS - 1) / R::WARPS), R::WARPS * kWarp, R::smem, stream>>>(g, ckpt, mt, md, my, mp);
+  return cudaGetLastError();
+}
+}  // namespace
+
+// Worth it from a few thousand series on (a thread per series); checkpoints of the whole batch at once (<= 12 GB)
+bool grad_mixed_applies(long long B, int N, int Jr, int Jc, long long stride) {
+  static const bool off = getenv("CEL_NO_LOCKSTEP_GRAD") != nullptr || getenv("CEL_GRAD_MIXED_OFF") != nullptr;   // A/B knobs
+  const int J = Jr + 2 * Jc;
+  if (off || Jr < 1 || J > 4 || stride <= 0 || (stride & 1) || B < 2048 || N < 1) return false;
+  const double ck = 8.0 * (J * (J + 1) / 2 + J) * ((N + kMixSeg - 1) / kMixSeg) * (double)B;
+  return ck <= 12.0e9;
+}
+
+size_t grad_mixed_scratch_doubles(long long B, int N, int Jr, int Jc) {
+  const int J = Jr + 2 * Jc;
+  const size_t warps = (size_t)((B + kWarp - 1) / kWarp), nseg = (size_t)(N + kMixSeg - 1) / kMixSeg;
+  const size_t ck = warps * nseg * (size_t)(J * (J + 1) / 2 + J) * kWarp;
+  const size_t coop = grad_scratch_doubles(B, N, J, grad_default_segment(N));      // the redo pass
+  return flag_doubles(B) + (ck > coop ? ck : coop);
+}
+
+cudaError_t launch_grad_mixed(const GradArgs& a, cudaStream_t stream, bool* used, int* launches) {
+  *used = false;
+  if (a.Jg != 0 || a.span || a.only || !grad_mixed_applies(a.B, a.N, a.Jr, a.Jc, a.stride)) return cudaSuccess;
+  int* flags = reinterpret_cast<int*>(a.scratch);
+  int* any_flag = flags + a.B;                         // (flag_doubles leaves room behind the B flags)
+  double* region = a.scratch + flag_doubles(a.B);
+  alignas(64) CUtensorMap mt, md, my, mp;
+  if (!(make_rows_map(&mt, a.t, a.B, a.N, a.stride, kMixSeg, false) && make_rows_map(&md, a.diag, a.B, a.N, a.stride, kMixSeg, false) &&
+        make_rows_map(&my, a.y, a.B, a.N, a.stride, kMixSeg, false) && make_rows_map(&mp, a.t, a.B, a.N, a.stride, 2, false)))
+    return cudaSuccess;
+  cudaError_t e = cudaMemsetAsync(any_flag, 0, sizeof(int), stream);
+  if (e != cudaSuccess) return e;
+  BatchArgs f{};
+  f.B = a.B; f.N = a.N; f.stride = a.stride; f.Jr = a.Jr; f.Jc = a.Jc; f.Jg = 0; f.ckpt_seg = kMixSeg;
+  f.coeffs = a.coeffs; f.coeff_stride = a.coeff_stride;
+  f.t = a.t; f.diag = a.diag; f.y = a.y;
+  f.out_logdet = a.out_logdet; f.out_quad = a.out_quad; f.out_half = a.out_val; f.status = a.status;
+  f.ckpt = region; f.flags = flags; f.any_flag = any_flag;
+  bool fwd = false;
+  e = launch_loglik_lockstep_ckpt(f, stream, &fwd);
+  if (e != cudaSuccess || !fwd) return e;
+  const int key = a.Jc * 8 + a.Jr;
+  switch (key) {
+    case 0 * 8 + 1: e = launch_mixed_reverse<0, 1>(a, region, mt, md, my, mp, stream); break;
+    case 0 * 8 + 2: e = launch_mixed_reverse<0, 2>(a, region, mt, md, my, mp, stream); break;
+    case 0 * 8 + 3: e = launch_mixed_reverse<0, 3>(a, region, mt, md, my, mp, stream); break;
+    case 0 * 8 + 4: e = launch_mixed_reverse<0, 4>(a, region, mt, md, my, mp, stream); break;
+    case 1 * 8 + 1: e = launch_mixed_reverse<1, 1>(a, region, mt, md, my, mp, stream); break;
+    case 1 * 8 + 2: e = launch_mixed_reverse<1, 2>(a, region, mt, md, my, mp, stream); break;
+    default: return cudaErrorInvalidValue;
+  }
+  if (e != cudaSuccess) return e;
+  // any series flagged: the cooperative kernel redoes the batch with its guarded arithmetic (it leaves at once otherwise)
+  GradArgs r = a;
+  r.run_if = any_flag; r.scratch = region; r.seg = grad_default_segment(a.N);
+  e = launch_grad_coop(r, stream);
+  if (e != cudaSuccess) return e;
+  if (launches) *launches += 3;
   *used = true;
   return cudaSuccess;
 }

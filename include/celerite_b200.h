@@ -161,8 +161,9 @@ int cel_batched_log_likelihood_ragged(cel_solver* s, int64_t B, int N, int64_t s
 
 /* Same sweep plus the reverse-mode gradient (solver.cpp:347-463 per series).
  * out_val[b] = -0.5*(quad+logdet) (no constant), out_grad[b*P + k], P = 1+2Jr+4Jc.
- * One or two complex terms (Jr = 0, Jc <= 2) take the thread-per-series two-kernel form (forward sweep
- * leaving checkpoints, reverse sweep over them); everything else the cooperative kernel.  The handle's
+ * One or two complex terms (Jr = 0, Jc <= 2), and real + complex terms with Jr + 2 Jc <= 4 in batches of >= 2,048
+ * series, take the thread-per-series two-kernel form (forward sweep leaving checkpoints, reverse sweep over
+ * them); everything else the cooperative kernel.  The handle's
  * scratch grows with the batch (checkpoints: 10 bytes per point at J = 2, 56 at J = 4, at most ~12 GB
  * at a time; larger batches go through in pieces). */
 int cel_batched_grad_log_likelihood(cel_solver* s, int64_t B, int N, int64_t stride,

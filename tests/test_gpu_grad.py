@@ -286,3 +286,62 @@ def test_batched_grad_with_one_coefficient_row_for_all(B, N, Jc, device):
         vref += 0.5 * np.pi * np.log(N)
         assert rel_sum(val[i], vref, N) < RTOL_SCALAR
         assert rel_grad(g[i], gref) < RTOL_GRAD, (i, g[i], gref)
+
+
+@pytest.mark.parametrize("B,N,Jr,Jc", [(2100, 300, 1, 1), (2500, 202, 2, 1), (2200, 150, 1, 0), (2300, 100, 2, 0),
+                                       (2050, 90, 3, 0), (2100, 124, 4, 0)])
+def test_batched_grad_with_real_terms_thread_per_series(B, N, Jr, Jc):
+    """Real + complex terms with J <= 4 (RealTerm + ComplexTerm is BASELINE config 1's kernel) in batches of
+    thousands take the two-kernel thread-per-series gradient over arrays (lockstep_grad2.cu, launch_grad_mixed:
+    forward with checkpoints, reverse, and a redo pass that leaves at once): 3 launches, every checked series
+    against the reference's AD; from host arrays as well."""
+    import torch
+    from celerite_b200 import synth
+    from celerite_b200.batched import BatchedSolver
+    b = synth.make_batch(B, N, Jr, Jc, seed=3 * B + N)
+    dev = torch.device("cuda:0")
+    tt = lambda a: torch.from_numpy(a).to(dev)  # noqa: E731
+    bs = BatchedSolver()
+    n0 = bs._lib.cel_launch_count(bs._h)
+    val, g, status = bs.grad_log_likelihood(tt(b["coeffs"]), tt(b["t"]), tt(b["diag"]), tt(b["y"]), Jr, Jc)
+    torch.cuda.synchronize()
+    assert bs._lib.cel_launch_count(bs._h) - n0 == 3
+    val, g, status = val.cpu().numpy(), g.cpu().numpy(), status.cpu().numpy()
+    hv, hg, hs = bs.grad_log_likelihood(b["coeffs"], b["t"], b["diag"], b["y"], Jr, Jc)
+    assert np.all(status == 0) and np.all(hs == 0)
+    assert np.allclose(hv, val, rtol=1e-13) and np.allclose(hg, g, rtol=1e-10, atol=1e-10)
+    chk = oracle.best()
+    for i in sorted(set(list(range(0, B, B // 7)) + [B - 1])):
+        j, ar, cr, ac, bc, cc, dc = synth.split_row(b["coeffs"][i], Jr, Jc)
+        p = oracle.Problem(j, ar, cr, ac, bc, cc, dc, b["t"][i], b["diag"][i])
+        st, vref, gref = chk.grad(p, b["y"][i])
+        vref += 0.5 * np.pi * np.log(N)
+        assert rel_sum(val[i], vref, N) < RTOL_SCALAR
+        assert rel_grad(g[i], gref) < RTOL_GRAD, (i, g[i], gref)
+
+
+def test_batched_grad_with_real_terms_redoes_the_batch_when_a_series_leaves_the_fast_path():
+    """One series with a negative pivot among 2,100: the forward kernel flags it, the cooperative kernel redoes the
+    batch (guarded arithmetic, the reference's failure semantics): status 3 and NaN there, everything else right."""
+    import torch
+    from celerite_b200 import synth
+    from celerite_b200.batched import BatchedSolver
+    B, N, Jr, Jc = 2100, 160, 1, 1
+    b = synth.make_batch(B, N, Jr, Jc, seed=4)
+    bad = 1234
+    b["diag"][bad, 77] = -60.0
+    dev = torch.device("cuda:0")
+    tt = lambda a: torch.from_numpy(a).to(dev)  # noqa: E731
+    bs = BatchedSolver()
+    val, g, status = bs.grad_log_likelihood(tt(b["coeffs"]), tt(b["t"]), tt(b["diag"]), tt(b["y"]), Jr, Jc)
+    val, g, status = val.cpu().numpy(), g.cpu().numpy(), status.cpu().numpy()
+    assert status[bad] == 3 and np.isnan(val[bad]) and np.all(np.isnan(g[bad]))
+    assert status.sum() == 3
+    chk = oracle.best()
+    for i in (0, bad - 1, bad + 1, B - 1):
+        j, ar, cr, ac, bc, cc, dc = synth.split_row(b["coeffs"][i], Jr, Jc)
+        p = oracle.Problem(j, ar, cr, ac, bc, cc, dc, b["t"][i], b["diag"][i])
+        st, vref, gref = chk.grad(p, b["y"][i])
+        vref += 0.5 * np.pi * np.log(N)
+        assert rel_sum(val[i], vref, N) < RTOL_SCALAR
+        assert rel_grad(g[i], gref) < RTOL_GRAD, (i, g[i], gref)
