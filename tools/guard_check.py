@@ -18,7 +18,8 @@ def intact(h, what):
     assert rc == 1, "guard band touched (or CEL_DEBUG_GUARD not set): %s -> %d" % (what, rc)
 
 
-for (B, N, Jr, Jc) in [(70, 404, 0, 1), (5, 2002, 0, 1), (33, 18, 0, 1), (6, 8192, 0, 3), (3, 4200, 1, 1), (9, 300, 0, 2)]:
+for (B, N, Jr, Jc) in [(70, 404, 0, 1), (5, 2002, 0, 1), (33, 18, 0, 1), (6, 8192, 0, 3), (3, 4200, 1, 1), (9, 300, 0, 2),
+                       (2100, 100, 1, 1), (2090, 62, 2, 1), (2500, 50, 0, 2)]:
     b = synth.make_batch(B, N, Jr, Jc, seed=B + N)
     out = bs.grad_log_likelihood(tt(b["coeffs"]), tt(b["t"]), tt(b["diag"]), tt(b["y"]), Jr, Jc)
     torch.cuda.synchronize()
