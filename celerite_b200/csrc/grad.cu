@@ -47,7 +47,6 @@ struct GradCfg {
   // and config 3 (1,024 series) wants all of them resident at once -- 7 per SM -- instead of a second, nearly
   // empty wave.  Tiles of 8 steps and ring slots of the packed triangle (not J x J) keep J = 32 at 31 KB.
   static constexpr int T = JP >= 24 ? 8 : 16;
-  static constexpr int JJ = JP * JP;
   // The J x J blocks of the records (P_n on the tape, S in a checkpoint) are symmetric: only the upper
   // triangle is kept, packed by columns (entry (k, j), k <= j, at j(j+1)/2 + k; lanes 0..j write column j
   // as one coalesced row).  At J = 32 the tape was 8.7 KB per step and bound the kernel (1.7 TB of DRAM
@@ -127,7 +126,7 @@ __global__ void __launch_bounds__(kWarp) k_grad_coop(GradArgs a) {
   double* v_s = u_s + T * JP;
   double* ut_s = v_s + T * JP;           // [T][JP] phi o u
   double* x_s = ut_s + T * JP;           // [2][2*JP]
-  double* p_s = x_s + 4 * JP;            // [RD][JJ]
+  double* p_s = x_s + 4 * JP;            // [RD][BLK]: ring of packed tape blocks
   double* cf_s = p_s + C::kP;
   double* r_s = cf_s + C::kCoef;         // [6][JP]
   double* m_s = r_s + C::kR;             // [JP][JP] M, entry (j, c) at j*JP + c (lane c owns column c)
